@@ -1,0 +1,198 @@
+"""ctypes loader for oracle/_build/libpbe_oracle.so (the C restatement of the reference).
+
+TEST INFRASTRUCTURE ONLY -- imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs; never by the product package `openpbe_b200`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "_build", "libpbe_oracle.so")
+
+COAL_NONE, COAL_CONSTANT, COAL_CT, COAL_TABLE = 0, 1, 2, 3
+BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
+DAUGHTER_UNIFORM_BINARY = 0
+
+_dp = C.POINTER(C.c_double)
+
+
+class KernelSpec(C.Structure):
+    _fields_ = [
+        ("coalescence", C.c_int),
+        ("coal_c", C.c_double * 4),
+        ("breakup", C.c_int),
+        ("br_c", C.c_double * 4),
+        ("daughter", C.c_int),
+        ("coal_div_vcell", C.c_int),
+        ("coal_table", _dp),
+        ("br_table", _dp),
+    ]
+
+
+def build(force: bool = False) -> str:
+    """Compile the oracle with the committed Makefile (gcc only)."""
+    src = os.path.join(_HERE, "pbe_oracle.c")
+    if (force or not os.path.exists(_LIB_PATH)
+            or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(src),
+                                                 os.path.getmtime(os.path.join(_HERE, "pbe_oracle.h")))):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        build()
+    L = C.CDLL(_LIB_PATH)
+    d, i, i64 = C.c_double, C.c_int, C.c_int64
+    L.orc_coal_ct.restype = d
+    L.orc_coal_ct.argtypes = [d] * 10 + [i]
+    L.orc_coal_constant.restype = d
+    L.orc_coal_constant.argtypes = [d]
+    L.orc_coal_none.restype = d
+    L.orc_break_ct.restype = d
+    L.orc_break_ct.argtypes = [d] * 7
+    L.orc_break_binary.restype = d
+    L.orc_break_binary.argtypes = [d]
+    L.orc_break_none.restype = d
+    L.orc_break_none.argtypes = [d]
+    L.orc_daughter_beta.restype = d
+    L.orc_daughter_beta.argtypes = [d, d]
+    L.orc_daughter_moment.restype = d
+    L.orc_daughter_moment.argtypes = [d, i]
+    L.orc_moc_source.restype = i
+    L.orc_moc_source.argtypes = [C.POINTER(KernelSpec), i, d, d, i64, i64, _dp, _dp, _dp, _dp, _dp, d,
+                                 _dp, _dp, _dp, _dp, i]
+    L.orc_moc_update.restype = None
+    L.orc_moc_update.argtypes = [i, i64, i64, _dp, _dp, d]
+    L.orc_moc_d.restype = None
+    L.orc_moc_d.argtypes = [i, d, i64, i64, _dp, _dp]
+    L.orc_moc_continuity.restype = d
+    L.orc_moc_continuity.argtypes = [i, d, i64, i64, _dp, _dp, _dp, _dp]
+    L.orc_wheeler.restype = None
+    L.orc_wheeler.argtypes = [i, _dp, _dp, _dp]
+    L.orc_tridiag_eig_firstrow.restype = i
+    L.orc_tridiag_eig_firstrow.argtypes = [i, _dp, _dp, _dp]
+    L.orc_qmom_source.restype = i
+    L.orc_qmom_source.argtypes = [C.POINTER(KernelSpec), i, i64, i64, _dp, _dp, _dp, _dp, _dp, _dp,
+                                  _dp, i, i]
+    L.orc_qmom_update.restype = None
+    L.orc_qmom_update.argtypes = [i, i64, i64, _dp, _dp, d, _dp]
+    L.orc_integrate_exp_neg.restype = d
+    L.orc_integrate_exp_neg.argtypes = [d]
+    L.orc_max_threads.restype = i
+    _lib = L
+    return L
+
+
+def _p(a):
+    if a is None:
+        return None
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_dp)
+
+
+def make_spec(coalescence="noCoalescence", coal_coeffs=(), breakup="noBreakup", br_coeffs=(),
+              coal_div_vcell=False, coal_table=None, br_table=None) -> KernelSpec:
+    """Kernel selection by the reference's TypeNames (coalescenceKernel.C:46-71 etc.)."""
+    cmap = {"noCoalescence": COAL_NONE, "constantCoalescence": COAL_CONSTANT,
+            "CoulaloglouTavlaridesC": COAL_CT, "table": COAL_TABLE}
+    bmap = {"noBreakup": BR_NONE, "binaryBreakup": BR_BINARY, "CoulaloglouTavlarides": BR_CT,
+            "table": BR_TABLE}
+    s = KernelSpec()
+    s.coalescence = cmap[coalescence]
+    s.breakup = bmap[breakup]
+    for k, v in enumerate(coal_coeffs):
+        s.coal_c[k] = float(v)
+    for k, v in enumerate(br_coeffs):
+        s.br_c[k] = float(v)
+    s.daughter = DAUGHTER_UNIFORM_BINARY
+    s.coal_div_vcell = int(bool(coal_div_vcell))
+    s._keep = (coal_table, br_table)
+    s.coal_table = _p(coal_table)
+    s.br_table = _p(br_table)
+    return s
+
+
+def moc_source(spec, N, xi1, relax, n, eps, rho, nu, dt, vcell=None, nthreads=1, want_parts=False):
+    """n: float64 [N, ncells] class-major.  Returns (S, scale[, coal, br])."""
+    n = np.ascontiguousarray(n, dtype=np.float64)
+    assert n.shape[0] == N
+    ncells = n.shape[1]
+    S = np.empty_like(n)
+    scale = np.empty_like(n)
+    coal = np.empty_like(n) if want_parts else None
+    br = np.empty_like(n) if want_parts else None
+    rc = lib().orc_moc_source(C.byref(spec), N, xi1, relax, ncells, ncells, _p(n), _p(eps), _p(rho),
+                              _p(nu), _p(vcell), dt, _p(S), _p(scale), _p(coal), _p(br), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"orc_moc_source failed: {rc}")
+    return (S, scale, coal, br) if want_parts else (S, scale)
+
+
+def moc_update(n, S, dt):
+    N, ncells = n.shape
+    lib().orc_moc_update(N, ncells, ncells, _p(n), _p(S), dt)
+
+
+def moc_d(n, xi1):
+    N, ncells = n.shape
+    d = np.empty(ncells)
+    lib().orc_moc_d(N, xi1, ncells, ncells, _p(n), _p(d))
+    return d
+
+
+def moc_continuity(n, xi1, alpha, vcell):
+    N, ncells = n.shape
+    err = np.empty(ncells)
+    mx = lib().orc_moc_continuity(N, xi1, ncells, ncells, _p(n), _p(alpha), _p(vcell), _p(err))
+    return mx, err
+
+
+def wheeler(m):
+    m = np.ascontiguousarray(m, dtype=np.float64)
+    order = m.size // 2
+    x = np.empty(order)
+    w = np.empty(order)
+    lib().orc_wheeler(order, _p(m), _p(x), _p(w))
+    return x, w
+
+
+def tridiag_eig_firstrow(d, e):
+    n = len(d)
+    dd = np.array(d, dtype=np.float64)
+    ee = np.zeros(n)
+    ee[: n - 1] = e
+    z = np.empty(n)
+    rc = lib().orc_tridiag_eig_firstrow(n, _p(dd), _p(ee), _p(z))
+    return rc, dd, z
+
+
+def qmom_source(spec, order, m, eps, rho, nu, vcell=None, reference_shaped=False, nthreads=1):
+    m = np.ascontiguousarray(m, dtype=np.float64)
+    assert m.shape[0] == 2 * order
+    ncells = m.shape[1]
+    S = np.empty_like(m)
+    scale = np.empty_like(m)
+    rc = lib().orc_qmom_source(C.byref(spec), order, ncells, ncells, _p(m), _p(eps), _p(rho), _p(nu),
+                               _p(vcell), _p(S), _p(scale), int(reference_shaped), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"orc_qmom_source failed: {rc}")
+    return S, scale
+
+
+def qmom_update(m, S, dt, want_d=True):
+    nm, ncells = m.shape
+    d = np.empty(ncells) if want_d else None
+    lib().orc_qmom_update(nm // 2, ncells, ncells, _p(m), _p(S), dt, _p(d))
+    return d

@@ -1,0 +1,113 @@
+/*
+ * pbe_oracle.h -- CPU restatement of OpenPBE's per-cell population-balance source path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it,
+ * and there only as the checker / the timed CPU baseline.  The product (libpbe_b200.so) never
+ * links, loads or calls this file and has no CPU fallback.
+ *
+ * Parity status: the reference (robertsawko/OpenPBE) cannot be compiled here -- every source
+ * file on the path includes OpenFOAM headers and MomentInversion.C needs Eigen3; neither is in
+ * the image.  This restatement is therefore pinned on the reference's own
+ * golden vectors: tests/unit_tests/breakup.cpp:6-59, coalescence.cpp:6-78,
+ * moment_inversion.cpp:15-49, integration.cpp:6-13, and on the 0-D analytical solutions of
+ * tests/integration/MOC/testConvergence.py:10-47 (tests/test_oracle_*.py).  The Eigen
+ * SelfAdjointEigenSolver call (MomentInversion.C:46-48; Eigen3 un-vendored, unpinned) is
+ * restated as an implicit-shift QL iteration on the symmetric tridiagonal Jacobi matrix and
+ * cross-checked against numpy.linalg.eigh.  The GSL QAGIU call (Integrator.H:21-22; GSL
+ * un-vendored, unpinned) is restated from the published QUADPACK algorithm (15-point
+ * Gauss-Kronrod on the (0,1] transform with adaptive bisection).
+ *
+ * All citations are file:line relative to the reference root.
+ */
+#ifndef PBE_ORACLE_H
+#define PBE_ORACLE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* kernel selectors: names follow the reference TypeNames */
+enum { ORC_COAL_NONE = 0, ORC_COAL_CONSTANT = 1, ORC_COAL_CT = 2, ORC_COAL_TABLE = 3 };
+enum { ORC_BR_NONE = 0, ORC_BR_BINARY = 1, ORC_BR_CT = 2, ORC_BR_TABLE = 3 };
+enum { ORC_DAUGHTER_UNIFORM_BINARY = 0 };
+
+typedef struct {
+    int coalescence;     /* ORC_COAL_* */
+    double coal_c[4];    /* constant: c[0]; CT: c1, c2, gamma, sigma */
+    int breakup;         /* ORC_BR_* */
+    double br_c[4];      /* CT: c1, c2, gamma, sigma */
+    int daughter;        /* ORC_DAUGHTER_* */
+    int coal_div_vcell;  /* 1 = historical "/ Vcell" variant (the stale golden of
+                            tests/unit_tests/coalescence.cpp:61-63); HEAD = 0 */
+    const double *coal_table; /* ORC_COAL_TABLE: [N][N] cell-independent S(xi_i, xi_j) */
+    const double *br_table;   /* ORC_BR_TABLE:   [N]    cell-independent g(xi_i)       */
+} orc_kernel_spec;
+
+/* ---- scalar kernels (the reference's Foam-free *Impl functors) ---------------------- */
+double orc_coal_ct(double c1, double c2, double gamma, double sigma, double xi1, double xi2,
+                   double eps, double rhoc, double nuc, double vcell, int div_vcell);
+double orc_coal_constant(double c);
+double orc_coal_none(void);
+double orc_break_ct(double c1, double c2, double gamma, double sigma, double xi, double rho_d,
+                    double eps);
+double orc_break_binary(double xi);
+double orc_break_none(double xi);
+double orc_daughter_beta(double xi1, double xi2);
+double orc_daughter_moment(double xi, int k);
+
+/* ---- method of classes -------------------------------------------------------------- */
+/* Fields are class-major SoA: n[i*stride + c], i < N, c < ncells (one contiguous field per
+ * class, as MOC.H:66).  S receives max(C_i + B_i, -relax n_i/dt) (MOC.C:87-91).  scale (may
+ * be NULL) receives sum|terms| of every product that entered S_i: the parity tolerance base.
+ * coal_only / br_only (may be NULL) receive C_i and B_i before the limiter.  vcell may be
+ * NULL (only read when spec->coal_div_vcell).  nthreads <= 1: the reference's single thread. */
+int orc_moc_source(const orc_kernel_spec *spec, int N, double xi1, double relax, int64_t ncells,
+                   int64_t stride, const double *n, const double *eps, const double *rho,
+                   const double *nu, const double *vcell, double dt, double *S, double *scale,
+                   double *coal_only, double *br_only, int nthreads);
+/* zero-flux explicit update, MOC.C:259-272 with phi = 0: n_k += dt S_k */
+void orc_moc_update(int N, int64_t ncells, int64_t stride, double *n, const double *S, double dt);
+/* number-mean diameter, MOC.C:282-290 */
+void orc_moc_d(int N, double xi1, int64_t ncells, int64_t stride, const double *n, double *d);
+/* continuity check MOC.C:254-279: err[c] = | sum_k xi_k n_k / V - alpha | ; returns max */
+double orc_moc_continuity(int N, double xi1, int64_t ncells, int64_t stride, const double *n,
+                          const double *alpha, const double *vcell, double *err);
+
+/* ---- Wheeler inversion (MomentInversion.C:9-51) -------------------------------------- */
+/* order = number of nodes; m has 2*order entries; x ascending, w = m0 * v0^2 */
+void orc_wheeler(int order, const double *m, double *x, double *w);
+/* symmetric tridiagonal eigen-solve: diag d[n], off-diag in e[0..n-2] (e must have n slots,
+ * the last is scratch); on exit d ascending and
+ * z[i] = first component of the i-th normalised eigenvector.  Returns 0, or 1 when the
+ * iteration limit was hit / the input was not finite (outputs are then NaN). */
+int orc_tridiag_eig_firstrow(int n, double *d, double *e, double *z);
+
+/* ---- QMOM (QMOM.C:215-267, 98-128) ---------------------------------------------------- */
+/* m[k*stride + c], k < 2*order.  S[k*stride + c] = coalescence + breakup moment source (NOT yet
+ * NaN-scrubbed).  scale as above.  reference_shaped != 0 recomputes the inversion for every
+ * k exactly as QMOM.C:231 does (timed baseline); 0 inverts once per cell (same results). */
+int orc_qmom_source(const orc_kernel_spec *spec, int order, int64_t ncells, int64_t stride,
+                    const double *m, const double *eps, const double *rho, const double *nu,
+                    const double *vcell, double *S, double *scale, int reference_shaped,
+                    int nthreads);
+/* NaN -> 0 scrub (QMOM.C:101-107), m += dt S (QMOM.C:193-197 with phi = 0), clamp to SMALL
+ * (QMOM.C:117-123), d = (6/pi m1/m0)^(1/3) (QMOM.C:125).  d may be NULL. */
+void orc_qmom_update(int order, int64_t ncells, int64_t stride, double *m, double *S, double dt,
+                     double *d);
+
+/* ---- semi-infinite integral (Integrator.H:12-27) -------------------------------------- */
+typedef double (*orc_integrand)(double x, void *params);
+double orc_integrate_qagiu(orc_integrand f, void *params, double lower, double epsabs,
+                           double epsrel, int limit, double *abserr, int *neval);
+/* convenience for tests: integral of exp(-x) from `lower` (tests/unit_tests/integration.cpp) */
+double orc_integrate_exp_neg(double lower);
+
+int orc_max_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
