@@ -1,0 +1,199 @@
+/*
+ * pbe_b200.h -- C ABI of libpbe_b200.so, the B200 (sm_100a) population-balance source engine.
+ *
+ * This is the drop-in boundary for the per-cell hot path of robertsawko/OpenPBE: what an
+ * OpenFOAM-side `libPBE.so` adapter binds instead of running the reference's
+ * CPU loops.  Plain pointers and sizes only; every function returns 0 on success or a
+ * PBE_E_* code, with a per-thread message behind pbe_last_error().  There is NO CPU fallback:
+ * every compute entry point launches sm_100a kernels and fails with PBE_E_CUDA without a device.
+ *
+ * Field layout (device and host entry points alike): class-major / moment-major
+ * structure-of-arrays FP64, `f[k*stride + c]`, cell index fastest -- the layout of the
+ * reference's PtrList<volScalarField> (src/PBESystem/MOC.H:66, QMOM.H:62) so an adapter
+ * stages OpenFOAM fields without transposition.
+ *
+ * Citations are file:line relative to the reference root.
+ */
+#ifndef PBE_B200_H
+#define PBE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PBE_B200_VERSION 100 /* 0.1.0 */
+
+/* ---- status codes (reference convention: FatalErrorIn(...) << exit(FatalError),
+ * PBEMethod.C:97-105; the adapter turns a non-zero status into FatalErrorIn) ------------- */
+enum {
+    PBE_OK = 0,
+    PBE_E_INVALID = 1,   /* bad argument (NULL handle, N < 1, stride < ncells, ...) */
+    PBE_E_UNKNOWN_TYPE = 2, /* unknown kernel / method TypeName (coalescenceKernel.C:57-65) */
+    PBE_E_CUDA = 3,      /* CUDA runtime error or no device: message has the cudaError string */
+    PBE_E_UNSUPPORTED = 4, /* valid request outside the device path's limits (e.g. N too big) */
+    PBE_E_NOMEM = 5
+};
+
+/* ---- run-time selectable kernels.  Values follow the reference TypeNames:
+ * coalescenceKernel <- noCoalescence | constantCoalescence | CoulaloglouTavlaridesC
+ *   (coalescenceKernels/{noCoalescence.H:49-52, constantCoalescence.H:51-54,
+ *    CoulaloglouTavlarides.C:69-90}),
+ * breakupKernel <- noBreakup | binaryBreakup | CoulaloglouTavlarides
+ *   (breakupKernels/{noBreakup.C:51-54, binaryBreakup.C:51-53, CoulaloglouTavlarides.C:77-93}),
+ * daughterParticleDistribution <- uniformBinaryBreakup
+ *   (daughterParticleDistributions/uniformBinaryBreakup.C:55-69).
+ * *_TABLE is the plug-in path for user kernels that do not depend on the cell
+ * (coalescenceKernel.H:85-90 virtual S()): the host evaluates the user functor once per
+ * class pair / class and uploads the table (MOC only). */
+enum { PBE_COAL_NONE = 0, PBE_COAL_CONSTANT = 1, PBE_COAL_CT = 2, PBE_COAL_TABLE = 3 };
+enum { PBE_BR_NONE = 0, PBE_BR_BINARY = 1, PBE_BR_CT = 2, PBE_BR_TABLE = 3 };
+enum { PBE_DAUGHTER_UNIFORM_BINARY = 0 };
+
+typedef struct pbe_kernel_spec {
+    int coalescence;          /* PBE_COAL_* */
+    double coal_c[4];         /* constant: c[0] (dict key `constant`); CT: c1, c2, gamma, sigma */
+    int breakup;              /* PBE_BR_* */
+    double br_c[4];           /* CT: c1, c2, gamma, sigma */
+    int daughter;             /* PBE_DAUGHTER_* */
+    const double *coal_table; /* PBE_COAL_TABLE: HOST [N][N], S(xi_i, xi_j); may be asymmetric */
+    const double *br_table;   /* PBE_BR_TABLE:   HOST [N],    g(xi_i) */
+} pbe_kernel_spec;
+
+/* TypeName -> enum, as the reference's run-time selection tables do.  Unknown names return
+ * PBE_E_UNKNOWN_TYPE and pbe_last_error() lists the valid ones (PBEMethod.C:97-105). */
+int pbe_coalescence_type(const char *type_name, int *out);
+int pbe_breakup_type(const char *type_name, int *out);
+int pbe_daughter_type(const char *type_name, int *out);
+
+const char *pbe_last_error(void);
+int pbe_version(void);
+
+/* ---- context: one per (process, device).  Owns streams, staging buffers, workspaces. --- */
+typedef struct pbe_ctx pbe_ctx;
+int pbe_ctx_create(int device, pbe_ctx **out);
+int pbe_ctx_destroy(pbe_ctx *ctx);
+/* name / SM count / bytes of HBM of the context's device */
+int pbe_ctx_info(pbe_ctx *ctx, char *name, int name_len, int *sm_count, int64_t *hbm_bytes);
+/* count of this library's kernel launches since the context was created (bench `gpu_launches`) */
+int64_t pbe_ctx_launch_count(pbe_ctx *ctx);
+/* Roofline denominator not in MEASURED_PEAKS.json: a register-resident DFMA-chain kernel,
+ * timed with CUDA events.  Returns TFLOP/s (2 flops per DFMA). */
+int pbe_measure_fp64_peak(pbe_ctx *ctx, double *tflops, double *ms);
+
+/* ======================================================================================= */
+/* Method of classes -- replaces MOC::correct()'s source path, src/PBESystem/MOC.C:87-184   */
+/* ======================================================================================= */
+typedef struct pbe_moc pbe_moc;
+
+/* MOCCoeffs{numberOfClasses, xi1, sourceRelaxation} (MOC.C:49-83): xi_i = xi1 (i+1). */
+int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
+                   double source_relaxation, pbe_moc **out);
+int pbe_moc_destroy(pbe_moc *moc);
+
+/* Optional fused outputs of one MOC launch; every pointer is a DEVICE pointer or NULL. */
+typedef struct pbe_moc_io {
+    const double *alpha;  /* [ncells] phase fraction: continuity check (MOC.C:254-279) */
+    const double *vcell;  /* [ncells] cell volumes (continuity check, global moments) */
+    double *S;            /* [N][stride] limited source max(C+B, -relax n/dt)  (MOC.C:87-91) */
+    double *d;            /* [ncells] number-mean diameter of the (updated) n   (MOC.C:282-290) */
+    double *moments;      /* [n_moments] += sum_c V_c sum_i xi_i^k n_i[c] (partial: this rank) */
+    int n_moments;        /* <= 8 */
+    double *cont_err_max; /* [1] max_c | sum_k xi_k n_k / V - alpha |  (MOC.C:276-279); caller
+                             zeroes it */
+} pbe_moc_io;
+
+/* S = limited source of the CURRENT n (read-only).  a1-a4 of SURVEY.md section 8. */
+int pbe_moc_source(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n,
+                   const double *eps, const double *rho, const double *nu, double dt, double *S,
+                   void *cuda_stream);
+/* One zero-flux explicit step in place: n_k += dt S_k (MOC.C:259-272 with phi = 0), plus the
+ * fused outputs requested in io (may be NULL). */
+int pbe_moc_step(pbe_moc *moc, int64_t ncells, int64_t stride, double *n, const double *eps,
+                 const double *rho, const double *nu, double dt, const pbe_moc_io *io,
+                 void *cuda_stream);
+/* d[c] = sum_i (6 xi_i/pi)^(1/3) n_i / sum_i n_i   (MOC.C:282-290, 43-45) */
+int pbe_moc_d(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n, double *d,
+              void *cuda_stream);
+/* per-class global min / max over cells (MOC.C:181-183, 238): out_min/out_max DEVICE [N] */
+int pbe_moc_class_minmax(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n,
+                         double *out_min, double *out_max, void *cuda_stream);
+
+/* HOST-buffer entry point: what the OpenFOAM adapter calls from MOC::correct().  Copies the
+ * fields host->device in cell chunks, runs pbe_moc_source per chunk, copies S back; copies and
+ * kernels of successive chunks overlap on the context's streams.  Synchronous on return.
+ * Pinned host memory (pbe_host_alloc) gives full PCIe rate; pageable memory works. */
+int pbe_moc_source_host(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n_host,
+                        const double *eps_host, const double *rho_host, const double *nu_host,
+                        double dt, double *S_host);
+
+/* ======================================================================================= */
+/* QMOM -- replaces QMOM::correct()'s source path, src/PBESystem/QMOM.C:85-129, 215-267,    */
+/* and wheeler_inversion(), src/PBESystem/MomentInversion.C:9-51                            */
+/* ======================================================================================= */
+typedef struct pbe_qmom pbe_qmom;
+#define PBE_QMOM_MAX_ORDER 4 /* QMOMCoeffs.quadratureOrder 1..4 (tests/integration/QMOM/setupCases.py:92) */
+
+int pbe_qmom_create(pbe_ctx *ctx, int order, const pbe_kernel_spec *spec, pbe_qmom **out);
+int pbe_qmom_destroy(pbe_qmom *q);
+
+/* S[k][c] for k < 2*order, NOT NaN-scrubbed (as momentSourceTerm returns it, QMOM.C:215-267).
+ * The inversion is done once per cell and reused for every k. */
+int pbe_qmom_source(pbe_qmom *q, int64_t ncells, int64_t stride, const double *m,
+                    const double *eps, const double *rho, const double *nu, double *S,
+                    void *cuda_stream);
+/* NaN->0 scrub (QMOM.C:101-107), m_k += dt S_k (QMOM.C:193-197 with phi = 0), clamp to SMALL =
+ * 1e-15 (QMOM.C:117-123), d = (6/pi m1/m0)^(1/3) (QMOM.C:125).  S (scrubbed) and d optional. */
+int pbe_qmom_step(pbe_qmom *q, int64_t ncells, int64_t stride, double *m, const double *eps,
+                  const double *rho, const double *nu, double dt, double *S, double *d,
+                  void *cuda_stream);
+/* batched wheeler_inversion: m [2*order][stride] -> x, w [order][stride]; x ascending. */
+int pbe_wheeler_batch(pbe_ctx *ctx, int order, int64_t ncells, int64_t stride, const double *m,
+                      double *x, double *w, void *cuda_stream);
+int pbe_qmom_source_host(pbe_qmom *q, int64_t ncells, int64_t stride, const double *m_host,
+                         const double *eps_host, const double *rho_host, const double *nu_host,
+                         double *S_host);
+
+/* ======================================================================================= */
+/* Scalar kernel functors evaluated ON THE DEVICE (batched) -- the reference's Foam-free     */
+/* *Impl::S surface (coalescenceKernels/CoulaloglouTavlarides.H:44-63, breakupKernels/       */
+/* CoulaloglouTavlarides.H:46-60; exported to Python by bindings/kernels.cpp:9-40).          */
+/* All arrays are HOST pointers of length count; results come back in out[].                 */
+/* ======================================================================================= */
+int pbe_eval_coalescence(pbe_ctx *ctx, const pbe_kernel_spec *spec, int64_t count,
+                         const double *xi1, const double *xi2, const double *eps,
+                         const double *rho, const double *nu, double *out);
+int pbe_eval_breakup(pbe_ctx *ctx, const pbe_kernel_spec *spec, int64_t count, const double *xi,
+                     const double *rho, const double *eps, double *out);
+/* beta(xi1, xi2) and moment(xi, k) of the daughter distribution */
+int pbe_eval_daughter_beta(pbe_ctx *ctx, int daughter, int64_t count, const double *xi1,
+                           const double *xi2, double *out);
+int pbe_eval_daughter_moment(pbe_ctx *ctx, int daughter, int64_t count, const double *xi,
+                             const int *k, double *out);
+/* integrate(f, lower) of Integrator.H:12-27 for the integrand family the reference's test
+ * pins (tests/unit_tests/integration.cpp:6-13): f(x) = exp(-rate x).  Device 15-point
+ * Gauss-Kronrod on the QAGIU transform with fixed-depth bisection, one thread per integral. */
+int pbe_eval_integrate_exp(pbe_ctx *ctx, int64_t count, const double *rate, const double *lower,
+                           double *out);
+
+/* ---- global diagnostics, Utility.C:4-10 printAvgMaxMin: out[0] = sum(f V), out[1] = sum V,
+ * out[2] = max f, out[3] = min f over this rank's cells (DEVICE out[4]); the caller
+ * all-reduces (sum, sum, max, min) across ranks -- NCCL in bench.py / the replay driver. */
+int pbe_field_avg_max_min(pbe_ctx *ctx, int64_t ncells, const double *f, const double *vcell,
+                          double *out4, void *cuda_stream);
+
+/* ---- memory helpers so a C/C++ host needs no CUDA headers ------------------------------ */
+int pbe_device_alloc(pbe_ctx *ctx, int64_t bytes, void **out);
+int pbe_device_free(pbe_ctx *ctx, void *p);
+int pbe_host_alloc(pbe_ctx *ctx, int64_t bytes, void **out); /* pinned */
+int pbe_host_free(pbe_ctx *ctx, void *p);
+int pbe_memcpy_h2d(pbe_ctx *ctx, void *dst, const void *src, int64_t bytes);
+int pbe_memcpy_d2h(pbe_ctx *ctx, void *dst, const void *src, int64_t bytes);
+int pbe_memset(pbe_ctx *ctx, void *dst, int value, int64_t bytes);
+int pbe_sync(pbe_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PBE_B200_H */

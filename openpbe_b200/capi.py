@@ -1,0 +1,132 @@
+"""ctypes binding of libpbe_b200.so (C ABI: include/pbe_b200.h).
+
+This is plumbing for tests/, bench.py and the Python tools: device memory and streams come from
+PyTorch tensors (`tensor.data_ptr()`), everything that computes is a hand-written sm_100a kernel
+inside the shared library.  There is no CPU fallback: if the library is missing or a call fails
+the error is raised, never papered over.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libpbe_b200.so")
+
+PBE_OK, PBE_E_INVALID, PBE_E_UNKNOWN_TYPE, PBE_E_CUDA, PBE_E_UNSUPPORTED, PBE_E_NOMEM = range(6)
+COAL_NONE, COAL_CONSTANT, COAL_CT, COAL_TABLE = 0, 1, 2, 3
+BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
+DAUGHTER_UNIFORM_BINARY = 0
+QMOM_MAX_ORDER = 4
+
+_dp = C.POINTER(C.c_double)
+_vp = C.c_void_p
+_i64 = C.c_int64
+
+
+class KernelSpec(C.Structure):
+    """struct pbe_kernel_spec"""
+
+    _fields_ = [
+        ("coalescence", C.c_int),
+        ("coal_c", C.c_double * 4),
+        ("breakup", C.c_int),
+        ("br_c", C.c_double * 4),
+        ("daughter", C.c_int),
+        ("coal_table", _dp),
+        ("br_table", _dp),
+    ]
+
+
+class MocIO(C.Structure):
+    """struct pbe_moc_io (device pointers)"""
+
+    _fields_ = [
+        ("alpha", _vp),
+        ("vcell", _vp),
+        ("S", _vp),
+        ("d", _vp),
+        ("moments", _vp),
+        ("n_moments", C.c_int),
+        ("cont_err_max", _vp),
+    ]
+
+
+class PbeError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libpbe_b200 error {code}: {msg}")
+        self.code = code
+        self.message = msg
+
+
+# every exported symbol of include/pbe_b200.h: name -> (restype, argtypes)
+PROTOTYPES = {
+    "pbe_coalescence_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
+    "pbe_breakup_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
+    "pbe_daughter_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
+    "pbe_last_error": (C.c_char_p, []),
+    "pbe_version": (C.c_int, []),
+    "pbe_ctx_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "pbe_ctx_destroy": (C.c_int, [_vp]),
+    "pbe_ctx_info": (C.c_int, [_vp, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(_i64)]),
+    "pbe_ctx_launch_count": (_i64, [_vp]),
+    "pbe_measure_fp64_peak": (C.c_int, [_vp, _dp, _dp]),
+    "pbe_moc_create": (C.c_int, [_vp, C.c_int, C.c_double, C.POINTER(KernelSpec), C.c_double,
+                                 C.POINTER(_vp)]),
+    "pbe_moc_destroy": (C.c_int, [_vp]),
+    "pbe_moc_source": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),
+    "pbe_moc_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, C.POINTER(MocIO),
+                               _vp]),
+    "pbe_moc_d": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
+    "pbe_moc_class_minmax": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "pbe_moc_source_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp]),
+    "pbe_qmom_create": (C.c_int, [_vp, C.c_int, C.POINTER(KernelSpec), C.POINTER(_vp)]),
+    "pbe_qmom_destroy": (C.c_int, [_vp]),
+    "pbe_qmom_source": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "pbe_qmom_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp, _vp]),
+    "pbe_wheeler_batch": (C.c_int, [_vp, C.c_int, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "pbe_qmom_source_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "pbe_eval_coalescence": (C.c_int, [_vp, C.POINTER(KernelSpec), _i64, _vp, _vp, _vp, _vp, _vp,
+                                       _vp]),
+    "pbe_eval_breakup": (C.c_int, [_vp, C.POINTER(KernelSpec), _i64, _vp, _vp, _vp, _vp]),
+    "pbe_eval_daughter_beta": (C.c_int, [_vp, C.c_int, _i64, _vp, _vp, _vp]),
+    "pbe_eval_daughter_moment": (C.c_int, [_vp, C.c_int, _i64, _vp, _vp, _vp]),
+    "pbe_eval_integrate_exp": (C.c_int, [_vp, _i64, _vp, _vp, _vp]),
+    "pbe_field_avg_max_min": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
+    "pbe_device_alloc": (C.c_int, [_vp, _i64, C.POINTER(_vp)]),
+    "pbe_device_free": (C.c_int, [_vp, _vp]),
+    "pbe_host_alloc": (C.c_int, [_vp, _i64, C.POINTER(_vp)]),
+    "pbe_host_free": (C.c_int, [_vp, _vp]),
+    "pbe_memcpy_h2d": (C.c_int, [_vp, _vp, _vp, _i64]),
+    "pbe_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, _i64]),
+    "pbe_memset": (C.c_int, [_vp, _vp, C.c_int, _i64]),
+    "pbe_sync": (C.c_int, [_vp]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load the shared library; raise (never fall back) when it is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(or make -C openpbe_b200/csrc).  openpbe_b200 has no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(L, name)  # AttributeError if the ABI lost a symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def last_error() -> str:
+    return lib().pbe_last_error().decode(errors="replace")
+
+
+def check(rc: int) -> None:
+    if rc != PBE_OK:
+        raise PbeError(rc, last_error())

@@ -1,0 +1,245 @@
+// pbe_api.cu -- context, error reporting, run-time selection by TypeName, memory helpers and
+// the FP64-peak micro-benchmark of libpbe_b200.so (C ABI: include/pbe_b200.h).
+#include <string.h>
+
+#include "pbe_common.h"
+
+namespace pbe {
+
+static thread_local std::string g_last_error;
+
+void set_error(const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+    set_error("CUDA error %d (%s) at %s:%d in %s", (int)e, cudaGetErrorString(e), file, line, what);
+    return PBE_E_CUDA;
+}
+
+int ensure_stage(pbe_ctx *ctx, size_t bytes_per_slot) {
+    if (ctx->stage_bytes >= bytes_per_slot) return PBE_OK;
+    for (int s = 0; s < kHostSlots; ++s) {
+        if (ctx->stage[s]) cudaFree(ctx->stage[s]);
+        ctx->stage[s] = nullptr;
+    }
+    ctx->stage_bytes = 0;
+    for (int s = 0; s < kHostSlots; ++s) PBE_CUDA(cudaMalloc(&ctx->stage[s], bytes_per_slot));
+    ctx->stage_bytes = bytes_per_slot;
+    return PBE_OK;
+}
+
+// ---- FP64 peak: 8 independent DFMA chains per thread, register resident -------------------
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, int iters, double a, double b) {
+    double x0 = threadIdx.x * 1e-3, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5,
+           x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            x0 = __fma_rn(x0, a, b);
+            x1 = __fma_rn(x1, a, b);
+            x2 = __fma_rn(x2, a, b);
+            x3 = __fma_rn(x3, a, b);
+            x4 = __fma_rn(x4, a, b);
+            x5 = __fma_rn(x5, a, b);
+            x6 = __fma_rn(x6, a, b);
+            x7 = __fma_rn(x7, a, b);
+        }
+    }
+    const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == 12345.678) out[0] = s; // never true: keeps the chains alive
+}
+
+} // namespace pbe
+
+using namespace pbe;
+
+extern "C" {
+
+const char *pbe_last_error(void) { return g_last_error.c_str(); }
+int pbe_version(void) { return PBE_B200_VERSION; }
+
+// ---- run-time selection by TypeName (coalescenceKernel.C:46-71, breakupKernel.C:46-68,
+// daughterParticleDistribution.C:54-81): unknown names fail and list the valid ones ---------
+static int lookup(const char *what, const char *name, const char *const *names, const int *vals,
+                  int count, int *out) {
+    PBE_REQUIRE(name != nullptr && out != nullptr, PBE_E_INVALID, "%s: NULL argument", what);
+    for (int i = 0; i < count; ++i)
+        if (strcmp(name, names[i]) == 0) {
+            *out = vals[i];
+            return PBE_OK;
+        }
+    std::string valid;
+    for (int i = 0; i < count; ++i) {
+        valid += (i ? " " : "");
+        valid += names[i];
+    }
+    set_error("Unknown %s type %s\n\nValid %s types are :\n(%s)", what, name, what, valid.c_str());
+    return PBE_E_UNKNOWN_TYPE;
+}
+
+int pbe_coalescence_type(const char *type_name, int *out) {
+    static const char *const n[] = {"noCoalescence", "constantCoalescence", "CoulaloglouTavlaridesC"};
+    static const int v[] = {PBE_COAL_NONE, PBE_COAL_CONSTANT, PBE_COAL_CT};
+    return lookup("coalescenceKernel", type_name, n, v, 3, out);
+}
+int pbe_breakup_type(const char *type_name, int *out) {
+    static const char *const n[] = {"noBreakup", "binaryBreakup", "CoulaloglouTavlarides"};
+    static const int v[] = {PBE_BR_NONE, PBE_BR_BINARY, PBE_BR_CT};
+    return lookup("breakupKernel", type_name, n, v, 3, out);
+}
+int pbe_daughter_type(const char *type_name, int *out) {
+    static const char *const n[] = {"uniformBinaryBreakup"};
+    static const int v[] = {PBE_DAUGHTER_UNIFORM_BINARY};
+    return lookup("daughterParticleDistribution", type_name, n, v, 1, out);
+}
+
+// ---- context ----------------------------------------------------------------------------
+int pbe_ctx_create(int device, pbe_ctx **out) {
+    PBE_REQUIRE(out != nullptr, PBE_E_INVALID, "pbe_ctx_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        set_error("pbe_ctx_create: no CUDA device (%s); libpbe_b200 has no CPU path",
+                  e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return PBE_E_CUDA;
+    }
+    PBE_REQUIRE(device >= 0 && device < count, PBE_E_INVALID,
+                "pbe_ctx_create: device %d out of range [0,%d)", device, count);
+    PBE_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    PBE_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        set_error("pbe_ctx_create: device %d (%s) is sm_%d%d; this library is built for sm_100a only",
+                  device, prop.name, prop.major, prop.minor);
+        return PBE_E_UNSUPPORTED;
+    }
+    pbe_ctx *ctx = new pbe_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    ctx->hbm_bytes = prop.totalGlobalMem;
+    strncpy(ctx->name, prop.name, sizeof(ctx->name) - 1);
+    for (int s = 0; s < kHostSlots; ++s) {
+        e = cudaStreamCreateWithFlags(&ctx->slot_stream[s], cudaStreamNonBlocking);
+        if (e != cudaSuccess) {
+            delete ctx;
+            return cuda_fail(e, "cudaStreamCreateWithFlags", __FILE__, __LINE__);
+        }
+    }
+    *out = ctx;
+    return PBE_OK;
+}
+
+int pbe_ctx_destroy(pbe_ctx *ctx) {
+    if (!ctx) return PBE_OK;
+    DeviceGuard g(ctx->device);
+    cudaDeviceSynchronize();
+    for (int s = 0; s < kHostSlots; ++s) {
+        if (ctx->stage[s]) cudaFree(ctx->stage[s]);
+        if (ctx->slot_stream[s]) cudaStreamDestroy(ctx->slot_stream[s]);
+    }
+    delete ctx;
+    return PBE_OK;
+}
+
+int pbe_ctx_info(pbe_ctx *ctx, char *name, int name_len, int *sm_count, int64_t *hbm_bytes) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_ctx_info: NULL context");
+    if (name && name_len > 0) {
+        strncpy(name, ctx->name, (size_t)name_len - 1);
+        name[name_len - 1] = 0;
+    }
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (hbm_bytes) *hbm_bytes = (int64_t)ctx->hbm_bytes;
+    return PBE_OK;
+}
+
+int64_t pbe_ctx_launch_count(pbe_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
+
+int pbe_measure_fp64_peak(pbe_ctx *ctx, double *tflops, double *ms_out) {
+    PBE_REQUIRE(ctx != nullptr && tflops != nullptr, PBE_E_INVALID, "pbe_measure_fp64_peak: NULL");
+    DeviceGuard g(ctx->device);
+    double *d_out = nullptr;
+    PBE_CUDA(cudaMalloc(&d_out, sizeof(double)));
+    const int iters = 4096, threads = 256, blocks = ctx->sm_count * 8;
+    cudaEvent_t e0, e1;
+    PBE_CUDA(cudaEventCreate(&e0));
+    PBE_CUDA(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        PBE_CUDA(cudaEventRecord(e0, 0));
+        fp64_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-7);
+        PBE_CUDA(cudaEventRecord(e1, 0));
+        PBE_CUDA(cudaEventSynchronize(e1));
+        ctx->launches++;
+        float ms = 0;
+        PBE_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    PBE_CUDA(cudaGetLastError());
+    const double flops = 2.0 * 64.0 * iters * (double)threads * blocks;
+    *tflops = flops / (best * 1e-3) / 1e12;
+    if (ms_out) *ms_out = best;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    return PBE_OK;
+}
+
+// ---- memory helpers ----------------------------------------------------------------------
+int pbe_device_alloc(pbe_ctx *ctx, int64_t bytes, void **out) {
+    PBE_REQUIRE(ctx && out && bytes >= 0, PBE_E_INVALID, "pbe_device_alloc: bad argument");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaMalloc(out, (size_t)bytes));
+    return PBE_OK;
+}
+int pbe_device_free(pbe_ctx *ctx, void *p) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_device_free: NULL context");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaFree(p));
+    return PBE_OK;
+}
+int pbe_host_alloc(pbe_ctx *ctx, int64_t bytes, void **out) {
+    PBE_REQUIRE(ctx && out && bytes >= 0, PBE_E_INVALID, "pbe_host_alloc: bad argument");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaHostAlloc(out, (size_t)bytes, cudaHostAllocDefault));
+    return PBE_OK;
+}
+int pbe_host_free(pbe_ctx *ctx, void *p) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_host_free: NULL context");
+    PBE_CUDA(cudaFreeHost(p));
+    return PBE_OK;
+}
+int pbe_memcpy_h2d(pbe_ctx *ctx, void *dst, const void *src, int64_t bytes) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_memcpy_h2d: NULL context");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyHostToDevice));
+    return PBE_OK;
+}
+int pbe_memcpy_d2h(pbe_ctx *ctx, void *dst, const void *src, int64_t bytes) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_memcpy_d2h: NULL context");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost));
+    return PBE_OK;
+}
+int pbe_memset(pbe_ctx *ctx, void *dst, int value, int64_t bytes) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_memset: NULL context");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaMemset(dst, value, (size_t)bytes));
+    return PBE_OK;
+}
+int pbe_sync(pbe_ctx *ctx) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_sync: NULL context");
+    DeviceGuard g(ctx->device);
+    PBE_CUDA(cudaDeviceSynchronize());
+    return PBE_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,114 @@
+// pbe_math.cuh -- FP64 device math for the PBE source kernels (sm_100a).
+//
+// The MOC kernel spends >70 % of its FP64 issue slots in exp(): a branch-free version with a
+// known instruction count (15 FP64-pipe instructions) is what the roofline model in DESIGN.md
+// counts.  The functions are __host__ __device__ so that tests/test_device_math_host.py can
+// compile this header with g++ and check the arithmetic against libm without a GPU; the
+// product only ever runs the device instantiation.
+#pragma once
+
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#if defined(__CUDACC__)
+#define PBE_HD __host__ __device__ __forceinline__
+#else
+#define PBE_HD inline
+#endif
+
+namespace pbe {
+
+PBE_HD double fma_(double a, double b, double c) {
+#if defined(__CUDA_ARCH__)
+    return __fma_rn(a, b, c);
+#else
+    return fma(a, b, c);
+#endif
+}
+
+PBE_HD int hi_word(double x) {
+#if defined(__CUDA_ARCH__)
+    return __double2hiint(x);
+#else
+    uint64_t u;
+    memcpy(&u, &x, 8);
+    return (int)(u >> 32);
+#endif
+}
+PBE_HD int lo_word(double x) {
+#if defined(__CUDA_ARCH__)
+    return __double2loint(x);
+#else
+    uint64_t u;
+    memcpy(&u, &x, 8);
+    return (int)(u & 0xffffffffu);
+#endif
+}
+PBE_HD double make_double(int hi, int lo) {
+#if defined(__CUDA_ARCH__)
+    return __hiloint2double(hi, lo);
+#else
+    uint64_t u = ((uint64_t)(uint32_t)hi << 32) | (uint32_t)lo;
+    double x;
+    memcpy(&x, &u, 8);
+    return x;
+#endif
+}
+
+// exp(x) for x <= 0 (the only sign the Coulaloglou-Tavlarides efficiencies produce:
+// coalescenceKernels/CoulaloglouTavlarides.C:84-88, breakupKernels/CoulaloglouTavlarides.C:86-90).
+// Cody-Waite reduction x = k ln2 + r, |r| <= ln2/2, degree-11 polynomial from
+// tools/gen_exp_coeffs.py (0.15 ulp in exact arithmetic; < 1 ulp measured after rounding),
+// 2^k applied by an integer add on the exponent field.  15 FP64-pipe instructions; the range
+// handling is done on the integer pipe so it costs no FP64 issue slot:
+//   * x <= -800 (including -inf): 0;  results below 2^-1021 are flushed to 0 (libm returns a
+//     denormal there; the difference is < 2.3e-308 absolute);
+//   * NaN propagates (k = 0 for the quiet NaN, the polynomial carries the NaN);
+//   * 0 < x <= 709 also works (not on the measured path); larger x is outside the contract.
+PBE_HD double exp_neg(double x) {
+    const double L2E = 1.4426950408889634074;         // 1/ln2
+    const double SHIFT = 6755399441055744.0;          // 1.5 * 2^52: round-to-nearest-int trick
+    const double LN2_HI = 6.93147180369123816490e-01; // high 33 bits of ln2
+    const double LN2_LO = 1.90821492927058770002e-10;
+    double t = fma_(x, L2E, SHIFT);
+    int k = lo_word(t);
+    double kd = t - SHIFT;
+    double r = fma_(kd, -LN2_HI, x);
+    r = fma_(kd, -LN2_LO, r);
+    double p = 2.510134692835034e-08;
+    p = fma_(p, r, 2.7621338669142925e-07);
+    p = fma_(p, r, 2.75572664186123e-06);
+    p = fma_(p, r, 2.4801518641395993e-05);
+    p = fma_(p, r, 0.00019841269864380513);
+    p = fma_(p, r, 0.0013888888918939168);
+    p = fma_(p, r, 0.008333333333329793);
+    p = fma_(p, r, 0.04166666666662064);
+    p = fma_(p, r, 0.16666666666666669);
+    p = fma_(p, r, 0.5000000000000001);
+    p = fma_(p, r, 1.0);
+    p = fma_(p, r, 1.0);
+    // p in [0.70, 1.42): its exponent field is 1022 or 1023; adding k keeps it normal for
+    // k in [-1021, 1023].
+    int hi = hi_word(p) + (int)((unsigned)k << 20);
+    double res = make_double(hi, lo_word(p));
+    // hi word of x in [hi(-800.0), hi(-inf)]  <=>  x <= -800
+    const unsigned ux = (unsigned)hi_word(x);
+    const bool under = (ux - 0xC0890000u) <= (0xFFF00000u - 0xC0890000u);
+    res = (under || k < -1021) ? 0.0 : res;
+    return res;
+}
+
+// pow(x, 1/3) with C pow() semantics for the arguments the reference feeds it
+// (coalescenceKernels/CoulaloglouTavlarides.C:75-76): negative finite x -> NaN, +-0 -> 0.
+PBE_HD double pow_third(double x) { return x < 0.0 ? NAN : cbrt(x); }
+
+// x^k for integer k >= 0 by repeated multiplication; pow(x, 0) = 1 for every x including 0 and
+// NaN, as C pow() (QMOM.C:248,255,260 call pow(double, label)).
+PBE_HD double pow_int(double x, int k) {
+    double r = 1.0;
+    for (int i = 0; i < k; ++i) r *= x;
+    return r;
+}
+
+} // namespace pbe

@@ -1,0 +1,475 @@
+// pbe_moc.cu -- host side of the method-of-classes path: table construction at create time,
+// launch configuration, the host-buffer pipeline.  Kernels: pbe_moc_kernel.cuh.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "pbe_common.h"
+#include "pbe_moc_kernel.cuh"
+
+using namespace pbe;
+
+struct pbe_moc {
+    pbe_ctx *ctx = nullptr;
+    int N = 0;
+    double xi1 = 0, relax = 1.0;
+    pbe_kernel_spec spec{};
+    int dcoal = DCOAL_OFF, dbr = DBR_TAB;
+    int block = 128;       // cells per CTA
+    int ctas_per_sm = 1;
+    size_t smem = 0;
+    MocParams base{};      // table pointers, chunk offsets, folded coefficients
+    double2 *d_pair = nullptr;
+    double *d_cls = nullptr;
+};
+
+namespace {
+
+typedef void (*moc_kernel_fn)(const MocParams);
+
+template <int BLOCK>
+moc_kernel_fn pick_kernel(int dcoal, int dbr) {
+#define PBE_PICK(C, B) \
+    if (dcoal == C && dbr == B) return (moc_kernel_fn)moc_source_kernel<C, B, BLOCK>;
+    PBE_PICK(DCOAL_OFF, DBR_TAB)
+    PBE_PICK(DCOAL_OFF, DBR_CT)
+    PBE_PICK(DCOAL_CT, DBR_TAB)
+    PBE_PICK(DCOAL_CT, DBR_CT)
+    PBE_PICK(DCOAL_SYM, DBR_TAB)
+    PBE_PICK(DCOAL_SYM, DBR_CT)
+    PBE_PICK(DCOAL_ASYM, DBR_TAB)
+    PBE_PICK(DCOAL_ASYM, DBR_CT)
+#undef PBE_PICK
+    return nullptr;
+}
+
+moc_kernel_fn kernel_for(const pbe_moc *m) {
+    return m->block == 128 ? pick_kernel<128>(m->dcoal, m->dbr) : pick_kernel<64>(m->dcoal, m->dbr);
+}
+
+// Pair geometry of the Coulaloglou-Tavlarides coalescence kernel, with the reference's own
+// libm calls (coalescenceKernels/CoulaloglouTavlarides.C:75-89): everything that does not
+// depend on the cell.
+void ct_pair_geometry(double xa, double xb, double *G, double *H) {
+    const double a = pow(xa, 1.0 / 3.0), b = pow(xb, 1.0 / 3.0);
+    *G = pow(a + b, 2) * pow(pow(xa, 2.0 / 9.0) + pow(xb, 2.0 / 9.0), 0.5);
+    *H = pow(a * b / (a + b), 4.0);
+}
+
+// d = sum_i dvol_i n_i / sum_i n_i  (MOC.C:282-290); one thread per cell, coalesced class rows
+__global__ void __launch_bounds__(256) moc_d_kernel(int N, int64_t ncells, int64_t stride,
+                                                    const double *__restrict__ n,
+                                                    const double *__restrict__ dvol,
+                                                    double *__restrict__ d) {
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < ncells; c += nthreads) {
+        double sum = 0.0, norm = 0.0;
+#pragma unroll 4
+        for (int i = 0; i < N; ++i) {
+            const double v = __ldg(n + (size_t)i * stride + c);
+            sum = fma_(__ldg(dvol + i), v, sum);
+            norm += v;
+        }
+        d[c] = sum / norm;
+    }
+}
+
+// per-class min / max over cells (MOC.C:181-183, :238): stage 1 = per-CTA partials
+__global__ void __launch_bounds__(256) moc_minmax_partial_kernel(int64_t ncells, int64_t stride,
+                                                                 const double *__restrict__ n,
+                                                                 double *__restrict__ part) {
+    const int k = blockIdx.y;
+    const double *row = n + (size_t)k * stride;
+    double mn = INFINITY, mx = -INFINITY;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < ncells; c += nthreads) {
+        const double v = __ldg(row + c);
+        mn = fmin(mn, v);
+        mx = fmax(mx, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    __shared__ double smn[8], smx[8];
+    if ((threadIdx.x & 31) == 0) {
+        smn[threadIdx.x >> 5] = mn;
+        smx[threadIdx.x >> 5] = mx;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) {
+            mn = fmin(mn, smn[w]);
+            mx = fmax(mx, smx[w]);
+        }
+        part[((size_t)k * gridDim.x + blockIdx.x) * 2 + 0] = mn;
+        part[((size_t)k * gridDim.x + blockIdx.x) * 2 + 1] = mx;
+    }
+}
+__global__ void moc_minmax_final_kernel(int nparts, const double *__restrict__ part,
+                                        double *__restrict__ out_min, double *__restrict__ out_max) {
+    const int k = blockIdx.x;
+    double mn = INFINITY, mx = -INFINITY;
+    for (int b = threadIdx.x; b < nparts; b += 32) {
+        mn = fmin(mn, part[((size_t)k * nparts + b) * 2 + 0]);
+        mx = fmax(mx, part[((size_t)k * nparts + b) * 2 + 1]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if (threadIdx.x == 0) {
+        if (out_min) out_min[k] = mn;
+        if (out_max) out_max[k] = mx;
+    }
+}
+
+int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
+    if (p.ncells == 0) return PBE_OK;
+    const int64_t nb = (p.ncells + m->block - 1) / m->block;
+    const int64_t cap = (int64_t)m->ctx->sm_count * m->ctas_per_sm;
+    const int grid = (int)std::min<int64_t>(nb, cap);
+    moc_kernel_fn fn = kernel_for(m);
+    void *args[] = {(void *)&p};
+    PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
+    m->ctx->launches++;
+    return PBE_OK;
+}
+
+int check_fields(const char *fn, const pbe_moc *m, int64_t ncells, int64_t stride, const void *n,
+                 const void *eps, const void *rho, const void *nu, double dt) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "%s: NULL handle", fn);
+    PBE_REQUIRE(ncells >= 0 && stride >= ncells, PBE_E_INVALID,
+                "%s: need 0 <= ncells <= stride (got %lld, %lld)", fn, (long long)ncells,
+                (long long)stride);
+    PBE_REQUIRE(ncells == 0 || (n && eps && rho && nu), PBE_E_INVALID, "%s: NULL field pointer", fn);
+    PBE_REQUIRE(dt > 0.0, PBE_E_INVALID, "%s: dt must be positive (got %g)", fn, dt);
+    return PBE_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
+                   double source_relaxation, pbe_moc **out) {
+    PBE_REQUIRE(ctx && spec && out, PBE_E_INVALID, "pbe_moc_create: NULL argument");
+    *out = nullptr;
+    PBE_REQUIRE(N >= 1, PBE_E_INVALID, "pbe_moc_create: numberOfClasses must be >= 1 (got %d)", N);
+    PBE_REQUIRE(xi1 > 0.0, PBE_E_INVALID, "pbe_moc_create: xi1 must be positive (got %g)", xi1);
+    PBE_REQUIRE(spec->coalescence >= PBE_COAL_NONE && spec->coalescence <= PBE_COAL_TABLE,
+                PBE_E_UNKNOWN_TYPE, "pbe_moc_create: unknown coalescenceKernel id %d",
+                spec->coalescence);
+    PBE_REQUIRE(spec->breakup >= PBE_BR_NONE && spec->breakup <= PBE_BR_TABLE, PBE_E_UNKNOWN_TYPE,
+                "pbe_moc_create: unknown breakupKernel id %d", spec->breakup);
+    PBE_REQUIRE(spec->daughter == PBE_DAUGHTER_UNIFORM_BINARY, PBE_E_UNKNOWN_TYPE,
+                "pbe_moc_create: unknown daughterParticleDistribution id %d", spec->daughter);
+    PBE_REQUIRE(spec->coalescence != PBE_COAL_TABLE || spec->coal_table, PBE_E_INVALID,
+                "pbe_moc_create: PBE_COAL_TABLE needs coal_table");
+    PBE_REQUIRE(spec->breakup != PBE_BR_TABLE || spec->br_table, PBE_E_INVALID,
+                "pbe_moc_create: PBE_BR_TABLE needs br_table");
+    DeviceGuard g(ctx->device);
+
+    pbe_moc *m = new pbe_moc();
+    m->ctx = ctx;
+    m->N = N;
+    m->xi1 = xi1;
+    m->relax = source_relaxation;
+    m->spec = *spec;
+    m->spec.coal_table = nullptr;
+    m->spec.br_table = nullptr;
+
+    std::vector<double> xi(N);
+    for (int i = 0; i < N; ++i) xi[i] = xi1 * (i + 1); // MOC.C:79
+
+    // ---- device evaluation mode ----------------------------------------------------------
+    switch (spec->coalescence) {
+    case PBE_COAL_NONE: m->dcoal = DCOAL_OFF; break;
+    case PBE_COAL_CONSTANT: m->dcoal = DCOAL_SYM; break;
+    case PBE_COAL_CT: m->dcoal = DCOAL_CT; break;
+    case PBE_COAL_TABLE: {
+        bool sym = true;
+        for (int i = 0; i < N && sym; ++i)
+            for (int j = 0; j < i; ++j)
+                if (spec->coal_table[(size_t)i * N + j] != spec->coal_table[(size_t)j * N + i]) {
+                    sym = false;
+                    break;
+                }
+        m->dcoal = sym ? DCOAL_SYM : DCOAL_ASYM;
+    } break;
+    }
+    m->dbr = (spec->breakup == PBE_BR_CT) ? DBR_CT : DBR_TAB;
+    if (N < 2) m->dcoal = DCOAL_OFF; // one class: no pair keeps its product inside the grid
+
+    // ---- pair table in traversal order: row blocks of TI classes, TI x TJ tiles ----------
+    MocParams &b = m->base;
+    b.N = N;
+    const int nrows = N / 2; // rows i with 2 i <= N - 2
+    b.nblocks = (m->dcoal == DCOAL_OFF) ? 0 : (nrows + MOC_TI - 1) / MOC_TI;
+    if (b.nblocks > MOC_MAX_BLOCKS) {
+        set_error("pbe_moc_create: numberOfClasses %d exceeds the device path's limit %d", N,
+                  2 * MOC_TI * MOC_MAX_BLOCKS);
+        delete m;
+        return PBE_E_UNSUPPORTED;
+    }
+    std::vector<double2> tab;
+    b.chunk_off[0] = 0;
+    b.chunk_max_pairs = 1;
+    for (int blk = 0; blk < b.nblocks; ++blk) {
+        const int i0 = blk * MOC_TI;
+        const int ntiles = (N - 1 - 2 * i0 + MOC_TJ - 1) / MOC_TJ;
+        for (int t = 0; t < ntiles; ++t)
+            for (int r = 0; r < MOC_TI; ++r)
+                for (int c = 0; c < MOC_TJ; ++c) {
+                    const int i = i0 + r, j = i0 + t * MOC_TJ + c;
+                    double2 v = make_double2(0.0, 0.0);
+                    if (i <= j && i + j <= N - 2) { // MOC.C:109 death bound, MOC.C:116 birth
+                        switch (spec->coalescence) {
+                        case PBE_COAL_CONSTANT: v.x = v.y = spec->coal_c[0]; break;
+                        case PBE_COAL_CT: ct_pair_geometry(xi[i], xi[j], &v.x, &v.y); break;
+                        case PBE_COAL_TABLE:
+                            v.x = spec->coal_table[(size_t)i * N + j];
+                            v.y = spec->coal_table[(size_t)j * N + i];
+                            break;
+                        }
+                        if (i == j) { // the diagonal pair feeds death once and birth with 1/2
+                            v.x *= 0.5;
+                            if (m->dcoal != DCOAL_CT) v.y *= 0.5;
+                        }
+                    }
+                    tab.push_back(v);
+                }
+        b.chunk_off[blk + 1] = (int)tab.size();
+        b.chunk_max_pairs = std::max(b.chunk_max_pairs, b.chunk_off[blk + 1] - b.chunk_off[blk]);
+    }
+
+    // ---- per-class tables ------------------------------------------------------------------
+    std::vector<double> cls((size_t)CLS_ROWS * (N + 1), 0.0);
+    for (int i = 0; i < N; ++i) {
+        double P = 0.0, Q = 0.0;
+        switch (spec->breakup) {
+        case PBE_BR_BINARY: P = xi[i] * xi[i]; break;            // binaryBreakup.C:51-53
+        case PBE_BR_CT:                                          // CoulaloglouTavlarides.C:83-92
+            P = 1.0 / pow(xi[i], 2.0 / 9.0);
+            Q = 1.0 / pow(xi[i], 5.0 / 9.0);
+            break;
+        case PBE_BR_TABLE: P = spec->br_table[i]; break;
+        default: break;                                          // noBreakup.C:51-54
+        }
+        cls[(size_t)CLS_BR_P * (N + 1) + i] = P;
+        cls[(size_t)CLS_BR_Q * (N + 1) + i] = Q;
+        cls[(size_t)CLS_W * (N + 1) + i] = (2.0 / xi[i]) * xi1; // beta(.,xi_i) dxi, MOC.C:146-154
+        cls[(size_t)CLS_DVOL * (N + 1) + i] = pow(6.0 / M_PI * xi[i], 1.0 / 3.0); // MOC.C:43-45
+        cls[(size_t)CLS_XI * (N + 1) + i] = xi[i];
+    }
+
+    // ---- folded coefficients (pbe_kernels.cuh uses the same algebra) --------------------------
+    {
+        const double c1 = spec->coal_c[0], c2 = spec->coal_c[1], gm = spec->coal_c[2],
+                     sg = spec->coal_c[3];
+        b.coalA = c1 / (1 + gm);
+        b.coalK = c2 / (sg * sg * ((1 + gm) * (1 + gm) * (1 + gm)));
+    }
+    {
+        const double c1 = spec->br_c[0], c2 = spec->br_c[1], gm = spec->br_c[2], sg = spec->br_c[3];
+        b.brA = c1 / (1 + gm);
+        b.brK = c2 * sg * ((1 + gm) * (1 + gm));
+    }
+
+    // ---- launch shape: 128 cells per CTA if the state fits in shared memory, else 64 ---------
+    m->block = 128;
+    m->smem = moc_smem_bytes(N, 128, b.chunk_max_pairs);
+    if (m->smem > ctx->smem_optin) {
+        m->block = 64;
+        m->smem = moc_smem_bytes(N, 64, b.chunk_max_pairs);
+    }
+    if (m->smem > ctx->smem_optin) {
+        set_error("pbe_moc_create: numberOfClasses %d needs %zu B of shared memory per CTA, device "
+                  "offers %zu",
+                  N, m->smem, ctx->smem_optin);
+        delete m;
+        return PBE_E_UNSUPPORTED;
+    }
+    moc_kernel_fn fn = kernel_for(m);
+    cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)m->smem);
+    if (e == cudaSuccess) {
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, m->block, m->smem);
+        m->ctas_per_sm = std::max(1, occ);
+    }
+    if (e == cudaSuccess && !tab.empty()) {
+        e = cudaMalloc(&m->d_pair, tab.size() * sizeof(double2));
+        if (e == cudaSuccess)
+            e = cudaMemcpy(m->d_pair, tab.data(), tab.size() * sizeof(double2), cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&m->d_cls, cls.size() * sizeof(double));
+    if (e == cudaSuccess)
+        e = cudaMemcpy(m->d_cls, cls.data(), cls.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        int rc = cuda_fail(e, "pbe_moc_create device setup", __FILE__, __LINE__);
+        pbe_moc_destroy(m);
+        return rc;
+    }
+    b.pair_tab = m->d_pair;
+    b.cls = m->d_cls;
+    *out = m;
+    return PBE_OK;
+}
+
+int pbe_moc_destroy(pbe_moc *m) {
+    if (!m) return PBE_OK;
+    DeviceGuard g(m->ctx->device);
+    if (m->d_pair) cudaFree(m->d_pair);
+    if (m->d_cls) cudaFree(m->d_cls);
+    delete m;
+    return PBE_OK;
+}
+
+int pbe_moc_source(pbe_moc *m, int64_t ncells, int64_t stride, const double *n, const double *eps,
+                   const double *rho, const double *nu, double dt, double *S, void *cuda_stream) {
+    int rc = check_fields("pbe_moc_source", m, ncells, stride, n, eps, rho, nu, dt);
+    if (rc) return rc;
+    PBE_REQUIRE(ncells == 0 || S != nullptr, PBE_E_INVALID, "pbe_moc_source: S is NULL");
+    DeviceGuard g(m->ctx->device);
+    MocParams p = m->base;
+    p.ncells = ncells;
+    p.stride = stride;
+    p.n_in = n;
+    p.n_out = nullptr;
+    p.S_out = S;
+    p.d_out = nullptr;
+    p.eps = eps;
+    p.rho = rho;
+    p.nu = nu;
+    p.alpha = p.vcell = nullptr;
+    p.relax_over_dt = m->relax / dt;
+    p.dt = dt;
+    p.do_step = 0;
+    p.moments = nullptr;
+    p.n_moments = 0;
+    p.cont_err_max = nullptr;
+    return launch(m, p, (cudaStream_t)cuda_stream);
+}
+
+int pbe_moc_step(pbe_moc *m, int64_t ncells, int64_t stride, double *n, const double *eps,
+                 const double *rho, const double *nu, double dt, const pbe_moc_io *io,
+                 void *cuda_stream) {
+    int rc = check_fields("pbe_moc_step", m, ncells, stride, n, eps, rho, nu, dt);
+    if (rc) return rc;
+    DeviceGuard g(m->ctx->device);
+    MocParams p = m->base;
+    p.ncells = ncells;
+    p.stride = stride;
+    p.n_in = n;
+    p.n_out = n;
+    p.eps = eps;
+    p.rho = rho;
+    p.nu = nu;
+    p.relax_over_dt = m->relax / dt;
+    p.dt = dt;
+    p.do_step = 1;
+    p.S_out = nullptr;
+    p.d_out = nullptr;
+    p.alpha = p.vcell = nullptr;
+    p.moments = nullptr;
+    p.n_moments = 0;
+    p.cont_err_max = nullptr;
+    if (io) {
+        PBE_REQUIRE(io->n_moments >= 0 && io->n_moments <= MOC_MAX_MOMENTS, PBE_E_INVALID,
+                    "pbe_moc_step: n_moments must be in [0,%d]", MOC_MAX_MOMENTS);
+        PBE_REQUIRE(io->cont_err_max == nullptr || (io->alpha && io->vcell), PBE_E_INVALID,
+                    "pbe_moc_step: the continuity check needs alpha and vcell");
+        p.S_out = io->S;
+        p.d_out = io->d;
+        p.alpha = io->alpha;
+        p.vcell = io->vcell;
+        p.moments = (io->n_moments > 0) ? io->moments : nullptr;
+        p.n_moments = io->n_moments;
+        p.cont_err_max = io->cont_err_max;
+    }
+    return launch(m, p, (cudaStream_t)cuda_stream);
+}
+
+int pbe_moc_d(pbe_moc *m, int64_t ncells, int64_t stride, const double *n, double *d,
+              void *cuda_stream) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_d: NULL handle");
+    PBE_REQUIRE(ncells >= 0 && stride >= ncells, PBE_E_INVALID, "pbe_moc_d: bad ncells/stride");
+    if (ncells == 0) return PBE_OK;
+    PBE_REQUIRE(n && d, PBE_E_INVALID, "pbe_moc_d: NULL field pointer");
+    DeviceGuard g(m->ctx->device);
+    const int grid = (int)std::min<int64_t>((ncells + 255) / 256, (int64_t)m->ctx->sm_count * 8);
+    moc_d_kernel<<<grid, 256, 0, (cudaStream_t)cuda_stream>>>(
+        m->N, ncells, stride, n, m->d_cls + (size_t)CLS_DVOL * (m->N + 1), d);
+    PBE_CUDA(cudaGetLastError());
+    m->ctx->launches++;
+    return PBE_OK;
+}
+
+int pbe_moc_class_minmax(pbe_moc *m, int64_t ncells, int64_t stride, const double *n,
+                         double *out_min, double *out_max, void *cuda_stream) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_class_minmax: NULL handle");
+    PBE_REQUIRE(ncells >= 0 && stride >= ncells, PBE_E_INVALID,
+                "pbe_moc_class_minmax: bad ncells/stride");
+    PBE_REQUIRE(n != nullptr || ncells == 0, PBE_E_INVALID, "pbe_moc_class_minmax: NULL field");
+    DeviceGuard g(m->ctx->device);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int nparts =
+        (int)std::max<int64_t>(1, std::min<int64_t>((ncells + 2047) / 2048, (int64_t)m->ctx->sm_count * 2));
+    double *part = nullptr;
+    PBE_CUDA(cudaMallocAsync(&part, (size_t)m->N * nparts * 2 * sizeof(double), st));
+    moc_minmax_partial_kernel<<<dim3(nparts, m->N), 256, 0, st>>>(ncells, stride, n, part);
+    moc_minmax_final_kernel<<<m->N, 32, 0, st>>>(nparts, part, out_min, out_max);
+    PBE_CUDA(cudaGetLastError());
+    PBE_CUDA(cudaFreeAsync(part, st));
+    m->ctx->launches += 2;
+    return PBE_OK;
+}
+
+// Host-buffer entry point: chunked three-slot pipeline H2D | kernel | D2H.
+int pbe_moc_source_host(pbe_moc *m, int64_t ncells, int64_t stride, const double *n_host,
+                        const double *eps_host, const double *rho_host, const double *nu_host,
+                        double dt, double *S_host) {
+    int rc = check_fields("pbe_moc_source_host", m, ncells, stride, n_host, eps_host, rho_host,
+                          nu_host, dt);
+    if (rc) return rc;
+    PBE_REQUIRE(ncells == 0 || S_host != nullptr, PBE_E_INVALID, "pbe_moc_source_host: S is NULL");
+    if (ncells == 0) return PBE_OK;
+    pbe_ctx *ctx = m->ctx;
+    DeviceGuard g(ctx->device);
+    const int N = m->N;
+    // chunk: whole waves of the persistent grid, about 512 MB of fields per slot
+    const int64_t wave = (int64_t)m->block * ctx->sm_count * m->ctas_per_sm;
+    const int64_t per_cell = (int64_t)(2 * N + 3) * sizeof(double);
+    int64_t C = std::max<int64_t>(1, ((int64_t)512 << 20) / per_cell / wave) * wave;
+    C = std::min(C, ((ncells + wave - 1) / wave) * wave);
+    rc = ensure_stage(ctx, (size_t)C * per_cell);
+    if (rc) return rc;
+    int64_t k = 0;
+    for (int64_t c0 = 0; c0 < ncells; c0 += C, ++k) {
+        const int64_t nc = std::min(C, ncells - c0);
+        const int s = (int)(k % kHostSlots);
+        cudaStream_t st = ctx->slot_stream[s];
+        double *dn = (double *)ctx->stage[s];
+        double *dS = dn + (size_t)N * C;
+        double *de = dS + (size_t)N * C;
+        double *dr = de + C;
+        double *dv = dr + C;
+        PBE_CUDA(cudaMemcpy2DAsync(dn, (size_t)C * 8, n_host + c0, (size_t)stride * 8, (size_t)nc * 8,
+                                   N, cudaMemcpyHostToDevice, st));
+        PBE_CUDA(cudaMemcpyAsync(de, eps_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st));
+        PBE_CUDA(cudaMemcpyAsync(dr, rho_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st));
+        PBE_CUDA(cudaMemcpyAsync(dv, nu_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st));
+        rc = pbe_moc_source(m, nc, C, dn, de, dr, dv, dt, dS, st);
+        if (rc) return rc;
+        PBE_CUDA(cudaMemcpy2DAsync(S_host + c0, (size_t)stride * 8, dS, (size_t)C * 8, (size_t)nc * 8,
+                                   N, cudaMemcpyDeviceToHost, st));
+    }
+    for (int s = 0; s < kHostSlots; ++s) PBE_CUDA(cudaStreamSynchronize(ctx->slot_stream[s]));
+    return PBE_OK;
+}
+
+} // extern "C"

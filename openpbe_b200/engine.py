@@ -1,0 +1,309 @@
+"""Thin Python handles over the C ABI, named after the reference's classes.
+
+`MOC` / `QMOM` correspond to PBEMethods::MOC / PBEMethods::QMOM (src/PBESystem/MOC.H:57-127,
+QMOM.H:55-112): constructed from the same coefficients (`numberOfClasses`, `xi1`,
+`sourceRelaxation`, `quadratureOrder`) and kernel TypeNames; `source()` / `step()` are the
+per-time-step work of `correct()` without the mesh-coupled transport.  Fields are torch CUDA
+tensors, float64, shape [N, ncells] (class-major, as the reference's PtrList<volScalarField>).
+All arithmetic happens inside libpbe_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import capi
+
+__all__ = ["Context", "MOC", "QMOM", "make_spec", "kernel_types"]
+
+_dp = C.POINTER(C.c_double)
+
+
+def kernel_types(coalescence: str, breakup: str, daughter: str = "uniformBinaryBreakup"):
+    """TypeName -> id through the library's run-time selection tables (raises on unknown)."""
+    L = capi.lib()
+    out = []
+    for fn, name in ((L.pbe_coalescence_type, coalescence), (L.pbe_breakup_type, breakup),
+                     (L.pbe_daughter_type, daughter)):
+        v = C.c_int(-1)
+        capi.check(fn(name.encode(), C.byref(v)))
+        out.append(v.value)
+    return tuple(out)
+
+
+def make_spec(coalescence: str = "noCoalescence", coal_coeffs: Sequence[float] = (),
+              breakup: str = "noBreakup", br_coeffs: Sequence[float] = (),
+              daughter: str = "uniformBinaryBreakup",
+              coal_table: Optional[np.ndarray] = None,
+              br_table: Optional[np.ndarray] = None) -> capi.KernelSpec:
+    """Kernel selection by the reference's TypeNames; `table` selects the user-kernel upload."""
+    s = capi.KernelSpec()
+    c_id = capi.COAL_TABLE if coalescence == "table" else None
+    b_id = capi.BR_TABLE if breakup == "table" else None
+    ids = kernel_types("noCoalescence" if c_id is not None else coalescence,
+                       "noBreakup" if b_id is not None else breakup, daughter)
+    s.coalescence = c_id if c_id is not None else ids[0]
+    s.breakup = b_id if b_id is not None else ids[1]
+    s.daughter = ids[2]
+    for k, v in enumerate(coal_coeffs):
+        s.coal_c[k] = float(v)
+    for k, v in enumerate(br_coeffs):
+        s.br_c[k] = float(v)
+    keep = []
+    if coal_table is not None:
+        ct = np.ascontiguousarray(coal_table, dtype=np.float64)
+        keep.append(ct)
+        s.coal_table = ct.ctypes.data_as(_dp)
+    if br_table is not None:
+        bt = np.ascontiguousarray(br_table, dtype=np.float64)
+        keep.append(bt)
+        s.br_table = bt.ctypes.data_as(_dp)
+    s._keep = keep
+    return s
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    assert t.dtype == torch.float64 and t.is_contiguous(), "fields are contiguous float64"
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class Context:
+    """pbe_ctx: one per (process, device)."""
+
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        self.device = int(device)
+        capi.check(capi.lib().pbe_ctx_create(self.device, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    def info(self):
+        name = C.create_string_buffer(128)
+        sm = C.c_int()
+        hbm = C.c_int64()
+        capi.check(capi.lib().pbe_ctx_info(self._h, name, 128, C.byref(sm), C.byref(hbm)))
+        return {"name": name.value.decode(), "sm_count": sm.value, "hbm_bytes": hbm.value}
+
+    def launch_count(self) -> int:
+        return int(capi.lib().pbe_ctx_launch_count(self._h))
+
+    def fp64_peak_tflops(self):
+        tf, ms = C.c_double(), C.c_double()
+        capi.check(capi.lib().pbe_measure_fp64_peak(self._h, C.byref(tf), C.byref(ms)))
+        return tf.value, ms.value
+
+    # ---- scalar functors on the device (host numpy in / out) --------------------------------
+    def eval_coalescence(self, spec, xi1, xi2, eps, rho, nu):
+        a = [np.ascontiguousarray(np.atleast_1d(v), dtype=np.float64) for v in (xi1, xi2, eps, rho, nu)]
+        a = np.broadcast_arrays(*a)
+        a = [np.ascontiguousarray(v) for v in a]
+        out = np.empty_like(a[0])
+        capi.check(capi.lib().pbe_eval_coalescence(
+            self._h, C.byref(spec), out.size, *[v.ctypes.data_as(C.c_void_p) for v in a],
+            out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def eval_breakup(self, spec, xi, rho, eps):
+        a = [np.ascontiguousarray(np.atleast_1d(v), dtype=np.float64) for v in (xi, rho, eps)]
+        a = [np.ascontiguousarray(v) for v in np.broadcast_arrays(*a)]
+        out = np.empty_like(a[0])
+        capi.check(capi.lib().pbe_eval_breakup(
+            self._h, C.byref(spec), out.size, *[v.ctypes.data_as(C.c_void_p) for v in a],
+            out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def eval_daughter_beta(self, xi1, xi2, daughter=capi.DAUGHTER_UNIFORM_BINARY):
+        a = [np.ascontiguousarray(np.atleast_1d(v), dtype=np.float64) for v in (xi1, xi2)]
+        a = [np.ascontiguousarray(v) for v in np.broadcast_arrays(*a)]
+        out = np.empty_like(a[0])
+        capi.check(capi.lib().pbe_eval_daughter_beta(
+            self._h, daughter, out.size, a[0].ctypes.data_as(C.c_void_p),
+            a[1].ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def eval_daughter_moment(self, xi, k, daughter=capi.DAUGHTER_UNIFORM_BINARY):
+        xi = np.ascontiguousarray(np.atleast_1d(xi), dtype=np.float64)
+        k = np.ascontiguousarray(np.broadcast_to(np.atleast_1d(k), xi.shape), dtype=np.int32)
+        out = np.empty_like(xi)
+        capi.check(capi.lib().pbe_eval_daughter_moment(
+            self._h, daughter, out.size, xi.ctypes.data_as(C.c_void_p),
+            k.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def eval_integrate_exp(self, rate, lower):
+        a = [np.ascontiguousarray(np.atleast_1d(v), dtype=np.float64) for v in (rate, lower)]
+        a = [np.ascontiguousarray(v) for v in np.broadcast_arrays(*a)]
+        out = np.empty_like(a[0])
+        capi.check(capi.lib().pbe_eval_integrate_exp(
+            self._h, out.size, a[0].ctypes.data_as(C.c_void_p), a[1].ctypes.data_as(C.c_void_p),
+            out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def wheeler_batch(self, m: torch.Tensor):
+        """m [2*order, ncells] -> (x, w) each [order, ncells]"""
+        nm, ncells = m.shape
+        order = nm // 2
+        x = torch.empty((order, ncells), dtype=torch.float64, device=m.device)
+        w = torch.empty_like(x)
+        capi.check(capi.lib().pbe_wheeler_batch(self._h, order, ncells, m.stride(0) if ncells else 0,
+                                                _ptr(m), _ptr(x), _ptr(w), _stream_ptr(m.device)))
+        return x, w
+
+    def field_avg_max_min(self, f: torch.Tensor, vcell: Optional[torch.Tensor] = None):
+        out = torch.empty(4, dtype=torch.float64, device=f.device)
+        capi.check(capi.lib().pbe_field_avg_max_min(self._h, f.numel(), _ptr(f), _ptr(vcell),
+                                                    _ptr(out), _stream_ptr(f.device)))
+        return out
+
+
+class MOC:
+    """pbe_moc: PBEMethods::MOC's source path (MOCCoeffs: numberOfClasses, xi1, sourceRelaxation)."""
+
+    def __init__(self, ctx: Context, numberOfClasses: int, xi1: float, spec: capi.KernelSpec,
+                 sourceRelaxation: float = 1.0):
+        self.ctx = ctx
+        self.N = int(numberOfClasses)
+        self.xi1 = float(xi1)
+        self._h = C.c_void_p()
+        capi.check(capi.lib().pbe_moc_create(ctx.handle, self.N, self.xi1, C.byref(spec),
+                                             float(sourceRelaxation), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_moc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dims(self, n):
+        assert n.dim() == 2 and n.shape[0] == self.N and n.stride(1) in (0, 1)
+        ncells = n.shape[1]
+        return ncells, (n.stride(0) if ncells else 0)
+
+    def source(self, n, eps, rho, nu, dt, out=None):
+        ncells, stride = self._dims(n)
+        S = torch.empty_like(n) if out is None else out
+        capi.check(capi.lib().pbe_moc_source(self._h, ncells, stride, _ptr(n), _ptr(eps), _ptr(rho),
+                                             _ptr(nu), float(dt), _ptr(S), _stream_ptr(n.device)))
+        return S
+
+    def step(self, n, eps, rho, nu, dt, *, S=None, d=None, alpha=None, vcell=None, moments=None,
+             cont_err_max=None):
+        """In-place n += dt S with the requested fused outputs."""
+        ncells, stride = self._dims(n)
+        io = capi.MocIO()
+        io.alpha = _ptr(alpha)
+        io.vcell = _ptr(vcell)
+        io.S = _ptr(S)
+        io.d = _ptr(d)
+        io.moments = _ptr(moments)
+        io.n_moments = 0 if moments is None else moments.numel()
+        io.cont_err_max = _ptr(cont_err_max)
+        capi.check(capi.lib().pbe_moc_step(self._h, ncells, stride, _ptr(n), _ptr(eps), _ptr(rho),
+                                           _ptr(nu), float(dt), C.byref(io), _stream_ptr(n.device)))
+        return n
+
+    def d(self, n):
+        ncells, stride = self._dims(n)
+        d = torch.empty(ncells, dtype=torch.float64, device=n.device)
+        capi.check(capi.lib().pbe_moc_d(self._h, ncells, stride, _ptr(n), _ptr(d), _stream_ptr(n.device)))
+        return d
+
+    def class_minmax(self, n):
+        ncells, stride = self._dims(n)
+        mn = torch.empty(self.N, dtype=torch.float64, device=n.device)
+        mx = torch.empty_like(mn)
+        capi.check(capi.lib().pbe_moc_class_minmax(self._h, ncells, stride, _ptr(n), _ptr(mn), _ptr(mx),
+                                                   _stream_ptr(n.device)))
+        return mn, mx
+
+    def source_host(self, n, eps, rho, nu, dt, out=None):
+        """Host-buffer entry point (numpy or CPU torch tensors; pinned memory gives full rate)."""
+        n_, eps_, rho_, nu_ = (_as_host(v) for v in (n, eps, rho, nu))
+        assert n_.shape[0] == self.N
+        S = torch.empty_like(n_) if out is None else _as_host(out)
+        capi.check(capi.lib().pbe_moc_source_host(
+            self._h, n_.shape[1], n_.stride(0) if n_.shape[1] else 0, _ptr(n_), _ptr(eps_), _ptr(rho_),
+            _ptr(nu_), float(dt), _ptr(S)))
+        return S
+
+
+def _as_host(v):
+    if isinstance(v, np.ndarray):
+        v = torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64))
+    assert v.device.type == "cpu" and v.dtype == torch.float64
+    return v
+
+
+class QMOM:
+    """pbe_qmom: PBEMethods::QMOM's source path (QMOMCoeffs: quadratureOrder)."""
+
+    def __init__(self, ctx: Context, quadratureOrder: int, spec: capi.KernelSpec):
+        self.ctx = ctx
+        self.order = int(quadratureOrder)
+        self._h = C.c_void_p()
+        capi.check(capi.lib().pbe_qmom_create(ctx.handle, self.order, C.byref(spec), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_qmom_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dims(self, m):
+        assert m.dim() == 2 and m.shape[0] == 2 * self.order
+        ncells = m.shape[1]
+        return ncells, (m.stride(0) if ncells else 0)
+
+    def source(self, m, eps, rho, nu, out=None):
+        ncells, stride = self._dims(m)
+        S = torch.empty_like(m) if out is None else out
+        capi.check(capi.lib().pbe_qmom_source(self._h, ncells, stride, _ptr(m), _ptr(eps), _ptr(rho),
+                                              _ptr(nu), _ptr(S), _stream_ptr(m.device)))
+        return S
+
+    def step(self, m, eps, rho, nu, dt, *, S=None, d=None):
+        ncells, stride = self._dims(m)
+        capi.check(capi.lib().pbe_qmom_step(self._h, ncells, stride, _ptr(m), _ptr(eps), _ptr(rho),
+                                            _ptr(nu), float(dt), _ptr(S), _ptr(d),
+                                            _stream_ptr(m.device)))
+        return m
+
+    def source_host(self, m, eps, rho, nu, out=None):
+        m_, eps_, rho_, nu_ = (_as_host(v) for v in (m, eps, rho, nu))
+        S = torch.empty_like(m_) if out is None else _as_host(out)
+        capi.check(capi.lib().pbe_qmom_source_host(
+            self._h, m_.shape[1], m_.stride(0) if m_.shape[1] else 0, _ptr(m_), _ptr(eps_), _ptr(rho_),
+            _ptr(nu_), _ptr(S)))
+        return S
