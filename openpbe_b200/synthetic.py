@@ -1,6 +1,6 @@
 """Seeded synthetic per-cell fields and the named workloads of BASELINE.json.
 
-Shared by tests/ and bench.py so that the oracle, the CPU baseline and the CUDA path see
+Shared by tests/ and bench.py so that the checker, the CPU baseline and the CUDA path see
 identical inputs.  Pure NumPy: this module never touches the GPU and never computes a source.
 
 Constants come from the reference tree (cited; the files themselves are not needed at run time):
@@ -69,7 +69,7 @@ def workload(name: str, ncells: int | None = None) -> Workload:
     elif name == "replay_qmom":
         w = workload("qmom3_ct")
         w.name, w.ncells = name, 4_000_000
-    elif name == "moc100_const":  # cell-independent variant (analytical oracles' kernels)
+    elif name == "moc100_const":  # cell-independent variant (the kernels of the 0-D analytical solutions)
         w = Workload(name, "MOC", 100, 16_000_000, xi1=0.1, dt=1e-3, coalescence="constantCoalescence",
                      coal_coeffs=(0.1,), breakup="binaryBreakup")
     elif name == "qmom3_const":
