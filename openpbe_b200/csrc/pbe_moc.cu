@@ -346,7 +346,7 @@ int pbe_moc_source(pbe_moc *m, int64_t ncells, int64_t stride, const double *n, 
     p.rho = rho;
     p.nu = nu;
     p.alpha = p.vcell = nullptr;
-    p.relax_over_dt = m->relax / dt;
+    p.relax = m->relax;
     p.dt = dt;
     p.do_step = 0;
     p.moments = nullptr;
@@ -369,7 +369,7 @@ int pbe_moc_step(pbe_moc *m, int64_t ncells, int64_t stride, double *n, const do
     p.eps = eps;
     p.rho = rho;
     p.nu = nu;
-    p.relax_over_dt = m->relax / dt;
+    p.relax = m->relax;
     p.dt = dt;
     p.do_step = 1;
     p.S_out = nullptr;

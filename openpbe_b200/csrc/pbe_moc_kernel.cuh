@@ -62,7 +62,7 @@ struct MocParams {
     const double *cls;           // [CLS_ROWS][N+1]
     double coalA, coalK;         // CT: A_c = coalA cbrt(eps); K_c = coalK rho eps (rho nu)
     double brA, brK;             // CT: Ab_c = brA cbrt(eps);  Kb_c = brK / (rho eps^(2/3))
-    double relax_over_dt, dt;
+    double relax, dt;            // limiter -relax n / dt (MOC.C:87-91)
     double *moments;             // may be NULL: [n_moments] atomicAdd
     int n_moments;
     double *cont_err_max;        // may be NULL: [1] atomic max (values >= 0)
@@ -332,7 +332,9 @@ __global__ void __launch_bounds__(BLOCK, 1) moc_source_kernel(const __grid_const
             const double B = R - gn;       // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
             R = fma_(cW[i], gn, R);
             const double C = A * sv[i * BLOCK + tid];
-            const double lim = -(p.relax_over_dt * ni); // MOC.C:87-91
+            // MOC.C:87-91: -relax n_i / dt with the reference's operation order (a true
+            // division), so that limited cells carry bit-identical values
+            const double lim = __dmul_rn(-p.relax, ni) / p.dt;
             double s = C + B;
             s = (s > lim) ? s : lim;
             if (p.S_out != nullptr && live) p.S_out[(size_t)i * p.stride + cell] = s;
