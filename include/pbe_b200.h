@@ -91,6 +91,13 @@ typedef struct pbe_moc pbe_moc;
 int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
                    double source_relaxation, pbe_moc **out);
 int pbe_moc_destroy(pbe_moc *moc);
+/* Two device kernels implement the same source path: the shared-memory kernel (any N the
+ * shared memory holds) and the tensor-memory kernel (accumulators in TMEM, 256 cells per CTA;
+ * N <= 118).  pbe_moc_create picks by occupancy; these calls let tests and benches pin one.
+ * Environment variable PBE_MOC_KERNEL=smem|tmem overrides the automatic choice at create. */
+enum { PBE_MOC_KERNEL_SMEM = 1, PBE_MOC_KERNEL_TMEM = 2 };
+int pbe_moc_set_kernel(pbe_moc *moc, int which); /* PBE_E_UNSUPPORTED if not available */
+int pbe_moc_get_kernel(pbe_moc *moc, int *which, int *cells_per_cta, int *ctas_per_sm);
 
 /* Optional fused outputs of one MOC launch; every pointer is a DEVICE pointer or NULL. */
 typedef struct pbe_moc_io {

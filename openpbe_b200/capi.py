@@ -18,6 +18,7 @@ COAL_NONE, COAL_CONSTANT, COAL_CT, COAL_TABLE = 0, 1, 2, 3
 BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
 DAUGHTER_UNIFORM_BINARY = 0
 QMOM_MAX_ORDER = 4
+MOC_KERNEL_SMEM, MOC_KERNEL_TMEM = 1, 2
 
 _dp = C.POINTER(C.c_double)
 _vp = C.c_void_p
@@ -74,6 +75,8 @@ PROTOTYPES = {
     "pbe_moc_create": (C.c_int, [_vp, C.c_int, C.c_double, C.POINTER(KernelSpec), C.c_double,
                                  C.POINTER(_vp)]),
     "pbe_moc_destroy": (C.c_int, [_vp]),
+    "pbe_moc_set_kernel": (C.c_int, [_vp, C.c_int]),
+    "pbe_moc_get_kernel": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "pbe_moc_source": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),
     "pbe_moc_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, C.POINTER(MocIO),
                                _vp]),

@@ -99,6 +99,34 @@ PBE_HD double exp_neg(double x) {
     return res;
 }
 
+// 2^y for y <= 0, |y| < 2^30 (the caller clamps; NaN propagates).  The pair loop of the TMEM
+// MOC kernel calls this once per class pair with y = (K_c log2 e) H_ij, so the argument
+// multiply replaces Cody-Waite: t = y + 1.5*2^52 rounds y to the nearest integer k, f = y - k
+// is exact, 2^f = 1 + f s(f) with s of degree 9 (tools/gen_exp2_coeffs.py: 5.7 ulp in exact
+// arithmetic; the rounding of y itself costs |y| ulp, which dominates).  13 FP64-pipe
+// instructions and 4 integer ones; results below 2^-1021 are flushed to 0.
+PBE_HD double exp2_neg_fast(double y) {
+    const double SHIFT = 6755399441055744.0; // 1.5 * 2^52
+    const double t = y + SHIFT;
+    const int k = lo_word(t);
+    const double f = y - (t - SHIFT);
+    double p = 7.0713011514345125e-09;
+    p = fma_(p, f, 1.020646529769823e-07);
+    p = fma_(p, f, 1.3215450204669348e-06);
+    p = fma_(p, f, 1.5252670450809624e-05);
+    p = fma_(p, f, 0.00015403530426708997);
+    p = fma_(p, f, 0.0013333558204141327);
+    p = fma_(p, f, 0.009618129107617852);
+    p = fma_(p, f, 0.055504108664637584);
+    p = fma_(p, f, 0.24022650695910078);
+    p = fma_(p, f, 0.6931471805599463);
+    p = fma_(p, f, 1.0);
+    const bool under = k < -1021;
+    const int hi = under ? 0 : hi_word(p) + (int)((unsigned)k << 20);
+    const int lo = under ? 0 : lo_word(p);
+    return make_double(hi, lo);
+}
+
 // pow(x, 1/3) with C pow() semantics for the arguments the reference feeds it
 // (coalescenceKernels/CoulaloglouTavlarides.C:75-76): negative finite x -> NaN, +-0 -> 0.
 PBE_HD double pow_third(double x) { return x < 0.0 ? NAN : cbrt(x); }

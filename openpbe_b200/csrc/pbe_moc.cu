@@ -1,12 +1,16 @@
 // pbe_moc.cu -- host side of the method-of-classes path: table construction at create time,
 // launch configuration, the host-buffer pipeline.  Kernels: pbe_moc_kernel.cuh.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <cmath>
 
 #include <algorithm>
 
 #include "pbe_common.h"
 #include "pbe_moc_kernel.cuh"
+#include "pbe_moc_tmem_kernel.cuh"
 
 using namespace pbe;
 
@@ -16,7 +20,14 @@ struct pbe_moc {
     double xi1 = 0, relax = 1.0;
     pbe_kernel_spec spec{};
     int dcoal = DCOAL_OFF, dbr = DBR_TAB;
-    int block = 128;       // cells per CTA
+    int block = 128;       // cells per CTA of the selected kernel
+    int smem_block = 128;  // shared-memory kernel: cells per CTA, CTAs per SM, bytes per CTA
+    int smem_ctas_per_sm = 1;
+    size_t smem_bytes = 0;
+    bool tmem_ok = false;  // tensor-memory kernel available for this N / table
+    bool use_tmem = false; // Blackwell fast path: accumulators in tensor memory, 256 cells per CTA
+    int tmem_cols = 0;     // TMEM columns per thread
+    size_t tmem_bytes = 0;
     int ctas_per_sm = 1;
     size_t smem = 0;
     MocParams base{};      // table pointers, chunk offsets, folded coefficients
@@ -44,8 +55,37 @@ moc_kernel_fn pick_kernel(int dcoal, int dbr) {
     return nullptr;
 }
 
+typedef void (*moct_kernel_fn)(const MocParams, const int);
+moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr) {
+#define PBE_PICK(C, B) \
+    if (dcoal == C && dbr == B) return (moct_kernel_fn)moc_tmem_kernel<C, B>;
+    PBE_PICK(DCOAL_OFF, DBR_TAB)
+    PBE_PICK(DCOAL_OFF, DBR_CT)
+    PBE_PICK(DCOAL_CT, DBR_TAB)
+    PBE_PICK(DCOAL_CT, DBR_CT)
+    PBE_PICK(DCOAL_SYM, DBR_TAB)
+    PBE_PICK(DCOAL_SYM, DBR_CT)
+    PBE_PICK(DCOAL_ASYM, DBR_TAB)
+    PBE_PICK(DCOAL_ASYM, DBR_CT)
+#undef PBE_PICK
+    return nullptr;
+}
+
 moc_kernel_fn kernel_for(const pbe_moc *m) {
-    return m->block == 128 ? pick_kernel<128>(m->dcoal, m->dbr) : pick_kernel<64>(m->dcoal, m->dbr);
+    return m->smem_block == 128 ? pick_kernel<128>(m->dcoal, m->dbr) : pick_kernel<64>(m->dcoal, m->dbr);
+}
+
+void select_kernel(pbe_moc *m, int which) {
+    m->use_tmem = (which == PBE_MOC_KERNEL_TMEM);
+    if (m->use_tmem) {
+        m->block = MOCT_BLOCK;
+        m->ctas_per_sm = 1;
+        m->smem = m->tmem_bytes;
+    } else {
+        m->block = m->smem_block;
+        m->ctas_per_sm = m->smem_ctas_per_sm;
+        m->smem = m->smem_bytes;
+    }
 }
 
 // Pair geometry of the Coulaloglou-Tavlarides coalescence kernel, with the reference's own
@@ -132,6 +172,14 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int64_t nb = (p.ncells + m->block - 1) / m->block;
     const int64_t cap = (int64_t)m->ctx->sm_count * m->ctas_per_sm;
     const int grid = (int)std::min<int64_t>(nb, cap);
+    if (m->use_tmem) {
+        moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr);
+        int cols = m->tmem_cols;
+        void *args[] = {(void *)&p, (void *)&cols};
+        PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
+        m->ctx->launches++;
+        return PBE_OK;
+    }
     moc_kernel_fn fn = kernel_for(m);
     void *args[] = {(void *)&p};
     PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
@@ -279,27 +327,54 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
         b.brK = c2 * sg * ((1 + gm) * (1 + gm));
     }
 
-    // ---- launch shape: 128 cells per CTA if the state fits in shared memory, else 64 ---------
-    m->block = 128;
-    m->smem = moc_smem_bytes(N, 128, b.chunk_max_pairs);
-    if (m->smem > ctx->smem_optin) {
-        m->block = 64;
-        m->smem = moc_smem_bytes(N, 64, b.chunk_max_pairs);
+    // ---- launch shape, shared-memory kernel: 128 cells per CTA if the state fits, else 64 -----
+    m->smem_block = 128;
+    m->smem_bytes = moc_smem_bytes(N, 128, b.chunk_max_pairs);
+    if (m->smem_bytes > ctx->smem_optin) {
+        m->smem_block = 64;
+        m->smem_bytes = moc_smem_bytes(N, 64, b.chunk_max_pairs);
     }
-    if (m->smem > ctx->smem_optin) {
+    if (m->smem_bytes > ctx->smem_optin) {
         set_error("pbe_moc_create: numberOfClasses %d needs %zu B of shared memory per CTA, device "
                   "offers %zu",
-                  N, m->smem, ctx->smem_optin);
+                  N, m->smem_bytes, ctx->smem_optin);
         delete m;
         return PBE_E_UNSUPPORTED;
     }
     moc_kernel_fn fn = kernel_for(m);
     cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)m->smem);
+                                         (int)m->smem_bytes);
     if (e == cudaSuccess) {
         int occ = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, m->block, m->smem);
-        m->ctas_per_sm = std::max(1, occ);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, m->smem_block,
+                                                          m->smem_bytes);
+        m->smem_ctas_per_sm = std::max(1, occ);
+    }
+    // ---- tensor-memory kernel (pbe_moc_tmem_kernel.cuh): 256 cells per CTA, accumulators in
+    // TMEM.  Available when the accumulators fit 256 columns per thread, n[N+1][256] fits in
+    // shared memory and (CT only) the H table spans less than 1e6, so that the clamp on K_c
+    // cannot change a result (see the kernel's header).
+    m->tmem_cols = moct_cols_per_thread(N);
+    m->tmem_bytes = moct_smem_bytes(N, b.chunk_max_pairs);
+    double hmax = 0.0, hmin = INFINITY;
+    if (m->dcoal == DCOAL_CT)
+        for (const double2 &v : tab)
+            if (v.x != 0.0) {
+                hmax = std::max(hmax, v.y);
+                hmin = std::min(hmin, v.y);
+            }
+    b.negK_floor = (hmax > 0.0) ? -1073741824.0 / hmax : -INFINITY;
+    m->tmem_ok = m->tmem_cols > 0 && m->tmem_bytes <= ctx->smem_optin &&
+                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= 1e-6 * hmax && std::isfinite(hmax)));
+    if (e == cudaSuccess && m->tmem_ok)
+        e = cudaFuncSetAttribute((const void *)pick_tmem_kernel(m->dcoal, m->dbr),
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m->tmem_bytes);
+    // auto rule: the shared-memory kernel keeps >= 3 CTAs (12 warps) per SM for small N; once
+    // shared memory caps it below that, TMEM accumulators give twice the warps per SM
+    select_kernel(m, (m->tmem_ok && m->smem_ctas_per_sm < 3) ? PBE_MOC_KERNEL_TMEM : PBE_MOC_KERNEL_SMEM);
+    if (const char *force = getenv("PBE_MOC_KERNEL")) {
+        if (strcmp(force, "smem") == 0) select_kernel(m, PBE_MOC_KERNEL_SMEM);
+        if (strcmp(force, "tmem") == 0 && m->tmem_ok) select_kernel(m, PBE_MOC_KERNEL_TMEM);
     }
     if (e == cudaSuccess && !tab.empty()) {
         e = cudaMalloc(&m->d_pair, tab.size() * sizeof(double2));
@@ -317,6 +392,26 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
     b.pair_tab = m->d_pair;
     b.cls = m->d_cls;
     *out = m;
+    return PBE_OK;
+}
+
+int pbe_moc_set_kernel(pbe_moc *m, int which) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_set_kernel: NULL handle");
+    PBE_REQUIRE(which == PBE_MOC_KERNEL_SMEM || which == PBE_MOC_KERNEL_TMEM, PBE_E_INVALID,
+                "pbe_moc_set_kernel: unknown kernel id %d", which);
+    PBE_REQUIRE(which != PBE_MOC_KERNEL_TMEM || m->tmem_ok, PBE_E_UNSUPPORTED,
+                "pbe_moc_set_kernel: the tensor-memory kernel is not available for numberOfClasses %d "
+                "(needs N <= %d, n[N+1][256] in shared memory and an H table spanning < 1e6)",
+                m->N, 128 - MOCT_PAD_CLASSES);
+    select_kernel(m, which);
+    return PBE_OK;
+}
+
+int pbe_moc_get_kernel(pbe_moc *m, int *which, int *cells_per_cta, int *ctas_per_sm) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_get_kernel: NULL handle");
+    if (which) *which = m->use_tmem ? PBE_MOC_KERNEL_TMEM : PBE_MOC_KERNEL_SMEM;
+    if (cells_per_cta) *cells_per_cta = m->block;
+    if (ctas_per_sm) *ctas_per_sm = m->ctas_per_sm;
     return PBE_OK;
 }
 

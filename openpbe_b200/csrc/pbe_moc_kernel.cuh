@@ -63,6 +63,7 @@ struct MocParams {
     double coalA, coalK;         // CT: A_c = coalA cbrt(eps); K_c = coalK rho eps (rho nu)
     double brA, brK;             // CT: Ab_c = brA cbrt(eps);  Kb_c = brK / (rho eps^(2/3))
     double relax, dt;            // limiter -relax n / dt (MOC.C:87-91)
+    double negK_floor;           // TMEM kernel: lower clamp of -K_c (pbe_moc_tmem_kernel.cuh)
     double *moments;             // may be NULL: [n_moments] atomicAdd
     int n_moments;
     double *cont_err_max;        // may be NULL: [1] atomic max (values >= 0)

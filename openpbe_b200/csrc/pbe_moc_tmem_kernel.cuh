@@ -1,0 +1,443 @@
+// pbe_moc_tmem_kernel.cuh -- method-of-classes source kernel, Blackwell fast path (sm_100a).
+//
+// Same arithmetic and the same traversal as pbe_moc_kernel.cuh (one thread per cell, each
+// unordered class pair evaluated once from the TMA-streamed {G,H} table, TI x TJ register
+// tiles), but the per-cell SOURCE ACCUMULATORS live in TENSOR MEMORY instead of shared memory:
+//
+//   * ncu on the shared-memory kernel (profiles/r01a_moc_ncu_details.txt) shows the FP64 pipe
+//     53 % busy with ONE warp per scheduler: 206 KB of shared memory per 128 cells is what caps
+//     the occupancy, and every fixed-latency dependency stall is exposed.
+//   * TMEM is 128 lanes x 512 32-bit columns per SM and idle on this path (no tensor-core
+//     work).  With the 32x32b access shape every thread owns one lane: 512 columns = 256
+//     doubles of private scratch.  Two warps share a lane quarter and split the columns, so
+//     a thread gets 256 columns = 128 FP64 accumulators -- enough for N <= 118 classes.
+//   * Shared memory then only holds the class densities n[N+1][256] (207 KB at N = 100), the
+//     table ring and the per-class tables: 256 cells = 8 warps per SM, two per scheduler, which
+//     is what hides the DFMA / LDS / LDTM latencies.
+//
+// Accumulator class c of a thread sits in columns colbase + 2c, 2c+1 of its lane.  A tile
+// retires its 4 column sums and 4 anti-diagonal sums with one tcgen05.ld.32x32b.x8 /
+// tcgen05.st.32x32b.x8 pair each (SASS LDTM / STTM).  Classes N .. N+9 are scratch bins for the
+// zero-weight padding slots of edge tiles, so no index is clamped on the accumulator side.
+#pragma once
+
+#include "pbe_moc_kernel.cuh"
+
+namespace pbe {
+
+constexpr int MOCT_BLOCK = 256;     // cells (threads) per CTA
+constexpr int MOCT_PAD_CLASSES = 10; // scratch bins above class N-1 (see header)
+
+// ---- TMEM helpers (PTX ISA 8.6 tcgen05; SASS UTCALLOC / LDTM / STTM) -------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(smem_dst)),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_fence_before_sync() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_fence_after_sync() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() {
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// four consecutive FP64 accumulators of this thread's lane
+struct Tm4 {
+    uint32_t r[8];
+};
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, Tm4 &v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v.r[0]), "=r"(v.r[1]), "=r"(v.r[2]), "=r"(v.r[3]), "=r"(v.r[4]),
+                   "=r"(v.r[5]), "=r"(v.r[6]), "=r"(v.r[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+// tcgen05.wait::ld with the loaded registers as in/out operands: a true dependency, so no
+// consumer of v can be scheduled above the wait
+__device__ __forceinline__ void tmem_wait_ld(Tm4 &v) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v.r[0]), "+r"(v.r[1]), "+r"(v.r[2]), "+r"(v.r[3]), "+r"(v.r[4]),
+                   "+r"(v.r[5]), "+r"(v.r[6]), "+r"(v.r[7])::"memory");
+}
+__device__ __forceinline__ void tmem_wait_ld(Tm4 &a, Tm4 &b) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(a.r[0]), "+r"(a.r[1]), "+r"(a.r[2]), "+r"(a.r[3]), "+r"(a.r[4]),
+                   "+r"(a.r[5]), "+r"(a.r[6]), "+r"(a.r[7]), "+r"(b.r[0]), "+r"(b.r[1]),
+                   "+r"(b.r[2]), "+r"(b.r[3]), "+r"(b.r[4]), "+r"(b.r[5]), "+r"(b.r[6]),
+                   "+r"(b.r[7])::"memory");
+}
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, const Tm4 &v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::
+                     "r"(taddr),
+                 "r"(v.r[0]), "r"(v.r[1]), "r"(v.r[2]), "r"(v.r[3]), "r"(v.r[4]), "r"(v.r[5]),
+                 "r"(v.r[6]), "r"(v.r[7])
+                 : "memory");
+}
+__device__ __forceinline__ double tm_get(const Tm4 &v, int k) {
+    return __hiloint2double((int)v.r[2 * k + 1], (int)v.r[2 * k]);
+}
+__device__ __forceinline__ void tm_set(Tm4 &v, int k, double x) {
+    v.r[2 * k] = (uint32_t)__double2loint(x);
+    v.r[2 * k + 1] = (uint32_t)__double2hiint(x);
+}
+// acc[c0 .. c0+3] += sgn * add[0..3]   (v holds the loaded accumulators)
+__device__ __forceinline__ void tm_axpy4(Tm4 &v, double sgn, const double *add) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) tm_set(v, k, fma_(sgn, add[k], tm_get(v, k)));
+}
+
+// shared-memory footprint of one CTA of the TMEM kernel
+__host__ __device__ inline size_t moct_smem_bytes(int N, int chunk_max_pairs) {
+    size_t b = 0;
+    b += (size_t)(N + 1) * MOCT_BLOCK * sizeof(double);   // n_s (row N = zero dummy class)
+    b += (size_t)2 * chunk_max_pairs * sizeof(double2);   // table ring
+    b += (size_t)CLS_ROWS * (N + 1) * sizeof(double);     // per-class tables
+    b += 2 * sizeof(uint64_t) + 16;                       // mbarriers, TMEM base address
+    return b;
+}
+// TMEM columns per thread: 2 per accumulator, N + pad classes rounded up to whole x8 groups,
+// then to a power of two >= 32 (allocation granularity); 0 if it does not fit
+__host__ __device__ inline int moct_cols_per_thread(int N) {
+    const int need = ((2 * (N + MOCT_PAD_CLASSES) + 7) / 8) * 8;
+    int c = 32;
+    while (c < need) c *= 2;
+    return c <= 256 ? c : 0;
+}
+
+// ---- one TI x TJ tile of class pairs (register tile; identical sums to moc_tile) ---------------
+// K2 = -K_c log2(e): the Coulaloglou-Tavlarides efficiency exp(-K_c H_ij) is 2^(K2 H_ij)
+// (coalescenceKernels/CoulaloglouTavlarides.C:84-88).
+template <int COAL>
+__device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, double K2,
+                                          const double (&ni)[MOC_TI], const double (&nj)[MOC_TJ],
+                                          double (&di)[MOC_TI], double (&dj)[MOC_TJ],
+                                          double (&bw)[MOC_TI + MOC_TJ - 1]) {
+#pragma unroll
+    for (int r = 0; r < MOC_TI; ++r) {
+#pragma unroll
+        for (int c = 0; c < MOC_TJ; ++c) {
+            const double2 gh = tab[r * MOC_TJ + c];
+            const double w = ni[r] * nj[c];
+            if (COAL == DCOAL_CT) {
+                const double e = exp2_neg_fast(K2 * gh.y);
+                const double eg = e * gh.x;
+                di[r] = fma_(eg, w, di[r]);
+                dj[c] = fma_(eg, w, dj[c]);
+                bw[r + c] = fma_(eg, w, bw[r + c]);
+            } else if (COAL == DCOAL_SYM) {
+                di[r] = fma_(gh.x, w, di[r]);
+                dj[c] = fma_(gh.x, w, dj[c]);
+                bw[r + c] = fma_(gh.x, w, bw[r + c]);
+            } else { // DCOAL_ASYM: x = S(xi_i, xi_j), y = S(xi_j, xi_i)
+                const double t1 = gh.x * w, t2 = gh.y * w;
+                di[r] += t1;
+                dj[c] += t2;
+                bw[r + c] += 0.5 * (t1 + t2);
+            }
+        }
+    }
+}
+
+// ---- all pairs owned by row block blk (rows i0 .. i0+TI-1) ------------------------------------
+// tacc = TMEM address of this thread's accumulator 0.
+template <int COAL>
+__device__ __forceinline__ void moct_row_block(const MocParams &p, int blk,
+                                               const double2 *__restrict__ tab, double K2,
+                                               const double *__restrict__ n_s, uint32_t tacc,
+                                               int tid) {
+    const int N = p.N;
+    const int i0 = blk * MOC_TI;
+    const int ntiles = (p.chunk_off[blk + 1] - p.chunk_off[blk]) / (MOC_TI * MOC_TJ);
+    // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets j0.. of the
+    // same tile, so the two read-modify-writes are serialised; every other block issues both
+    // loads before the tile's arithmetic and hides the TMEM latency behind it
+    const bool alias = (i0 + 1 < MOC_TJ);
+    double ni[MOC_TI], di[MOC_TI], bw[MOC_TI + MOC_TJ - 1];
+#pragma unroll
+    for (int r = 0; r < MOC_TI; ++r) {
+        ni[r] = n_s[min(i0 + r, N) * MOCT_BLOCK + tid];
+        di[r] = 0.0;
+    }
+#pragma unroll
+    for (int q = 0; q < MOC_TI + MOC_TJ - 1; ++q) bw[q] = 0.0;
+
+    int j0 = i0;
+#pragma unroll 1
+    for (int t = 0; t < ntiles; ++t, j0 += MOC_TJ, tab += MOC_TI * MOC_TJ) {
+        double nj[MOC_TJ], dj[MOC_TJ];
+#pragma unroll
+        for (int c = 0; c < MOC_TJ; ++c) {
+            nj[c] = n_s[min(j0 + c, N) * MOCT_BLOCK + tid];
+            dj[c] = 0.0;
+        }
+        const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
+        const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
+        Tm4 vd, vb;
+        tmem_wait_st(); // the previous tile's stores have landed
+        if (!alias) {
+            tmem_ld4(a_dj, vd);
+            tmem_ld4(a_bw, vb);
+        }
+        moct_tile<COAL>(tab, K2, ni, nj, di, dj, bw);
+        if (!alias) {
+            tmem_wait_ld(vd, vb);
+            tm_axpy4(vd, -1.0, dj); // death of class j
+            tm_axpy4(vb, 1.0, bw);  // birth of class i+j+1: the TJ lowest anti-diagonals
+            tmem_st4(a_dj, vd);
+            tmem_st4(a_bw, vb);
+        } else {
+            tmem_ld4(a_dj, vd);
+            tmem_wait_ld(vd);
+            tm_axpy4(vd, -1.0, dj);
+            tmem_st4(a_dj, vd);
+            tmem_wait_st();
+            tmem_ld4(a_bw, vb);
+            tmem_wait_ld(vb);
+            tm_axpy4(vb, 1.0, bw);
+            tmem_st4(a_bw, vb);
+        }
+#pragma unroll
+        for (int q = 0; q < MOC_TI + MOC_TJ - 1; ++q)
+            bw[q] = (q + MOC_TJ < MOC_TI + MOC_TJ - 1) ? bw[q + MOC_TJ] : 0.0;
+    }
+    // flush the TI-1 anti-diagonals still in the window and the row sums (death of class i);
+    // the two targets never overlap (i0 + j0 + 1 > i0 + TI - 1 because j0 >= i0 + TJ here)
+    {
+        const uint32_t a_k = tacc + 2u * (uint32_t)(i0 + j0 + 1);
+        const uint32_t a_i = tacc + 2u * (uint32_t)i0;
+        Tm4 vk, vi;
+        tmem_wait_st();
+        tmem_ld4(a_k, vk);
+        tmem_ld4(a_i, vi);
+        tmem_wait_ld(vk, vi);
+        tm_axpy4(vk, 1.0, bw); // bw[TI-1 ..] are zero after the shift
+        tm_axpy4(vi, -1.0, di);
+        tmem_st4(a_k, vk);
+        tmem_st4(a_i, vi);
+    }
+}
+
+// ---- the kernel: one persistent CTA per SM, 256 cells per batch ---------------------------------
+// p.negK_floor (MocParams) = -2^30 / max H: with it the 2^y argument stays inside
+// exp2_neg_fast's |y| < 2^31 contract; the host only selects this kernel when every H_ij >=
+// 1e-6 max H, so a clamped cell has every efficiency < 2^-1021 = 0 either way.
+template <int COAL, int BR>
+__global__ void __launch_bounds__(MOCT_BLOCK, 1)
+    moc_tmem_kernel(const __grid_constant__ MocParams p, const int tmem_cols_per_thread) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int BLOCK = MOCT_BLOCK;
+    const int N = p.N;
+    const int tid = threadIdx.x;
+    double2 *ring = reinterpret_cast<double2 *>(smem_raw);
+    double *n_s = reinterpret_cast<double *>(ring + 2 * (size_t)p.chunk_max_pairs);
+    double *cls_s = n_s + (size_t)(N + 1) * BLOCK;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(cls_s + CLS_ROWS * (N + 1));
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 2);
+
+    const int64_t nbatches = (p.ncells + BLOCK - 1) / BLOCK;
+    const int64_t my_batches =
+        (nbatches > (int64_t)blockIdx.x) ? (nbatches - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t total_q = (COAL == DCOAL_OFF) ? 0 : my_batches * p.nblocks;
+
+    // ---- tensor-memory accumulators: warp 0 allocates 2 x cols_per_thread columns -------------
+    const uint32_t tmem_cols = 2u * (uint32_t)tmem_cols_per_thread;
+    if (tid < 32) tmem_alloc(tmem_base_s, tmem_cols);
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+    }
+    for (int k = tid; k < CLS_ROWS * (N + 1); k += BLOCK) cls_s[k] = p.cls[k];
+    n_s[N * BLOCK + tid] = 0.0; // dummy class: absorbs padded table slots
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    const uint32_t tmem_base = *tmem_base_s;
+    const int warp = tid >> 5;
+    // lane quarter of this warp in bits 31:16, this thread's column half in bits 15:0
+    const uint32_t tacc = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) +
+                          (uint32_t)((warp >> 2) * tmem_cols_per_thread);
+    const int n_acc_groups = (N + MOCT_PAD_CLASSES + 3) / 4;
+
+    auto issue = [&](int64_t q) {
+        const int blk = (int)(q % p.nblocks);
+        const int off = p.chunk_off[blk];
+        const unsigned bytes = (unsigned)(p.chunk_off[blk + 1] - off) * (unsigned)sizeof(double2);
+        uint64_t *bar = &bars[q & 1];
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(ring + (q & 1) * (size_t)p.chunk_max_pairs, p.pair_tab + off, bytes, bar);
+    };
+    if (tid == 0) {
+        if (0 < total_q) issue(0);
+        if (1 < total_q) issue(1);
+    }
+
+    const double *cBP = cls_s + CLS_BR_P * (N + 1);
+    const double *cBQ = cls_s + CLS_BR_Q * (N + 1);
+    const double *cW = cls_s + CLS_W * (N + 1);
+    const double *cDV = cls_s + CLS_DVOL * (N + 1);
+    const double *cXI = cls_s + CLS_XI * (N + 1);
+
+    double macc[MOC_MAX_MOMENTS];
+#pragma unroll
+    for (int k = 0; k < MOC_MAX_MOMENTS; ++k) macc[k] = 0.0;
+    double cerr = 0.0;
+    const bool want_diag = (p.moments != nullptr) || (p.cont_err_max != nullptr);
+
+    int64_t q = 0;
+    for (int64_t batch = blockIdx.x; batch < nbatches; batch += gridDim.x) {
+        const int64_t cell = batch * BLOCK + tid;
+        const bool live = cell < p.ncells;
+        const int64_t cc = live ? cell : p.ncells - 1;
+
+        // stage this cell's class densities (coalesced: lane = cell); pull the next batch's
+        // lines into L2 meanwhile (one request per 32-B sector)
+        {
+            const double *src = p.n_in + cc;
+            const int64_t ncell = cell + (int64_t)gridDim.x * BLOCK;
+            const bool pf = ((tid & 3) == 0) && (ncell < p.ncells);
+#pragma unroll 10
+            for (int i = 0; i < N; ++i) {
+                n_s[i * BLOCK + tid] = __ldg(src + (size_t)i * p.stride);
+                if (pf)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p.n_in + (size_t)i * p.stride + ncell));
+            }
+        }
+        // zero the accumulators (classes 0 .. N+pad, whole x8 groups)
+        if (COAL != DCOAL_OFF) {
+            Tm4 z;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) z.r[k] = 0u;
+            for (int g = 0; g < n_acc_groups; ++g) tmem_st4(tacc + 8u * (uint32_t)g, z);
+        }
+        const double eps = __ldg(p.eps + cc), rho = __ldg(p.rho + cc), nu = __ldg(p.nu + cc);
+        const double eps13 = cbrt(eps);
+        double A = 1.0, K2 = 0.0;
+        if (COAL == DCOAL_CT) {
+            A = p.coalA * eps13;
+            double negK = -(p.coalK * rho * eps * (rho * nu));
+            negK = (negK < p.negK_floor) ? p.negK_floor : negK; // NaN stays NaN
+            K2 = negK * 1.4426950408889634074;
+        }
+
+        if (COAL != DCOAL_OFF) {
+#pragma unroll 1
+            for (int blk = 0; blk < p.nblocks; ++blk, ++q) {
+                mbar_wait(&bars[q & 1], (unsigned)((q >> 1) & 1));
+                moct_row_block<COAL>(p, blk, ring + (q & 1) * (size_t)p.chunk_max_pairs, K2, n_s,
+                                     tacc, tid);
+                __syncthreads(); // every warp is done with ring slot q&1
+                if (tid == 0 && q + 2 < total_q) issue(q + 2);
+            }
+            tmem_wait_st();
+        }
+
+        // ---- epilogue: breakup (suffix sum), limiter, update, d, diagnostics ----------------
+        double Ab = 0.0, negKb = 0.0;
+        if (BR == DBR_CT) {
+            Ab = p.brA * eps13;
+            negKb = -(p.brK / (rho * (eps13 * eps13)));
+        }
+        double R = 0.0, sum_d = 0.0, sum_n = 0.0;
+        double mloc[MOC_MAX_MOMENTS];
+#pragma unroll
+        for (int k = 0; k < MOC_MAX_MOMENTS; ++k) mloc[k] = 0.0;
+#pragma unroll 1
+        for (int c4 = ((N - 1) >> 2) << 2; c4 >= 0; c4 -= 4) {
+            Tm4 v;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v.r[k] = 0u;
+            if (COAL != DCOAL_OFF) {
+                tmem_ld4(tacc + 2u * (uint32_t)c4, v);
+                tmem_wait_ld(v);
+            }
+#pragma unroll
+            for (int r = 3; r >= 0; --r) {
+                const int i = c4 + r;
+                if (i < N) {
+                    const double ni = n_s[i * BLOCK + tid];
+                    // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
+                    double g = cBP[i];
+                    if (BR == DBR_CT) g = (Ab * g) * exp_neg(negKb * cBQ[i]);
+                    const double gn = g * ni;
+                    const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
+                    R = fma_(cW[i], gn, R);
+                    const double C = A * tm_get(v, r);
+                    // MOC.C:87-91: -relax n_i / dt, a true division as in the reference
+                    const double lim = __dmul_rn(-p.relax, ni) / p.dt;
+                    double s = C + B;
+                    s = (s > lim) ? s : lim;
+                    if (p.S_out != nullptr && live) p.S_out[(size_t)i * p.stride + cell] = s;
+                    double nn = ni;
+                    if (p.do_step) {
+                        nn = __dadd_rn(ni, __dmul_rn(p.dt, s)); // n += dt S (MOC.C:259-272, phi = 0)
+                        if (live) p.n_out[(size_t)i * p.stride + cell] = nn;
+                    }
+                    sum_d = fma_(cDV[i], nn, sum_d);
+                    sum_n += nn;
+                    if (want_diag) {
+                        const double x = cXI[i];
+                        double pw = nn;
+#pragma unroll
+                        for (int k = 0; k < MOC_MAX_MOMENTS; ++k) {
+                            if (k < p.n_moments || k == 1) mloc[k] += pw;
+                            pw *= x;
+                        }
+                    }
+                }
+            }
+        }
+        if (p.d_out != nullptr && live) p.d_out[cell] = sum_d / sum_n; // MOC.C:282-290
+        if (want_diag && live) {
+            const double V = (p.vcell != nullptr) ? __ldg(p.vcell + cell) : 1.0;
+#pragma unroll
+            for (int k = 0; k < MOC_MAX_MOMENTS; ++k) macc[k] = fma_(V, mloc[k], macc[k]);
+            if (p.cont_err_max != nullptr && p.alpha != nullptr) {
+                const double e = fabs(mloc[1] / V - __ldg(p.alpha + cell)); // MOC.C:254-279
+                cerr = (e > cerr) ? e : cerr;
+            }
+        }
+    }
+
+    if (want_diag) {
+        // block reduction through the (now idle) n_s columns, one atomic per CTA per value
+        __syncthreads();
+        double *red = n_s;
+        for (int k = 0; k < MOC_MAX_MOMENTS + 1; ++k) {
+            const bool is_err = (k == MOC_MAX_MOMENTS);
+            if (!is_err && (p.moments == nullptr || k >= p.n_moments)) continue;
+            if (is_err && p.cont_err_max == nullptr) continue;
+            double v = is_err ? cerr : macc[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double u = __shfl_xor_sync(0xffffffffu, v, o);
+                v = is_err ? ((u > v) ? u : v) : (v + u);
+            }
+            if ((tid & 31) == 0) red[tid >> 5] = v;
+            __syncthreads();
+            if (tid == 0) {
+                double t = red[0];
+                for (int w = 1; w < BLOCK / 32; ++w) t = is_err ? ((red[w] > t) ? red[w] : t) : t + red[w];
+                if (is_err)
+                    atomic_max_nonneg(p.cont_err_max, t);
+                else
+                    atomicAdd(p.moments + k, t);
+            }
+            __syncthreads();
+        }
+    }
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+} // namespace pbe

@@ -201,6 +201,17 @@ class MOC:
         except Exception:
             pass
 
+    def set_kernel(self, which: str):
+        """Pin the device kernel: "smem" or "tmem" (raises PbeError if unavailable for this N)."""
+        ids = {"smem": capi.MOC_KERNEL_SMEM, "tmem": capi.MOC_KERNEL_TMEM}
+        capi.check(capi.lib().pbe_moc_set_kernel(self._h, ids[which]))
+
+    def kernel(self):
+        w, b, c = C.c_int(), C.c_int(), C.c_int()
+        capi.check(capi.lib().pbe_moc_get_kernel(self._h, C.byref(w), C.byref(b), C.byref(c)))
+        return {"kernel": {capi.MOC_KERNEL_SMEM: "smem", capi.MOC_KERNEL_TMEM: "tmem"}[w.value],
+                "cells_per_cta": b.value, "ctas_per_sm": c.value}
+
     def _dims(self, n):
         assert n.dim() == 2 and n.shape[0] == self.N and n.stride(1) in (0, 1)
         ncells = n.shape[1]
