@@ -125,6 +125,7 @@ int pbe_ctx_create(int device, pbe_ctx **out) {
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
     ctx->hbm_bytes = prop.totalGlobalMem;
     strncpy(ctx->name, prop.name, sizeof(ctx->name) - 1);
     for (int s = 0; s < kHostSlots; ++s) {

@@ -40,6 +40,7 @@ struct pbe_ctx {
     int device = 0;
     int sm_count = 0;
     size_t smem_optin = 0;
+    size_t smem_per_sm = 0;
     size_t hbm_bytes = 0;
     char name[128] = {0};
     std::atomic<int64_t> launches{0};

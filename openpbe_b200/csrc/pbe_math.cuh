@@ -104,7 +104,7 @@ PBE_HD double exp_neg(double x) {
 // multiply replaces Cody-Waite: t = y + 1.5*2^52 rounds y to the nearest integer k, f = y - k
 // is exact, 2^f = 1 + f s(f) with s of degree 9 (tools/gen_exp2_coeffs.py: 5.7 ulp in exact
 // arithmetic; the rounding of y itself costs |y| ulp, which dominates).  13 FP64-pipe
-// instructions and 4 integer ones; results below 2^-1021 are flushed to 0.
+// instructions and 2 integer ones.
 PBE_HD double exp2_neg_fast(double y) {
     const double SHIFT = 6755399441055744.0; // 1.5 * 2^52
     const double t = y + SHIFT;
@@ -121,9 +121,12 @@ PBE_HD double exp2_neg_fast(double y) {
     p = fma_(p, f, 0.24022650695910078);
     p = fma_(p, f, 0.6931471805599463);
     p = fma_(p, f, 1.0);
-    const bool under = k < -1021;
-    const int hi = under ? 0 : hi_word(p) + (int)((unsigned)k << 20);
-    const int lo = under ? 0 : lo_word(p);
+    // 2^k by an integer add on the exponent field (p is in [0.70, 1.42): field 1022 or 1023).
+    // k is clamped at -1022 instead of testing for underflow: results below 2^-1022 come out
+    // as a denormal-range value < 2.3e-308 where exp() itself is denormal.
+    const int kc = (k > -1022) ? k : -1022;
+    const int hi = hi_word(p) + (int)((unsigned)kc << 20);
+    const int lo = lo_word(p);
     return make_double(hi, lo);
 }
 

@@ -26,8 +26,10 @@ struct pbe_moc {
     size_t smem_bytes = 0;
     bool tmem_ok = false;  // tensor-memory kernel available for this N / table
     bool use_tmem = false; // Blackwell fast path: accumulators in tensor memory, 256 cells per CTA
-    int tmem_cols = 0;     // TMEM columns per thread
+    int tmem_cols = 0;     // TMEM columns per thread (= per CTA: one lane per thread)
+    int tmem_ctas_per_sm = 1;
     size_t tmem_bytes = 0;
+    MoctSched sched{};     // ring schedule of the tensor-memory kernel
     int ctas_per_sm = 1;
     size_t smem = 0;
     MocParams base{};      // table pointers, chunk offsets, folded coefficients
@@ -55,7 +57,7 @@ moc_kernel_fn pick_kernel(int dcoal, int dbr) {
     return nullptr;
 }
 
-typedef void (*moct_kernel_fn)(const MocParams, const int);
+typedef void (*moct_kernel_fn)(const MocParams, const MoctSched);
 moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr) {
 #define PBE_PICK(C, B) \
     if (dcoal == C && dbr == B) return (moct_kernel_fn)moc_tmem_kernel<C, B>;
@@ -79,7 +81,7 @@ void select_kernel(pbe_moc *m, int which) {
     m->use_tmem = (which == PBE_MOC_KERNEL_TMEM);
     if (m->use_tmem) {
         m->block = MOCT_BLOCK;
-        m->ctas_per_sm = 1;
+        m->ctas_per_sm = m->tmem_ctas_per_sm;
         m->smem = m->tmem_bytes;
     } else {
         m->block = m->smem_block;
@@ -174,8 +176,7 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int grid = (int)std::min<int64_t>(nb, cap);
     if (m->use_tmem) {
         moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr);
-        int cols = m->tmem_cols;
-        void *args[] = {(void *)&p, (void *)&cols};
+        void *args[] = {(void *)&p, (void *)&m->sched};
         PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
         m->ctx->launches++;
         return PBE_OK;
@@ -350,12 +351,36 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
                                                           m->smem_bytes);
         m->smem_ctas_per_sm = std::max(1, occ);
     }
-    // ---- tensor-memory kernel (pbe_moc_tmem_kernel.cuh): 256 cells per CTA, accumulators in
-    // TMEM.  Available when the accumulators fit 256 columns per thread, n[N+1][256] fits in
-    // shared memory and (CT only) the H table spans less than 1e6, so that the clamp on K_c
-    // cannot change a result (see the kernel's header).
-    m->tmem_cols = moct_cols_per_thread(N);
-    m->tmem_bytes = moct_smem_bytes(N, b.chunk_max_pairs);
+    // ---- tensor-memory kernel (pbe_moc_tmem_kernel.cuh): 128 cells per CTA, accumulators in
+    // TMEM, two or more CTAs per SM.  Available when the accumulators fit 256 columns per
+    // thread, n[N+1][128] fits in shared memory and (CT only) the H table spans less than 1e6, so
+    // that the clamp on K_c cannot change a result (see the kernel's header).  Its table ring
+    // holds sub-chunks of at most MOCT_SUB_TILES tiles of one row block.
+    {
+        MoctSched &sc = m->sched;
+        sc.nsubs = 0;
+        sc.slot_pairs = 1;
+        sc.sub_off[0] = 0;
+        bool fits = true;
+        for (int blk = 0; blk < b.nblocks && fits; ++blk) {
+            sc.blk_sub0[blk] = (unsigned short)sc.nsubs;
+            const int ntiles = (b.chunk_off[blk + 1] - b.chunk_off[blk]) / (MOC_TI * MOC_TJ);
+            for (int t0 = 0; t0 < ntiles; t0 += MOCT_SUB_TILES) {
+                if (sc.nsubs >= MOCT_MAX_SUBS) {
+                    fits = false;
+                    break;
+                }
+                const int nt = std::min(MOCT_SUB_TILES, ntiles - t0);
+                sc.sub_off[sc.nsubs + 1] = sc.sub_off[sc.nsubs] + nt * MOC_TI * MOC_TJ;
+                sc.slot_pairs = std::max(sc.slot_pairs, nt * MOC_TI * MOC_TJ);
+                ++sc.nsubs;
+            }
+        }
+        sc.blk_sub0[b.nblocks] = (unsigned short)sc.nsubs;
+        m->tmem_cols = fits ? moct_cols_per_thread(N) : 0;
+        sc.tmem_cols = m->tmem_cols;
+        m->tmem_bytes = moct_smem_bytes(N, sc.slot_pairs);
+    }
     double hmax = 0.0, hmin = INFINITY;
     if (m->dcoal == DCOAL_CT)
         for (const double2 &v : tab)
@@ -364,14 +389,47 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
                 hmin = std::min(hmin, v.y);
             }
     b.negK_floor = (hmax > 0.0) ? -1073741824.0 / hmax : -INFINITY;
+    double qmax = 0.0, qmin = INFINITY; // CT breakup exponent table xi^(-5/9)
+    if (m->dbr == DBR_CT)
+        for (int i = 0; i < N; ++i) {
+            qmax = std::max(qmax, cls[(size_t)CLS_BR_Q * (N + 1) + i]);
+            qmin = std::min(qmin, cls[(size_t)CLS_BR_Q * (N + 1) + i]);
+        }
+    b.negKb_floor = (qmax > 0.0) ? -1073741824.0 / qmax : -INFINITY;
     m->tmem_ok = m->tmem_cols > 0 && m->tmem_bytes <= ctx->smem_optin &&
-                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= 1e-6 * hmax && std::isfinite(hmax)));
-    if (e == cudaSuccess && m->tmem_ok)
-        e = cudaFuncSetAttribute((const void *)pick_tmem_kernel(m->dcoal, m->dbr),
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m->tmem_bytes);
-    // auto rule: the shared-memory kernel keeps >= 3 CTAs (12 warps) per SM for small N; once
-    // shared memory caps it below that, TMEM accumulators give twice the warps per SM
-    select_kernel(m, (m->tmem_ok && m->smem_ctas_per_sm < 3) ? PBE_MOC_KERNEL_TMEM : PBE_MOC_KERNEL_SMEM);
+                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= 1e-6 * hmax && std::isfinite(hmax))) &&
+                 (m->dbr != DBR_CT || (qmax > 0.0 && qmin >= 1e-6 * qmax && std::isfinite(qmax)));
+    if (e == cudaSuccess && m->tmem_ok) {
+        const void *tfn = (const void *)pick_tmem_kernel(m->dcoal, m->dbr);
+        e = cudaFuncSetAttribute(tfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m->tmem_bytes);
+        cudaFuncAttributes fa{};
+        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, tfn);
+        if (e == cudaSuccess) {
+            // cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for a kernel that holds a
+            // tcgen05.alloc (it cannot see the column count), so the residency limit is computed
+            // here: registers (allocated per warp in units of 256), shared memory (+1 KB the
+            // driver reserves per CTA) and the SM's 512 TMEM columns.
+            const int regs_per_warp = ((fa.numRegs * 32 + 255) / 256) * 256;
+            const int by_regs = 65536 / (regs_per_warp * (MOCT_BLOCK / 32));
+            const int by_smem = (int)(ctx->smem_per_sm / (m->tmem_bytes + fa.sharedSizeBytes + 1024));
+            const int by_tmem = 512 / m->tmem_cols;
+            m->tmem_ctas_per_sm = std::max(1, std::min(std::min(by_regs, by_smem), std::min(by_tmem, 4)));
+            if (const char *f = getenv("PBE_MOC_TMEM_CTAS")) m->tmem_ctas_per_sm = std::max(1, atoi(f));
+            // stagger = 1/k of the batch time of a CTA running alone: FP64-pipe instructions per
+            // cell (19 per pair, 45 per class) x 2 cycles at the ~60 % pipe use of one warp per
+            // scheduler (profiles/r01a)
+            double frac = 1.0;
+            if (const char *f = getenv("PBE_MOC_STAGGER")) frac = atof(f);
+            const double solo = (19.0 * (double)(tab.size()) + 45.0 * N) * 2.0 / 0.6;
+            m->sched.stagger_cycles =
+                (m->tmem_ctas_per_sm > 1) ? (int)std::min(2.0e9, frac * solo / m->tmem_ctas_per_sm) : 0;
+        }
+    }
+    // auto rule: the tensor-memory kernel wherever it keeps at least as many warps per SM as the
+    // shared-memory kernel (it has the shorter instruction stream per pair)
+    select_kernel(m, (m->tmem_ok && m->tmem_ctas_per_sm * MOCT_BLOCK >= m->smem_ctas_per_sm * m->smem_block)
+                         ? PBE_MOC_KERNEL_TMEM
+                         : PBE_MOC_KERNEL_SMEM);
     if (const char *force = getenv("PBE_MOC_KERNEL")) {
         if (strcmp(force, "smem") == 0) select_kernel(m, PBE_MOC_KERNEL_SMEM);
         if (strcmp(force, "tmem") == 0 && m->tmem_ok) select_kernel(m, PBE_MOC_KERNEL_TMEM);

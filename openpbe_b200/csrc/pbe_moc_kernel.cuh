@@ -64,6 +64,7 @@ struct MocParams {
     double brA, brK;             // CT: Ab_c = brA cbrt(eps);  Kb_c = brK / (rho eps^(2/3))
     double relax, dt;            // limiter -relax n / dt (MOC.C:87-91)
     double negK_floor;           // TMEM kernel: lower clamp of -K_c (pbe_moc_tmem_kernel.cuh)
+    double negKb_floor;          // TMEM kernel: lower clamp of -Kb_c
     double *moments;             // may be NULL: [n_moments] atomicAdd
     int n_moments;
     double *cont_err_max;        // may be NULL: [1] atomic max (values >= 0)

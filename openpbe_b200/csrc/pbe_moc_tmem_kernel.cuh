@@ -8,25 +8,32 @@
 //     53 % busy with ONE warp per scheduler: 206 KB of shared memory per 128 cells is what caps
 //     the occupancy, and every fixed-latency dependency stall is exposed.
 //   * TMEM is 128 lanes x 512 32-bit columns per SM and idle on this path (no tensor-core
-//     work).  With the 32x32b access shape every thread owns one lane: 512 columns = 256
-//     doubles of private scratch.  Two warps share a lane quarter and split the columns, so
-//     a thread gets 256 columns = 128 FP64 accumulators -- enough for N <= 118 classes.
-//   * Shared memory then only holds the class densities n[N+1][256] (207 KB at N = 100), the
-//     table ring and the per-class tables: 256 cells = 8 warps per SM, two per scheduler, which
-//     is what hides the DFMA / LDS / LDTM latencies.
+//     work).  With the 32x32b access shape every thread of a 128-thread CTA owns one lane; a
+//     CTA that allocates 256 columns gives each thread 128 FP64 accumulators -- enough for
+//     N <= 118 classes -- and TWO such CTAs fit one SM's 512 columns.
+//   * Shared memory then only holds the class densities n[N+1][128] (103 KB at N = 100) and the
+//     table ring (2 x 3.3 KB): two CTAs = 256 cells = 8 warps per SM, two per scheduler.  The
+//     two CTAs are independent, so one is usually inside the FP64-dense pair sweep while the
+//     other runs its latency-bound staging loads or epilogue (ncu r01b: with one 256-thread
+//     CTA per SM the phases were in lockstep and prologue + epilogue cost 30 % of the time).
 //
-// Accumulator class c of a thread sits in columns colbase + 2c, 2c+1 of its lane.  A tile
-// retires its 4 column sums and 4 anti-diagonal sums with one tcgen05.ld.32x32b.x8 /
-// tcgen05.st.32x32b.x8 pair each (SASS LDTM / STTM).  Classes N .. N+9 are scratch bins for the
-// zero-weight padding slots of edge tiles, so no index is clamped on the accumulator side.
+// Accumulator class c of a thread sits in columns 2c, 2c+1 of its lane.  A tile retires its 4
+// column sums and 4 anti-diagonal sums with one tcgen05.ld.32x32b.x8 / tcgen05.st.32x32b.x8
+// pair each (SASS LDTM / STTM).  Classes N .. N+9 are scratch bins for the zero-weight padding
+// slots of edge tiles, so no index is clamped on the accumulator side.
 #pragma once
 
 #include "pbe_moc_kernel.cuh"
 
 namespace pbe {
 
-constexpr int MOCT_BLOCK = 256;     // cells (threads) per CTA
-constexpr int MOCT_PAD_CLASSES = 10; // scratch bins above class N-1 (see header)
+constexpr int MOCT_BLOCK = 128;       // cells (threads) per CTA
+constexpr int MOCT_PAD_CLASSES = 10;  // scratch bins above class N-1 (see header)
+constexpr int MOCT_SUB_TILES = 13;    // ring slot = at most 13 tiles (3328 B) of one row block
+constexpr int MOCT_MAX_SUBS = 2 * MOC_MAX_BLOCKS;
+
+
+
 
 // ---- TMEM helpers (PTX ISA 8.6 tcgen05; SASS UTCALLOC / LDTM / STTM) -------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t ncols) {
@@ -95,13 +102,23 @@ __device__ __forceinline__ void tm_axpy4(Tm4 &v, double sgn, const double *add) 
     for (int k = 0; k < 4; ++k) tm_set(v, k, fma_(sgn, add[k], tm_get(v, k)));
 }
 
+// launch-time schedule of the table ring: row blocks cut into sub-chunks of <= MOCT_SUB_TILES tiles
+struct MoctSched {
+    int nsubs;                                   // sub-chunks per cell batch
+    int slot_pairs;                              // ring slot size in pairs
+    int tmem_cols;                               // TMEM columns this CTA allocates (power of 2)
+    int stagger_cycles;                          // start-up delay per co-resident CTA slot
+    int sub_off[MOCT_MAX_SUBS + 1];              // pair offset of every sub-chunk in pair_tab
+    unsigned short blk_sub0[MOC_MAX_BLOCKS + 1]; // first sub-chunk of every row block
+};
+
 // shared-memory footprint of one CTA of the TMEM kernel
-__host__ __device__ inline size_t moct_smem_bytes(int N, int chunk_max_pairs) {
+__host__ __device__ inline size_t moct_smem_bytes(int N, int slot_pairs) {
     size_t b = 0;
-    b += (size_t)(N + 1) * MOCT_BLOCK * sizeof(double);   // n_s (row N = zero dummy class)
-    b += (size_t)2 * chunk_max_pairs * sizeof(double2);   // table ring
-    b += (size_t)CLS_ROWS * (N + 1) * sizeof(double);     // per-class tables
-    b += 2 * sizeof(uint64_t) + 16;                       // mbarriers, TMEM base address
+    b += (size_t)(N + 1) * MOCT_BLOCK * sizeof(double); // n_s (row N = zero dummy class)
+    b += (size_t)2 * slot_pairs * sizeof(double2);      // table ring
+    b += (size_t)CLS_ROWS * (N + 1) * sizeof(double);   // per-class tables
+    b += 2 * sizeof(uint64_t) + 16;                     // mbarriers, TMEM base address
     return b;
 }
 // TMEM columns per thread: 2 per accumulator, N + pad classes rounded up to whole x8 groups,
@@ -111,6 +128,13 @@ __host__ __device__ inline int moct_cols_per_thread(int N) {
     int c = 32;
     while (c < need) c *= 2;
     return c <= 256 ? c : 0;
+}
+
+__device__ __forceinline__ double ldg_stream(const double *p) {
+    // streaming load that does not allocate in L1
+    double v;
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
 }
 
 // ---- one TI x TJ tile of class pairs (register tile; identical sums to moc_tile) ---------------
@@ -147,98 +171,19 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
     }
 }
 
-// ---- all pairs owned by row block blk (rows i0 .. i0+TI-1) ------------------------------------
-// tacc = TMEM address of this thread's accumulator 0.
-template <int COAL>
-__device__ __forceinline__ void moct_row_block(const MocParams &p, int blk,
-                                               const double2 *__restrict__ tab, double K2,
-                                               const double *__restrict__ n_s, uint32_t tacc,
-                                               int tid) {
-    const int N = p.N;
-    const int i0 = blk * MOC_TI;
-    const int ntiles = (p.chunk_off[blk + 1] - p.chunk_off[blk]) / (MOC_TI * MOC_TJ);
-    // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets j0.. of the
-    // same tile, so the two read-modify-writes are serialised; every other block issues both
-    // loads before the tile's arithmetic and hides the TMEM latency behind it
-    const bool alias = (i0 + 1 < MOC_TJ);
-    double ni[MOC_TI], di[MOC_TI], bw[MOC_TI + MOC_TJ - 1];
-#pragma unroll
-    for (int r = 0; r < MOC_TI; ++r) {
-        ni[r] = n_s[min(i0 + r, N) * MOCT_BLOCK + tid];
-        di[r] = 0.0;
-    }
-#pragma unroll
-    for (int q = 0; q < MOC_TI + MOC_TJ - 1; ++q) bw[q] = 0.0;
-
-    int j0 = i0;
-#pragma unroll 1
-    for (int t = 0; t < ntiles; ++t, j0 += MOC_TJ, tab += MOC_TI * MOC_TJ) {
-        double nj[MOC_TJ], dj[MOC_TJ];
-#pragma unroll
-        for (int c = 0; c < MOC_TJ; ++c) {
-            nj[c] = n_s[min(j0 + c, N) * MOCT_BLOCK + tid];
-            dj[c] = 0.0;
-        }
-        const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
-        const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
-        Tm4 vd, vb;
-        tmem_wait_st(); // the previous tile's stores have landed
-        if (!alias) {
-            tmem_ld4(a_dj, vd);
-            tmem_ld4(a_bw, vb);
-        }
-        moct_tile<COAL>(tab, K2, ni, nj, di, dj, bw);
-        if (!alias) {
-            tmem_wait_ld(vd, vb);
-            tm_axpy4(vd, -1.0, dj); // death of class j
-            tm_axpy4(vb, 1.0, bw);  // birth of class i+j+1: the TJ lowest anti-diagonals
-            tmem_st4(a_dj, vd);
-            tmem_st4(a_bw, vb);
-        } else {
-            tmem_ld4(a_dj, vd);
-            tmem_wait_ld(vd);
-            tm_axpy4(vd, -1.0, dj);
-            tmem_st4(a_dj, vd);
-            tmem_wait_st();
-            tmem_ld4(a_bw, vb);
-            tmem_wait_ld(vb);
-            tm_axpy4(vb, 1.0, bw);
-            tmem_st4(a_bw, vb);
-        }
-#pragma unroll
-        for (int q = 0; q < MOC_TI + MOC_TJ - 1; ++q)
-            bw[q] = (q + MOC_TJ < MOC_TI + MOC_TJ - 1) ? bw[q + MOC_TJ] : 0.0;
-    }
-    // flush the TI-1 anti-diagonals still in the window and the row sums (death of class i);
-    // the two targets never overlap (i0 + j0 + 1 > i0 + TI - 1 because j0 >= i0 + TJ here)
-    {
-        const uint32_t a_k = tacc + 2u * (uint32_t)(i0 + j0 + 1);
-        const uint32_t a_i = tacc + 2u * (uint32_t)i0;
-        Tm4 vk, vi;
-        tmem_wait_st();
-        tmem_ld4(a_k, vk);
-        tmem_ld4(a_i, vi);
-        tmem_wait_ld(vk, vi);
-        tm_axpy4(vk, 1.0, bw); // bw[TI-1 ..] are zero after the shift
-        tm_axpy4(vi, -1.0, di);
-        tmem_st4(a_k, vk);
-        tmem_st4(a_i, vi);
-    }
-}
-
-// ---- the kernel: one persistent CTA per SM, 256 cells per batch ---------------------------------
+// ---- the kernel: two persistent CTAs per SM, 128 cells per batch ----------------------------------
 // p.negK_floor (MocParams) = -2^30 / max H: with it the 2^y argument stays inside
 // exp2_neg_fast's |y| < 2^31 contract; the host only selects this kernel when every H_ij >=
-// 1e-6 max H, so a clamped cell has every efficiency < 2^-1021 = 0 either way.
+// 1e-6 max H, so a clamped cell has every efficiency below 2^-1022 either way.
 template <int COAL, int BR>
-__global__ void __launch_bounds__(MOCT_BLOCK, 1)
-    moc_tmem_kernel(const __grid_constant__ MocParams p, const int tmem_cols_per_thread) {
+__global__ void __launch_bounds__(MOCT_BLOCK, 2)
+    moc_tmem_kernel(const __grid_constant__ MocParams p, const __grid_constant__ MoctSched sc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int BLOCK = MOCT_BLOCK;
     const int N = p.N;
     const int tid = threadIdx.x;
     double2 *ring = reinterpret_cast<double2 *>(smem_raw);
-    double *n_s = reinterpret_cast<double *>(ring + 2 * (size_t)p.chunk_max_pairs);
+    double *n_s = reinterpret_cast<double *>(ring + 2 * (size_t)sc.slot_pairs);
     double *cls_s = n_s + (size_t)(N + 1) * BLOCK;
     uint64_t *bars = reinterpret_cast<uint64_t *>(cls_s + CLS_ROWS * (N + 1));
     uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 2);
@@ -246,11 +191,10 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
     const int64_t nbatches = (p.ncells + BLOCK - 1) / BLOCK;
     const int64_t my_batches =
         (nbatches > (int64_t)blockIdx.x) ? (nbatches - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const int64_t total_q = (COAL == DCOAL_OFF) ? 0 : my_batches * p.nblocks;
+    const int64_t total_q = (COAL == DCOAL_OFF) ? 0 : my_batches * sc.nsubs;
 
-    // ---- tensor-memory accumulators: warp 0 allocates 2 x cols_per_thread columns -------------
-    const uint32_t tmem_cols = 2u * (uint32_t)tmem_cols_per_thread;
-    if (tid < 32) tmem_alloc(tmem_base_s, tmem_cols);
+    // ---- tensor-memory accumulators: warp 0 allocates, everybody reads the base address ---------
+    if (tid < 32) tmem_alloc(tmem_base_s, (uint32_t)sc.tmem_cols);
     if (tid == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
@@ -262,19 +206,31 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
     __syncthreads();
     tmem_fence_after_sync();
     const uint32_t tmem_base = *tmem_base_s;
-    const int warp = tid >> 5;
-    // lane quarter of this warp in bits 31:16, this thread's column half in bits 15:0
-    const uint32_t tacc = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) +
-                          (uint32_t)((warp >> 2) * tmem_cols_per_thread);
+    // lane quarter of this warp in bits 31:16; the thread's accumulators start at column 0
+    const uint32_t tacc = tmem_base + ((uint32_t)((tid >> 5) * 32) << 16);
     const int n_acc_groups = (N + MOCT_PAD_CLASSES + 3) / 4;
 
+    // Co-resident CTAs start together and every batch costs the same, so left alone they stay
+    // in lockstep: staging loads and epilogues of both would coincide and leave the FP64 pipe
+    // idle.  The TMEM allocator hands the first CTA of an SM columns [0, cols), the second
+    // [cols, 2 cols) ...: that slot index staggers the start by a fraction of a batch, once.
+    if (sc.stagger_cycles > 0 && my_batches >= 2) {
+        const uint32_t slot = (tmem_base & 0xFFFFu) / (uint32_t)sc.tmem_cols;
+        if (slot != 0 && tid == 0) {
+            const long long t0 = clock64();
+            const long long wait = (long long)sc.stagger_cycles * (long long)slot;
+            while (clock64() - t0 < wait) __nanosleep(200);
+        }
+        __syncthreads();
+    }
+
     auto issue = [&](int64_t q) {
-        const int blk = (int)(q % p.nblocks);
-        const int off = p.chunk_off[blk];
-        const unsigned bytes = (unsigned)(p.chunk_off[blk + 1] - off) * (unsigned)sizeof(double2);
+        const int s = (int)(q % sc.nsubs);
+        const int off = sc.sub_off[s];
+        const unsigned bytes = (unsigned)(sc.sub_off[s + 1] - off) * (unsigned)sizeof(double2);
         uint64_t *bar = &bars[q & 1];
         mbar_expect_tx(bar, bytes);
-        bulk_g2s(ring + (q & 1) * (size_t)p.chunk_max_pairs, p.pair_tab + off, bytes, bar);
+        bulk_g2s(ring + (q & 1) * (size_t)sc.slot_pairs, p.pair_tab + off, bytes, bar);
     };
     if (tid == 0) {
         if (0 < total_q) issue(0);
@@ -292,6 +248,9 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
     for (int k = 0; k < MOC_MAX_MOMENTS; ++k) macc[k] = 0.0;
     double cerr = 0.0;
     const bool want_diag = (p.moments != nullptr) || (p.cont_err_max != nullptr);
+    // per-class moment work: none / sum and volume only (continuity check) / all eight powers
+    const int mom_mode = !want_diag ? 0 : ((p.moments == nullptr || p.n_moments <= 2) ? 1 : 2);
+    const double inv_dt = 1.0 / p.dt;
 
     int64_t q = 0;
     for (int64_t batch = blockIdx.x; batch < nbatches; batch += gridDim.x) {
@@ -307,7 +266,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
             const bool pf = ((tid & 3) == 0) && (ncell < p.ncells);
 #pragma unroll 10
             for (int i = 0; i < N; ++i) {
-                n_s[i * BLOCK + tid] = __ldg(src + (size_t)i * p.stride);
+                n_s[i * BLOCK + tid] = ldg_stream(src + (size_t)i * p.stride);
                 if (pf)
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(p.n_in + (size_t)i * p.stride + ncell));
             }
@@ -329,30 +288,146 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
             K2 = negK * 1.4426950408889634074;
         }
 
+        // ---- pair sweep: row blocks of TI classes, each in <= MOCT_SUB_TILES-tile ring slots ------
         if (COAL != DCOAL_OFF) {
 #pragma unroll 1
-            for (int blk = 0; blk < p.nblocks; ++blk, ++q) {
-                mbar_wait(&bars[q & 1], (unsigned)((q >> 1) & 1));
-                moct_row_block<COAL>(p, blk, ring + (q & 1) * (size_t)p.chunk_max_pairs, K2, n_s,
-                                     tacc, tid);
-                __syncthreads(); // every warp is done with ring slot q&1
-                if (tid == 0 && q + 2 < total_q) issue(q + 2);
+            for (int blk = 0; blk < p.nblocks; ++blk) {
+                const int i0 = blk * MOC_TI;
+                // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets
+                // j0.. of the same tile, so the two read-modify-writes are serialised
+                const bool alias = (i0 + 1 < MOC_TJ);
+                double ni[MOC_TI], di[MOC_TI], bw[MOC_TI + MOC_TJ - 1];
+#pragma unroll
+                for (int r = 0; r < MOC_TI; ++r) {
+                    ni[r] = n_s[min(i0 + r, N) * BLOCK + tid];
+                    di[r] = 0.0;
+                }
+#pragma unroll
+                for (int w = 0; w < MOC_TI + MOC_TJ - 1; ++w) bw[w] = 0.0;
+                int j0 = i0;
+#pragma unroll 1
+                for (int s = sc.blk_sub0[blk]; s < (int)sc.blk_sub0[blk + 1]; ++s, ++q) {
+                    mbar_wait(&bars[q & 1], (unsigned)((q >> 1) & 1));
+                    const double2 *__restrict__ tab = ring + (q & 1) * (size_t)sc.slot_pairs;
+                    const int ntiles = (sc.sub_off[s + 1] - sc.sub_off[s]) / (MOC_TI * MOC_TJ);
+#pragma unroll 1
+                    for (int t = 0; t < ntiles; ++t, j0 += MOC_TJ, tab += MOC_TI * MOC_TJ) {
+                        double nj[MOC_TJ], dj[MOC_TJ];
+#pragma unroll
+                        for (int c = 0; c < MOC_TJ; ++c) {
+                            nj[c] = n_s[min(j0 + c, N) * BLOCK + tid];
+                            dj[c] = 0.0;
+                        }
+                        const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
+                        const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
+                        Tm4 vd, vb;
+                        tmem_wait_st(); // the previous tile's stores have landed
+                        if (!alias) {
+                            tmem_ld4(a_dj, vd);
+                            tmem_ld4(a_bw, vb);
+                        }
+                        moct_tile<COAL>(tab, K2, ni, nj, di, dj, bw);
+                        if (!alias) {
+                            tmem_wait_ld(vd, vb);
+                            tm_axpy4(vd, -1.0, dj); // death of class j
+                            tm_axpy4(vb, 1.0, bw);  // birth of class i+j+1: TJ lowest anti-diagonals
+                            tmem_st4(a_dj, vd);
+                            tmem_st4(a_bw, vb);
+                        } else {
+                            tmem_ld4(a_dj, vd);
+                            tmem_wait_ld(vd);
+                            tm_axpy4(vd, -1.0, dj);
+                            tmem_st4(a_dj, vd);
+                            tmem_wait_st();
+                            tmem_ld4(a_bw, vb);
+                            tmem_wait_ld(vb);
+                            tm_axpy4(vb, 1.0, bw);
+                            tmem_st4(a_bw, vb);
+                        }
+#pragma unroll
+                        for (int w = 0; w < MOC_TI + MOC_TJ - 1; ++w)
+                            bw[w] = (w + MOC_TJ < MOC_TI + MOC_TJ - 1) ? bw[w + MOC_TJ] : 0.0;
+                    }
+                    __syncthreads(); // every warp is done with ring slot q&1
+                    if (tid == 0 && q + 2 < total_q) issue(q + 2);
+                }
+                // flush the TI-1 anti-diagonals still in the window and the row sums (death of
+                // class i); the targets never overlap (j0 >= i0 + TJ here)
+                {
+                    const uint32_t a_k = tacc + 2u * (uint32_t)(i0 + j0 + 1);
+                    const uint32_t a_i = tacc + 2u * (uint32_t)i0;
+                    Tm4 vk, vi;
+                    tmem_wait_st();
+                    tmem_ld4(a_k, vk);
+                    tmem_ld4(a_i, vi);
+                    tmem_wait_ld(vk, vi);
+                    tm_axpy4(vk, 1.0, bw); // bw[TI-1 ..] are zero after the shift
+                    tm_axpy4(vi, -1.0, di);
+                    tmem_st4(a_k, vk);
+                    tmem_st4(a_i, vi);
+                }
             }
             tmem_wait_st();
         }
 
         // ---- epilogue: breakup (suffix sum), limiter, update, d, diagnostics ----------------
-        double Ab = 0.0, negKb = 0.0;
+        double Ab = 0.0, Kb2 = 0.0;
         if (BR == DBR_CT) {
             Ab = p.brA * eps13;
-            negKb = -(p.brK / (rho * (eps13 * eps13)));
+            double negKb = -(p.brK / (rho * (eps13 * eps13)));
+            negKb = (negKb < p.negKb_floor) ? p.negKb_floor : negKb; // NaN stays NaN
+            Kb2 = negKb * 1.4426950408889634074;
         }
         double R = 0.0, sum_d = 0.0, sum_n = 0.0;
         double mloc[MOC_MAX_MOMENTS];
 #pragma unroll
         for (int k = 0; k < MOC_MAX_MOMENTS; ++k) mloc[k] = 0.0;
+        const bool wS = live && (p.S_out != nullptr);
+        const bool wN = live && (p.do_step != 0);
+        const int c4top = ((N - 1) >> 2) << 2;
+        // output pointers walk down one class row per class (no 64-bit multiply per store)
+        double *pS = (p.S_out != nullptr ? p.S_out : p.n_out) + (size_t)(c4top + 3) * p.stride + cc;
+        double *pN = (p.do_step ? p.n_out : pS) + (p.do_step ? (size_t)(c4top + 3) * p.stride + cc : 0);
+
+        auto class_body = [&](const int i, const double acc) {
+            const double ni = n_s[i * BLOCK + tid];
+            // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
+            double g = cBP[i];
+            if (BR == DBR_CT) g = (Ab * g) * exp2_neg_fast(Kb2 * cBQ[i]);
+            const double gn = g * ni;
+            const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
+            R = fma_(cW[i], gn, R);
+            double s = fma_(A, acc, B);
+            // MOC.C:87-91: max(s, -relax n_i / dt).  The reference divides; a product with 1/dt
+            // is within 2 ulp of that, so the true division (bit-identical limited values) is
+            // only evaluated when s is within 1e-15 of the limit.
+            const double num = __dmul_rn(-p.relax, ni);
+            const double lim0 = num * inv_dt;
+            if (!(s > fma_(fabs(lim0), 1e-15, lim0))) {
+                const double lim = num / p.dt;
+                s = (s > lim) ? s : lim;
+            }
+            if (wS) *pS = s;
+            // n += dt S (MOC.C:259-272, phi = 0)
+            const double nn = p.do_step ? __dadd_rn(ni, __dmul_rn(p.dt, s)) : ni;
+            if (wN) *pN = nn;
+            sum_d = fma_(cDV[i], nn, sum_d);
+            sum_n += nn;
+            if (mom_mode == 1) {
+                mloc[0] += nn;
+                mloc[1] = fma_(cXI[i], nn, mloc[1]);
+            } else if (mom_mode == 2) {
+                const double x = cXI[i];
+                double pw = nn;
+#pragma unroll
+                for (int k = 0; k < MOC_MAX_MOMENTS; ++k) {
+                    mloc[k] += pw;
+                    pw *= x;
+                }
+            }
+        };
 #pragma unroll 1
-        for (int c4 = ((N - 1) >> 2) << 2; c4 >= 0; c4 -= 4) {
+        for (int c4 = c4top; c4 >= 0; c4 -= 4) {
             Tm4 v;
 #pragma unroll
             for (int k = 0; k < 8; ++k) v.r[k] = 0u;
@@ -360,39 +435,19 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
                 tmem_ld4(tacc + 2u * (uint32_t)c4, v);
                 tmem_wait_ld(v);
             }
+            if (c4 + 3 < N) { // whole group of four classes: no per-class bound test
 #pragma unroll
-            for (int r = 3; r >= 0; --r) {
-                const int i = c4 + r;
-                if (i < N) {
-                    const double ni = n_s[i * BLOCK + tid];
-                    // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
-                    double g = cBP[i];
-                    if (BR == DBR_CT) g = (Ab * g) * exp_neg(negKb * cBQ[i]);
-                    const double gn = g * ni;
-                    const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
-                    R = fma_(cW[i], gn, R);
-                    const double C = A * tm_get(v, r);
-                    // MOC.C:87-91: -relax n_i / dt, a true division as in the reference
-                    const double lim = __dmul_rn(-p.relax, ni) / p.dt;
-                    double s = C + B;
-                    s = (s > lim) ? s : lim;
-                    if (p.S_out != nullptr && live) p.S_out[(size_t)i * p.stride + cell] = s;
-                    double nn = ni;
-                    if (p.do_step) {
-                        nn = __dadd_rn(ni, __dmul_rn(p.dt, s)); // n += dt S (MOC.C:259-272, phi = 0)
-                        if (live) p.n_out[(size_t)i * p.stride + cell] = nn;
-                    }
-                    sum_d = fma_(cDV[i], nn, sum_d);
-                    sum_n += nn;
-                    if (want_diag) {
-                        const double x = cXI[i];
-                        double pw = nn;
+                for (int r = 3; r >= 0; --r) {
+                    class_body(c4 + r, tm_get(v, r));
+                    pS -= p.stride;
+                    pN -= p.stride;
+                }
+            } else {
 #pragma unroll
-                        for (int k = 0; k < MOC_MAX_MOMENTS; ++k) {
-                            if (k < p.n_moments || k == 1) mloc[k] += pw;
-                            pw *= x;
-                        }
-                    }
+                for (int r = 3; r >= 0; --r) {
+                    if (c4 + r < N) class_body(c4 + r, tm_get(v, r));
+                    pS -= p.stride;
+                    pN -= p.stride;
                 }
             }
         }
@@ -437,7 +492,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 1)
     }
     tmem_fence_before_sync();
     __syncthreads();
-    if (tid < 32) tmem_dealloc(tmem_base, tmem_cols);
+    if (tid < 32) tmem_dealloc(tmem_base, (uint32_t)sc.tmem_cols);
 }
 
 } // namespace pbe
