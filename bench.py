@@ -49,16 +49,18 @@ METRIC = "moc100_cell_class_updates_per_s"
 UNIT = "cell-class-updates/s"
 
 # ---- algorithmic work per cell ----------------------------
-# FP64-pipe instruction convention: FMA = 2 flops, add / mul = 1.
-#   per unordered class pair (CT coalescence): K*H (1) + exp (14 FMA + 1 add = 29) + e*G (1) +
-#   n_i*n_j (1) + *w (1) + 3 accumulations (3) = 36 flops in 22 FP64-pipe instructions
-#   per class (CT breakup + epilogue): Kb*Q (1) + exp (29) + Ab*P*e (2) + g*n (1) + R - gn (1) +
-#   suffix FMA (2) + A*C (1) + C + B (1) + limiter mul (1) + update mul/add (2) + d FMA (2) +
-#   sum_n (1) + moments (2 * 6) = 57 flops
-FLOPS_PER_PAIR_CT = 36.0
-FLOPS_PER_PAIR_TAB = 6.0
-FLOPS_PER_CLASS_CT = 57.0
-FLOPS_PER_CLASS_TAB = 27.0
+# (1) SURVEY.md 8(d) convention -- what `roofline.achieved` uses: add/mul = 1, FMA = 2, div/sqrt = 1,
+#     one FP64 exp = 32; P(N) = unordered class pairs with i + j <= N - 2:
+#       MOC + CT coalescence + CT breakup: 40 + 41 P(N) + 40 N  flops / cell  (106 540 at N = 100)
+#       MOC + constant / table kernels:     9 P(N) + 8 N
+# (2) SASS-counted FP64-pipe instructions of the kernel that runs (pbe_moc_tmem_kernel.cuh, cuobjdump
+#     of the tile loop and the epilogue): 18.9 per pair, 44 per class with 6 moments.  The FP64 pipe
+#     retires one warp instruction per scheduler every 2 cycles whatever the opcode, so
+#     instructions x 2 / DFMA-peak is the pipe utilisation (`roofline.fp64_pipe_frac`).
+FP64_INSTR_PER_PAIR_CT = 18.9
+FP64_INSTR_PER_PAIR_TAB = 4.0
+FP64_INSTR_PER_CLASS_CT = 44.0
+FP64_INSTR_PER_CLASS_TAB = 30.0
 FLOPS_QMOM3_CT = 1300.0
 FLOPS_QMOM3_CONST = 600.0
 
@@ -69,11 +71,22 @@ def n_pairs(N: int) -> int:
 
 
 def moc_flops_per_cell(w) -> float:
+    """SURVEY.md 8(d) algorithmic flops per cell (exp = 32 flops)."""
     ct_c = w.coalescence == "CoulaloglouTavlaridesC"
     ct_b = w.breakup == "CoulaloglouTavlarides"
     pairs = 0 if w.coalescence == "noCoalescence" else n_pairs(w.N)
-    return pairs * (FLOPS_PER_PAIR_CT if ct_c else FLOPS_PER_PAIR_TAB) + w.N * (
-        FLOPS_PER_CLASS_CT if ct_b else FLOPS_PER_CLASS_TAB)
+    if ct_c or ct_b:
+        return 40.0 + (41.0 if ct_c else 9.0) * pairs + (40.0 if ct_b else 8.0) * w.N
+    return 9.0 * pairs + 8.0 * w.N
+
+
+def moc_fp64_instr_per_cell(w) -> float:
+    """SASS-counted FP64-pipe instructions per cell of the tensor-memory kernel."""
+    ct_c = w.coalescence == "CoulaloglouTavlaridesC"
+    ct_b = w.breakup == "CoulaloglouTavlarides"
+    pairs = 0 if w.coalescence == "noCoalescence" else n_pairs(w.N)
+    return pairs * (FP64_INSTR_PER_PAIR_CT if ct_c else FP64_INSTR_PER_PAIR_TAB) + w.N * (
+        FP64_INSTR_PER_CLASS_CT if ct_b else FP64_INSTR_PER_CLASS_TAB)
 
 
 def moc_bytes_per_cell(N: int) -> float:
@@ -370,12 +383,20 @@ def run_b200(args):
     tf = cells * flops_cell / (kern_ms * 1e-3) / 1e12
     gbs = cells * bytes_cell / (kern_ms * 1e-3) / 1e9
     fp64_nominal = info["sm_count"] * 64 * 2 * 1.965e9 / 1e12
+    kinfo = moc.kernel()
+    instr_cell = moc_fp64_instr_per_cell(w)
+    pipe_frac = cells * instr_cell * 2.0 / (kern_ms * 1e-3) / 1e12 / fp64_tf
     roofline = {
         "bound": "fp64", "achieved": tf, "peak": fp64_tf, "unit": "TFLOP/s", "frac": tf / fp64_tf,
-        "traffic": None, "kernel": "moc_source_kernel<CT,CT,128>", "kernel_ms": kern_ms,
+        "traffic": None, "kernel_ms": kern_ms,
+        "kernel": ("moc_tmem_kernel<CT,CT>" if kinfo["kernel"] == "tmem" else "moc_source_kernel<CT,CT,128>")
+                  + f" ({kinfo['cells_per_cta']} cells/CTA, {kinfo['ctas_per_sm']} CTA/SM)",
         "peak_source": "measured in this run: register-resident DFMA chains (pbe_measure_fp64_peak); "
                        f"nominal {fp64_nominal:.1f} TFLOP/s at 1965 MHz",
-        "flops_per_cell": flops_cell, "flops_convention": "FMA=2, add/mul=1; exp = 14 FMA + 1 add (SASS-counted)",
+        "flops_per_cell": flops_cell,
+        "flops_convention": "SURVEY.md 8(d): add/mul=1, FMA=2, exp=32: 40 + 41 P(N) + 40 N per cell",
+        "fp64_pipe_frac": pipe_frac, "fp64_pipe_instr_per_cell": instr_cell,
+        "fp64_pipe_note": "SASS-counted FP64-pipe instructions x 2 / DFMA peak = share of FP64 issue slots used",
         "hbm": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
                 "bytes_per_cell": bytes_cell, "peak_source": hbm_src},
     }

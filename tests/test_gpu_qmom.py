@@ -136,13 +136,16 @@ def test_step_scrub_clamp_diameter(ctx, oracle):
     S = torch.empty_like(m)
     d = torch.empty(w.ncells, dtype=torch.float64, device="cuda")
     dt = 1e-3
+    S_raw = q.source(m, T(f["eps"]), T(f["rho"]), T(f["nu"])).cpu().numpy()   # before the scrub
     q.step(m, T(f["eps"]), T(f["rho"]), T(f["nu"]), dt, S=S, d=d)
     So, scale = oracle.qmom_source(ospec, 3, m_h, f["eps"], f["rho"], f["nu"], nthreads=8)
+    nan_o = np.isnan(So)
     m_o = m_h.copy()
     d_o = oracle.qmom_update(m_o, So, dt)   # scrubs So in place
     S, m, d = S.cpu().numpy(), m.cpu().numpy(), d.cpu().numpy()
     assert not np.isnan(S).any() and not np.isnan(m).any()
-    assert np.array_equal(S == 0.0, So == 0.0)                 # same cells scrubbed
+    assert np.array_equal(np.isnan(S_raw), nan_o) and nan_o.any()   # same entries are NaN ...
+    assert np.all(S[nan_o] == 0.0) and np.all(So[nan_o] == 0.0)     # ... and scrubbed to 0 (QMOM.C:101-107)
     assert np.all(m >= 1e-15)                                  # QMOM realisability floor (SMALL)
     assert np.all(m[:, 7] == 1e-15)
     well = (f["nodes"][1] / f["nodes"][0] > 1.001)
