@@ -1,0 +1,197 @@
+// pbe_replay -- Foam-free replay of the reference's "run only the PBE" driver
+// (applications/PBEFoam/PBEFoam.C:56-67: while (runTime.run()) { runTime++; fluid.correct(); })
+// on synthetic per-cell fields: BASELINE.json configs[4].  MOC and QMOM run side by side through
+// the PBEMethod mirror of include/pbe_method.hpp; every step does what PBEDiameter::correct() does
+// (PBEDiameter.H:95-99): method_->correct(); d_ = method_->d().
+//
+//   pbe_replay [--cells 4000000] [--steps 10] [--classes 50] [--order 3] [--device 0]
+//              [--dict file]        (a PBEDiameterCoeffs-style dictionary; default: the c01 case)
+//
+// Prints one JSON line per method per step (wall ms with the diameter read-back, volume-averaged
+// / max / min diameter as printAvgMaxMin would, Utility.C:4-10) and a summary line per method.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+#include <iterator>
+
+#include "pbe_method.hpp"
+
+namespace {
+
+// splitmix64: small, seedable, identical on every host
+struct Rng {
+    uint64_t s;
+    explicit Rng(uint64_t seed) : s(seed) {}
+    uint64_t next() {
+        uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    double uniform() { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); }
+    double uniform(double a, double b) { return a + (b - a) * uniform(); }
+};
+
+// c01 validation case (tests/validation/simmons_and_azzopardi/c01/constant/phaseProperties:24-50,
+// .../thermophysicalProperties.acps:38,47, .../system/controlDict:28)
+const char *kDefaultDict = R"(
+    coalescenceKernel CoulaloglouTavlaridesC;
+    breakupKernel CoulaloglouTavlarides;
+    daughterParticleDistribution uniformBinaryBreakup;
+    CoulaloglouTavlaridesCCoeffs { c1 4.5e6; c2 1.891e12; gamma 0; sigma 0.01; }
+    CoulaloglouTavlaridesCoeffs  { c1 0.1;   c2 0.06354;  gamma 0; sigma 0.01; }
+    uniformBinaryBreakupCoeffs { }
+)";
+
+double lognormalVolumePdf(double v, double dmean = 5.0e-4, double dstd = 5.0e-5) {
+    // number pdf in volume space of a log-normal diameter distribution
+    // (tests/validation/simmons_and_azzopardi/setupCases.py:22-40)
+    const double var = dstd * dstd;
+    const double mu = std::log(dmean / std::sqrt(1 + var / (dmean * dmean)));
+    const double sg = std::sqrt(std::log(1 + var / (dmean * dmean)));
+    const double d = std::cbrt(6.0 * v / M_PI);
+    const double z = (std::log(d) - mu) / sg;
+    return std::exp(-0.5 * z * z) / (d * sg * std::sqrt(2 * M_PI)) * (2.0 / (M_PI * d * d));
+}
+
+struct Stats {
+    double avg, mx, mn;
+};
+Stats avgMaxMin(const std::vector<double> &f, const std::vector<double> &V) {
+    double sfv = 0, sv = 0, mx = -INFINITY, mn = INFINITY;
+    for (size_t c = 0; c < f.size(); ++c) {
+        sfv += f[c] * V[c];
+        sv += V[c];
+        mx = std::max(mx, f[c]);
+        mn = std::min(mn, f[c]);
+    }
+    return {sfv / sv, mx, mn};
+}
+
+void replay(const char *label, pbe::PBEMethod &m, const std::vector<double> &V, int steps, int64_t cells,
+            double unitsPerCell, const char *unit) {
+    double total = 0;
+    for (int s = 0; s < steps; ++s) {
+        auto t0 = std::chrono::steady_clock::now();
+        m.correct();                              // PBEDiameter::correct(): method_->correct();
+        const std::vector<double> &d = m.d();     //                         d_ = method_->d();
+        auto t1 = std::chrono::steady_clock::now();
+        const double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        if (s > 0) total += ms; // step 0 carries one-time warm-up
+        const Stats st = avgMaxMin(d, V);
+        std::printf("{\"method\": \"%s\", \"step\": %d, \"ms\": %.3f, \"d_avg\": %.9e, \"d_max\": %.9e, "
+                    "\"d_min\": %.9e}\n",
+                    label, s, ms, st.avg, st.mx, st.mn);
+    }
+    if (steps > 1) {
+        const double ms = total / (steps - 1);
+        std::printf("{\"method\": \"%s\", \"summary\": true, \"cells\": %lld, \"ms_per_step\": %.3f, "
+                    "\"%s\": %.4e}\n",
+                    label, (long long)cells, ms, unit, cells * unitsPerCell / (ms * 1e-3));
+    }
+}
+
+} // namespace
+
+int main(int argc, char **argv) {
+    int64_t cells = 4000000;
+    int steps = 10, classes = 50, order = 3, device = 0;
+    std::string dictFile;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto val = [&]() -> const char * {
+            if (i + 1 >= argc) {
+                std::fprintf(stderr, "missing value after %s\n", a.c_str());
+                std::exit(2);
+            }
+            return argv[++i];
+        };
+        if (a == "--cells") cells = (int64_t)std::atof(val());
+        else if (a == "--steps") steps = std::atoi(val());
+        else if (a == "--classes") classes = std::atoi(val());
+        else if (a == "--order") order = std::atoi(val());
+        else if (a == "--device") device = std::atoi(val());
+        else if (a == "--dict") dictFile = val();
+        else {
+            std::fprintf(stderr, "unknown option %s\n", a.c_str());
+            return 2;
+        }
+    }
+    try {
+        std::string text = kDefaultDict;
+        if (!dictFile.empty()) {
+            std::ifstream in(dictFile);
+            if (!in) throw pbe::FatalError("cannot open " + dictFile);
+            text.assign(std::istreambuf_iterator<char>(in), std::istreambuf_iterator<char>());
+        }
+        // ---- synthetic phase fields, seed 20240611 -------------------------------
+        Rng rng(20240611);
+        std::vector<double> eps(cells), alpha(cells), rho(cells, 1166.0), nu(cells, 1.599752e-3 / 1166.0),
+            V(cells, 1e-9);
+        for (int64_t c = 0; c < cells; ++c) {
+            eps[c] = std::pow(10.0, rng.uniform(-3.0, 0.0));
+            alpha[c] = rng.uniform(0.01, 0.10);
+        }
+        pbe::Phase phase;
+        phase.name = "acps";
+        phase.ncells = cells;
+        phase.alpha = alpha.data();
+        phase.rho = rho.data();
+        phase.nu = nu.data();
+        phase.epsilon = eps.data();
+        phase.V = V.data();
+        phase.deltaT = 2.5e-4;
+        phase.device = device;
+
+        {   // ---- methodOfClasses: c01 grid, xi1 = 3.5918876006043295e-12 at 50 classes -----------
+            pbe::Dictionary dict = pbe::Dictionary::parse(text, "PBEDiameterCoeffs");
+            dict.set("method", "methodOfClasses");
+            const double xi1 = 3.5918876006043295e-12 * 50.0 / classes;
+            dict.subDictOrAdd("MOCCoeffs").set("numberOfClasses", (double)classes).set("xi1", xi1);
+            std::vector<double> p(classes), n0((size_t)classes * cells);
+            double norm = 0;
+            for (int i = 0; i < classes; ++i) {
+                p[i] = lognormalVolumePdf(xi1 * (i + 1)) + 1e-300;
+                norm += p[i] * xi1 * (i + 1);
+            }
+            for (int i = 0; i < classes; ++i)
+                for (int64_t c = 0; c < cells; ++c)
+                    n0[(size_t)i * cells + c] = alpha[c] * V[c] * p[i] / norm * std::exp2(rng.uniform(-1.0, 1.0));
+            pbe::PBEMethods::MOC moc(dict, phase, n0.data());
+            std::vector<double>().swap(n0);
+            replay("methodOfClasses", moc, V, steps, cells, classes, "cell_class_updates_per_s");
+            std::printf("{\"method\": \"methodOfClasses\", \"min_n0\": %.6e, \"continuity_error\": %.6e}\n",
+                        moc.classMin(0), moc.continuityError());
+        }
+        {   // ---- quadratureMethodOfMoments: moments of a random `order`-node quadrature per cell --
+            pbe::Dictionary dict = pbe::Dictionary::parse(text, "PBEDiameterCoeffs");
+            dict.set("method", "quadratureMethodOfMoments");
+            dict.subDictOrAdd("QMOMCoeffs").set("quadratureOrder", (double)order);
+            std::vector<double> m0((size_t)2 * order * cells);
+            std::vector<double> x(order), w(order);
+            for (int64_t c = 0; c < cells; ++c) {
+                for (int i = 0; i < order; ++i) {
+                    x[i] = std::pow(10.0, rng.uniform(-12.0, std::log10(3e-10)));
+                    w[i] = rng.uniform(1e5, 1e7);
+                }
+                for (int k = 0; k < 2 * order; ++k) {
+                    double s = 0;
+                    for (int i = 0; i < order; ++i) s += w[i] * std::pow(x[i], k);
+                    m0[(size_t)k * cells + c] = s;
+                }
+            }
+            pbe::PBEMethods::QMOM q(dict, phase, m0.data());
+            std::vector<double>().swap(m0);
+            replay("quadratureMethodOfMoments", q, V, steps, cells, 1.0, "cell_updates_per_s");
+            const auto a = q.avgMaxMin(0);
+            std::printf("{\"method\": \"quadratureMethodOfMoments\", \"m0_avg\": %.6e, \"m0_max\": %.6e, "
+                        "\"m0_min\": %.6e}\n", a.avg, a.max, a.min);
+        }
+    } catch (const pbe::FatalError &e) {
+        std::cerr << e.what() << "\n\nFOAM exiting\n";
+        return 1;
+    }
+    return 0;
+}

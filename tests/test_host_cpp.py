@@ -1,0 +1,104 @@
+"""The C++ host layer above the C ABI: include/pbe_method.hpp (Foam-free mirror of PBEMethod /
+MOC / QMOM and the kernel factories) and apps/pbe_replay (the PBEFoam-shaped driver).
+
+CPU part: the header compiles with plain g++ against libpbe_b200.so, the dictionary parser reads
+the reference's phaseProperties syntax, run-time selection fails like PBEMethod::New
+(PBEMethod.C:97-105), and without a GPU construction fails loudly (no CPU fallback).
+GPU part: the replay driver runs MOC and QMOM side by side and its MOC result matches the oracle.
+"""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIBDIR = os.path.join(ROOT, "openpbe_b200", "lib")
+
+PROBE = r'''
+#include "pbe_method.hpp"
+#include <cstdio>
+int main(int argc, char**) {
+    // syntax of tests/integration/MOC/diffs/phaseProperties.coalescence:19-48
+    auto d = pbe::Dictionary::parse(R"(
+        method methodOfClasses;   // comment
+        MOCCoeffs { numberOfClasses 10; xi1 1.0; usingMULES on; }
+        coalescenceKernel constantCoalescence; /* block */ breakupKernel noBreakup;
+        daughterParticleDistribution uniformBinaryBreakup;
+        constantCoalescenceCoeffs { constant 0.1; } noBreakupCoeffs { } uniformBinaryBreakupCoeffs { }
+    )", "PBEDiameterCoeffs");
+    std::printf("method=%s N=%d xi1=%g mules=%d relax=%g c=%g\n", d.lookup("method").c_str(),
+                d.subDict("MOCCoeffs").readLabel("numberOfClasses"), d.subDict("MOCCoeffs").readScalar("xi1"),
+                (int)d.subDict("MOCCoeffs").lookupOrDefault<bool>("usingMULES", false),
+                d.subDict("MOCCoeffs").lookupOrDefault<double>("sourceRelaxation", 1.0),
+                d.subDict("constantCoalescenceCoeffs").readScalar("constant"));
+    pbe_kernel_spec s = pbe::kernelSpecFromDict(d);
+    std::printf("spec=%d,%d,%d,%g\n", s.coalescence, s.breakup, s.daughter, s.coal_c[0]);
+    pbe::Phase ph; ph.deltaT = 1e-3;
+    const char* cases[] = {"method bogus;", "method methodOfMoments;", "nomethod 1;"};
+    for (const char* c : cases) {
+        try { pbe::PBEMethod::New(pbe::Dictionary::parse(c), ph); std::printf("no error\n"); }
+        catch (const pbe::FatalError& e) { std::printf("FATAL<<%s>>\n", e.what()); }
+    }
+    try { auto bad = d; bad.set("coalescenceKernel", "Madsen"); pbe::kernelSpecFromDict(bad); }
+    catch (const pbe::FatalError& e) { std::printf("FATAL<<%s>>\n", e.what()); }
+    if (argc > 1) {  // construction needs a device: must fail loudly without one
+        try { auto m = pbe::PBEMethod::New(d, ph); std::printf("constructed\n"); }
+        catch (const pbe::FatalError& e) { std::printf("FATAL<<%s>>\n", e.what()); }
+    }
+    return 0;
+}
+'''
+
+
+@pytest.fixture(scope="module")
+def probe(tmp_path_factory):
+    if not os.path.exists(os.path.join(LIBDIR, "libpbe_b200.so")):
+        pytest.skip("libpbe_b200.so not built")
+    d = tmp_path_factory.mktemp("hostcpp")
+    src = d / "probe.cpp"
+    src.write_text(PROBE)
+    exe = d / "probe"
+    subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I",
+                           os.path.join(ROOT, "include"), str(src), "-o", str(exe), "-L", LIBDIR,
+                           "-lpbe_b200", f"-Wl,-rpath,{LIBDIR}"])
+    return str(exe)
+
+
+def test_dictionary_and_runtime_selection(probe):
+    out = subprocess.check_output([probe], text=True)
+    assert "method=methodOfClasses N=10 xi1=1 mules=1 relax=1 c=0.1" in out
+    assert "spec=1,0,0,0.1" in out                      # constantCoalescence, noBreakup, uniformBinaryBreakup
+    assert "Unknown pbeModelType type bogus" in out and "Valid PBEMethod types are" in out
+    assert "(dummy methodOfClasses quadratureMethodOfMoments)" in out
+    assert "methodOfMoments is not part of the B200 source engine" in out
+    assert 'keyword method is undefined in dictionary' in out
+    assert "Unknown coalescenceKernel type Madsen" in out and "CoulaloglouTavlaridesC" in out
+
+
+def test_construction_fails_loudly_without_gpu(probe):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    out = subprocess.check_output([probe, "construct"], text=True)
+    assert "constructed" not in out
+    assert "no CUDA device" in out and "no CPU path" in out
+
+
+@pytest.mark.gpu
+def test_replay_driver_moc_and_qmom(oracle):
+    exe = os.path.join(ROOT, "apps", "pbe_replay")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "apps"), "-s"])
+    out = subprocess.check_output([exe, "--cells", "20000", "--steps", "3", "--classes", "30"], text=True)
+    rows = [json.loads(ln) for ln in out.splitlines() if ln.startswith("{")]
+    moc = [r for r in rows if r["method"] == "methodOfClasses" and "step" in r]
+    qm = [r for r in rows if r["method"] == "quadratureMethodOfMoments" and "step" in r]
+    assert len(moc) == 3 and len(qm) == 3
+    for r in moc + qm:   # diameters stay in the physical range of the log-normal initial condition
+        assert 1e-5 < r["d_min"] <= r["d_avg"] <= r["d_max"] < 2e-3 and np.isfinite(r["ms"])
+    summ = [r for r in rows if r.get("summary")]
+    assert {r["method"] for r in summ} == {"methodOfClasses", "quadratureMethodOfMoments"}
+    tail = [r for r in rows if "continuity_error" in r][0]
+    assert tail["min_n0"] >= 0.0 and np.isfinite(tail["continuity_error"])
