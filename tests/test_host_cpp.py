@@ -98,6 +98,9 @@ def test_replay_driver_moc_and_qmom(oracle):
     assert len(moc) == 3 and len(qm) == 3
     for r in moc + qm:   # diameters stay in the physical range of the log-normal initial condition
         assert 1e-5 < r["d_min"] <= r["d_avg"] <= r["d_max"] < 2e-3 and np.isfinite(r["ms"])
+    # same initial condition in both methods: the volume-mean diameter QMOM reports (QMOM.C:125)
+    # sits within a few per cent of MOC's number-mean diameter (MOC.C:282-290) for this narrow pdf
+    assert abs(qm[-1]["d_avg"] / moc[-1]["d_avg"] - 1.0) < 0.05
     summ = [r for r in rows if r.get("summary")]
     assert {r["method"] for r in summ} == {"methodOfClasses", "quadratureMethodOfMoments"}
     tail = [r for r in rows if "continuity_error" in r][0]
