@@ -130,6 +130,77 @@ PBE_HD double exp2_neg_fast(double y) {
     return make_double(hi, lo);
 }
 
+#if defined(__CUDACC__)
+// exp_neg with its polynomial in constant memory: FP64 immediates cost two UMOVs each wherever
+// the call is inlined into straight-line code (the QMOM kernel has nine calls and no loop to
+// hoist them out of; ncu r01f: 218 UMOV per cell); c[bank][offset] operands cost nothing.
+static __constant__ double PBE_EXP_C[16] = {2.510134692835034e-08,  2.7621338669142925e-07, 2.75572664186123e-06,
+                                     2.4801518641395993e-05, 0.00019841269864380513, 0.0013888888918939168,
+                                     0.008333333333329793,   0.04166666666662064,    0.16666666666666669,
+                                     0.5000000000000001,     1.4426950408889634074,  6755399441055744.0,
+                                     -6.93147180369123816490e-01, -1.90821492927058770002e-10, 0.0, 0.0};
+__device__ __forceinline__ double exp_neg_c(double x) {
+    const double SHIFT = PBE_EXP_C[11];
+    double t = __fma_rn(x, PBE_EXP_C[10], SHIFT);
+    int k = __double2loint(t);
+    double kd = t - SHIFT;
+    double r = __fma_rn(kd, PBE_EXP_C[12], x);
+    r = __fma_rn(kd, PBE_EXP_C[13], r);
+    double p = PBE_EXP_C[0];
+#pragma unroll
+    for (int i = 1; i < 10; ++i) p = __fma_rn(p, r, PBE_EXP_C[i]);
+    p = __fma_rn(p, r, 1.0);
+    p = __fma_rn(p, r, 1.0);
+    int hi = __double2hiint(p) + (int)((unsigned)k << 20);
+    double res = __hiloint2double(hi, __double2loint(p));
+    const unsigned ux = (unsigned)__double2hiint(x);
+    const bool under = (ux - 0xC0890000u) <= (0xFFF00000u - 0xC0890000u);
+    return (under || k < -1021) ? 0.0 : res;
+}
+
+// 1/x for normal x by MUFU.RCP64H + two Newton steps: no denormal / special-case slow path
+// (the IEEE division emits one behind a branch).  <= 1 ulp; 0, inf, NaN behave like 1/x.
+__device__ __forceinline__ double rcp_fast(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = __fma_rn(__fma_rn(-x, r, 1.0), r, r);
+    r = __fma_rn(__fma_rn(-x, r, 1.0), r, r);
+    return r;
+}
+
+// ninth roots of a node volume: r = x^(1/9), u = x^(-1/9), from which the Coulaloglou-
+// Tavlarides kernels take x^(1/3) = r^3, x^(2/9) = r^2, x^(-2/9) = u^2, x^(-5/9) = u^5
+// (coalescenceKernels/CoulaloglouTavlarides.C:75-88, breakupKernels/CoulaloglouTavlarides.C:
+// 83-92).  x is scaled by 2^(-9k) into [2^-5, 2^5]; an FP32 seed 2^(-log2(x)/9) (MUFU.LG2 /
+// MUFU.EX2, |e| < 1e-5) is corrected ONCE with the third-order series of (1 - e)^(-1/9),
+// e = 1 - x u^9, division-free: 13 FP64 instructions for both roots against ~60 for two cbrt()
+// and a division.  pow() semantics at the edges: x < 0 or NaN -> NaN, 0 -> (0, inf),
+// inf -> (inf, 0); denormal x is outside the contract.
+__device__ __forceinline__ void ninth_roots(double x, double &r, double &u) {
+    const int hi = __double2hiint(x), lo = __double2loint(x);
+    const int ex = ((hi >> 20) & 0x7ff) - 1023;
+    const int k = (ex * 7282 + 32768) >> 16; // ~ ex / 9
+    const double xs = __hiloint2double(hi - ((9 * k) << 20), lo);
+    const float lf = __log2f((float)xs);
+    const double u0 = (double)exp2f(lf * (-1.0f / 9.0f));
+    const double u2 = u0 * u0, u4 = u2 * u2, u8 = u4 * u4;
+    const double e = __fma_rn(-(xs * u0), u8, 1.0);
+    const double c = __fma_rn(__fma_rn(95.0 / 2187.0, e, 5.0 / 81.0), e, 1.0 / 9.0);
+    const double us = __fma_rn(u0 * e, c, u0);
+    const double v2 = us * us, v4 = v2 * v2;
+    const double rs = xs * (v4 * v4);
+    // undo the scaling: u = us 2^-k, r = rs 2^k
+    u = __hiloint2double(__double2hiint(us) - (k << 20), __double2loint(us));
+    r = __hiloint2double(__double2hiint(rs) + (k << 20), __double2loint(rs));
+    const bool pos_normal = (x > 0.0) && (x < __longlong_as_double(0x7ff0000000000000LL));
+    if (!pos_normal) {
+        const double bad = (x == 0.0) ? 0.0 : ((x > 0.0) ? x : NAN); // 0, +inf, NaN (x < 0 or NaN)
+        r = bad;
+        u = (x == 0.0) ? __longlong_as_double(0x7ff0000000000000LL) : ((x > 0.0) ? 0.0 : NAN);
+    }
+}
+#endif
+
 // pow(x, 1/3) with C pow() semantics for the arguments the reference feeds it
 // (coalescenceKernels/CoulaloglouTavlarides.C:75-76): negative finite x -> NaN, +-0 -> 0.
 PBE_HD double pow_third(double x) { return x < 0.0 ? NAN : cbrt(x); }

@@ -23,13 +23,31 @@ int grid_for(pbe_ctx *ctx, int64_t n, int threads, int per_sm) {
 int launch_qmom(pbe_qmom *q, const QmomParams &p, cudaStream_t st) {
     if (p.ncells == 0) return PBE_OK;
     const int grid = grid_for(q->ctx, p.ncells, 128, 16);
+    // one instantiation per (order, coalescenceKernel, breakupKernel): pbe_qmom_create has
+    // already restricted the ids to {none, constant, CT} x {none, binary, CT}
+#define PBE_Q_LAUNCH(N, C, B) qmom_kernel<N, C, B><<<grid, 128, 0, st>>>(p)
+#define PBE_Q_BR(N, C)                                                                             \
+    switch (q->ks.br) {                                                                            \
+    case PBE_BR_NONE: PBE_Q_LAUNCH(N, C, PBE_BR_NONE); break;                                      \
+    case PBE_BR_BINARY: PBE_Q_LAUNCH(N, C, PBE_BR_BINARY); break;                                  \
+    default: PBE_Q_LAUNCH(N, C, PBE_BR_CT); break;                                                 \
+    }
+#define PBE_Q_COAL(N)                                                                              \
+    switch (q->ks.coal) {                                                                          \
+    case PBE_COAL_NONE: PBE_Q_BR(N, PBE_COAL_NONE) break;                                          \
+    case PBE_COAL_CONSTANT: PBE_Q_BR(N, PBE_COAL_CONSTANT) break;                                  \
+    default: PBE_Q_BR(N, PBE_COAL_CT) break;                                                       \
+    }
     switch (q->order) {
-    case 1: qmom_kernel<1><<<grid, 128, 0, st>>>(p); break;
-    case 2: qmom_kernel<2><<<grid, 128, 0, st>>>(p); break;
-    case 3: qmom_kernel<3><<<grid, 128, 0, st>>>(p); break;
-    case 4: qmom_kernel<4><<<grid, 128, 0, st>>>(p); break;
+    case 1: PBE_Q_COAL(1) break;
+    case 2: PBE_Q_COAL(2) break;
+    case 3: PBE_Q_COAL(3) break;
+    case 4: PBE_Q_COAL(4) break;
     default: set_error("pbe_qmom: order %d not instantiated", q->order); return PBE_E_UNSUPPORTED;
     }
+#undef PBE_Q_COAL
+#undef PBE_Q_BR
+#undef PBE_Q_LAUNCH
     PBE_CUDA(cudaGetLastError());
     q->ctx->launches++;
     return PBE_OK;
