@@ -34,6 +34,14 @@ PBE_HD bool finite_(double x) {
     return std::isfinite(x);
 #endif
 }
+// reciprocal without the IEEE-division slow path on the device (<= 1 ulp; pbe_math.cuh)
+PBE_HD double rcp_(double x) {
+#if defined(__CUDA_ARCH__)
+    return rcp_fast(x);
+#else
+    return 1.0 / x;
+#endif
+}
 PBE_HD double rsqrt_(double x) {
 #if defined(__CUDA_ARCH__)
     return rsqrt(x);
@@ -146,9 +154,9 @@ PBE_HD bool tridiag_ql_firstrow(double (&d)[N], double (&e)[N], double (&z)[N]) 
 // p, q become the eigenvalues; (zp, zq) -- the first-row components carried in this basis --
 // are rotated with it.  e == 0 leaves everything untouched.
 PBE_HD void rot2_firstrow(double &p, double &q, double e, double &zp, double &zq) {
-    const double theta = (q - p) / (2.0 * e);
+    const double theta = (q - p) * rcp_(2.0 * e);
     const double at = fabs(theta);
-    double t = 1.0 / (at + sqrt(fma_(theta, theta, 1.0))); // smaller root of t^2 + 2 theta t - 1
+    double t = rcp_(at + sqrt(fma_(theta, theta, 1.0))); // smaller root of t^2 + 2 theta t - 1
     t = (theta < 0.0) ? -t : t;
     t = (e == 0.0) ? 0.0 : t; // also covers theta = 0/0
     const double c = rsqrt_(fma_(t, t, 1.0));
@@ -344,7 +352,9 @@ PBE_HD void wheeler_dev(const double (&m)[2 * N], double (&x)[N], double (&w)[N]
                 const double t = sub_rn_(sc[col + 1], mul_rn_(a[k - 1], sc[col]));
                 sn[col] = sub_rn_(t, mul_rn_(b[k - 1], sp[col]));
             }
-            a[k] = add_rn_(-(sc[k] / sc[k - 1]), sn[k + 1] / sn[k]);
+            // sigma row 1 is the moment row: sc[1] / sc[0] at k = 1 is a[0], bit for bit
+            const double prev = (k == 1) ? a[0] : sc[k] / sc[k - 1];
+            a[k] = add_rn_(-prev, sn[k + 1] / sn[k]);
             b[k] = sn[k] / sc[k - 1];
 #pragma unroll
             for (int j = 0; j < 2 * N; ++j) {

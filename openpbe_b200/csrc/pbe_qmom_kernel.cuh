@@ -41,10 +41,10 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
     CellCoef cc;
     cc.A = cc.negK = cc.Ab = cc.negKb = 0.0;
     if (ct_c || ct_b) cc = cell_coef(ks, eps, rho, nu);
-    double ra[N], rp[N], ia[N], gw[N]; // x^(1/3), x^(2/9), x^(-1/3), w_i g_i
+    double ra[N], rp[N], ia[N], r1[N], gw[N]; // x^(1/3), x^(2/9), x^(-1/3), x^(1/9), w_i g_i
 #pragma unroll
     for (int i = 0; i < N; ++i) {
-        ra[i] = rp[i] = ia[i] = 0.0;
+        ra[i] = rp[i] = ia[i] = r1[i] = 0.0;
         double g = 0.0;
         if (ct_c || ct_b) {
             double r9, u9;
@@ -52,6 +52,7 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
             const double r2 = r9 * r9, u2 = u9 * u9;
             ra[i] = r2 * r9;
             rp[i] = r2;
+            r1[i] = r9;
             ia[i] = u2 * u9;
             if (ct_b) // breakupKernels/CoulaloglouTavlarides.C:83-92
                 g = (cc.Ab * u2) * exp_neg_c(cc.negKb * (ia[i] * u2));
@@ -68,7 +69,15 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
 #pragma unroll
         for (int j = i; j < N; ++j) {
             double S = 0.0;
-            if (ct_c) { // coalescenceKernels/CoulaloglouTavlarides.C:69-90
+            if (ct_c && j == i) {
+                // equal volumes: a + b = 2a, sqrt(2 x^(2/9)) = sqrt(2) x^(1/9), a b/(a + b) = a/2;
+                // t = x^(1/3) x^(-1/3) is 1, or NaN exactly where 0*0/(0+0) is (xi = 0, inf)
+                const double t = ra[i] * ia[i];
+                const double G = (4.0 * 1.41421356237309504880) * (ra[i] * ra[i]) * r1[i];
+                const double h = (0.5 * ra[i]) * t;
+                const double h2 = h * h;
+                S = (cc.A * G) * exp_neg_c(cc.negK * (h2 * h2));
+            } else if (ct_c) { // coalescenceKernels/CoulaloglouTavlarides.C:69-90
                 const double sa = ra[i] + ra[j];
                 const double G = (sa * sa) * sqrt(rp[i] + rp[j]);
                 const double h = rcp_fast(ia[i] + ia[j]); // a b / (a + b)

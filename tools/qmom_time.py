@@ -2,6 +2,8 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
+from openpbe_b200 import capi
+capi.LIB_PATH = os.environ.get('PBE_LIB', capi.LIB_PATH)  # A/B builds of the library
 from openpbe_b200 import engine, synthetic
 
 ctx = engine.Context(0)
@@ -21,7 +23,8 @@ for nm, order in (("qmom3_ct", 3), ("qmom3_const", 3), ("qmom3_ct", 2), ("qmom3_
     for what in ("source", "step"):
         t = 1e9
         for _ in range(5):
-            m = m0.clone(); flush.zero_()
+            m = m0.clone()
+            if not os.environ.get('NOFLUSH'): flush.zero_()
             e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
             e0.record()
             if what == "source":
