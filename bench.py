@@ -93,6 +93,18 @@ def moc_bytes_per_cell(N: int) -> float:
     return 8.0 * (2 * N + 3)  # read N n_i + eps, rho, nu; write N n_i (or S_i)
 
 
+def load_traffic(key: str, cells: int):
+    """dram bytes per launch from the committed ncu capture (profiles/r01_traffic.json), scaled by
+    the cell count when the bench runs another size; None when there is no capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as fh:
+            t = json.load(fh)[key]
+        per_cell = (t["dram_bytes_read"] + t["dram_bytes_write"]) / t["cells"]
+        return per_cell * cells
+    except Exception:
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -388,7 +400,10 @@ def run_b200(args):
     pipe_frac = cells * instr_cell * 2.0 / (kern_ms * 1e-3) / 1e12 / fp64_tf
     roofline = {
         "bound": "fp64", "achieved": tf, "peak": fp64_tf, "unit": "TFLOP/s", "frac": tf / fp64_tf,
-        "traffic": None, "kernel_ms": kern_ms,
+        "traffic": load_traffic("moc_tmem_kernel", cells) if (kinfo["kernel"] == "tmem" and N == 100) else None,
+        "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_traffic.json "
+                          "(captured at 1.6e7 cells; scaled per cell for other sizes)",
+        "algorithmic_bytes": cells * bytes_cell, "kernel_ms": kern_ms,
         "kernel": ("moc_tmem_kernel<CT,CT>" if kinfo["kernel"] == "tmem" else "moc_source_kernel<CT,CT,128>")
                   + f" ({kinfo['cells_per_cta']} cells/CTA, {kinfo['ctas_per_sm']} CTA/SM)",
         "peak_source": "measured in this run: register-resident DFMA chains (pbe_measure_fp64_peak); "
@@ -454,12 +469,17 @@ def run_b200(args):
         def qstep():
             q.step(mq, qe, qr, qn, wq.dt, S=Sq, d=dq)
 
+        # every step starts from the synthetic state (restored outside the timed region): with
+        # quadrature weights of 1e5..1e7 the explicit update leaves most moments on the SMALL clamp
+        # after one step (QMOM.C:117-123), and later steps would time the degenerate-cell path
         for _ in range(max(3, args.warmup)):
+            mq.copy_(m0)
             qstep()
         barrier()
         tot = 0.0
         qsteps = max(3, args.steps)
         for _ in range(qsteps):
+            mq.copy_(m0)
             flush.zero_()
             e0.record()
             qstep()
@@ -475,7 +495,8 @@ def run_b200(args):
                 "workload": "qmom3_ct: Wheeler inversion + 6 moment sources + scrub/update/clamp/d, CT kernels",
                 "l2": "flushed between timed launches (256 MB memset)",
                 "roofline": {"bound": "hbm", "achieved": qgbs, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": qgbs / hbm_peak, "bytes_per_cell": qbytes, "traffic": None,
+                             "frac": qgbs / hbm_peak, "bytes_per_cell": qbytes, "traffic": load_traffic("qmom_kernel", qc),
+                             "algorithmic_bytes": qc * qbytes,
                              "fp64_tflops": qtf, "fp64_frac": qtf / fp64_tf}}
         del m0, mq, Sq, flush
 

@@ -201,6 +201,54 @@ __device__ __forceinline__ void ninth_roots(double x, double &r, double &u) {
 }
 #endif
 
+// 2^y for y <= ~0, |y| < 2^27 (the caller clamps; NaN propagates), table-driven:
+//   16 y = 16 k + j + 16 f,  j in 0..15,  |f| <= 1/32:   2^y = 2^k T[j] (1 + f s(f)),
+// T[j] = 2^(j/16) read from a 128-byte table (16 FP64 entries = the 32 shared-memory banks once:
+// any mix of j across a warp is conflict-free), s of degree 5 (tools/gen_exp2_table_coeffs.py:
+// 0.11 ulp in exact arithmetic).  t = y + 1.5*2^48 rounds y to a multiple of 1/16 whose integer
+// 16 k + j sits in the low word of t.  10 FP64-pipe instructions (3 add, 6 fma, 1 mul) against
+// 13 for exp2_neg_fast; the table read and the integer work run on other pipes.
+#define PBE_EXP2_TAB_INIT                                                                          \
+    {1.0, 1.0442737824274138, 1.0905077326652577, 1.1387886347566916, 1.189207115002721,          \
+     1.241857812073484, 1.2968395546510096, 1.3542555469368927, 1.4142135623730951,                \
+     1.4768261459394993, 1.5422108254079407, 1.6104903319492543, 1.681792830507429,                \
+     1.7562521603732995, 1.8340080864093424, 1.9152065613971474}
+#if defined(__CUDACC__)
+static __constant__ double PBE_EXP2_TAB[16] = PBE_EXP2_TAB_INIT; // staged into shared memory by the kernels
+#endif
+PBE_HD double exp2_neg_tab(double y, const double *T) {
+    const double SHIFT = 422212465065984.0; // 1.5 * 2^48: ulp = 1/16
+    const double t = y + SHIFT;
+    const int m = lo_word(t);
+    const double f = y - (t - SHIFT);
+    double s = 0.00015403727871878627;
+    s = fma_(s, f, 0.0013333786067768005);
+    s = fma_(s, f, 0.009618129106890753);
+    s = fma_(s, f, 0.05550410865630706);
+    s = fma_(s, f, 0.24022650695910075);
+    s = fma_(s, f, 0.6931471805599457);
+    // Integer side kept on the ALU pipe (rotate + mask instead of shifts, which ptxas lowers to
+    // IMAD on the FMA pipe: tools/ubench_fp64_issue.cu shows FMA-pipe instructions taking FP64
+    // dispatch slots on sm_100a).  Table byte offset = (m & 15) * 8 = rotl(m, 3) & 0x78.
+#if defined(__CUDA_ARCH__)
+    const double Tj = *reinterpret_cast<const double *>(reinterpret_cast<const char *>(T) +
+                                                        (__funnelshift_l(m, m, 3) & 0x78));
+#else
+    const double Tj = T[m & 15];
+#endif
+    const double p = fma_(Tj * f, s, Tj); // in [1, 2): exponent field 1023
+    // 2^k by an integer add on the exponent field, k = m >> 4 clamped at -1022 (denormal-range
+    // results come out below 4.5e-308 instead of being rounded, like exp2_neg_fast):
+    // k << 20 = rotl(m, 16) & 0xFFF00000
+    const int mc = (m > -1022 * 16) ? m : -1022 * 16;
+#if defined(__CUDA_ARCH__)
+    const int kbits = (int)(__funnelshift_l(mc, mc, 16) & 0xFFF00000u);
+#else
+    const int kbits = (int)((unsigned)(mc >> 4) << 20);
+#endif
+    return make_double(hi_word(p) + kbits, lo_word(p));
+}
+
 // pow(x, 1/3) with C pow() semantics for the arguments the reference feeds it
 // (coalescenceKernels/CoulaloglouTavlarides.C:75-76): negative finite x -> NaN, +-0 -> 0.
 PBE_HD double pow_third(double x) { return x < 0.0 ? NAN : cbrt(x); }

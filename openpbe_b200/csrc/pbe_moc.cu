@@ -34,6 +34,7 @@ struct pbe_moc {
     size_t smem = 0;
     MocParams base{};      // table pointers, chunk offsets, folded coefficients
     double2 *d_pair = nullptr;
+    double2 *d_pair_log = nullptr; // CT, tensor-memory kernel: {log2 G_ij, H_ij}
     double *d_cls = nullptr;
 };
 
@@ -176,6 +177,7 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int grid = (int)std::min<int64_t>(nb, cap);
     if (m->use_tmem) {
         moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr);
+        if (m->dcoal == DCOAL_CT) p.pair_tab = m->d_pair_log;
         void *args[] = {(void *)&p, (void *)&m->sched};
         PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
         m->ctx->launches++;
@@ -388,7 +390,7 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
                 hmax = std::max(hmax, v.y);
                 hmin = std::min(hmin, v.y);
             }
-    b.negK_floor = (hmax > 0.0) ? -1073741824.0 / hmax : -INFINITY;
+    b.negK_floor = (hmax > 0.0) ? -67108864.0 / hmax : -INFINITY; // -2^26 / max H
     double qmax = 0.0, qmin = INFINITY; // CT breakup exponent table xi^(-5/9)
     if (m->dbr == DBR_CT)
         for (int i = 0; i < N; ++i) {
@@ -397,7 +399,7 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
         }
     b.negKb_floor = (qmax > 0.0) ? -1073741824.0 / qmax : -INFINITY;
     m->tmem_ok = m->tmem_cols > 0 && m->tmem_bytes <= ctx->smem_optin &&
-                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= 1e-6 * hmax && std::isfinite(hmax))) &&
+                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= hmax / 65536.0 && std::isfinite(hmax))) &&
                  (m->dbr != DBR_CT || (qmax > 0.0 && qmin >= 1e-6 * qmax && std::isfinite(qmax)));
     if (e == cudaSuccess && m->tmem_ok) {
         const void *tfn = (const void *)pick_tmem_kernel(m->dcoal, m->dbr);
@@ -439,6 +441,17 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
         if (e == cudaSuccess)
             e = cudaMemcpy(m->d_pair, tab.data(), tab.size() * sizeof(double2), cudaMemcpyHostToDevice);
     }
+    if (e == cudaSuccess && m->tmem_ok && m->dcoal == DCOAL_CT) {
+        // the tensor-memory kernel folds G into the exponent: S = A 2^(log2 G - K log2(e) H).
+        // Zero-weight padding slots get log2 G = -4096: 2^y is then below 4.5e-308 and is
+        // multiplied by the dummy class density 0.
+        std::vector<double2> tl(tab.size());
+        for (size_t k = 0; k < tab.size(); ++k)
+            tl[k] = make_double2(tab[k].x > 0.0 ? std::log2(tab[k].x) : -4096.0, tab[k].y);
+        e = cudaMalloc(&m->d_pair_log, tl.size() * sizeof(double2));
+        if (e == cudaSuccess)
+            e = cudaMemcpy(m->d_pair_log, tl.data(), tl.size() * sizeof(double2), cudaMemcpyHostToDevice);
+    }
     if (e == cudaSuccess) e = cudaMalloc(&m->d_cls, cls.size() * sizeof(double));
     if (e == cudaSuccess)
         e = cudaMemcpy(m->d_cls, cls.data(), cls.size() * sizeof(double), cudaMemcpyHostToDevice);
@@ -477,6 +490,7 @@ int pbe_moc_destroy(pbe_moc *m) {
     if (!m) return PBE_OK;
     DeviceGuard g(m->ctx->device);
     if (m->d_pair) cudaFree(m->d_pair);
+    if (m->d_pair_log) cudaFree(m->d_pair_log);
     if (m->d_cls) cudaFree(m->d_cls);
     delete m;
     return PBE_OK;

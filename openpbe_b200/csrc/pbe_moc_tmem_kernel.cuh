@@ -119,6 +119,7 @@ __host__ __device__ inline size_t moct_smem_bytes(int N, int slot_pairs) {
     b += (size_t)2 * slot_pairs * sizeof(double2);      // table ring
     b += (size_t)CLS_ROWS * (N + 1) * sizeof(double);   // per-class tables
     b += 2 * sizeof(uint64_t) + 16;                     // mbarriers, TMEM base address
+    b += 16 * sizeof(double);                           // 2^(j/16) table of exp2_neg_tab
     return b;
 }
 // TMEM columns per thread: 2 per accumulator, N + pad classes rounded up to whole x8 groups,
@@ -138,10 +139,12 @@ __device__ __forceinline__ double ldg_stream(const double *p) {
 }
 
 // ---- one TI x TJ tile of class pairs (register tile; identical sums to moc_tile) ---------------
-// K2 = -K_c log2(e): the Coulaloglou-Tavlarides efficiency exp(-K_c H_ij) is 2^(K2 H_ij)
-// (coalescenceKernels/CoulaloglouTavlarides.C:84-88).
+// K2 = -K_c log2(e): the Coulaloglou-Tavlarides kernel value G_ij exp(-K_c H_ij) is
+// 2^(log2 G_ij + K2 H_ij) (coalescenceKernels/CoulaloglouTavlarides.C:77-88); the CT table holds
+// {log2 G, H} and T16 is the 2^(j/16) table of exp2_neg_tab: 14 FP64-pipe instructions per pair.
 template <int COAL>
 __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, double K2,
+                                          const double *__restrict__ T16,
                                           const double (&ni)[MOC_TI], const double (&nj)[MOC_TJ],
                                           double (&di)[MOC_TI], double (&dj)[MOC_TJ],
                                           double (&bw)[MOC_TI + MOC_TJ - 1]) {
@@ -152,8 +155,7 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
             const double2 gh = tab[r * MOC_TJ + c];
             const double w = ni[r] * nj[c];
             if (COAL == DCOAL_CT) {
-                const double e = exp2_neg_fast(K2 * gh.y);
-                const double eg = e * gh.x;
+                const double eg = exp2_neg_tab(fma_(K2, gh.y, gh.x), T16);
                 di[r] = fma_(eg, w, di[r]);
                 dj[c] = fma_(eg, w, dj[c]);
                 bw[r + c] = fma_(eg, w, bw[r + c]);
@@ -172,9 +174,9 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
 }
 
 // ---- the kernel: two persistent CTAs per SM, 128 cells per batch ----------------------------------
-// p.negK_floor (MocParams) = -2^30 / max H: with it the 2^y argument stays inside
-// exp2_neg_fast's |y| < 2^31 contract; the host only selects this kernel when every H_ij >=
-// 1e-6 max H, so a clamped cell has every efficiency below 2^-1022 either way.
+// p.negK_floor (MocParams) = -2^26 / max H: with it the 2^y argument stays inside
+// exp2_neg_tab's |y| < 2^27 contract; the host only selects this kernel when every H_ij >=
+// 2^-16 max H, so a clamped cell has every efficiency below 2^-1024 either way.
 template <int COAL, int BR>
 __global__ void __launch_bounds__(MOCT_BLOCK, 2)
     moc_tmem_kernel(const __grid_constant__ MocParams p, const __grid_constant__ MoctSched sc) {
@@ -187,6 +189,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
     double *cls_s = n_s + (size_t)(N + 1) * BLOCK;
     uint64_t *bars = reinterpret_cast<uint64_t *>(cls_s + CLS_ROWS * (N + 1));
     uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 2);
+    double *T16 = reinterpret_cast<double *>(bars + 4); // 16-byte aligned: bars + 2 is, + 16 B
 
     const int64_t nbatches = (p.ncells + BLOCK - 1) / BLOCK;
     const int64_t my_batches =
@@ -202,6 +205,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
     }
     for (int k = tid; k < CLS_ROWS * (N + 1); k += BLOCK) cls_s[k] = p.cls[k];
     n_s[N * BLOCK + tid] = 0.0; // dummy class: absorbs padded table slots
+    if (tid < 16) T16[tid] = PBE_EXP2_TAB[tid];
     tmem_fence_before_sync();
     __syncthreads();
     tmem_fence_after_sync();
@@ -326,7 +330,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                             tmem_ld4(a_dj, vd);
                             tmem_ld4(a_bw, vb);
                         }
-                        moct_tile<COAL>(tab, K2, ni, nj, di, dj, bw);
+                        moct_tile<COAL>(tab, K2, T16, ni, nj, di, dj, bw);
                         if (!alias) {
                             tmem_wait_ld(vd, vb);
                             tm_axpy4(vd, -1.0, dj); // death of class j
