@@ -393,40 +393,75 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
         double *pS = (p.S_out != nullptr ? p.S_out : p.n_out) + (size_t)(c4top + 3) * p.stride + cc;
         double *pN = (p.do_step ? p.n_out : pS) + (p.do_step ? (size_t)(c4top + 3) * p.stride + cc : 0);
 
-        auto class_body = [&](const int i, const double acc) {
-            const double ni = n_s[i * BLOCK + tid];
-            // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
-            double g = cBP[i];
-            if (BR == DBR_CT) g = (Ab * g) * exp2_neg_fast(Kb2 * cBQ[i]);
-            const double gn = g * ni;
-            const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
-            R = fma_(cW[i], gn, R);
-            double s = fma_(A, acc, B);
-            // MOC.C:87-91: max(s, -relax n_i / dt).  The reference divides; a product with 1/dt
-            // is within 2 ulp of that, so the true division (bit-identical limited values) is
-            // only evaluated when s is within 1e-15 of the limit.
-            const double num = __dmul_rn(-p.relax, ni);
-            const double lim0 = num * inv_dt;
-            if (!(s > fma_(fabs(lim0), 1e-15, lim0))) {
-                const double lim = num / p.dt;
-                s = (s > lim) ? s : lim;
-            }
-            if (wS) *pS = s;
-            // n += dt S (MOC.C:259-272, phi = 0)
-            const double nn = p.do_step ? __dadd_rn(ni, __dmul_rn(p.dt, s)) : ni;
-            if (wN) *pN = nn;
-            sum_d = fma_(cDV[i], nn, sum_d);
-            sum_n += nn;
-            if (mom_mode == 1) {
-                mloc[0] += nn;
-                mloc[1] = fma_(cXI[i], nn, mloc[1]);
-            } else if (mom_mode == 2) {
-                const double x = cXI[i];
-                double pw = nn;
+        // Four classes per tensor-memory load, written as straight-line code over the group: the
+        // four breakup exponentials, limiter tests and moment chains are independent and
+        // interleave (two warps per scheduler leave little else to hide latency); only the suffix
+        // sum R runs serially, and the limiter's true division sits behind ONE rare branch per
+        // group instead of one per class.
+        auto group_body = [&](const int c4, const Tm4 &v, const bool full) {
+            double ni4[4], s4[4], num4[4];
+            bool need = false, need4[4];
 #pragma unroll
-                for (int k = 0; k < MOC_MAX_MOMENTS; ++k) {
-                    mloc[k] += pw;
-                    pw *= x;
+            for (int r = 3; r >= 0; --r) {
+                const int i = c4 + r;
+                const bool on = full || (i < N);
+                const int ii = on ? i : N; // row N: zero dummy class, zero table entries
+                const double ni = n_s[ii * BLOCK + tid];
+                // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
+                double g = cBP[ii];
+                if (BR == DBR_CT) g = (Ab * g) * exp2_neg_tab(Kb2 * cBQ[ii], T16);
+                const double gn = g * ni;
+                const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
+                R = fma_(cW[ii], gn, R);
+                const double s = fma_(A, tm_get(v, r), B);
+                // MOC.C:87-91: max(s, -relax n_i / dt).  The reference divides; a product with
+                // 1/dt is within 2 ulp of that, so the true division (bit-identical limited
+                // values) is only evaluated when s is within 1e-15 of the limit.
+                const double num = __dmul_rn(-p.relax, ni);
+                const double lim0 = num * inv_dt;
+                need4[r] = on && !(s > fma_(fabs(lim0), 1e-15, lim0));
+                need |= need4[r];
+                ni4[r] = ni;
+                s4[r] = s;
+                num4[r] = num;
+            }
+            if (need) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    if (need4[r]) {
+                        const double lim = num4[r] / p.dt;
+                        s4[r] = (s4[r] > lim) ? s4[r] : lim;
+                    }
+            }
+#pragma unroll
+            for (int r = 3; r >= 0; --r) {
+                const int i = c4 + r;
+                const bool on = full || (i < N);
+                const int ii = on ? i : N;
+                const double s = s4[r];
+                if (wS && on) *pS = s;
+                // n += dt S (MOC.C:259-272, phi = 0)
+                double nn = p.do_step ? __dadd_rn(ni4[r], __dmul_rn(p.dt, s)) : ni4[r];
+                nn = on ? nn : 0.0; // classes past N-1 of the last group do not exist
+                if (wN && on) *pN = nn;
+                pS -= p.stride;
+                pN -= p.stride;
+                sum_d = fma_(cDV[ii], nn, sum_d);
+                sum_n += nn;
+                if (mom_mode == 1) {
+                    mloc[0] += nn;
+                    mloc[1] = fma_(cXI[ii], nn, mloc[1]);
+                } else if (mom_mode == 2) {
+                    // xi^k n for k = 0..7 as two chains (even / odd powers) of depth 3
+                    const double x = cXI[ii], x2 = x * x;
+                    double pe = nn, po = nn * x;
+#pragma unroll
+                    for (int k = 0; k < MOC_MAX_MOMENTS; k += 2) {
+                        mloc[k] += pe;
+                        mloc[k + 1] += po;
+                        pe *= x2;
+                        po *= x2;
+                    }
                 }
             }
         };
@@ -439,21 +474,10 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                 tmem_ld4(tacc + 2u * (uint32_t)c4, v);
                 tmem_wait_ld(v);
             }
-            if (c4 + 3 < N) { // whole group of four classes: no per-class bound test
-#pragma unroll
-                for (int r = 3; r >= 0; --r) {
-                    class_body(c4 + r, tm_get(v, r));
-                    pS -= p.stride;
-                    pN -= p.stride;
-                }
-            } else {
-#pragma unroll
-                for (int r = 3; r >= 0; --r) {
-                    if (c4 + r < N) class_body(c4 + r, tm_get(v, r));
-                    pS -= p.stride;
-                    pN -= p.stride;
-                }
-            }
+            if (c4 + 3 < N)
+                group_body(c4, v, true);
+            else
+                group_body(c4, v, false);
         }
         if (p.d_out != nullptr && live) p.d_out[cell] = sum_d / sum_n; // MOC.C:282-290
         if (want_diag && live) {
