@@ -142,14 +142,16 @@ __device__ __forceinline__ double ldg_stream(const double *p) {
 // K2 = -K_c log2(e): the Coulaloglou-Tavlarides kernel value G_ij exp(-K_c H_ij) is
 // 2^(log2 G_ij + K2 H_ij) (coalescenceKernels/CoulaloglouTavlarides.C:77-88); the CT table holds
 // {log2 G, H} and T16 is the 2^(j/16) table of exp2_neg_tab: 14 FP64-pipe instructions per pair.
-template <int COAL>
+// Rows R0 .. R1-1 of the tile only: the kernel issues its tensor-memory traffic between the two
+// halves of a tile (see the pair sweep).
+template <int COAL, int R0 = 0, int R1 = MOC_TI>
 __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, double K2,
                                           const double *__restrict__ T16,
                                           const double (&ni)[MOC_TI], const double (&nj)[MOC_TJ],
                                           double (&di)[MOC_TI], double (&dj)[MOC_TJ],
                                           double (&bw)[MOC_TI + MOC_TJ - 1]) {
 #pragma unroll
-    for (int r = 0; r < MOC_TI; ++r) {
+    for (int r = R0; r < R1; ++r) {
 #pragma unroll
         for (int c = 0; c < MOC_TJ; ++c) {
             const double2 gh = tab[r * MOC_TJ + c];
@@ -258,6 +260,9 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
 
     int64_t q = 0;
     for (int64_t batch = blockIdx.x; batch < nbatches; batch += gridDim.x) {
+#ifdef PBE_PHASE_TIMING // scratch builds only (tools/moc_phase_time.py): cycles per phase
+        const long long tp0 = clock64();
+#endif
         const int64_t cell = batch * BLOCK + tid;
         const bool live = cell < p.ncells;
         const int64_t cc = live ? cell : p.ncells - 1;
@@ -292,6 +297,9 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
             K2 = negK * 1.4426950408889634074;
         }
 
+#ifdef PBE_PHASE_TIMING
+        const long long tp1 = clock64();
+#endif
         // ---- pair sweep: row blocks of TI classes, each in <= MOCT_SUB_TILES-tile ring slots ------
         if (COAL != DCOAL_OFF) {
 #pragma unroll 1
@@ -325,12 +333,15 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                         const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
                         const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
                         Tm4 vd, vb;
+                        // first half of the tile covers the latency of the previous tile's
+                        // stores, the second half that of this tile's loads
+                        moct_tile<COAL, 0, MOC_TI / 2>(tab, K2, T16, ni, nj, di, dj, bw);
                         tmem_wait_st(); // the previous tile's stores have landed
                         if (!alias) {
                             tmem_ld4(a_dj, vd);
                             tmem_ld4(a_bw, vb);
                         }
-                        moct_tile<COAL>(tab, K2, T16, ni, nj, di, dj, bw);
+                        moct_tile<COAL, MOC_TI / 2, MOC_TI>(tab, K2, T16, ni, nj, di, dj, bw);
                         if (!alias) {
                             tmem_wait_ld(vd, vb);
                             tm_axpy4(vd, -1.0, dj); // death of class j
@@ -374,6 +385,9 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
             tmem_wait_st();
         }
 
+#ifdef PBE_PHASE_TIMING
+        const long long tp2 = clock64();
+#endif
         // ---- epilogue: breakup (suffix sum), limiter, update, d, diagnostics ----------------
         double Ab = 0.0, Kb2 = 0.0;
         if (BR == DBR_CT) {
@@ -479,6 +493,14 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
             else
                 group_body(c4, v, false);
         }
+#ifdef PBE_PHASE_TIMING
+        if (tid == 0 && p.moments != nullptr) { // overwrites moments 5..7 with phase cycles
+            const long long tp3 = clock64();
+            atomicAdd(p.moments + 5, (double)(tp1 - tp0));
+            atomicAdd(p.moments + 6, (double)(tp2 - tp1));
+            atomicAdd(p.moments + 7, (double)(tp3 - tp2));
+        }
+#endif
         if (p.d_out != nullptr && live) p.d_out[cell] = sum_d / sum_n; // MOC.C:282-290
         if (want_diag && live) {
             const double V = (p.vcell != nullptr) ? __ldg(p.vcell + cell) : 1.0;

@@ -24,7 +24,9 @@ __global__ void __launch_bounds__(1024) k(double *out, int *iout, float *fout, i
             x[i] = __fma_rn(x[i], a, 1e-9);
 #pragma unroll
             for (int j = 0; j < J; ++j) {
-                if (KIND == 0) asm volatile("xor.b32 %0, %0, %1;" : "+r"(y[j][i]) : "r"(ia)); // one LOP3, 8 J independent chains
+                if (KIND == 0) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(y[j][i]) : "r"(ia), "r"(it)); // one LOP3 (3-input xor with the loop counter: not foldable), 8 J independent chains
+                if (KIND == 2) asm volatile("shf.l.wrap.b32 %0, %0, %1, %2;" : "+r"(y[j][i]) : "r"(ia), "r"(it)); // one SHF
+                if (KIND == 3) asm volatile("mad.lo.s32 %0, %0, %1, %2;" : "+r"(y[j][i]) : "r"(ia), "r"(it)); // one IMAD
                 if (KIND == 1) f[j][i] = __fmaf_rn(f[j][i], fa, 1e-9f);    // one FFMA
             }
         }
@@ -80,13 +82,17 @@ void run(const char *name, int warps_per_smsp) {
 }
 
 int main() {
-    for (int w : {1, 2, 4, 8}) {
+    for (int w : {2, 8}) {
         run<0, 0>("DFMA only", w);
         run<1, 0>("DFMA + 1 int", w);
         run<2, 0>("DFMA + 2 int", w);
         run<4, 0>("DFMA + 4 int", w);
         run<1, 1>("DFMA + 1 FFMA", w);
         run<2, 1>("DFMA + 2 FFMA", w);
+        run<1, 2>("DFMA + 1 SHF", w);
+        run<2, 2>("DFMA + 2 SHF", w);
+        run<1, 3>("DFMA + 1 IMAD", w);
+        run<2, 3>("DFMA + 2 IMAD", w);
     }
     return 0;
 }
