@@ -203,6 +203,15 @@ def dist_env():
 # ==================================================================================================
 # reference arm: the reference's CPU algorithm (oracle port), all host threads, bounded sample
 # ==================================================================================================
+def host_threads() -> int:
+    """Host threads this process may use.  Not omp_get_max_threads(): torchrun exports
+    OMP_NUM_THREADS=1 to every rank, which would time the reference arm on one core."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_reference_rate(w, sample_cells: int, nthreads: int, repeats: int = 1):
     """cell-class-updates/s of the reference-shaped CPU loops (oracle/pbe_oracle.c) on a slice."""
     from openpbe_b200 import synthetic
@@ -227,7 +236,7 @@ def run_reference(args):
 
     orc.build()
     w = synthetic.workload(args.workload)
-    threads = orc.lib().orc_max_threads()
+    threads = host_threads()
     sample = args.cpu_sample_cells
     f = synthetic.moc_fields(w, ncells=sample)
     sp = orc.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
@@ -275,7 +284,21 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # keep stdout to the one JSON line: NCCL_DEBUG=VERSION/INFO prints its banner there
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        # ... and whatever the communicator set-up still writes to fd 1 goes to stderr instead
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            t = torch.zeros(1, device=dev)
+            dist.all_reduce(t)  # creates the communicator now, inside the redirect
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
     ctx = engine.Context(local)
     info = ctx.info()
 
@@ -506,7 +529,7 @@ def run_b200(args):
         from oracle import cpu_oracle as orc
 
         orc.build()
-        threads = orc.lib().orc_max_threads()
+        threads = host_threads()
         rate, secs = cpu_reference_rate(w, args.cpu_sample_cells, threads)
         rate1, secs1 = cpu_reference_rate(w, max(64, args.cpu_sample_cells // max(1, threads)), 1)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
