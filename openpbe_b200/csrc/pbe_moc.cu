@@ -25,6 +25,7 @@ struct pbe_moc {
     int smem_ctas_per_sm = 1;
     size_t smem_bytes = 0;
     bool tmem_ok = false;  // tensor-memory kernel available for this N / table
+    bool tmem_wide = false; // tensor-memory kernel walking two table tiles per step (more registers)
     bool use_tmem = false; // Blackwell fast path: accumulators in tensor memory, 256 cells per CTA
     int tmem_cols = 0;     // TMEM columns per thread (= per CTA: one lane per thread)
     int tmem_ctas_per_sm = 1;
@@ -59,9 +60,10 @@ moc_kernel_fn pick_kernel(int dcoal, int dbr) {
 }
 
 typedef void (*moct_kernel_fn)(const MocParams, const MoctSched);
-moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr) {
-#define PBE_PICK(C, B) \
-    if (dcoal == C && dbr == B) return (moct_kernel_fn)moc_tmem_kernel<C, B>;
+moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr, bool wide) {
+#define PBE_PICK(C, B)                                                                             \
+    if (dcoal == C && dbr == B)                                                                    \
+        return wide ? (moct_kernel_fn)moc_tmem_kernel<C, B, true> : (moct_kernel_fn)moc_tmem_kernel<C, B, false>;
     PBE_PICK(DCOAL_OFF, DBR_TAB)
     PBE_PICK(DCOAL_OFF, DBR_CT)
     PBE_PICK(DCOAL_CT, DBR_TAB)
@@ -176,7 +178,7 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int64_t cap = (int64_t)m->ctx->sm_count * m->ctas_per_sm;
     const int grid = (int)std::min<int64_t>(nb, cap);
     if (m->use_tmem) {
-        moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr);
+        moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr, m->tmem_wide);
         if (m->dcoal == DCOAL_CT) p.pair_tab = m->d_pair_log;
         void *args[] = {(void *)&p, (void *)&m->sched};
         PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
@@ -397,16 +399,21 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
             qmax = std::max(qmax, cls[(size_t)CLS_BR_Q * (N + 1) + i]);
             qmin = std::min(qmin, cls[(size_t)CLS_BR_Q * (N + 1) + i]);
         }
-    b.negKb_floor = (qmax > 0.0) ? -1073741824.0 / qmax : -INFINITY;
+    b.negKb_floor = (qmax > 0.0) ? -67108864.0 / qmax : -INFINITY; // -2^26 / max xi^(-5/9)
     m->tmem_ok = m->tmem_cols > 0 && m->tmem_bytes <= ctx->smem_optin &&
                  (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= hmax / 65536.0 && std::isfinite(hmax))) &&
-                 (m->dbr != DBR_CT || (qmax > 0.0 && qmin >= 1e-6 * qmax && std::isfinite(qmax)));
+                 (m->dbr != DBR_CT || (qmax > 0.0 && qmin >= qmax / 65536.0 && std::isfinite(qmax)));
     if (e == cudaSuccess && m->tmem_ok) {
-        const void *tfn = (const void *)pick_tmem_kernel(m->dcoal, m->dbr);
-        e = cudaFuncSetAttribute(tfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m->tmem_bytes);
+        // Two instantiations: the wide one (two table tiles per step, ~190 registers) is faster
+        // per CTA but caps residency at 2 CTAs per SM; it is used where shared memory or tensor
+        // memory cap it there anyway (N >~ 60), the narrow one (~160 registers) elsewhere.
+        const void *tfn = nullptr;
         cudaFuncAttributes fa{};
-        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, tfn);
-        if (e == cudaSuccess) {
+        for (int wide = 1; wide >= 0 && e == cudaSuccess; --wide) {
+            tfn = (const void *)pick_tmem_kernel(m->dcoal, m->dbr, wide != 0);
+            e = cudaFuncSetAttribute(tfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m->tmem_bytes);
+            if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, tfn);
+            if (e != cudaSuccess) break;
             // cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for a kernel that holds a
             // tcgen05.alloc (it cannot see the column count), so the residency limit is computed
             // here: registers (allocated per warp in units of 256), shared memory (+1 KB the
@@ -415,7 +422,12 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
             const int by_regs = 65536 / (regs_per_warp * (MOCT_BLOCK / 32));
             const int by_smem = (int)(ctx->smem_per_sm / (m->tmem_bytes + fa.sharedSizeBytes + 1024));
             const int by_tmem = 512 / m->tmem_cols;
-            m->tmem_ctas_per_sm = std::max(1, std::min(std::min(by_regs, by_smem), std::min(by_tmem, 4)));
+            const int other = std::min(by_smem, std::min(by_tmem, 4));
+            m->tmem_ctas_per_sm = std::max(1, std::min(by_regs, other));
+            m->tmem_wide = (wide != 0);
+            if (by_regs >= other) break; // registers do not cost a CTA: keep this instantiation
+        }
+        if (e == cudaSuccess) {
             if (const char *f = getenv("PBE_MOC_TMEM_CTAS")) m->tmem_ctas_per_sm = std::max(1, atoi(f));
             // stagger = 1/k of the batch time of a CTA running alone: FP64-pipe instructions per
             // cell (19 per pair, 45 per class) x 2 cycles at the ~60 % pipe use of one warp per

@@ -144,32 +144,33 @@ __device__ __forceinline__ double ldg_stream(const double *p) {
 // {log2 G, H} and T16 is the 2^(j/16) table of exp2_neg_tab: 14 FP64-pipe instructions per pair.
 // Rows R0 .. R1-1 of the tile only: the kernel issues its tensor-memory traffic between the two
 // halves of a tile (see the pair sweep).
-template <int COAL, int R0 = 0, int R1 = MOC_TI>
+template <int COAL, int R0 = 0, int R1 = MOC_TI, int C0 = 0, int NJ = MOC_TJ>
 __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, double K2,
                                           const double *__restrict__ T16,
-                                          const double (&ni)[MOC_TI], const double (&nj)[MOC_TJ],
-                                          double (&di)[MOC_TI], double (&dj)[MOC_TJ],
-                                          double (&bw)[MOC_TI + MOC_TJ - 1]) {
+                                          const double (&ni)[MOC_TI], const double (&nj)[NJ],
+                                          double (&di)[MOC_TI], double (&dj)[NJ],
+                                          double (&bw)[MOC_TI + NJ - 1]) {
+    // C0: column offset of this table tile inside a double-width register tile (NJ = 2 TJ)
 #pragma unroll
     for (int r = R0; r < R1; ++r) {
 #pragma unroll
         for (int c = 0; c < MOC_TJ; ++c) {
             const double2 gh = tab[r * MOC_TJ + c];
-            const double w = ni[r] * nj[c];
+            const double w = ni[r] * nj[C0 + c];
             if (COAL == DCOAL_CT) {
                 const double eg = exp2_neg_tab(fma_(K2, gh.y, gh.x), T16);
                 di[r] = fma_(eg, w, di[r]);
-                dj[c] = fma_(eg, w, dj[c]);
-                bw[r + c] = fma_(eg, w, bw[r + c]);
+                dj[C0 + c] = fma_(eg, w, dj[C0 + c]);
+                bw[r + C0 + c] = fma_(eg, w, bw[r + C0 + c]);
             } else if (COAL == DCOAL_SYM) {
                 di[r] = fma_(gh.x, w, di[r]);
-                dj[c] = fma_(gh.x, w, dj[c]);
-                bw[r + c] = fma_(gh.x, w, bw[r + c]);
+                dj[C0 + c] = fma_(gh.x, w, dj[C0 + c]);
+                bw[r + C0 + c] = fma_(gh.x, w, bw[r + C0 + c]);
             } else { // DCOAL_ASYM: x = S(xi_i, xi_j), y = S(xi_j, xi_i)
                 const double t1 = gh.x * w, t2 = gh.y * w;
                 di[r] += t1;
-                dj[c] += t2;
-                bw[r + c] += 0.5 * (t1 + t2);
+                dj[C0 + c] += t2;
+                bw[r + C0 + c] += 0.5 * (t1 + t2);
             }
         }
     }
@@ -179,7 +180,7 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
 // p.negK_floor (MocParams) = -2^26 / max H: with it the 2^y argument stays inside
 // exp2_neg_tab's |y| < 2^27 contract; the host only selects this kernel when every H_ij >=
 // 2^-16 max H, so a clamped cell has every efficiency below 2^-1024 either way.
-template <int COAL, int BR>
+template <int COAL, int BR, bool WIDE>
 __global__ void __launch_bounds__(MOCT_BLOCK, 2)
     moc_tmem_kernel(const __grid_constant__ MocParams p, const __grid_constant__ MoctSched sc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -308,26 +309,69 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                 // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets
                 // j0.. of the same tile, so the two read-modify-writes are serialised
                 const bool alias = (i0 + 1 < MOC_TJ);
-                double ni[MOC_TI], di[MOC_TI], bw[MOC_TI + MOC_TJ - 1];
+                // Row blocks from i0 = 2 TJ - 1 on walk the table two tiles at a time (a TI x 2TJ
+                // register tile: 32 independent pair chains, one tensor-memory round trip and
+                // one loop trip per 32 pairs); below that the 2TJ column targets and the 2TJ
+                // anti-diagonal targets of one step would overlap.
+                const bool wide = WIDE && (i0 + 1 >= 2 * MOC_TJ);
+                constexpr int NJ2 = 2 * MOC_TJ, NB2 = MOC_TI + 2 * MOC_TJ - 1;
+                double ni[MOC_TI], di[MOC_TI], bw[NB2];
 #pragma unroll
                 for (int r = 0; r < MOC_TI; ++r) {
                     ni[r] = n_s[min(i0 + r, N) * BLOCK + tid];
                     di[r] = 0.0;
                 }
 #pragma unroll
-                for (int w = 0; w < MOC_TI + MOC_TJ - 1; ++w) bw[w] = 0.0;
+                for (int w = 0; w < NB2; ++w) bw[w] = 0.0;
                 int j0 = i0;
 #pragma unroll 1
                 for (int s = sc.blk_sub0[blk]; s < (int)sc.blk_sub0[blk + 1]; ++s, ++q) {
                     mbar_wait(&bars[q & 1], (unsigned)((q >> 1) & 1));
                     const double2 *__restrict__ tab = ring + (q & 1) * (size_t)sc.slot_pairs;
                     const int ntiles = (sc.sub_off[s + 1] - sc.sub_off[s]) / (MOC_TI * MOC_TJ);
+                    int t = 0;
+                    if (wide) {
 #pragma unroll 1
-                    for (int t = 0; t < ntiles; ++t, j0 += MOC_TJ, tab += MOC_TI * MOC_TJ) {
-                        double nj[MOC_TJ], dj[MOC_TJ];
+                        for (; t + 1 < ntiles; t += 2, j0 += NJ2, tab += 2 * MOC_TI * MOC_TJ) {
+                            double nj[NJ2], dj[NJ2];
 #pragma unroll
-                        for (int c = 0; c < MOC_TJ; ++c) {
-                            nj[c] = n_s[min(j0 + c, N) * BLOCK + tid];
+                            for (int c = 0; c < NJ2; ++c) {
+                                nj[c] = n_s[min(j0 + c, N) * BLOCK + tid];
+                                dj[c] = 0.0;
+                            }
+                            const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
+                            const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
+                            Tm4 vd0, vd1, vb0, vb1;
+                            // the first table tile covers the latency of the previous step's
+                            // stores, the second that of this step's loads
+                            moct_tile<COAL, 0, MOC_TI, 0, NJ2>(tab, K2, T16, ni, nj, di, dj, bw);
+                            tmem_wait_st();
+                            tmem_ld4(a_dj, vd0);
+                            tmem_ld4(a_dj + 8u, vd1);
+                            tmem_ld4(a_bw, vb0);
+                            tmem_ld4(a_bw + 8u, vb1);
+                            moct_tile<COAL, 0, MOC_TI, MOC_TJ, NJ2>(tab + MOC_TI * MOC_TJ, K2, T16, ni, nj,
+                                                                    di, dj, bw);
+                            tmem_wait_ld(vd0, vd1);
+                            tmem_wait_ld(vb0, vb1);
+                            tm_axpy4(vd0, -1.0, dj); // death of class j
+                            tm_axpy4(vd1, -1.0, dj + MOC_TJ);
+                            tm_axpy4(vb0, 1.0, bw);  // birth of class i+j+1: 2TJ lowest anti-diagonals
+                            tm_axpy4(vb1, 1.0, bw + MOC_TJ);
+                            tmem_st4(a_dj, vd0);
+                            tmem_st4(a_dj + 8u, vd1);
+                            tmem_st4(a_bw, vb0);
+                            tmem_st4(a_bw + 8u, vb1);
+#pragma unroll
+                            for (int w = 0; w < NB2; ++w) bw[w] = (w + NJ2 < NB2) ? bw[w + NJ2] : 0.0;
+                        }
+                    }
+#pragma unroll 1
+                    for (; t < ntiles; ++t, j0 += MOC_TJ, tab += MOC_TI * MOC_TJ) {
+                        double nj[NJ2], dj[NJ2];
+#pragma unroll
+                        for (int c = 0; c < NJ2; ++c) {
+                            nj[c] = (c < MOC_TJ) ? n_s[min(j0 + c, N) * BLOCK + tid] : 0.0;
                             dj[c] = 0.0;
                         }
                         const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
@@ -335,13 +379,13 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                         Tm4 vd, vb;
                         // first half of the tile covers the latency of the previous tile's
                         // stores, the second half that of this tile's loads
-                        moct_tile<COAL, 0, MOC_TI / 2>(tab, K2, T16, ni, nj, di, dj, bw);
+                        moct_tile<COAL, 0, MOC_TI / 2, 0, NJ2>(tab, K2, T16, ni, nj, di, dj, bw);
                         tmem_wait_st(); // the previous tile's stores have landed
                         if (!alias) {
                             tmem_ld4(a_dj, vd);
                             tmem_ld4(a_bw, vb);
                         }
-                        moct_tile<COAL, MOC_TI / 2, MOC_TI>(tab, K2, T16, ni, nj, di, dj, bw);
+                        moct_tile<COAL, MOC_TI / 2, MOC_TI, 0, NJ2>(tab, K2, T16, ni, nj, di, dj, bw);
                         if (!alias) {
                             tmem_wait_ld(vd, vb);
                             tm_axpy4(vd, -1.0, dj); // death of class j
@@ -360,8 +404,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                             tmem_st4(a_bw, vb);
                         }
 #pragma unroll
-                        for (int w = 0; w < MOC_TI + MOC_TJ - 1; ++w)
-                            bw[w] = (w + MOC_TJ < MOC_TI + MOC_TJ - 1) ? bw[w + MOC_TJ] : 0.0;
+                        for (int w = 0; w < NB2; ++w) bw[w] = (w + MOC_TJ < NB2) ? bw[w + MOC_TJ] : 0.0;
                     }
                     __syncthreads(); // every warp is done with ring slot q&1
                     if (tid == 0 && q + 2 < total_q) issue(q + 2);
