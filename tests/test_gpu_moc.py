@@ -100,6 +100,23 @@ def test_source_parity_kernel_combinations(ctx, oracle, N, coal, cc, br, bc):
     assert_parity(S, So, scale)
 
 
+# ---- cells far outside the synthetic range: efficiencies from 1 down to below 2^-1022, the
+# exponent clamps of the tensor-memory kernel (negK_floor, negKb_floor) and its 2^k floor ----------
+@pytest.mark.parametrize("N", [30, 100])
+def test_source_parity_extreme_cells(ctx, oracle, N, moc_kernel):
+    rng = np.random.default_rng(N)
+    ncells = 160
+    n = rng.uniform(1e5, 1e7, (N, ncells))
+    eps = 10.0 ** rng.uniform(-12.0, 12.0, ncells)        # exp(-K H): K H from ~1e-20 to ~1e40
+    rho = 10.0 ** rng.uniform(-2.0, 5.0, ncells)
+    nu = 10.0 ** rng.uniform(-9.0, 0.0, ncells)
+    eps[:4] = [1e-300, 1e300, 1e-30, 1e30]
+    S, So, scale = run_pair(ctx, oracle, N, 3e-10 / N, n, eps, rho, nu, 2.5e-4,
+                            "CoulaloglouTavlaridesC", CT, "CoulaloglouTavlarides", CT)
+    assert np.isfinite(So).all()
+    assert_parity(S, So, scale)
+
+
 # ---- ragged / empty cell counts, padded stride -------------------------------------------------
 @pytest.mark.parametrize("ncells", [1, 2, 31, 32, 33, 127, 128, 129, 255, 256, 257, 1000, 148 * 128 + 5, 148 * 256 + 5])
 def test_source_parity_ragged_cells(ctx, oracle, ncells):
