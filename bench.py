@@ -57,9 +57,9 @@ UNIT = "cell-class-updates/s"
 #     of the tile loop and the epilogue): 18.9 per pair, 44 per class with 6 moments.  The FP64 pipe
 #     retires one warp instruction per scheduler every 2 cycles whatever the opcode, so
 #     instructions x 2 / DFMA-peak is the pipe utilisation (`roofline.fp64_pipe_frac`).
-FP64_INSTR_PER_PAIR_CT = 16.5   # 15.25 per table slot x 2704 slots / 2500 valid pairs at N = 100 (8 % zero padding)
+FP64_INSTR_PER_PAIR_CT = 14.3   # 13.25 per table slot x 2704 slots / 2500 valid pairs at N = 100 (8 % zero padding)
 FP64_INSTR_PER_PAIR_TAB = 4.0
-FP64_INSTR_PER_CLASS_CT = 43.5  # ncu r01p: 45 583 FP64 warp instructions per cell in total
+FP64_INSTR_PER_CLASS_CT = 41.5  # ncu r01p (16-entry table, 2 more per exponential): 45 583 FP64 instructions per cell
 FP64_INSTR_PER_CLASS_TAB = 30.0
 FLOPS_QMOM3_CT = 1300.0
 FLOPS_QMOM3_CONST = 600.0

@@ -202,49 +202,97 @@ __device__ __forceinline__ void ninth_roots(double x, double &r, double &u) {
 #endif
 
 // 2^y for y <= ~0, |y| < 2^27 (the caller clamps; NaN propagates), table-driven:
-//   16 y = 16 k + j + 16 f,  j in 0..15,  |f| <= 1/32:   2^y = 2^k T[j] (1 + f s(f)),
-// T[j] = 2^(j/16) read from a 128-byte table (16 FP64 entries = the 32 shared-memory banks once:
-// any mix of j across a warp is conflict-free), s of degree 5 (tools/gen_exp2_table_coeffs.py:
-// 0.11 ulp in exact arithmetic).  t = y + 1.5*2^48 rounds y to a multiple of 1/16 whose integer
-// 16 k + j sits in the low word of t.  10 FP64-pipe instructions (3 add, 6 fma, 1 mul) against
-// 13 for exp2_neg_fast; the table read and the integer work run on other pipes.
-#define PBE_EXP2_TAB_INIT                                                                          \
-    {1.0, 1.0442737824274138, 1.0905077326652577, 1.1387886347566916, 1.189207115002721,          \
-     1.241857812073484, 1.2968395546510096, 1.3542555469368927, 1.4142135623730951,                \
-     1.4768261459394993, 1.5422108254079407, 1.6104903319492543, 1.681792830507429,                \
-     1.7562521603732995, 1.8340080864093424, 1.9152065613971474}
+//   2^LOGT y = 2^LOGT k + j + 2^LOGT f,  j in 0..2^LOGT-1,  |f| <= 2^-(LOGT+1):
+//   2^y = 2^k T[j] (1 + f s(f)),   T[j] = 2^(j / 2^LOGT) read from shared memory.
+// t = y + 1.5*2^(52-LOGT) rounds y to a multiple of 2^-LOGT whose integer 2^LOGT k + j sits in
+// the low word of t.  Three sizes (tools/gen_exp2_table_coeffs.py):
+//   LOGT 4:  16 entries (128 B = the 32 banks once: any mix of j across a warp is conflict-free),
+//            s of degree 5, 0.11 ulp in exact arithmetic, 10 FP64-pipe instructions
+//   LOGT 5:  32 entries, s of degree 4 (1.2e-16),  9 FP64-pipe instructions, <= 2-way conflicts
+//   LOGT 7: 128 entries, s of degree 3 (1.3e-16),  8 FP64-pipe instructions, <= 8-way conflicts
+// against 13 for exp2_neg_fast; the table read and the integer work run on other pipes.
+#define PBE_EXP2_TAB128_INIT                                                                       \
+    {1.0, 1.0054299011128027, 1.0108892860517005, 1.016378314910953, \
+     1.0218971486541166, 1.0274459491187637, 1.0330248790212284, 1.0386341019613787, \
+     1.0442737824274138, 1.0499440858006872, 1.0556451783605572, 1.061377227289262, \
+     1.0671404006768237, 1.0729348675259756, 1.0787607977571199, 1.0846183622133092, \
+     1.0905077326652577, 1.0964290818163769, 1.102382583307841, 1.1083684117236787, \
+     1.1143867425958924, 1.1204377524096067, 1.1265216186082418, 1.1326385195987192, \
+     1.1387886347566916, 1.1449721444318042, 1.1511892299529827, 1.1574400736337511, \
+     1.1637248587775775, 1.1700437696832502, 1.1763969916502812, 1.182784710984341, \
+     1.189207115002721, 1.1956643920398273, 1.202156731452703, 1.2086843236265816, \
+     1.215247359980469, 1.2218460329727576, 1.22848053610687, 1.2351510639369334, \
+     1.241857812073484, 1.2486009771892048, 1.255380757024691, 1.2621973503942507, \
+     1.2690509571917332, 1.275941778396392, 1.2828700160787783, 1.2898358734066657, \
+     1.2968395546510096, 1.3038812651919358, 1.3109612115247644, 1.318079601266064, \
+     1.3252366431597413, 1.3324325470831615, 1.339667524053303, 1.3469417862329458, \
+     1.3542555469368927, 1.3616090206382248, 1.3690024229745905, 1.3764359707545302, \
+     1.383909881963832, 1.3914243757719262, 1.3989796725383112, 1.4065759938190154, \
+     1.4142135623730951, 1.4218926021691656, 1.42961333839197, 1.4373759974489824, \
+     1.4451808069770467, 1.4530279958490526, 1.460917794180647, 1.4688504333369818, \
+     1.4768261459394993, 1.4848451658727524, 1.4929077282912648, 1.5010140696264256, \
+     1.5091644275934228, 1.5173590411982147, 1.5255981507445384, 1.533881997840956, \
+     1.5422108254079407, 1.550584877685, 1.559004400237837, 1.567469639965553, \
+     1.5759808451078865, 1.5845382652524937, 1.593142151342267, 1.6017927556826934, \
+     1.6104903319492543, 1.6192351351948637, 1.6280274218573478, 1.6368674497669644, \
+     1.645755478153965, 1.6546917676561943, 1.6636765803267364, 1.6727101796415966, \
+     1.681792830507429, 1.6909247992693053, 1.7001063537185235, 1.709337763100463, \
+     1.718619298122478, 1.7279512309618377, 1.7373338352737062, 1.746767386199169, \
+     1.7562521603732995, 1.7657884359332727, 1.7753764925265212, 1.785016611318935, \
+     1.7947090750031072, 1.804454167806624, 1.8142521755003989, 1.8241033854070534, \
+     1.8340080864093424, 1.843966568958626, 1.8539791250833855, 1.864046048397789, \
+     1.8741676341103, 1.8843441790323345, 1.8945759815869656, 1.9048633418176741, \
+     1.9152065613971474, 1.925605943636125, 1.9360617934922943, 1.9465744175792332, \
+     1.9571441241754002, 1.9677712232331759, 1.978456026387951, 1.9891988469672663}
 #if defined(__CUDACC__)
-static __constant__ double PBE_EXP2_TAB[16] = PBE_EXP2_TAB_INIT; // staged into shared memory by the kernels
+static __constant__ double PBE_EXP2_TAB128[128] = PBE_EXP2_TAB128_INIT; // staged into shared memory by the kernels
 #endif
+template <int LOGT>
 PBE_HD double exp2_neg_tab(double y, const double *T) {
-    const double SHIFT = 422212465065984.0; // 1.5 * 2^48: ulp = 1/16
+    static_assert(LOGT == 4 || LOGT == 5 || LOGT == 7, "table sizes with a fitted polynomial");
+    const double SHIFT = 6755399441055744.0 / (double)(1 << LOGT); // 1.5 * 2^(52 - LOGT)
     const double t = y + SHIFT;
     const int m = lo_word(t);
     const double f = y - (t - SHIFT);
-    double s = 0.00015403727871878627;
-    s = fma_(s, f, 0.0013333786067768005);
-    s = fma_(s, f, 0.009618129106890753);
-    s = fma_(s, f, 0.05550410865630706);
-    s = fma_(s, f, 0.24022650695910075);
-    s = fma_(s, f, 0.6931471805599457);
+    double s;
+    if (LOGT == 4) {
+        s = 0.00015403727871878627;
+        s = fma_(s, f, 0.0013333786067768005);
+        s = fma_(s, f, 0.009618129106890753);
+        s = fma_(s, f, 0.05550410865630706);
+        s = fma_(s, f, 0.24022650695910075);
+        s = fma_(s, f, 0.6931471805599457);
+    } else if (LOGT == 5) {
+        s = 0.001333360562976466;
+        s = fma_(s, f, 0.009618177060432826);
+        s = fma_(s, f, 0.05550410866452594);
+        s = fma_(s, f, 0.24022650695611508);
+        s = fma_(s, f, 0.6931471805599453);
+    } else {
+        s = 0.009618131505263852;
+        s = fma_(s, f, 0.05550412941916238);
+        s = fma_(s, f, 0.24022650695909606);
+        s = fma_(s, f, 0.6931471805599049);
+    }
     // Integer side kept on the ALU pipe (rotate + mask instead of shifts, which ptxas lowers to
     // IMAD on the FMA pipe: tools/ubench_fp64_issue.cu shows FMA-pipe instructions taking FP64
-    // dispatch slots on sm_100a).  Table byte offset = (m & 15) * 8 = rotl(m, 3) & 0x78.
+    // dispatch slots on sm_100a).  Table byte offset = (m & (2^LOGT - 1)) * 8 = rotl(m, 3) & mask.
+    constexpr int NT = 1 << LOGT;
 #if defined(__CUDA_ARCH__)
     const double Tj = *reinterpret_cast<const double *>(reinterpret_cast<const char *>(T) +
-                                                        (__funnelshift_l(m, m, 3) & 0x78));
+                                                        (__funnelshift_l(m, m, 3) & ((NT - 1) << 3)));
 #else
-    const double Tj = T[m & 15];
+    const double Tj = T[m & (NT - 1)];
 #endif
     const double p = fma_(Tj * f, s, Tj); // in [1, 2): exponent field 1023
-    // 2^k by an integer add on the exponent field, k = m >> 4 clamped at -1022 (denormal-range
+    // 2^k by an integer add on the exponent field, k = m >> LOGT clamped at -1022 (denormal-range
     // results come out below 4.5e-308 instead of being rounded, like exp2_neg_fast):
-    // k << 20 = rotl(m, 16) & 0xFFF00000
-    const int mc = (m > -1022 * 16) ? m : -1022 * 16;
+    // k << 20 = rotl(m, 20 - LOGT) & 0xFFF00000
+    const int mc = (m > -1022 * NT) ? m : -1022 * NT;
 #if defined(__CUDA_ARCH__)
-    const int kbits = (int)(__funnelshift_l(mc, mc, 16) & 0xFFF00000u);
+    const int kbits = (int)(__funnelshift_l(mc, mc, 20 - LOGT) & 0xFFF00000u);
 #else
-    const int kbits = (int)((unsigned)(mc >> 4) << 20);
+    const int kbits = (int)((unsigned)(mc >> LOGT) << 20);
 #endif
     return make_double(hi_word(p) + kbits, lo_word(p));
 }

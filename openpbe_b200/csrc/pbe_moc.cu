@@ -392,17 +392,19 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
                 hmax = std::max(hmax, v.y);
                 hmin = std::min(hmin, v.y);
             }
-    b.negK_floor = (hmax > 0.0) ? -67108864.0 / hmax : -INFINITY; // -2^26 / max H
+    // exp2_neg_tab<LOGT> needs |2^LOGT y| < 2^31: |K log2(e) H| <= 1.45 * 2^(29 - LOGT)
+    const double exp_arg_cap = (double)(1 << (29 - MOCT_LOGT));
+    b.negK_floor = (hmax > 0.0) ? -exp_arg_cap / hmax : -INFINITY;
     double qmax = 0.0, qmin = INFINITY; // CT breakup exponent table xi^(-5/9)
     if (m->dbr == DBR_CT)
         for (int i = 0; i < N; ++i) {
             qmax = std::max(qmax, cls[(size_t)CLS_BR_Q * (N + 1) + i]);
             qmin = std::min(qmin, cls[(size_t)CLS_BR_Q * (N + 1) + i]);
         }
-    b.negKb_floor = (qmax > 0.0) ? -67108864.0 / qmax : -INFINITY; // -2^26 / max xi^(-5/9)
+    b.negKb_floor = (qmax > 0.0) ? -exp_arg_cap / qmax : -INFINITY;
     m->tmem_ok = m->tmem_cols > 0 && m->tmem_bytes <= ctx->smem_optin &&
-                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= hmax / 65536.0 && std::isfinite(hmax))) &&
-                 (m->dbr != DBR_CT || (qmax > 0.0 && qmin >= qmax / 65536.0 && std::isfinite(qmax)));
+                 (m->dcoal != DCOAL_CT || (hmax > 0.0 && hmin >= hmax * (1024.0 / exp_arg_cap) && std::isfinite(hmax))) &&
+                 (m->dbr != DBR_CT || (qmax > 0.0 && qmin >= qmax * (1024.0 / exp_arg_cap) && std::isfinite(qmax)));
     if (e == cudaSuccess && m->tmem_ok) {
         // Two instantiations: the wide one (two table tiles per step, ~190 registers) is faster
         // per CTA but caps residency at 2 CTAs per SM; it is used where shared memory or tensor

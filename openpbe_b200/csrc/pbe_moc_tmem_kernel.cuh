@@ -29,7 +29,14 @@ namespace pbe {
 
 constexpr int MOCT_BLOCK = 128;       // cells (threads) per CTA
 constexpr int MOCT_PAD_CLASSES = 10;  // scratch bins above class N-1 (see header)
-constexpr int MOCT_SUB_TILES = 13;    // ring slot = at most 13 tiles (3328 B) of one row block
+constexpr int MOCT_SUB_TILES = 12;    // ring slot = at most 12 tiles (3072 B) of one row block
+#ifndef PBE_MOCT_LOGT
+#define PBE_MOCT_LOGT 7
+#endif
+// log2 of the 2^y table size (exp2_neg_tab: 4, 5 or 7).  Measured at N = 100, 6.06e6 cells:
+// 16 entries 22.80 ms, 32 entries 21.96 ms, 128 entries 21.08 ms -- the two FP64 instructions the
+// shorter polynomial saves per pair outweigh the bank conflicts of the 1 KB table.
+constexpr int MOCT_LOGT = PBE_MOCT_LOGT;
 constexpr int MOCT_MAX_SUBS = 2 * MOC_MAX_BLOCKS;
 
 
@@ -119,7 +126,7 @@ __host__ __device__ inline size_t moct_smem_bytes(int N, int slot_pairs) {
     b += (size_t)2 * slot_pairs * sizeof(double2);      // table ring
     b += (size_t)CLS_ROWS * (N + 1) * sizeof(double);   // per-class tables
     b += 2 * sizeof(uint64_t) + 16;                     // mbarriers, TMEM base address
-    b += 16 * sizeof(double);                           // 2^(j/16) table of exp2_neg_tab
+    b += (size_t)(1 << MOCT_LOGT) * sizeof(double);     // 2^(j/2^LOGT) table of exp2_neg_tab
     return b;
 }
 // TMEM columns per thread: 2 per accumulator, N + pad classes rounded up to whole x8 groups,
@@ -141,7 +148,7 @@ __device__ __forceinline__ double ldg_stream(const double *p) {
 // ---- one TI x TJ tile of class pairs (register tile; identical sums to moc_tile) ---------------
 // K2 = -K_c log2(e): the Coulaloglou-Tavlarides kernel value G_ij exp(-K_c H_ij) is
 // 2^(log2 G_ij + K2 H_ij) (coalescenceKernels/CoulaloglouTavlarides.C:77-88); the CT table holds
-// {log2 G, H} and T16 is the 2^(j/16) table of exp2_neg_tab: 14 FP64-pipe instructions per pair.
+// {log2 G, H} and T16 is the 2^(j/2^LOGT) table of exp2_neg_tab: 13 FP64-pipe instructions per pair.
 // Rows R0 .. R1-1 of the tile only: the kernel issues its tensor-memory traffic between the two
 // halves of a tile (see the pair sweep).
 template <int COAL, int R0 = 0, int R1 = MOC_TI, int C0 = 0, int NJ = MOC_TJ>
@@ -158,7 +165,7 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
             const double2 gh = tab[r * MOC_TJ + c];
             const double w = ni[r] * nj[C0 + c];
             if (COAL == DCOAL_CT) {
-                const double eg = exp2_neg_tab(fma_(K2, gh.y, gh.x), T16);
+                const double eg = exp2_neg_tab<MOCT_LOGT>(fma_(K2, gh.y, gh.x), T16);
                 di[r] = fma_(eg, w, di[r]);
                 dj[C0 + c] = fma_(eg, w, dj[C0 + c]);
                 bw[r + C0 + c] = fma_(eg, w, bw[r + C0 + c]);
@@ -177,9 +184,9 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
 }
 
 // ---- the kernel: two persistent CTAs per SM, 128 cells per batch ----------------------------------
-// p.negK_floor (MocParams) = -2^26 / max H: with it the 2^y argument stays inside
-// exp2_neg_tab's |y| < 2^27 contract; the host only selects this kernel when every H_ij >=
-// 2^-16 max H, so a clamped cell has every efficiency below 2^-1024 either way.
+// p.negK_floor (MocParams) = -2^(29-LOGT) / max H: with it 2^LOGT y of exp2_neg_tab stays inside
+// an int32; the host only selects this kernel when every H_ij >= 2^(LOGT-19) max H, so a clamped
+// cell has every efficiency below 2^-1024 either way.
 template <int COAL, int BR, bool WIDE>
 __global__ void __launch_bounds__(MOCT_BLOCK, 2)
     moc_tmem_kernel(const __grid_constant__ MocParams p, const __grid_constant__ MoctSched sc) {
@@ -208,7 +215,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
     }
     for (int k = tid; k < CLS_ROWS * (N + 1); k += BLOCK) cls_s[k] = p.cls[k];
     n_s[N * BLOCK + tid] = 0.0; // dummy class: absorbs padded table slots
-    if (tid < 16) T16[tid] = PBE_EXP2_TAB[tid];
+    if (tid < (1 << MOCT_LOGT)) T16[tid] = PBE_EXP2_TAB128[tid << (7 - MOCT_LOGT)];
     tmem_fence_before_sync();
     __syncthreads();
     tmem_fence_after_sync();
@@ -466,7 +473,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
                 const double ni = n_s[ii * BLOCK + tid];
                 // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
                 double g = cBP[ii];
-                if (BR == DBR_CT) g = (Ab * g) * exp2_neg_tab(Kb2 * cBQ[ii], T16);
+                if (BR == DBR_CT) g = (Ab * g) * exp2_neg_tab<MOCT_LOGT>(Kb2 * cBQ[ii], T16);
                 const double gn = g * ni;
                 const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
                 R = fma_(cW[ii], gn, R);
