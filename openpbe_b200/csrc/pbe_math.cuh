@@ -297,6 +297,18 @@ PBE_HD double exp2_neg_tab(double y, const double *T) {
     return make_double(hi_word(p) + kbits, lo_word(p));
 }
 
+#if defined(__CUDACC__)
+// exp(x) = 2^(x log2 e) for x <= 0 given y = x log2(e), through the 128-entry table: 8 FP64-pipe
+// instructions; results below 2^-1100 (incl. y = -inf) are 0, NaN propagates (its hi word is
+// outside [hi(-1100.0), hi(-inf)]).
+__device__ __forceinline__ double exp2_neg_tab_safe(double y, const double *T128) {
+    const double r = exp2_neg_tab<7>(y, T128);
+    const unsigned uy = (unsigned)__double2hiint(y);
+    const bool under = (uy - 0xC0913000u) <= (0xFFF00000u - 0xC0913000u);
+    return under ? 0.0 : r;
+}
+#endif
+
 // pow(x, 1/3) with C pow() semantics for the arguments the reference feeds it
 // (coalescenceKernels/CoulaloglouTavlarides.C:75-76): negative finite x -> NaN, +-0 -> 0.
 PBE_HD double pow_third(double x) { return x < 0.0 ? NAN : cbrt(x); }

@@ -36,11 +36,14 @@ namespace pbe {
 template <int N, int COAL, int BR>
 __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const double (&x)[N],
                                                   const double (&w)[N], double eps, double rho,
-                                                  double nu, double (&out)[2 * N]) {
+                                                  double nu, const double *__restrict__ T128,
+                                                  double (&out)[2 * N]) {
     constexpr bool ct_c = (COAL == PBE_COAL_CT), ct_b = (BR == PBE_BR_CT);
     CellCoef cc;
     cc.A = cc.negK = cc.Ab = cc.negKb = 0.0;
     if (ct_c || ct_b) cc = cell_coef(ks, eps, rho, nu);
+    // exponentials as 2^(K log2(e) .) through the shared-memory table (exp2_neg_tab_safe)
+    const double K2 = cc.negK * 1.4426950408889634074, Kb2 = cc.negKb * 1.4426950408889634074;
     double ra[N], rp[N], ia[N], r1[N], gw[N]; // x^(1/3), x^(2/9), x^(-1/3), x^(1/9), w_i g_i
 #pragma unroll
     for (int i = 0; i < N; ++i) {
@@ -55,7 +58,7 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
             r1[i] = r9;
             ia[i] = u2 * u9;
             if (ct_b) // breakupKernels/CoulaloglouTavlarides.C:83-92
-                g = (cc.Ab * u2) * exp_neg_c(cc.negKb * (ia[i] * u2));
+                g = (cc.Ab * u2) * exp2_neg_tab_safe(Kb2 * (ia[i] * u2), T128);
         }
         if (BR == PBE_BR_BINARY) g = x[i] * x[i]; // binaryBreakup.C:51-53
         gw[i] = w[i] * g;
@@ -76,13 +79,13 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
                 const double G = (4.0 * 1.41421356237309504880) * (ra[i] * ra[i]) * r1[i];
                 const double h = (0.5 * ra[i]) * t;
                 const double h2 = h * h;
-                S = (cc.A * G) * exp_neg_c(cc.negK * (h2 * h2));
+                S = (cc.A * G) * exp2_neg_tab_safe(K2 * (h2 * h2), T128);
             } else if (ct_c) { // coalescenceKernels/CoulaloglouTavlarides.C:69-90
                 const double sa = ra[i] + ra[j];
                 const double G = (sa * sa) * sqrt(rp[i] + rp[j]);
                 const double h = rcp_fast(ia[i] + ia[j]); // a b / (a + b)
                 const double h2 = h * h;
-                S = (cc.A * G) * exp_neg_c(cc.negK * (h2 * h2));
+                S = (cc.A * G) * exp2_neg_tab_safe(K2 * (h2 * h2), T128);
             } else if (COAL == PBE_COAL_CONSTANT) {
                 S = ks.coal_const;
             }
@@ -142,6 +145,9 @@ struct QmomParams {
 
 template <int N, int COAL, int BR>
 __global__ void __launch_bounds__(128) qmom_kernel(const __grid_constant__ QmomParams p) {
+    __shared__ double T128[128]; // 2^(j/128), exp2_neg_tab<7>
+    T128[threadIdx.x] = PBE_EXP2_TAB128[threadIdx.x];
+    __syncthreads();
     const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
     for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < p.ncells; c += nthreads) {
         double m[2 * N], x[N], w[N], S[2 * N];
@@ -149,7 +155,7 @@ __global__ void __launch_bounds__(128) qmom_kernel(const __grid_constant__ QmomP
         for (int k = 0; k < 2 * N; ++k) m[k] = __ldg(p.m_in + (size_t)k * p.stride + c);
         const double eps = __ldg(p.eps + c), rho = __ldg(p.rho + c), nu = __ldg(p.nu + c);
         wheeler_dev<N>(m, x, w);
-        qmom_cell_sources<N, COAL, BR>(p.ks, x, w, eps, rho, nu, S);
+        qmom_cell_sources<N, COAL, BR>(p.ks, x, w, eps, rho, nu, T128, S);
         if (p.do_step) {
 #pragma unroll
             for (int k = 0; k < 2 * N; ++k) {
