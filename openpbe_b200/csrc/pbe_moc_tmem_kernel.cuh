@@ -187,8 +187,9 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
 // p.negK_floor (MocParams) = -2^(29-LOGT) / max H: with it 2^LOGT y of exp2_neg_tab stays inside
 // an int32; the host only selects this kernel when every H_ij >= 2^(LOGT-19) max H, so a clamped
 // cell has every efficiency below 2^-1024 either way.
+// The narrow instantiation is the one used where three CTAs fit an SM: its registers are capped for that.
 template <int COAL, int BR, bool WIDE>
-__global__ void __launch_bounds__(MOCT_BLOCK, 2)
+__global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
     moc_tmem_kernel(const __grid_constant__ MocParams p, const __grid_constant__ MoctSched sc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int BLOCK = MOCT_BLOCK;
@@ -275,15 +276,21 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
         const bool live = cell < p.ncells;
         const int64_t cc = live ? cell : p.ncells - 1;
 
-        // stage this cell's class densities (coalesced: lane = cell); pull the next batch's
-        // lines into L2 meanwhile (one request per 32-B sector)
+        // stage this cell's class densities (coalesced: lane = cell) with asynchronous 8-byte
+        // global->shared copies (LDGSTS): all N are in flight at once, no register round trip;
+        // they are waited for just before the pair sweep, behind the accumulator zeroing and the
+        // per-cell coefficients.  The next batch's lines are pulled into L2 meanwhile (one
+        // request per 32-B sector).
         {
             const double *src = p.n_in + cc;
             const int64_t ncell = cell + (int64_t)gridDim.x * BLOCK;
             const bool pf = ((tid & 3) == 0) && (ncell < p.ncells);
-#pragma unroll 10
-            for (int i = 0; i < N; ++i) {
-                n_s[i * BLOCK + tid] = ldg_stream(src + (size_t)i * p.stride);
+            uint32_t dst = smem_u32(n_s + tid);
+#pragma unroll 4
+            for (int i = 0; i < N; ++i, dst += BLOCK * (uint32_t)sizeof(double)) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst),
+                             "l"(src + (size_t)i * p.stride)
+                             : "memory");
                 if (pf)
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(p.n_in + (size_t)i * p.stride + ncell));
             }
@@ -305,6 +312,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, 2)
             K2 = negK * 1.4426950408889634074;
         }
 
+        asm volatile("cp.async.wait_all;" ::: "memory"); // n_s column of this thread is complete
 #ifdef PBE_PHASE_TIMING
         const long long tp1 = clock64();
 #endif
