@@ -520,13 +520,24 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                 pN -= p.stride;
                 sum_d = fma_(cDV[ii], nn, sum_d);
                 sum_n += nn;
-                if (mom_mode == 1) {
-                    mloc[0] += nn;
-                    mloc[1] = fma_(cXI[ii], nn, mloc[1]);
-                } else if (mom_mode == 2) {
+                ni4[r] = nn; // reused: the updated density, for the moment sums below
+            }
+            // moment sums of the four classes behind ONE uniform branch (a branch per class
+            // would cut the group into basic blocks and serialise the classes)
+            if (mom_mode == 1) {
+#pragma unroll
+                for (int r = 3; r >= 0; --r) {
+                    const int ii = (full || (c4 + r < N)) ? c4 + r : N;
+                    mloc[0] += ni4[r];
+                    mloc[1] = fma_(cXI[ii], ni4[r], mloc[1]);
+                }
+            } else if (mom_mode == 2) {
+#pragma unroll
+                for (int r = 3; r >= 0; --r) {
                     // xi^k n for k = 0..7 as two chains (even / odd powers) of depth 3
+                    const int ii = (full || (c4 + r < N)) ? c4 + r : N;
                     const double x = cXI[ii], x2 = x * x;
-                    double pe = nn, po = nn * x;
+                    double pe = ni4[r], po = ni4[r] * x;
 #pragma unroll
                     for (int k = 0; k < MOC_MAX_MOMENTS; k += 2) {
                         mloc[k] += pe;
@@ -537,19 +548,23 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                 }
             }
         };
+        // the accumulators of the next group are fetched from tensor memory while this group is
+        // being worked on
+        Tm4 v, vn;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v.r[k] = vn.r[k] = 0u;
+        if (COAL != DCOAL_OFF) tmem_ld4(tacc + 2u * (uint32_t)c4top, v);
 #pragma unroll 1
         for (int c4 = c4top; c4 >= 0; c4 -= 4) {
-            Tm4 v;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v.r[k] = 0u;
             if (COAL != DCOAL_OFF) {
-                tmem_ld4(tacc + 2u * (uint32_t)c4, v);
                 tmem_wait_ld(v);
+                if (c4 >= 4) tmem_ld4(tacc + 2u * (uint32_t)(c4 - 4), vn);
             }
             if (c4 + 3 < N)
                 group_body(c4, v, true);
             else
                 group_body(c4, v, false);
+            v = vn;
         }
 #ifdef PBE_PHASE_TIMING
         if (tid == 0 && p.moments != nullptr) { // overwrites moments 5..7 with phase cycles
