@@ -109,6 +109,19 @@ __device__ __forceinline__ void tm_axpy4(Tm4 &v, double sgn, const double *add) 
     for (int k = 0; k < 4; ++k) tm_set(v, k, fma_(sgn, add[k], tm_get(v, k)));
 }
 
+// v[0..3] hold 16 consecutive accumulators (a window starting at class j0): window[OFF + w] +=
+// add[w] for w < NW, with every index a compile-time constant once unrolled
+template <int OFF, int NW>
+__device__ __forceinline__ void tm_window_add(Tm4 (&v)[4], const double *add) {
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        constexpr int dummy = 0;
+        (void)dummy;
+        const int idx = OFF + w;
+        tm_set(v[idx >> 2], idx & 3, tm_get(v[idx >> 2], idx & 3) + add[w]);
+    }
+}
+
 // launch-time schedule of the table ring: row blocks cut into sub-chunks of <= MOCT_SUB_TILES tiles
 struct MoctSched {
     int nsubs;                                   // sub-chunks per cell batch
@@ -324,11 +337,15 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                 // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets
                 // j0.. of the same tile, so the two read-modify-writes are serialised
                 const bool alias = (i0 + 1 < MOC_TJ);
-                // Row blocks from i0 = 2 TJ - 1 on walk the table two tiles at a time (a TI x 2TJ
-                // register tile: 32 independent pair chains, one tensor-memory round trip and
-                // one loop trip per 32 pairs); below that the 2TJ column targets and the 2TJ
-                // anti-diagonal targets of one step would overlap.
-                const bool wide = WIDE && (i0 + 1 >= 2 * MOC_TJ);
+                // The wide instantiation walks the table two tiles at a time (a TI x 2TJ register
+                // tile: 32 independent pair chains, one tensor-memory round trip and one loop trip
+                // per 32 pairs).  From i0 = 2 TJ - 1 on, the 2TJ column targets j0.. and the 2TJ
+                // anti-diagonal targets i0+j0+1.. are disjoint (four x8 loads at two places);
+                // for the first two row blocks (i0 = 0, TI) they overlap, so ONE 16-class window
+                // starting at j0 is loaded and both updates are applied to it in registers.
+                const bool wide = WIDE;
+                const int wmode = (i0 + 1 >= 2 * MOC_TJ) ? 0 : (i0 == 0 ? 1 : 2);
+                static_assert(!WIDE || (MOC_TI == 4 && MOC_TJ == 4), "window offsets below assume 4 x 4 tiles");
                 constexpr int NJ2 = 2 * MOC_TJ, NB2 = MOC_TI + 2 * MOC_TJ - 1;
                 double ni[MOC_TI], di[MOC_TI], bw[NB2];
 #pragma unroll
@@ -356,27 +373,36 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                             }
                             const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
                             const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
-                            Tm4 vd0, vd1, vb0, vb1;
+                            // four x8 groups: columns + anti-diagonals (wmode 0) or one window
+                            const uint32_t a2 = (wmode == 0) ? a_bw : a_dj + 16u;
+                            Tm4 v[4];
                             // the first table tile covers the latency of the previous step's
                             // stores, the second that of this step's loads
                             moct_tile<COAL, 0, MOC_TI, 0, NJ2>(tab, K2, T16, ni, nj, di, dj, bw);
                             tmem_wait_st();
-                            tmem_ld4(a_dj, vd0);
-                            tmem_ld4(a_dj + 8u, vd1);
-                            tmem_ld4(a_bw, vb0);
-                            tmem_ld4(a_bw + 8u, vb1);
+                            tmem_ld4(a_dj, v[0]);
+                            tmem_ld4(a_dj + 8u, v[1]);
+                            tmem_ld4(a2, v[2]);
+                            tmem_ld4(a2 + 8u, v[3]);
                             moct_tile<COAL, 0, MOC_TI, MOC_TJ, NJ2>(tab + MOC_TI * MOC_TJ, K2, T16, ni, nj,
                                                                     di, dj, bw);
-                            tmem_wait_ld(vd0, vd1);
-                            tmem_wait_ld(vb0, vb1);
-                            tm_axpy4(vd0, -1.0, dj); // death of class j
-                            tm_axpy4(vd1, -1.0, dj + MOC_TJ);
-                            tm_axpy4(vb0, 1.0, bw);  // birth of class i+j+1: 2TJ lowest anti-diagonals
-                            tm_axpy4(vb1, 1.0, bw + MOC_TJ);
-                            tmem_st4(a_dj, vd0);
-                            tmem_st4(a_dj + 8u, vd1);
-                            tmem_st4(a_bw, vb0);
-                            tmem_st4(a_bw + 8u, vb1);
+                            tmem_wait_ld(v[0], v[1]);
+                            tmem_wait_ld(v[2], v[3]);
+                            tm_axpy4(v[0], -1.0, dj); // death of class j
+                            tm_axpy4(v[1], -1.0, dj + MOC_TJ);
+                            // birth of class i+j+1: the 2TJ lowest anti-diagonals of the window
+                            if (wmode == 0) {
+                                tm_axpy4(v[2], 1.0, bw);
+                                tm_axpy4(v[3], 1.0, bw + MOC_TJ);
+                            } else if (wmode == 1) {
+                                tm_window_add<1, 2 * MOC_TJ>(v, bw); // i0 = 0: classes j0+1 ..
+                            } else {
+                                tm_window_add<MOC_TI + 1, 2 * MOC_TJ>(v, bw); // i0 = TI: classes j0+5 ..
+                            }
+                            tmem_st4(a_dj, v[0]);
+                            tmem_st4(a_dj + 8u, v[1]);
+                            tmem_st4(a2, v[2]);
+                            tmem_st4(a2 + 8u, v[3]);
 #pragma unroll
                             for (int w = 0; w < NB2; ++w) bw[w] = (w + NJ2 < NB2) ? bw[w + NJ2] : 0.0;
                         }
