@@ -109,14 +109,13 @@ __device__ __forceinline__ void tm_axpy4(Tm4 &v, double sgn, const double *add) 
     for (int k = 0; k < 4; ++k) tm_set(v, k, fma_(sgn, add[k], tm_get(v, k)));
 }
 
-// v[0..3] hold 16 consecutive accumulators (a window starting at class j0): window[OFF + w] +=
+// v[0..NV-1] hold 4 NV consecutive accumulators (a window starting at class j0): window[OFF + w] +=
 // add[w] for w < NW, with every index a compile-time constant once unrolled
-template <int OFF, int NW>
-__device__ __forceinline__ void tm_window_add(Tm4 (&v)[4], const double *add) {
+template <int OFF, int NW, int NV>
+__device__ __forceinline__ void tm_window_add(Tm4 (&v)[NV], const double *add) {
+    static_assert(OFF + NW <= 4 * NV, "window too small");
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
-        constexpr int dummy = 0;
-        (void)dummy;
         const int idx = OFF + w;
         tm_set(v[idx >> 2], idx & 3, tm_get(v[idx >> 2], idx & 3) + add[w]);
     }
@@ -334,9 +333,9 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
 #pragma unroll 1
             for (int blk = 0; blk < p.nblocks; ++blk) {
                 const int i0 = blk * MOC_TI;
-                // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets
-                // j0.. of the same tile, so the two read-modify-writes are serialised
+                // row block 0: the anti-diagonal targets i0+j0+1.. overlap the column targets j0..
                 const bool alias = (i0 + 1 < MOC_TJ);
+                static_assert(MOC_TI == MOC_TJ, "alias <=> i0 == 0 (window offset 1) needs TI == TJ");
                 // The wide instantiation walks the table two tiles at a time (a TI x 2TJ register
                 // tile: 32 independent pair chains, one tensor-memory round trip and one loop trip
                 // per 32 pairs).  From i0 = 2 TJ - 1 on, the 2TJ column targets j0.. and the 2TJ
@@ -395,9 +394,9 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                                 tm_axpy4(v[2], 1.0, bw);
                                 tm_axpy4(v[3], 1.0, bw + MOC_TJ);
                             } else if (wmode == 1) {
-                                tm_window_add<1, 2 * MOC_TJ>(v, bw); // i0 = 0: classes j0+1 ..
+                                tm_window_add<1, 2 * MOC_TJ, 4>(v, bw); // i0 = 0: classes j0+1 ..
                             } else {
-                                tm_window_add<MOC_TI + 1, 2 * MOC_TJ>(v, bw); // i0 = TI: classes j0+5 ..
+                                tm_window_add<MOC_TI + 1, 2 * MOC_TJ, 4>(v, bw); // i0 = TI: classes j0+5 ..
                             }
                             tmem_st4(a_dj, v[0]);
                             tmem_st4(a_dj + 8u, v[1]);
@@ -417,33 +416,25 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                         }
                         const uint32_t a_dj = tacc + 2u * (uint32_t)j0;
                         const uint32_t a_bw = tacc + 2u * (uint32_t)(i0 + j0 + 1);
-                        Tm4 vd, vb;
+                        // row block 0: the TJ anti-diagonal targets j0+1.. overlap the column
+                        // targets j0..: one 2TJ-class window takes both updates
+                        const uint32_t a1 = alias ? a_dj + 8u : a_bw;
+                        Tm4 v[2];
                         // first half of the tile covers the latency of the previous tile's
                         // stores, the second half that of this tile's loads
                         moct_tile<COAL, 0, MOC_TI / 2, 0, NJ2>(tab, K2, T16, ni, nj, di, dj, bw);
                         tmem_wait_st(); // the previous tile's stores have landed
-                        if (!alias) {
-                            tmem_ld4(a_dj, vd);
-                            tmem_ld4(a_bw, vb);
-                        }
+                        tmem_ld4(a_dj, v[0]);
+                        tmem_ld4(a1, v[1]);
                         moct_tile<COAL, MOC_TI / 2, MOC_TI, 0, NJ2>(tab, K2, T16, ni, nj, di, dj, bw);
-                        if (!alias) {
-                            tmem_wait_ld(vd, vb);
-                            tm_axpy4(vd, -1.0, dj); // death of class j
-                            tm_axpy4(vb, 1.0, bw);  // birth of class i+j+1: TJ lowest anti-diagonals
-                            tmem_st4(a_dj, vd);
-                            tmem_st4(a_bw, vb);
-                        } else {
-                            tmem_ld4(a_dj, vd);
-                            tmem_wait_ld(vd);
-                            tm_axpy4(vd, -1.0, dj);
-                            tmem_st4(a_dj, vd);
-                            tmem_wait_st();
-                            tmem_ld4(a_bw, vb);
-                            tmem_wait_ld(vb);
-                            tm_axpy4(vb, 1.0, bw);
-                            tmem_st4(a_bw, vb);
-                        }
+                        tmem_wait_ld(v[0], v[1]);
+                        tm_axpy4(v[0], -1.0, dj); // death of class j
+                        if (!alias)
+                            tm_axpy4(v[1], 1.0, bw); // birth of class i+j+1: TJ lowest anti-diagonals
+                        else
+                            tm_window_add<1, MOC_TJ, 2>(v, bw);
+                        tmem_st4(a_dj, v[0]);
+                        tmem_st4(a1, v[1]);
 #pragma unroll
                         for (int w = 0; w < NB2; ++w) bw[w] = (w + MOC_TJ < NB2) ? bw[w + MOC_TJ] : 0.0;
                     }
