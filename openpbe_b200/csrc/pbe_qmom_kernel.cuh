@@ -154,6 +154,17 @@ __global__ void __launch_bounds__(128) qmom_kernel(const __grid_constant__ QmomP
 #pragma unroll
         for (int k = 0; k < 2 * N; ++k) m[k] = __ldg(p.m_in + (size_t)k * p.stride + c);
         const double eps = __ldg(p.eps + c), rho = __ldg(p.rho + c), nu = __ldg(p.nu + c);
+        // pull the next grid-stride cell's lines into L2 meanwhile (one request per 32-B sector):
+        // the loads of the next trip then see L2, not HBM, latency
+        if ((threadIdx.x & 3) == 0 && c + nthreads < p.ncells) {
+            const int64_t cn = c + nthreads;
+#pragma unroll
+            for (int k = 0; k < 2 * N; ++k)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p.m_in + (size_t)k * p.stride + cn));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.eps + cn));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.rho + cn));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.nu + cn));
+        }
         wheeler_dev<N>(m, x, w);
         qmom_cell_sources<N, COAL, BR>(p.ks, x, w, eps, rho, nu, T128, S);
         if (p.do_step) {
