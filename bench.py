@@ -521,6 +521,23 @@ def run_b200(args):
                              "frac": qgbs / hbm_peak, "bytes_per_cell": qbytes, "traffic": load_traffic("qmom_kernel", qc),
                              "algorithmic_bytes": qc * qbytes,
                              "fp64_tflops": qtf, "fp64_frac": qtf / fp64_tf}}
+        if not args.no_e2e:
+            # the same metric through the host-buffer entry the adapter's QMOM::correct() calls
+            # (pinned host m, eps, rho, nu -> S), copies inside the timed region
+            mp = mh.pin_memory()
+            sp = [t.pin_memory() for t in fq_small]
+            Sh = torch.empty((2 * wq.N, qc), dtype=torch.float64, pin_memory=True)
+            q.source_host(mp, *sp, out=Sh)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                q.source_host(mp, *sp, out=Sh)
+            torch.cuda.synchronize()
+            tq = allmax((time.perf_counter() - t0) / 3)
+            qmom["e2e"] = {"value": world * qc / tq, "unit": "cell-updates/s", "ms_per_step": tq * 1e3,
+                           "h2d_bytes_per_step": (2 * wq.N + 3) * qc * 8, "d2h_bytes_per_step": 2 * wq.N * qc * 8,
+                           "call": "pbe_qmom_source_host (pinned host m,eps,rho,nu -> S), synchronous"}
+            del mp, sp, Sh
         del m0, mq, Sq, flush
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) -----------------------------
