@@ -59,7 +59,7 @@ UNIT = "cell-class-updates/s"
 #     instructions x 2 / DFMA-peak is the pipe utilisation (`roofline.fp64_pipe_frac`).
 FP64_INSTR_PER_PAIR_CT = 14.3   # 13.25 per table slot x 2704 slots / 2500 valid pairs at N = 100 (8 % zero padding)
 FP64_INSTR_PER_PAIR_TAB = 4.0
-FP64_INSTR_PER_CLASS_CT = 42.3  # ncu r01w: 39 975 FP64 warp instructions per cell in total at N = 100
+FP64_INSTR_PER_CLASS_CT = 42.3  # ncu r01w (arithmetic unchanged since): 39 975 FP64 warp instructions per cell in total at N = 100
 FP64_INSTR_PER_CLASS_TAB = 30.0
 FLOPS_QMOM3_CT = 1300.0
 FLOPS_QMOM3_CONST = 600.0
