@@ -163,6 +163,47 @@ int pbe_qmom_source_host(pbe_qmom *q, int64_t ncells, int64_t stride, const doub
                          double *S_host);
 
 /* ======================================================================================= */
+/* Transport of the class / moment fields (first slice) --       */
+/* replaces the explicit update of MOC::solveWithMULES, src/PBESystem/MOC.C:198-272, and     */
+/* QMOM::solveWithMULES, src/PBESystem/QMOM.C:131-197, for the divergence scheme             */
+/* `Gauss upwind` (the MULES-limited high-order correction is then identically zero):        */
+/*   psi_k <- (psi_k rDeltaT + S_k - (1/V) sum_f phi_f psi_k,f) / rDeltaT                     */
+/* with OpenFOAM's upwind face value and MULES::explicitSolve (rho = 1, Sp = 0).             */
+/* ======================================================================================= */
+typedef struct pbe_mesh pbe_mesh;
+/* OpenFOAM face addressing (fvMesh::owner() / neighbour(), boundary patches' faceCells()):
+ * internal faces 0 .. n_internal_faces-1, then the boundary faces of all patches in patch
+ * order, each with its owner cell.  HOST arrays, copied; vcell = mesh.V() (MOC.C:276).
+ * Builds the device-side cell -> faces table once per mesh. */
+int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, const int32_t *owner,
+                    const int32_t *neighbour, int64_t n_boundary_faces,
+                    const int32_t *boundary_owner, const double *vcell, pbe_mesh **out);
+int pbe_mesh_destroy(pbe_mesh *mesh);
+int pbe_mesh_info(pbe_mesh *mesh, int64_t *ncells, int64_t *n_internal_faces,
+                  int64_t *n_boundary_faces, int *max_faces_per_cell);
+/* How the device tables split the cells: "regular" cells (no boundary face, exactly
+ * *faces_per_regular_cell internal faces -- the mesh's most common count among 4, 5, 6) go through
+ * the register-resident kernel, all others through the general one. */
+int pbe_mesh_regular_cells(pbe_mesh *mesh, int *faces_per_regular_cell, int64_t *n_regular);
+
+/* fvSchemes divSchemes entry "div(phi,n.*)" -> enum; anything but upwind returns
+ * PBE_E_UNKNOWN_TYPE with the valid names listed (the reference's FatalError convention). */
+enum { PBE_DIV_UPWIND = 0 };
+int pbe_div_scheme_type(const char *scheme_name, int *out);
+
+/* One explicit transport + source update of nfields fields psi [nfields][stride] (DEVICE).
+ * phi: DEVICE [n_internal_faces + n_boundary_faces] volumetric face flux of the phase
+ * (phase_.phi(), MOC.C:200), positive from owner to neighbour / out of the domain.
+ * psi_b: DEVICE [nfields][stride_b] boundary-face values (Nk.boundaryField()), or NULL for
+ * zero-gradient on every boundary face.  S: DEVICE [nfields][stride] explicit source or NULL.
+ * psi_out must not alias psi.  Per-cell sums run in ascending face order, as
+ * fvc::surfaceIntegrate's loops do. */
+int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stride,
+                           const double *psi, const double *phi, const double *psi_b,
+                           int64_t stride_b, const double *S, double dt, double *psi_out,
+                           void *cuda_stream);
+
+/* ======================================================================================= */
 /* Scalar kernel functors evaluated ON THE DEVICE (batched) -- the reference's Foam-free     */
 /* *Impl::S surface (coalescenceKernels/CoulaloglouTavlarides.H:44-63, breakupKernels/       */
 /* CoulaloglouTavlarides.H:46-60; exported to Python by bindings/kernels.cpp:9-40).          */

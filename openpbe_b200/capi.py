@@ -19,6 +19,7 @@ BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
 DAUGHTER_UNIFORM_BINARY = 0
 QMOM_MAX_ORDER = 4
 MOC_KERNEL_SMEM, MOC_KERNEL_TMEM = 1, 2
+DIV_UPWIND = 0
 
 _dp = C.POINTER(C.c_double)
 _vp = C.c_void_p
@@ -89,6 +90,14 @@ PROTOTYPES = {
     "pbe_qmom_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp, _vp]),
     "pbe_wheeler_batch": (C.c_int, [_vp, C.c_int, _i64, _i64, _vp, _vp, _vp, _vp]),
     "pbe_qmom_source_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "pbe_mesh_create": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp, C.POINTER(_vp)]),
+    "pbe_mesh_destroy": (C.c_int, [_vp]),
+    "pbe_mesh_info": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64),
+                                C.POINTER(C.c_int)]),
+    "pbe_mesh_regular_cells": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(_i64)]),
+    "pbe_div_scheme_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
+    "pbe_transport_explicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
+                                         C.c_double, _vp, _vp]),
     "pbe_eval_coalescence": (C.c_int, [_vp, C.POINTER(KernelSpec), _i64, _vp, _vp, _vp, _vp, _vp,
                                        _vp]),
     "pbe_eval_breakup": (C.c_int, [_vp, C.POINTER(KernelSpec), _i64, _vp, _vp, _vp, _vp]),

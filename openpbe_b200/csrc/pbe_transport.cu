@@ -1,0 +1,395 @@
+// pbe_transport.cu -- explicit transport of class / moment fields on a face-addressed mesh
+// (first slice).
+//
+// What it replaces: the update at the end of MOC::solveWithMULES (src/PBESystem/MOC.C:198-272)
+// and QMOM::solveWithMULES (src/PBESystem/QMOM.C:131-197),
+//     phiNk = lambda (phiHO - phiUpwind) + upwind(mesh, phi).flux(Nk);
+//     MULES::explicitSolve(geometricOneField(), Nk, phiNk, zeroField(), S[k]);
+// for the divergence scheme `Gauss upwind`, where the limited correction is identically zero.
+// The vanLeer / MULES-limited correction is the next slice.
+//
+// Device layout.  pbe_mesh_create turns OpenFOAM's face addressing (owner / neighbour lists)
+// into cell-centred tables whose entries are in ascending face order per cell -- the order
+// fvc::surfaceIntegrate's face loops add them in -- so per-cell sums are bit-identical to a face
+// loop.  Cells are split in two sets:
+//   * regular cells: no boundary face and exactly F internal faces (F = the mesh's most common
+//     count: 6 for hexahedra, 4 for tetrahedra, 5 for prisms).  ELL table [F][ncells], cell
+//     fastest; one thread per cell keeps its F (neighbour, signed flux, lambda) triples in
+//     registers and sweeps a chunk of fields with F + 2 loads, 4 F + 9 FP64 instructions and no
+//     branch per field.
+//   * everything else (boundary cells, other face counts): a compact CSR list, one thread per
+//     listed cell, any number of faces, patch values from psi_b.
+// HBM-bound: 24 B per cell-field (psi and S in, psi out); neighbour gathers are L1 / L2 hits.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "pbe_common.h"
+
+#ifndef PBE_TR_CTAS
+#define PBE_TR_CTAS 4
+#endif
+#ifndef PBE_TR_PD
+#define PBE_TR_PD 4 // prefetch distance (fields) of the two streamed rows
+#endif
+
+struct pbe_mesh {
+    pbe_ctx *ctx = nullptr;
+    int64_t ncells = 0, nint = 0, nbnd = 0, nirr = 0;
+    int maxf = 0; // most faces on any cell (info)
+    int F = 0;    // face count of the regular cells (0: none)
+    int32_t *d_other = nullptr; // [F][ncells]: neighbour cell; row 0 holds -1 for irregular cells
+    int32_t *d_face = nullptr;  // [F][ncells]: face index f (this cell owns it) or ~f (it is the neighbour)
+    double *d_vcell = nullptr;  // [ncells]
+    // irregular cells, CSR: entries of cell irr_cell[i] are irr_ptr[i] .. irr_ptr[i+1]-1
+    int32_t *d_irr_cell = nullptr, *d_irr_ptr = nullptr;
+    int32_t *d_irr_other = nullptr; // >= 0 neighbour cell; -(b + 2) boundary face b
+    int32_t *d_irr_face = nullptr;  // as d_face (boundary faces: n_internal + b)
+};
+
+namespace pbe {
+
+struct TransportParams {
+    int64_t ncells, stride, stride_b, nint, nirr;
+    int nfields, chunk;
+    const int32_t *other, *face, *irr_cell, *irr_ptr, *irr_other, *irr_face;
+    const double *vcell, *psi, *phi, *psi_b, *S;
+    double *out;
+    double rdt;  // 1/dt, as MULES::explicitSolve forms it
+    double rrdt; // RN(1/rdt): reciprocal for div_by
+};
+
+// Correctly rounded a / b from y = RN(1/b) (Markstein): q0 = RN(a y), r = a - b q0 (exact in an
+// FMA), q = RN(q0 + r y).  Outside a comfortable exponent range (results that could be subnormal,
+// overflow, non-finite operands) the IEEE division is used, so the quotient is bit-identical to
+// `a / b` everywhere; three FP64 instructions instead of the ~30 of the division's full sequence.
+__device__ __forceinline__ double div_by(double a, double b, double y) {
+    const double q0 = __dmul_rn(a, y);
+    const int hi = __double2hiint(q0) & 0x7ff00000;
+    if (hi < 0x10000000 || hi > 0x6ff00000) return __ddiv_rn(a, b); // |q0| outside [2^-767, 2^768): rare
+    return __fma_rn(__fma_rn(-q0, b, a), y, q0);
+}
+
+// One face seen from one of its two cells.  The face loop adds the flux on the owner side and
+// subtracts it on the neighbour side; -(phi f) == (-phi) f exactly, so the signed flux
+// phs = +-phi is stored and the sum is a plain addition.  The face value
+// lambda (psi_P - psi_N) + psi_N (surfaceInterpolationScheme::interpolate, lambda = pos(phi)) is
+// fma(lam, mine - theirs, N) with lam = +-lambda: the product is exact (lambda is 0 or 1), hence
+// the FMA rounds once, exactly like the reference's multiply-then-add.
+struct Side {
+    double phs; // own side ? phi : -phi
+    int lam_hi; // high word of lam = own side ? pos(phi) : -pos(phi); sign bit = "neighbour side"
+};
+
+__device__ __forceinline__ Side make_side(int32_t face, const double *phi) {
+    const bool own = face >= 0;
+    const double ph = __ldg(phi + (own ? face : ~face));
+    const double lambda = ph >= 0.0 ? 1.0 : 0.0;
+    return Side{own ? ph : -ph, __double2hiint(own ? lambda : -lambda)};
+}
+
+__device__ __forceinline__ double add_internal(double acc, const Side &t, double mine, double theirs) {
+    const double N = (t.lam_hi >= 0) ? theirs : mine;
+    const double fv = __fma_rn(__hiloint2double(t.lam_hi, 0), __dsub_rn(mine, theirs), N);
+    return __dadd_rn(acc, __dmul_rn(t.phs, fv));
+}
+
+__device__ __forceinline__ double updated(const TransportParams &p, double mine, double Su, double acc,
+                                          double V, double rV) {
+    const double div = div_by(acc, V, rV);
+    const double num = __dsub_rn(__dadd_rn(__dmul_rn(mine, p.rdt), Su), div);
+    return div_by(num, p.rdt, p.rrdt);
+}
+
+template <int F>
+__global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(TransportParams p) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x; // 32-bit labels (pbe_mesh_create checks)
+    if (c >= p.ncells) return;
+    int oth[F];
+    oth[0] = __ldg(p.other + c);
+    if (oth[0] < 0) return; // irregular cell: transport_upwind_irregular_kernel
+    Side sd[F];
+#pragma unroll
+    for (int s = 0; s < F; ++s) {
+        if (s > 0) oth[s] = __ldg(p.other + (size_t)s * p.ncells + c);
+        sd[s] = make_side(__ldg(p.face + (size_t)s * p.ncells + c), p.phi);
+    }
+    const double V = __ldg(p.vcell + c);
+    const double rV = __ddiv_rn(1.0, V);
+    const int k0 = blockIdx.y * p.chunk;
+    const int k1 = min(p.nfields, k0 + p.chunk);
+    const double *row = p.psi + (size_t)k0 * p.stride;
+    const double *srow = (p.S != nullptr) ? p.S + (size_t)k0 * p.stride : nullptr;
+    double *orow = p.out + (size_t)k0 * p.stride;
+    const bool pf_lane = (threadIdx.x & 3) == 0;
+#pragma unroll 2
+    for (int k = k0; k < k1; ++k, row += p.stride, orow += p.stride) {
+#if PBE_TR_PD > 0
+        // the two streamed rows of a field a few iterations ahead are pulled into L2 meanwhile
+        // (one request per 32-B sector); the neighbour gathers are L1 / L2 hits
+        if (pf_lane && k + PBE_TR_PD < k1) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(row + (size_t)PBE_TR_PD * p.stride + c));
+            if (srow != nullptr)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(srow + (size_t)PBE_TR_PD * p.stride + c));
+        }
+#endif
+        const double mine = __ldg(row + c);
+        double th[F];
+#pragma unroll
+        for (int s = 0; s < F; ++s) th[s] = __ldg(row + oth[s]);
+        double Su = 0.0;
+        if (srow != nullptr) {
+            Su = __ldg(srow + c);
+            srow += p.stride;
+        }
+        double acc = 0.0;
+#pragma unroll
+        for (int s = 0; s < F; ++s) acc = add_internal(acc, sd[s], mine, th[s]);
+        __stcs(orow + c, updated(p, mine, Su, acc, V, rV));
+    }
+}
+
+// boundary cells and cells with another face count: one thread per listed cell
+__global__ void __launch_bounds__(128) transport_upwind_irregular_kernel(TransportParams p) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.nirr) return;
+    const int c = __ldg(p.irr_cell + i);
+    const int e0 = __ldg(p.irr_ptr + i), e1 = __ldg(p.irr_ptr + i + 1);
+    const double V = __ldg(p.vcell + c);
+    const double rV = __ddiv_rn(1.0, V);
+    const int k0 = blockIdx.y * p.chunk;
+    const int k1 = min(p.nfields, k0 + p.chunk);
+    for (int k = k0; k < k1; ++k) {
+        const double *row = p.psi + (size_t)k * p.stride;
+        const double mine = __ldg(row + c);
+        double acc = 0.0;
+        for (int e = e0; e < e1; ++e) {
+            const int oth = __ldg(p.irr_other + e);
+            const int face = __ldg(p.irr_face + e);
+            if (oth >= 0) {
+                acc = add_internal(acc, make_side(face, p.phi), mine, __ldg(row + oth));
+            } else { // boundary face: patch value (NULL psi_b = zero-gradient = the cell's own value)
+                const double pv = (p.psi_b != nullptr) ? __ldg(p.psi_b + (size_t)k * p.stride_b - (oth + 2)) : mine;
+                acc = __dadd_rn(acc, __dmul_rn(__ldg(p.phi + face), pv));
+            }
+        }
+        const double Su = (p.S != nullptr) ? __ldg(p.S + (size_t)k * p.stride + c) : 0.0;
+        p.out[(size_t)k * p.stride + c] = updated(p, mine, Su, acc, V, rV);
+    }
+}
+
+} // namespace pbe
+
+using namespace pbe;
+
+extern "C" {
+
+int pbe_div_scheme_type(const char *name, int *out) {
+    PBE_REQUIRE(name != nullptr && out != nullptr, PBE_E_INVALID, "pbe_div_scheme_type: NULL argument");
+    if (!strcmp(name, "upwind") || !strcmp(name, "Gauss upwind")) {
+        *out = PBE_DIV_UPWIND;
+        return PBE_OK;
+    }
+    set_error("Unknown or not yet supported divergence scheme \"%s\" for the device transport\n\n"
+              "Valid schemes are :\n(\nupwind\n)\n"
+              "(limited schemes such as vanLeer with the MULES correction are the next slice of "
+              "SURVEY.md row f2)",
+              name);
+    return PBE_E_UNKNOWN_TYPE;
+}
+
+int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, const int32_t *owner,
+                    const int32_t *neighbour, int64_t n_boundary_faces,
+                    const int32_t *boundary_owner, const double *vcell, pbe_mesh **out) {
+    PBE_REQUIRE(ctx != nullptr && out != nullptr, PBE_E_INVALID, "pbe_mesh_create: NULL argument");
+    *out = nullptr;
+    PBE_REQUIRE(ncells >= 1 && n_internal_faces >= 0 && n_boundary_faces >= 0, PBE_E_INVALID,
+                "pbe_mesh_create: bad sizes (ncells %lld, internal faces %lld, boundary faces %lld)",
+                (long long)ncells, (long long)n_internal_faces, (long long)n_boundary_faces);
+    PBE_REQUIRE(ncells < INT32_MAX - 256 && 2 * n_internal_faces + n_boundary_faces < INT32_MAX - 2,
+                PBE_E_UNSUPPORTED, "pbe_mesh_create: 32-bit labels (WM_LABEL_SIZE=32) exceeded");
+    PBE_REQUIRE(vcell != nullptr && (n_internal_faces == 0 || (owner && neighbour)) &&
+                    (n_boundary_faces == 0 || boundary_owner),
+                PBE_E_INVALID, "pbe_mesh_create: NULL array");
+    std::vector<int32_t> cnt((size_t)ncells, 0), bcnt((size_t)ncells, 0);
+    for (int64_t f = 0; f < n_internal_faces; ++f) {
+        const int32_t o = owner[f], n = neighbour[f];
+        PBE_REQUIRE(o >= 0 && o < ncells && n >= 0 && n < ncells && o != n, PBE_E_INVALID,
+                    "pbe_mesh_create: internal face %lld has owner %d, neighbour %d (ncells %lld)",
+                    (long long)f, o, n, (long long)ncells);
+        cnt[o]++;
+        cnt[n]++;
+    }
+    for (int64_t b = 0; b < n_boundary_faces; ++b) {
+        const int32_t o = boundary_owner[b];
+        PBE_REQUIRE(o >= 0 && o < ncells, PBE_E_INVALID,
+                    "pbe_mesh_create: boundary face %lld has owner %d (ncells %lld)", (long long)b, o,
+                    (long long)ncells);
+        bcnt[o]++;
+    }
+    // F: the most common face count among cells without boundary faces, if a kernel exists for it
+    int maxf = 0;
+    int64_t hist[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int64_t c = 0; c < ncells; ++c) {
+        maxf = std::max(maxf, (int)(cnt[c] + bcnt[c]));
+        if (bcnt[c] == 0 && cnt[c] >= 4 && cnt[c] <= 6) hist[cnt[c]]++;
+    }
+    int F = 0;
+    for (int f = 4; f <= 6; ++f)
+        if (hist[f] > 0 && (F == 0 || hist[f] > hist[F])) F = f;
+    auto regular = [&](int64_t c) { return F > 0 && bcnt[c] == 0 && cnt[c] == F; };
+    // irregular cells -> CSR
+    std::vector<int32_t> irr_cell, irr_ptr(1, 0), slot_of((size_t)ncells, -1);
+    for (int64_t c = 0; c < ncells; ++c)
+        if (!regular(c)) {
+            slot_of[c] = (int32_t)irr_cell.size();
+            irr_cell.push_back((int32_t)c);
+            irr_ptr.push_back(irr_ptr.back() + cnt[c] + bcnt[c]);
+        }
+    const int64_t nirr = (int64_t)irr_cell.size();
+    std::vector<int32_t> irr_other((size_t)irr_ptr.back()), irr_face((size_t)irr_ptr.back());
+    const int Fa = std::max(F, 1);
+    std::vector<int32_t> other((size_t)Fa * ncells, -1), face((size_t)Fa * ncells, 0), fill((size_t)ncells, 0);
+    // ascending face order per cell = the order of fvc::surfaceIntegrate's face loops
+    auto put = [&](int32_t c, int32_t oth, int32_t fc) {
+        const int32_t k = fill[c]++;
+        if (slot_of[c] < 0) {
+            other[(size_t)k * ncells + c] = oth;
+            face[(size_t)k * ncells + c] = fc;
+        } else {
+            irr_other[(size_t)irr_ptr[slot_of[c]] + k] = oth;
+            irr_face[(size_t)irr_ptr[slot_of[c]] + k] = fc;
+        }
+    };
+    for (int64_t f = 0; f < n_internal_faces; ++f) {
+        put(owner[f], neighbour[f], (int32_t)f);
+        put(neighbour[f], owner[f], ~(int32_t)f);
+    }
+    for (int64_t b = 0; b < n_boundary_faces; ++b)
+        put(boundary_owner[b], -(int32_t)b - 2, (int32_t)(n_internal_faces + b));
+
+    pbe_mesh *m = new (std::nothrow) pbe_mesh;
+    PBE_REQUIRE(m != nullptr, PBE_E_NOMEM, "pbe_mesh_create: out of host memory");
+    m->ctx = ctx;
+    m->ncells = ncells;
+    m->nint = n_internal_faces;
+    m->nbnd = n_boundary_faces;
+    m->nirr = nirr;
+    m->maxf = maxf;
+    m->F = F;
+    DeviceGuard g(ctx->device);
+    cudaError_t e = cudaSuccess;
+    auto upload = [&](auto **dst, const auto &v) {
+        if (e != cudaSuccess) return;
+        const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(v[0]);
+        e = cudaMalloc((void **)dst, bytes);
+        if (e == cudaSuccess && !v.empty()) e = cudaMemcpy(*dst, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
+    };
+    upload(&m->d_other, other);
+    upload(&m->d_face, face);
+    upload(&m->d_irr_cell, irr_cell);
+    upload(&m->d_irr_ptr, irr_ptr);
+    upload(&m->d_irr_other, irr_other);
+    upload(&m->d_irr_face, irr_face);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&m->d_vcell, (size_t)ncells * sizeof(double));
+    if (e == cudaSuccess)
+        e = cudaMemcpy(m->d_vcell, vcell, (size_t)ncells * sizeof(double), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        pbe_mesh_destroy(m);
+        return cuda_fail(e, "pbe_mesh_create: device tables", __FILE__, __LINE__);
+    }
+    *out = m;
+    return PBE_OK;
+}
+
+int pbe_mesh_destroy(pbe_mesh *m) {
+    if (m == nullptr) return PBE_OK;
+    DeviceGuard g(m->ctx->device);
+    cudaFree(m->d_other);
+    cudaFree(m->d_face);
+    cudaFree(m->d_vcell);
+    cudaFree(m->d_irr_cell);
+    cudaFree(m->d_irr_ptr);
+    cudaFree(m->d_irr_other);
+    cudaFree(m->d_irr_face);
+    delete m;
+    return PBE_OK;
+}
+
+int pbe_mesh_info(pbe_mesh *m, int64_t *ncells, int64_t *n_internal_faces,
+                  int64_t *n_boundary_faces, int *max_faces_per_cell) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_mesh_info: NULL mesh");
+    if (ncells) *ncells = m->ncells;
+    if (n_internal_faces) *n_internal_faces = m->nint;
+    if (n_boundary_faces) *n_boundary_faces = m->nbnd;
+    if (max_faces_per_cell) *max_faces_per_cell = m->maxf;
+    return PBE_OK;
+}
+
+int pbe_mesh_regular_cells(pbe_mesh *m, int *faces_per_regular_cell, int64_t *n_regular) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_mesh_regular_cells: NULL mesh");
+    if (faces_per_regular_cell) *faces_per_regular_cell = m->F;
+    if (n_regular) *n_regular = m->ncells - m->nirr;
+    return PBE_OK;
+}
+
+int pbe_transport_explicit(pbe_mesh *m, int scheme, int nfields, int64_t stride, const double *psi,
+                           const double *phi, const double *psi_b, int64_t stride_b,
+                           const double *S, double dt, double *psi_out, void *cuda_stream) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_transport_explicit: NULL mesh");
+    PBE_REQUIRE(scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
+                "pbe_transport_explicit: scheme %d is not available on the device (valid: "
+                "PBE_DIV_UPWIND)", scheme);
+    PBE_REQUIRE(nfields >= 0 && stride >= m->ncells, PBE_E_INVALID,
+                "pbe_transport_explicit: bad nfields/stride (%d, %lld; mesh has %lld cells)", nfields,
+                (long long)stride, (long long)m->ncells);
+    PBE_REQUIRE(dt > 0.0, PBE_E_INVALID, "pbe_transport_explicit: dt must be positive");
+    if (nfields == 0) return PBE_OK;
+    PBE_REQUIRE(psi && psi_out && (phi || m->nint + m->nbnd == 0), PBE_E_INVALID,
+                "pbe_transport_explicit: NULL pointer");
+    PBE_REQUIRE(psi != psi_out, PBE_E_INVALID,
+                "pbe_transport_explicit: psi_out must not alias psi (neighbours read old values)");
+    PBE_REQUIRE(psi_b == nullptr || stride_b >= m->nbnd, PBE_E_INVALID,
+                "pbe_transport_explicit: stride_b < boundary faces");
+    pbe_ctx *ctx = m->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    TransportParams p{m->ncells, stride, stride_b, m->nint, m->nirr, nfields, 1,
+                      m->d_other, m->d_face, m->d_irr_cell, m->d_irr_ptr, m->d_irr_other, m->d_irr_face,
+                      m->d_vcell, psi, phi, psi_b, S, psi_out, 1.0 / dt, 1.0 / (1.0 / dt)};
+    // fields per CTA (grid.y = field chunks): few enough that the rows a wave of CTAs gathers
+    // neighbours from stay in L2, many enough to amortise the per-cell face data; small meshes
+    // get more chunks so that every SM has work
+    auto chunk_for = [&](int64_t blocks, int start) {
+        int chunk = std::min(start, nfields);
+        while (chunk > 1 && blocks * ((nfields + chunk - 1) / chunk) < (int64_t)ctx->sm_count * 8)
+            chunk = (chunk + 1) / 2;
+        return chunk;
+    };
+    if (m->F > 0 && m->nirr < m->ncells) {
+        int start = 25;
+        if (const char *e = getenv("PBE_TRANSPORT_CHUNK")) start = std::max(1, atoi(e));
+        const int64_t blocks = (m->ncells + 255) / 256;
+        p.chunk = chunk_for(blocks, start);
+        dim3 grid((unsigned)blocks, (unsigned)((nfields + p.chunk - 1) / p.chunk));
+        switch (m->F) {
+        case 4: transport_upwind_kernel<4><<<grid, 256, 0, st>>>(p); break;
+        case 5: transport_upwind_kernel<5><<<grid, 256, 0, st>>>(p); break;
+        default: transport_upwind_kernel<6><<<grid, 256, 0, st>>>(p); break;
+        }
+        PBE_CUDA(cudaGetLastError());
+        ctx->launches++;
+    }
+    if (m->nirr > 0) {
+        const int64_t blocks = (m->nirr + 127) / 128;
+        p.chunk = chunk_for(blocks, 10);
+        dim3 grid((unsigned)blocks, (unsigned)((nfields + p.chunk - 1) / p.chunk));
+        transport_upwind_irregular_kernel<<<grid, 128, 0, st>>>(p);
+        PBE_CUDA(cudaGetLastError());
+        ctx->launches++;
+    }
+    return PBE_OK;
+}
+
+} // extern "C"

@@ -318,3 +318,61 @@ class QMOM:
             self._h, m_.shape[1], m_.stride(0) if m_.shape[1] else 0, _ptr(m_), _ptr(eps_), _ptr(rho_),
             _ptr(nu_), _ptr(S)))
         return S
+
+
+def div_scheme(name: str) -> int:
+    """fvSchemes `div(phi,n.*)` entry -> PBE_DIV_*; unknown / unsupported names raise PbeError."""
+    out = C.c_int()
+    capi.check(capi.lib().pbe_div_scheme_type(name.encode(), C.byref(out)))
+    return out.value
+
+
+class Mesh:
+    """pbe_mesh: OpenFOAM face addressing (owner / neighbour / boundary faceCells, V) on the device,
+    and the explicit transport + source update of MOC::solveWithMULES (MOC.C:198-272) /
+    QMOM::solveWithMULES (QMOM.C:131-197) for `Gauss upwind`."""
+
+    def __init__(self, ctx: Context, owner, neighbour, boundary_owner, vcell):
+        self.ctx = ctx
+        own = np.ascontiguousarray(owner, dtype=np.int32)
+        nei = np.ascontiguousarray(neighbour, dtype=np.int32)
+        bown = np.ascontiguousarray(boundary_owner, dtype=np.int32)
+        V = np.ascontiguousarray(vcell, dtype=np.float64)
+        assert own.shape == nei.shape and own.ndim == 1 and bown.ndim == 1 and V.ndim == 1
+        self.ncells, self.n_internal, self.n_boundary = V.size, own.size, bown.size
+        self._h = C.c_void_p()
+        capi.check(capi.lib().pbe_mesh_create(
+            ctx.handle, V.size, own.size, own.ctypes.data, nei.ctypes.data, bown.size,
+            bown.ctypes.data, V.ctypes.data, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_mesh_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        a, b, c, d = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
+        capi.check(capi.lib().pbe_mesh_info(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        F, nreg = C.c_int(), C.c_int64()
+        capi.check(capi.lib().pbe_mesh_regular_cells(self._h, C.byref(F), C.byref(nreg)))
+        return {"ncells": a.value, "internal_faces": b.value, "boundary_faces": c.value,
+                "max_faces_per_cell": d.value, "faces_per_regular_cell": F.value,
+                "regular_cells": nreg.value}
+
+    def transport_explicit(self, psi, phi, dt, *, psi_b=None, S=None, out=None, scheme="upwind"):
+        """psi [K][ncells] -> (psi rDeltaT + S - div(phi psi_upwind)) / rDeltaT, new tensor or `out`."""
+        assert psi.dim() == 2
+        K, ncells = psi.shape
+        out = torch.empty_like(psi) if out is None else out
+        capi.check(capi.lib().pbe_transport_explicit(
+            self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), K,
+            psi.stride(0) if ncells else 0, _ptr(psi), _ptr(phi), _ptr(psi_b),
+            0 if psi_b is None else psi_b.stride(0), _ptr(S), float(dt), _ptr(out),
+            _stream_ptr(psi.device)))
+        return out

@@ -154,3 +154,31 @@ def qmom_fields(w: Workload, seed: int = SEED, offset: int = 0, ncells: int | No
     f["nodes"] = nodes
     f["weights"] = weights
     return f
+
+
+def block_mesh(nx: int, ny: int, nz: int, lengths=(1.0, 1.0, 1.0), velocity=(1.0, 0.0, 0.0)):
+    """A blockMesh-style hex block in OpenFOAM face addressing: internal faces ordered by owner,
+    then neighbour (upper-triangular order), boundary faces patch by patch (x-, x+, y-, y+, z-,
+    z+).  Returns owner, neighbour, boundary_owner, vcell, phi (uniform velocity dotted with the
+    face area vectors; boundary values outward-positive), and the patch start offsets."""
+    dx, dy, dz = lengths[0] / nx, lengths[1] / ny, lengths[2] / nz
+    idx = np.arange(nx * ny * nz, dtype=np.int64).reshape(nz, ny, nx)
+    u, v, w = velocity
+    own, nei, ph = [], [], []
+    for sl_o, sl_n, flux in (((slice(None), slice(None), slice(0, nx - 1)), (slice(None), slice(None), slice(1, nx)), u * dy * dz),
+                             ((slice(None), slice(0, ny - 1), slice(None)), (slice(None), slice(1, ny), slice(None)), v * dx * dz),
+                             ((slice(0, nz - 1), slice(None), slice(None)), (slice(1, nz), slice(None), slice(None)), w * dx * dy)):
+        o, n = idx[sl_o].ravel(), idx[sl_n].ravel()
+        own.append(o); nei.append(n); ph.append(np.full(o.size, flux))
+    own, nei, ph = np.concatenate(own), np.concatenate(nei), np.concatenate(ph)
+    order = np.lexsort((nei, own))
+    own, nei, ph = own[order], nei[order], ph[order]
+    bown, bph, starts = [], [], [0]
+    for cells, flux in ((idx[:, :, 0], -u * dy * dz), (idx[:, :, -1], u * dy * dz),
+                        (idx[:, 0, :], -v * dx * dz), (idx[:, -1, :], v * dx * dz),
+                        (idx[0, :, :], -w * dx * dy), (idx[-1, :, :], w * dx * dy)):
+        bown.append(cells.ravel()); bph.append(np.full(cells.size, flux)); starts.append(starts[-1] + cells.size)
+    bown, bph = np.concatenate(bown), np.concatenate(bph)
+    return {"owner": own.astype(np.int32), "neighbour": nei.astype(np.int32),
+            "boundary_owner": bown.astype(np.int32), "vcell": np.full(nx * ny * nz, dx * dy * dz),
+            "phi": np.concatenate([ph, bph]), "patch_start": np.array(starts), "shape": (nx, ny, nz)}

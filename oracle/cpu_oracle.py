@@ -91,6 +91,10 @@ def lib() -> C.CDLL:
     L.orc_integrate_exp_neg.restype = d
     L.orc_integrate_exp_neg.argtypes = [d]
     L.orc_max_threads.restype = i
+    ip = C.POINTER(C.c_int32)
+    L.orc_transport_upwind_explicit.restype = None
+    L.orc_transport_upwind_explicit.argtypes = [i64, i64, ip, ip, i64, ip, _dp, i, i64, _dp, _dp, _dp,
+                                                i64, _dp, d, _dp]
     _lib = L
     return L
 
@@ -196,3 +200,20 @@ def qmom_update(m, S, dt, want_d=True):
     d = np.empty(ncells) if want_d else None
     lib().orc_qmom_update(nm // 2, ncells, ncells, _p(m), _p(S), dt, _p(d))
     return d
+
+
+def transport_upwind_explicit(owner, neighbour, boundary_owner, vcell, psi, phi, dt, psi_b=None, S=None):
+    """MULES::explicitSolve with the upwind flux on OpenFOAM face addressing (see pbe_oracle.h;
+    parity unpinned: OpenFOAM itself is absent).  psi [K][ncells] -> new psi."""
+    ip = C.POINTER(C.c_int32)
+    own, nei, bown = (np.ascontiguousarray(a, dtype=np.int32) for a in (owner, neighbour, boundary_owner))
+    psi = np.ascontiguousarray(psi, dtype=np.float64)
+    K, ncells = psi.shape
+    out = np.empty_like(psi)
+    if psi_b is not None:
+        psi_b = np.ascontiguousarray(psi_b, dtype=np.float64)
+    lib().orc_transport_upwind_explicit(
+        ncells, own.size, own.ctypes.data_as(ip), nei.ctypes.data_as(ip), bown.size,
+        bown.ctypes.data_as(ip), _p(np.ascontiguousarray(vcell, dtype=np.float64)), K, ncells, _p(psi),
+        _p(np.ascontiguousarray(phi, dtype=np.float64)), _p(psi_b), bown.size, _p(S), float(dt), _p(out))
+    return out

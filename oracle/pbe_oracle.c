@@ -530,3 +530,35 @@ static double exp_neg(double x, void *p) {
 double orc_integrate_exp_neg(double lower) {
     return orc_integrate_qagiu(exp_neg, NULL, lower, 1e-7, 0.0, 1000, NULL, NULL);
 }
+
+/* ---- transport (row f2, first slice): see pbe_oracle.h for the OpenFOAM functions restated --- */
+void orc_transport_upwind_explicit(int64_t ncells, int64_t nint, const int32_t *owner,
+                                   const int32_t *neighbour, int64_t nbnd, const int32_t *bowner,
+                                   const double *vcell, int nfields, int64_t stride,
+                                   const double *psi, const double *phi, const double *psi_b,
+                                   int64_t stride_b, const double *S, double dt, double *out) {
+    const double rDeltaT = 1.0 / dt;
+    double *ivf = (double *)malloc(sizeof(double) * (size_t)(ncells > 0 ? ncells : 1));
+    for (int k = 0; k < nfields; ++k) {
+        const double *f = psi + (size_t)k * stride;
+        for (int64_t c = 0; c < ncells; ++c) ivf[c] = 0.0;
+        for (int64_t fi = 0; fi < nint; ++fi) { /* upwind<scalar>(mesh, phi).flux(psi) */
+            const double lambda = phi[fi] >= 0.0 ? 1.0 : 0.0; /* pos() */
+            const double P = f[owner[fi]], N = f[neighbour[fi]];
+            const double face = lambda * (P - N) + N;
+            const double flux = phi[fi] * face;
+            ivf[owner[fi]] += flux;
+            ivf[neighbour[fi]] -= flux;
+        }
+        for (int64_t b = 0; b < nbnd; ++b) {
+            const double face = psi_b ? psi_b[(size_t)k * stride_b + b] : f[bowner[b]];
+            ivf[bowner[b]] += phi[nint + b] * face;
+        }
+        for (int64_t c = 0; c < ncells; ++c) {
+            const double div = ivf[c] / vcell[c];
+            const double Su = S ? S[(size_t)k * stride + c] : 0.0;
+            out[(size_t)k * stride + c] = (f[c] * rDeltaT + Su - div) / rDeltaT;
+        }
+    }
+    free(ivf);
+}

@@ -105,6 +105,25 @@ double orc_integrate_qagiu(orc_integrand f, void *params, double lower, double e
 /* convenience for tests: integral of exp(-x) from `lower` (tests/unit_tests/integration.cpp) */
 double orc_integrate_exp_neg(double lower);
 
+/* ---- transport, SURVEY 8 row f2 (first slice): MULES::explicitSolve with the upwind face flux,
+ * i.e. MOC::solveWithMULES (MOC.C:198-272) / QMOM::solveWithMULES (QMOM.C:131-197) when the
+ * divergence scheme of the case is `Gauss upwind` (the limited correction phiCorr is then zero).
+ * PARITY UNPINNED: OpenFOAM is a third-party dependency absent from the reference tree and from
+ * this image; the loops restate OpenFOAM 3.0.x from its published sources:
+ *   face value   lambda (psi_P - psi_N) + psi_N, lambda = pos(phi_f)    (surfaceInterpolationScheme
+ *                ::interpolate with upwind::weights = pos(faceFlux)); boundary faces take the
+ *                patch value psi_b (NULL = zero-gradient = the owner cell's value)
+ *   divergence   fvc::surfaceIntegrate: ivf[own] += flux, ivf[nei] -= flux over internal faces
+ *                in face order, then boundary faces, then ivf /= V
+ *   update       psi = (psi0 rDeltaT + Su - div) / rDeltaT, rDeltaT = 1/dt  (rho = 1, Sp = 0)
+ * Faces: OpenFOAM addressing, internal faces 0..nint-1 (owner, neighbour), boundary faces
+ * nint..nint+nbnd-1 with their owner cell; phi has nint + nbnd entries. */
+void orc_transport_upwind_explicit(int64_t ncells, int64_t nint, const int32_t *owner,
+                                   const int32_t *neighbour, int64_t nbnd, const int32_t *bowner,
+                                   const double *vcell, int nfields, int64_t stride,
+                                   const double *psi, const double *phi, const double *psi_b,
+                                   int64_t stride_b, const double *S, double dt, double *out);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -1,0 +1,172 @@
+"""Row f2 (first slice): explicit upwind transport + source update on OpenFOAM face addressing.
+
+CPU part: properties of the oracle restatement (parity unpinned: OpenFOAM is not on this machine,
+so the restated MULES::explicitSolve / upwind / surfaceIntegrate loops are checked against what the
+scheme must do analytically).  GPU part: the device kernels against the oracle, bit for bit.
+"""
+import numpy as np
+import pytest
+
+from oracle import cpu_oracle as orc
+from openpbe_b200 import capi, synthetic
+
+
+def chain_mesh(n, u=1.0, dx=1.0):
+    m = synthetic.block_mesh(n, 1, 1, lengths=(n * dx, 1.0, 1.0), velocity=(u, 0.0, 0.0))
+    return m
+
+
+def random_mesh(rng, ncells, nint, nbnd):
+    """Any owner < neighbour pair list is a valid face addressing for the update (topology only)."""
+    a = rng.integers(0, ncells, size=nint)
+    b = (a + 1 + rng.integers(0, ncells - 1, size=nint)) % ncells
+    own, nei = np.minimum(a, b), np.maximum(a, b)
+    order = np.lexsort((nei, own))
+    return {"owner": own[order].astype(np.int32), "neighbour": nei[order].astype(np.int32),
+            "boundary_owner": rng.integers(0, ncells, size=nbnd).astype(np.int32),
+            "vcell": rng.uniform(0.5, 2.0, ncells), "phi": rng.normal(size=nint + nbnd)}
+
+
+def test_block_mesh_addressing():
+    m = synthetic.block_mesh(4, 3, 2)
+    assert m["owner"].size == 3 * 3 * 2 + 4 * 2 * 2 + 4 * 3 * 1
+    assert np.all(m["owner"] < m["neighbour"])
+    assert np.all(np.diff(m["owner"]) >= 0)  # upper-triangular order
+    assert m["boundary_owner"].size == 2 * (3 * 2 + 4 * 2 + 4 * 3)
+    # a uniform velocity is divergence-free: per-cell flux sums vanish
+    div = np.zeros(24)
+    ni = m["owner"].size
+    np.add.at(div, m["owner"], m["phi"][:ni]); np.add.at(div, m["neighbour"], -m["phi"][:ni])
+    np.add.at(div, m["boundary_owner"], m["phi"][ni:])
+    assert np.abs(div).max() < 1e-15
+
+
+def test_oracle_cfl_one_shift_is_exact():
+    # 1-D chain, u dt / dx = 1: upwind moves every value exactly one cell downstream
+    n = 16
+    m = chain_mesh(n)
+    psi = np.arange(1.0, n + 1)[None, :].repeat(2, 0) * np.array([[1.0], [3.0]])
+    psi_b = np.zeros((2, m["boundary_owner"].size)); psi_b[:, 0] = [7.0, 9.0]  # inflow values at x-
+    psi_b[:, 1] = psi[:, -1]  # zero-gradient at the outlet; side patches carry no flux
+    out = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi,
+                                        m["phi"], 1.0, psi_b=psi_b)
+    np.testing.assert_array_equal(out[:, 1:], psi[:, :-1])
+    np.testing.assert_array_equal(out[:, 0], [7.0, 9.0])
+
+
+def test_oracle_conservation_and_source():
+    rng = np.random.default_rng(5)
+    m = synthetic.block_mesh(7, 5, 3, velocity=(0.3, -0.2, 0.1))
+    ni = m["owner"].size
+    phi = m["phi"].copy(); phi[:ni] = rng.normal(size=ni) * 1e-3; phi[ni:] = 0.0  # closed box
+    psi = rng.uniform(0.0, 1.0, (3, 105)); S = rng.normal(size=(3, 105))
+    dt = 0.01
+    out = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, phi, dt, S=S)
+    V = m["vcell"]
+    np.testing.assert_allclose((out * V).sum(1), (psi * V).sum(1) + dt * (S * V).sum(1), rtol=1e-13)
+    # zero flux: the MULES form of n + dt S (MOC.C:259-272 as the 0-D integration tests run it)
+    out0 = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], V, psi, 0 * phi, dt, S=S)
+    np.testing.assert_allclose(out0, psi + dt * S, rtol=1e-14)
+
+
+def test_oracle_upwind_is_bounded():
+    # divergence-free flux, CFL < 1, zero-gradient outflow / fixed inflow: no new extrema
+    rng = np.random.default_rng(6)
+    m = synthetic.block_mesh(9, 8, 4, velocity=(1.0, 0.5, -0.25))
+    psi = rng.uniform(1.0, 2.0, (2, 288))
+    psi_b = rng.uniform(1.0, 2.0, (2, m["boundary_owner"].size))
+    outflow = m["phi"][m["owner"].size:] >= 0
+    psi_b[:, outflow] = psi[:, m["boundary_owner"][outflow]]  # zeroGradient where the flow leaves
+    dt = 0.4 * (1 / 9) / 1.75
+    out = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], dt, psi_b=psi_b)
+    assert out.min() >= 1.0 - 1e-12 and out.max() <= 2.0 + 1e-12
+
+
+def test_div_scheme_names():
+    out = capi.C.c_int(-1)
+    assert capi.lib().pbe_div_scheme_type(b"Gauss upwind", capi.C.byref(out)) == capi.PBE_OK and out.value == capi.DIV_UPWIND
+    rc = capi.lib().pbe_div_scheme_type(b"Gauss vanLeer", capi.C.byref(out))
+    assert rc == capi.PBE_E_UNKNOWN_TYPE
+    msg = capi.last_error()
+    assert "vanLeer" in msg and "Valid schemes are" in msg and "upwind" in msg
+
+
+# ------------------------------------------------------------------------------------------------
+gpu = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from openpbe_b200 import engine
+    return engine.Context(0)
+
+
+def _run_device(ctx, m, psi, phi, dt, psi_b=None, S=None):
+    import torch
+    from openpbe_b200 import engine
+    dev = torch.device("cuda:0")
+    T = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    out = mesh.transport_explicit(T(psi), T(phi), dt, psi_b=T(psi_b), S=T(S))
+    return out.cpu().numpy(), mesh.info()
+
+
+@gpu
+@pytest.mark.parametrize("shape", [(12, 9, 7), (33, 1, 1), (17, 13, 1), (300, 40, 9)])
+@pytest.mark.parametrize("K", [1, 6, 30])
+def test_device_matches_oracle_block(ctx, shape, K):
+    rng = np.random.default_rng(shape[0] * 100 + K)
+    m = synthetic.block_mesh(*shape, velocity=(1.0, -0.7, 0.3))
+    nc = m["vcell"].size
+    phi = m["phi"] * rng.uniform(0.5, 1.5, m["phi"].size) * rng.choice([1.0, 1.0, -1.0, 0.0], m["phi"].size)
+    psi = rng.uniform(0.0, 1e8, (K, nc)) * rng.choice([1.0, 1e-20], (K, nc))
+    S = rng.normal(size=(K, nc)) * 1e9
+    psi_b = rng.uniform(0.0, 1e8, (K, m["boundary_owner"].size))
+    dt = 2.5e-4
+    for kw in ({}, {"psi_b": psi_b}, {"S": S}, {"psi_b": psi_b, "S": S}):
+        want = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, phi, dt, **kw)
+        got, info = _run_device(ctx, m, psi, phi, dt, **kw)
+        assert info["max_faces_per_cell"] == 6
+        nreg = max(shape[0] - 2, 0) * max(shape[1] - 2, 0) * max(shape[2] - 2, 0)
+        assert info["regular_cells"] == nreg and (nreg == 0 or info["faces_per_regular_cell"] == 6)
+        np.testing.assert_array_equal(got, want)
+
+
+@gpu
+@pytest.mark.parametrize("nint,nbnd", [(0, 0), (40, 3), (900, 120), (5000, 0)])
+def test_device_matches_oracle_random_topology(ctx, nint, nbnd):
+    # polyhedral-style connectivity: many faces per cell (generic kernel), cells without faces
+    rng = np.random.default_rng(nint + nbnd)
+    m = random_mesh(rng, 301, nint, nbnd)
+    psi = rng.normal(size=(5, 301)); S = rng.normal(size=(5, 301))
+    psi_b = rng.normal(size=(5, nbnd)) if nbnd else None
+    want = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.01, psi_b=psi_b, S=S)
+    got, _ = _run_device(ctx, m, psi, m["phi"], 0.01, psi_b=psi_b, S=S)
+    np.testing.assert_array_equal(got, want)
+
+
+@gpu
+def test_device_nonfinite_pattern_matches(ctx):
+    rng = np.random.default_rng(9)
+    m = synthetic.block_mesh(10, 6, 4, velocity=(1.0, 1.0, 1.0))
+    psi = rng.uniform(size=(3, 240)); psi[0, 17] = np.nan; psi[1, 100] = np.inf; psi[2, 5] = -np.inf
+    want = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.01)
+    got, _ = _run_device(ctx, m, psi, m["phi"], 0.01)
+    np.testing.assert_array_equal(got, want)  # NaN == NaN positionally in assert_array_equal
+
+
+@gpu
+def test_device_argument_errors(ctx):
+    import torch
+    from openpbe_b200 import engine
+    m = synthetic.block_mesh(4, 4, 4)
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    psi = torch.zeros(2, 64, dtype=torch.float64, device="cuda:0")
+    phi = torch.zeros(m["phi"].size, dtype=torch.float64, device="cuda:0")
+    with pytest.raises(capi.PbeError, match="alias"):
+        mesh.transport_explicit(psi, phi, 0.1, out=psi)
+    with pytest.raises(capi.PbeError, match="vanLeer"):
+        mesh.transport_explicit(psi, phi, 0.1, scheme="Gauss vanLeer")
+    with pytest.raises(capi.PbeError, match="owner"):
+        engine.Mesh(ctx, [0, 70], [1, 2], [], np.ones(64))
+    assert mesh.transport_explicit(psi[:0], phi, 0.1).shape == (0, 64)
