@@ -540,6 +540,59 @@ def run_b200(args):
             del mp, sp, Sh
         del m0, mq, Sq, flush
 
+    # ---- transport of the class fields (first slice) --------------------------
+    transport = None
+    if not args.no_transport:
+        tn = int(args.transport_n)
+        # one n^3 block per GPU: z-slabs of an n x n x (n world) block, processor patches between them
+        tm = synthetic.block_slab_part(tn, rank, world, velocity=(1.0, 0.5, 0.25))
+        tmesh = engine.Mesh(ctx, tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"])
+        tmesh.set_coupled(*tm["coupled"])
+        halo_x = sharding.HaloExchange(tm, dev, mesh=tmesh) if world > 1 else None
+        tinfo = tmesh.info()
+        tc, tK = tn ** 3, N
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(20240611 + rank)
+        tpsi = torch.rand(tK, tc, dtype=torch.float64, device=dev, generator=gen)
+        tS = torch.rand(tK, tc, dtype=torch.float64, device=dev, generator=gen)
+        tout = torch.empty_like(tpsi)
+        tphi = torch.from_numpy(tm["phi"]).to(dev)
+        tdt = 0.4 / (tn * 1.75)  # CFL 0.4
+        l0 = ctx.launch_count()
+
+        def tstep():
+            halo = halo_x.exchange(tpsi) if halo_x is not None else None
+            tmesh.transport_explicit(tpsi, tphi, tdt, S=tS, out=tout, psi_halo=halo)
+
+        for _ in range(max(3, args.warmup)):
+            tstep()
+        t_launches = (ctx.launch_count() - l0) // max(3, args.warmup)
+        barrier()
+        tsteps = max(3, args.steps)
+        e0.record()
+        for _ in range(tsteps):
+            tstep()
+        e1.record()
+        torch.cuda.synchronize()
+        tms = allmax(e0.elapsed_time(e1) / tsteps)
+        # psi and S in, psi out per cell-field; V, 6 x (neighbour, face) labels and 3 face fluxes per cell
+        tbytes = tc * (24.0 * tK + 8 + 6 * 8 + 3 * 8)
+        tgbs = tbytes / (tms * 1e-3) / 1e9
+        transport = {"metric": "transport_cell_field_updates_per_s", "value": world * tc * tK / (tms * 1e-3),
+                     "unit": "cell-field-updates/s", "ms_per_step": tms, "cells_per_gpu": tc, "fields": tK,
+                     "workload": f"explicit upwind transport + source update (MULES::explicitSolve form) of {tK} "
+                                 f"class fields on a {tn}^3 hex block in OpenFOAM face addressing, uniform "
+                                 "velocity (1, 0.5, 0.25), CFL 0.4; one block per GPU"
+                                 + (f", z-slabs of one {tn}x{tn}x{tn * world} block: halo exchange of "
+                                    f"{tK} x {tn * tn} values per processor patch (NCCL send/recv) inside the "
+                                    "timed step" if world > 1 else ""),
+                     "l2": f"fields ({3 * tc * tK * 8 / 1e9:.1f} GB) exceed the 126 MB L2",
+                     "mesh": tinfo, "launches_per_step": int(t_launches),
+                     "roofline": {"bound": "hbm", "achieved": tgbs, "peak": hbm_peak, "unit": "GB/s",
+                                  "frac": tgbs / hbm_peak, "algorithmic_bytes": tbytes,
+                                  "traffic": load_traffic("transport_upwind_kernel", tc)}}
+        del tpsi, tS, tout, tphi, tmesh
+
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) -----------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -570,7 +623,7 @@ def run_b200(args):
                                       if world > 1 else "1 GPU",
                        "device": info["name"], "sm_count": info["sm_count"]},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-            "cpu_baseline": cpu, "qmom": qmom,
+            "cpu_baseline": cpu, "qmom": qmom, "transport": transport,
             "checks": {"n_min_after_steps": n_min, "global_moments": gmom, "input_fill_s": t_gen},
         }
         print(json.dumps(line), flush=True)
@@ -592,6 +645,8 @@ def main():
     ap.add_argument("--cpu-sample-cells", type=int, default=8000)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-qmom", action="store_true")
+    ap.add_argument("--no-transport", action="store_true")
+    ap.add_argument("--transport-n", type=int, default=160, help="transport leg: hex block of n^3 cells")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     _, world, _ = dist_env()

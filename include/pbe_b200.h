@@ -203,6 +203,21 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
                            int64_t stride_b, const double *S, double dt, double *psi_out,
                            void *cuda_stream);
 
+/* Decomposed meshes (one sub-domain per GPU; cells block-partitioned as on the source path).
+ * Boundary faces [first, first + count) of this sub-domain are processor-patch faces; the face
+ * value there is OpenFOAM's coupled interpolation pos(phi_b) psi_own + (1 - pos(phi_b)) psi_across,
+ * with psi_across delivered per step in psi_halo [nfields][stride_h] (DEVICE; entry j = the cell
+ * across coupled face first + j).  pbe_gather_cells packs the values the neighbouring ranks need
+ * (out[k][j] = psi[k][cells[j]], cells DEVICE int32); the exchange itself is the caller's
+ * (NCCL send / recv over NVLink in openpbe_b200/sharding.py). */
+int pbe_mesh_set_coupled(pbe_mesh *mesh, int64_t first_boundary_face, int64_t count);
+int pbe_gather_cells(pbe_ctx *ctx, int nfields, int64_t stride, const double *psi, int64_t n,
+                     const int32_t *cells, double *out, int64_t stride_out, void *cuda_stream);
+int pbe_transport_explicit_halo(pbe_mesh *mesh, int scheme, int nfields, int64_t stride,
+                                const double *psi, const double *phi, const double *psi_b,
+                                int64_t stride_b, const double *psi_halo, int64_t stride_h,
+                                const double *S, double dt, double *psi_out, void *cuda_stream);
+
 /* ======================================================================================= */
 /* Scalar kernel functors evaluated ON THE DEVICE (batched) -- the reference's Foam-free     */
 /* *Impl::S surface (coalescenceKernels/CoulaloglouTavlarides.H:44-63, breakupKernels/       */

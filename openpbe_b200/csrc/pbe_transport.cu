@@ -27,11 +27,12 @@
 
 #include "pbe_common.h"
 
+// Resident 256-thread CTAs per SM the regular-cell kernel is compiled for (64 registers).  Measured
+// on B200, 160^3 cells x 100 fields: 4 CTAs 3.70 ms, 3 CTAs (80 registers) 3.80 ms; an L2 prefetch
+// of the streamed rows four fields ahead changes nothing (the loop is issue- and latency-bound at
+// ~150 instructions per warp and field, not waiting on DRAM alone).
 #ifndef PBE_TR_CTAS
 #define PBE_TR_CTAS 4
-#endif
-#ifndef PBE_TR_PD
-#define PBE_TR_PD 4 // prefetch distance (fields) of the two streamed rows
 #endif
 
 struct pbe_mesh {
@@ -46,6 +47,7 @@ struct pbe_mesh {
     int32_t *d_irr_cell = nullptr, *d_irr_ptr = nullptr;
     int32_t *d_irr_other = nullptr; // >= 0 neighbour cell; -(b + 2) boundary face b
     int32_t *d_irr_face = nullptr;  // as d_face (boundary faces: n_internal + b)
+    int64_t coupled0 = 0, ncoupled = 0; // boundary faces [coupled0, coupled0 + ncoupled): processor patches
 };
 
 namespace pbe {
@@ -55,6 +57,8 @@ struct TransportParams {
     int nfields, chunk;
     const int32_t *other, *face, *irr_cell, *irr_ptr, *irr_other, *irr_face;
     const double *vcell, *psi, *phi, *psi_b, *S;
+    const double *psi_halo; // [nfields][stride_h]: cell values across the coupled faces
+    int64_t stride_h, coupled0, ncoupled;
     double *out;
     double rdt;  // 1/dt, as MULES::explicitSolve forms it
     double rrdt; // RN(1/rdt): reciprocal for div_by
@@ -122,18 +126,8 @@ __global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(Tran
     const double *row = p.psi + (size_t)k0 * p.stride;
     const double *srow = (p.S != nullptr) ? p.S + (size_t)k0 * p.stride : nullptr;
     double *orow = p.out + (size_t)k0 * p.stride;
-    const bool pf_lane = (threadIdx.x & 3) == 0;
 #pragma unroll 2
     for (int k = k0; k < k1; ++k, row += p.stride, orow += p.stride) {
-#if PBE_TR_PD > 0
-        // the two streamed rows of a field a few iterations ahead are pulled into L2 meanwhile
-        // (one request per 32-B sector); the neighbour gathers are L1 / L2 hits
-        if (pf_lane && k + PBE_TR_PD < k1) {
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(row + (size_t)PBE_TR_PD * p.stride + c));
-            if (srow != nullptr)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(srow + (size_t)PBE_TR_PD * p.stride + c));
-        }
-#endif
         const double mine = __ldg(row + c);
         double th[F];
 #pragma unroll
@@ -170,13 +164,33 @@ __global__ void __launch_bounds__(128) transport_upwind_irregular_kernel(Transpo
             if (oth >= 0) {
                 acc = add_internal(acc, make_side(face, p.phi), mine, __ldg(row + oth));
             } else { // boundary face: patch value (NULL psi_b = zero-gradient = the cell's own value)
-                const double pv = (p.psi_b != nullptr) ? __ldg(p.psi_b + (size_t)k * p.stride_b - (oth + 2)) : mine;
-                acc = __dadd_rn(acc, __dmul_rn(__ldg(p.phi + face), pv));
+                const int64_t b = -(int64_t)oth - 2;
+                const double ph = __ldg(p.phi + face);
+                double pv;
+                if (b >= p.coupled0 && b < p.coupled0 + p.ncoupled) {
+                    // processor patch: pLambda psi_own + (1 - pLambda) psi_across, pLambda = pos(phi_b)
+                    const double w = ph >= 0.0 ? 1.0 : 0.0;
+                    const double across = __ldg(p.psi_halo + (size_t)k * p.stride_h + (b - p.coupled0));
+                    pv = __dadd_rn(__dmul_rn(w, mine), __dmul_rn(__dsub_rn(1.0, w), across));
+                } else {
+                    pv = (p.psi_b != nullptr) ? __ldg(p.psi_b + (size_t)k * p.stride_b + b) : mine;
+                }
+                acc = __dadd_rn(acc, __dmul_rn(ph, pv));
             }
         }
         const double Su = (p.S != nullptr) ? __ldg(p.S + (size_t)k * p.stride + c) : 0.0;
         p.out[(size_t)k * p.stride + c] = updated(p, mine, Su, acc, V, rV);
     }
+}
+
+// halo packing: out[k][j] = psi[k][cells[j]]
+__global__ void __launch_bounds__(256) gather_cells_kernel(int nfields, int64_t stride, const double *psi,
+                                                           int64_t n, const int32_t *cells, double *out,
+                                                           int64_t stride_out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int c = __ldg(cells + j);
+    for (int k = blockIdx.y; k < nfields; k += gridDim.y) out[(size_t)k * stride_out + j] = __ldg(psi + (size_t)k * stride + c);
 }
 
 } // namespace pbe
@@ -334,9 +348,41 @@ int pbe_mesh_regular_cells(pbe_mesh *m, int *faces_per_regular_cell, int64_t *n_
     return PBE_OK;
 }
 
+int pbe_mesh_set_coupled(pbe_mesh *m, int64_t first_boundary_face, int64_t count) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_mesh_set_coupled: NULL mesh");
+    PBE_REQUIRE(first_boundary_face >= 0 && count >= 0 && first_boundary_face + count <= m->nbnd,
+                PBE_E_INVALID, "pbe_mesh_set_coupled: faces [%lld, %lld) outside the %lld boundary faces",
+                (long long)first_boundary_face, (long long)(first_boundary_face + count), (long long)m->nbnd);
+    m->coupled0 = first_boundary_face;
+    m->ncoupled = count;
+    return PBE_OK;
+}
+
+int pbe_gather_cells(pbe_ctx *ctx, int nfields, int64_t stride, const double *psi, int64_t n,
+                     const int32_t *cells, double *out, int64_t stride_out, void *cuda_stream) {
+    PBE_REQUIRE(ctx != nullptr, PBE_E_INVALID, "pbe_gather_cells: NULL context");
+    PBE_REQUIRE(nfields >= 0 && n >= 0 && stride_out >= n, PBE_E_INVALID, "pbe_gather_cells: bad sizes");
+    if (nfields == 0 || n == 0) return PBE_OK;
+    PBE_REQUIRE(psi && cells && out, PBE_E_INVALID, "pbe_gather_cells: NULL pointer");
+    DeviceGuard g(ctx->device);
+    dim3 grid((unsigned)((n + 255) / 256), (unsigned)std::min(nfields, 64));
+    gather_cells_kernel<<<grid, 256, 0, (cudaStream_t)cuda_stream>>>(nfields, stride, psi, n, cells, out, stride_out);
+    PBE_CUDA(cudaGetLastError());
+    ctx->launches++;
+    return PBE_OK;
+}
+
 int pbe_transport_explicit(pbe_mesh *m, int scheme, int nfields, int64_t stride, const double *psi,
                            const double *phi, const double *psi_b, int64_t stride_b,
                            const double *S, double dt, double *psi_out, void *cuda_stream) {
+    return pbe_transport_explicit_halo(m, scheme, nfields, stride, psi, phi, psi_b, stride_b, nullptr, 0, S,
+                                       dt, psi_out, cuda_stream);
+}
+
+int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t stride,
+                                const double *psi, const double *phi, const double *psi_b,
+                                int64_t stride_b, const double *psi_halo, int64_t stride_h,
+                                const double *S, double dt, double *psi_out, void *cuda_stream) {
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_transport_explicit: NULL mesh");
     PBE_REQUIRE(scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
                 "pbe_transport_explicit: scheme %d is not available on the device (valid: "
@@ -352,12 +398,17 @@ int pbe_transport_explicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
                 "pbe_transport_explicit: psi_out must not alias psi (neighbours read old values)");
     PBE_REQUIRE(psi_b == nullptr || stride_b >= m->nbnd, PBE_E_INVALID,
                 "pbe_transport_explicit: stride_b < boundary faces");
+    PBE_REQUIRE(m->ncoupled == 0 || (psi_halo != nullptr && stride_h >= m->ncoupled), PBE_E_INVALID,
+                "pbe_transport_explicit: the mesh has %lld coupled (processor) faces: "
+                "pbe_transport_explicit_halo needs psi_halo [nfields][stride_h >= %lld]",
+                (long long)m->ncoupled, (long long)m->ncoupled);
     pbe_ctx *ctx = m->ctx;
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     TransportParams p{m->ncells, stride, stride_b, m->nint, m->nirr, nfields, 1,
                       m->d_other, m->d_face, m->d_irr_cell, m->d_irr_ptr, m->d_irr_other, m->d_irr_face,
-                      m->d_vcell, psi, phi, psi_b, S, psi_out, 1.0 / dt, 1.0 / (1.0 / dt)};
+                      m->d_vcell, psi, phi, psi_b, S, psi_halo, stride_h, m->coupled0, m->ncoupled,
+                      psi_out, 1.0 / dt, 1.0 / (1.0 / dt)};
     // fields per CTA (grid.y = field chunks): few enough that the rows a wave of CTAs gathers
     // neighbours from stay in L2, many enough to amortise the per-cell face data; small meshes
     // get more chunks so that every SM has work

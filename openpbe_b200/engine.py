@@ -365,14 +365,32 @@ class Mesh:
                 "max_faces_per_cell": d.value, "faces_per_regular_cell": F.value,
                 "regular_cells": nreg.value}
 
-    def transport_explicit(self, psi, phi, dt, *, psi_b=None, S=None, out=None, scheme="upwind"):
+    def set_coupled(self, first_boundary_face: int, count: int):
+        """Mark boundary faces [first, first+count) as processor-patch faces (decomposed mesh)."""
+        capi.check(capi.lib().pbe_mesh_set_coupled(self._h, int(first_boundary_face), int(count)))
+        self.n_coupled = int(count)
+
+    def gather_cells(self, psi, cells, out=None):
+        """out[k][j] = psi[k][cells[j]] (halo packing); cells: int32 device tensor."""
+        K, ncells = psi.shape
+        n = cells.numel()
+        assert cells.dtype == torch.int32 and cells.is_contiguous() and cells.device == psi.device
+        out = torch.empty((K, n), dtype=psi.dtype, device=psi.device) if out is None else out
+        capi.check(capi.lib().pbe_gather_cells(self.ctx.handle, K, psi.stride(0) if ncells else 0, _ptr(psi), n,
+                                               C.c_void_p(cells.data_ptr()), _ptr(out), out.stride(0) if n else 0,
+                                               _stream_ptr(psi.device)))
+        return out
+
+    def transport_explicit(self, psi, phi, dt, *, psi_b=None, S=None, out=None, scheme="upwind",
+                           psi_halo=None):
         """psi [K][ncells] -> (psi rDeltaT + S - div(phi psi_upwind)) / rDeltaT, new tensor or `out`."""
         assert psi.dim() == 2
         K, ncells = psi.shape
         out = torch.empty_like(psi) if out is None else out
-        capi.check(capi.lib().pbe_transport_explicit(
+        capi.check(capi.lib().pbe_transport_explicit_halo(
             self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), K,
             psi.stride(0) if ncells else 0, _ptr(psi), _ptr(phi), _ptr(psi_b),
-            0 if psi_b is None else psi_b.stride(0), _ptr(S), float(dt), _ptr(out),
+            0 if psi_b is None else psi_b.stride(0), _ptr(psi_halo),
+            0 if psi_halo is None else psi_halo.stride(0), _ptr(S), float(dt), _ptr(out),
             _stream_ptr(psi.device)))
         return out

@@ -48,3 +48,88 @@ def avg_max_min(partials: torch.Tensor, group=None):
     mn = partials[3:4].clone()
     reduce_diagnostics(s, mn, mx, group)
     return (s[0] / s[1]).item(), mx.item(), mn.item()
+
+
+# ---- transport: decomposed meshes and the halo exchange ------------------------
+# The only data-path exchange of the engine.  Cells stay block-partitioned exactly as on the source
+# path; a face whose two cells live on different ranks becomes a processor-patch face on both
+# (appended after the physical boundary faces, grouped by neighbouring rank, in ascending global
+# face order on both sides -- OpenFOAM's decomposePar convention), and before every transport step
+# each rank sends the field values of its cells along those faces to the rank across.
+import numpy as np  # noqa: E402
+
+
+def rank_of_cell(cells, ncells: int, world: int):
+    begins = np.array([shard_range(ncells, r, world)[0] for r in range(world)] + [ncells])
+    return np.searchsorted(begins, cells, side="right") - 1
+
+
+def partition_mesh(mesh: dict, rank: int, world: int) -> dict:
+    """Sub-domain `rank` of a mesh dict (owner, neighbour, boundary_owner, vcell, phi as
+    synthetic.block_mesh returns them).  Adds: coupled = (first boundary face, count),
+    neighbours = [(rank, first coupled face, count)], send_cells (local, one per coupled face),
+    halo_cells_global (the cell across each coupled face), cell_range, phys_faces."""
+    own, nei, bown = (np.asarray(mesh[k], dtype=np.int64) for k in ("owner", "neighbour", "boundary_owner"))
+    V, phi = np.asarray(mesh["vcell"]), np.asarray(mesh["phi"])
+    nc, ni = V.size, own.size
+    lo, hi = shard_range(nc, rank, world)
+    o_in, n_in = (own >= lo) & (own < hi), (nei >= lo) & (nei < hi)
+    internal, cut = o_in & n_in, o_in ^ n_in
+    cut_faces = np.nonzero(cut)[0]
+    mine = np.where(o_in, own, nei)[cut]
+    across = np.where(o_in, nei, own)[cut]
+    sign = np.where(o_in[cut], 1.0, -1.0)  # phi is positive owner -> neighbour; patch flux is outward
+    other = rank_of_cell(across, nc, world)
+    order = np.lexsort((cut_faces, other))
+    phys = np.nonzero((bown >= lo) & (bown < hi))[0]
+    groups, start = [], 0
+    for q in np.unique(other):
+        cnt = int(np.sum(other == q))
+        groups.append((int(q), start, cnt))
+        start += cnt
+    return {
+        "owner": (own[internal] - lo).astype(np.int32), "neighbour": (nei[internal] - lo).astype(np.int32),
+        "boundary_owner": np.concatenate([bown[phys] - lo, mine[order] - lo]).astype(np.int32),
+        "vcell": V[lo:hi].copy(),
+        "phi": np.concatenate([phi[:ni][internal], phi[ni:][phys], (sign * phi[:ni][cut])[order]]),
+        "coupled": (int(phys.size), int(cut_faces.size)), "neighbours": groups,
+        "send_cells": (mine[order] - lo).astype(np.int32), "halo_cells_global": across[order],
+        "cell_range": (lo, hi), "phys_faces": phys,
+    }
+
+
+class HaloExchange:
+    """Per-step exchange of the values along the processor patches: pack (device gather kernel, or
+    plain indexing for CPU tensors in the gloo tests), one send + one receive per neighbouring rank
+    (`torch.distributed` point-to-point: NCCL over NVLink between GPUs), unpack into the
+    [fields][coupled faces] layout pbe_transport_explicit_halo reads."""
+
+    def __init__(self, part: dict, device, mesh=None, group=None):
+        self.groups = part["neighbours"]
+        self.n = part["coupled"][1]
+        self.mesh = mesh  # engine.Mesh (device packing) or None (CPU tensors)
+        self.group = group
+        self.send_cells = torch.from_numpy(part["send_cells"]).to(device)
+
+    def pack(self, psi: torch.Tensor, q_start: int, q_count: int) -> torch.Tensor:
+        idx = self.send_cells[q_start:q_start + q_count]
+        if self.mesh is not None and psi.is_cuda:
+            return self.mesh.gather_cells(psi, idx)
+        return psi[:, idx.long()].contiguous()
+
+    def exchange(self, psi: torch.Tensor) -> torch.Tensor:
+        halo = torch.empty((psi.shape[0], self.n), dtype=psi.dtype, device=psi.device)
+        if not self.groups:
+            return halo
+        ops, recvs = [], []
+        for q, start, count in self.groups:
+            s = self.pack(psi, start, count)
+            r = torch.empty_like(s)
+            recvs.append((r, start, count))
+            ops.append(dist.P2POp(dist.isend, s, q, self.group))
+            ops.append(dist.P2POp(dist.irecv, r, q, self.group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        for r, start, count in recvs:
+            halo[:, start:start + count] = r
+        return halo

@@ -182,3 +182,23 @@ def block_mesh(nx: int, ny: int, nz: int, lengths=(1.0, 1.0, 1.0), velocity=(1.0
     return {"owner": own.astype(np.int32), "neighbour": nei.astype(np.int32),
             "boundary_owner": bown.astype(np.int32), "vcell": np.full(nx * ny * nz, dx * dy * dz),
             "phi": np.concatenate([ph, bph]), "patch_start": np.array(starts), "shape": (nx, ny, nz)}
+
+
+def block_slab_part(n: int, rank: int, world: int, velocity=(1.0, 0.5, 0.25)):
+    """Sub-domain `rank` of an n x n x (n world) hex block cut into z-slabs of n^3 cells, built
+    directly (what sharding.partition_mesh gives for the global block, without generating it):
+    the z- / z+ patches of the local block are the processor patches towards rank-1 / rank+1."""
+    m = block_mesh(n, n, n, lengths=(1.0, 1.0, 1.0), velocity=velocity)
+    ps = m["patch_start"]
+    lo_c, hi_c = rank > 0, rank < world - 1
+    first = ps[4] if lo_c else ps[5]
+    count = (ps[5] - ps[4] if lo_c else 0) + (ps[6] - ps[5] if hi_c else 0)
+    groups, start = [], 0
+    if lo_c:
+        groups.append((rank - 1, 0, int(ps[5] - ps[4]))); start = int(ps[5] - ps[4])
+    if hi_c:
+        groups.append((rank + 1, start, int(ps[6] - ps[5])))
+    send = m["boundary_owner"][first:first + count].copy()
+    m.update({"coupled": (int(first) if count else int(ps[6]), int(count)), "neighbours": groups,
+              "send_cells": send.astype(np.int32), "cell_range": (rank * n ** 3, (rank + 1) * n ** 3)})
+    return m

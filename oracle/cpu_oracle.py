@@ -95,6 +95,9 @@ def lib() -> C.CDLL:
     L.orc_transport_upwind_explicit.restype = None
     L.orc_transport_upwind_explicit.argtypes = [i64, i64, ip, ip, i64, ip, _dp, i, i64, _dp, _dp, _dp,
                                                 i64, _dp, d, _dp]
+    L.orc_transport_upwind_explicit_coupled.restype = None
+    L.orc_transport_upwind_explicit_coupled.argtypes = [i64, i64, ip, ip, i64, ip, _dp, i, i64, _dp, _dp,
+                                                        _dp, i64, i64, i64, _dp, i64, _dp, d, _dp]
     _lib = L
     return L
 
@@ -202,9 +205,11 @@ def qmom_update(m, S, dt, want_d=True):
     return d
 
 
-def transport_upwind_explicit(owner, neighbour, boundary_owner, vcell, psi, phi, dt, psi_b=None, S=None):
+def transport_upwind_explicit(owner, neighbour, boundary_owner, vcell, psi, phi, dt, psi_b=None, S=None,
+                              coupled=None, psi_halo=None):
     """MULES::explicitSolve with the upwind flux on OpenFOAM face addressing (see pbe_oracle.h;
-    parity unpinned: OpenFOAM itself is absent).  psi [K][ncells] -> new psi."""
+    parity unpinned: OpenFOAM itself is absent).  psi [K][ncells] -> new psi.  coupled = (first, count)
+    marks processor-patch boundary faces whose across-the-face cell values are psi_halo [K][count]."""
     ip = C.POINTER(C.c_int32)
     own, nei, bown = (np.ascontiguousarray(a, dtype=np.int32) for a in (owner, neighbour, boundary_owner))
     psi = np.ascontiguousarray(psi, dtype=np.float64)
@@ -212,8 +217,13 @@ def transport_upwind_explicit(owner, neighbour, boundary_owner, vcell, psi, phi,
     out = np.empty_like(psi)
     if psi_b is not None:
         psi_b = np.ascontiguousarray(psi_b, dtype=np.float64)
-    lib().orc_transport_upwind_explicit(
+    c0, nc = coupled if coupled is not None else (0, 0)
+    if nc:
+        psi_halo = np.ascontiguousarray(psi_halo, dtype=np.float64)
+        assert psi_halo.shape == (K, nc)
+    lib().orc_transport_upwind_explicit_coupled(
         ncells, own.size, own.ctypes.data_as(ip), nei.ctypes.data_as(ip), bown.size,
         bown.ctypes.data_as(ip), _p(np.ascontiguousarray(vcell, dtype=np.float64)), K, ncells, _p(psi),
-        _p(np.ascontiguousarray(phi, dtype=np.float64)), _p(psi_b), bown.size, _p(S), float(dt), _p(out))
+        _p(np.ascontiguousarray(phi, dtype=np.float64)), _p(psi_b), bown.size, c0, nc,
+        _p(psi_halo) if nc else None, nc, _p(S), float(dt), _p(out))
     return out

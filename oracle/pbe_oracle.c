@@ -537,6 +537,18 @@ void orc_transport_upwind_explicit(int64_t ncells, int64_t nint, const int32_t *
                                    const double *vcell, int nfields, int64_t stride,
                                    const double *psi, const double *phi, const double *psi_b,
                                    int64_t stride_b, const double *S, double dt, double *out) {
+    orc_transport_upwind_explicit_coupled(ncells, nint, owner, neighbour, nbnd, bowner, vcell, nfields,
+                                          stride, psi, phi, psi_b, stride_b, 0, 0, NULL, 0, S, dt, out);
+}
+
+void orc_transport_upwind_explicit_coupled(int64_t ncells, int64_t nint, const int32_t *owner,
+                                           const int32_t *neighbour, int64_t nbnd,
+                                           const int32_t *bowner, const double *vcell, int nfields,
+                                           int64_t stride, const double *psi, const double *phi,
+                                           const double *psi_b, int64_t stride_b, int64_t coupled0,
+                                           int64_t ncoupled, const double *psi_halo,
+                                           int64_t stride_h, const double *S, double dt,
+                                           double *out) {
     const double rDeltaT = 1.0 / dt;
     double *ivf = (double *)malloc(sizeof(double) * (size_t)(ncells > 0 ? ncells : 1));
     for (int k = 0; k < nfields; ++k) {
@@ -551,7 +563,15 @@ void orc_transport_upwind_explicit(int64_t ncells, int64_t nint, const int32_t *
             ivf[neighbour[fi]] -= flux;
         }
         for (int64_t b = 0; b < nbnd; ++b) {
-            const double face = psi_b ? psi_b[(size_t)k * stride_b + b] : f[bowner[b]];
+            double face;
+            if (b >= coupled0 && b < coupled0 + ncoupled) {
+                /* coupled (processor) patch: pLambda patchInternalField + (1 - pLambda)
+                 * patchNeighbourField, pLambda = pos(phi_b) */
+                const double w = phi[nint + b] >= 0.0 ? 1.0 : 0.0;
+                face = w * f[bowner[b]] + (1.0 - w) * psi_halo[(size_t)k * stride_h + (b - coupled0)];
+            } else {
+                face = psi_b ? psi_b[(size_t)k * stride_b + b] : f[bowner[b]];
+            }
             ivf[bowner[b]] += phi[nint + b] * face;
         }
         for (int64_t c = 0; c < ncells; ++c) {

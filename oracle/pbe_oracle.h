@@ -123,6 +123,20 @@ void orc_transport_upwind_explicit(int64_t ncells, int64_t nint, const int32_t *
                                    const double *vcell, int nfields, int64_t stride,
                                    const double *psi, const double *phi, const double *psi_b,
                                    int64_t stride_b, const double *S, double dt, double *out);
+/* The same on one sub-domain of a decomposed mesh: boundary faces coupled0 .. coupled0+ncoupled-1
+ * are processor-patch faces; psi_halo[k*stride_h + j] is the value of the cell across coupled face
+ * j (patchNeighbourField) and the face value is OpenFOAM's coupled-patch interpolation
+ * pLambda psi_own + (1 - pLambda) psi_halo with pLambda = pos(phi_b) (surfaceInterpolationScheme::
+ * interpolate, coupled branch).  A decomposed run therefore differs from the serial one in the last
+ * bit on the cells next to a processor patch -- in OpenFOAM and here alike. */
+void orc_transport_upwind_explicit_coupled(int64_t ncells, int64_t nint, const int32_t *owner,
+                                           const int32_t *neighbour, int64_t nbnd,
+                                           const int32_t *bowner, const double *vcell, int nfields,
+                                           int64_t stride, const double *psi, const double *phi,
+                                           const double *psi_b, int64_t stride_b, int64_t coupled0,
+                                           int64_t ncoupled, const double *psi_halo,
+                                           int64_t stride_h, const double *S, double dt,
+                                           double *out);
 
 int orc_max_threads(void);
 

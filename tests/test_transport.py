@@ -170,3 +170,137 @@ def test_device_argument_errors(ctx):
     with pytest.raises(capi.PbeError, match="owner"):
         engine.Mesh(ctx, [0, 70], [1, 2], [], np.ones(64))
     assert mesh.transport_explicit(psi[:0], phi, 0.1).shape == (0, 64)
+
+
+# ---- decomposed meshes (row f2 x row e): partition, halo exchange, coupled faces ----------------
+def _decomposed_oracle(m, world, psi, dt, S=None, psi_b=None):
+    """Every sub-domain through the coupled oracle, halos taken straight from the global field."""
+    from openpbe_b200 import sharding
+    out = np.empty_like(psi)
+    parts = []
+    for r in range(world):
+        p = sharding.partition_mesh(m, r, world)
+        lo, hi = p["cell_range"]
+        nphys, ncpl = p["coupled"]
+        pb = None
+        if psi_b is not None:
+            pb = np.zeros((psi.shape[0], nphys + ncpl)); pb[:, :nphys] = psi_b[:, p["phys_faces"]]
+        out[:, lo:hi] = orc.transport_upwind_explicit(
+            p["owner"], p["neighbour"], p["boundary_owner"], p["vcell"], psi[:, lo:hi], p["phi"], dt, psi_b=pb,
+            S=None if S is None else np.ascontiguousarray(S[:, lo:hi]), coupled=p["coupled"],
+            psi_halo=psi[:, p["halo_cells_global"]])
+        parts.append(p)
+    return out, parts
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_partition_matches_serial_to_rounding(world):
+    rng = np.random.default_rng(world)
+    m = synthetic.block_mesh(6, 5, 8, velocity=(0.3, -0.2, 0.4))
+    m["phi"] = m["phi"] * rng.uniform(0.5, 1.5, m["phi"].size) * rng.choice([1.0, -1.0], m["phi"].size)
+    psi = rng.uniform(1.0, 2.0, (3, 240)); S = rng.normal(size=(3, 240))
+    psi_b = rng.uniform(1.0, 2.0, (3, m["boundary_owner"].size))
+    serial = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.01, psi_b=psi_b, S=S)
+    dec, parts = _decomposed_oracle(m, world, psi, 0.01, S=S, psi_b=psi_b)
+    np.testing.assert_allclose(dec, serial, rtol=1e-13)
+    # only cells on a processor patch may differ (coupled interpolation rounds differently)
+    touched = np.zeros(240, bool)
+    for r, p in enumerate(parts):
+        touched[p["cell_range"][0] + p["send_cells"]] = True
+        # both sides list the shared faces in the same order
+        for q, start, cnt in p["neighbours"]:
+            back = [g for g in parts[q]["neighbours"] if g[0] == r][0]
+            np.testing.assert_array_equal(p["halo_cells_global"][start:start + cnt],
+                                          parts[q]["cell_range"][0] + parts[q]["send_cells"][back[1]:back[1] + back[2]])
+    np.testing.assert_array_equal(dec[:, ~touched], serial[:, ~touched])
+    assert touched.sum() < 240
+
+
+def test_block_slab_part_is_the_partition_of_the_global_block():
+    from openpbe_b200 import sharding
+    n, world = 4, 3
+    g = synthetic.block_mesh(n, n, n * world, lengths=(1.0, 1.0, float(world)), velocity=(1.0, 0.5, 0.25))
+    for r in range(world):
+        a = sharding.partition_mesh(g, r, world)
+        b = synthetic.block_slab_part(n, r, world)
+        for k in ("owner", "neighbour", "send_cells"):
+            np.testing.assert_array_equal(a[k], b[k])
+        assert a["coupled"][1] == b["coupled"][1] and a["neighbours"] == b["neighbours"]
+        # same faces; the global block lists its z patches after the side patches just like the slab
+        nphys = a["coupled"][0]
+        assert sorted(a["boundary_owner"][:nphys]) == sorted(np.delete(b["boundary_owner"], np.arange(b["coupled"][0], b["coupled"][0] + b["coupled"][1])))
+        np.testing.assert_array_equal(a["boundary_owner"][nphys:], b["boundary_owner"][b["coupled"][0]:b["coupled"][0] + b["coupled"][1]])
+        np.testing.assert_allclose(a["phi"][nphys + a["owner"].size:], b["phi"][b["owner"].size + b["coupled"][0]:][:b["coupled"][1]], rtol=1e-15)
+
+
+def _halo_worker(rank, world, port, out):
+    import os
+    import torch
+    import torch.distributed as dist
+    from openpbe_b200 import sharding
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(11)
+    m = synthetic.block_mesh(5, 4, 6, velocity=(0.3, 0.2, 0.4))
+    psi = rng.uniform(1.0, 2.0, (4, 120))
+    p = sharding.partition_mesh(m, rank, world)
+    lo, hi = p["cell_range"]
+    hx = sharding.HaloExchange(p, "cpu")
+    halo = hx.exchange(torch.from_numpy(np.ascontiguousarray(psi[:, lo:hi]))).numpy()
+    np.testing.assert_array_equal(halo, psi[:, p["halo_cells_global"]])
+    new = orc.transport_upwind_explicit(p["owner"], p["neighbour"], p["boundary_owner"], p["vcell"], psi[:, lo:hi],
+                                        p["phi"], 0.02, coupled=p["coupled"], psi_halo=halo)
+    parts = [None] * world
+    dist.all_gather_object(parts, (lo, hi, new))
+    if rank == 0:
+        full = np.empty_like(psi)
+        for a, b, v in parts:
+            full[:, a:b] = v
+        np.save(out, full)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_halo_exchange_gloo(tmp_path):
+    import os
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "t.npy")
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(_halo_worker, args=(2, port, out), nprocs=2, join=True)
+    rng = np.random.default_rng(11)
+    m = synthetic.block_mesh(5, 4, 6, velocity=(0.3, 0.2, 0.4))
+    psi = rng.uniform(1.0, 2.0, (4, 120))
+    want, _ = _decomposed_oracle(m, 2, psi, 0.02)
+    np.testing.assert_array_equal(np.load(out), want)
+
+
+@gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_device_decomposed_matches_oracle(ctx, world):
+    import torch
+    from openpbe_b200 import engine, sharding
+    rng = np.random.default_rng(40 + world)
+    m = synthetic.block_mesh(11, 9, 12, velocity=(0.3, -0.2, 0.4))
+    m["phi"] = m["phi"] * rng.uniform(0.5, 1.5, m["phi"].size) * rng.choice([1.0, -1.0, 0.0], m["phi"].size)
+    nc = 11 * 9 * 12
+    psi = rng.uniform(0.0, 2.0, (7, nc)); S = rng.normal(size=(7, nc))
+    psi_b = rng.uniform(1.0, 2.0, (7, m["boundary_owner"].size))
+    want, parts = _decomposed_oracle(m, world, psi, 0.01, S=S, psi_b=psi_b)
+    dev = torch.device("cuda:0")
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    for p in parts:
+        lo, hi = p["cell_range"]
+        nphys, ncpl = p["coupled"]
+        mesh = engine.Mesh(ctx, p["owner"], p["neighbour"], p["boundary_owner"], p["vcell"])
+        mesh.set_coupled(nphys, ncpl)
+        pb = np.zeros((7, nphys + ncpl)); pb[:, :nphys] = psi_b[:, p["phys_faces"]]
+        loc = T(psi[:, lo:hi])
+        # what this rank would send is what its neighbours' halos hold
+        sent = mesh.gather_cells(loc, T(p["send_cells"])).cpu().numpy()
+        np.testing.assert_array_equal(sent, psi[:, lo + p["send_cells"]])
+        with pytest.raises(capi.PbeError, match="coupled"):
+            mesh.transport_explicit(loc, T(p["phi"]), 0.01)
+        got = mesh.transport_explicit(loc, T(p["phi"]), 0.01, psi_b=T(pb), S=T(S[:, lo:hi]),
+                                      psi_halo=T(psi[:, p["halo_cells_global"]]))
+        np.testing.assert_array_equal(got.cpu().numpy(), want[:, lo:hi])
