@@ -34,6 +34,9 @@
 #ifndef PBE_TR_CTAS
 #define PBE_TR_CTAS 4
 #endif
+#ifndef PBE_TR_STAGES
+#define PBE_TR_STAGES 2 // 0: register-staged loop; 2..4: cp.async pipeline depth (measured: 2, 3, 4 alike)
+#endif
 
 struct pbe_mesh {
     pbe_ctx *ctx = nullptr;
@@ -48,6 +51,9 @@ struct pbe_mesh {
     int32_t *d_irr_other = nullptr; // >= 0 neighbour cell; -(b + 2) boundary face b
     int32_t *d_irr_face = nullptr;  // as d_face (boundary faces: n_internal + b)
     int64_t coupled0 = 0, ncoupled = 0; // boundary faces [coupled0, coupled0 + ncoupled): processor patches
+    // the irregular cells' kernel runs beside the regular cells' one (disjoint outputs): fork / join
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace pbe {
@@ -83,27 +89,38 @@ __device__ __forceinline__ double div_by(double a, double b, double y) {
 // the FMA rounds once, exactly like the reference's multiply-then-add.
 struct Side {
     double phs; // own side ? phi : -phi
-    int lam_hi; // high word of lam = own side ? pos(phi) : -pos(phi); sign bit = "neighbour side"
+    double lam; // own side ? pos(phi) : -pos(phi): +-1 or +-0; the sign bit says "neighbour side"
 };
 
 __device__ __forceinline__ Side make_side(int32_t face, const double *phi) {
     const bool own = face >= 0;
     const double ph = __ldg(phi + (own ? face : ~face));
     const double lambda = ph >= 0.0 ? 1.0 : 0.0;
-    return Side{own ? ph : -ph, __double2hiint(own ? lambda : -lambda)};
+    return Side{own ? ph : -ph, own ? lambda : -lambda};
 }
 
 __device__ __forceinline__ double add_internal(double acc, const Side &t, double mine, double theirs) {
-    const double N = (t.lam_hi >= 0) ? theirs : mine;
-    const double fv = __fma_rn(__hiloint2double(t.lam_hi, 0), __dsub_rn(mine, theirs), N);
+    const double N = (__double2hiint(t.lam) >= 0) ? theirs : mine;
+    const double fv = __fma_rn(t.lam, __dsub_rn(mine, theirs), N);
     return __dadd_rn(acc, __dmul_rn(t.phs, fv));
 }
 
+// psi_new = ((psi rDeltaT + Su) - acc / V) / rDeltaT with both quotients correctly rounded (div_by's
+// sequence; one range test for the two of them)
 __device__ __forceinline__ double updated(const TransportParams &p, double mine, double Su, double acc,
                                           double V, double rV) {
-    const double div = div_by(acc, V, rV);
-    const double num = __dsub_rn(__dadd_rn(__dmul_rn(mine, p.rdt), Su), div);
-    return div_by(num, p.rdt, p.rrdt);
+    const double a = __dadd_rn(__dmul_rn(mine, p.rdt), Su);
+    const double q0 = __dmul_rn(acc, rV);
+    const double div = __fma_rn(__fma_rn(-q0, V, acc), rV, q0);
+    const double num = __dsub_rn(a, div);
+    const double r0 = __dmul_rn(num, p.rrdt);
+    const double res = __fma_rn(__fma_rn(-r0, p.rdt, num), p.rrdt, r0);
+    const unsigned h0 = (unsigned)__double2hiint(q0) & 0x7ff00000u, h1 = (unsigned)__double2hiint(r0) & 0x7ff00000u;
+    // exponents of both first guesses inside [2^-767, 2^768): otherwise (zero, subnormal, huge,
+    // non-finite) take the IEEE divisions
+    if (min(h0, h1) < 0x10000000u || max(h0, h1) > 0x6ff00000u)
+        return div_by(__dsub_rn(a, div_by(acc, V, rV)), p.rdt, p.rrdt);
+    return res;
 }
 
 template <int F>
@@ -144,39 +161,141 @@ __global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(Tran
     }
 }
 
-// boundary cells and cells with another face count: one thread per listed cell
+// The same sweep with the loads of the next PBE_TR_STAGES-1 fields in flight as asynchronous
+// global->shared copies (LDGSTS): every thread copies ITS OWN F + 2 values of a field into its own
+// column of a shared-memory stage and reads them back after cp.async.wait_group -- no data is
+// shared between threads, so no barrier is needed; the copies hold no registers while they are in
+// flight, which is what the register-staged loop above runs out of (ncu: 7.2 of 13.5 stall cycles
+// per issue are long-scoreboard waits).
+template <int F, int D>
+__global__ void __launch_bounds__(256) transport_upwind_async_kernel(TransportParams p) {
+    extern __shared__ double tr_sm[]; // [D][F + 2][256]
+    const int tid = threadIdx.x;
+    const int c = blockIdx.x * blockDim.x + tid;
+    if (c >= p.ncells) return;
+    int oth[F];
+    oth[0] = __ldg(p.other + c);
+    if (oth[0] < 0) return; // irregular cell
+    Side sd[F];
+#pragma unroll
+    for (int s = 0; s < F; ++s) {
+        if (s > 0) oth[s] = __ldg(p.other + (size_t)s * p.ncells + c);
+        sd[s] = make_side(__ldg(p.face + (size_t)s * p.ncells + c), p.phi);
+    }
+    const double V = __ldg(p.vcell + c);
+    const double rV = __ddiv_rn(1.0, V);
+    const int k0 = blockIdx.y * p.chunk;
+    const int nk = min(p.nfields, k0 + p.chunk) - k0;
+    const double *row = p.psi + (size_t)k0 * p.stride;       // row of the field being ISSUED
+    const double *srow = (p.S != nullptr) ? p.S + (size_t)k0 * p.stride : nullptr;
+    double *orow = p.out + (size_t)k0 * p.stride;
+    const uint32_t sm0 = (uint32_t)__cvta_generic_to_shared(tr_sm + tid);
+    constexpr uint32_t kStageBytes = (F + 2) * 256 * sizeof(double);
+    auto cp8 = [](uint32_t dst, const double *src) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+    };
+    auto issue = [&](int k) {
+        if (k < nk) {
+            const uint32_t d = sm0 + (uint32_t)(k % D) * kStageBytes;
+            cp8(d, row + c);
+#pragma unroll
+            for (int s = 0; s < F; ++s) cp8(d + (uint32_t)(1 + s) * 256u * 8u, row + oth[s]);
+            if (srow != nullptr) {
+                cp8(d + (uint32_t)(F + 1) * 256u * 8u, srow + c);
+                srow += p.stride;
+            }
+            row += p.stride;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int k = 0; k < D - 1; ++k) issue(k);
+    for (int k = 0; k < nk; ++k, orow += p.stride) {
+        issue(k + D - 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(D - 1) : "memory");
+        const double *st = tr_sm + (size_t)(k % D) * ((F + 2) * 256) + tid;
+        const double mine = st[0];
+        double acc = 0.0;
+#pragma unroll
+        for (int s = 0; s < F; ++s) acc = add_internal(acc, sd[s], mine, st[(1 + s) * 256]);
+        const double Su = (p.S != nullptr) ? st[(F + 1) * 256] : 0.0;
+        __stcs(orow + c, updated(p, mine, Su, acc, V, rV));
+    }
+}
+
+// boundary cells and cells with another face count: one thread per listed cell.  Up to kIrrRegs
+// faces are decoded once into registers (like the regular cells'), so a field costs independent
+// loads only; cells with more faces re-read their list per field.
+constexpr int kIrrRegs = 8;
+
+struct IrrFace {
+    int32_t oth; // >= 0 neighbour cell; -(b + 2) boundary face b; -1 unused
+    Side sd;     // internal: signed flux / lambda; boundary: phs = phi_b, lam = 1 if coupled
+};
+
+__device__ __forceinline__ IrrFace load_irr(const TransportParams &p, int e) {
+    IrrFace t;
+    t.oth = __ldg(p.irr_other + e);
+    const int face = __ldg(p.irr_face + e);
+    if (t.oth >= 0) {
+        t.sd = make_side(face, p.phi);
+    } else {
+        const int64_t b = -(int64_t)t.oth - 2;
+        t.sd.phs = __ldg(p.phi + face);
+        t.sd.lam = (b >= p.coupled0 && b < p.coupled0 + p.ncoupled) ? 1.0 : 0.0;
+    }
+    return t;
+}
+
+// address of the value across the face (own value for zero-gradient patches)
+__device__ __forceinline__ const double *irr_addr(const TransportParams &p, const IrrFace &t, const double *row,
+                                                  int k, int c) {
+    if (t.oth >= 0) return row + t.oth;
+    const int64_t b = -(int64_t)t.oth - 2;
+    if (t.sd.lam != 0.0) return p.psi_halo + (size_t)k * p.stride_h + (b - p.coupled0);
+    return (p.psi_b != nullptr) ? p.psi_b + (size_t)k * p.stride_b + b : row + c;
+}
+
+__device__ __forceinline__ double add_irr(double acc, const IrrFace &t, double mine, double theirs) {
+    if (t.oth >= 0) return add_internal(acc, t.sd, mine, theirs);
+    double pv = theirs; // patch value
+    if (t.sd.lam != 0.0) {  // processor patch: pLambda psi_own + (1 - pLambda) psi_across, pLambda = pos(phi_b)
+        const double w = t.sd.phs >= 0.0 ? 1.0 : 0.0;
+        pv = __dadd_rn(__dmul_rn(w, mine), __dmul_rn(__dsub_rn(1.0, w), theirs));
+    }
+    return __dadd_rn(acc, __dmul_rn(t.sd.phs, pv));
+}
+
 __global__ void __launch_bounds__(128) transport_upwind_irregular_kernel(TransportParams p) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.nirr) return;
     const int c = __ldg(p.irr_cell + i);
     const int e0 = __ldg(p.irr_ptr + i), e1 = __ldg(p.irr_ptr + i + 1);
+    const int ne = e1 - e0;
     const double V = __ldg(p.vcell + c);
     const double rV = __ddiv_rn(1.0, V);
     const int k0 = blockIdx.y * p.chunk;
     const int k1 = min(p.nfields, k0 + p.chunk);
+    IrrFace fc[kIrrRegs];
+#pragma unroll
+    for (int s = 0; s < kIrrRegs; ++s) {
+        fc[s].oth = -1;
+        fc[s].sd = Side{0.0, 0.0};
+        if (s < ne) fc[s] = load_irr(p, e0 + s);
+    }
     for (int k = k0; k < k1; ++k) {
         const double *row = p.psi + (size_t)k * p.stride;
         const double mine = __ldg(row + c);
+        double th[kIrrRegs];
+#pragma unroll
+        for (int s = 0; s < kIrrRegs; ++s) th[s] = (s < ne) ? __ldg(irr_addr(p, fc[s], row, k, c)) : 0.0;
         double acc = 0.0;
-        for (int e = e0; e < e1; ++e) {
-            const int oth = __ldg(p.irr_other + e);
-            const int face = __ldg(p.irr_face + e);
-            if (oth >= 0) {
-                acc = add_internal(acc, make_side(face, p.phi), mine, __ldg(row + oth));
-            } else { // boundary face: patch value (NULL psi_b = zero-gradient = the cell's own value)
-                const int64_t b = -(int64_t)oth - 2;
-                const double ph = __ldg(p.phi + face);
-                double pv;
-                if (b >= p.coupled0 && b < p.coupled0 + p.ncoupled) {
-                    // processor patch: pLambda psi_own + (1 - pLambda) psi_across, pLambda = pos(phi_b)
-                    const double w = ph >= 0.0 ? 1.0 : 0.0;
-                    const double across = __ldg(p.psi_halo + (size_t)k * p.stride_h + (b - p.coupled0));
-                    pv = __dadd_rn(__dmul_rn(w, mine), __dmul_rn(__dsub_rn(1.0, w), across));
-                } else {
-                    pv = (p.psi_b != nullptr) ? __ldg(p.psi_b + (size_t)k * p.stride_b + b) : mine;
-                }
-                acc = __dadd_rn(acc, __dmul_rn(ph, pv));
-            }
+#pragma unroll
+        for (int s = 0; s < kIrrRegs; ++s)
+            if (s < ne) acc = add_irr(acc, fc[s], mine, th[s]);
+        for (int e = e0 + kIrrRegs; e < e1; ++e) { // polyhedral cells with many faces
+            const IrrFace t = load_irr(p, e);
+            acc = add_irr(acc, t, mine, __ldg(irr_addr(p, t, row, k, c)));
         }
         const double Su = (p.S != nullptr) ? __ldg(p.S + (size_t)k * p.stride + c) : 0.0;
         p.out[(size_t)k * p.stride + c] = updated(p, mine, Su, acc, V, rV);
@@ -306,6 +425,9 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     upload(&m->d_irr_ptr, irr_ptr);
     upload(&m->d_irr_other, irr_other);
     upload(&m->d_irr_face, irr_face);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMalloc((void **)&m->d_vcell, (size_t)ncells * sizeof(double));
     if (e == cudaSuccess)
         e = cudaMemcpy(m->d_vcell, vcell, (size_t)ncells * sizeof(double), cudaMemcpyHostToDevice);
@@ -327,6 +449,9 @@ int pbe_mesh_destroy(pbe_mesh *m) {
     cudaFree(m->d_irr_ptr);
     cudaFree(m->d_irr_other);
     cudaFree(m->d_irr_face);
+    if (m->ev_fork) cudaEventDestroy(m->ev_fork);
+    if (m->ev_join) cudaEventDestroy(m->ev_join);
+    if (m->side) cudaStreamDestroy(m->side);
     delete m;
     return PBE_OK;
 }
@@ -418,27 +543,51 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
             chunk = (chunk + 1) / 2;
         return chunk;
     };
-    if (m->F > 0 && m->nirr < m->ncells) {
+    const bool have_regular = m->F > 0 && m->nirr < m->ncells;
+    if (m->nirr > 0) {
+        // beside the regular cells' kernel when there is one (few, latency-bound threads)
+        cudaStream_t is = have_regular ? m->side : st;
+        if (have_regular) {
+            PBE_CUDA(cudaEventRecord(m->ev_fork, st));
+            PBE_CUDA(cudaStreamWaitEvent(is, m->ev_fork, 0));
+        }
+        TransportParams q = p;
+        const int64_t blocks = (m->nirr + 127) / 128;
+        q.chunk = chunk_for(blocks, 10);
+        dim3 grid((unsigned)blocks, (unsigned)((nfields + q.chunk - 1) / q.chunk));
+        transport_upwind_irregular_kernel<<<grid, 128, 0, is>>>(q);
+        PBE_CUDA(cudaGetLastError());
+        ctx->launches++;
+        if (have_regular) PBE_CUDA(cudaEventRecord(m->ev_join, is));
+    }
+    if (have_regular) {
         int start = 25;
         if (const char *e = getenv("PBE_TRANSPORT_CHUNK")) start = std::max(1, atoi(e));
         const int64_t blocks = (m->ncells + 255) / 256;
         p.chunk = chunk_for(blocks, start);
         dim3 grid((unsigned)blocks, (unsigned)((nfields + p.chunk - 1) / p.chunk));
-        switch (m->F) {
-        case 4: transport_upwind_kernel<4><<<grid, 256, 0, st>>>(p); break;
-        case 5: transport_upwind_kernel<5><<<grid, 256, 0, st>>>(p); break;
-        default: transport_upwind_kernel<6><<<grid, 256, 0, st>>>(p); break;
-        }
-        PBE_CUDA(cudaGetLastError());
-        ctx->launches++;
+        static const int variant = getenv("PBE_TRANSPORT_KERNEL") ? atoi(getenv("PBE_TRANSPORT_KERNEL")) : PBE_TR_STAGES;
+        auto launch_async = [&](auto kern, int F, int D) {
+            const size_t smem = (size_t)D * (F + 2) * 256 * sizeof(double);
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            kern<<<grid, 256, smem, st>>>(p);
+        };
+#define PBE_TR_ASYNC(F)                                                                      \
+    switch (variant) {                                                                       \
+    case 2: launch_async(transport_upwind_async_kernel<F, 2>, F, 2); break;                  \
+    case 3: launch_async(transport_upwind_async_kernel<F, 3>, F, 3); break;                  \
+    case 4: launch_async(transport_upwind_async_kernel<F, 4>, F, 4); break;                  \
+    default: transport_upwind_kernel<F><<<grid, 256, 0, st>>>(p); break;                     \
     }
-    if (m->nirr > 0) {
-        const int64_t blocks = (m->nirr + 127) / 128;
-        p.chunk = chunk_for(blocks, 10);
-        dim3 grid((unsigned)blocks, (unsigned)((nfields + p.chunk - 1) / p.chunk));
-        transport_upwind_irregular_kernel<<<grid, 128, 0, st>>>(p);
+        switch (m->F) {
+        case 4: PBE_TR_ASYNC(4); break;
+        case 5: PBE_TR_ASYNC(5); break;
+        default: PBE_TR_ASYNC(6); break;
+        }
+#undef PBE_TR_ASYNC
         PBE_CUDA(cudaGetLastError());
         ctx->launches++;
+        if (m->nirr > 0) PBE_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
     }
     return PBE_OK;
 }
