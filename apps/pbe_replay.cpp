@@ -6,6 +6,8 @@
 //
 //   pbe_replay [--cells 4000000] [--steps 10] [--classes 50] [--order 3] [--device 0]
 //              [--dict file]        (a PBEDiameterCoeffs-style dictionary; default: the c01 case)
+//              [--mesh nx ny nz [--velocity u v w]]   hex block in OpenFOAM face addressing: MOC then runs
+//                                   MOC::solveWithMULES (source + explicit upwind transport, MOC.C:198-272)
 //
 // Prints one JSON line per method per step (wall ms with the diameter read-back, volume-averaged
 // / max / min diameter as printAvgMaxMin would, Utility.C:4-10) and a summary line per method.
@@ -100,6 +102,8 @@ int main(int argc, char **argv) {
     int64_t cells = 4000000;
     int steps = 10, classes = 50, order = 3, device = 0;
     std::string dictFile;
+    int meshN[3] = {0, 0, 0};
+    double vel[3] = {1.0, 0.5, 0.25};
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto val = [&]() -> const char * {
@@ -115,6 +119,11 @@ int main(int argc, char **argv) {
         else if (a == "--order") order = std::atoi(val());
         else if (a == "--device") device = std::atoi(val());
         else if (a == "--dict") dictFile = val();
+        else if (a == "--mesh") { // nx ny nz hex block: MOC runs solveWithMULES (transport + source)
+            for (int k = 0; k < 3; ++k) meshN[k] = std::atoi(val());
+            cells = (int64_t)meshN[0] * meshN[1] * meshN[2];
+        } else if (a == "--velocity")
+            for (int k = 0; k < 3; ++k) vel[k] = std::atof(val());
         else {
             std::fprintf(stderr, "unknown option %s\n", a.c_str());
             return 2;
@@ -145,6 +154,47 @@ int main(int argc, char **argv) {
         phase.V = V.data();
         phase.deltaT = 2.5e-4;
         phase.device = device;
+        // ---- optional hex block in OpenFOAM face addressing (blockMesh order: internal faces by
+        // owner then neighbour; patches x-, x+, y-, y+, z-, z+), unit cube, uniform velocity ----
+        pbe::FaceMesh fm;
+        std::vector<int32_t> own, nei, bown;
+        std::vector<double> phiF;
+        if (meshN[0] > 0) {
+            const int nx = meshN[0], ny = meshN[1], nz = meshN[2];
+            const double dx = 1.0 / nx, dy = 1.0 / ny, dz = 1.0 / nz;
+            std::fill(V.begin(), V.end(), dx * dy * dz);
+            for (int64_t c = 0; c < cells; ++c) alpha[c] *= 1e-9 / (dx * dy * dz); // n0 ~ alpha V as without a mesh
+            auto id = [&](int i, int j, int k) { return (int32_t)(i + (int64_t)nx * (j + (int64_t)ny * k)); };
+            for (int k = 0; k < nz; ++k)
+                for (int j = 0; j < ny; ++j)
+                    for (int i = 0; i < nx; ++i) {
+                        if (i + 1 < nx) own.push_back(id(i, j, k)), nei.push_back(id(i + 1, j, k)), phiF.push_back(vel[0] * dy * dz);
+                        if (j + 1 < ny) own.push_back(id(i, j, k)), nei.push_back(id(i, j + 1, k)), phiF.push_back(vel[1] * dx * dz);
+                        if (k + 1 < nz) own.push_back(id(i, j, k)), nei.push_back(id(i, j, k + 1)), phiF.push_back(vel[2] * dx * dy);
+                    }
+            auto patch = [&](int axis, int side) {
+                const int n[3] = {nx, ny, nz};
+                const double area[3] = {dy * dz, dx * dz, dx * dy};
+                int lo[3] = {0, 0, 0}, hi[3] = {nx, ny, nz};
+                lo[axis] = side ? n[axis] - 1 : 0;
+                hi[axis] = lo[axis] + 1;
+                for (int k = lo[2]; k < hi[2]; ++k)
+                    for (int j = lo[1]; j < hi[1]; ++j)
+                        for (int i = lo[0]; i < hi[0]; ++i) {
+                            bown.push_back(id(i, j, k));
+                            phiF.push_back((side ? 1.0 : -1.0) * vel[axis] * area[axis]);
+                        }
+            };
+            for (int axis = 0; axis < 3; ++axis) patch(axis, 0), patch(axis, 1);
+            fm.nInternalFaces = (int64_t)own.size();
+            fm.nBoundaryFaces = (int64_t)bown.size();
+            fm.owner = own.data(), fm.neighbour = nei.data(), fm.boundaryOwner = bown.data();
+            fm.phi = phiF.data();
+            phase.mesh = &fm;
+            // CFL 0.4 on the block
+            phase.deltaT = 0.4 / (std::fabs(vel[0]) * nx + std::fabs(vel[1]) * ny + std::fabs(vel[2]) * nz + 1e-300);
+            if (phase.deltaT > 2.5e-4) phase.deltaT = 2.5e-4;
+        }
 
         // QMOM starts from the moments of the MOC initial condition (same physical state in both
         // methods, as the reference's side-by-side validation cases do:
@@ -164,6 +214,7 @@ int main(int argc, char **argv) {
             dict.set("method", "methodOfClasses");
             const double xi1 = 3.5918876006043295e-12 * 50.0 / classes;
             dict.subDictOrAdd("MOCCoeffs").set("numberOfClasses", (double)classes).set("xi1", xi1);
+            if (phase.mesh) dict.subDictOrAdd("MOCCoeffs").set("usingMULES", std::string("true"));
             std::vector<double> p(classes), n0((size_t)classes * cells);
             double norm = 0;
             for (int i = 0; i < classes; ++i) {
@@ -198,7 +249,9 @@ int main(int argc, char **argv) {
             };
             rescale("CoulaloglouTavlaridesCCoeffs", 7.0 / 9.0, 4.0 / 3.0, 0.00487, 0.008);
             rescale("CoulaloglouTavlaridesCoeffs", -2.0 / 9.0, -5.0 / 9.0, 0.00487, 0.008);
-            pbe::PBEMethods::QMOM q(dict, phase, m0.data());
+            pbe::Phase qphase = phase;
+            qphase.mesh = nullptr; // moment transport (QMOM.C:131-197) is driven through the C ABI directly
+            pbe::PBEMethods::QMOM q(dict, qphase, m0.data());
             std::vector<double>().swap(m0);
             replay("quadratureMethodOfMoments", q, V, steps, cells, 1.0, "cell_updates_per_s", std::cbrt(volUnit));
             const auto a = q.avgMaxMin(0);

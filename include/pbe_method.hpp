@@ -196,6 +196,19 @@ struct Phase {
     const double *V = nullptr;       // mesh.V()
     double deltaT = 0.0;             // runTime.deltaT()
     int device = 0;                  // CUDA device the state lives on
+    const struct FaceMesh *mesh = nullptr; // fvMesh addressing + phase_.phi(): enables transport
+};
+
+// ---- stand-in for fvMesh's face addressing, phase_.phi() and fvSchemes' div(phi,n.*) entry ------------
+// (what MOC::solveWithMULES reads, MOC.C:198-272).  HOST arrays owned by the caller; phi is re-read
+// (uploaded) at every correct(), like the reference re-reads phase_.phi().
+struct FaceMesh {
+    int64_t nInternalFaces = 0, nBoundaryFaces = 0;
+    const int32_t *owner = nullptr, *neighbour = nullptr; // fvMesh::owner() / neighbour()
+    const int32_t *boundaryOwner = nullptr;               // faceCells of every patch, patch order
+    const double *phi = nullptr;                          // [nInternalFaces + nBoundaryFaces]
+    const double *boundaryValues = nullptr; // [fields][nBoundaryFaces] patch values, null = zeroGradient
+    std::string divScheme = "Gauss upwind"; // fvSchemes: "div\\(phi,n.*\\)"
 };
 
 // ---- RAII over the C-ABI context and device buffers -------------------------------------------------
@@ -359,8 +372,25 @@ public:
         d_host_.assign((size_t)nc, 0.0);
         if (nc) check(pbe_moc_d(h_, nc, nc, n_.data(), d_dev_.data(), nullptr), "MOC::MOC d");
         d_stale_ = true;
+        if (phase.mesh && nc) {
+            const FaceMesh &fm = *phase.mesh;
+            if (!usingMULES_)
+                throw FatalError("MOC: usingMULES false selects the implicit fvm::ddt + fvm::div solve "
+                                 "(MOC.C:186-198), which has no device path; set usingMULES true");
+            if (!phase.V) throw FatalError("MOC: transport needs the cell volumes (Phase::V)");
+            check(pbe_div_scheme_type(fm.divScheme.c_str(), &scheme_), "MOC::MOC div(phi,n.*)");
+            check(pbe_mesh_create(ctx_.get(), nc, fm.nInternalFaces, fm.owner, fm.neighbour, fm.nBoundaryFaces,
+                                  fm.boundaryOwner, phase.V, &mesh_),
+                  "MOC::MOC mesh");
+            const int64_t nf = fm.nInternalFaces + fm.nBoundaryFaces;
+            phi_ = DeviceArray(ctx_, std::max<int64_t>(nf, 1));
+            S_ = DeviceArray(ctx_, (int64_t)N_ * nc);
+            nNew_ = DeviceArray(ctx_, (int64_t)N_ * nc);
+            if (fm.boundaryValues) psiB_ = DeviceArray(ctx_, std::max<int64_t>((int64_t)N_ * fm.nBoundaryFaces, 1));
+        }
     }
     ~MOC() override {
+        if (mesh_) pbe_mesh_destroy(mesh_);
         if (h_) pbe_moc_destroy(h_);
     }
 
@@ -369,6 +399,10 @@ public:
     void correct() override {
         const int64_t nc = phase_.ncells;
         if (nc == 0) return;
+        if (mesh_) {
+            solveWithMULES();
+            return;
+        }
         pbe_moc_io io;
         std::memset(&io, 0, sizeof(io));
         io.d = d_dev_.data();
@@ -382,6 +416,29 @@ public:
         check(pbe_moc_step(h_, nc, nc, n_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, &io,
                            nullptr),
               "MOC::correct");
+        check(pbe_moc_class_minmax(h_, nc, nc, n_.data(), diag_.data(), diag_.data() + N_, nullptr),
+              "MOC::correct minmax");
+        d_stale_ = true;
+        diag_stale_ = true;
+    }
+    // MOC::solveWithMULES (MOC.C:198-272) for `Gauss upwind`: S_k of the current n, then
+    // n_k <- (n_k rDeltaT + S_k - div(phi n_k)) / rDeltaT on the device, d, per-class min / max.
+    // (The continuity print of MOC.C:276-279 is left to continuityError() of the zero-flux path.)
+    void solveWithMULES() {
+        const int64_t nc = phase_.ncells;
+        const FaceMesh &fm = *phase_.mesh;
+        const int64_t nf = fm.nInternalFaces + fm.nBoundaryFaces;
+        if (nf) phi_.upload(fm.phi, nf);
+        if (fm.boundaryValues && fm.nBoundaryFaces) psiB_.upload(fm.boundaryValues, (int64_t)N_ * fm.nBoundaryFaces);
+        check(pbe_moc_source(h_, nc, nc, n_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, S_.data(),
+                             nullptr),
+              "MOC::correct source");
+        check(pbe_transport_explicit(mesh_, scheme_, N_, nc, n_.data(), phi_.data(),
+                                     fm.boundaryValues ? psiB_.data() : nullptr, fm.nBoundaryFaces, S_.data(),
+                                     phase_.deltaT, nNew_.data(), nullptr),
+              "MOC::correct transport");
+        std::swap(n_, nNew_);
+        check(pbe_moc_d(h_, nc, nc, n_.data(), d_dev_.data(), nullptr), "MOC::correct d");
         check(pbe_moc_class_minmax(h_, nc, nc, n_.data(), diag_.data(), diag_.data() + N_, nullptr),
               "MOC::correct minmax");
         d_stale_ = true;
@@ -423,7 +480,9 @@ private:
     int N_ = 0;
     double xi1_ = 0, relax_ = 1.0;
     bool usingMULES_ = false;
-    DeviceArray n_, d_dev_, diag_;
+    pbe_mesh *mesh_ = nullptr;
+    int scheme_ = 0;
+    DeviceArray n_, d_dev_, diag_, phi_, S_, nNew_, psiB_;
     mutable std::vector<double> d_host_, diag_host_;
     mutable bool d_stale_ = true, diag_stale_ = true;
 };
