@@ -6,8 +6,9 @@
 //
 //   pbe_replay [--cells 4000000] [--steps 10] [--classes 50] [--order 3] [--device 0]
 //              [--dict file]        (a PBEDiameterCoeffs-style dictionary; default: the c01 case)
-//              [--mesh nx ny nz [--velocity u v w]]   hex block in OpenFOAM face addressing: MOC then runs
-//                                   MOC::solveWithMULES (source + explicit upwind transport, MOC.C:198-272)
+//              [--mesh nx ny nz [--velocity u v w]]   hex block in OpenFOAM face addressing: both methods then
+//                                   run solveWithMULES (source + explicit upwind transport, MOC.C:198-272,
+//                                   QMOM.C:131-197)
 //
 // Prints one JSON line per method per step (wall ms with the diameter read-back, volume-averaged
 // / max / min diameter as printAvgMaxMin would, Utility.C:4-10) and a summary line per method.
@@ -249,9 +250,8 @@ int main(int argc, char **argv) {
             };
             rescale("CoulaloglouTavlaridesCCoeffs", 7.0 / 9.0, 4.0 / 3.0, 0.00487, 0.008);
             rescale("CoulaloglouTavlaridesCoeffs", -2.0 / 9.0, -5.0 / 9.0, 0.00487, 0.008);
-            pbe::Phase qphase = phase;
-            qphase.mesh = nullptr; // moment transport (QMOM.C:131-197) is driven through the C ABI directly
-            pbe::PBEMethods::QMOM q(dict, qphase, m0.data());
+            if (phase.mesh) dict.subDictOrAdd("QMOMCoeffs").set("usingMULES", std::string("true"));
+            pbe::PBEMethods::QMOM q(dict, phase, m0.data());
             std::vector<double>().swap(m0);
             replay("quadratureMethodOfMoments", q, V, steps, cells, 1.0, "cell_updates_per_s", std::cbrt(volUnit));
             const auto a = q.avgMaxMin(0);

@@ -203,6 +203,14 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
                            int64_t stride_b, const double *S, double dt, double *psi_out,
                            void *cuda_stream);
 
+/* QMOM::correct() with transport (QMOM.C:85-129): pbe_qmom_source -> pbe_field_scrub_nan(S)
+ * (NaN -> 0, QMOM.C:101-107) -> pbe_transport_explicit on the 2*order moment fields
+ * (QMOM.C:131-197) -> pbe_qmom_clamp_d: m_k = max(m_k, SMALL = 1e-15) (QMOM.C:117-123) and
+ * d = (6/pi m1/m0)^(1/3) (QMOM.C:125; d may be NULL).  All pointers DEVICE. */
+int pbe_field_scrub_nan(pbe_ctx *ctx, int64_t count, double *f, void *cuda_stream);
+int pbe_qmom_clamp_d(pbe_ctx *ctx, int nmoments, int64_t ncells, int64_t stride, double *m, double *d,
+                     void *cuda_stream);
+
 /* Decomposed meshes (one sub-domain per GPU; cells block-partitioned as on the source path).
  * Boundary faces [first, first + count) of this sub-domain are processor-patch faces; the face
  * value there is OpenFOAM's coupled interpolation pos(phi_b) psi_own + (1 - pos(phi_b)) psi_across,

@@ -509,6 +509,21 @@ public:
             m_.upload(m0, (int64_t)2 * order_ * nc);
         else
             m_.zero();
+        if (phase.mesh && nc) {
+            const FaceMesh &fm = *phase.mesh;
+            if (!usingMULES_)
+                throw FatalError("QMOM: usingMULES false selects the implicit fvm::ddt + fvm::div solve "
+                                 "(QMOM.C:199-209), which has no device path; set usingMULES true");
+            if (!phase.V) throw FatalError("QMOM: transport needs the cell volumes (Phase::V)");
+            check(pbe_div_scheme_type(fm.divScheme.c_str(), &scheme_), "QMOM::QMOM div(phi,m.*)");
+            check(pbe_mesh_create(ctx_.get(), nc, fm.nInternalFaces, fm.owner, fm.neighbour, fm.nBoundaryFaces,
+                                  fm.boundaryOwner, phase.V, &mesh_),
+                  "QMOM::QMOM mesh");
+            phi_ = DeviceArray(ctx_, std::max<int64_t>(fm.nInternalFaces + fm.nBoundaryFaces, 1));
+            mNew_ = DeviceArray(ctx_, (int64_t)2 * order_ * nc);
+            if (fm.boundaryValues)
+                psiB_ = DeviceArray(ctx_, std::max<int64_t>((int64_t)2 * order_ * fm.nBoundaryFaces, 1));
+        }
         d_host_.assign((size_t)nc, 0.0);
         if (m0 && order_ >= 1) { // d_ = pow(6/pi m1/m0, 1/3) at construction, QMOM.C:81
             for (int64_t c2 = 0; c2 < nc; ++c2)
@@ -517,6 +532,7 @@ public:
         }
     }
     ~QMOM() override {
+        if (mesh_) pbe_mesh_destroy(mesh_);
         if (h_) pbe_qmom_destroy(h_);
     }
 
@@ -524,6 +540,24 @@ public:
     void correct() override {
         const int64_t nc = phase_.ncells;
         if (nc == 0) return;
+        if (mesh_) { // sources, NaN scrub, solveWithMULES (QMOM.C:131-197, Gauss upwind), clamp, d
+            const FaceMesh &fm = *phase_.mesh;
+            const int nm = 2 * order_;
+            const int64_t nf = fm.nInternalFaces + fm.nBoundaryFaces;
+            if (nf) phi_.upload(fm.phi, nf);
+            if (fm.boundaryValues && fm.nBoundaryFaces) psiB_.upload(fm.boundaryValues, (int64_t)nm * fm.nBoundaryFaces);
+            check(pbe_qmom_source(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), S_.data(), nullptr),
+                  "QMOM::correct source");
+            check(pbe_field_scrub_nan(ctx_.get(), (int64_t)nm * nc, S_.data(), nullptr), "QMOM::correct scrub");
+            check(pbe_transport_explicit(mesh_, scheme_, nm, nc, m_.data(), phi_.data(),
+                                         fm.boundaryValues ? psiB_.data() : nullptr, fm.nBoundaryFaces, S_.data(),
+                                         phase_.deltaT, mNew_.data(), nullptr),
+                  "QMOM::correct transport");
+            std::swap(m_, mNew_);
+            check(pbe_qmom_clamp_d(ctx_.get(), nm, nc, nc, m_.data(), d_dev_.data(), nullptr), "QMOM::correct clamp");
+            d_stale_ = true;
+            return;
+        }
         check(pbe_qmom_step(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, S_.data(),
                             d_dev_.data(), nullptr),
               "QMOM::correct");
@@ -563,7 +597,9 @@ private:
     pbe_qmom *h_ = nullptr;
     int order_ = 0;
     bool usingMULES_ = false;
-    DeviceArray m_, S_, d_dev_, diag_;
+    pbe_mesh *mesh_ = nullptr;
+    int scheme_ = 0;
+    DeviceArray m_, S_, d_dev_, diag_, phi_, mNew_, psiB_;
     mutable std::vector<double> d_host_;
     mutable bool d_stale_ = true;
 };

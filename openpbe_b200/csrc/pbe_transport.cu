@@ -312,6 +312,31 @@ __global__ void __launch_bounds__(256) gather_cells_kernel(int nfields, int64_t 
     for (int k = blockIdx.y; k < nfields; k += gridDim.y) out[(size_t)k * stride_out + j] = __ldg(psi + (size_t)k * stride + c);
 }
 
+// QMOM::correct()'s steps either side of the moment transport (QMOM.C:98-128)
+__global__ void __launch_bounds__(256) scrub_nan_kernel(int64_t count, double *f) {
+    const int64_t n = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += n) {
+        const double v = f[i];
+        if (v != v) f[i] = 0.0; // QMOM.C:101-107
+    }
+}
+
+__global__ void __launch_bounds__(256) clamp_d_kernel(int nmoments, int64_t ncells, int64_t stride, double *m,
+                                                      double *d) {
+    const int64_t n = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < ncells; c += n) {
+        double m0 = 0.0, m1 = 0.0;
+        for (int k = 0; k < nmoments; ++k) {
+            double v = m[(size_t)k * stride + c];
+            // max(moment, SMALL), QMOM.C:117-123; written like the fused step's clamp (NaN -> SMALL)
+            if (!(v > 1.0e-15)) m[(size_t)k * stride + c] = v = 1.0e-15;
+            if (k == 0) m0 = v;
+            if (k == 1) m1 = v;
+        }
+        if (d != nullptr && nmoments >= 2) d[c] = cbrt(6.0 / 3.14159265358979323846 * m1 / m0); // QMOM.C:125
+    }
+}
+
 } // namespace pbe
 
 using namespace pbe;
@@ -492,6 +517,32 @@ int pbe_gather_cells(pbe_ctx *ctx, int nfields, int64_t stride, const double *ps
     DeviceGuard g(ctx->device);
     dim3 grid((unsigned)((n + 255) / 256), (unsigned)std::min(nfields, 64));
     gather_cells_kernel<<<grid, 256, 0, (cudaStream_t)cuda_stream>>>(nfields, stride, psi, n, cells, out, stride_out);
+    PBE_CUDA(cudaGetLastError());
+    ctx->launches++;
+    return PBE_OK;
+}
+
+int pbe_field_scrub_nan(pbe_ctx *ctx, int64_t count, double *f, void *cuda_stream) {
+    PBE_REQUIRE(ctx != nullptr && count >= 0, PBE_E_INVALID, "pbe_field_scrub_nan: bad argument");
+    if (count == 0) return PBE_OK;
+    PBE_REQUIRE(f != nullptr, PBE_E_INVALID, "pbe_field_scrub_nan: NULL field");
+    DeviceGuard g(ctx->device);
+    const int grid = (int)std::min<int64_t>((count + 255) / 256, (int64_t)ctx->sm_count * 16);
+    scrub_nan_kernel<<<grid, 256, 0, (cudaStream_t)cuda_stream>>>(count, f);
+    PBE_CUDA(cudaGetLastError());
+    ctx->launches++;
+    return PBE_OK;
+}
+
+int pbe_qmom_clamp_d(pbe_ctx *ctx, int nmoments, int64_t ncells, int64_t stride, double *m, double *d,
+                     void *cuda_stream) {
+    PBE_REQUIRE(ctx != nullptr && nmoments >= 0 && ncells >= 0 && stride >= ncells, PBE_E_INVALID,
+                "pbe_qmom_clamp_d: bad argument");
+    if (nmoments == 0 || ncells == 0) return PBE_OK;
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_qmom_clamp_d: NULL moments");
+    DeviceGuard g(ctx->device);
+    const int grid = (int)std::min<int64_t>((ncells + 255) / 256, (int64_t)ctx->sm_count * 16);
+    clamp_d_kernel<<<grid, 256, 0, (cudaStream_t)cuda_stream>>>(nmoments, ncells, stride, m, d);
     PBE_CUDA(cudaGetLastError());
     ctx->launches++;
     return PBE_OK;

@@ -171,6 +171,19 @@ class Context:
                                                 _ptr(m), _ptr(x), _ptr(w), _stream_ptr(m.device)))
         return x, w
 
+    def scrub_nan(self, f: torch.Tensor):
+        """NaN -> 0 in place (QMOM.C:101-107)."""
+        capi.check(capi.lib().pbe_field_scrub_nan(self.handle, f.numel(), _ptr(f), _stream_ptr(f.device)))
+        return f
+
+    def qmom_clamp_d(self, m: torch.Tensor, want_d: bool = True):
+        """m_k = max(m_k, SMALL) in place and d = (6/pi m1/m0)^(1/3) (QMOM.C:117-125)."""
+        K, ncells = m.shape
+        d = torch.empty(ncells, dtype=torch.float64, device=m.device) if want_d else None
+        capi.check(capi.lib().pbe_qmom_clamp_d(self.handle, K, ncells, m.stride(0) if ncells else 0, _ptr(m),
+                                               _ptr(d), _stream_ptr(m.device)))
+        return d
+
     def field_avg_max_min(self, f: torch.Tensor, vcell: Optional[torch.Tensor] = None):
         out = torch.empty(4, dtype=torch.float64, device=f.device)
         capi.check(capi.lib().pbe_field_avg_max_min(self._h, f.numel(), _ptr(f), _ptr(vcell),

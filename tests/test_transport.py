@@ -304,3 +304,39 @@ def test_device_decomposed_matches_oracle(ctx, world):
         got = mesh.transport_explicit(loc, T(p["phi"]), 0.01, psi_b=T(pb), S=T(S[:, lo:hi]),
                                       psi_halo=T(psi[:, p["halo_cells_global"]]))
         np.testing.assert_array_equal(got.cpu().numpy(), want[:, lo:hi])
+
+
+@gpu
+def test_qmom_correct_with_transport_sequence(ctx):
+    """QMOM::correct() with mesh transport (QMOM.C:85-129, 131-197): sources -> NaN scrub ->
+    explicit upwind transport of the 2*order moments -> clamp to SMALL -> d, each device step
+    against its restatement."""
+    import torch
+    from openpbe_b200 import engine
+    wq = synthetic.workload("qmom3_ct", 12 * 10 * 8)
+    fq = synthetic.qmom_fields(wq)
+    tm = synthetic.block_mesh(12, 10, 8, velocity=(1.0, -0.5, 0.25))
+    dev = torch.device("cuda:0")
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    q = engine.QMOM(ctx, wq.N, engine.make_spec(wq.coalescence, wq.coal_coeffs, wq.breakup, wq.br_coeffs))
+    m = T(fq["m"])
+    S = q.source(m, T(fq["eps"]), T(fq["rho"]), T(fq["nu"]))
+    S_raw = S.cpu().numpy().copy()
+    S_raw[0, 3] = np.nan  # at least one NaN to scrub, whatever the synthetic cells give
+    S = T(S_raw)
+    ctx.scrub_nan(S)
+    S_scrubbed = np.where(np.isnan(S_raw), 0.0, S_raw)
+    np.testing.assert_array_equal(S.cpu().numpy(), S_scrubbed)
+    mesh = engine.Mesh(ctx, tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"])
+    dt = 1e-3
+    m_new = mesh.transport_explicit(m, T(tm["phi"]), dt, S=S)
+    want = orc.transport_upwind_explicit(tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"], fq["m"],
+                                         tm["phi"], dt, S=S_scrubbed)
+    np.testing.assert_array_equal(m_new.cpu().numpy(), want)
+    m_new[2, 7] = -1.0  # something to clamp
+    m_new[3, 9] = float("nan")
+    d = ctx.qmom_clamp_d(m_new)
+    want[2, 7] = -1.0; want[3, 9] = np.nan
+    clamped = np.where(want > 1e-15, want, 1e-15)
+    np.testing.assert_array_equal(m_new.cpu().numpy(), clamped)
+    np.testing.assert_allclose(d.cpu().numpy(), np.cbrt(6.0 / np.pi * clamped[1] / clamped[0]), rtol=4e-16)
