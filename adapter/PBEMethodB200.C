@@ -99,7 +99,7 @@ static inline std::string fieldName(const char *stem, label i) {
 MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     : PBEMethod(pbeProperties, phase), runTime(phase.mesh().time()), deltaXi_("deltaXi", 0.0),
       numberOfClasses_(0), usingMULES_(false), source_term_relaxation_(1.0), moc_(nullptr), nHost_(nullptr),
-      SHost_(nullptr), continuityError_(0.0) {
+      SHost_(nullptr), continuityError_(0.0), b200Mesh_(nullptr), divScheme_(PBE_DIV_UPWIND) {
     const dictionary &MOCDict_ = pbeProperties.subDict("MOCCoeffs"); // MOC.C:51-60
     numberOfClasses_ = readLabel(MOCDict_.lookup("numberOfClasses"));
     deltaXi_ = dimensionedScalar("deltaXi", readScalar(MOCDict_.lookup("xi1")));
@@ -114,11 +114,25 @@ MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     const int64_t bytes = (int64_t)sizeof(double) * numberOfClasses_ * phase.size();
     b200Check(pbe_host_alloc(ctx_, bytes, (void **)&nHost_), "MOC::MOC");
     b200Check(pbe_host_alloc(ctx_, bytes, (void **)&SHost_), "MOC::MOC");
+    const fvMesh &mesh = phase.mesh();
+    if (mesh.hasFaces() && usingMULES_) {
+        // fvSchemes divSchemes "div\\(phi,n.*\\)" (the shim reads it from MOCCoeffs); a scheme without a
+        // device path is a FatalError listing the valid ones, like any other run-time selection
+        const word scheme = MOCDict_.lookupOrDefault<word>("divScheme", "Gauss upwind");
+        b200Check(pbe_div_scheme_type(scheme.c_str(), &divScheme_), "MOC::MOC div(phi,n.*)");
+        std::vector<int32_t> own(mesh.owner().begin(), mesh.owner().end()),
+            nei(mesh.neighbour().begin(), mesh.neighbour().end()),
+            bfc(mesh.boundaryFaceCells_.begin(), mesh.boundaryFaceCells_.end());
+        b200Check(pbe_mesh_create(ctx_, mesh.nCells(), mesh.nInternalFaces(), own.data(), nei.data(),
+                                  (int64_t)bfc.size(), bfc.data(), mesh.V().cdata(), &b200Mesh_),
+                  "MOC::MOC mesh");
+    }
 }
 
 MOC::~MOC() {
     if (nHost_) pbe_host_free(ctx_, nHost_);
     if (SHost_) pbe_host_free(ctx_, SHost_);
+    if (b200Mesh_) pbe_mesh_destroy(b200Mesh_);
     if (moc_) pbe_moc_destroy(moc_);
 }
 
@@ -131,6 +145,10 @@ void MOC::correct() {
         std::memcpy(nHost_ + (size_t)k * nCells, classNumberDensity_[k].internalField().cdata(),
                     sizeof(double) * nCells);
     updatePhaseFields();
+    if (b200Mesh_) {
+        correctWithTransport();
+        return;
+    }
     b200Check(pbe_moc_source_host(moc_, nCells, nCells, nHost_, epsilonData(), rhoHost_.cdata(), nuHost_.cdata(),
                                   runTime.deltaT().value(), SHost_),
               "MOC::correct");
@@ -146,6 +164,42 @@ void MOC::correct() {
         const scalarField &f = classNumberDensity_[k].internalField();
         forAll(f, c) mn = f[c] < mn ? f[c] : mn;
         if (k == 0 || k == numberOfClasses_ - 1) Info << "min(n" << k << ") " << mn << endl; // MOC.C:181-183
+    }
+}
+
+// MOC::correct() with solveWithMULES (MOC.C:198-272) and `Gauss upwind`: one call; the class fields
+// travel to the device once, sources and the transport update run there, the new fields come back.
+void MOC::correctWithTransport() {
+    const label nCells = phase_.size();
+    b200Check(pbe_moc_correct_host(moc_, b200Mesh_, divScheme_, nCells, nHost_, epsilonData(), rhoHost_.cdata(),
+                                   nuHost_.cdata(), phase_.phi().cdata(), nullptr /* zeroGradient patches */, 0,
+                                   runTime.deltaT().value(), nullptr),
+              "MOC::correct");
+    forAll(classNumberDensity_, k)
+        std::memcpy(classNumberDensity_[k].internalField().data_ptr(), nHost_ + (size_t)k * nCells,
+                    sizeof(double) * nCells);
+    continuityCheck();
+    forAll(classNumberDensity_, k) {
+        scalar mn = HUGE_VAL;
+        const scalarField &f = classNumberDensity_[k].internalField();
+        forAll(f, c) mn = f[c] < mn ? f[c] : mn;
+        if (k == 0 || k == numberOfClasses_ - 1) Info << "min(n" << k << ") " << mn << endl; // MOC.C:181-183
+    }
+}
+
+void MOC::continuityCheck() { // MOC.C:254-279: max |sum_k xi_k n_k / V - alpha|
+    const label nCells = phase_.size();
+    scalarField volumeSum(nCells, 0.0);
+    forAll(classNumberDensity_, k) {
+        const scalarField &n = classNumberDensity_[k].internalField();
+        const scalar xi = deltaXi_.value() * (k + 1);
+        forAll(n, c) volumeSum[c] += xi * n[c];
+    }
+    continuityError_ = 0.0;
+    const scalarField &V = phase_.mesh().V();
+    forAll(volumeSum, c) {
+        const scalar e = std::fabs(volumeSum[c] / V[c] - phase_[c]);
+        continuityError_ = e > continuityError_ ? e : continuityError_;
     }
 }
 

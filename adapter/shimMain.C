@@ -4,7 +4,9 @@
 // Fields come from a raw FP64 file so that tests/test_adapter_shim.py can compare the result with
 // the oracle.  Shim build only (adapter/foam_shim): test infrastructure, not the product.
 //
-//   shimMain <dict file> <input.bin> <output.bin> <steps>
+//   shimMain <dict file> <input.bin> <output.bin> <steps> [mesh.bin]
+//   mesh  : [nInternal, nBoundary] (FP64), owner[nInternal], neighbour[nInternal], faceCells[nBoundary]
+//           (int32), phi[nInternal + nBoundary] (FP64): face addressing and the phase's face flux
 //   input : [K, nCells, dt, cellVolume] then state[K][nCells], epsilon, rho, nu, alpha [nCells] each
 //           (K = numberOfClasses for methodOfClasses, 2 quadratureOrder for QMOM)
 //   output: state[K][nCells], d[nCells], continuity error (MOC; 0 for QMOM)
@@ -37,6 +39,20 @@ int main(int argc, char **argv) {
 
         Time runTime(hdr[2]);
         fvMesh mesh(runTime, nCells, hdr[3]);
+        if (argc > 5) {
+            std::FILE *mf = std::fopen(argv[5], "rb");
+            double mh[2];
+            if (!mf || std::fread(mh, 8, 2, mf) != 2) return 3;
+            const size_t ni = (size_t)mh[0], nb = (size_t)mh[1];
+            std::vector<int32_t> own(ni), nei(ni), bfc(nb);
+            bool mok = std::fread(own.data(), 4, ni, mf) == ni && std::fread(nei.data(), 4, ni, mf) == ni &&
+                       std::fread(bfc.data(), 4, nb, mf) == nb;
+            mesh.setFaces(std::vector<label>(own.begin(), own.end()), std::vector<label>(nei.begin(), nei.end()),
+                          std::vector<label>(bfc.begin(), bfc.end()));
+            mok = mok && std::fread(mesh.phi_.data_ptr(), 8, ni + nb, mf) == ni + nb;
+            std::fclose(mf);
+            if (!mok) return 3;
+        }
         phaseModel phase(mesh, "air", 0.0, 0.0, 0.0);
         volScalarField epsilon("epsilon." + phase.name(), mesh);
         for (label c = 0; c < nCells; ++c) {

@@ -203,6 +203,19 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
                            int64_t stride_b, const double *S, double dt, double *psi_out,
                            void *cuda_stream);
 
+/* HOST-buffer MOC::correct() with solveWithMULES (MOC.C:159-184, 198-272): what the OpenFOAM-side
+ * adapter calls when the case's div(phi,n.*) scheme is on the device.  n_host [N][stride] is
+ * updated in place (N = the method's numberOfClasses, ncells = the mesh's); phi_host
+ * [internal + boundary faces]; psi_b_host [N][stride_b] patch values or NULL (zero-gradient);
+ * d_host [ncells] receives MOC::d() of the new fields or is NULL.  Uploads overlap the source
+ * kernel (cell chunks), downloads overlap the transport kernels (field chunks); the fields stay
+ * on the device in between.  Synchronous on return. */
+int pbe_moc_num_classes(pbe_moc *moc, int *N, pbe_ctx **ctx);
+int pbe_moc_correct_host(pbe_moc *moc, pbe_mesh *mesh, int scheme, int64_t stride, double *n_host,
+                         const double *eps_host, const double *rho_host, const double *nu_host,
+                         const double *phi_host, const double *psi_b_host, int64_t stride_b,
+                         double dt, double *d_host);
+
 /* QMOM::correct() with transport (QMOM.C:85-129): pbe_qmom_source -> pbe_field_scrub_nan(S)
  * (NaN -> 0, QMOM.C:101-107) -> pbe_transport_explicit on the 2*order moment fields
  * (QMOM.C:131-197) -> pbe_qmom_clamp_d: m_k = max(m_k, SMALL = 1e-15) (QMOM.C:117-123) and

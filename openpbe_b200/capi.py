@@ -98,6 +98,9 @@ PROTOTYPES = {
     "pbe_div_scheme_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
     "pbe_transport_explicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
                                          C.c_double, _vp, _vp]),
+    "pbe_moc_num_classes": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(_vp)]),
+    "pbe_moc_correct_host": (C.c_int, [_vp, _vp, C.c_int, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64,
+                                       C.c_double, _vp]),
     "pbe_field_scrub_nan": (C.c_int, [_vp, _i64, _vp, _vp]),
     "pbe_qmom_clamp_d": (C.c_int, [_vp, C.c_int, _i64, _i64, _vp, _vp, _vp]),
     "pbe_mesh_set_coupled": (C.c_int, [_vp, _i64, _i64]),

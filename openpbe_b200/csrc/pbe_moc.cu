@@ -500,6 +500,13 @@ int pbe_moc_get_kernel(pbe_moc *m, int *which, int *cells_per_cta, int *ctas_per
     return PBE_OK;
 }
 
+int pbe_moc_num_classes(pbe_moc *m, int *N, pbe_ctx **ctx) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_num_classes: NULL handle");
+    if (N) *N = m->N;
+    if (ctx) *ctx = m->ctx;
+    return PBE_OK;
+}
+
 int pbe_moc_destroy(pbe_moc *m) {
     if (!m) return PBE_OK;
     DeviceGuard g(m->ctx->device);

@@ -54,6 +54,9 @@ struct pbe_mesh {
     // the irregular cells' kernel runs beside the regular cells' one (disjoint outputs): fork / join
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // resident fields of the host-buffer entry (pbe_moc_correct_host), grown on demand
+    double *res = nullptr;
+    size_t res_doubles = 0;
 };
 
 namespace pbe {
@@ -474,6 +477,7 @@ int pbe_mesh_destroy(pbe_mesh *m) {
     cudaFree(m->d_irr_ptr);
     cudaFree(m->d_irr_other);
     cudaFree(m->d_irr_face);
+    cudaFree(m->res);
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);
     if (m->side) cudaStreamDestroy(m->side);
@@ -639,6 +643,87 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
         PBE_CUDA(cudaGetLastError());
         ctx->launches++;
         if (m->nirr > 0) PBE_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
+    }
+    return PBE_OK;
+}
+
+// MOC::correct() with solveWithMULES, host buffers in and out: what the OpenFOAM-side adapter
+// calls.  The class fields are uploaded in cell chunks and the source kernel runs on each chunk as
+// it arrives (three streams: copies overlap kernels); n and S stay on the device; the transport
+// update then runs in field chunks, each chunk's new values copied back while the next chunk is
+// being computed.
+int pbe_moc_correct_host(pbe_moc *moc, pbe_mesh *m, int scheme, int64_t stride, double *n_host,
+                         const double *eps_host, const double *rho_host, const double *nu_host,
+                         const double *phi_host, const double *psi_b_host, int64_t stride_b, double dt,
+                         double *d_host) {
+    PBE_REQUIRE(moc != nullptr && m != nullptr, PBE_E_INVALID, "pbe_moc_correct_host: NULL handle");
+    int N = 0;
+    pbe_ctx *mctx = nullptr;
+    int rc = pbe_moc_num_classes(moc, &N, &mctx);
+    if (rc) return rc;
+    pbe_ctx *ctx = m->ctx;
+    PBE_REQUIRE(mctx == ctx, PBE_E_INVALID, "pbe_moc_correct_host: method and mesh belong to different contexts");
+    PBE_REQUIRE(m->ncoupled == 0, PBE_E_UNSUPPORTED,
+                "pbe_moc_correct_host: decomposed meshes go through pbe_transport_explicit_halo");
+    const int64_t nc = m->ncells, nf = m->nint + m->nbnd;
+    PBE_REQUIRE(stride >= nc && n_host && eps_host && rho_host && nu_host && (phi_host || nf == 0) && dt > 0.0,
+                PBE_E_INVALID, "pbe_moc_correct_host: bad argument");
+    PBE_REQUIRE(psi_b_host == nullptr || stride_b >= m->nbnd, PBE_E_INVALID,
+                "pbe_moc_correct_host: stride_b < boundary faces");
+    DeviceGuard g(ctx->device);
+    const size_t field = (size_t)N * nc;
+    const size_t nb = psi_b_host ? (size_t)N * m->nbnd : 0;
+    const size_t need = 3 * field + 4 * (size_t)nc + (size_t)nf + nb;
+    if (m->res_doubles < need) {
+        cudaFree(m->res);
+        m->res = nullptr;
+        m->res_doubles = 0;
+        PBE_CUDA(cudaMalloc((void **)&m->res, need * sizeof(double)));
+        m->res_doubles = need;
+    }
+    double *dn = m->res, *dS = dn + field, *dnew = dS + field, *de = dnew + field, *dr = de + nc, *dv = dr + nc,
+           *dd = dv + nc, *dphi = dd + nc, *dpb = dphi + nf;
+    // ---- upload + sources, cell chunks ----------------------------------------------------------
+    int block = 128, ctas = 1;
+    pbe_moc_get_kernel(moc, nullptr, &block, &ctas);
+    const int64_t wave = (int64_t)block * ctx->sm_count * ctas;
+    int64_t C = std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)N * 8) / wave) * wave;
+    int64_t k = 0;
+    for (int64_t c0 = 0; c0 < nc; c0 += C, ++k) {
+        const int64_t cn = std::min(C, nc - c0);
+        cudaStream_t st = ctx->slot_stream[k % kHostSlots];
+        PBE_CUDA(cudaMemcpy2DAsync(dn + c0, (size_t)nc * 8, n_host + c0, (size_t)stride * 8, (size_t)cn * 8, N,
+                                   cudaMemcpyHostToDevice, st));
+        PBE_CUDA(cudaMemcpyAsync(de + c0, eps_host + c0, (size_t)cn * 8, cudaMemcpyHostToDevice, st));
+        PBE_CUDA(cudaMemcpyAsync(dr + c0, rho_host + c0, (size_t)cn * 8, cudaMemcpyHostToDevice, st));
+        PBE_CUDA(cudaMemcpyAsync(dv + c0, nu_host + c0, (size_t)cn * 8, cudaMemcpyHostToDevice, st));
+        rc = pbe_moc_source(moc, cn, nc, dn + c0, de + c0, dr + c0, dv + c0, dt, dS + c0, st);
+        if (rc) return rc;
+    }
+    if (nf) PBE_CUDA(cudaMemcpyAsync(dphi, phi_host, (size_t)nf * 8, cudaMemcpyHostToDevice, ctx->slot_stream[0]));
+    if (nb)
+        PBE_CUDA(cudaMemcpy2DAsync(dpb, (size_t)m->nbnd * 8, psi_b_host, (size_t)stride_b * 8, (size_t)m->nbnd * 8, N,
+                                   cudaMemcpyHostToDevice, ctx->slot_stream[0]));
+    for (int s = 0; s < kHostSlots; ++s) PBE_CUDA(cudaStreamSynchronize(ctx->slot_stream[s]));
+    // ---- transport + download, field chunks -----------------------------------------------------
+    const int KC = std::max(1, std::min(N, (int)(((int64_t)256 << 20) / (nc * 8) + 1)));
+    k = 0;
+    for (int k0 = 0; k0 < N; k0 += KC, ++k) {
+        const int kn = std::min(KC, N - k0);
+        cudaStream_t st = ctx->slot_stream[k % kHostSlots];
+        rc = pbe_transport_explicit(m, scheme, kn, nc, dn + (size_t)k0 * nc, dphi,
+                                    nb ? dpb + (size_t)k0 * m->nbnd : nullptr, m->nbnd, dS + (size_t)k0 * nc, dt,
+                                    dnew + (size_t)k0 * nc, st);
+        if (rc) return rc;
+        PBE_CUDA(cudaMemcpy2DAsync(n_host + (size_t)k0 * stride, (size_t)stride * 8, dnew + (size_t)k0 * nc,
+                                   (size_t)nc * 8, (size_t)nc * 8, kn, cudaMemcpyDeviceToHost, st));
+    }
+    for (int s = 0; s < kHostSlots; ++s) PBE_CUDA(cudaStreamSynchronize(ctx->slot_stream[s]));
+    if (d_host != nullptr) { // MOC::d(), MOC.C:282-290, of the updated fields
+        rc = pbe_moc_d(moc, nc, nc, dnew, dd, ctx->slot_stream[0]);
+        if (rc) return rc;
+        PBE_CUDA(cudaMemcpyAsync(d_host, dd, (size_t)nc * 8, cudaMemcpyDeviceToHost, ctx->slot_stream[0]));
+        PBE_CUDA(cudaStreamSynchronize(ctx->slot_stream[0]));
     }
     return PBE_OK;
 }

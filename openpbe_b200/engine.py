@@ -378,6 +378,18 @@ class Mesh:
                 "max_faces_per_cell": d.value, "faces_per_regular_cell": F.value,
                 "regular_cells": nreg.value}
 
+    def moc_correct_host(self, moc: "MOC", n, eps, rho, nu, phi, dt, *, psi_b=None, want_d=True,
+                         scheme="upwind"):
+        """Host-buffer MOC::correct() with solveWithMULES: n [N][ncells] (CPU tensor / numpy) is
+        updated in place; returns d (CPU tensor) or None."""
+        n_, eps_, rho_, nu_, phi_ = (_as_host(v) for v in (n, eps, rho, nu, phi))
+        pb = None if psi_b is None else _as_host(psi_b)
+        d = torch.empty(n_.shape[1], dtype=torch.float64) if want_d else None
+        capi.check(capi.lib().pbe_moc_correct_host(
+            moc._h, self._h, div_scheme(scheme), n_.stride(0), _ptr(n_), _ptr(eps_), _ptr(rho_), _ptr(nu_),
+            _ptr(phi_), _ptr(pb), 0 if pb is None else pb.stride(0), float(dt), _ptr(d)))
+        return d
+
     def set_coupled(self, first_boundary_face: int, count: int):
         """Mark boundary faces [first, first+count) as processor-patch faces (decomposed mesh)."""
         capi.check(capi.lib().pbe_mesh_set_coupled(self._h, int(first_boundary_face), int(count)))

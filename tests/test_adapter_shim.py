@@ -114,3 +114,46 @@ def test_qmom_correct_matches_oracle(shim, tmp_path, oracle):
     assert np.all(np.abs(m - m_o)[:, well] <= dt * 1e-9 * scale[:, well] + 4e-16 * np.abs(m_o[:, well]))
     np.testing.assert_allclose(d[well], d_o[well], rtol=1e-9)
     assert np.all(m >= 1e-15)
+
+
+def _write_mesh(path, m):
+    with open(path, "wb") as fh:
+        np.array([m["owner"].size, m["boundary_owner"].size], dtype=np.float64).tofile(fh)
+        for k in ("owner", "neighbour", "boundary_owner"):
+            m[k].astype(np.int32).tofile(fh)
+        m["phi"].astype(np.float64).tofile(fh)
+
+
+@pytest.mark.gpu
+def test_moc_correct_with_transport_matches_oracle(shim, tmp_path, oracle):
+    """MOC::correct() with solveWithMULES (MOC.C:198-272, Gauss upwind) through the adapter: sources
+    and the explicit transport update on the device, against oracle sources + the face-loop oracle."""
+    tm = synthetic.block_mesh(14, 11, 9, velocity=(1.0, -0.5, 0.25))
+    nc = 14 * 11 * 9
+    w = synthetic.workload("moc30_ct", nc)
+    f = synthetic.moc_fields(w)
+    vcell = float(tm["vcell"][0])
+    text = ("method methodOfClasses; MOCCoeffs { numberOfClasses %d; xi1 %r; usingMULES on; divScheme Gauss upwind; }"
+            % (w.N, w.xi1) + C01 % (tuple(w.coal_coeffs) + tuple(w.br_coeffs)))
+    K = w.N
+    (tmp_path / "dict").write_text(text)
+    np.concatenate([[K, nc, w.dt, vcell], f["n"].ravel(), f["eps"], f["rho"], f["nu"], f["alpha"]]).tofile(tmp_path / "in.bin")
+    _write_mesh(tmp_path / "mesh.bin", tm)
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "2",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout + p.stderr
+    r = np.fromfile(tmp_path / "out.bin")
+    n, d = r[:K * nc].reshape(K, nc), r[K * nc:K * nc + nc]
+    sp = oracle.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+    n_o = f["n"].copy()
+    for _ in range(2):
+        S, scale = oracle.moc_source(sp, w.N, w.xi1, w.relax, n_o, f["eps"], f["rho"], f["nu"], w.dt)
+        n_o = oracle.transport_upwind_explicit(tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"], n_o,
+                                               tm["phi"], w.dt, S=S)
+    assert np.all(np.abs(n - n_o) <= 4 * w.dt * 1e-12 * scale + 1e-14 * np.abs(n_o))
+    np.testing.assert_allclose(d, oracle.moc_d(n_o, w.xi1), rtol=1e-12)
+    # a scheme without a device path is a FatalError that lists the valid ones
+    (tmp_path / "dict").write_text(text.replace("Gauss upwind", "Gauss vanLeer"))
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 1 and "vanLeer" in p.stdout and "Valid schemes are" in p.stdout and "FOAM exiting" in p.stdout

@@ -340,3 +340,35 @@ def test_qmom_correct_with_transport_sequence(ctx):
     clamped = np.where(want > 1e-15, want, 1e-15)
     np.testing.assert_array_equal(m_new.cpu().numpy(), clamped)
     np.testing.assert_allclose(d.cpu().numpy(), np.cbrt(6.0 / np.pi * clamped[1] / clamped[0]), rtol=4e-16)
+
+
+@gpu
+@pytest.mark.parametrize("with_patch_values", [False, True])
+def test_moc_correct_host_equals_resident_path(ctx, with_patch_values):
+    """pbe_moc_correct_host (the adapter's entry: host buffers, chunked uploads, sources and
+    transport on the device) gives exactly what the resident calls give."""
+    import torch
+    from openpbe_b200 import engine
+    tm = synthetic.block_mesh(20, 16, 12, velocity=(1.0, -0.5, 0.25))
+    nc = 20 * 16 * 12
+    w = synthetic.workload("moc30_ct", nc)
+    f = synthetic.moc_fields(w)
+    moc = engine.MOC(ctx, w.N, w.xi1, engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs), w.relax)
+    mesh = engine.Mesh(ctx, tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"])
+    dev = torch.device("cuda:0")
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    psi_b = None
+    if with_patch_values:
+        psi_b = np.ascontiguousarray(f["n"][:, tm["boundary_owner"]] * 0.5)
+    n = T(f["n"])
+    S = moc.source(n, T(f["eps"]), T(f["rho"]), T(f["nu"]), w.dt)
+    want = mesh.transport_explicit(n, T(tm["phi"]), w.dt, S=S, psi_b=None if psi_b is None else T(psi_b))
+    want_d = moc.d(want).cpu().numpy()
+    n_host = torch.from_numpy(f["n"].copy())
+    d = mesh.moc_correct_host(moc, n_host, f["eps"], f["rho"], f["nu"], tm["phi"], w.dt, psi_b=psi_b)
+    np.testing.assert_array_equal(n_host.numpy(), want.cpu().numpy())
+    np.testing.assert_array_equal(d.numpy(), want_d)
+    # and against the oracle's face loop on the device sources
+    ref = orc.transport_upwind_explicit(tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"], f["n"],
+                                        tm["phi"], w.dt, S=S.cpu().numpy(), psi_b=psi_b)
+    np.testing.assert_array_equal(n_host.numpy(), ref)
