@@ -591,6 +591,26 @@ def run_b200(args):
                      "roofline": {"bound": "hbm", "achieved": tgbs, "peak": hbm_peak, "unit": "GB/s",
                                   "frac": tgbs / hbm_peak, "algorithmic_bytes": tbytes,
                                   "traffic": load_traffic("transport_upwind_kernel", tc)}}
+        if not args.no_e2e and world == 1:
+            # MOC::correct() with solveWithMULES through the host-buffer entry the adapter calls
+            # (pinned host class fields in, updated fields + d out; sources + transport on the device)
+            ft = synthetic.moc_fields(w, ncells=min(tc, 200_000))
+            rep = (tc + ft["n"].shape[1] - 1) // ft["n"].shape[1]
+            nh = torch.from_numpy(np.tile(ft["n"], (1, rep))[:, :tc].copy()).pin_memory()
+            sm = [torch.from_numpy(np.tile(ft[k], rep)[:tc].copy()).pin_memory() for k in ("eps", "rho", "nu")]
+            ph = torch.from_numpy(tm["phi"]).pin_memory()
+            tmesh.moc_correct_host(moc, nh, *sm, ph, w.dt)
+            t0 = time.perf_counter()
+            for _ in range(2):
+                dh = tmesh.moc_correct_host(moc, nh, *sm, ph, w.dt)
+            te = (time.perf_counter() - t0) / 2
+            transport["e2e"] = {"value": tc * tK / te, "unit": "cell-class-updates/s", "ms_per_step": te * 1e3,
+                                "h2d_bytes_per_step": (tK + 3) * tc * 8 + tm["phi"].size * 8,
+                                "d2h_bytes_per_step": (tK + 1) * tc * 8,
+                                "call": "pbe_moc_correct_host (pinned host n, eps, rho, nu, phi -> n, d): "
+                                        "sources + upwind transport update, synchronous",
+                                "d_mean": float(dh.mean())}
+            del nh, sm, ph
         del tpsi, tS, tout, tphi, tmesh
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) -----------------------------
