@@ -561,8 +561,14 @@ def run_b200(args):
         l0 = ctx.launch_count()
 
         def tstep():
-            halo = halo_x.exchange(tpsi) if halo_x is not None else None
-            tmesh.transport_explicit(tpsi, tphi, tdt, S=tS, out=tout, psi_halo=halo)
+            if halo_x is None:
+                tmesh.transport_explicit(tpsi, tphi, tdt, S=tS, out=tout)
+                return
+            # interior (regular) cells read no halo value: their update overlaps the exchange
+            h = halo_x.start(tpsi)
+            tmesh.transport_explicit(tpsi, tphi, tdt, S=tS, out=tout, cells=capi.CELLS_REGULAR)
+            halo = halo_x.finish(h)
+            tmesh.transport_explicit(tpsi, tphi, tdt, S=tS, out=tout, psi_halo=halo, cells=capi.CELLS_IRREGULAR)
 
         for _ in range(max(3, args.warmup)):
             tstep()
@@ -585,7 +591,7 @@ def run_b200(args):
                                  "velocity (1, 0.5, 0.25), CFL 0.4; one block per GPU"
                                  + (f", z-slabs of one {tn}x{tn}x{tn * world} block: halo exchange of "
                                     f"{tK} x {tn * tn} values per processor patch (NCCL send/recv) inside the "
-                                    "timed step" if world > 1 else ""),
+                                    "timed step, overlapped with the interior cells' update" if world > 1 else ""),
                      "l2": f"fields ({3 * tc * tK * 8 / 1e9:.1f} GB) exceed the 126 MB L2",
                      "mesh": tinfo, "launches_per_step": int(t_launches),
                      "roofline": {"bound": "hbm", "achieved": tgbs, "peak": hbm_peak, "unit": "GB/s",

@@ -238,6 +238,15 @@ int pbe_transport_explicit_halo(pbe_mesh *mesh, int scheme, int nfields, int64_t
                                 const double *psi, const double *phi, const double *psi_b,
                                 int64_t stride_b, const double *psi_halo, int64_t stride_h,
                                 const double *S, double dt, double *psi_out, void *cuda_stream);
+/* The same update restricted to one of the two cell sets of pbe_mesh_regular_cells, so that the
+ * halo exchange overlaps the bulk of the work: launch PBE_CELLS_REGULAR (interior cells: they read
+ * no halo value, psi_halo may be NULL) while the exchange is in flight, then PBE_CELLS_IRREGULAR
+ * (boundary and processor-patch cells) once psi_halo has arrived.  Both together = PBE_CELLS_ALL. */
+enum { PBE_CELLS_ALL = 0, PBE_CELLS_REGULAR = 1, PBE_CELLS_IRREGULAR = 2 };
+int pbe_transport_explicit_part(pbe_mesh *mesh, int scheme, int which, int nfields, int64_t stride,
+                                const double *psi, const double *phi, const double *psi_b,
+                                int64_t stride_b, const double *psi_halo, int64_t stride_h,
+                                const double *S, double dt, double *psi_out, void *cuda_stream);
 
 /* ======================================================================================= */
 /* Scalar kernel functors evaluated ON THE DEVICE (batched) -- the reference's Foam-free     */

@@ -20,6 +20,7 @@ DAUGHTER_UNIFORM_BINARY = 0
 QMOM_MAX_ORDER = 4
 MOC_KERNEL_SMEM, MOC_KERNEL_TMEM = 1, 2
 DIV_UPWIND = 0
+CELLS_ALL, CELLS_REGULAR, CELLS_IRREGULAR = 0, 1, 2
 
 _dp = C.POINTER(C.c_double)
 _vp = C.c_void_p
@@ -107,6 +108,8 @@ PROTOTYPES = {
     "pbe_gather_cells": (C.c_int, [_vp, C.c_int, _i64, _vp, _i64, _vp, _vp, _i64, _vp]),
     "pbe_transport_explicit_halo": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp, _i64,
                                               _vp, C.c_double, _vp, _vp]),
+    "pbe_transport_explicit_part": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
+                                              _i64, _vp, C.c_double, _vp, _vp]),
     "pbe_eval_coalescence": (C.c_int, [_vp, C.POINTER(KernelSpec), _i64, _vp, _vp, _vp, _vp, _vp,
                                        _vp]),
     "pbe_eval_breakup": (C.c_int, [_vp, C.POINTER(KernelSpec), _i64, _vp, _vp, _vp, _vp]),

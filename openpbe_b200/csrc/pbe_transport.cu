@@ -563,6 +563,16 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
                                 const double *psi, const double *phi, const double *psi_b,
                                 int64_t stride_b, const double *psi_halo, int64_t stride_h,
                                 const double *S, double dt, double *psi_out, void *cuda_stream) {
+    return pbe_transport_explicit_part(m, scheme, PBE_CELLS_ALL, nfields, stride, psi, phi, psi_b, stride_b,
+                                       psi_halo, stride_h, S, dt, psi_out, cuda_stream);
+}
+
+int pbe_transport_explicit_part(pbe_mesh *m, int scheme, int which, int nfields, int64_t stride,
+                                const double *psi, const double *phi, const double *psi_b,
+                                int64_t stride_b, const double *psi_halo, int64_t stride_h,
+                                const double *S, double dt, double *psi_out, void *cuda_stream) {
+    PBE_REQUIRE(which == PBE_CELLS_ALL || which == PBE_CELLS_REGULAR || which == PBE_CELLS_IRREGULAR,
+                PBE_E_INVALID, "pbe_transport_explicit_part: which must be PBE_CELLS_ALL / _REGULAR / _IRREGULAR");
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_transport_explicit: NULL mesh");
     PBE_REQUIRE(scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
                 "pbe_transport_explicit: scheme %d is not available on the device (valid: "
@@ -578,7 +588,8 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
                 "pbe_transport_explicit: psi_out must not alias psi (neighbours read old values)");
     PBE_REQUIRE(psi_b == nullptr || stride_b >= m->nbnd, PBE_E_INVALID,
                 "pbe_transport_explicit: stride_b < boundary faces");
-    PBE_REQUIRE(m->ncoupled == 0 || (psi_halo != nullptr && stride_h >= m->ncoupled), PBE_E_INVALID,
+    PBE_REQUIRE(m->ncoupled == 0 || which == PBE_CELLS_REGULAR || (psi_halo != nullptr && stride_h >= m->ncoupled),
+                PBE_E_INVALID,
                 "pbe_transport_explicit: the mesh has %lld coupled (processor) faces: "
                 "pbe_transport_explicit_halo needs psi_halo [nfields][stride_h >= %lld]",
                 (long long)m->ncoupled, (long long)m->ncoupled);
@@ -598,8 +609,8 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
             chunk = (chunk + 1) / 2;
         return chunk;
     };
-    const bool have_regular = m->F > 0 && m->nirr < m->ncells;
-    if (m->nirr > 0) {
+    const bool have_regular = m->F > 0 && m->nirr < m->ncells && which != PBE_CELLS_IRREGULAR;
+    if (m->nirr > 0 && which != PBE_CELLS_REGULAR) {
         // beside the regular cells' kernel when there is one (few, latency-bound threads)
         cudaStream_t is = have_regular ? m->side : st;
         if (have_regular) {
@@ -621,7 +632,7 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
         const int64_t blocks = (m->ncells + 255) / 256;
         p.chunk = chunk_for(blocks, start);
         dim3 grid((unsigned)blocks, (unsigned)((nfields + p.chunk - 1) / p.chunk));
-        static const int variant = getenv("PBE_TRANSPORT_KERNEL") ? atoi(getenv("PBE_TRANSPORT_KERNEL")) : PBE_TR_STAGES;
+        const int variant = getenv("PBE_TRANSPORT_KERNEL") ? atoi(getenv("PBE_TRANSPORT_KERNEL")) : PBE_TR_STAGES;
         auto launch_async = [&](auto kern, int F, int D) {
             const size_t smem = (size_t)D * (F + 2) * 256 * sizeof(double);
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -642,7 +653,7 @@ int pbe_transport_explicit_halo(pbe_mesh *m, int scheme, int nfields, int64_t st
 #undef PBE_TR_ASYNC
         PBE_CUDA(cudaGetLastError());
         ctx->launches++;
-        if (m->nirr > 0) PBE_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
+        if (m->nirr > 0 && which != PBE_CELLS_REGULAR) PBE_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
     }
     return PBE_OK;
 }

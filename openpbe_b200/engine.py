@@ -407,13 +407,13 @@ class Mesh:
         return out
 
     def transport_explicit(self, psi, phi, dt, *, psi_b=None, S=None, out=None, scheme="upwind",
-                           psi_halo=None):
+                           psi_halo=None, cells=capi.CELLS_ALL):
         """psi [K][ncells] -> (psi rDeltaT + S - div(phi psi_upwind)) / rDeltaT, new tensor or `out`."""
         assert psi.dim() == 2
         K, ncells = psi.shape
         out = torch.empty_like(psi) if out is None else out
-        capi.check(capi.lib().pbe_transport_explicit_halo(
-            self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), K,
+        capi.check(capi.lib().pbe_transport_explicit_part(
+            self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), int(cells), K,
             psi.stride(0) if ncells else 0, _ptr(psi), _ptr(phi), _ptr(psi_b),
             0 if psi_b is None else psi_b.stride(0), _ptr(psi_halo),
             0 if psi_halo is None else psi_halo.stride(0), _ptr(S), float(dt), _ptr(out),

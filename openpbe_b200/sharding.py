@@ -118,9 +118,15 @@ class HaloExchange:
         return psi[:, idx.long()].contiguous()
 
     def exchange(self, psi: torch.Tensor) -> torch.Tensor:
+        return self.finish(self.start(psi))
+
+    def start(self, psi: torch.Tensor):
+        """Pack and post the sends / receives; returns a handle for finish().  Work enqueued on the
+        current stream between start() and finish() (the regular cells' update, which reads no
+        halo value) overlaps the transfers."""
         halo = torch.empty((psi.shape[0], self.n), dtype=psi.dtype, device=psi.device)
         if not self.groups:
-            return halo
+            return halo, [], []
         ops, recvs = [], []
         for q, start, count in self.groups:
             s = self.pack(psi, start, count)
@@ -128,7 +134,11 @@ class HaloExchange:
             recvs.append((r, start, count))
             ops.append(dist.P2POp(dist.isend, s, q, self.group))
             ops.append(dist.P2POp(dist.irecv, r, q, self.group))
-        for w in dist.batch_isend_irecv(ops):
+        return halo, dist.batch_isend_irecv(ops), recvs
+
+    def finish(self, handle) -> torch.Tensor:
+        halo, works, recvs = handle
+        for w in works:
             w.wait()
         for r, start, count in recvs:
             halo[:, start:start + count] = r

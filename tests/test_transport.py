@@ -304,6 +304,12 @@ def test_device_decomposed_matches_oracle(ctx, world):
         got = mesh.transport_explicit(loc, T(p["phi"]), 0.01, psi_b=T(pb), S=T(S[:, lo:hi]),
                                       psi_halo=T(psi[:, p["halo_cells_global"]]))
         np.testing.assert_array_equal(got.cpu().numpy(), want[:, lo:hi])
+        # the same in two parts (interior first, then boundary / processor-patch cells): the overlap form
+        two = torch.full_like(got, float("nan"))
+        mesh.transport_explicit(loc, T(p["phi"]), 0.01, psi_b=T(pb), S=T(S[:, lo:hi]), out=two, cells=capi.CELLS_REGULAR)
+        mesh.transport_explicit(loc, T(p["phi"]), 0.01, psi_b=T(pb), S=T(S[:, lo:hi]), out=two,
+                                psi_halo=T(psi[:, p["halo_cells_global"]]), cells=capi.CELLS_IRREGULAR)
+        np.testing.assert_array_equal(two.cpu().numpy(), want[:, lo:hi])
 
 
 @gpu
@@ -372,3 +378,30 @@ def test_moc_correct_host_equals_resident_path(ctx, with_patch_values):
     ref = orc.transport_upwind_explicit(tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"], f["n"],
                                         tm["phi"], w.dt, S=S.cpu().numpy(), psi_b=psi_b)
     np.testing.assert_array_equal(n_host.numpy(), ref)
+
+
+def circulant_mesh(rng, n, degree):
+    """Every cell has exactly `degree` internal faces and no boundary face (offsets 1, 2, (3 |
+    antipode)): the three register-resident kernels (F = 4, 5, 6) each get a mesh of their own."""
+    offs = {4: (1, 2), 5: (1, 2), 6: (1, 2, 3)}[degree]
+    pairs = {(min(c, (c + o) % n), max(c, (c + o) % n)) for c in range(n) for o in offs}
+    if degree == 5:
+        pairs |= {(c, c + n // 2) for c in range(n // 2)}
+    own, nei = map(np.array, zip(*sorted(pairs)))
+    return {"owner": own.astype(np.int32), "neighbour": nei.astype(np.int32),
+            "boundary_owner": np.zeros(0, np.int32), "vcell": rng.uniform(0.5, 2.0, n),
+            "phi": rng.normal(size=own.size)}
+
+
+@gpu
+@pytest.mark.parametrize("degree", [4, 5, 6])
+@pytest.mark.parametrize("kernel", ["0", "2", "3"])
+def test_device_regular_kernels_every_face_count(ctx, degree, kernel, monkeypatch):
+    monkeypatch.setenv("PBE_TRANSPORT_KERNEL", kernel)  # register-staged / cp.async 2 and 3 stages
+    rng = np.random.default_rng(degree)
+    m = circulant_mesh(rng, 1000, degree)
+    psi = rng.normal(size=(9, 1000)); S = rng.normal(size=(9, 1000))
+    want = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.05, S=S)
+    got, info = _run_device(ctx, m, psi, m["phi"], 0.05, S=S)
+    assert info["faces_per_regular_cell"] == degree and info["regular_cells"] == 1000
+    np.testing.assert_array_equal(got, want)
