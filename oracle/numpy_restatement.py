@@ -122,3 +122,34 @@ def qmom_source_cell(spec, order, m, eps, rho, nu):
             bs += w[i] * float(_break(spec, x[i], r, e)) * (daughter_moment(x[i], k) - np.power(x[i], float(k)))
         out[k] = cs + bs
     return out
+
+
+def transport_upwind_explicit(owner, neighbour, boundary_owner, vcell, psi, phi, dt, psi_b=None, S=None,
+                              coupled=(0, 0), psi_halo=None):
+    """Independent restatement of MULES::explicitSolve with the upwind flux (see pbe_oracle.h for the
+    OpenFOAM functions it follows).  np.add.at accumulates unbuffered in index order = face order,
+    so the result is bit-identical to the C face loop."""
+    own, nei, bown = (np.asarray(a, dtype=np.int64) for a in (owner, neighbour, boundary_owner))
+    psi = np.asarray(psi, dtype=np.float64)
+    ni, nb = own.size, bown.size
+    rDeltaT = 1.0 / dt
+    out = np.empty_like(psi)
+    c0, ncpl = coupled
+    for k in range(psi.shape[0]):
+        f = psi[k]
+        lam = np.where(phi[:ni] >= 0.0, 1.0, 0.0)
+        face = lam * (f[own] - f[nei]) + f[nei]
+        flux = phi[:ni] * face
+        # interleave += on the owner and -= on the neighbour in face order
+        idx = np.empty(2 * ni, dtype=np.int64); idx[0::2] = own; idx[1::2] = nei
+        val = np.empty(2 * ni); val[0::2] = flux; val[1::2] = -flux
+        ivf = np.zeros(f.size)
+        np.add.at(ivf, idx, val)
+        bval = f[bown].copy() if psi_b is None else np.asarray(psi_b[k], dtype=np.float64).copy()
+        if ncpl:
+            w = np.where(phi[ni + c0:ni + c0 + ncpl] >= 0.0, 1.0, 0.0)
+            bval[c0:c0 + ncpl] = w * f[bown[c0:c0 + ncpl]] + (1.0 - w) * psi_halo[k]
+        np.add.at(ivf, bown, phi[ni:ni + nb] * bval)
+        Su = 0.0 if S is None else S[k]
+        out[k] = (f * rDeltaT + Su - ivf / vcell) / rDeltaT
+    return out

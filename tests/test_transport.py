@@ -405,3 +405,41 @@ def test_device_regular_kernels_every_face_count(ctx, degree, kernel, monkeypatc
     got, info = _run_device(ctx, m, psi, m["phi"], 0.05, S=S)
     assert info["faces_per_regular_cell"] == degree and info["regular_cells"] == 1000
     np.testing.assert_array_equal(got, want)
+
+
+def test_c_oracle_equals_numpy_restatement():
+    from oracle import numpy_restatement as npo
+    rng = np.random.default_rng(77)
+    m = synthetic.block_mesh(9, 7, 5, velocity=(0.3, -0.2, 0.4))
+    m["phi"] = m["phi"] * rng.uniform(0.5, 1.5, m["phi"].size) * rng.choice([1.0, -1.0, 0.0], m["phi"].size)
+    psi = rng.uniform(0.0, 2.0, (4, 315)); S = rng.normal(size=(4, 315))
+    psi_b = rng.uniform(0.0, 2.0, (4, m["boundary_owner"].size))
+    for kw in ({}, {"S": S}, {"psi_b": psi_b, "S": S}):
+        a = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.01, **kw)
+        b = npo.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.01, **kw)
+        np.testing.assert_array_equal(a, b)
+    # a sub-domain with processor-patch faces
+    from openpbe_b200 import sharding
+    p = sharding.partition_mesh(m, 1, 3)
+    lo, hi = p["cell_range"]
+    halo = psi[:, p["halo_cells_global"]]
+    a = orc.transport_upwind_explicit(p["owner"], p["neighbour"], p["boundary_owner"], p["vcell"], psi[:, lo:hi], p["phi"],
+                                      0.01, coupled=p["coupled"], psi_halo=halo)
+    b = npo.transport_upwind_explicit(p["owner"], p["neighbour"], p["boundary_owner"], p["vcell"], psi[:, lo:hi], p["phi"],
+                                      0.01, coupled=p["coupled"], psi_halo=halo)
+    np.testing.assert_array_equal(a, b)
+
+
+def test_oracle_first_order_convergence_1d():
+    # smooth profile advected over a fixed time: the upwind error halves when dx and dt halve
+    errs = []
+    for n in (50, 100, 200):
+        m = chain_mesh(n, u=1.0, dx=1.0 / n)
+        x = (np.arange(n) + 0.5) / n
+        psi = np.exp(-200.0 * (x - 0.3) ** 2)[None, :]
+        dt = 0.5 / n
+        for _ in range(int(round(0.3 / dt))):
+            psi = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], dt)
+        exact = np.exp(-200.0 * (x - 0.6) ** 2)
+        errs.append(np.abs(psi[0] - exact).sum() / n)
+    assert errs[1] < 0.75 * errs[0] and errs[2] < 0.7 * errs[1]
