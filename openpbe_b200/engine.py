@@ -72,6 +72,14 @@ def _ptr(t: Optional[torch.Tensor]):
     return C.c_void_p(t.data_ptr())
 
 
+def _ptr_rows(t: Optional[torch.Tensor]):
+    """[rows][cols] float64 with unit column stride (rows may be padded): pointer to element (0, 0)."""
+    if t is None:
+        return None
+    assert t.dtype == torch.float64 and t.dim() == 2 and (t.shape[1] <= 1 or t.stride(1) == 1)
+    return C.c_void_p(t.data_ptr())
+
+
 def _stream_ptr(device) -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
@@ -415,7 +423,7 @@ class Mesh:
         capi.check(capi.lib().pbe_transport_explicit_part(
             self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), int(cells), K,
             psi.stride(0) if ncells else 0, _ptr(psi), _ptr(phi), _ptr(psi_b),
-            0 if psi_b is None else psi_b.stride(0), _ptr(psi_halo),
+            0 if psi_b is None else psi_b.stride(0), _ptr_rows(psi_halo),
             0 if psi_halo is None else psi_halo.stride(0), _ptr(S), float(dt), _ptr(out),
             _stream_ptr(psi.device)))
         return out

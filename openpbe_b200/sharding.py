@@ -143,3 +143,60 @@ class HaloExchange:
         for r, start, count in recvs:
             halo[:, start:start + count] = r
         return halo
+
+
+class PeerHaloExchange:
+    """The halo exchange as stores into peer memory: every rank's halo buffer lives in symmetric
+    memory (torch.distributed._symmetric_memory: cudaMalloc'd, peer-mapped over NVLink / NVSwitch),
+    and the pack kernel (pbe_gather_cells) of the sending rank writes the values straight into the
+    receiving rank's buffer -- pack and transfer are one kernel, there is no send / receive pair and
+    no unpack copy.  One device-side barrier per step (symmetric-memory signal pads) orders the
+    stores before the reads.  Two buffers alternate, so a rank that runs ahead writes step t+1's
+    values while its neighbour still reads step t's.  Same start() / finish() protocol as
+    HaloExchange; needs a CUDA device per rank (no CPU form)."""
+
+    def __init__(self, part: dict, device, mesh, nfields: int, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.mesh, self.K = mesh, int(nfields)
+        self.groups = part["neighbours"]
+        self.n = part["coupled"][1]
+        group = group if group is not None else dist.group.WORLD
+        rank = dist.get_rank(group)
+        everyone = [None] * dist.get_world_size(group)
+        dist.all_gather_object(everyone, (self.n, self.groups), group=group)
+        self.nmax = max(1, max(n for n, _ in everyone))
+        # where my values land in each neighbour's buffer: that neighbour's group for me
+        self.targets = []
+        for q, start, count in self.groups:
+            back = [g for g in everyone[q][1] if g[0] == rank]
+            assert len(back) == 1 and back[0][2] == count, "processor patches of the two sides differ"
+            self.targets.append((q, start, count, back[0][1]))
+        self.buf = symm_mem.empty((2, self.K, self.nmax), dtype=torch.float64, device=device)
+        self.hdl = symm_mem.rendezvous(self.buf, group)
+        self.ptrs = list(self.hdl.buffer_ptrs)
+        self.send_cells = torch.from_numpy(part["send_cells"]).to(device)
+        self.parity = 0
+        self.hdl.barrier(channel=0)
+
+    def start(self, psi: torch.Tensor):
+        from . import capi
+        from .engine import _stream_ptr
+
+        p = self.parity
+        self.parity ^= 1
+        K, ncells = psi.shape
+        assert K == self.K and psi.is_contiguous()
+        for q, start, count, rstart in self.targets:
+            out = self.ptrs[q] + ((p * K) * self.nmax + rstart) * 8
+            capi.check(capi.lib().pbe_gather_cells(
+                self.mesh.ctx.handle, K, psi.stride(0), psi.data_ptr(), count,
+                self.send_cells.data_ptr() + 4 * start, out, self.nmax, _stream_ptr(psi.device)))
+        return p
+
+    def finish(self, p: int) -> torch.Tensor:
+        self.hdl.barrier(channel=0)  # every rank's packs of this step have landed
+        return self.buf[p][:, :self.n]  # [K][n coupled faces], row stride nmax
+
+    def exchange(self, psi: torch.Tensor) -> torch.Tensor:
+        return self.finish(self.start(psi))
