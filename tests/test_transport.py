@@ -443,3 +443,36 @@ def test_oracle_first_order_convergence_1d():
         exact = np.exp(-200.0 * (x - 0.6) ** 2)
         errs.append(np.abs(psi[0] - exact).sum() / n)
     assert errs[1] < 0.75 * errs[0] and errs[2] < 0.7 * errs[1]
+
+
+@gpu
+def test_device_padded_strides_through_the_c_abi(ctx):
+    """stride > ncells and stride_b > boundary faces (fields that are rows of bigger allocations)."""
+    import torch
+    from openpbe_b200 import engine
+    rng = np.random.default_rng(123)
+    m = synthetic.block_mesh(13, 9, 6, velocity=(1.0, -0.7, 0.3))
+    nc, nb, K, pad, padb = 13 * 9 * 6, m["boundary_owner"].size, 5, 37, 11
+    psi = rng.normal(size=(K, nc)); S = rng.normal(size=(K, nc)); psi_b = rng.normal(size=(K, nb))
+    want = orc.transport_upwind_explicit(m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"], psi, m["phi"], 0.02,
+                                         psi_b=psi_b, S=S)
+    dev = torch.device("cuda:0")
+    big = lambda a, p: torch.from_numpy(np.pad(a, ((0, 0), (0, p)), constant_values=np.nan)).to(dev)
+    Psi, Ss, Pb = big(psi, pad), big(S, pad), big(psi_b, padb)
+    out = torch.full((K, nc + pad), -7.0, dtype=torch.float64, device=dev)
+    phi = torch.from_numpy(m["phi"]).to(dev)
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    capi.check(capi.lib().pbe_transport_explicit(mesh._h, capi.DIV_UPWIND, K, nc + pad, Psi.data_ptr(), phi.data_ptr(),
+                                                 Pb.data_ptr(), nb + padb, Ss.data_ptr(), 0.02, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    np.testing.assert_array_equal(got[:, :nc], want)
+    assert np.all(got[:, nc:] == -7.0)  # the padding is never written
+    # halo packing with padded rows on both sides
+    cells = torch.from_numpy(rng.integers(0, nc, 50).astype(np.int32)).to(dev)
+    packed = torch.full((K, 64), -1.0, dtype=torch.float64, device=dev)
+    capi.check(capi.lib().pbe_gather_cells(ctx.handle, K, nc + pad, Psi.data_ptr(), 50, cells.data_ptr(),
+                                           packed.data_ptr(), 64, None))
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(packed.cpu().numpy()[:, :50], psi[:, cells.cpu().numpy()])
+    assert np.all(packed.cpu().numpy()[:, 50:] == -1.0)
