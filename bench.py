@@ -651,6 +651,23 @@ def run_b200(args):
                          "no extrapolation needed (cells independent)",
                "single_thread_value": rate1, "single_thread_seconds": secs1}
 
+    if cpu is not None and transport is not None:
+        # the face loop of the transport update on one host core (the reference is serial per
+        # rank), on a bounded sample: a 96^3 block, all fields
+        from oracle import cpu_oracle as orc2
+
+        sm_ = synthetic.block_mesh(96, 96, 96, velocity=(1.0, 0.5, 0.25))
+        rs = np.random.default_rng(5)
+        ps = rs.uniform(size=(N, 96 ** 3))
+        Ss = rs.uniform(size=(N, 96 ** 3))
+        t0 = time.perf_counter()
+        orc2.transport_upwind_explicit(sm_["owner"], sm_["neighbour"], sm_["boundary_owner"], sm_["vcell"], ps,
+                                       sm_["phi"], 1e-3, S=Ss)
+        tsec = time.perf_counter() - t0
+        transport["cpu_baseline"] = {"value": N * 96 ** 3 / tsec, "unit": "cell-field-updates/s", "cores": 1,
+                                     "kind": "port", "sample": f"96^3 cells x {N} fields, one step, face loop of "
+                                     f"oracle/pbe_oracle.c (OpenFOAM-shaped), {tsec:.2f} s"}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
