@@ -163,6 +163,37 @@ int pbe_qmom_source_host(pbe_qmom *q, int64_t ncells, int64_t stride, const doub
                          double *S_host);
 
 /* ======================================================================================= */
+/* methodOfMoments (first slice) -- replaces the per-cell part of          */
+/* MOM::correct(), src/PBESystem/MOM.C:148-236, and its nested-integral source terms,       */
+/* MOM.C:259-311 (coalescence) and MOM.C:313-362 (breakup).  Three moments m0, m1, m2;       */
+/* presumed gamma density with k = m1^2 / (m2 m0 - m1^2 + SMALL), theta = (m0 m2 - m1^2) /   */
+/* max(m0 m1, SMALL) (MOM.C:151-161).  integrate() (Integrator.H:12-27, GSL QAGIU) becomes a */
+/* fixed-depth 15-point Gauss-Kronrod rule on the same x = lower + (1-t)/t transform with    */
+/* `panels` equal panels of (0,1] (0 = default), the one at the lower limit bisected         */
+/* PBE_MOM_GRADED_LEVELS times.  The implicit fvm::ddt + fvm::div solve of   */
+/* MOM.C:211-222 is out of scope (zero-flux update only).  Parity unpinned in the reference. */
+/* ======================================================================================= */
+typedef struct pbe_mom pbe_mom;
+#define PBE_MOM_DEFAULT_PANELS 12
+#define PBE_MOM_MAX_PANELS 28
+#define PBE_MOM_GRADED_LEVELS 20 /* bisections of the panel next to the lower limit */
+
+int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mom **out);
+int pbe_mom_destroy(pbe_mom *h);
+/* S[k][c] = coalescenceSourceTerm(k) + breakupSourceTerm(k), k < 3, NOT NaN-scrubbed
+ * (MOM::momentSourceTerm, MOM.C:244-254).  m, S: [3][stride] device arrays.  gamma (optional,
+ * [3][stride]) receives gamma_c0, gamma_k, gamma_theta (MOM.C:151-161).  Cells whose moments give
+ * k <= 0 or theta <= 0 (Boost.Math raises a domain error there) get NaN sources. */
+int pbe_mom_source(pbe_mom *h, int64_t ncells, int64_t stride, const double *m, const double *eps,
+                   const double *rho, const double *nu, double *S, double *gamma,
+                   void *cuda_stream);
+/* NaN->0 scrub (MOM.C:198-207), m_k += dt S_k (MOM.C:211-222 with phi = 0), clamp to SMALL =
+ * 1e-15 (MOM.C:224-231), d = (6/pi m1/m0)^(1/3) (MOM.C:233).  S (scrubbed), d, gamma optional. */
+int pbe_mom_step(pbe_mom *h, int64_t ncells, int64_t stride, double *m, const double *eps,
+                 const double *rho, const double *nu, double dt, double *S, double *d, double *gamma,
+                 void *cuda_stream);
+
+/* ======================================================================================= */
 /* Transport of the class / moment fields (first slice) --       */
 /* replaces the explicit update of MOC::solveWithMULES, src/PBESystem/MOC.C:198-272, and     */
 /* QMOM::solveWithMULES, src/PBESystem/QMOM.C:131-197, for the divergence scheme             */

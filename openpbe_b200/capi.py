@@ -91,6 +91,10 @@ PROTOTYPES = {
     "pbe_qmom_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp, _vp]),
     "pbe_wheeler_batch": (C.c_int, [_vp, C.c_int, _i64, _i64, _vp, _vp, _vp, _vp]),
     "pbe_qmom_source_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "pbe_mom_create": (C.c_int, [_vp, C.c_int, C.POINTER(KernelSpec), C.POINTER(_vp)]),
+    "pbe_mom_destroy": (C.c_int, [_vp]),
+    "pbe_mom_source": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "pbe_mom_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp, _vp, _vp]),
     "pbe_mesh_create": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp, C.POINTER(_vp)]),
     "pbe_mesh_destroy": (C.c_int, [_vp]),
     "pbe_mesh_info": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64),

@@ -341,6 +341,47 @@ class QMOM:
         return S
 
 
+class MOM:
+    """pbe_mom: PBEMethods::MOM's per-cell path (methodOfMoments, MOM.C:148-236, 259-362): three
+    moments, presumed gamma density, nested integrals on a fixed-depth Gauss-Kronrod rule."""
+
+    def __init__(self, ctx: Context, spec: capi.KernelSpec, panels: int = 0):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        capi.check(capi.lib().pbe_mom_create(ctx.handle, int(panels), C.byref(spec), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_mom_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def _dims(m):
+        assert m.dim() == 2 and m.shape[0] == 3
+        ncells = m.shape[1]
+        return ncells, (m.stride(0) if ncells else 0)
+
+    def source(self, m, eps, rho, nu, out=None, gamma=None):
+        ncells, stride = self._dims(m)
+        S = torch.empty_like(m) if out is None else out
+        capi.check(capi.lib().pbe_mom_source(self._h, ncells, stride, _ptr(m), _ptr(eps), _ptr(rho),
+                                             _ptr(nu), _ptr(S), _ptr(gamma), _stream_ptr(m.device)))
+        return S
+
+    def step(self, m, eps, rho, nu, dt, *, S=None, d=None, gamma=None):
+        ncells, stride = self._dims(m)
+        capi.check(capi.lib().pbe_mom_step(self._h, ncells, stride, _ptr(m), _ptr(eps), _ptr(rho),
+                                           _ptr(nu), float(dt), _ptr(S), _ptr(d), _ptr(gamma),
+                                           _stream_ptr(m.device)))
+        return m
+
+
 def div_scheme(name: str) -> int:
     """fvSchemes `div(phi,n.*)` entry -> PBE_DIV_*; unknown / unsupported names raise PbeError."""
     out = C.c_int()
