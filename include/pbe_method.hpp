@@ -5,7 +5,7 @@
 //   * class PBEMethod { virtual void correct() = 0; virtual const volScalarField d() const = 0;
 //     static autoPtr<PBEMethod> New(const dictionary&, const phaseModel&); }   PBEMethod.H:62-126
 //   * run-time selection by the dictionary word `method` with the reference's TypeNames
-//     "methodOfClasses" (MOC.H:100), "quadratureMethodOfMoments" (QMOM.H:87), "dummy"
+//     "methodOfClasses" (MOC.H:100), "quadratureMethodOfMoments" (QMOM.H:87), "methodOfMoments" (MOM.H:92), "dummy"
 //     (dummy.H:67); unknown names fail listing the valid ones                  PBEMethod.C:81-108
 //   * kernel selection by `coalescenceKernel` / `breakupKernel` /
 //     `daughterParticleDistribution` with coefficients in `<TypeName>Coeffs`
@@ -604,6 +604,75 @@ private:
     mutable bool d_stale_ = true;
 };
 
+// ---- methodOfMoments (MOM.H:55-96, MOM.C:60-236): three moments, presumed gamma density -----------------
+class MOM : public PBEMethod {
+public:
+    static constexpr const char *typeName = "methodOfMoments";
+
+    // m0: initial moment fields m0, m1, m2, HOST [3][ncells] (MUST_READ "m<i>", MOM.C:128-141)
+    MOM(const Dictionary &pbeProperties, const Phase &phase, const double *m0 = nullptr)
+        : PBEMethod(pbeProperties, phase) {
+        const Dictionary &c = pbeProperties.subDict("MOMCoeffs"); // MOM.C:68
+        // the reference reads nothing from MOMCoeffs; quadraturePanels sets the fixed rule that
+        // stands in for integrate()'s adaptive QAGIU (0 = PBE_MOM_DEFAULT_PANELS)
+        const int panels = (int)c.lookupOrDefault<double>("quadraturePanels", 0.0);
+        if (phase.mesh)
+            throw FatalError("MOM: moment transport is the implicit fvm::ddt + fvm::div solve (MOM.C:211-222), "
+                             "which has no device path; run methodOfMoments without a FaceMesh");
+        check(pbe_mom_create(ctx_.get(), panels, &spec_, &h_), "MOM::MOM");
+        stageCellFields();
+        const int64_t nc = phase.ncells;
+        m_ = DeviceArray(ctx_, 3 * nc), S_ = DeviceArray(ctx_, 3 * nc), gamma_ = DeviceArray(ctx_, 3 * nc);
+        d_dev_ = DeviceArray(ctx_, nc);
+        if (m0)
+            m_.upload(m0, 3 * nc);
+        else
+            m_.zero();
+        d_host_.assign((size_t)nc, 0.0);
+        if (m0) { // d_ = pow(6/pi m1/m0, 1/3) at construction, MOM.C:143
+            for (int64_t c2 = 0; c2 < nc; ++c2)
+                d_host_[(size_t)c2] = std::pow(6.0 / M_PI * m0[nc + c2] / m0[c2], 1.0 / 3.0);
+            d_stale_ = false;
+        }
+    }
+    ~MOM() override {
+        if (h_) pbe_mom_destroy(h_);
+    }
+
+    // MOM::correct(): gamma parameters, moment sources, NaN scrub, zero-flux update, clamp, d (MOM.C:148-236)
+    void correct() override {
+        const int64_t nc = phase_.ncells;
+        if (nc == 0) return;
+        check(pbe_mom_step(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, S_.data(),
+                           d_dev_.data(), gamma_.data(), nullptr),
+              "MOM::correct");
+        d_stale_ = true;
+    }
+    const std::vector<double> &d() const override {
+        if (d_stale_ && phase_.ncells) {
+            check(pbe_sync(ctx_.get()), "MOM::d");
+            d_dev_.download(d_host_.data(), phase_.ncells);
+            d_stale_ = false;
+        }
+        return d_host_;
+    }
+    // field k of: moments (m0, m1, m2), their scrubbed sources, or gamma_c0 / gamma_k / gamma_theta
+    enum Field { Moment, Source, Gamma };
+    std::vector<double> field(Field which, int k) const {
+        std::vector<double> v((size_t)phase_.ncells);
+        check(pbe_sync(ctx_.get()), "MOM::field");
+        const DeviceArray &a = which == Moment ? m_ : which == Source ? S_ : gamma_;
+        if (phase_.ncells) a.download(v.data(), phase_.ncells, (int64_t)k * phase_.ncells);
+        return v;
+    }
+
+private:
+    pbe_mom *h_ = nullptr;
+    DeviceArray m_, S_, gamma_, d_dev_;
+    mutable std::vector<double> d_host_;
+    mutable bool d_stale_ = true;
+};
+
 // ---- dummy (dummy.H:55-79): constant diameter from dummyCoeffs.constantDiameter --------------------------
 class dummy : public PBEMethod {
 public:
@@ -620,7 +689,7 @@ private:
 
 } // namespace PBEMethods
 
-// addToRunTimeSelectionTable(PBEMethod, X, dictionary): MOC.C:38-39, QMOM.C:50-51, dummy.C:37-38
+// addToRunTimeSelectionTable(PBEMethod, X, dictionary): MOC.C:38-39, QMOM.C:50-51, MOM.C:50-51, dummy.C:37-38
 inline void registerBuiltinMethods() {
     auto &t = PBEMethod::table();
     if (!t.empty()) return;
@@ -630,14 +699,16 @@ inline void registerBuiltinMethods() {
     t[PBEMethods::QMOM::typeName] = [](const Dictionary &d, const Phase &p) {
         return std::unique_ptr<PBEMethod>(new PBEMethods::QMOM(d, p));
     };
+    t[PBEMethods::MOM::typeName] = [](const Dictionary &d, const Phase &p) {
+        return std::unique_ptr<PBEMethod>(new PBEMethods::MOM(d, p));
+    };
     t[PBEMethods::dummy::typeName] = [](const Dictionary &d, const Phase &p) {
         return std::unique_ptr<PBEMethod>(new PBEMethods::dummy(d, p));
     };
 }
 
 // PBEMethod::New (PBEMethod.C:81-108): word(dict.lookup("method")) -> table lookup; unknown names
-// are fatal and list the valid ones.  "methodOfMoments" (MOM.H:92) is not built into this library
-// (GSL + Boost.Math, outside the accelerated path) and is reported as such.
+// are fatal and list the valid ones.
 inline std::unique_ptr<PBEMethod> PBEMethod::New(const Dictionary &pbeProperties, const Phase &phase) {
     registerBuiltinMethods();
     const std::string method = pbeProperties.lookup("method");
@@ -652,7 +723,6 @@ inline std::unique_ptr<PBEMethod> PBEMethod::New(const Dictionary &pbeProperties
             first = false;
         }
         os << ")";
-        if (method == "methodOfMoments") os << "\n(methodOfMoments is not part of the B200 source engine)";
         throw FatalError(os.str());
     }
     return it->second(pbeProperties, phase);

@@ -8,9 +8,8 @@
 // version keeps the transform and the 15-point rule on a FIXED set of panels (`panels` equal
 // panels of (0,1], the one next to t = 1 bisected PBE_MOM_GRADED_LEVELS times towards the lower
 // limit, where the gamma density is x^(k-1)): with a fixed rule the kernel evaluations
-// of the inner integrals are shared by the three moment indices and by the birth and death
-// integrals, so a cell costs (15 panels)^2 kernel evaluations instead of 6 nested adaptive
-// runs.  Parity is UNPINNED in the reference (no MOM test exists; Boost.Math / GSL absent
+// are shared by the three moment indices and by the birth and death integrals, so a cell
+// costs (15 panels)^2 / 2 coalescence-kernel evaluations instead of 6 nested adaptive runs.  Parity is UNPINNED in the reference (no MOM test exists; Boost.Math / GSL absent
 // here): the tests compare against nested adaptive QUADPACK QAGI integrals in the reference's
 // shape and against closed forms for the cell-independent kernels (tests/test_mom.py).
 //
@@ -135,40 +134,38 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) mom_kernel(MomParams p) {
         for (int q = lane; q < nq; q += 32) fq[q] = wq[q] * (m0 * pdf(xq[q]));
         __syncwarp();
 
+        // Coalescence (MOM.C:278-308), birth / 2 - death.  Every built-in kernel is symmetric in
+        // (xi, xi'), so the two double integrals fold into one sum over unordered node pairs:
+        //   k = 0: -1/2 sum f_a f_b S_ab;  k = 1: 0 exactly (volume is conserved);
+        //   k = 2: 1/2 (xa + xb)^2 - 1/2 (xa^2 + xb^2) = xa xb.
+        // Breakup (MOM.C:338-361): exchanging the order of the two integrals turns
+        //   int_0^inf xi^k int_xi^inf beta(xi, xi') g(xi') n(xi') dxi' dxi   into
+        //   int_0^inf moment(xi', k) g(xi') n(xi') dxi',  moment = int_0^xi' xi^k beta dxi = 2 xi'^k / (k+1)
+        // (daughterParticleDistribution::moment, uniformBinaryBreakup.C:62-69 -- the form
+        // QMOM.C:252-262 uses), one pass over the nodes instead of a nested integral per node.
         double s0 = 0.0, s1 = 0.0, s2 = 0.0;
         for (int a = lane; a < nq; a += 32) {
             const double xa = xq[a], fa = fq[a];
             const NodeRoots na{ra[a], rp[a]};
             if (p.ks.coal != PBE_COAL_NONE) {
-                // MOM.C:278-308: birth / 2 - death with the inner integrals on the same nodes
-                double c0 = 0.0, c1 = 0.0, c2 = 0.0;
-                for (int b = 0; b < nq; ++b) {
-                    const double xb = xq[b];
+                double c0 = 0.0, c2 = 0.0;
+                for (int b = 0; b < a; ++b) {
                     const NodeRoots nb{ra[b], rp[b]};
                     const double t = fq[b] * coal_S(p.ks, cc, na, nb);
-                    const double sum = xa + xb;
-                    c0 = fma_(t, -0.5, c0);
-                    c1 = fma_(t, 0.5 * sum - xa, c1);
-                    c2 = fma_(t, 0.5 * (sum * sum) - xa * xa, c2);
+                    c0 += t;
+                    c2 = fma_(t, xq[b], c2);
                 }
-                s0 = fma_(fa, c0, s0);
-                s1 = fma_(fa, c1, s1);
-                s2 = fma_(fa, c2, s2);
+                const double tdiag = 0.5 * (fa * coal_S(p.ks, cc, na, na)); // pair (a, a) counts once
+                c0 += tdiag;
+                c2 = fma_(tdiag, xa, c2);
+                s0 = fma_(-fa, c0, s0);             // 2 * (-1/2) * fa * sum_b
+                s2 = fma_(2.0 * (fa * xa), c2, s2);
             }
             if (p.ks.br != PBE_BR_NONE) {
-                // MOM.C:338-361: inner integral from xi = xa upwards, x' = xa + (1 - t) / t
-                double birth = 0.0;
-                for (int b = 0; b < nq; ++b) {
-                    const double xp = xa + xq[b];
-                    NodeRoots np{0.0, 0.0};
-                    if (p.ks.br == PBE_BR_CT) np = node_roots(xp);
-                    birth = fma_(wq[b] * daughter_beta(xa, xp),
-                                 break_S(p.ks, cc, xp, np) * (m0 * pdf(xp)), birth);
-                }
-                const double term = wq[a] * birth - break_S(p.ks, cc, xa, na) * fa;
-                s0 += term;
-                s1 = fma_(xa, term, s1);
-                s2 = fma_(xa * xa, term, s2);
+                const double gn = break_S(p.ks, cc, xa, na) * fa;
+                s0 += gn * (daughter_moment_from_pow(1.0, 0) - 1.0);
+                s1 = fma_(xa * gn, daughter_moment_from_pow(1.0, 1) - 1.0, s1);
+                s2 = fma_(xa * xa * gn, daughter_moment_from_pow(1.0, 2) - 1.0, s2);
             }
         }
 #pragma unroll

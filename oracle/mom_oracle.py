@@ -14,8 +14,10 @@ Two flavours:
   mom_source_cell        reference-shaped: nested adaptive integrals, one per (term, moment index),
                          exactly the lambdas of MOM.C:259-311 and MOM.C:313-362;
   mom_source_cell_fixed  the fixed-depth rule the device kernel uses (same transform and 15-point
-                         rule on a fixed, graded panel set), vectorised in NumPy -- pins the device
-                         arithmetic tightly, while the first flavour pins the rule's accuracy.
+                         rule on a fixed, graded panel set; coalescence folded over unordered pairs,
+                         breakup with the order of integration exchanged), vectorised in NumPy --
+                         pins the device arithmetic tightly, while the first flavour pins the
+                         rule's (and the two identities') accuracy against the reference's shape.
 """
 from __future__ import annotations
 
@@ -123,18 +125,15 @@ def mom_source_cell_fixed(spec, m, eps, rho, nu, panels=12):
     f = w * m0 * gamma_pdf(k, theta, x)
     out = np.zeros(3)
     if spec["coalescence"] != "noCoalescence":
-        Sab = _S(spec, x[:, None], x[None, :], eps, rho, nu)
-        tt = f[:, None] * f[None, :] * Sab
-        xs = x[:, None] + x[None, :]
-        for mi in range(3):
-            out[mi] += np.sum(tt * (0.5 * xs ** mi - x[:, None] ** mi))
+        # symmetric kernels: birth / 2 - death folds to (-1/2, 0, xa xb) per pair
+        tt = f[:, None] * f[None, :] * _S(spec, x[:, None], x[None, :], eps, rho, nu)
+        out[0] += -0.5 * np.sum(tt)
+        out[2] += np.sum(tt * x[:, None] * x[None, :])
     if spec["breakup"] != "noBreakup":
-        xp = x[:, None] + x[None, :]
-        inner = np.sum(w[None, :] * npo.daughter_beta(x[:, None], xp) * _g(spec, xp, eps, rho)
-                       * (m0 * gamma_pdf(k, theta, xp)), axis=1)
-        term = w * inner - _g(spec, x, eps, rho) * f
+        # order of integration exchanged: int moment(xi', k) g n dxi' (uniformBinaryBreakup.C:62-69)
+        gn = _g(spec, x, eps, rho) * f
         for mi in range(3):
-            out[mi] += np.sum(x ** mi * term)
+            out[mi] += np.sum((npo.daughter_moment(x, mi) - x ** mi) * gn)
     return out
 
 

@@ -71,8 +71,7 @@ def test_dictionary_and_runtime_selection(probe):
     assert "method=methodOfClasses N=10 xi1=1 mules=1 relax=1 c=0.1" in out
     assert "spec=1,0,0,0.1" in out                      # constantCoalescence, noBreakup, uniformBinaryBreakup
     assert "Unknown pbeModelType type bogus" in out and "Valid PBEMethod types are" in out
-    assert "(dummy methodOfClasses quadratureMethodOfMoments)" in out
-    assert "methodOfMoments is not part of the B200 source engine" in out
+    assert "(dummy methodOfClasses methodOfMoments quadratureMethodOfMoments)" in out
     assert 'keyword method is undefined in dictionary' in out
     assert "Unknown coalescenceKernel type Madsen" in out and "CoulaloglouTavlaridesC" in out
 
@@ -138,3 +137,70 @@ def test_replay_driver_with_transport(oracle):
         assert abs(a["d_avg"] / b["d_avg"] - 1) < 1e-9 and abs(a["d_max"] / b["d_max"] - 1) < 1e-9
     tail = [r for r in rows if "min_n0" in r][0]
     assert tail["min_n0"] >= 0.0
+
+
+MOM_PROBE = r'''
+#include "pbe_method.hpp"
+#include <cstdio>
+// PBEMethod::New -> methodOfMoments (MOM.C:60-236) on a few cells with O(1) moments; prints the
+// moments, scrubbed sources, gamma parameters and d after one correct().
+int main() {
+    const int nc = 6;
+    std::vector<double> m(3 * nc), eps(nc, 1.0), rho(nc, 1.0), nu(nc, 1.0);
+    for (int c = 0; c < nc; ++c) {
+        const double m0 = 1.0 + 0.3 * c, k = 1.5 + 0.4 * c, th = 0.2 + 0.05 * c;
+        m[c] = m0; m[nc + c] = m0 * k * th; m[2 * nc + c] = m0 * k * (k + 1) * th * th;
+    }
+    pbe::Phase ph; ph.ncells = nc; ph.deltaT = 1e-2; ph.epsilon = eps.data(); ph.rho = rho.data(); ph.nu = nu.data();
+    auto dict = pbe::Dictionary::parse(R"(
+        method methodOfMoments; MOMCoeffs { }
+        coalescenceKernel constantCoalescence; breakupKernel binaryBreakup;
+        daughterParticleDistribution uniformBinaryBreakup;
+        constantCoalescenceCoeffs { constant 0.1; } binaryBreakupCoeffs { } uniformBinaryBreakupCoeffs { }
+    )");
+    try {
+        pbe::PBEMethods::MOM mom(dict, ph, m.data());
+        std::printf("d0 %.17g\n", mom.d()[2]);
+        mom.correct();
+        for (int c = 0; c < nc; ++c) {
+            std::printf("cell");
+            for (int k = 0; k < 3; ++k) std::printf(" %.17g", m[k * nc + c]);
+            for (auto f : {pbe::PBEMethods::MOM::Moment, pbe::PBEMethods::MOM::Source, pbe::PBEMethods::MOM::Gamma})
+                for (int k = 0; k < 3; ++k) std::printf(" %.17g", mom.field(f, k)[c]);
+            std::printf(" %.17g\n", mom.d()[c]);
+        }
+        auto viaNew = pbe::PBEMethod::New(dict, ph);
+        viaNew->correct();
+        std::printf("new ok %zu\n", viaNew->d().size());
+    } catch (const pbe::FatalError &e) { std::printf("FATAL<<%s>>\n", e.what()); return 1; }
+    return 0;
+}
+'''
+
+
+@pytest.mark.gpu
+def test_method_of_moments_host_mirror(tmp_path):
+    """pbe::PBEMethods::MOM (the MOM class of MOM.H:55-96 over pbe_mom_step) against the closed
+    forms of the gamma closure for constantCoalescence + binaryBreakup."""
+    from oracle import mom_oracle as mo
+    src = tmp_path / "mom_probe.cpp"
+    src.write_text(MOM_PROBE)
+    exe = tmp_path / "mom_probe"
+    subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I",
+                           os.path.join(ROOT, "include"), str(src), "-o", str(exe), "-L", LIBDIR,
+                           "-lpbe_b200", f"-Wl,-rpath,{LIBDIR}"])
+    out = subprocess.check_output([str(exe)], text=True)
+    assert "new ok 6" in out
+    rows = [np.array(ln.split()[1:], dtype=float) for ln in out.splitlines() if ln.startswith("cell")]
+    assert len(rows) == 6
+    for r in rows:
+        m_in, m_out, S, gam, d = r[0:3], r[3:6], r[6:9], r[9:12], r[12]
+        coal, br = mo.closed_form_constant_binary(m_in, 0.1)
+        np.testing.assert_allclose(S, coal + br, rtol=0, atol=1e-10 * max(1.0, np.max(np.abs(coal + br))))
+        np.testing.assert_allclose(gam, mo.gamma_params(*m_in), rtol=1e-14)
+        _, want, dwant = mo.mom_step_cell(S, m_in, 1e-2)
+        np.testing.assert_allclose(m_out, want, rtol=1e-15)
+        np.testing.assert_allclose(d, dwant, rtol=1e-14)
+    d0 = float([ln for ln in out.splitlines() if ln.startswith("d0")][0].split()[1])
+    r2 = rows[2]
+    assert d0 == (6 / np.pi * r2[1] / r2[0]) ** (1 / 3) or abs(d0 / (6 / np.pi * r2[1] / r2[0]) ** (1 / 3) - 1) < 1e-15
