@@ -28,6 +28,8 @@ a side stream (the only cross-rank traffic: cells are independent).
                itself needs OpenFOAM + Eigen3 + GSL and cannot be built here.
   * `qmom`   : the second half of the metric (QMOM 6 moments, BASELINE configs[1], 1e7 cells / GPU)
                with its own value / roofline, measured after the MOC region.
+  * `mom`    : methodOfMoments (first slice): pbe_mom_step on 2e5 cells / GPU with
+               the CT kernels at O(1) scales, FP64 roofline by the SURVEY flop convention.
 """
 from __future__ import annotations
 
@@ -540,6 +542,45 @@ def run_b200(args):
             del mp, sp, Sh
         del m0, mq, Sq, flush
 
+    # ---- methodOfMoments (first slice) -----------------------------------------
+    mom_leg = None
+    if not args.no_mom:
+        mc = int(args.mom_cells)
+        rng = np.random.default_rng(20240611 + rank)
+        gm0, gk, gth = rng.uniform(0.5, 3.0, mc), rng.uniform(1.5, 4.0, mc), rng.uniform(0.15, 0.6, mc)
+        mm0 = torch.from_numpy(np.stack([gm0, gm0 * gk * gth, gm0 * gk * (gk + 1) * gth ** 2])).to(dev)
+        me, mr, mn = (torch.from_numpy(rng.uniform(lo, hi, mc)).to(dev)
+                      for lo, hi in ((0.5, 2.0), (0.8, 1.2), (0.5, 1.5)))
+        ct1 = (1.0, 1.0, 0.0, 1.0)  # O(1) scales: where integrate()'s epsabs 1e-7 means something
+        mom = engine.MOM(ctx, engine.make_spec("CoulaloglouTavlaridesC", ct1, "CoulaloglouTavlarides", ct1))
+        mwork, md = mm0.clone(), torch.empty(mc, dtype=torch.float64, device=dev)
+        for _ in range(3):
+            mwork.copy_(mm0)
+            mom.step(mwork, me, mr, mn, 1e-3, d=md)
+        barrier()
+        tot, msteps = 0.0, min(5, max(3, args.steps))
+        for _ in range(msteps):
+            mwork.copy_(mm0)
+            e0.record()
+            mom.step(mwork, me, mr, mn, 1e-3, d=md)
+            e1.record()
+            torch.cuda.synchronize()
+            tot += e0.elapsed_time(e1)
+        mms = allmax(tot / msteps)
+        nq = 15 * (12 + 20)
+        # convention of SURVEY 8(d): exp = 32, sqrt / div = 1, FMA = 2; per unordered node pair of the CT
+        # kernel 4 add + 7 mul + sqrt + div + exp + 2 FMA = 49; per node the gamma pdf (log, exp, 4) = 68
+        mflops = 49.0 * (nq * (nq + 1) / 2) + 68.0 * nq
+        mtf = mc * mflops / (mms * 1e-3) / 1e12
+        mom_leg = {"metric": "mom3_cell_updates_per_s", "value": world * mc / (mms * 1e-3), "unit": "cell-updates/s",
+                   "ms_per_step": mms, "cells_per_gpu": mc, "quadrature_nodes": nq,
+                   "workload": "methodOfMoments: gamma closure + coalescence / breakup source integrals (CT kernels, "
+                               "O(1) scales) on the fixed graded Gauss-Kronrod rule + scrub/update/clamp/d",
+                   "l2": "compute-bound: 56 B per cell of HBM traffic, no flush needed",
+                   "roofline": {"bound": "fp64", "achieved": mtf, "peak": fp64_tf, "unit": "TFLOP/s",
+                                "frac": mtf / fp64_tf, "flops_per_cell": mflops, "traffic": None}}
+        del mm0, mwork
+
     # ---- transport of the class fields (first slice) --------------------------
     transport = None
     if not args.no_transport:
@@ -683,7 +724,7 @@ def run_b200(args):
                                       if world > 1 else "1 GPU",
                        "device": info["name"], "sm_count": info["sm_count"]},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-            "cpu_baseline": cpu, "qmom": qmom, "transport": transport,
+            "cpu_baseline": cpu, "qmom": qmom, "transport": transport, "mom": mom_leg,
             "checks": {"n_min_after_steps": n_min, "global_moments": gmom, "input_fill_s": t_gen},
         }
         print(json.dumps(line), flush=True)
@@ -706,6 +747,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-qmom", action="store_true")
     ap.add_argument("--no-transport", action="store_true")
+    ap.add_argument("--no-mom", action="store_true")
+    ap.add_argument("--mom-cells", type=float, default=200000, help="methodOfMoments leg: cells per GPU")
     ap.add_argument("--halo-nccl", action="store_true", help="transport leg: NCCL send/recv halo exchange")
     ap.add_argument("--transport-n", type=int, default=160, help="transport leg: hex block of n^3 cells")
     ap.add_argument("--no-cpu", action="store_true")
