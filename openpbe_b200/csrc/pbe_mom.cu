@@ -13,8 +13,9 @@
 // here): the tests compare against nested adaptive QUADPACK QAGI integrals in the reference's
 // shape and against closed forms for the cell-independent kernels (tests/test_mom.py).
 //
-// One warp per cell: lanes split the outer nodes, the inner loop runs over the warp's
-// shared-memory copy of the cell's weighted density at the nodes.
+// One warp per two cells: lanes split the outer nodes, the inner loop runs over the warp's
+// shared-memory copies of the cells' weighted density at the nodes; the cell-independent factors
+// of the CT coalescence kernel come from a per-handle pair table.
 #include <algorithm>
 
 #include "pbe_common.h"
@@ -26,6 +27,7 @@ struct pbe_mom {
     pbe_ctx *ctx = nullptr;
     int panels = 0;
     DevKernelSpec ks{};
+    double *pair_tab = nullptr; // device, owned
 };
 
 namespace {
@@ -64,6 +66,7 @@ struct MomParams {
     double dt;
     int do_step;
     int panels;
+    const double *pair_tab; // CT coalescence: G, H of every node pair, [2][nq][nq], or NULL
     DevKernelSpec ks;
 };
 
@@ -82,7 +85,51 @@ struct GammaPdf {
     }
 };
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32) mom_kernel(MomParams p) {
+// node q of the rule: panels in u = 1 - t: [h, 1) in P - 1 equal panels, [0, h) bisected
+// PBE_MOM_GRADED_LEVELS times towards u = 0 (x = 0), where the gamma density behaves like
+// x^(k-1) -- the panels an adaptive QAGIU run ends up with for non-integer shapes
+__device__ __forceinline__ void mom_node(int P, int q, double &x, double &w) {
+    const double h = 1.0 / P;
+    const int panel = q / 15, j = q - 15 * panel;
+    double lo, hi;
+    if (panel < P - 1) {
+        lo = (panel + 1) * h;
+        hi = (panel + 2) * h;
+    } else {
+        const int l = panel - (P - 1);
+        hi = ldexp(h, -l);
+        lo = (l < PBE_MOM_GRADED_LEVELS) ? ldexp(h, -(l + 1)) : 0.0;
+    }
+    const double uc = 0.5 * (lo + hi), uh = 0.5 * (hi - lo);
+    const double u = uc + uh * GK15_X[j];
+    const double t = 1.0 - u;
+    x = u / t;
+    w = GK15_W[j] * uh / (t * t);
+}
+
+// The CT coalescence kernel factorises into per-cell and per-pair parts, S = A_c G_ab
+// exp(negK_c H_ab) (pbe_kernels.cuh coal_ct; the form the MOC kernel tabulates per class pair):
+// G and H of every node pair are cell-independent and built once per handle, laid out [b][a]
+// so that the lanes of a warp (consecutive a) read consecutive addresses.  3.7 MB at 480
+// nodes: resident in the 126 MB L2.
+__global__ void mom_pair_table_kernel(int P, int nq, double *__restrict__ tab) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)nq * nq) return;
+    const int a = (int)(idx % nq), b = (int)(idx / nq);
+    double xa, xb, w;
+    mom_node(P, a, xa, w);
+    mom_node(P, b, xb, w);
+    const NodeRoots na = node_roots(xa), nb = node_roots(xb);
+    const double sab = na.a + nb.a;
+    const double hh = na.a * nb.a / sab;
+    const double h2 = hh * hh;
+    tab[idx] = (sab * sab) * sqrt(na.p + nb.p);
+    tab[(int64_t)nq * nq + idx] = h2 * h2;
+}
+
+// NC cells per warp share every table / node load of the pair sweep
+template <int NC>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, NC == 1 ? 6 : 3) mom_kernel(MomParams p) {
     extern __shared__ double sh[];
     const int P = p.panels, npan = P + PBE_MOM_GRADED_LEVELS;
     const int nq = 15 * npan;
@@ -91,47 +138,37 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) mom_kernel(MomParams p) {
     double *ra = wq + nq;       // x^(1/3)
     double *rp = ra + nq;       // x^(2/9)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    double *fq = rp + nq + (size_t)warp * nq; // this warp's cell: wq * m0 * pdf(x)
+    double *fq = rp + nq + (size_t)warp * NC * nq; // this warp's cells: wq * m0 * pdf(x)
 
-    // panels in u = 1 - t: [h, 1) in P - 1 equal panels, [0, h) bisected PBE_MOM_GRADED_LEVELS
-    // times towards u = 0 (x = 0), where the gamma density behaves like x^(k-1) -- the panels an
-    // adaptive QAGIU run ends up with for non-integer shapes
-    const double h = 1.0 / P;
     for (int q = threadIdx.x; q < nq; q += blockDim.x) {
-        const int panel = q / 15, j = q - 15 * panel;
-        double lo, hi;
-        if (panel < P - 1) {
-            lo = (panel + 1) * h;
-            hi = (panel + 2) * h;
-        } else {
-            const int l = panel - (P - 1);
-            hi = ldexp(h, -l);
-            lo = (l < PBE_MOM_GRADED_LEVELS) ? ldexp(h, -(l + 1)) : 0.0;
-        }
-        const double uc = 0.5 * (lo + hi), uh = 0.5 * (hi - lo);
-        const double u = uc + uh * GK15_X[j];
-        const double t = 1.0 - u;
-        const double x = u / t;
+        double x, w;
+        mom_node(P, q, x, w);
         xq[q] = x;
-        wq[q] = GK15_W[j] * uh / (t * t);
+        wq[q] = w;
         const NodeRoots r = node_roots(x);
         ra[q] = r.a;
         rp[q] = r.p;
     }
     __syncthreads();
 
+    const bool use_tab = (p.ks.coal == PBE_COAL_CT) && p.pair_tab != nullptr;
     const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerCta;
-    for (int64_t c = (int64_t)blockIdx.x * kWarpsPerCta + warp; c < p.ncells; c += nwarps) {
-        const double m0 = p.m_in[c], m1 = p.m_in[p.stride + c], m2 = p.m_in[2 * p.stride + c];
-        // MOM.C:151-161
-        const double var = m2 * m0 - m1 * m1;
-        const double gk = (m1 * m1) / (var + kSmall);
-        const double gtheta = (m0 * m2 - m1 * m1) / fmax(m0 * m1, kSmall);
-        const GammaPdf pdf(gk, gtheta);
-        const CellCoef cc = cell_coef(p.ks, p.eps[c], p.rho[c], p.nu[c]);
-
+    for (int64_t cb = ((int64_t)blockIdx.x * kWarpsPerCta + warp) * NC; cb < p.ncells; cb += nwarps * NC) {
+        double m0[NC], m1[NC], m2[NC], gk[NC], gtheta[NC];
+        CellCoef cc[NC];
         __syncwarp();
-        for (int q = lane; q < nq; q += 32) fq[q] = wq[q] * (m0 * pdf(xq[q]));
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+            const int64_t c = (cb + i < p.ncells) ? cb + i : p.ncells - 1; // odd tail: recomputed, not written
+            m0[i] = p.m_in[c], m1[i] = p.m_in[p.stride + c], m2[i] = p.m_in[2 * p.stride + c];
+            // MOM.C:151-161
+            const double var = m2[i] * m0[i] - m1[i] * m1[i];
+            gk[i] = (m1[i] * m1[i]) / (var + kSmall);
+            gtheta[i] = (m0[i] * m2[i] - m1[i] * m1[i]) / fmax(m0[i] * m1[i], kSmall);
+            const GammaPdf pdf(gk[i], gtheta[i]);
+            cc[i] = cell_coef(p.ks, p.eps[c], p.rho[c], p.nu[c]);
+            for (int q = lane; q < nq; q += 32) fq[i * nq + q] = wq[q] * (m0[i] * pdf(xq[q]));
+        }
         __syncwarp();
 
         // Coalescence (MOM.C:278-308), birth / 2 - death.  Every built-in kernel is symmetric in
@@ -143,58 +180,106 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) mom_kernel(MomParams p) {
         //   int_0^inf moment(xi', k) g(xi') n(xi') dxi',  moment = int_0^xi' xi^k beta dxi = 2 xi'^k / (k+1)
         // (daughterParticleDistribution::moment, uniformBinaryBreakup.C:62-69 -- the form
         // QMOM.C:252-262 uses), one pass over the nodes instead of a nested integral per node.
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+        double s0[NC], s1[NC], s2[NC];
+#pragma unroll
+        for (int i = 0; i < NC; ++i) s0[i] = s1[i] = s2[i] = 0.0;
         for (int a = lane; a < nq; a += 32) {
-            const double xa = xq[a], fa = fq[a];
+            const double xa = xq[a];
             const NodeRoots na{ra[a], rp[a]};
             if (p.ks.coal != PBE_COAL_NONE) {
-                double c0 = 0.0, c2 = 0.0;
-                for (int b = 0; b < a; ++b) {
-                    const NodeRoots nb{ra[b], rp[b]};
-                    const double t = fq[b] * coal_S(p.ks, cc, na, nb);
-                    c0 += t;
-                    c2 = fma_(t, xq[b], c2);
+                double c0[NC], c2[NC];
+#pragma unroll
+                for (int i = 0; i < NC; ++i) c0[i] = c2[i] = 0.0;
+                if (use_tab) {
+                    const double *Gt = p.pair_tab + a, *Ht = Gt + (size_t)nq * nq;
+#pragma unroll 4
+                    for (int b = 0; b < a; ++b) {
+                        const double G = __ldg(Gt + (size_t)b * nq), H = __ldg(Ht + (size_t)b * nq);
+                        const double xb = xq[b];
+#pragma unroll
+                        for (int i = 0; i < NC; ++i) {
+                            const double t = (fq[i * nq + b] * G) * exp(cc[i].negK * H);
+                            c0[i] += t;
+                            c2[i] = fma_(t, xb, c2[i]);
+                        }
+                    }
+                    const double G = __ldg(Gt + (size_t)a * nq), H = __ldg(Ht + (size_t)a * nq);
+#pragma unroll
+                    for (int i = 0; i < NC; ++i) { // pair (a, a) counts once
+                        const double t = 0.5 * ((fq[i * nq + a] * G) * exp(cc[i].negK * H));
+                        c0[i] = (c0[i] + t) * cc[i].A;
+                        c2[i] = fma_(t, xa, c2[i]) * cc[i].A;
+                    }
+                } else {
+                    for (int b = 0; b < a; ++b) {
+                        const NodeRoots nb{ra[b], rp[b]};
+                        const double xb = xq[b];
+#pragma unroll
+                        for (int i = 0; i < NC; ++i) {
+                            const double t = fq[i * nq + b] * coal_S(p.ks, cc[i], na, nb);
+                            c0[i] += t;
+                            c2[i] = fma_(t, xb, c2[i]);
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < NC; ++i) {
+                        const double t = 0.5 * (fq[i * nq + a] * coal_S(p.ks, cc[i], na, na));
+                        c0[i] += t;
+                        c2[i] = fma_(t, xa, c2[i]);
+                    }
                 }
-                const double tdiag = 0.5 * (fa * coal_S(p.ks, cc, na, na)); // pair (a, a) counts once
-                c0 += tdiag;
-                c2 = fma_(tdiag, xa, c2);
-                s0 = fma_(-fa, c0, s0);             // 2 * (-1/2) * fa * sum_b
-                s2 = fma_(2.0 * (fa * xa), c2, s2);
+#pragma unroll
+                for (int i = 0; i < NC; ++i) {
+                    const double fa = fq[i * nq + a];
+                    s0[i] = fma_(-fa, c0[i], s0[i]); // 2 * (-1/2) * fa * sum_b
+                    s2[i] = fma_(2.0 * (fa * xa), c2[i], s2[i]);
+                }
             }
             if (p.ks.br != PBE_BR_NONE) {
-                const double gn = break_S(p.ks, cc, xa, na) * fa;
-                s0 += gn * (daughter_moment_from_pow(1.0, 0) - 1.0);
-                s1 = fma_(xa * gn, daughter_moment_from_pow(1.0, 1) - 1.0, s1);
-                s2 = fma_(xa * xa * gn, daughter_moment_from_pow(1.0, 2) - 1.0, s2);
+#pragma unroll
+                for (int i = 0; i < NC; ++i) {
+                    const double gn = break_S(p.ks, cc[i], xa, na) * fq[i * nq + a];
+                    s0[i] += gn * (daughter_moment_from_pow(1.0, 0) - 1.0);
+                    s1[i] = fma_(xa * gn, daughter_moment_from_pow(1.0, 1) - 1.0, s1[i]);
+                    s2[i] = fma_(xa * xa * gn, daughter_moment_from_pow(1.0, 2) - 1.0, s2[i]);
+                }
             }
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            s0 += __shfl_xor_sync(0xffffffffu, s0, o);
-            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        for (int i = 0; i < NC; ++i) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                s0[i] += __shfl_xor_sync(0xffffffffu, s0[i], o);
+                s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], o);
+                s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], o);
+            }
         }
         if (lane == 0) {
-            double S[3] = {s0, s1, s2};
-            if (p.gamma_out) {
-                p.gamma_out[c] = m0;
-                p.gamma_out[p.stride + c] = gk;
-                p.gamma_out[2 * p.stride + c] = gtheta;
-            }
-            if (p.do_step) {
-                double m[3] = {m0, m1, m2};
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    if (isnan(S[k])) S[k] = 0.0;                   // MOM.C:198-207
-                    const double v = fma_(p.dt, S[k], m[k]);       // ddt(m) = S, zero flux
-                    m[k] = (v > kSmall) ? v : kSmall;              // MOM.C:224-231
-                    p.m_out[k * p.stride + c] = m[k];
+            for (int i = 0; i < NC; ++i) {
+                const int64_t c = cb + i;
+                if (c >= p.ncells) break;
+                double S[3] = {s0[i], s1[i], s2[i]};
+                if (p.gamma_out) {
+                    p.gamma_out[c] = m0[i];
+                    p.gamma_out[p.stride + c] = gk[i];
+                    p.gamma_out[2 * p.stride + c] = gtheta[i];
                 }
-                if (p.d_out) p.d_out[c] = cbrt(6.0 / 3.14159265358979323846 * m[1] / m[0]); // MOM.C:233
-            }
-            if (p.S_out) {
+                if (p.do_step) {
+                    double m[3] = {m0[i], m1[i], m2[i]};
 #pragma unroll
-                for (int k = 0; k < 3; ++k) p.S_out[k * p.stride + c] = S[k];
+                    for (int k = 0; k < 3; ++k) {
+                        if (isnan(S[k])) S[k] = 0.0;                   // MOM.C:198-207
+                        const double v = fma_(p.dt, S[k], m[k]);       // ddt(m) = S, zero flux
+                        m[k] = (v > kSmall) ? v : kSmall;              // MOM.C:224-231
+                        p.m_out[k * p.stride + c] = m[k];
+                    }
+                    if (p.d_out) p.d_out[c] = cbrt(6.0 / 3.14159265358979323846 * m[1] / m[0]); // MOM.C:233
+                }
+                if (p.S_out) {
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) p.S_out[k * p.stride + c] = S[k];
+                }
             }
         }
     }
@@ -214,12 +299,19 @@ int launch_mom(pbe_mom *h, MomParams &p, cudaStream_t st) {
     if (p.ncells == 0) return PBE_OK;
     p.panels = h->panels;
     p.ks = h->ks;
+    p.pair_tab = h->pair_tab;
     const int nq = 15 * (h->panels + PBE_MOM_GRADED_LEVELS);
-    const size_t smem = (size_t)(4 + kWarpsPerCta) * nq * sizeof(double);
-    // one warp per cell; 8 CTAs of 4 warps per SM, grid-stride beyond that
-    const int64_t ctas = (p.ncells + kWarpsPerCta - 1) / kWarpsPerCta;
+    // CT coalescence (pair table): two cells per warp share every table load; the cell-independent
+    // kernels have nothing to share and run one cell per warp (measured: 13.8 vs 85 ms per 4e5 cells)
+    const int NC = h->pair_tab ? 2 : 1;
+    const size_t smem = (size_t)(4 + NC * kWarpsPerCta) * nq * sizeof(double);
+    // up to 8 CTAs of 4 warps per SM, grid-stride beyond that
+    const int64_t ctas = (p.ncells + NC * kWarpsPerCta - 1) / (NC * kWarpsPerCta);
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, (int64_t)h->ctx->sm_count * 8));
-    mom_kernel<<<grid, kWarpsPerCta * 32, smem, st>>>(p);
+    if (NC == 2)
+        mom_kernel<2><<<grid, kWarpsPerCta * 32, smem, st>>>(p);
+    else
+        mom_kernel<1><<<grid, kWarpsPerCta * 32, smem, st>>>(p);
     PBE_CUDA(cudaGetLastError());
     h->ctx->launches++;
     return PBE_OK;
@@ -249,11 +341,38 @@ int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mo
     h->ctx = ctx;
     h->panels = panels;
     h->ks = make_dev_spec(*spec);
+    DeviceGuard g(ctx->device);
+    const int nq = 15 * (panels + PBE_MOM_GRADED_LEVELS);
+    // 12 rows of nq doubles per CTA (4 node tables + 2 cells x 4 warps): above 48 KB from 33 panels on
+    cudaError_t e = cudaFuncSetAttribute(mom_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)((4 + 2 * kWarpsPerCta) * nq * sizeof(double)));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(mom_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)((4 + kWarpsPerCta) * nq * sizeof(double)));
+    if (e == cudaSuccess && spec->coalescence == PBE_COAL_CT) {
+        e = cudaMalloc(&h->pair_tab, (size_t)2 * nq * nq * sizeof(double));
+        if (e == cudaSuccess) {
+            const int64_t n = (int64_t)nq * nq;
+            mom_pair_table_kernel<<<(unsigned)((n + 255) / 256), 256>>>(panels, nq, h->pair_tab);
+            e = cudaGetLastError();
+            if (e == cudaSuccess) e = cudaDeviceSynchronize();
+            ctx->launches++;
+        }
+    }
+    if (e != cudaSuccess) {
+        if (h->pair_tab) cudaFree(h->pair_tab);
+        delete h;
+        return cuda_fail(e, "pbe_mom_create", __FILE__, __LINE__);
+    }
     *out = h;
     return PBE_OK;
 }
 
 int pbe_mom_destroy(pbe_mom *h) {
+    if (h && h->pair_tab) {
+        DeviceGuard g(h->ctx->device);
+        cudaFree(h->pair_tab);
+    }
     delete h;
     return PBE_OK;
 }
