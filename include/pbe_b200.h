@@ -144,6 +144,7 @@ typedef struct pbe_qmom pbe_qmom;
 
 int pbe_qmom_create(pbe_ctx *ctx, int order, const pbe_kernel_spec *spec, pbe_qmom **out);
 int pbe_qmom_destroy(pbe_qmom *q);
+int pbe_qmom_order(pbe_qmom *q, int *order, pbe_ctx **ctx); /* QMOMCoeffs.quadratureOrder */
 
 /* S[k][c] for k < 2*order, NOT NaN-scrubbed (as momentSourceTerm returns it, QMOM.C:215-267).
  * The inversion is done once per cell and reused for every k. */
@@ -242,6 +243,8 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
  * kernel (cell chunks), downloads overlap the transport kernels (field chunks); the fields stay
  * on the device in between.  Synchronous on return. */
 int pbe_moc_num_classes(pbe_moc *moc, int *N, pbe_ctx **ctx);
+/* MOCCoeffs of the handle: xi1 (MOC.C:56) and sourceRelaxation (MOC.C:60); either may be NULL */
+int pbe_moc_coeffs(pbe_moc *moc, double *xi1, double *source_relaxation);
 int pbe_moc_correct_host(pbe_moc *moc, pbe_mesh *mesh, int scheme, int64_t stride, double *n_host,
                          const double *eps_host, const double *rho_host, const double *nu_host,
                          const double *phi_host, const double *psi_b_host, int64_t stride_b,
@@ -280,6 +283,93 @@ int pbe_transport_explicit_part(pbe_mesh *mesh, int scheme, int which, int nfiel
                                 const double *S, double dt, double *psi_out, void *cuda_stream);
 
 /* ======================================================================================= */
+/* Resident state -- correct() the way the reference's solver sees it.  The reference's     */
+/* methods OWN their class / moment fields (PtrList<volScalarField> classNumberDensity_,     */
+/* src/PBESystem/MOC.H:66, read MUST_READ at construction MOC.C:69-77, written by            */
+/* runTime.write(); QMOM.H:62, QMOM.C:72-79); once per time step the solver calls            */
+/* PBEDiameter::correct() { method_->correct(); d_ = method_->d(); } (PBEDiameter.H:95-99,   */
+/* applications/PBEFoam/PBEFoam.C:56-67) and reads only d.  A pbe_*_state is that owned     */
+/* state on the device: per step only this step's phase fields go in (epsilon, rho, nu,      */
+/* alpha: 32 B/cell, plus the face flux when a mesh is attached) and d comes out (8 B/cell); */
+/* the class / moment fields cross the bus at construction and at write time only.           */
+/* ======================================================================================= */
+typedef struct pbe_moc_state pbe_moc_state;
+
+/* vcell_host [ncells] = mesh.V() (continuity check, global moments) or NULL.  The state
+ * allocates n [N][ncells] and the per-cell rows on the method's device, plus one event pool. */
+int pbe_moc_state_create(pbe_moc *moc, int64_t ncells, const double *vcell_host,
+                         pbe_moc_state **out);
+int pbe_moc_state_destroy(pbe_moc_state *st);
+/* construction: the MUST_READ fields n0..n{N-1} (MOC.C:69-77), host [N][stride] */
+int pbe_moc_state_upload(pbe_moc_state *st, int64_t stride, const double *n_host);
+/* runTime.write(): the AUTO_WRITE fields back to the host, [N][stride] */
+int pbe_moc_state_download(pbe_moc_state *st, int64_t stride, double *n_host);
+/* the same for the cell range [cell0, cell0 + count) only: n_host [N][stride] holds those cells
+ * (construction / write-out in pieces when the host cannot hold all class fields at once) */
+int pbe_moc_state_upload_range(pbe_moc_state *st, int64_t cell0, int64_t count, int64_t stride,
+                               const double *n_host);
+int pbe_moc_state_download_range(pbe_moc_state *st, int64_t cell0, int64_t count, int64_t stride,
+                                 double *n_host);
+/* MOC::d() of the CURRENT fields (PBEDiameter's constructor, PBEDiameter.C:64-75) -> host */
+int pbe_moc_state_d(pbe_moc_state *st, double *d_host);
+/* device views for callers that chain their own device work: n [N][*stride], d [ncells] */
+int pbe_moc_state_device(pbe_moc_state *st, double **n_dev, int64_t *stride, double **d_dev);
+/* MOC::solveWithMULES (MOC.C:198-272) instead of the zero-flux update: the mesh's face
+ * addressing and the div(phi,n.*) scheme; correct_resident then wants phi_host. */
+int pbe_moc_state_attach_mesh(pbe_moc_state *st, pbe_mesh *mesh, int scheme);
+
+/* What MOC::correct() prints every step (MOC.C:181-183, 276-279) plus configs[3]'s global
+ * moments.  HOST memory; the caller all-reduces across ranks (pbe_comm_*). */
+typedef struct pbe_moc_diag {
+    double *class_min;   /* [N] or NULL: min over this rank's cells of n_k        (MOC.C:181-183) */
+    double *class_max;   /* [N] or NULL                                           (MOC.C:238)     */
+    double cont_err_max; /* out: max_c |sum_k xi_k n_k / V - alpha| (needs alpha) (MOC.C:276-279) */
+    int n_moments;       /* in: 0..8 */
+    double moments[8];   /* out: sum_c V_c sum_i xi_i^k n_i[c] over this rank's cells (needs vcell) */
+} pbe_moc_diag;
+
+/* One MOC::correct() + d(): HOST eps, rho, nu, alpha [ncells] in, HOST d [ncells] out.
+ * rho_host / nu_host may be NULL after the first call: the values of the previous call are kept
+ * (constant-property phases).  alpha_host NULL: no continuity check.  phi_host [internal +
+ * boundary faces] and psi_b_host [N][stride_b] (NULL = zero-gradient patches) only with an
+ * attached mesh.  d_host NULL leaves d on the device.  Cells are processed in chunks: the
+ * uploads of chunk k+1 and the download of d for chunk k-1 overlap the kernel of chunk k.
+ * Pinned host memory (pbe_host_alloc / pbe_host_register) gives full PCIe rate and true overlap.
+ * Synchronous on return. */
+int pbe_moc_correct_resident(pbe_moc_state *st, const double *eps_host, const double *rho_host,
+                             const double *nu_host, const double *alpha_host,
+                             const double *phi_host, const double *psi_b_host, int64_t stride_b,
+                             double dt, double *d_host, pbe_moc_diag *diag);
+
+typedef struct pbe_qmom_state pbe_qmom_state;
+int pbe_qmom_state_create(pbe_qmom *q, int64_t ncells, const double *vcell_host,
+                          pbe_qmom_state **out);
+int pbe_qmom_state_destroy(pbe_qmom_state *st);
+int pbe_qmom_state_upload(pbe_qmom_state *st, int64_t stride, const double *m_host);  /* QMOM.C:72-79 */
+int pbe_qmom_state_download(pbe_qmom_state *st, int64_t stride, double *m_host);
+int pbe_qmom_state_d(pbe_qmom_state *st, double *d_host); /* d = (6/pi m1/m0)^(1/3), QMOM.C:81 */
+int pbe_qmom_state_device(pbe_qmom_state *st, double **m_dev, int64_t *stride, double **d_dev,
+                          double **S_dev);
+int pbe_qmom_state_attach_mesh(pbe_qmom_state *st, pbe_mesh *mesh, int scheme);
+
+/* printAvgMaxMin (Utility.C:4-10) of what QMOM::correct() prints each step: per moment source
+ * (QMOM.C:109), per moment (QMOM.C:122) and d (QMOM.C:128).  Each entry is {sum f V, sum V, max,
+ * min} over this rank's cells (V = 1 without vcell); avg = [0] / [1] after the cross-rank
+ * reduction.  Pointers are HOST arrays or NULL (not wanted). */
+typedef struct pbe_qmom_diag {
+    double *source; /* [2*order][4] */
+    double *moment; /* [2*order][4] */
+    double *d;      /* [4] */
+} pbe_qmom_diag;
+
+/* One QMOM::correct() (QMOM.C:85-129): sources, NaN scrub, update (zero flux, or transport with
+ * an attached mesh), clamp to SMALL, d.  Argument conventions as pbe_moc_correct_resident. */
+int pbe_qmom_correct_resident(pbe_qmom_state *st, const double *eps_host, const double *rho_host,
+                              const double *nu_host, const double *phi_host,
+                              const double *psi_b_host, int64_t stride_b, double dt,
+                              double *d_host, pbe_qmom_diag *diag);
+
+/* ======================================================================================= */
 /* Scalar kernel functors evaluated ON THE DEVICE (batched) -- the reference's Foam-free     */
 /* *Impl::S surface (coalescenceKernels/CoulaloglouTavlarides.H:44-63, breakupKernels/       */
 /* CoulaloglouTavlarides.H:46-60; exported to Python by bindings/kernels.cpp:9-40).          */
@@ -312,6 +402,10 @@ int pbe_device_alloc(pbe_ctx *ctx, int64_t bytes, void **out);
 int pbe_device_free(pbe_ctx *ctx, void *p);
 int pbe_host_alloc(pbe_ctx *ctx, int64_t bytes, void **out); /* pinned */
 int pbe_host_free(pbe_ctx *ctx, void *p);
+/* page-lock memory the caller already owns (an OpenFOAM field's storage) so that the *_resident
+ * and *_host entries copy it at full PCIe rate and asynchronously */
+int pbe_host_register(pbe_ctx *ctx, void *p, int64_t bytes);
+int pbe_host_unregister(pbe_ctx *ctx, void *p);
 int pbe_memcpy_h2d(pbe_ctx *ctx, void *dst, const void *src, int64_t bytes);
 int pbe_memcpy_d2h(pbe_ctx *ctx, void *dst, const void *src, int64_t bytes);
 int pbe_memset(pbe_ctx *ctx, void *dst, int value, int64_t bytes);

@@ -55,6 +55,24 @@ class MocIO(C.Structure):
     ]
 
 
+class MocDiag(C.Structure):
+    """struct pbe_moc_diag (host pointers)"""
+
+    _fields_ = [
+        ("class_min", _vp),
+        ("class_max", _vp),
+        ("cont_err_max", C.c_double),
+        ("n_moments", C.c_int),
+        ("moments", C.c_double * 8),
+    ]
+
+
+class QmomDiag(C.Structure):
+    """struct pbe_qmom_diag (host pointers)"""
+
+    _fields_ = [("source", _vp), ("moment", _vp), ("d", _vp)]
+
+
 class PbeError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"libpbe_b200 error {code}: {msg}")
@@ -104,6 +122,30 @@ PROTOTYPES = {
     "pbe_transport_explicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
                                          C.c_double, _vp, _vp]),
     "pbe_moc_num_classes": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(_vp)]),
+    "pbe_moc_coeffs": (C.c_int, [_vp, _dp, _dp]),
+    "pbe_qmom_order": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(_vp)]),
+    "pbe_moc_state_create": (C.c_int, [_vp, _i64, _vp, C.POINTER(_vp)]),
+    "pbe_moc_state_destroy": (C.c_int, [_vp]),
+    "pbe_moc_state_upload": (C.c_int, [_vp, _i64, _vp]),
+    "pbe_moc_state_download": (C.c_int, [_vp, _i64, _vp]),
+    "pbe_moc_state_upload_range": (C.c_int, [_vp, _i64, _i64, _i64, _vp]),
+    "pbe_moc_state_download_range": (C.c_int, [_vp, _i64, _i64, _i64, _vp]),
+    "pbe_moc_state_d": (C.c_int, [_vp, _vp]),
+    "pbe_moc_state_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_i64), C.POINTER(_vp)]),
+    "pbe_moc_state_attach_mesh": (C.c_int, [_vp, _vp, C.c_int]),
+    "pbe_moc_correct_resident": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_double, _vp,
+                                           C.POINTER(MocDiag)]),
+    "pbe_qmom_state_create": (C.c_int, [_vp, _i64, _vp, C.POINTER(_vp)]),
+    "pbe_qmom_state_destroy": (C.c_int, [_vp]),
+    "pbe_qmom_state_upload": (C.c_int, [_vp, _i64, _vp]),
+    "pbe_qmom_state_download": (C.c_int, [_vp, _i64, _vp]),
+    "pbe_qmom_state_d": (C.c_int, [_vp, _vp]),
+    "pbe_qmom_state_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_i64), C.POINTER(_vp), C.POINTER(_vp)]),
+    "pbe_qmom_state_attach_mesh": (C.c_int, [_vp, _vp, C.c_int]),
+    "pbe_qmom_correct_resident": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_double, _vp,
+                                            C.POINTER(QmomDiag)]),
+    "pbe_host_register": (C.c_int, [_vp, _vp, _i64]),
+    "pbe_host_unregister": (C.c_int, [_vp, _vp]),
     "pbe_moc_correct_host": (C.c_int, [_vp, _vp, C.c_int, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64,
                                        C.c_double, _vp]),
     "pbe_field_scrub_nan": (C.c_int, [_vp, _i64, _vp, _vp]),

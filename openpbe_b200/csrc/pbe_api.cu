@@ -34,6 +34,20 @@ int ensure_stage(pbe_ctx *ctx, size_t bytes_per_slot) {
     return PBE_OK;
 }
 
+cudaError_t raise_dyn_smem(pbe_ctx *ctx, const void *fn, size_t bytes) {
+    std::lock_guard<std::mutex> lk(ctx->smem_mu);
+    size_t &cur = ctx->smem_limit[fn];
+    if (bytes <= cur) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) cur = bytes;
+    return e;
+}
+
+void drain_slot_streams(pbe_ctx *ctx) {
+    for (int s = 0; s < kHostSlots; ++s)
+        if (ctx->slot_stream[s]) cudaStreamSynchronize(ctx->slot_stream[s]);
+}
+
 // ---- FP64 peak: 8 independent DFMA chains per thread, register resident -------------------
 __global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, int iters, double a, double b) {
     double x0 = threadIdx.x * 1e-3, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5,

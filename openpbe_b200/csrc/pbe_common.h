@@ -7,6 +7,8 @@
 #include <stdio.h>
 
 #include <atomic>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -48,10 +50,20 @@ struct pbe_ctx {
     // staging for the host-buffer entry points (grown on demand, freed with the context)
     void *stage[pbe::kHostSlots] = {nullptr, nullptr, nullptr};
     size_t stage_bytes = 0;
+    // cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the kernel instantiation (per device),
+    // not to a handle: the largest request any handle of this context has made so far
+    std::mutex smem_mu;
+    std::map<const void *, size_t> smem_limit;
 };
 
 namespace pbe {
 int ensure_stage(pbe_ctx *ctx, size_t bytes_per_slot);
+// Raise (never lower) the dynamic shared-memory limit of a kernel before a launch that needs
+// `bytes`: handles with different table sizes that share one instantiation stay independent.
+cudaError_t raise_dyn_smem(pbe_ctx *ctx, const void *fn, size_t bytes);
+// Wait for every host-pipeline stream of the context (error paths of the host-buffer entries:
+// asynchronous copies must not outlive the call that was handed the caller's buffers).
+void drain_slot_streams(pbe_ctx *ctx);
 struct DeviceGuard {
     int prev = -1;
     explicit DeviceGuard(int dev) {

@@ -181,12 +181,15 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
         moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr, m->tmem_wide);
         if (m->dcoal == DCOAL_CT) p.pair_tab = m->d_pair_log;
         void *args[] = {(void *)&p, (void *)&m->sched};
+        // another handle of this instantiation may have been created since with a smaller table
+        PBE_CUDA(raise_dyn_smem(m->ctx, (const void *)fn, m->smem));
         PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
         m->ctx->launches++;
         return PBE_OK;
     }
     moc_kernel_fn fn = kernel_for(m);
     void *args[] = {(void *)&p};
+    PBE_CUDA(raise_dyn_smem(m->ctx, (const void *)fn, m->smem));
     PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
     m->ctx->launches++;
     return PBE_OK;
@@ -347,8 +350,7 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
         return PBE_E_UNSUPPORTED;
     }
     moc_kernel_fn fn = kernel_for(m);
-    cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)m->smem_bytes);
+    cudaError_t e = raise_dyn_smem(ctx, (const void *)fn, m->smem_bytes);
     if (e == cudaSuccess) {
         int occ = 0;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, m->smem_block,
@@ -413,7 +415,7 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
         cudaFuncAttributes fa{};
         for (int wide = 1; wide >= 0 && e == cudaSuccess; --wide) {
             tfn = (const void *)pick_tmem_kernel(m->dcoal, m->dbr, wide != 0);
-            e = cudaFuncSetAttribute(tfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m->tmem_bytes);
+            e = raise_dyn_smem(ctx, tfn, m->tmem_bytes);
             if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, tfn);
             if (e != cudaSuccess) break;
             // cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for a kernel that holds a
@@ -457,8 +459,9 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
     }
     if (e == cudaSuccess && m->tmem_ok && m->dcoal == DCOAL_CT) {
         // the tensor-memory kernel folds G into the exponent: S = A 2^(log2 G - K log2(e) H).
-        // Zero-weight padding slots get log2 G = -4096: 2^y is then below 4.5e-308 and is
-        // multiplied by the dummy class density 0.
+        // Zero-weight padding slots get {log2 G, H} = {-4096, 0}: y = -4096 exactly, for which
+        // exp2_neg_tab returns exactly 0 (integer argument below -1023), so a padding slot between
+        // two real classes adds exactly nothing -- as in the shared-memory kernel.
         std::vector<double2> tl(tab.size());
         for (size_t k = 0; k < tab.size(); ++k)
             tl[k] = make_double2(tab[k].x > 0.0 ? std::log2(tab[k].x) : -4096.0, tab[k].y);
@@ -504,6 +507,13 @@ int pbe_moc_num_classes(pbe_moc *m, int *N, pbe_ctx **ctx) {
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_num_classes: NULL handle");
     if (N) *N = m->N;
     if (ctx) *ctx = m->ctx;
+    return PBE_OK;
+}
+
+int pbe_moc_coeffs(pbe_moc *m, double *xi1, double *source_relaxation) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_coeffs: NULL handle");
+    if (xi1) *xi1 = m->xi1;
+    if (source_relaxation) *source_relaxation = m->relax;
     return PBE_OK;
 }
 
@@ -636,8 +646,9 @@ int pbe_moc_source_host(pbe_moc *m, int64_t ncells, int64_t stride, const double
     C = std::min(C, ((ncells + wave - 1) / wave) * wave);
     rc = ensure_stage(ctx, (size_t)C * per_cell);
     if (rc) return rc;
-    int64_t k = 0;
-    for (int64_t c0 = 0; c0 < ncells; c0 += C, ++k) {
+    // one chunk; a failure leaves the loop so that the streams are drained before returning (the
+    // copies already queued still read / write the caller's buffers)
+    auto chunk = [&](int64_t c0, int64_t k) -> int {
         const int64_t nc = std::min(C, ncells - c0);
         const int s = (int)(k % kHostSlots);
         cudaStream_t st = ctx->slot_stream[s];
@@ -651,10 +662,17 @@ int pbe_moc_source_host(pbe_moc *m, int64_t ncells, int64_t stride, const double
         PBE_CUDA(cudaMemcpyAsync(de, eps_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st));
         PBE_CUDA(cudaMemcpyAsync(dr, rho_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st));
         PBE_CUDA(cudaMemcpyAsync(dv, nu_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st));
-        rc = pbe_moc_source(m, nc, C, dn, de, dr, dv, dt, dS, st);
-        if (rc) return rc;
+        int rc2 = pbe_moc_source(m, nc, C, dn, de, dr, dv, dt, dS, st);
+        if (rc2) return rc2;
         PBE_CUDA(cudaMemcpy2DAsync(S_host + c0, (size_t)stride * 8, dS, (size_t)C * 8, (size_t)nc * 8,
                                    N, cudaMemcpyDeviceToHost, st));
+        return PBE_OK;
+    };
+    int64_t k = 0;
+    for (int64_t c0 = 0; c0 < ncells && rc == PBE_OK; c0 += C, ++k) rc = chunk(c0, k);
+    if (rc) {
+        drain_slot_streams(ctx);
+        return rc;
     }
     for (int s = 0; s < kHostSlots; ++s) PBE_CUDA(cudaStreamSynchronize(ctx->slot_stream[s]));
     return PBE_OK;

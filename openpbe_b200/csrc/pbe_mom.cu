@@ -308,6 +308,8 @@ int launch_mom(pbe_mom *h, MomParams &p, cudaStream_t st) {
     // up to 8 CTAs of 4 warps per SM, grid-stride beyond that
     const int64_t ctas = (p.ncells + NC * kWarpsPerCta - 1) / (NC * kWarpsPerCta);
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, (int64_t)h->ctx->sm_count * 8));
+    // the limit belongs to the instantiation: a handle with fewer panels may have been created since
+    PBE_CUDA(raise_dyn_smem(h->ctx, NC == 2 ? (const void *)mom_kernel<2> : (const void *)mom_kernel<1>, smem));
     if (NC == 2)
         mom_kernel<2><<<grid, kWarpsPerCta * 32, smem, st>>>(p);
     else
@@ -344,11 +346,9 @@ int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mo
     DeviceGuard g(ctx->device);
     const int nq = 15 * (panels + PBE_MOM_GRADED_LEVELS);
     // 12 rows of nq doubles per CTA (4 node tables + 2 cells x 4 warps): above 48 KB from 33 panels on
-    cudaError_t e = cudaFuncSetAttribute(mom_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)((4 + 2 * kWarpsPerCta) * nq * sizeof(double)));
+    cudaError_t e = raise_dyn_smem(ctx, (const void *)mom_kernel<2>, (4 + 2 * kWarpsPerCta) * nq * sizeof(double));
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(mom_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)((4 + kWarpsPerCta) * nq * sizeof(double)));
+        e = raise_dyn_smem(ctx, (const void *)mom_kernel<1>, (4 + kWarpsPerCta) * nq * sizeof(double));
     if (e == cudaSuccess && spec->coalescence == PBE_COAL_CT) {
         e = cudaMalloc(&h->pair_tab, (size_t)2 * nq * nq * sizeof(double));
         if (e == cudaSuccess) {

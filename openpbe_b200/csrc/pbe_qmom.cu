@@ -245,6 +245,13 @@ int pbe_qmom_create(pbe_ctx *ctx, int order, const pbe_kernel_spec *spec, pbe_qm
     return PBE_OK;
 }
 
+int pbe_qmom_order(pbe_qmom *q, int *order, pbe_ctx **ctx) {
+    PBE_REQUIRE(q != nullptr, PBE_E_INVALID, "pbe_qmom_order: NULL handle");
+    if (order) *order = q->order;
+    if (ctx) *ctx = q->ctx;
+    return PBE_OK;
+}
+
 int pbe_qmom_destroy(pbe_qmom *q) {
     delete q;
     return PBE_OK;
@@ -313,9 +320,20 @@ int pbe_wheeler_batch(pbe_ctx *ctx, int order, int64_t ncells, int64_t stride, c
     return PBE_OK;
 }
 
+static int qmom_source_host_impl(pbe_qmom *q, int64_t ncells, int64_t stride, const double *m_host,
+                                 const double *eps_host, const double *rho_host, const double *nu_host,
+                                 double *S_host);
 int pbe_qmom_source_host(pbe_qmom *q, int64_t ncells, int64_t stride, const double *m_host,
                          const double *eps_host, const double *rho_host, const double *nu_host,
                          double *S_host) {
+    const int rc = qmom_source_host_impl(q, ncells, stride, m_host, eps_host, rho_host, nu_host, S_host);
+    // a failure mid-pipeline leaves copies queued that still touch the caller's buffers
+    if (rc != PBE_OK && q != nullptr) drain_slot_streams(q->ctx);
+    return rc;
+}
+static int qmom_source_host_impl(pbe_qmom *q, int64_t ncells, int64_t stride, const double *m_host,
+                                 const double *eps_host, const double *rho_host, const double *nu_host,
+                                 double *S_host) {
     int rc = check_q("pbe_qmom_source_host", q, ncells, stride, m_host, eps_host, rho_host, nu_host);
     if (rc) return rc;
     PBE_REQUIRE(ncells == 0 || S_host, PBE_E_INVALID, "pbe_qmom_source_host: S is NULL");

@@ -663,10 +663,24 @@ int pbe_transport_explicit_part(pbe_mesh *m, int scheme, int which, int nfields,
 // it arrives (three streams: copies overlap kernels); n and S stay on the device; the transport
 // update then runs in field chunks, each chunk's new values copied back while the next chunk is
 // being computed.
+static int moc_correct_host_impl(pbe_moc *moc, pbe_mesh *m, int scheme, int64_t stride, double *n_host,
+                                 const double *eps_host, const double *rho_host, const double *nu_host,
+                                 const double *phi_host, const double *psi_b_host, int64_t stride_b, double dt,
+                                 double *d_host);
 int pbe_moc_correct_host(pbe_moc *moc, pbe_mesh *m, int scheme, int64_t stride, double *n_host,
                          const double *eps_host, const double *rho_host, const double *nu_host,
                          const double *phi_host, const double *psi_b_host, int64_t stride_b, double dt,
                          double *d_host) {
+    const int rc = moc_correct_host_impl(moc, m, scheme, stride, n_host, eps_host, rho_host, nu_host, phi_host,
+                                         psi_b_host, stride_b, dt, d_host);
+    // a failure mid-pipeline leaves copies queued that still touch the caller's buffers
+    if (rc != PBE_OK && m != nullptr) drain_slot_streams(m->ctx);
+    return rc;
+}
+static int moc_correct_host_impl(pbe_moc *moc, pbe_mesh *m, int scheme, int64_t stride, double *n_host,
+                                 const double *eps_host, const double *rho_host, const double *nu_host,
+                                 const double *phi_host, const double *psi_b_host, int64_t stride_b, double dt,
+                                 double *d_host) {
     PBE_REQUIRE(moc != nullptr && m != nullptr, PBE_E_INVALID, "pbe_moc_correct_host: NULL handle");
     int N = 0;
     pbe_ctx *mctx = nullptr;

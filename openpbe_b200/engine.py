@@ -17,7 +17,7 @@ import torch
 
 from . import capi
 
-__all__ = ["Context", "MOC", "QMOM", "make_spec", "kernel_types"]
+__all__ = ["Context", "MOC", "QMOM", "MOM", "MOCState", "QMOMState", "Mesh", "make_spec", "kernel_types"]
 
 _dp = C.POINTER(C.c_double)
 
@@ -284,6 +284,168 @@ class MOC:
             self._h, n_.shape[1], n_.stride(0) if n_.shape[1] else 0, _ptr(n_), _ptr(eps_), _ptr(rho_),
             _ptr(nu_), float(dt), _ptr(S)))
         return S
+
+
+class _CudaBuf:
+    """A raw device pointer with the __cuda_array_interface__ torch.as_tensor understands: zero-copy
+    views of memory the library owns (the resident states)."""
+
+    def __init__(self, ptr: int, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": "<f8",
+                                         "data": (int(ptr), False), "version": 2, "strides": None}
+
+
+def _device_view(ptr: int, shape, device: int):
+    if any(int(x) == 0 for x in shape):
+        return torch.empty(tuple(shape), dtype=torch.float64, device=f"cuda:{device}")
+    return torch.as_tensor(_CudaBuf(ptr, shape), device=f"cuda:{device}")
+
+
+def _hptr(t):
+    """host tensor (or None) -> void* for the resident entries"""
+    return None if t is None else C.c_void_p(_as_host(t).data_ptr())
+
+
+class MOCState:
+    """pbe_moc_state: the class fields owned on the device, as PBEMethods::MOC owns
+    classNumberDensity_ (MOC.H:66, MOC.C:69-77); `correct()` is one MOC::correct() + d() with only
+    this step's phase fields crossing the bus (PBEDiameter.H:95-99)."""
+
+    def __init__(self, moc: "MOC", ncells: int, vcell=None, n0=None, mesh: "Mesh" = None, scheme="upwind"):
+        self.moc, self.ncells = moc, int(ncells)
+        self._h = C.c_void_p()
+        self._mesh = mesh  # keep alive
+        capi.check(capi.lib().pbe_moc_state_create(moc._h, self.ncells, _hptr(vcell), C.byref(self._h)))
+        if n0 is not None:
+            self.upload(n0)
+        if mesh is not None:
+            capi.check(capi.lib().pbe_moc_state_attach_mesh(self._h, mesh._h, div_scheme(scheme)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_moc_state_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, n):
+        n_ = _as_host(n)
+        assert n_.shape == (self.moc.N, self.ncells)
+        capi.check(capi.lib().pbe_moc_state_upload(self._h, n_.stride(0) if self.ncells else 0, _ptr_rows(n_)))
+
+    def download(self, out=None):
+        out = torch.empty((self.moc.N, self.ncells), dtype=torch.float64) if out is None else _as_host(out)
+        capi.check(capi.lib().pbe_moc_state_download(self._h, out.stride(0) if self.ncells else 0, _ptr_rows(out)))
+        return out
+
+    def upload_range(self, cell0: int, n):
+        """n [N][count]: the class fields of cells [cell0, cell0 + count)"""
+        n_ = _as_host(n)
+        capi.check(capi.lib().pbe_moc_state_upload_range(self._h, int(cell0), n_.shape[1],
+                                                         n_.stride(0) if n_.shape[1] else 0, _ptr_rows(n_)))
+
+    def download_range(self, cell0: int, count: int):
+        out = torch.empty((self.moc.N, int(count)), dtype=torch.float64)
+        capi.check(capi.lib().pbe_moc_state_download_range(self._h, int(cell0), int(count),
+                                                           out.stride(0) if count else 0, _ptr_rows(out)))
+        return out
+
+    def device_fields(self):
+        """zero-copy torch views of the state's device memory: (n [N][ncells], d [ncells])"""
+        n, stride, d = C.c_void_p(), C.c_int64(), C.c_void_p()
+        capi.check(capi.lib().pbe_moc_state_device(self._h, C.byref(n), C.byref(stride), C.byref(d)))
+        assert stride.value == self.ncells
+        dev = self.moc.ctx.device
+        return (_device_view(n.value, (self.moc.N, self.ncells), dev), _device_view(d.value, (self.ncells,), dev))
+
+    def d(self):
+        d = torch.empty(self.ncells, dtype=torch.float64)
+        capi.check(capi.lib().pbe_moc_state_d(self._h, _ptr(d)))
+        return d
+
+    def correct(self, eps, rho, nu, alpha, dt, *, phi=None, psi_b=None, d_out=None, want_d=True,
+                minmax=False, n_moments=0):
+        """One MOC::correct() + d(): host eps, rho, nu, alpha in; returns (d, diag dict)."""
+        d = d_out if d_out is not None else (torch.empty(self.ncells, dtype=torch.float64) if want_d else None)
+        diag = capi.MocDiag()
+        mn = mx = None
+        if minmax:
+            mn, mx = np.empty(self.moc.N), np.empty(self.moc.N)
+            diag.class_min, diag.class_max = mn.ctypes.data, mx.ctypes.data
+        diag.n_moments = int(n_moments)
+        pb = None if psi_b is None else _as_host(psi_b)
+        capi.check(capi.lib().pbe_moc_correct_resident(
+            self._h, _hptr(eps), _hptr(rho), _hptr(nu), _hptr(alpha), _hptr(phi), _hptr(pb),
+            0 if pb is None else pb.stride(0), float(dt), _hptr(d), C.byref(diag)))
+        return d, {"class_min": mn, "class_max": mx, "cont_err_max": diag.cont_err_max,
+                   "moments": list(diag.moments)[:int(n_moments)]}
+
+
+class QMOMState:
+    """pbe_qmom_state: the moment fields owned on the device (QMOM.H:62, QMOM.C:72-79);
+    `correct()` is one QMOM::correct() (QMOM.C:85-129)."""
+
+    def __init__(self, q: "QMOM", ncells: int, vcell=None, m0=None, mesh: "Mesh" = None, scheme="upwind"):
+        self.q, self.ncells = q, int(ncells)
+        self._h = C.c_void_p()
+        self._mesh = mesh
+        capi.check(capi.lib().pbe_qmom_state_create(q._h, self.ncells, _hptr(vcell), C.byref(self._h)))
+        if m0 is not None:
+            self.upload(m0)
+        if mesh is not None:
+            capi.check(capi.lib().pbe_qmom_state_attach_mesh(self._h, mesh._h, div_scheme(scheme)))
+
+    def close(self):
+        if self._h:
+            capi.lib().pbe_qmom_state_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, m):
+        m_ = _as_host(m)
+        assert m_.shape == (2 * self.q.order, self.ncells)
+        capi.check(capi.lib().pbe_qmom_state_upload(self._h, m_.stride(0) if self.ncells else 0, _ptr_rows(m_)))
+
+    def download(self, out=None):
+        out = torch.empty((2 * self.q.order, self.ncells), dtype=torch.float64) if out is None else _as_host(out)
+        capi.check(capi.lib().pbe_qmom_state_download(self._h, out.stride(0) if self.ncells else 0, _ptr_rows(out)))
+        return out
+
+    def d(self):
+        d = torch.empty(self.ncells, dtype=torch.float64)
+        capi.check(capi.lib().pbe_qmom_state_d(self._h, _ptr(d)))
+        return d
+
+    def device_fields(self):
+        """zero-copy torch views of the state's device memory: (m [2 order][ncells], d [ncells])"""
+        m, stride, d, S = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_void_p()
+        capi.check(capi.lib().pbe_qmom_state_device(self._h, C.byref(m), C.byref(stride), C.byref(d), C.byref(S)))
+        dev = self.q.ctx.device
+        return (_device_view(m.value, (2 * self.q.order, self.ncells), dev), _device_view(d.value, (self.ncells,), dev))
+
+    def correct(self, eps, rho, nu, dt, *, phi=None, psi_b=None, d_out=None, want_d=True, stats=False):
+        """One QMOM::correct(); returns (d, stats dict of [rows][4] = sum f V, sum V, max, min)."""
+        d = d_out if d_out is not None else (torch.empty(self.ncells, dtype=torch.float64) if want_d else None)
+        diag, out = None, {}
+        if stats:
+            nm = 2 * self.q.order
+            out = {"source": np.empty((nm, 4)), "moment": np.empty((nm, 4)), "d": np.empty(4)}
+            diag = capi.QmomDiag()
+            diag.source, diag.moment, diag.d = (out[k].ctypes.data for k in ("source", "moment", "d"))
+        pb = None if psi_b is None else _as_host(psi_b)
+        capi.check(capi.lib().pbe_qmom_correct_resident(
+            self._h, _hptr(eps), _hptr(rho), _hptr(nu), _hptr(phi), _hptr(pb), 0 if pb is None else pb.stride(0),
+            float(dt), _hptr(d), None if diag is None else C.byref(diag)))
+        return d, out
 
 
 def _as_host(v):
