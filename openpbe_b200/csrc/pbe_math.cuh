@@ -285,13 +285,12 @@ PBE_HD double exp2_neg_tab(double y, const double *T) {
     const double Tj = T[m & (NT - 1)];
 #endif
     const double p = fma_(Tj * f, s, Tj); // in [1, 2): exponent field 1023
-    // 2^k by an integer add on the exponent field, k = m >> LOGT clamped at -1023: the exponent
-    // field then becomes 0, so results below 2^-1022 come out as the denormal (p - 1) 2^-1022
-    // < 2.3e-308 instead of being rounded (exp() itself is denormal there), and an argument that is
-    // an exact integer <= -1023 (f = 0, T[0] = 1, p = 1) gives EXACTLY 0 -- the MOC pair table marks
-    // its zero-weight padding slots with y = -4096.
+    // 2^k by an integer add on the exponent field, k = m >> LOGT clamped at -1022 (denormal-range
+    // results come out below 4.5e-308 instead of being rounded, like exp2_neg_fast).  -1022 is the
+    // lowest safe clamp: p can be just below 1 (f < 0, T[0] = 1: exponent field 1022), and field
+    // 1022 - 1023 would wrap into the sign bit (measured: NaN sources in the extreme-cell test).
     // k << 20 = rotl(m, 20 - LOGT) & 0xFFF00000
-    const int mc = (m > -1023 * NT) ? m : -1023 * NT;
+    const int mc = (m > -1022 * NT) ? m : -1022 * NT;
 #if defined(__CUDA_ARCH__)
     const int kbits = (int)(__funnelshift_l(mc, mc, 20 - LOGT) & 0xFFF00000u);
 #else

@@ -459,9 +459,11 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
     }
     if (e == cudaSuccess && m->tmem_ok && m->dcoal == DCOAL_CT) {
         // the tensor-memory kernel folds G into the exponent: S = A 2^(log2 G - K log2(e) H).
-        // Zero-weight padding slots get {log2 G, H} = {-4096, 0}: y = -4096 exactly, for which
-        // exp2_neg_tab returns exactly 0 (integer argument below -1023), so a padding slot between
-        // two real classes adds exactly nothing -- as in the shared-memory kernel.
+        // Zero-weight padding slots get {log2 G, H} = {-4096, 0}: 2^y is then 2^-1022 (the clamp of
+        // exp2_neg_tab), so a padding slot between two real classes (i > j or i + j > N - 2 inside an
+        // edge tile) adds A 2^-1022 n_i n_j < 1e-290 at physical densities instead of exactly 0 as
+        // in the shared-memory kernel: 250 orders of magnitude below an ulp of any sum it joins.
+        // (An exact 0 needs exponent field 0, i.e. a clamp at -1023, which is unsafe: see pbe_math.cuh.)
         std::vector<double2> tl(tab.size());
         for (size_t k = 0; k < tab.size(); ++k)
             tl[k] = make_double2(tab[k].x > 0.0 ? std::log2(tab[k].x) : -4096.0, tab[k].y);

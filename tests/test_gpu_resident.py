@@ -4,7 +4,8 @@ The reference's methods own their class / moment fields (MOC.H:66, MOC.C:69-77; 
 PBEDiameter::correct() is `method_->correct(); d_ = method_->d();` (PBEDiameter.H:95-99).  The
 checker is the oracle (oracle/pbe_oracle.c): K resident steps + download must equal K oracle steps
     n <- n + dt max(C + B, -relax n / dt)            (MOC.C:87-91, 259-272 with phi = 0)
-within 1e-12 * sum |terms| * dt per step (the tolerance of SURVEY.md 8c carried through the update),
+within 1e-12 * sum |terms| * dt + 2 ulp(n) per step (the tolerance of SURVEY.md 8c carried through the
+update, plus the update's own rounding),
 d must equal MOC::d() of those fields, and the diagnostics (per-class min, continuity error, global
 moments) their NumPy restatements.
 """
@@ -34,8 +35,10 @@ def oracle_moc_steps(orc, w, f, K, alpha_scale=None):
     budget = np.zeros_like(n)
     for _ in range(K):
         S, scale = orc.moc_source(sp, w.N, w.xi1, w.relax, n, f["eps"], f["rho"], f["nu"], w.dt, nthreads=8)
-        budget += 1e-12 * scale * w.dt
         orc.moc_update(n, S, w.dt)
+        # 1e-12 sum|terms| on S, plus the rounding of the update itself: the device forms
+        # fma(dt, S, n), the oracle n + dt S -- up to an ulp of n apart where dt S << n
+        budget += 1e-12 * scale * w.dt + 4.5e-16 * np.abs(n)
     return n, budget, orc.moc_d(n, w.xi1)
 
 
@@ -137,9 +140,11 @@ def test_moc_resident_with_transport_matches_oracle(ctx, oracle):
         S, scale = oracle.moc_source(sp, w.N, w.xi1, w.relax, n_o, f["eps"], f["rho"], f["nu"], w.dt)
         n_o = oracle.transport_upwind_explicit(tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"], n_o,
                                                tm["phi"], w.dt, S=S)
-        budget = 2.0 * budget + 1e-12 * scale * w.dt  # earlier differences are advected (CFL < 1)
+        budget = budget + 1e-12 * scale * w.dt + 4.5e-16 * np.abs(n_o)
     n_g = st.download().numpy()
-    assert np.all(np.abs(n_g - n_o) <= budget + 1e-12 * np.abs(n_o))
+    # earlier differences are advected between neighbouring cells (CFL < 1): compare per class with
+    # the largest budget of the class
+    assert np.all(np.abs(n_g - n_o) <= 4.0 * budget.max(axis=1, keepdims=True) + 1e-12 * np.abs(n_o))
     assert np.allclose(d.numpy(), oracle.moc_d(n_g, w.xi1), rtol=1e-12)
     assert np.array_equal(diag["class_min"], n_g.min(axis=1))
     cont, _ = oracle.moc_continuity(n_g, w.xi1, alpha, tm["vcell"])
@@ -173,7 +178,7 @@ def test_qmom_resident_steps_match_oracle(ctx, oracle, monkeypatch, name, ncells
     d, stats = st.correct(f["eps"], f["rho"], f["nu"], w.dt, stats=True)
     m_g = st.download().numpy()
     ok = np.isfinite(So).all(axis=0) & (f["nodes"][1] / f["nodes"][0] > 1.001) & (f["nodes"][2] / f["nodes"][1] > 1.001)
-    tol = 1e-9 * scale * w.dt + 1e-15
+    tol = 1e-9 * scale * w.dt + 4.5e-16 * np.abs(m_o) + 1e-15
     assert np.all(np.abs(m_g - m_o)[:, ok] <= tol[:, ok])
     assert np.all(m_g >= 1e-15)  # clamp to SMALL (QMOM.C:117-123): moment realisability floor
     assert np.allclose(d.numpy()[ok], d_o[ok], rtol=1e-9)
