@@ -228,7 +228,7 @@ def host_threads() -> int:
 
 
 def cpu_arm():
-    """(kind, moc_source(w, fields, nthreads) -> seconds, description)"""
+    """(kind, moc(w, fields, nthreads, nsteps, warmup) -> seconds per correct(), description)"""
     from oracle import cpu_oracle as orc
 
     orc.build()
@@ -236,24 +236,26 @@ def cpu_arm():
         from oracle import ref_oracle as ref
 
         if ref.available():
-            def run_ref(w, f, nthreads):
-                t = time.perf_counter()
-                ref.moc_source(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs, w.N, w.xi1, w.relax, f["n"],
-                               f["eps"], f["rho"], f["nu"], w.dt, nthreads=nthreads)
-                return time.perf_counter() - t
+            def run_ref(w, f, nthreads, nsteps=1, warmup=0):
+                return ref.correct_timed("methodOfClasses", w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs, f["n"],
+                                         f["eps"], f["rho"], f["nu"], w.dt, N=w.N, xi1=w.xi1, relax=w.relax,
+                                         nthreads=nthreads, nsteps=nsteps, warmup=warmup)
 
             return "reference", run_ref, ("the reference's own MOC.C / CoulaloglouTavlarides.C / uniformBinaryBreakup.C "
-                                          "compiled unmodified against the OpenFOAM API shim (oracle/_ref), "
-                                          "MOC::classSourceTerm for every class; one process per host thread on "
+                                          "compiled unmodified against the OpenFOAM API shim (oracle/_ref): "
+                                          "MOC::correct() + d() in a time loop; one process per host thread on "
                                           "disjoint cell blocks, as decomposePar + mpirun runs it")
     except Exception:  # noqa: BLE001 -- no _ref on this box: fall back to the port, and say so in `kind`
         pass
 
-    def run_port(w, f, nthreads):
+    def run_port(w, f, nthreads, nsteps=1, warmup=0):
         sp = orc.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+        for _ in range(warmup):
+            orc.moc_source(sp, w.N, w.xi1, w.relax, f["n"], f["eps"], f["rho"], f["nu"], w.dt, nthreads=nthreads)
         t = time.perf_counter()
-        orc.moc_source(sp, w.N, w.xi1, w.relax, f["n"], f["eps"], f["rho"], f["nu"], w.dt, nthreads=nthreads)
-        return time.perf_counter() - t
+        for _ in range(nsteps):
+            orc.moc_source(sp, w.N, w.xi1, w.relax, f["n"], f["eps"], f["rho"], f["nu"], w.dt, nthreads=nthreads)
+        return (time.perf_counter() - t) / max(1, nsteps)
 
     return "port", run_port, ("oracle/pbe_oracle.c reference-shaped loops (MOC.C:92-157 order, pow/exp per ordered "
                               "pair), OpenMP over cells")
@@ -269,17 +271,29 @@ def cpu_moc_rate(w, sample_cells: int, nthreads: int, run, repeats: int = 1):
 
 
 def cpu_qmom_rate(wq, sample_cells: int, nthreads: int):
-    """cell-updates/s of the reference-shaped QMOM source (one wheeler_inversion per moment index,
-    QMOM.C:231; benchmarks/moment_inversion.cpp:5-12) -- the oracle port: MomentInversion.C needs Eigen."""
+    """(cell-updates/s, seconds, kind, how) of the reference-shaped QMOM correct(): one wheeler_inversion per
+    moment index (QMOM.C:231; benchmarks/moment_inversion.cpp:5-12)."""
     from openpbe_b200 import synthetic
     from oracle import cpu_oracle as orc
 
     f = synthetic.qmom_fields(wq, ncells=sample_cells)
+    try:
+        from oracle import ref_oracle as ref
+
+        if ref.available():
+            secs = ref.correct_timed("quadratureMethodOfMoments", wq.coalescence, wq.coal_coeffs, wq.breakup,
+                                     wq.br_coeffs, f["m"], f["eps"], f["rho"], f["nu"], wq.dt, order=wq.N,
+                                     nthreads=nthreads)
+            return sample_cells / secs, secs, "reference", ("the reference's own QMOM.C + MomentInversion.C compiled "
+                                                            "unmodified (oracle/_ref); Eigen is absent: its "
+                                                            "SelfAdjointEigenSolver is the shim's Jacobi rotations")
+    except Exception:  # noqa: BLE001
+        pass
     sp = orc.make_spec(wq.coalescence, wq.coal_coeffs, wq.breakup, wq.br_coeffs)
     t = time.perf_counter()
     orc.qmom_source(sp, wq.N, f["m"], f["eps"], f["rho"], f["nu"], reference_shaped=True, nthreads=nthreads)
     secs = time.perf_counter() - t
-    return sample_cells / secs, secs
+    return sample_cells / secs, secs, "port", "oracle/pbe_oracle.c, reference-shaped (MomentInversion.C needs Eigen)"
 
 
 def run_reference(args):
@@ -293,12 +307,8 @@ def run_reference(args):
     threads = host_threads()
     sample = args.cpu_sample_cells
     f = synthetic.moc_fields(w, ncells=sample)
-    for _ in range(args.warmup):
-        run(w, f, threads)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        run(w, f, threads)
-    dt = (time.perf_counter() - t0) / max(1, args.steps)
+    # one time loop: `warmup` untimed correct() calls, then `steps` timed ones (fields evolve, as in PBEFoam)
+    dt = run(w, f, threads, nsteps=max(1, args.steps), warmup=args.warmup)
     value = sample * w.N / dt
     desc = f"{sample} cells of {w.name} (N={w.N}) per step; {how}; {threads} host threads"
     line = {
@@ -1046,12 +1056,12 @@ def run_b200(args):
                                        "single_thread_value": r1}
             cpu["legs"]["config1_moc30"] = config1["cpu_baseline"]
         if qmom is not None:
-            r, s = cpu_qmom_rate(wq, int(args.cpu_qmom_cells), threads)
-            r1, s1 = cpu_qmom_rate(wq, max(1000, int(args.cpu_qmom_cells) // threads), 1)
-            qmom["cpu_baseline"] = {"value": r, "unit": "cell-updates/s", "cores": threads, "kind": "port",
+            r, s, qkind, qhow = cpu_qmom_rate(wq, int(args.cpu_qmom_cells), threads)
+            r1, s1, _, _ = cpu_qmom_rate(wq, max(1000, int(args.cpu_qmom_cells) // threads), 1)
+            qmom["cpu_baseline"] = {"value": r, "unit": "cell-updates/s", "cores": threads, "kind": qkind,
                                     "sample": f"{int(args.cpu_qmom_cells)} cells of configs[1], reference-shaped: one "
                                               "wheeler_inversion per moment index (QMOM.C:231), pow/exp per kernel "
-                                              f"evaluation; oracle/pbe_oracle.c (MomentInversion.C needs Eigen), {s:.1f} s",
+                                              f"evaluation; {qhow}; {s:.1f} s",
                                     "single_thread_value": r1}
             cpu["legs"]["qmom"] = qmom["cpu_baseline"]
         if replay is not None:
@@ -1059,8 +1069,8 @@ def run_b200(args):
             replay["moc"]["cpu_baseline"] = {"value": r, "unit": UNIT, "cores": threads, "kind": kind,
                                              "sample": f"20000 cells of configs[4] (MOC 50 classes), {s:.1f} s",
                                              "ms_per_step_at_4e6_cells": 4e6 * wrm.N / r * 1e3}
-            rq, sq = cpu_qmom_rate(wrq, 200_000, threads)
-            replay["qmom"]["cpu_baseline"] = {"value": rq, "unit": "cell-updates/s", "cores": threads, "kind": "port",
+            rq, sq, qk, _ = cpu_qmom_rate(wrq, 200_000, threads)
+            replay["qmom"]["cpu_baseline"] = {"value": rq, "unit": "cell-updates/s", "cores": threads, "kind": qk,
                                               "sample": f"200000 cells of configs[4] (QMOM order 3), {sq:.1f} s",
                                               "ms_per_step_at_4e6_cells": 4e6 / rq * 1e3}
             cpu["legs"]["replay_moc50"] = replay["moc"]["cpu_baseline"]
