@@ -10,6 +10,12 @@
 #include "pbe_math.cuh"
 #include "../../include/pbe_b200.h"
 
+// 1: division- and call-free device math in the per-cell scalars of the QMOM kernel (cbrt_pos_fast,
+// rcp_fast, sqrt_pos_fast; <= 3 ulp each, inside the 1e-9 sum|terms| tolerance of SURVEY.md 8c)
+#ifndef PBE_QMOM_FASTMATH
+#define PBE_QMOM_FASTMATH 1
+#endif
+
 namespace pbe {
 
 // Device view of pbe_kernel_spec with the cell-independent algebra folded on the host.
@@ -51,14 +57,22 @@ struct CellCoef {
 
 PBE_HD CellCoef cell_coef(const DevKernelSpec &k, double eps, double rho, double nu) {
     CellCoef c;
+#if defined(__CUDA_ARCH__) && PBE_QMOM_FASTMATH
+    const double e13 = cbrt_pos_fast(eps);
+#else
     const double e13 = pow_third(eps);
+#endif
     // coalescenceKernels/CoulaloglouTavlarides.C:77-88 (wrapper :52-60 feeds the DISPERSED
     // phase rho and nu into the parameters named rhoc, nuc)
     c.A = k.coalA * e13;
     c.negK = -(k.coalK * rho * eps * (rho * nu));
     // breakupKernels/CoulaloglouTavlarides.C:83-92
     c.Ab = k.brA * e13;
+#if defined(__CUDA_ARCH__) && PBE_QMOM_FASTMATH
+    c.negKb = -(k.brK * rcp_fast(rho * (e13 * e13)));
+#else
     c.negKb = -(k.brK / (rho * (e13 * e13)));
+#endif
     return c;
 }
 

@@ -168,6 +168,42 @@ __device__ __forceinline__ double rcp_fast(double x) {
     return r;
 }
 
+// x^(1/3) for positive normal x without libm's cbrt() (~30 FP64 instructions and a call): the
+// exponent is split off (x = xs 8^k, xs in [1/4, 8)), an FP32 seed u0 = 2^(-log2(xs)/3) (MUFU.LG2 /
+// MUFU.EX2, |e| < 1e-6) is corrected ONCE with the second-order series of (1 - e)^(-1/3),
+// e = 1 - xs u0^3, and x^(1/3) = xs u^2: 10 FP64-pipe instructions, <= 3 ulp.  Everything else
+// (<= 0, denormal, inf, NaN) takes the libm call behind one rarely taken branch, with pow(x, 1/3)'s
+// sign convention of pow_third() below.
+__device__ __forceinline__ double cbrt_pos_fast(double x) {
+    const int hi = __double2hiint(x);
+    const unsigned ex_field = (unsigned)(hi >> 20) - 1u; // sign bit set or field 0 / 0x7ff -> out of range
+    if (ex_field >= 0x7feu) return (x < 0.0) ? NAN : cbrt(x);
+    const int ex = (int)ex_field - 1022;
+    const int k = (ex * 21846 + 32768) >> 16; // ~ ex / 3, rounded
+    const double xs = __hiloint2double(hi - ((3 * k) << 20), __double2loint(x));
+    const float lf = __log2f((float)xs);
+    const double u0 = (double)exp2f(lf * (-1.0f / 3.0f));
+    const double u2 = u0 * u0;
+    const double e = __fma_rn(-(xs * u0), u2, 1.0);
+    const double c = __fma_rn(2.0 / 9.0, e, 1.0 / 3.0);
+    const double us = __fma_rn(u0 * e, c, u0);
+    const double rs = xs * (us * us);
+    return __hiloint2double(__double2hiint(rs) + (k << 20), __double2loint(rs));
+}
+
+// sqrt(x) for positive normal x: MUFU.RSQ64H seed, one Newton step on 1/sqrt, one correction of
+// the root (8 FP64-pipe instructions, <= 1 ulp, no slow-path call); 0, inf, negative, NaN as sqrt().
+__device__ __forceinline__ double sqrt_pos_fast(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double h = 0.5 * x;
+    y = y * __fma_rn(-(h * y), y, 1.5);
+    double s = x * y;
+    s = __fma_rn(__fma_rn(-s, s, x), 0.5 * y, s);
+    // x = 0 -> y = inf, s = NaN; x = inf -> y = 0, s = NaN; x < 0 -> NaN already
+    return (x == 0.0 || x == __longlong_as_double(0x7ff0000000000000LL)) ? x : s;
+}
+
 // ninth roots of a node volume: r = x^(1/9), u = x^(-1/9), from which the Coulaloglou-
 // Tavlarides kernels take x^(1/3) = r^3, x^(2/9) = r^2, x^(-2/9) = u^2, x^(-5/9) = u^5
 // (coalescenceKernels/CoulaloglouTavlarides.C:75-88, breakupKernels/CoulaloglouTavlarides.C:

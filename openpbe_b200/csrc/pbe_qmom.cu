@@ -1,5 +1,7 @@
 // pbe_qmom.cu -- host side of the QMOM path (launch dispatch on the quadrature order, the
 // host-buffer pipeline) and the batched device evaluators of the scalar kernel functors.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "pbe_common.h"
@@ -23,9 +25,23 @@ int grid_for(pbe_ctx *ctx, int64_t n, int threads, int per_sm) {
 // 16 CTAs of 128 cells per SM, grid-stride over the cells.  Measured on B200 (1e7 cells, CT + CT):
 // a persistent grid of exactly SMs x resident CTAs is 6 % slower (co-resident CTAs stay in
 // lockstep: loads and FP64 phases coincide), more CTAs change nothing.
+// Grid = `waves` x the resident CTAs (occupancy x SMs), grid-stride over the cells.  Measured on B200
+// (1e7 cells, CT + CT, fused step, L2 flushed; profiles/r02c_qmom_ab.jsonl): 1 wave (a persistent
+// grid) 0.678 ms -- co-resident CTAs stay in lockstep, loads and FP64 phases coincide --, 3 waves
+// 0.647, the old fixed 16 CTAs per SM 0.643 (3.2 waves: ends in a partial wave), 8 waves 0.625:
+// shorter CTAs de-phase and shrink the tail.  PBE_QMOM_WAVES overrides (0 = 16 CTAs per SM).
 template <int N, int C, int B>
 void launch_q(pbe_qmom *q, const QmomParams &p, cudaStream_t st) {
-    const int grid = grid_for(q->ctx, p.ncells, 128, 16);
+    static int resident = 0; // per instantiation, same on every B200 of the node
+    if (resident == 0) {
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, qmom_kernel<N, C, B>, 128, 0) != cudaSuccess || occ < 1)
+            occ = 4;
+        resident = occ;
+    }
+    const char *we = getenv("PBE_QMOM_WAVES");
+    const int waves = we ? atoi(we) : 8;
+    const int grid = waves > 0 ? grid_for(q->ctx, p.ncells, 128, resident * waves) : grid_for(q->ctx, p.ncells, 128, 16);
     qmom_kernel<N, C, B><<<grid, 128, 0, st>>>(p);
 }
 

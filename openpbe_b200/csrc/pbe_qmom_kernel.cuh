@@ -82,7 +82,11 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
                 S = (cc.A * G) * exp2_neg_tab_safe(K2 * (h2 * h2), T128);
             } else if (ct_c) { // coalescenceKernels/CoulaloglouTavlarides.C:69-90
                 const double sa = ra[i] + ra[j];
+#if PBE_QMOM_FASTMATH
+                const double G = (sa * sa) * sqrt_pos_fast(rp[i] + rp[j]);
+#else
                 const double G = (sa * sa) * sqrt(rp[i] + rp[j]);
+#endif
                 const double h = rcp_fast(ia[i] + ia[j]); // a b / (a + b)
                 const double h2 = h * h;
                 S = (cc.A * G) * exp2_neg_tab_safe(K2 * (h2 * h2), T128);
@@ -143,8 +147,13 @@ struct QmomParams {
     DevKernelSpec ks;
 };
 
+#ifdef PBE_QMOM_MIN_CTAS // A/B builds: resident CTAs per SM the register allocation must allow
+#define PBE_QMOM_BOUNDS __launch_bounds__(128, PBE_QMOM_MIN_CTAS)
+#else
+#define PBE_QMOM_BOUNDS __launch_bounds__(128)
+#endif
 template <int N, int COAL, int BR>
-__global__ void __launch_bounds__(128) qmom_kernel(const __grid_constant__ QmomParams p) {
+__global__ void PBE_QMOM_BOUNDS qmom_kernel(const __grid_constant__ QmomParams p) {
     __shared__ double T128[128]; // 2^(j/128), exp2_neg_tab<7>
     T128[threadIdx.x] = PBE_EXP2_TAB128[threadIdx.x];
     __syncthreads();
@@ -176,7 +185,11 @@ __global__ void __launch_bounds__(128) qmom_kernel(const __grid_constant__ QmomP
                 p.m_out[(size_t)k * p.stride + c] = m[k];
             }
             if (p.d_out != nullptr && N >= 1)
+#if PBE_QMOM_FASTMATH
+                p.d_out[c] = cbrt_pos_fast((6.0 / 3.14159265358979323846 * m[1]) * rcp_fast(m[0])); // QMOM.C:125
+#else
                 p.d_out[c] = cbrt(6.0 / 3.14159265358979323846 * m[1] / m[0]); // QMOM.C:125
+#endif
         }
         if (p.S_out != nullptr) {
 #pragma unroll
