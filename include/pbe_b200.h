@@ -218,10 +218,38 @@ int pbe_mesh_info(pbe_mesh *mesh, int64_t *ncells, int64_t *n_internal_faces,
  * the register-resident kernel, all others through the general one. */
 int pbe_mesh_regular_cells(pbe_mesh *mesh, int *faces_per_regular_cell, int64_t *n_regular);
 
-/* fvSchemes divSchemes entry "div(phi,n.*)" -> enum; anything but upwind returns
- * PBE_E_UNKNOWN_TYPE with the valid names listed (the reference's FatalError convention). */
-enum { PBE_DIV_UPWIND = 0 };
+/* fvSchemes divSchemes entry "div(phi,n.*)" -> enum ("Gauss upwind" | "upwind" | "Gauss vanLeer" |
+ * "vanLeer"); anything else returns PBE_E_UNKNOWN_TYPE with the valid names listed (the
+ * reference's FatalError convention).  The reference's validation case selects Gauss vanLeer
+ * (tests/validation/simmons_and_azzopardi/c01/system/fvSchemes:34). */
+enum { PBE_DIV_UPWIND = 0, PBE_DIV_VANLEER = 1 };
 int pbe_div_scheme_type(const char *scheme_name, int *out);
+
+/* Mesh geometry the limited schemes need (fvMesh::Sf(), C(), weights()): HOST arrays, copied.
+ * Sf [n_internal + n_boundary][3] face area vectors (owner -> neighbour / outward), C [ncells][3]
+ * cell centres, weights [n_internal] linear interpolation weights. */
+int pbe_mesh_set_geometry(pbe_mesh *mesh, const double *Sf, const double *C, const double *weights);
+
+/* The MULES-limited update of MOC::solveWithMULES (MOC.C:198-272) / QMOM::solveWithMULES
+ * (QMOM.C:131-197) on nfields DEVICE fields psi [nfields][stride]:
+ *   phiCorr_k = fvc::flux(phi, psi_k, scheme) - upwind flux, limited by MULES::limit against
+ *   [psi_min, psi_max[k]] with n_limiter_iter sweeps (OpenFOAM's nLimiterIter, default 3), then
+ *   MULES::limitSum over the fields, then psi_k <- (psi_k rDeltaT + S_k - div(phiCorr_k + upwind)) / rDeltaT.
+ * psi_max: DEVICE [nfields] (pbe_moc_psi_max / pbe_qmom_psi_max); psi_b, S as pbe_transport_explicit.
+ * With PBE_DIV_UPWIND the correction is identically zero and the result equals
+ * pbe_transport_explicit's.  Uncoupled patches only (no processor patches yet: PBE_E_UNSUPPORTED).
+ * OpenFOAM's MULES is third-party code: parity unpinned. */
+int pbe_transport_mules(pbe_mesh *mesh, int scheme, int nfields, int64_t stride, const double *psi,
+                        const double *phi, const double *psi_b, int64_t stride_b, const double *S,
+                        const double *psi_max, double psi_min, int n_limiter_iter, double dt,
+                        double *psi_out, void *cuda_stream);
+/* psi_max[k] = max_c(alpha V / xi_k) (MOC.C:238), DEVICE in / out */
+int pbe_moc_psi_max(pbe_moc *moc, int64_t ncells, const double *alpha, const double *vcell,
+                    double *psi_max, void *cuda_stream);
+/* psi_max[k] = 1.2 max(m_k) over cells and patch values (QMOM.C:171), DEVICE in / out */
+int pbe_qmom_psi_max(pbe_ctx *ctx, int nmoments, int64_t ncells, int64_t stride, const double *m,
+                     int64_t n_boundary_faces, int64_t stride_b, const double *psi_b,
+                     double *psi_max, void *cuda_stream);
 
 /* One explicit transport + source update of nfields fields psi [nfields][stride] (DEVICE).
  * phi: DEVICE [n_internal_faces + n_boundary_faces] volumetric face flux of the phase

@@ -19,7 +19,7 @@ BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
 DAUGHTER_UNIFORM_BINARY = 0
 QMOM_MAX_ORDER = 4
 MOC_KERNEL_SMEM, MOC_KERNEL_TMEM = 1, 2
-DIV_UPWIND = 0
+DIV_UPWIND, DIV_VANLEER = 0, 1
 CELLS_ALL, CELLS_REGULAR, CELLS_IRREGULAR = 0, 1, 2
 
 _dp = C.POINTER(C.c_double)
@@ -121,6 +121,11 @@ PROTOTYPES = {
     "pbe_div_scheme_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
     "pbe_transport_explicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
                                          C.c_double, _vp, _vp]),
+    "pbe_mesh_set_geometry": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "pbe_transport_mules": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp, _vp, C.c_double,
+                                      C.c_int, C.c_double, _vp, _vp]),
+    "pbe_moc_psi_max": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
+    "pbe_qmom_psi_max": (C.c_int, [_vp, C.c_int, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _vp]),
     "pbe_moc_num_classes": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(_vp)]),
     "pbe_moc_coeffs": (C.c_int, [_vp, _dp, _dp]),
     "pbe_qmom_order": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(_vp)]),

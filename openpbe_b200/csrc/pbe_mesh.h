@@ -1,0 +1,37 @@
+// pbe_mesh.h -- the device-side mesh handle shared by pbe_transport.cu (explicit upwind update) and
+// pbe_mules.cu (MULES-limited update): OpenFOAM face addressing turned into cell-centred tables.
+#pragma once
+
+#include "pbe_common.h"
+
+struct pbe_mesh {
+    pbe_ctx *ctx = nullptr;
+    int64_t ncells = 0, nint = 0, nbnd = 0, nirr = 0;
+    int maxf = 0; // most faces on any cell (info)
+    int F = 0;    // face count of the regular cells (0: none)
+    int32_t *d_other = nullptr; // [F][ncells]: neighbour cell; row 0 holds -1 for irregular cells
+    int32_t *d_face = nullptr;  // [F][ncells]: face index f (this cell owns it) or ~f (it is the neighbour)
+    double *d_vcell = nullptr;  // [ncells]
+    // irregular cells, CSR: entries of cell irr_cell[i] are irr_ptr[i] .. irr_ptr[i+1]-1
+    int32_t *d_irr_cell = nullptr, *d_irr_ptr = nullptr;
+    int32_t *d_irr_other = nullptr; // >= 0 neighbour cell; -(b + 2) boundary face b
+    int32_t *d_irr_face = nullptr;  // as d_face (boundary faces: n_internal + b)
+    int64_t coupled0 = 0, ncoupled = 0; // boundary faces [coupled0, coupled0 + ncoupled): processor patches
+    // the irregular cells' kernel runs beside the regular cells' one (disjoint outputs): fork / join
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // resident fields of the host-buffer entry (pbe_moc_correct_host), grown on demand
+    double *res = nullptr;
+    size_t res_doubles = 0;
+    // ---- MULES path (pbe_mules.cu) ------------------------------------------------------------------
+    // CSR over all cells, ascending face order: entries of cell c are csr_ptr[c] .. csr_ptr[c+1]-1;
+    // csr_other >= 0: the cell across an internal face, -(b + 2): boundary face b; csr_face: f (this
+    // cell owns it), ~f (it is the neighbour), nint + b for boundary faces
+    int32_t *d_csr_ptr = nullptr, *d_csr_other = nullptr, *d_csr_face = nullptr;
+    int32_t *d_owner = nullptr, *d_neigh = nullptr, *d_bown = nullptr; // face -> cells
+    // geometry for the limited schemes (pbe_mesh_set_geometry): Sf [3][nint + nbnd], C [3][ncells]
+    // (component-major for coalescing), linear weights [nint]
+    double *d_Sf = nullptr, *d_C = nullptr, *d_w = nullptr;
+    double *mules_ws = nullptr; // workspace of pbe_transport_mules, grown on demand
+    size_t mules_ws_doubles = 0;
+};

@@ -250,7 +250,7 @@ struct pbe_moc_state {
     pbe_mesh *mesh = nullptr;
     int scheme = 0;
     int64_t nf = 0, nbnd = 0;
-    double *S = nullptr, *nNew = nullptr, *phi = nullptr, *psi_b = nullptr;
+    double *S = nullptr, *nNew = nullptr, *phi = nullptr, *psi_b = nullptr, *psi_max = nullptr;
     // diagnostics: [N][4] row statistics, then cont_err, then 8 moments
     double *diag = nullptr, *part = nullptr, *diag_host = nullptr;
     int parts_total = 0;
@@ -264,7 +264,7 @@ void free_moc_state(pbe_moc_state *s) {
     DeviceGuard g(s->ctx->device);
     s->pipe.drain();
     for (double *p : {s->n, s->eps, s->rho, s->nu, s->alpha, s->vcell, s->d, s->S, s->nNew, s->phi, s->psi_b,
-                      s->diag, s->part})
+                      s->psi_max, s->diag, s->part})
         if (p) cudaFree(p);
     if (s->diag_host) cudaFreeHost(s->diag_host);
     s->pipe.destroy();
@@ -382,8 +382,16 @@ int moc_correct_impl(pbe_moc_state *s, const double *eps_h, const double *rho_h,
         // MOC::solveWithMULES (MOC.C:198-272): transport + source update of all fields, then d,
         // the continuity check (MOC.C:254-279) and the per-class statistics of the new fields
         PBE_CUDA(cudaStreamWaitEvent(P.s_comp, P.ev_in[nchunks - 1], 0));
-        int rc = pbe_transport_explicit(s->mesh, s->scheme, N, nc, s->n, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
+        int rc;
+        if (s->scheme == PBE_DIV_UPWIND) { // the limited correction is identically zero
+            rc = pbe_transport_explicit(s->mesh, s->scheme, N, nc, s->n, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
                                         s->S, dt, s->nNew, P.s_comp);
+        } else { // MULES::limit against max(alpha V / xi_k) (MOC.C:238-249), limitSum, explicitSolve
+            rc = pbe_moc_psi_max(s->moc, nc, s->alpha, s->vcell, s->psi_max, P.s_comp);
+            if (rc) return rc;
+            rc = pbe_transport_mules(s->mesh, s->scheme, N, nc, s->n, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd, s->S,
+                                     s->psi_max, 0.0, 3, dt, s->nNew, P.s_comp);
+        }
         if (rc) return rc;
         std::swap(s->n, s->nNew);
         rc = pbe_moc_d(s->moc, nc, nc, s->n, s->d, P.s_comp);
@@ -557,11 +565,12 @@ int pbe_moc_state_attach_mesh(pbe_moc_state *s, pbe_mesh *mesh, int scheme) {
                 (long long)mc, (long long)s->nc);
     DeviceGuard g(s->ctx->device);
     const size_t field = (size_t)s->N * std::max<int64_t>(s->nc, 1);
-    for (double **p : {&s->S, &s->nNew, &s->phi, &s->psi_b})
+    for (double **p : {&s->S, &s->nNew, &s->phi, &s->psi_b, &s->psi_max})
         if (*p) {
             cudaFree(*p);
             *p = nullptr;
         }
+    PBE_CUDA(cudaMalloc((void **)&s->psi_max, (size_t)s->N * 8));
     PBE_CUDA(cudaMalloc((void **)&s->S, field * 8));
     PBE_CUDA(cudaMalloc((void **)&s->nNew, field * 8));
     PBE_CUDA(cudaMalloc((void **)&s->phi, (size_t)std::max<int64_t>(nint + nbnd, 1) * 8));
@@ -591,6 +600,10 @@ int pbe_moc_correct_resident(pbe_moc_state *s, const double *eps_host, const dou
                 "pbe_moc_correct_resident: phi / psi_b without an attached mesh (pbe_moc_state_attach_mesh)");
     PBE_REQUIRE(psi_b_host == nullptr || stride_b >= s->nbnd, PBE_E_INVALID,
                 "pbe_moc_correct_resident: stride_b < boundary faces");
+    PBE_REQUIRE(s->mesh == nullptr || s->scheme == PBE_DIV_UPWIND || (alpha_host != nullptr && s->have_vcell),
+                PBE_E_INVALID,
+                "pbe_moc_correct_resident: the MULES limiter's bound max(alpha V / xi_k) (MOC.C:238) needs alpha "
+                "and the cell volumes");
     DeviceGuard g(s->ctx->device);
     const int rc = moc_correct_impl(s, eps_host, rho_host, nu_host, alpha_host, phi_host, psi_b_host, stride_b, dt,
                                     d_host, diag);
@@ -613,7 +626,7 @@ struct pbe_qmom_state {
     pbe_mesh *mesh = nullptr;
     int scheme = 0;
     int64_t nf = 0, nbnd = 0;
-    double *mNew = nullptr, *phi = nullptr, *psi_b = nullptr;
+    double *mNew = nullptr, *phi = nullptr, *psi_b = nullptr, *psi_max = nullptr;
     double *diag = nullptr, *part = nullptr, *diag_host = nullptr; // [2 nm + 1][4]
     int parts_total = 0;
     Pipeline pipe;
@@ -625,7 +638,8 @@ void free_qmom_state(pbe_qmom_state *s) {
     if (!s) return;
     DeviceGuard g(s->ctx->device);
     s->pipe.drain();
-    for (double *p : {s->m, s->S, s->eps, s->rho, s->nu, s->vcell, s->d, s->mNew, s->phi, s->psi_b, s->diag, s->part})
+    for (double *p : {s->m, s->S, s->eps, s->rho, s->nu, s->vcell, s->d, s->mNew, s->phi, s->psi_b, s->psi_max, s->diag,
+                      s->part})
         if (p) cudaFree(p);
     if (s->diag_host) cudaFreeHost(s->diag_host);
     s->pipe.destroy();
@@ -693,8 +707,16 @@ int qmom_correct_impl(pbe_qmom_state *s, const double *eps_h, const double *rho_
     if (s->mesh) {
         int rc = pbe_field_scrub_nan(ctx, (int64_t)nm * nc, s->S, P.s_comp); // QMOM.C:101-107
         if (rc) return rc;
-        rc = pbe_transport_explicit(s->mesh, s->scheme, nm, nc, s->m, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
-                                    s->S, dt, s->mNew, P.s_comp); // QMOM.C:131-197
+        if (s->scheme == PBE_DIV_UPWIND) {
+            rc = pbe_transport_explicit(s->mesh, s->scheme, nm, nc, s->m, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
+                                        s->S, dt, s->mNew, P.s_comp); // QMOM.C:131-197
+        } else { // MULES::limit against 1.2 max(m_k) (QMOM.C:171-182), limitSum, explicitSolve
+            rc = pbe_qmom_psi_max(ctx, nm, nc, nc, s->m, s->nbnd, s->nbnd, psi_b_h ? s->psi_b : nullptr, s->psi_max,
+                                  P.s_comp);
+            if (rc) return rc;
+            rc = pbe_transport_mules(s->mesh, s->scheme, nm, nc, s->m, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd, s->S,
+                                     s->psi_max, 0.0, 3, dt, s->mNew, P.s_comp);
+        }
         if (rc) return rc;
         std::swap(s->m, s->mNew);
         rc = pbe_qmom_clamp_d(ctx, nm, nc, nc, s->m, s->d, P.s_comp); // QMOM.C:117-125
@@ -835,11 +857,12 @@ int pbe_qmom_state_attach_mesh(pbe_qmom_state *s, pbe_mesh *mesh, int scheme) {
     PBE_REQUIRE(mc == s->nc, PBE_E_INVALID, "pbe_qmom_state_attach_mesh: the mesh has %lld cells, the state %lld",
                 (long long)mc, (long long)s->nc);
     DeviceGuard g(s->ctx->device);
-    for (double **p : {&s->mNew, &s->phi, &s->psi_b})
+    for (double **p : {&s->mNew, &s->phi, &s->psi_b, &s->psi_max})
         if (*p) {
             cudaFree(*p);
             *p = nullptr;
         }
+    PBE_CUDA(cudaMalloc((void **)&s->psi_max, (size_t)s->nm * 8));
     PBE_CUDA(cudaMalloc((void **)&s->mNew, (size_t)s->nm * std::max<int64_t>(s->nc, 1) * 8));
     PBE_CUDA(cudaMalloc((void **)&s->phi, (size_t)std::max<int64_t>(nint + nbnd, 1) * 8));
     PBE_CUDA(cudaMalloc((void **)&s->psi_b, (size_t)s->nm * std::max<int64_t>(nbnd, 1) * 8));

@@ -38,26 +38,7 @@
 #define PBE_TR_STAGES 2 // 0: register-staged loop; 2..4: cp.async pipeline depth (measured: 2, 3, 4 alike)
 #endif
 
-struct pbe_mesh {
-    pbe_ctx *ctx = nullptr;
-    int64_t ncells = 0, nint = 0, nbnd = 0, nirr = 0;
-    int maxf = 0; // most faces on any cell (info)
-    int F = 0;    // face count of the regular cells (0: none)
-    int32_t *d_other = nullptr; // [F][ncells]: neighbour cell; row 0 holds -1 for irregular cells
-    int32_t *d_face = nullptr;  // [F][ncells]: face index f (this cell owns it) or ~f (it is the neighbour)
-    double *d_vcell = nullptr;  // [ncells]
-    // irregular cells, CSR: entries of cell irr_cell[i] are irr_ptr[i] .. irr_ptr[i+1]-1
-    int32_t *d_irr_cell = nullptr, *d_irr_ptr = nullptr;
-    int32_t *d_irr_other = nullptr; // >= 0 neighbour cell; -(b + 2) boundary face b
-    int32_t *d_irr_face = nullptr;  // as d_face (boundary faces: n_internal + b)
-    int64_t coupled0 = 0, ncoupled = 0; // boundary faces [coupled0, coupled0 + ncoupled): processor patches
-    // the irregular cells' kernel runs beside the regular cells' one (disjoint outputs): fork / join
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    // resident fields of the host-buffer entry (pbe_moc_correct_host), grown on demand
-    double *res = nullptr;
-    size_t res_doubles = 0;
-};
+#include "pbe_mesh.h"
 
 namespace pbe {
 
@@ -352,10 +333,12 @@ int pbe_div_scheme_type(const char *name, int *out) {
         *out = PBE_DIV_UPWIND;
         return PBE_OK;
     }
+    if (!strcmp(name, "vanLeer") || !strcmp(name, "Gauss vanLeer")) {
+        *out = PBE_DIV_VANLEER;
+        return PBE_OK;
+    }
     set_error("Unknown or not yet supported divergence scheme \"%s\" for the device transport\n\n"
-              "Valid schemes are :\n(\nupwind\n)\n"
-              "(limited schemes such as vanLeer with the MULES correction are the next slice of "
-              "SURVEY.md row f2)",
+              "Valid schemes are :\n2\n(\nupwind\nvanLeer\n)",
               name);
     return PBE_E_UNKNOWN_TYPE;
 }
@@ -430,6 +413,25 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     for (int64_t b = 0; b < n_boundary_faces; ++b)
         put(boundary_owner[b], -(int32_t)b - 2, (int32_t)(n_internal_faces + b));
 
+    // one CSR over ALL cells, ascending face order per cell (internal faces, then boundary faces): the
+    // MULES kernels (pbe_mules.cu) walk it; entries as in the irregular-cell list
+    std::vector<int32_t> csr_ptr((size_t)ncells + 1, 0);
+    for (int64_t c = 0; c < ncells; ++c) csr_ptr[c + 1] = csr_ptr[c] + cnt[c] + bcnt[c];
+    std::vector<int32_t> csr_other((size_t)csr_ptr[ncells]), csr_face((size_t)csr_ptr[ncells]), cfill((size_t)ncells, 0);
+    auto cput = [&](int32_t c, int32_t oth, int32_t fc) {
+        const size_t k = (size_t)csr_ptr[c] + cfill[c]++;
+        csr_other[k] = oth;
+        csr_face[k] = fc;
+    };
+    for (int64_t f = 0; f < n_internal_faces; ++f) {
+        cput(owner[f], neighbour[f], (int32_t)f);
+        cput(neighbour[f], owner[f], ~(int32_t)f);
+    }
+    for (int64_t b = 0; b < n_boundary_faces; ++b)
+        cput(boundary_owner[b], -(int32_t)b - 2, (int32_t)(n_internal_faces + b));
+    std::vector<int32_t> own_v(owner, owner + n_internal_faces), nei_v(neighbour, neighbour + n_internal_faces),
+        bown_v(boundary_owner, boundary_owner + n_boundary_faces);
+
     pbe_mesh *m = new (std::nothrow) pbe_mesh;
     PBE_REQUIRE(m != nullptr, PBE_E_NOMEM, "pbe_mesh_create: out of host memory");
     m->ctx = ctx;
@@ -453,6 +455,12 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     upload(&m->d_irr_ptr, irr_ptr);
     upload(&m->d_irr_other, irr_other);
     upload(&m->d_irr_face, irr_face);
+    upload(&m->d_csr_ptr, csr_ptr);
+    upload(&m->d_csr_other, csr_other);
+    upload(&m->d_csr_face, csr_face);
+    upload(&m->d_owner, own_v);
+    upload(&m->d_neigh, nei_v);
+    upload(&m->d_bown, bown_v);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming);
@@ -477,6 +485,16 @@ int pbe_mesh_destroy(pbe_mesh *m) {
     cudaFree(m->d_irr_ptr);
     cudaFree(m->d_irr_other);
     cudaFree(m->d_irr_face);
+    cudaFree(m->d_csr_ptr);
+    cudaFree(m->d_csr_other);
+    cudaFree(m->d_csr_face);
+    cudaFree(m->d_owner);
+    cudaFree(m->d_neigh);
+    cudaFree(m->d_bown);
+    cudaFree(m->d_Sf);
+    cudaFree(m->d_C);
+    cudaFree(m->d_w);
+    cudaFree(m->mules_ws);
     cudaFree(m->res);
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);

@@ -275,6 +275,13 @@ class MOC:
                                                    _stream_ptr(n.device)))
         return mn, mx
 
+    def psi_max(self, alpha, vcell):
+        """max_c(alpha V / xi_k) per class (MOC.C:238): the upper bound MULES::limit is given"""
+        out = torch.empty(self.N, dtype=torch.float64, device=alpha.device)
+        capi.check(capi.lib().pbe_moc_psi_max(self._h, alpha.numel(), _ptr(alpha), _ptr(vcell), _ptr(out),
+                                              _stream_ptr(alpha.device)))
+        return out
+
     def source_host(self, n, eps, rho, nu, dt, out=None):
         """Host-buffer entry point (numpy or CPU torch tensors; pinned memory gives full rate)."""
         n_, eps_, rho_, nu_ = (_as_host(v) for v in (n, eps, rho, nu))
@@ -600,6 +607,25 @@ class Mesh:
             moc._h, self._h, div_scheme(scheme), n_.stride(0), _ptr(n_), _ptr(eps_), _ptr(rho_), _ptr(nu_),
             _ptr(phi_), _ptr(pb), 0 if pb is None else pb.stride(0), float(dt), _ptr(d)))
         return d
+
+    def set_geometry(self, Sf, C_, weights):
+        """fvMesh::Sf() [faces][3], C() [ncells][3], weights() [internal faces] for the limited schemes"""
+        a = [np.ascontiguousarray(v, dtype=np.float64) for v in (Sf, C_, weights)]
+        assert a[0].shape == (self.n_internal + self.n_boundary, 3) and a[1].shape == (self.ncells, 3)
+        assert a[2].shape == (self.n_internal,)
+        capi.check(capi.lib().pbe_mesh_set_geometry(self._h, a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data))
+
+    def transport_mules(self, psi, phi, dt, psi_max, *, scheme="vanLeer", psi_b=None, S=None, out=None, psi_min=0.0,
+                        n_limiter_iter=3):
+        """MOC::solveWithMULES's transport (MOC.C:198-272): limited high-order correction + upwind,
+        limitSum over the fields, MULES::explicitSolve.  psi_max: device tensor [K]."""
+        K, ncells = psi.shape
+        out = torch.empty_like(psi) if out is None else out
+        capi.check(capi.lib().pbe_transport_mules(
+            self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), K, psi.stride(0) if ncells else 0,
+            _ptr(psi), _ptr(phi), _ptr(psi_b), 0 if psi_b is None else psi_b.stride(0), _ptr(S), _ptr(psi_max),
+            float(psi_min), int(n_limiter_iter), float(dt), _ptr(out), _stream_ptr(psi.device)))
+        return out
 
     def set_coupled(self, first_boundary_face: int, count: int):
         """Mark boundary faces [first, first+count) as processor-patch faces (decomposed mesh)."""

@@ -164,24 +164,32 @@ def block_mesh(nx: int, ny: int, nz: int, lengths=(1.0, 1.0, 1.0), velocity=(1.0
     dx, dy, dz = lengths[0] / nx, lengths[1] / ny, lengths[2] / nz
     idx = np.arange(nx * ny * nz, dtype=np.int64).reshape(nz, ny, nx)
     u, v, w = velocity
-    own, nei, ph = [], [], []
-    for sl_o, sl_n, flux in (((slice(None), slice(None), slice(0, nx - 1)), (slice(None), slice(None), slice(1, nx)), u * dy * dz),
-                             ((slice(None), slice(0, ny - 1), slice(None)), (slice(None), slice(1, ny), slice(None)), v * dx * dz),
-                             ((slice(0, nz - 1), slice(None), slice(None)), (slice(1, nz), slice(None), slice(None)), w * dx * dy)):
+    own, nei, ph, sf = [], [], [], []
+    for sl_o, sl_n, flux, area in (
+            ((slice(None), slice(None), slice(0, nx - 1)), (slice(None), slice(None), slice(1, nx)), u * dy * dz, (dy * dz, 0.0, 0.0)),
+            ((slice(None), slice(0, ny - 1), slice(None)), (slice(None), slice(1, ny), slice(None)), v * dx * dz, (0.0, dx * dz, 0.0)),
+            ((slice(0, nz - 1), slice(None), slice(None)), (slice(1, nz), slice(None), slice(None)), w * dx * dy, (0.0, 0.0, dx * dy))):
         o, n = idx[sl_o].ravel(), idx[sl_n].ravel()
-        own.append(o); nei.append(n); ph.append(np.full(o.size, flux))
-    own, nei, ph = np.concatenate(own), np.concatenate(nei), np.concatenate(ph)
+        own.append(o); nei.append(n); ph.append(np.full(o.size, flux)); sf.append(np.tile(np.array(area), (o.size, 1)))
+    own, nei, ph, sf = np.concatenate(own), np.concatenate(nei), np.concatenate(ph), np.concatenate(sf)
     order = np.lexsort((nei, own))
-    own, nei, ph = own[order], nei[order], ph[order]
-    bown, bph, starts = [], [], [0]
-    for cells, flux in ((idx[:, :, 0], -u * dy * dz), (idx[:, :, -1], u * dy * dz),
-                        (idx[:, 0, :], -v * dx * dz), (idx[:, -1, :], v * dx * dz),
-                        (idx[0, :, :], -w * dx * dy), (idx[-1, :, :], w * dx * dy)):
+    own, nei, ph, sf = own[order], nei[order], ph[order], sf[order]
+    bown, bph, bsf, starts = [], [], [], [0]
+    for cells, flux, area in ((idx[:, :, 0], -u * dy * dz, (-dy * dz, 0.0, 0.0)), (idx[:, :, -1], u * dy * dz, (dy * dz, 0.0, 0.0)),
+                              (idx[:, 0, :], -v * dx * dz, (0.0, -dx * dz, 0.0)), (idx[:, -1, :], v * dx * dz, (0.0, dx * dz, 0.0)),
+                              (idx[0, :, :], -w * dx * dy, (0.0, 0.0, -dx * dy)), (idx[-1, :, :], w * dx * dy, (0.0, 0.0, dx * dy))):
         bown.append(cells.ravel()); bph.append(np.full(cells.size, flux)); starts.append(starts[-1] + cells.size)
-    bown, bph = np.concatenate(bown), np.concatenate(bph)
+        bsf.append(np.tile(np.array(area), (cells.size, 1)))
+    bown, bph, bsf = np.concatenate(bown), np.concatenate(bph), np.concatenate(bsf)
+    # geometry for the limited schemes (fvMesh::Sf(), C(), weights()): outward-from-owner face area
+    # vectors, cell centres, linear interpolation weights (1/2 on a uniform block)
+    kz, ky, kx = np.meshgrid(np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+    centres = np.stack([(kx.ravel() + 0.5) * dx, (ky.ravel() + 0.5) * dy, (kz.ravel() + 0.5) * dz], axis=1)
     return {"owner": own.astype(np.int32), "neighbour": nei.astype(np.int32),
             "boundary_owner": bown.astype(np.int32), "vcell": np.full(nx * ny * nz, dx * dy * dz),
-            "phi": np.concatenate([ph, bph]), "patch_start": np.array(starts), "shape": (nx, ny, nz)}
+            "phi": np.concatenate([ph, bph]), "patch_start": np.array(starts), "shape": (nx, ny, nz),
+            "Sf": np.ascontiguousarray(np.concatenate([sf, bsf])), "C": np.ascontiguousarray(centres),
+            "weights": np.full(own.size, 0.5)}
 
 
 def block_slab_part(n: int, rank: int, world: int, velocity=(1.0, 0.5, 0.25)):

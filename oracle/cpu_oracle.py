@@ -227,3 +227,64 @@ def transport_upwind_explicit(owner, neighbour, boundary_owner, vcell, psi, phi,
         _p(np.ascontiguousarray(phi, dtype=np.float64)), _p(psi_b), bown.size, c0, nc,
         _p(psi_halo) if nc else None, nc, _p(S), float(dt), _p(out))
     return out
+
+
+# ---- MULES-limited transport (oracle/pbe_oracle_mules.c; parity unpinned: OpenFOAM restated) ----------
+class OrcMesh(C.Structure):
+    _fields_ = [("ncells", C.c_int64), ("nint", C.c_int64), ("nbnd", C.c_int64), ("owner", C.c_void_p),
+                ("neighbour", C.c_void_p), ("bown", C.c_void_p), ("V", C.c_void_p), ("Sf", C.c_void_p),
+                ("C", C.c_void_p), ("weights", C.c_void_p)]
+
+
+DIV_SCHEMES = {"upwind": 0, "Gauss upwind": 0, "vanLeer": 1, "Gauss vanLeer": 1}
+
+
+def _orc_mesh(mesh: dict):
+    keep = {k: np.ascontiguousarray(mesh[k], dtype=np.int32) for k in ("owner", "neighbour", "boundary_owner")}
+    keep["V"] = np.ascontiguousarray(mesh["vcell"], dtype=np.float64)
+    for k in ("Sf", "C", "weights"):
+        keep[k] = np.ascontiguousarray(mesh[k], dtype=np.float64) if mesh.get(k) is not None else None
+    m = OrcMesh()
+    m.ncells, m.nint, m.nbnd = keep["V"].size, keep["owner"].size, keep["boundary_owner"].size
+    m.owner, m.neighbour, m.bown = (keep[k].ctypes.data for k in ("owner", "neighbour", "boundary_owner"))
+    m.V = keep["V"].ctypes.data
+    m.Sf, m.C, m.weights = (keep[k].ctypes.data if keep[k] is not None else None for k in ("Sf", "C", "weights"))
+    return m, keep
+
+
+def transport_mules(mesh: dict, scheme: str, psi, phi, dt, psi_max, *, S=None, psi_b=None, psi_min=0.0, n_limiter_iter=3):
+    """The call sequence of MOC::solveWithMULES (MOC.C:198-272) on psi [K][ncells]: high-order flux of
+    `scheme`, MULES::limit per field against psi_max[k] / psi_min, limitSum over the fields, upwind
+    flux + MULES::explicitSolve.  Returns the new fields."""
+    m, keep = _orc_mesh(mesh)
+    out = np.array(psi, dtype=np.float64, order="C", copy=True)
+    K, nc = out.shape
+    S = np.zeros_like(out) if S is None else np.ascontiguousarray(S, dtype=np.float64)
+    pb = None if psi_b is None else np.ascontiguousarray(psi_b, dtype=np.float64)
+    pmax = np.ascontiguousarray(np.broadcast_to(np.asarray(psi_max, dtype=np.float64), (K,)))
+    fn = lib().orc_transport_mules
+    fn.restype = C.c_int
+    fn.argtypes = [C.POINTER(OrcMesh), C.c_int, C.c_int, C.c_int64, _dp, _dp, _dp, C.c_int64, _dp, _dp, C.c_double,
+                   C.c_int, C.c_double]
+    rc = fn(C.byref(m), DIV_SCHEMES[scheme], K, nc, _p(out), _p(np.ascontiguousarray(phi, dtype=np.float64)), _p(pb),
+            0 if pb is None else pb.shape[1], _p(S), _p(pmax), float(psi_min), int(n_limiter_iter), float(dt))
+    if rc != 0:
+        raise RuntimeError(f"orc_transport_mules failed: {rc}")
+    del keep
+    return out
+
+
+def div_flux(mesh: dict, scheme: str, phi, psi, psi_b=None):
+    """fvc::flux(phi, psi, scheme) on every face [internal + boundary]"""
+    m, keep = _orc_mesh(mesh)
+    psi = np.ascontiguousarray(psi, dtype=np.float64)
+    out = np.empty(m.nint + m.nbnd)
+    fn = lib().orc_div_flux
+    fn.restype = C.c_int
+    fn.argtypes = [C.POINTER(OrcMesh), C.c_int, _dp, _dp, _dp, _dp]
+    rc = fn(C.byref(m), DIV_SCHEMES[scheme], _p(np.ascontiguousarray(phi, dtype=np.float64)), _p(psi),
+            _p(None if psi_b is None else np.ascontiguousarray(psi_b, dtype=np.float64)), _p(out))
+    if rc != 0:
+        raise RuntimeError(f"orc_div_flux failed: {rc}")
+    del keep
+    return out

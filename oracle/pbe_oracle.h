@@ -138,6 +138,34 @@ void orc_transport_upwind_explicit_coupled(int64_t ncells, int64_t nint, const i
                                            int64_t stride_h, const double *S, double dt,
                                            double *out);
 
+/* ---- transport, SURVEY 8 row f2 (second slice): the MULES-limited path of MOC::solveWithMULES
+ * (MOC.C:198-280) / QMOM::solveWithMULES (QMOM.C:131-197) for the schemes the reference's cases
+ * select (`Gauss vanLeer`, tests/validation/simmons_and_azzopardi/c01/system/fvSchemes:34; and
+ * `Gauss upwind`).  pbe_oracle_mules.c; PARITY UNPINNED (OpenFOAM 3.0.x restated, see that file). */
+typedef struct orc_mesh {
+    int64_t ncells, nint, nbnd;
+    const int32_t *owner, *neighbour, *bown; /* OpenFOAM face addressing; bown = faceCells of all patches */
+    const double *V;                         /* mesh.V() */
+    const double *Sf;                        /* [nint + nbnd][3] face area vectors (limited schemes) or NULL */
+    const double *C;                         /* [ncells][3] cell centres or NULL */
+    const double *weights;                   /* [nint] linear interpolation weights (mesh.weights()) or NULL */
+} orc_mesh;
+enum { ORC_DIV_UPWIND = 0, ORC_DIV_VANLEER = 1 };
+void orc_upwind_flux(const orc_mesh *m, const double *phi, const double *psi, const double *psi_b, double *out);
+void orc_gauss_linear_grad(const orc_mesh *m, const double *psi, const double *psi_b, double *grad);
+void orc_vanleer_flux(const orc_mesh *m, const double *phi, const double *psi, const double *psi_b, double *out);
+int orc_div_flux(const orc_mesh *m, int scheme, const double *phi, const double *psi, const double *psi_b, double *out);
+void orc_mules_limiter(const orc_mesh *m, double *lambda, double rDeltaT, const double *psi, const double *psi_b,
+                       const double *phiBD, const double *phiCorr, const double *Su, double psiMax, double psiMin,
+                       int nLimiterIter);
+void orc_mules_limit(const orc_mesh *m, double rDeltaT, const double *psi, const double *psi_b, const double *phi,
+                     double *phiPsi, const double *Su, double psiMax, double psiMin, int nLimiterIter);
+void orc_mules_limit_sum(int nfields, int64_t nint, int64_t stride_f, double *corr);
+void orc_mules_explicit_solve(const orc_mesh *m, double rDeltaT, double *psi, const double *phiPsi, const double *Su);
+int orc_transport_mules(const orc_mesh *m, int scheme, int nfields, int64_t stride, double *psi, const double *phi,
+                        const double *psi_b, int64_t stride_b, const double *S, const double *psiMax, double psiMin,
+                        int nLimiterIter, double dt);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -10,178 +10,59 @@
 
 namespace Foam {
 
-// ---- Gauss linear gradient (gradSchemes default of the reference's cases) -----------------------------
-static std::vector<vector> gaussLinearGrad(const volScalarField &vf) {
-    const fvMesh &mesh = vf.mesh();
-    const label ni = mesh.nInternalFaces();
-    std::vector<vector> g((size_t)mesh.nCells(), vector{0, 0, 0});
-    for (label f = 0; f < ni; ++f) {
-        const label own = mesh.owner_[f], nei = mesh.neighbour_[f];
-        const scalar w = mesh.weights_[f];
-        const scalar ssf = w * (vf[own] - vf[nei]) + vf[nei]; // linear interpolate: lambda*(P - N) + N
-        const vector Sfssf = ssf * mesh.Sf_[f];
-        g[own] = g[own] + Sfssf;
-        g[nei] = g[nei] - Sfssf;
-    }
-    for (label b = 0; b < (label)mesh.boundaryFaceCells_.size(); ++b) {
-        const label c = mesh.boundaryFaceCells_[b];
-        g[c] = g[c] + vf.patchValue(b) * mesh.Sf_[ni + b];
-    }
-    for (label c = 0; c < mesh.nCells(); ++c) g[c] = (1.0 / mesh.V()[c]) * g[c];
-    return g;
+extern "C" {
+#include "../pbe_oracle.h"
 }
 
-// NVDTVD::r (LimitedScheme/NVDTVD.H) and the vanLeer limiter (vanLeer.H)
-static inline scalar nvdtvd_r(const scalar faceFlux, const scalar phiP, const scalar phiN, const vector &gradcP,
-                              const vector &gradcN, const vector &d) {
-    const scalar gradf = phiN - phiP;
-    scalar gradcf;
-    if (faceFlux > 0)
-        gradcf = d & gradcP;
-    else
-        gradcf = d & gradcN;
-    if (mag(gradcf) >= 1000 * mag(gradf))
-        return 2 * 1000 * sign(gradcf) * sign(gradf) - 1;
-    return 2 * (gradcf / gradf) - 1;
+// The OpenFOAM algorithms themselves live in oracle/pbe_oracle_mules.c (plain C on plain arrays) so that
+// ONE restatement serves both the reference's own call sequence (through this shim) and the port's
+// (orc_transport_mules); the functions below only unpack the shim's containers.
+static orc_mesh as_orc(const fvMesh &mesh) {
+    orc_mesh m;
+    m.ncells = mesh.nCells();
+    m.nint = mesh.nInternalFaces();
+    m.nbnd = (int64_t)mesh.boundaryFaceCells_.size();
+    m.owner = mesh.owner_.data();
+    m.neighbour = mesh.neighbour_.data();
+    m.bown = mesh.boundaryFaceCells_.data();
+    m.V = mesh.V().data();
+    static_assert(sizeof(Vec3) == 3 * sizeof(double), "Vec3 is three packed doubles");
+    m.Sf = ((label)mesh.Sf_.size() == mesh.nFaces() && mesh.nFaces() > 0) ? &mesh.Sf_[0].x : nullptr;
+    m.C = (mesh.nCells() > 0) ? &mesh.C()[0].x : nullptr;
+    m.weights = (mesh.weights_.size() == mesh.nInternalFaces() && mesh.nInternalFaces() > 0) ? mesh.weights_.data() : nullptr;
+    return m;
 }
+static const double *patch_values(const volScalarField &vf) { return vf.bf_.empty() ? nullptr : vf.bf_.data(); }
 
 namespace fvc {
-// fvc::flux(phi, vf, name) = scheme(mesh, phi, divScheme(name)).dotInterpolate(phi, vf):
-// phi * (weights * P + (1 - weights) * N) with the scheme's weights; patch values on boundary faces.
+// fvc::flux(phi, vf, name) = scheme(mesh, phi, divScheme(name)).dotInterpolate(phi, vf)
 surfaceScalarField flux(const surfaceScalarField &phi, const volScalarField &vf, const word &name) {
     const fvMesh &mesh = vf.mesh();
     const word scheme = mesh.divScheme(name);
-    if (scheme == "Gauss upwind" || scheme == "upwind") return upwind<scalar>(mesh, phi).flux(vf);
-    if (scheme != "Gauss vanLeer" && scheme != "vanLeer")
+    int id = -1;
+    if (scheme == "Gauss upwind" || scheme == "upwind") id = ORC_DIV_UPWIND;
+    if (scheme == "Gauss vanLeer" || scheme == "vanLeer") id = ORC_DIV_VANLEER;
+    if (id < 0)
         FatalErrorIn("fvc::flux") << "unknown discretisation scheme " << scheme
                                   << "\n\nValid schemes are :\n2\n(\nupwind\nvanLeer\n)" << exit(FatalError);
-    // limitedScheme<vanLeer>: limiter(r), weights = limiter * w_linear + (1 - limiter) * pos(phi)
-    const label ni = mesh.nInternalFaces();
-    if ((label)mesh.Sf_.size() != mesh.nFaces() || mesh.weights_.size() != ni)
-        FatalErrorIn("fvc::flux") << "scheme " << scheme << " needs the mesh geometry (Sf, C, weights)" << exit(FatalError);
-    const std::vector<vector> gradc = gaussLinearGrad(vf);
     surfaceScalarField r("flux(" + vf.name() + ")", mesh);
-    for (label f = 0; f < ni; ++f) {
-        const label own = mesh.owner_[f], nei = mesh.neighbour_[f];
-        const vector d = mesh.C()[nei] - mesh.C()[own];
-        const scalar rr = nvdtvd_r(phi[f], vf[own], vf[nei], gradc[own], gradc[nei], d);
-        const scalar limiter = (rr + mag(rr)) / (1 + mag(rr)); // vanLeer
-        const scalar w = limiter * mesh.weights_[f] + (1.0 - limiter) * pos(phi[f]);
-        r[f] = phi[f] * (w * (vf[own] - vf[nei]) + vf[nei]);
-    }
-    // uncoupled patches: the limiter is 1 and the face value the patch value
-    for (label b = 0; b < (label)mesh.boundaryFaceCells_.size(); ++b) r[ni + b] = phi[ni + b] * vf.patchValue(b);
+    const orc_mesh m = as_orc(mesh);
+    if (orc_div_flux(&m, id, phi.f_.data(), vf.internalField().data(), patch_values(vf), r.f_.data()) != 0)
+        FatalErrorIn("fvc::flux") << "scheme " << scheme << " needs the mesh geometry (Sf, C, weights)" << exit(FatalError);
     return r;
 }
 } // namespace fvc
 
 namespace MULES {
 
-// MULESTemplates.C: limiter().  rho = geometricOneField, Sp = zeroField (what MOC.C:240-249 and
-// QMOM.C:173-182 pass); no coupled patches, no moving mesh, smoothLimiter = 0.
 void limiter(scalarField &allLambda, const scalar rDeltaT, const volScalarField &psi, const surfaceScalarField &phiBD,
              const surfaceScalarField &phiCorr, const volScalarField &Su, const scalar psiMax, const scalar psiMin) {
-    const fvMesh &mesh = psi.mesh();
-    const scalarField &psiIf = psi.internalField();
-    const label nLimiterIter = mesh.nLimiterIter_;
-    const volScalarField &psi0f = psi.oldTime();
-    const std::vector<label> &owner = mesh.owner_, &neighb = mesh.neighbour_, &bfc = mesh.boundaryFaceCells_;
-    const scalarField &V = mesh.Vsc();
-    const label ni = mesh.nInternalFaces(), nb = (label)bfc.size(), nc = psiIf.size();
-
-    scalarField psiMaxn(nc, psiMin), psiMinn(nc, psiMax);
-    scalarField sumPhiBD(nc, 0.0), sumPhip(nc, VSMALL), mSumPhim(nc, VSMALL);
-
-    for (label facei = 0; facei < ni; ++facei) {
-        const label own = owner[facei], nei = neighb[facei];
-        psiMaxn[own] = max(psiMaxn[own], psiIf[nei]);
-        psiMinn[own] = min(psiMinn[own], psiIf[nei]);
-        psiMaxn[nei] = max(psiMaxn[nei], psiIf[own]);
-        psiMinn[nei] = min(psiMinn[nei], psiIf[own]);
-        sumPhiBD[own] += phiBD[facei];
-        sumPhiBD[nei] -= phiBD[facei];
-        const scalar phiCorrf = phiCorr[facei];
-        if (phiCorrf > 0.0) {
-            sumPhip[own] += phiCorrf;
-            mSumPhim[nei] += phiCorrf;
-        } else {
-            mSumPhim[own] -= phiCorrf;
-            sumPhip[nei] -= phiCorrf;
-        }
-    }
-    for (label b = 0; b < nb; ++b) { // uncoupled patches: the patch value bounds the cell
-        const label pfCelli = bfc[b];
-        const scalar psiPf = psi.patchValue(b);
-        psiMaxn[pfCelli] = max(psiMaxn[pfCelli], psiPf);
-        psiMinn[pfCelli] = min(psiMinn[pfCelli], psiPf);
-    }
-    for (label b = 0; b < nb; ++b) {
-        const label pfCelli = bfc[b];
-        sumPhiBD[pfCelli] += phiBD[ni + b];
-        const scalar phiCorrf = phiCorr[ni + b];
-        if (phiCorrf > 0.0)
-            sumPhip[pfCelli] += phiCorrf;
-        else
-            mSumPhim[pfCelli] -= phiCorrf;
-    }
-    for (label c = 0; c < nc; ++c) {
-        psiMaxn[c] = min(psiMaxn[c], psiMax);
-        psiMinn[c] = max(psiMinn[c], psiMin);
-    }
-    // psiMaxn = V*((rho*rDeltaT - Sp)*psiMaxn - Su - rho*rDeltaT*psi0) + sumPhiBD, rho = 1, Sp = 0
-    for (label c = 0; c < nc; ++c) {
-        psiMaxn[c] = V[c] * ((rDeltaT - 0.0) * psiMaxn[c] - Su[c] - rDeltaT * psi0f[c]) + sumPhiBD[c];
-        psiMinn[c] = V[c] * (Su[c] - (rDeltaT - 0.0) * psiMinn[c] + rDeltaT * psi0f[c]) - sumPhiBD[c];
-    }
-
-    scalarField sumlPhip(nc), mSumlPhim(nc);
-    for (int j = 0; j < nLimiterIter; j++) {
-        sumlPhip = 0.0;
-        mSumlPhim = 0.0;
-        for (label facei = 0; facei < ni; ++facei) {
-            const label own = owner[facei], nei = neighb[facei];
-            const scalar lambdaPhiCorrf = allLambda[facei] * phiCorr[facei];
-            if (lambdaPhiCorrf > 0.0) {
-                sumlPhip[own] += lambdaPhiCorrf;
-                mSumlPhim[nei] += lambdaPhiCorrf;
-            } else {
-                mSumlPhim[own] -= lambdaPhiCorrf;
-                sumlPhip[nei] -= lambdaPhiCorrf;
-            }
-        }
-        for (label b = 0; b < nb; ++b) {
-            const label pfCelli = bfc[b];
-            const scalar lambdaPhiCorrf = allLambda[ni + b] * phiCorr[ni + b];
-            if (lambdaPhiCorrf > 0.0)
-                sumlPhip[pfCelli] += lambdaPhiCorrf;
-            else
-                mSumlPhim[pfCelli] -= lambdaPhiCorrf;
-        }
-        for (label celli = 0; celli < nc; ++celli) {
-            sumlPhip[celli] = max(min((sumlPhip[celli] + psiMaxn[celli]) / (mSumPhim[celli] - SMALL), 1.0), 0.0);
-            mSumlPhim[celli] = max(min((mSumlPhim[celli] + psiMinn[celli]) / (sumPhip[celli] + SMALL), 1.0), 0.0);
-        }
-        const scalarField &lambdam = sumlPhip;
-        const scalarField &lambdap = mSumlPhim;
-        for (label facei = 0; facei < ni; ++facei) {
-            if (phiCorr[facei] > 0.0)
-                allLambda[facei] = min(allLambda[facei], min(lambdap[owner[facei]], lambdam[neighb[facei]]));
-            else
-                allLambda[facei] = min(allLambda[facei], min(lambdam[owner[facei]], lambdap[neighb[facei]]));
-        }
-        for (label b = 0; b < nb; ++b) { // uncoupled patch: limit outlet faces only
-            if ((phiBD[ni + b] + phiCorr[ni + b]) > SMALL * SMALL) {
-                const label pfCelli = bfc[b];
-                if (phiCorr[ni + b] > 0.0)
-                    allLambda[ni + b] = min(allLambda[ni + b], lambdap[pfCelli]);
-                else
-                    allLambda[ni + b] = min(allLambda[ni + b], lambdam[pfCelli]);
-            }
-        }
-    }
+    const orc_mesh m = as_orc(psi.mesh());
+    orc_mules_limiter(&m, allLambda.data(), rDeltaT, psi.internalField().data(), patch_values(psi), phiBD.f_.data(),
+                      phiCorr.f_.data(), Su.internalField().data(), psiMax, psiMin, psi.mesh().nLimiterIter_);
 }
 
-// MULESTemplates.C: limit()
+// MULESTemplates.C: limit(): phiBD = upwind flux; phiCorr = phiPsi - phiBD; limiter; returnCorr
 void limit(const scalar rDeltaT, const geometricOneField &, const volScalarField &psi, const surfaceScalarField &phi,
            surfaceScalarField &phiPsi, const zeroField &, const volScalarField &Su, const scalar psiMax,
            const scalar psiMin, const bool returnCorr) {
@@ -198,44 +79,27 @@ void limit(const scalar rDeltaT, const geometricOneField &, const volScalarField
     }
 }
 
-// MULES.C: limitSum() on the internal faces (boundary patches only when coupled: none here)
+// MULES.C: limitSum() over the fields, internal faces
 void limitSum(PtrList<surfaceScalarField> &phiPsiCorrs) {
-    if (phiPsiCorrs.size() == 0) return;
-    const label ni = phiPsiCorrs[0].mesh().nInternalFaces();
-    for (label facei = 0; facei < ni; ++facei) {
-        scalar sumPos = 0, sumNeg = 0;
-        for (int phasei = 0; phasei < phiPsiCorrs.size(); phasei++) {
-            if (phiPsiCorrs[phasei][facei] > 0)
-                sumPos += phiPsiCorrs[phasei][facei];
-            else
-                sumNeg += phiPsiCorrs[phasei][facei];
-        }
-        const scalar sum = sumPos + sumNeg;
-        if (sum > 0 && sumPos > VSMALL) {
-            const scalar lambda = -sumNeg / sumPos;
-            for (int phasei = 0; phasei < phiPsiCorrs.size(); phasei++)
-                if (phiPsiCorrs[phasei][facei] > 0) phiPsiCorrs[phasei][facei] *= lambda;
-        } else if (sum < 0 && sumNeg < -VSMALL) {
-            const scalar lambda = -sumPos / sumNeg;
-            for (int phasei = 0; phasei < phiPsiCorrs.size(); phasei++)
-                if (phiPsiCorrs[phasei][facei] < 0) phiPsiCorrs[phasei][facei] *= lambda;
-        }
-    }
+    const label K = phiPsiCorrs.size();
+    if (K == 0) return;
+    const label nf = phiPsiCorrs[0].size(), ni = phiPsiCorrs[0].mesh().nInternalFaces();
+    std::vector<double> all((size_t)K * (size_t)(nf > 0 ? nf : 1));
+    for (label k = 0; k < K; ++k)
+        for (label f = 0; f < nf; ++f) all[(size_t)k * nf + f] = phiPsiCorrs[k][f];
+    orc_mules_limit_sum(K, ni, nf, all.data());
+    for (label k = 0; k < K; ++k)
+        for (label f = 0; f < nf; ++f) phiPsiCorrs[k][f] = all[(size_t)k * nf + f];
 }
 
-// MULESTemplates.C: explicitSolve() with rho = 1, Sp = 0:
-//   psi = (psi0 rDeltaT + Su - surfaceIntegrate(phiPsi)) / rDeltaT,  rDeltaT = 1 / deltaTValue
+// MULESTemplates.C: explicitSolve() with rho = 1, Sp = 0
 void explicitSolve(const geometricOneField &, volScalarField &psi, const surfaceScalarField &phiPsi, const zeroField &,
                    const volScalarField &Su) {
     Info << "MULES: Solving for " << psi.name() << endl;
     refProbe::record(psi.name(), Su.internalField());
-    const fvMesh &mesh = psi.mesh();
-    const scalar rDeltaT = 1.0 / mesh.time().deltaTValue();
-    scalarField psi0(psi.internalField());
-    scalarField &psiIf = psi.internalField();
-    psiIf = 0.0;
-    fvc::surfaceIntegrate(psiIf, phiPsi);
-    for (label c = 0; c < psiIf.size(); ++c) psiIf[c] = (psi0[c] * rDeltaT + Su[c] - psiIf[c]) / rDeltaT;
+    const orc_mesh m = as_orc(psi.mesh());
+    orc_mules_explicit_solve(&m, 1.0 / psi.mesh().time().deltaTValue(), psi.internalField().data(), phiPsi.f_.data(),
+                             Su.internalField().data());
 }
 
 } // namespace MULES
