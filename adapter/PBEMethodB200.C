@@ -14,13 +14,15 @@ void b200Check(int rc, const char *where) {
 
 // coalescenceKernel::New / breakupKernel::New / daughterParticleDistribution::New
 // (coalescenceKernel.C:52-70, breakupKernel.C:52-70, daughterParticleDistribution.C:63-81): the
-// TypeName is looked up in the library's tables; an unknown one fails listing the valid types.
+// TypeName is looked up in the library's tables -- an unknown one fails listing the valid types -- and
+// the coefficients come from pbeDict.subDict(<TypeName> + "Coeffs"), which is fatal when absent.
 pbe_kernel_spec b200KernelSpec(const dictionary &pbeProperties) {
     pbe_kernel_spec s;
     std::memset(&s, 0, sizeof(s));
     const word ck(pbeProperties.lookup("coalescenceKernel"));
+    Info << "Selecting coalescence model: " << ck << endl;
     b200Check(pbe_coalescence_type(ck.c_str(), &s.coalescence), "coalescenceKernel::New");
-    const dictionary &cd = pbeProperties.optionalSubDict(ck + "Coeffs");
+    const dictionary &cd = pbeProperties.subDict(ck + "Coeffs");
     if (s.coalescence == PBE_COAL_CONSTANT) {
         s.coal_c[0] = readScalar(cd.lookup("constant")); // constantCoalescence.C:48
     } else if (s.coalescence == PBE_COAL_CT) {           // coalescenceKernels/CoulaloglouTavlarides.C:39-42
@@ -30,8 +32,9 @@ pbe_kernel_spec b200KernelSpec(const dictionary &pbeProperties) {
         s.coal_c[3] = cd.lookupOrDefault<scalar>("sigma", 0.047);
     }
     const word bk(pbeProperties.lookup("breakupKernel"));
+    Info << "Selecting breakup model: " << bk << endl;
     b200Check(pbe_breakup_type(bk.c_str(), &s.breakup), "breakupKernel::New");
-    const dictionary &bd = pbeProperties.optionalSubDict(bk + "Coeffs");
+    const dictionary &bd = pbeProperties.subDict(bk + "Coeffs");
     if (s.breakup == PBE_BR_CT) { // breakupKernels/CoulaloglouTavlarides.C:46-49
         s.br_c[0] = bd.lookupOrDefault<scalar>("c1", 0.00487);
         s.br_c[1] = bd.lookupOrDefault<scalar>("c2", 0.008);
@@ -39,7 +42,9 @@ pbe_kernel_spec b200KernelSpec(const dictionary &pbeProperties) {
         s.br_c[3] = bd.lookupOrDefault<scalar>("sigma", 0.047);
     }
     const word dk(pbeProperties.lookup("daughterParticleDistribution"));
+    Info << "Selecting daughter particle model: " << dk << endl;
     b200Check(pbe_daughter_type(dk.c_str(), &s.daughter), "daughterParticleDistribution::New");
+    (void)pbeProperties.subDict(dk + "Coeffs");
     return s;
 }
 
@@ -84,22 +89,79 @@ void PBEMethod::updatePhaseFields() {
     std::memcpy(nuHost_.data_ptr(), tnu().internalField().cdata(), sizeof(scalar) * phase_.size());
 }
 
-namespace PBEMethods {
+int PBEMethod::divSchemeOf(const dictionary &coeffs, const char *where) const {
+#ifdef PBE_B200_REAL_OPENFOAM
+    // fvSchemes: divSchemes { "div\\(phi,n.*\\)" Gauss vanLeer; }  (c01/system/fvSchemes:34)
+    ITstream &is = phase_.mesh().divScheme("div(phi,n0)");
+    word scheme(is);
+    if (!is.eof()) scheme += " " + word(is);
+#else
+    const word scheme = phase_.mesh().divScheme_.empty() ? coeffs.lookupOrDefault<word>("divScheme", "Gauss upwind")
+                                                         : phase_.mesh().divScheme_;
+#endif
+    int id = PBE_DIV_UPWIND;
+    b200Check(pbe_div_scheme_type(scheme.c_str(), &id), where); // unknown: FatalError listing the valid ones
+    return id;
+}
 
-// ---- MOC ------------------------------------------------------------------------------------------
-defineTypeNameAndDebug(MOC, 0);
-addToRunTimeSelectionTable(PBEMethod, MOC, dictionary);
+pbe_mesh *PBEMethod::newDeviceMesh(int scheme, const char *where) const {
+    const fvMesh &mesh = phase_.mesh();
+    pbe_mesh *m = nullptr;
+#ifdef PBE_B200_REAL_OPENFOAM
+    std::vector<int32_t> own(mesh.owner().begin(), mesh.owner().end()), nei(mesh.neighbour().begin(), mesh.neighbour().end()), bfc;
+    forAll(mesh.boundary(), patchi) {
+        const labelUList &fc = mesh.boundary()[patchi].faceCells();
+        bfc.insert(bfc.end(), fc.begin(), fc.end());
+    }
+    b200Check(pbe_mesh_create(ctx_, mesh.nCells(), mesh.nInternalFaces(), own.data(), nei.data(), (int64_t)bfc.size(),
+                              bfc.data(), mesh.V().field().cdata(), &m), where);
+    if (scheme != PBE_DIV_UPWIND) {
+        std::vector<double> Sf(3 * mesh.nFaces()), C(3 * mesh.nCells());
+        forAll(mesh.Sf().internalField(), f) for (int d = 0; d < 3; ++d) Sf[3 * f + d] = mesh.Sf().internalField()[f][d];
+        label f0 = mesh.nInternalFaces();
+        forAll(mesh.boundary(), patchi) forAll(mesh.boundary()[patchi], i) {
+            for (int d = 0; d < 3; ++d) Sf[3 * f0 + d] = mesh.Sf().boundaryField()[patchi][i][d];
+            ++f0;
+        }
+        forAll(mesh.C().internalField(), c) for (int d = 0; d < 3; ++d) C[3 * c + d] = mesh.C().internalField()[c][d];
+        b200Check(pbe_mesh_set_geometry(m, Sf.data(), C.data(), mesh.weights().internalField().cdata()), where);
+    }
+#else
+    std::vector<int32_t> own(mesh.owner().begin(), mesh.owner().end()), nei(mesh.neighbour().begin(), mesh.neighbour().end()),
+        bfc(mesh.boundaryFaceCells_.begin(), mesh.boundaryFaceCells_.end());
+    b200Check(pbe_mesh_create(ctx_, mesh.nCells(), mesh.nInternalFaces(), own.data(), nei.data(), (int64_t)bfc.size(),
+                              bfc.data(), mesh.V().cdata(), &m), where);
+    if (scheme != PBE_DIV_UPWIND) {
+        if (!mesh.hasGeometry())
+            FatalErrorIn(where) << "the limited divergence scheme needs fvMesh::Sf(), C() and weights()" << exit(FatalError);
+        b200Check(pbe_mesh_set_geometry(m, mesh.Sf_.data(), mesh.C_.data(), mesh.weights_.data()), where);
+    }
+#endif
+    return m;
+}
+
+namespace PBEMethods {
 
 static inline std::string fieldName(const char *stem, label i) {
     std::ostringstream os;
     os << stem << i;
     return os.str();
 }
+//- printAvgMaxMin (Utility.C:4-10) from the {sum f V, sum V, max, min} partials the library returns
+//  (a parallel run reduces the four numbers over the ranks first: sum, sum, max, min)
+static inline void printAvgMaxMin(const word &name, const scalar *s) {
+    Info << name << ": avg, max,min " << s[0] / s[1] << ", " << s[2] << ", " << s[3] << endl;
+}
+
+// ---- MOC ------------------------------------------------------------------------------------------
+defineTypeNameAndDebug(MOC, 0);
+addToRunTimeSelectionTable(PBEMethod, MOC, dictionary);
 
 MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     : PBEMethod(pbeProperties, phase), runTime(phase.mesh().time()), deltaXi_("deltaXi", 0.0),
-      numberOfClasses_(0), usingMULES_(false), source_term_relaxation_(1.0), moc_(nullptr), nHost_(nullptr),
-      SHost_(nullptr), continuityError_(0.0), b200Mesh_(nullptr), divScheme_(PBE_DIV_UPWIND) {
+      numberOfClasses_(0), usingMULES_(false), source_term_relaxation_(1.0), moc_(nullptr), state_(nullptr),
+      b200Mesh_(nullptr), d_("d." + phase.name(), phase.mesh(), 0.0, false), continuityError_(0.0), hostStale_(false),
+      deviceStale_(true) {
     const dictionary &MOCDict_ = pbeProperties.subDict("MOCCoeffs"); // MOC.C:51-60
     numberOfClasses_ = readLabel(MOCDict_.lookup("numberOfClasses"));
     deltaXi_ = dimensionedScalar("deltaXi", readScalar(MOCDict_.lookup("xi1")));
@@ -107,137 +169,117 @@ MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     source_term_relaxation_ = MOCDict_.lookupOrDefault<scalar>("sourceRelaxation", 1.0);
     Info << "Creating " << numberOfClasses_ << " class" << (numberOfClasses_ > 1 ? "es" : "") << endl;
     classNumberDensity_ = PtrList<volScalarField>(numberOfClasses_);
-    forAll(classNumberDensity_, i) // MOC.C:69-77: fields n0 .. n<N-1>, registered on the mesh
+    classMin_ = scalarField(numberOfClasses_, 0.0);
+    forAll(classNumberDensity_, i) // MOC.C:69-77: fields n0 .. n<N-1>, MUST_READ, registered on the mesh
         classNumberDensity_.set(i, new volScalarField(fieldName("n", i), phase.mesh()));
     b200Check(pbe_moc_create(ctx_, numberOfClasses_, deltaXi_.value(), &spec_, source_term_relaxation_, &moc_),
               "MOC::MOC");
-    const int64_t bytes = (int64_t)sizeof(double) * numberOfClasses_ * phase.size();
-    b200Check(pbe_host_alloc(ctx_, bytes, (void **)&nHost_), "MOC::MOC");
-    b200Check(pbe_host_alloc(ctx_, bytes, (void **)&SHost_), "MOC::MOC");
     const fvMesh &mesh = phase.mesh();
-    if (mesh.hasFaces() && usingMULES_) {
-        // fvSchemes divSchemes "div\\(phi,n.*\\)" (the shim reads it from MOCCoeffs); a scheme without a
-        // device path is a FatalError listing the valid ones, like any other run-time selection
-        const word scheme = MOCDict_.lookupOrDefault<word>("divScheme", "Gauss upwind");
-        b200Check(pbe_div_scheme_type(scheme.c_str(), &divScheme_), "MOC::MOC div(phi,n.*)");
-        std::vector<int32_t> own(mesh.owner().begin(), mesh.owner().end()),
-            nei(mesh.neighbour().begin(), mesh.neighbour().end()),
-            bfc(mesh.boundaryFaceCells_.begin(), mesh.boundaryFaceCells_.end());
-        b200Check(pbe_mesh_create(ctx_, mesh.nCells(), mesh.nInternalFaces(), own.data(), nei.data(),
-                                  (int64_t)bfc.size(), bfc.data(), mesh.V().cdata(), &b200Mesh_),
-                  "MOC::MOC mesh");
+    b200Check(pbe_moc_state_create(moc_, mesh.nCells(), mesh.V().cdata(), &state_), "MOC::MOC");
+    if (mesh.hasFaces()) {
+        if (!usingMULES_) {
+#ifdef PBE_B200_REAL_OPENFOAM
+            // implicit path (MOC.C:186-198): kept on the host, see correct()
+#else
+            FatalErrorIn("MOC::MOC") << "usingMULES false selects the implicit fvm::ddt + fvm::div solve (MOC.C:186-198), "
+                                        "which has no device path; set usingMULES true" << exit(FatalError);
+#endif
+        } else {
+            const int scheme = divSchemeOf(MOCDict_, "MOC::MOC div(phi,n.*)");
+            b200Mesh_ = newDeviceMesh(scheme, "MOC::MOC mesh");
+            b200Check(pbe_moc_state_attach_mesh(state_, b200Mesh_, scheme), "MOC::MOC");
+        }
+    } else if (!usingMULES_) {
+        // no faces: fvm::ddt(n) == S and MULES::explicitSolve both reduce to n += dt S
+        Info << "MOC: no face fluxes on this mesh: explicit zero-flux update (usingMULES false would solve the same "
+                "diagonal system)" << endl;
     }
 }
 
 MOC::~MOC() {
-    if (nHost_) pbe_host_free(ctx_, nHost_);
-    if (SHost_) pbe_host_free(ctx_, SHost_);
+    if (state_) pbe_moc_state_destroy(state_);
     if (b200Mesh_) pbe_mesh_destroy(b200Mesh_);
     if (moc_) pbe_moc_destroy(moc_);
 }
 
-// MOC::correct(), MOC.C:159-184.  Replaced: the breakup-rate cache fill (:162-171),
-// coalescence_().update() (:173) and the N calls of classSourceTerm(k) (:174-175, i.e.
-// :87-157).  Kept: the transport step (:177-180) and the min(n_k) prints (:181-183).
-void MOC::correct() {
+void MOC::upload() { // each field is contiguous: it becomes row k of the class-major device block
     const label nCells = phase_.size();
-    forAll(classNumberDensity_, k) // each field is contiguous: it becomes row k of the class-major block
-        std::memcpy(nHost_ + (size_t)k * nCells, classNumberDensity_[k].internalField().cdata(),
-                    sizeof(double) * nCells);
+    std::vector<double> stage((size_t)numberOfClasses_ * nCells);
+    forAll(classNumberDensity_, k)
+        std::memcpy(stage.data() + (size_t)k * nCells, classNumberDensity_[k].internalField().cdata(), sizeof(double) * nCells);
+    b200Check(pbe_moc_state_upload(state_, nCells, stage.data()), "MOC::upload");
+    deviceStale_ = false;
+    hostStale_ = false;
+}
+
+void MOC::download() const { // runTime.write(): the AUTO_WRITE fields n<k>
+    const label nCells = phase_.size();
+    std::vector<double> stage((size_t)numberOfClasses_ * nCells);
+    b200Check(pbe_moc_state_download(state_, nCells, stage.data()), "MOC::download");
+    forAll(classNumberDensity_, k)
+        std::memcpy(classNumberDensity_[k].internalField().data_ptr(), stage.data() + (size_t)k * nCells, sizeof(double) * nCells);
+    hostStale_ = false;
+}
+
+volScalarField &MOC::classNumberDensity(label k) {
+    if (hostStale_) download();
+    deviceStale_ = true; // the caller may write it
+    return classNumberDensity_[k];
+}
+
+// MOC::correct(), MOC.C:159-184, in one library call: the breakup-rate cache fill (:162-171),
+// coalescence_().update() (:173), the N classSourceTerm(k) (:174-175, i.e. :87-157), solveWithMULES (:198-272: limited
+// high-order flux, MULES::limit, limitSum, explicitSolve -- or the zero-flux update when the mesh has no
+// faces), the continuity check (:254-279), the min(n_k) prints (:181-183) and d() (:282-290).
+void MOC::correct() {
+    if (deviceStale_) upload();
     updatePhaseFields();
-    if (b200Mesh_) {
-        correctWithTransport();
+#ifdef PBE_B200_REAL_OPENFOAM
+    if (!usingMULES_ && phase_.mesh().nInternalFaces() > 0) {
+        // implicit path: the sources come from the device, the reference's solveWithFVM(S) (MOC.C:186-198)
+        // runs unchanged on the host fields, which are then uploaded again
+        const label nCells = phase_.size();
+        std::vector<double> nH((size_t)numberOfClasses_ * nCells), SH(nH.size());
+        b200Check(pbe_moc_state_download(state_, nCells, nH.data()), "MOC::correct");
+        b200Check(pbe_moc_source_host(moc_, nCells, nCells, nH.data(), epsilonData(), rhoHost_.cdata(), nuHost_.cdata(),
+                                      runTime.deltaT().value(), SH.data()), "MOC::correct");
+        download();
+        PtrList<volScalarField> S(numberOfClasses_);
+        forAll(classNumberDensity_, k) {
+            S.set(k, new volScalarField(IOobject("S", runTime.timeName(), phase_.mesh()), phase_.mesh(),
+                                        dimensionedScalar("S", classNumberDensity_[k].dimensions() / dimTime, 0)));
+            std::memcpy(S[k].internalField().begin(), SH.data() + (size_t)k * nCells, sizeof(double) * nCells);
+        }
+        solveWithFVM(S);
+        deviceStale_ = true;
+        d_ = d();
         return;
     }
-    b200Check(pbe_moc_source_host(moc_, nCells, nCells, nHost_, epsilonData(), rhoHost_.cdata(), nuHost_.cdata(),
-                                  runTime.deltaT().value(), SHost_),
-              "MOC::correct");
-#ifdef PBE_B200_REAL_OPENFOAM
-    // wrap row k of SHost_ as the field classSourceTerm(k) used to return, then
-    // if (usingMULES_) solveWithMULES(S); else solveWithFVM(S);          (MOC.C:177-180, unchanged)
-#error "transport step: use the reference's solveWithMULES / solveWithFVM here"
-#else
-    solveZeroFlux(SHost_);
 #endif
-    forAll(classNumberDensity_, k) {
-        scalar mn = HUGE_VAL;
-        const scalarField &f = classNumberDensity_[k].internalField();
-        forAll(f, c) mn = f[c] < mn ? f[c] : mn;
-        if (k == 0 || k == numberOfClasses_ - 1) Info << "min(n" << k << ") " << mn << endl; // MOC.C:181-183
-    }
-}
-
-// MOC::correct() with solveWithMULES (MOC.C:198-272) and `Gauss upwind`: one call; the class fields
-// travel to the device once, sources and the transport update run there, the new fields come back.
-void MOC::correctWithTransport() {
-    const label nCells = phase_.size();
-    b200Check(pbe_moc_correct_host(moc_, b200Mesh_, divScheme_, nCells, nHost_, epsilonData(), rhoHost_.cdata(),
-                                   nuHost_.cdata(), phase_.phi().cdata(), nullptr /* zeroGradient patches */, 0,
-                                   runTime.deltaT().value(), nullptr),
+    pbe_moc_diag diag;
+    std::memset(&diag, 0, sizeof(diag));
+    diag.class_min = classMin_.data_ptr();
+    b200Check(pbe_moc_correct_resident(state_, epsilonData(), rhoHost_.cdata(), nuHost_.cdata(),
+                                       phase_.internalField().cdata(), b200Mesh_ ? phase_.phi().cdata() : nullptr,
+                                       nullptr /* zeroGradient patches */, 0, runTime.deltaT().value(),
+                                       d_.internalField().data_ptr(), &diag),
               "MOC::correct");
-    forAll(classNumberDensity_, k)
-        std::memcpy(classNumberDensity_[k].internalField().data_ptr(), nHost_ + (size_t)k * nCells,
-                    sizeof(double) * nCells);
-    continuityCheck();
-    forAll(classNumberDensity_, k) {
-        scalar mn = HUGE_VAL;
-        const scalarField &f = classNumberDensity_[k].internalField();
-        forAll(f, c) mn = f[c] < mn ? f[c] : mn;
-        if (k == 0 || k == numberOfClasses_ - 1) Info << "min(n" << k << ") " << mn << endl; // MOC.C:181-183
-    }
+    hostStale_ = true;
+    continuityError_ = diag.cont_err_max;
+    Info << "Max continuity error between advection and PBE: " << continuityError_ << endl; // MOC.C:278-279
+    forAll(classNumberDensity_, k) // MOC.C:181-183 (a parallel run takes the min over the ranks)
+        Info << "min(n" << k << ") " << classMin_[k] << endl;
+    if (runTime.outputTime()) download(); // the solver writes the registered fields after this step
 }
 
-void MOC::continuityCheck() { // MOC.C:254-279: max |sum_k xi_k n_k / V - alpha|
-    const label nCells = phase_.size();
-    scalarField volumeSum(nCells, 0.0);
-    forAll(classNumberDensity_, k) {
-        const scalarField &n = classNumberDensity_[k].internalField();
-        const scalar xi = deltaXi_.value() * (k + 1);
-        forAll(n, c) volumeSum[c] += xi * n[c];
-    }
-    continuityError_ = 0.0;
-    const scalarField &V = phase_.mesh().V();
-    forAll(volumeSum, c) {
-        const scalar e = std::fabs(volumeSum[c] / V[c] - phase_[c]);
-        continuityError_ = e > continuityError_ ? e : continuityError_;
-    }
-}
-
-void MOC::solveZeroFlux(const double *S) {
-    const label nCells = phase_.size();
-    const scalar dt = runTime.deltaT().value();
-    scalarField volumeSum(nCells, 0.0);
-    forAll(classNumberDensity_, k) { // MULES::explicitSolve(1, n_k, phi = 0, Sp = 0, Su = S_k), MOC.C:259-272
-        scalarField &n = classNumberDensity_[k].internalField();
-        const scalar xi = deltaXi_.value() * (k + 1);
-        forAll(n, c) {
-            n[c] = n[c] + dt * S[(size_t)k * nCells + c];
-            volumeSum[c] += xi * n[c];
-        }
-    }
-    continuityError_ = 0.0; // MOC.C:254-279: max |sum_k xi_k n_k / V - alpha|
-    const scalarField &V = phase_.mesh().V();
-    forAll(volumeSum, c) {
-        const scalar e = std::fabs(volumeSum[c] / V[c] - phase_[c]);
-        continuityError_ = e > continuityError_ ? e : continuityError_;
-    }
-}
-
-// MOC::d(), MOC.C:282-290 with volumeToDiameter (:43-45): number-mean diameter
+// MOC::d(), MOC.C:282-290 with volumeToDiameter (:43-45): number-mean diameter of the CURRENT fields
 const volScalarField MOC::d() const {
-    volScalarField result("diameter", phase_.mesh(), 0.0, false);
-    const label nCells = phase_.size();
-    scalarField num(nCells, 0.0), den(nCells, 0.0);
-    forAll(classNumberDensity_, k) {
-        const scalar dk = std::pow(6.0 / pi * deltaXi_.value() * (k + 1), 1.0 / 3.0);
-        const scalarField &n = classNumberDensity_[k].internalField();
-        forAll(n, c) {
-            num[c] += dk * n[c];
-            den[c] += n[c];
-        }
+    if (deviceStale_ || !hostStale_) { // nothing stepped since the fields were last written: recompute from them
+        MOC &self = const_cast<MOC &>(*this);
+        if (deviceStale_) self.upload();
+        b200Check(pbe_moc_state_d(state_, self.d_.internalField().data_ptr()), "MOC::d");
     }
-    forAll(num, c) result[c] = num[c] / den[c];
-    return result;
+    return d_;
 }
 
 // ---- QMOM -----------------------------------------------------------------------------------------
@@ -247,59 +289,153 @@ addToRunTimeSelectionTable(PBEMethod, QMOM, dictionary);
 QMOM::QMOM(const dictionary &pbeProperties, const phaseModel &phase)
     : PBEMethod(pbeProperties, phase), runTime(phase.mesh().time()),
       quadratureOrder_(readLabel(pbeProperties.subDict("QMOMCoeffs").lookup("quadratureOrder"))), // QMOM.C:63
-      moments_(2 * quadratureOrder_), qmom_(nullptr), mHost_(nullptr), SHost_(nullptr),
-      d_("diameter", phase.mesh(), 0.0) {
+      usingMULES_(pbeProperties.subDict("QMOMCoeffs").lookupOrDefault<bool>("usingMULES", false)),
+      moments_(2 * quadratureOrder_), qmom_(nullptr), state_(nullptr), b200Mesh_(nullptr),
+      d_("diameter", phase.mesh(), 0.0), stats_((4 * quadratureOrder_ + 1) * 4, 0.0), hostStale_(false), deviceStale_(true) {
     forAll(moments_, k) moments_.set(k, new volScalarField(fieldName("m", k), phase.mesh())); // QMOM.C:72-79
     b200Check(pbe_qmom_create(ctx_, quadratureOrder_, &spec_, &qmom_), "QMOM::QMOM");
-    const int64_t bytes = (int64_t)sizeof(double) * moments_.size() * phase.size();
-    b200Check(pbe_host_alloc(ctx_, bytes, (void **)&mHost_), "QMOM::QMOM");
-    b200Check(pbe_host_alloc(ctx_, bytes, (void **)&SHost_), "QMOM::QMOM");
+    const fvMesh &mesh = phase.mesh();
+    b200Check(pbe_qmom_state_create(qmom_, mesh.nCells(), mesh.V().cdata(), &state_), "QMOM::QMOM");
+    if (mesh.hasFaces()) {
+        if (!usingMULES_)
+            FatalErrorIn("QMOM::QMOM") << "usingMULES false selects the implicit fvm::ddt + fvm::div solve (QMOM.C:199-209), "
+                                          "which has no device path; set usingMULES true" << exit(FatalError);
+        const int scheme = divSchemeOf(pbeProperties.subDict("QMOMCoeffs"), "QMOM::QMOM div(phi,m.*)");
+        b200Mesh_ = newDeviceMesh(scheme, "QMOM::QMOM mesh");
+        b200Check(pbe_qmom_state_attach_mesh(state_, b200Mesh_, scheme), "QMOM::QMOM");
+    }
 }
 
 QMOM::~QMOM() {
-    if (mHost_) pbe_host_free(ctx_, mHost_);
-    if (SHost_) pbe_host_free(ctx_, SHost_);
+    if (state_) pbe_qmom_state_destroy(state_);
+    if (b200Mesh_) pbe_mesh_destroy(b200Mesh_);
     if (qmom_) pbe_qmom_destroy(qmom_);
 }
 
-// QMOM::correct(), QMOM.C:85-129.  Replaced: the 2N calls of momentSourceTerm(k) (:88-96, i.e.
-// :215-267 with one wheeler_inversion per moment index).  Kept on the OpenFOAM side: the NaN
-// scrub (:98-110), the transport step (:112-115), the SMALL clamp (:117-123) and d_ (:125).
-void QMOM::correct() {
+void QMOM::upload() {
     const label nCells = phase_.size();
+    std::vector<double> stage((size_t)moments_.size() * nCells);
     forAll(moments_, k)
-        std::memcpy(mHost_ + (size_t)k * nCells, moments_[k].internalField().cdata(), sizeof(double) * nCells);
-    updatePhaseFields();
-    b200Check(pbe_qmom_source_host(qmom_, nCells, nCells, mHost_, epsilonData(), rhoHost_.cdata(), nuHost_.cdata(),
-                                   SHost_),
-              "QMOM::correct");
-    const scalar dt = runTime.deltaT().value();
-    forAll(moments_, k) {
-        scalarField &m = moments_[k].internalField();
-        forAll(m, c) {
-            scalar S = SHost_[(size_t)k * nCells + c];
-            if (std::isnan(S)) S = 0.0; // QMOM.C:101-107
-#ifdef PBE_B200_REAL_OPENFOAM
-#error "transport step: use the reference's solveWithMULES / solveWithFVM here (QMOM.C:112-115)"
-#endif
-            m[c] = m[c] + dt * S;       // QMOM.C:193-197 with phi = 0
-            m[c] = m[c] > SMALL ? m[c] : SMALL; // QMOM.C:117-123
-        }
-    }
-    forAll(d_.internalField(), c) // QMOM.C:125
-        d_[c] = std::pow(6.0 / pi * moments_[1][c] / moments_[0][c], 1.0 / 3.0);
+        std::memcpy(stage.data() + (size_t)k * nCells, moments_[k].internalField().cdata(), sizeof(double) * nCells);
+    b200Check(pbe_qmom_state_upload(state_, nCells, stage.data()), "QMOM::upload");
+    b200Check(pbe_qmom_state_d(state_, d_.internalField().data_ptr()), "QMOM::upload"); // d_ = pow(6/pi m1/m0, 1/3), QMOM.C:81
+    deviceStale_ = false;
+    hostStale_ = false;
 }
+
+void QMOM::download() const {
+    const label nCells = phase_.size();
+    std::vector<double> stage((size_t)moments_.size() * nCells);
+    b200Check(pbe_qmom_state_download(state_, nCells, stage.data()), "QMOM::download");
+    forAll(moments_, k)
+        std::memcpy(moments_[k].internalField().data_ptr(), stage.data() + (size_t)k * nCells, sizeof(double) * nCells);
+    hostStale_ = false;
+}
+
+volScalarField &QMOM::moment(label k) {
+    if (hostStale_) download();
+    deviceStale_ = true;
+    return moments_[k];
+}
+
+// QMOM::correct(), QMOM.C:85-129, in one library call: the 2N momentSourceTerm(k) (:88-96, i.e. :215-267 with one
+// inversion per cell instead of one per moment index), the NaN scrub (:98-107), solveWithMULES (:131-197) or the
+// zero-flux update, the SMALL clamp (:117-123), d_ (:125) and the printAvgMaxMin partials (:109, :122, :128).
+void QMOM::correct() {
+    if (deviceStale_) upload();
+    updatePhaseFields();
+    const label nm = moments_.size();
+    pbe_qmom_diag diag;
+    diag.source = stats_.data_ptr();
+    diag.moment = stats_.data_ptr() + 4 * nm;
+    diag.d = stats_.data_ptr() + 8 * nm;
+    b200Check(pbe_qmom_correct_resident(state_, epsilonData(), rhoHost_.cdata(), nuHost_.cdata(),
+                                        b200Mesh_ ? phase_.phi().cdata() : nullptr, nullptr, 0, runTime.deltaT().value(),
+                                        d_.internalField().data_ptr(), &diag),
+              "QMOM::correct");
+    hostStale_ = true;
+    Info << "moment sources:" << endl; // QMOM.C:97-110
+    for (label k = 0; k < nm; ++k) printAvgMaxMin(fieldName("m", k) + "Source", diag.source + 4 * k);
+    for (label k = 0; k < nm; ++k) printAvgMaxMin(fieldName("m", k), diag.moment + 4 * k); // QMOM.C:117-123
+    printAvgMaxMin("diameter", diag.d);                                                      // QMOM.C:128
+    if (runTime.outputTime()) download();
+}
+
+// ---- MOM ------------------------------------------------------------------------------------------
+defineTypeNameAndDebug(MOM, 0);
+addToRunTimeSelectionTable(PBEMethod, MOM, dictionary);
+
+MOM::MOM(const dictionary &pbeProperties, const phaseModel &phase)
+    : PBEMethod(pbeProperties, phase), runTime(phase.mesh().time()), moments_(3), mom_(nullptr), mDev_(nullptr),
+      epsDev_(nullptr), rhoDev_(nullptr), nuDev_(nullptr), dDev_(nullptr), d_("diameter", phase.mesh(), 0.0) {
+    const dictionary &MOMDict_ = pbeProperties.subDict("MOMCoeffs"); // MOM.C:68
+    forAll(moments_, k) moments_.set(k, new volScalarField(fieldName("m", k), phase.mesh())); // MOM.C:128-141
+    if (phase.mesh().hasFaces())
+        FatalErrorIn("MOM::MOM") << "methodOfMoments transports its moments with the implicit fvm::ddt + fvm::div solve "
+                                    "(MOM.C:211-222), which has no device path" << exit(FatalError);
+    // the reference reads nothing from MOMCoeffs; quadraturePanels sizes the fixed rule standing in for QAGIU
+    b200Check(pbe_mom_create(ctx_, MOMDict_.lookupOrDefault<label>("quadraturePanels", 0), &spec_, &mom_), "MOM::MOM");
+    const int64_t row = (int64_t)sizeof(double) * (phase.size() > 0 ? phase.size() : 1);
+    b200Check(pbe_device_alloc(ctx_, 3 * row, (void **)&mDev_), "MOM::MOM");
+    for (double **p : {&epsDev_, &rhoDev_, &nuDev_, &dDev_}) b200Check(pbe_device_alloc(ctx_, row, (void **)p), "MOM::MOM");
+}
+
+MOM::~MOM() {
+    for (double *p : {mDev_, epsDev_, rhoDev_, nuDev_, dDev_})
+        if (p) pbe_device_free(ctx_, p);
+    if (mom_) pbe_mom_destroy(mom_);
+}
+
+// MOM::correct(), MOM.C:148-236: gamma parameters, the nested-integral moment sources, NaN scrub, zero-flux
+// update, SMALL clamp and d on the device (pbe_mom_step); the three moment fields travel both ways every step
+void MOM::correct() {
+    Info << "updating size moments" << endl; // MOM.C:150
+    const label nCells = phase_.size();
+    if (nCells == 0) return;
+    updatePhaseFields();
+    const int64_t row = (int64_t)sizeof(double) * nCells;
+    forAll(moments_, k)
+        b200Check(pbe_memcpy_h2d(ctx_, mDev_ + (size_t)k * nCells, moments_[k].internalField().cdata(), row), "MOM::correct");
+    b200Check(pbe_memcpy_h2d(ctx_, epsDev_, epsilonData(), row), "MOM::correct");
+    b200Check(pbe_memcpy_h2d(ctx_, rhoDev_, rhoHost_.cdata(), row), "MOM::correct");
+    b200Check(pbe_memcpy_h2d(ctx_, nuDev_, nuHost_.cdata(), row), "MOM::correct");
+    b200Check(pbe_mom_step(mom_, nCells, nCells, mDev_, epsDev_, rhoDev_, nuDev_, runTime.deltaT().value(), nullptr, dDev_,
+                           nullptr, nullptr),
+              "MOM::correct");
+    b200Check(pbe_sync(ctx_), "MOM::correct");
+    forAll(moments_, k)
+        b200Check(pbe_memcpy_d2h(ctx_, moments_[k].internalField().data_ptr(), mDev_ + (size_t)k * nCells, row), "MOM::correct");
+    b200Check(pbe_memcpy_d2h(ctx_, d_.internalField().data_ptr(), dDev_, row), "MOM::correct");
+}
+
+// ---- dummy (dummy.C:45-70) ------------------------------------------------------------------------
+defineTypeNameAndDebug(dummy, 0);
+addToRunTimeSelectionTable(PBEMethod, dummy, dictionary);
+
+dummy::dummy(const dictionary &pbeProperties, const phaseModel &phase)
+    : PBEMethod(pbeProperties, phase),
+      d_("d." + phase.name(), phase.mesh(), readScalar(pbeProperties.subDict("dummyCoeffs").lookup("constantDiameter")), false) {}
 
 } // namespace PBEMethods
 
-// ---- PBEDiameter (PBEDiameter.C:46-75, PBEDiameter.H:95-99) -----------------------------------------
-diameterModels::PBEDiameter::PBEDiameter(const dictionary &diameterProperties, const phaseModel &phase)
-    : method_(PBEMethod::New(diameterProperties, phase)), d_("d." + phase.name(), phase.mesh(), 0.0) {}
+// ---- PBEDiameter (PBEDiameter.C:36-81, PBEDiameter.H:95-112) ------------------------------------------
+namespace diameterModels {
+defineTypeNameAndDebug(PBEDiameter, 0);
+addToRunTimeSelectionTable(diameterModel, PBEDiameter, dictionary);
 
-void diameterModels::PBEDiameter::correct() {
+PBEDiameter::PBEDiameter(const dictionary &diameterProperties, const phaseModel &phase)
+    : diameterModel(diameterProperties, phase), method_(PBEMethod::New(diameterProperties, phase)),
+      d_("d." + phase.name(), phase.mesh(), 0.0) {
+    // d_(IOobject(...), method_->d()), PBEDiameter.C:64-75
+    const volScalarField d0(method_->d());
+    forAll(d_.internalField(), c) d_[c] = d0[c];
+}
+
+void PBEDiameter::correct() {
     method_->correct();
     const volScalarField d(method_->d());
     forAll(d_.internalField(), c) d_[c] = d[c];
 }
+} // namespace diameterModels
 
 } // namespace Foam

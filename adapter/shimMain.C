@@ -5,8 +5,11 @@
 // the oracle.  Shim build only (adapter/foam_shim): test infrastructure, not the product.
 //
 //   shimMain <dict file> <input.bin> <output.bin> <steps> [mesh.bin]
+//   dict  : the PBEDiameterCoeffs dictionary; the driver wraps it as the phase's `diameterModel PBEDiameter;
+//           PBEDiameterCoeffs { ... }` and goes through diameterModel::New, as the solver's phaseModel does
 //   mesh  : [nInternal, nBoundary] (FP64), owner[nInternal], neighbour[nInternal], faceCells[nBoundary]
-//           (int32), phi[nInternal + nBoundary] (FP64): face addressing and the phase's face flux
+//           (int32), phi[nInternal + nBoundary] (FP64): face addressing and the phase's face flux; optionally
+//           followed by Sf[faces][3], C[cells][3], weights[nInternal] (FP64) for the limited schemes
 //   input : [K, nCells, dt, cellVolume] then state[K][nCells], epsilon, rho, nu, alpha [nCells] each
 //           (K = numberOfClasses for methodOfClasses, 2 quadratureOrder for QMOM)
 //   output: state[K][nCells], d[nCells], continuity error (MOC; 0 for QMOM)
@@ -50,6 +53,13 @@ int main(int argc, char **argv) {
             mesh.setFaces(std::vector<label>(own.begin(), own.end()), std::vector<label>(nei.begin(), nei.end()),
                           std::vector<label>(bfc.begin(), bfc.end()));
             mok = mok && std::fread(mesh.phi_.data_ptr(), 8, ni + nb, mf) == ni + nb;
+            std::vector<double> Sf(3 * (ni + nb)), Cc(3 * (size_t)nCells), wts(ni);
+            if (mok && std::fread(Sf.data(), 8, Sf.size(), mf) == Sf.size() && std::fread(Cc.data(), 8, Cc.size(), mf) == Cc.size() &&
+                std::fread(wts.data(), 8, ni, mf) == ni) {
+                mesh.Sf_ = Sf;
+                mesh.C_ = Cc;
+                mesh.weights_ = wts;
+            }
             std::fclose(mf);
             if (!mok) return 3;
         }
@@ -61,25 +71,32 @@ int main(int argc, char **argv) {
             phase.nuField()[c] = nu[c];
             epsilon[c] = eps[c];
         }
-        diameterModels::PBEDiameter diameter(dict, phase);
+        // twoPhaseEulerFoam: phaseModel's constructor calls diameterModel::New(phaseDict_, *this)
+        const dictionary phaseDict =
+            dictionary::fromString("diameterModel PBEDiameter; PBEDiameterCoeffs { " + text + " }", "phaseProperties.air");
+        autoPtr<diameterModel> dPtr = diameterModel::New(phaseDict, phase);
+        diameterModels::PBEDiameter &diameter = dynamic_cast<diameterModels::PBEDiameter &>(dPtr());
         PBEMethods::MOC *moc = dynamic_cast<PBEMethods::MOC *>(&diameter.method());
         PBEMethods::QMOM *qmom = dynamic_cast<PBEMethods::QMOM *>(&diameter.method());
-        for (label k = 0; k < K; ++k) {
-            volScalarField &fld = moc ? moc->classNumberDensity(k) : qmom->moment(k);
-            for (label c = 0; c < nCells; ++c) fld[c] = state[(size_t)k * nCells + c];
-        }
+        PBEMethods::MOM *mom = dynamic_cast<PBEMethods::MOM *>(&diameter.method());
+        auto field = [&](label k) -> volScalarField * {
+            return moc ? &moc->classNumberDensity(k) : qmom ? &qmom->moment(k) : mom ? &mom->moment(k) : nullptr;
+        };
+        for (label k = 0; k < K; ++k)
+            if (volScalarField *fld = field(k))
+                for (label c = 0; c < nCells; ++c) (*fld)[c] = state[(size_t)k * nCells + c];
         const int steps = std::atoi(argv[4]);
+        runTime.setWriteInterval(steps > 0 ? steps : 1); // the last step is a write step: fields are synchronised
         for (int s = 0; s < steps; ++s) {
             runTime++;
             diameter.correct();
         }
-        for (label k = 0; k < K; ++k) {
-            const volScalarField &fld = moc ? moc->classNumberDensity(k) : qmom->moment(k);
-            for (label c = 0; c < nCells; ++c) state[(size_t)k * nCells + c] = fld[c];
-        }
+        for (label k = 0; k < K; ++k)
+            if (volScalarField *fld = field(k))
+                for (label c = 0; c < nCells; ++c) state[(size_t)k * nCells + c] = (*fld)[c];
         f = std::fopen(argv[3], "wb");
         std::fwrite(state.data(), 8, state.size(), f);
-        std::fwrite(diameter.d().internalField().cdata(), 8, nCells, f);
+        std::fwrite(diameter.d()().internalField().cdata(), 8, nCells, f);
         const double ce = moc ? moc->continuityError() : 0.0;
         std::fwrite(&ce, 8, 1, f);
         std::fclose(f);

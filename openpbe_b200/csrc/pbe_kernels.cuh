@@ -57,24 +57,29 @@ struct CellCoef {
 
 PBE_HD CellCoef cell_coef(const DevKernelSpec &k, double eps, double rho, double nu) {
     CellCoef c;
-#if defined(__CUDA_ARCH__) && PBE_QMOM_FASTMATH
-    const double e13 = cbrt_pos_fast(eps);
-#else
     const double e13 = pow_third(eps);
-#endif
     // coalescenceKernels/CoulaloglouTavlarides.C:77-88 (wrapper :52-60 feeds the DISPERSED
     // phase rho and nu into the parameters named rhoc, nuc)
     c.A = k.coalA * e13;
     c.negK = -(k.coalK * rho * eps * (rho * nu));
     // breakupKernels/CoulaloglouTavlarides.C:83-92
     c.Ab = k.brA * e13;
-#if defined(__CUDA_ARCH__) && PBE_QMOM_FASTMATH
-    c.negKb = -(k.brK * rcp_fast(rho * (e13 * e13)));
-#else
     c.negKb = -(k.brK / (rho * (e13 * e13)));
-#endif
     return c;
 }
+#if defined(__CUDACC__)
+// the same with call- and division-free device math (QMOM kernel only; the batched functor
+// evaluators behind pbe_eval_* keep the libm forms above and their 1e-13 tolerance)
+__device__ __forceinline__ CellCoef cell_coef_fast(const DevKernelSpec &k, double eps, double rho, double nu) {
+    CellCoef c;
+    const double e13 = cbrt_pos_fast(eps);
+    c.A = k.coalA * e13;
+    c.negK = -(k.coalK * rho * eps * (rho * nu));
+    c.Ab = k.brA * e13;
+    c.negKb = -(k.brK * rcp_fast(rho * (e13 * e13)));
+    return c;
+}
+#endif
 
 // node-dependent roots: a = xi^(1/3), p = xi^(2/9)
 struct NodeRoots {

@@ -41,7 +41,11 @@ __device__ __forceinline__ void qmom_cell_sources(const DevKernelSpec &ks, const
     constexpr bool ct_c = (COAL == PBE_COAL_CT), ct_b = (BR == PBE_BR_CT);
     CellCoef cc;
     cc.A = cc.negK = cc.Ab = cc.negKb = 0.0;
+#if PBE_QMOM_FASTMATH
+    if (ct_c || ct_b) cc = cell_coef_fast(ks, eps, rho, nu);
+#else
     if (ct_c || ct_b) cc = cell_coef(ks, eps, rho, nu);
+#endif
     // exponentials as 2^(K log2(e) .) through the shared-memory table (exp2_neg_tab_safe)
     const double K2 = cc.negK * 1.4426950408889634074, Kb2 = cc.negKb * 1.4426950408889634074;
     double ra[N], rp[N], ia[N], r1[N], gw[N]; // x^(1/3), x^(2/9), x^(-1/3), x^(1/9), w_i g_i

@@ -593,8 +593,8 @@ int pbe_transport_explicit_part(pbe_mesh *m, int scheme, int which, int nfields,
                 PBE_E_INVALID, "pbe_transport_explicit_part: which must be PBE_CELLS_ALL / _REGULAR / _IRREGULAR");
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_transport_explicit: NULL mesh");
     PBE_REQUIRE(scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
-                "pbe_transport_explicit: scheme %d is not available on the device (valid: "
-                "PBE_DIV_UPWIND)", scheme);
+                "pbe_transport_explicit: only Gauss upwind (PBE_DIV_UPWIND) takes the unlimited explicit update; "
+                "limited schemes (Gauss vanLeer, id %d) go through pbe_transport_mules", scheme);
     PBE_REQUIRE(nfields >= 0 && stride >= m->ncells, PBE_E_INVALID,
                 "pbe_transport_explicit: bad nfields/stride (%d, %lld; mesh has %lld cells)", nfields,
                 (long long)stride, (long long)m->ncells);
@@ -708,6 +708,9 @@ static int moc_correct_host_impl(pbe_moc *moc, pbe_mesh *m, int scheme, int64_t 
     PBE_REQUIRE(mctx == ctx, PBE_E_INVALID, "pbe_moc_correct_host: method and mesh belong to different contexts");
     PBE_REQUIRE(m->ncoupled == 0, PBE_E_UNSUPPORTED,
                 "pbe_moc_correct_host: decomposed meshes go through pbe_transport_explicit_halo");
+    PBE_REQUIRE(scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
+                "pbe_moc_correct_host: Gauss upwind only; limited schemes (Gauss vanLeer) need the phase fraction for "
+                "the MULES bound: use pbe_moc_state_attach_mesh + pbe_moc_correct_resident");
     const int64_t nc = m->ncells, nf = m->nint + m->nbnd;
     PBE_REQUIRE(stride >= nc && n_host && eps_host && rho_host && nu_host && (phi_host || nf == 0) && dt > 0.0,
                 PBE_E_INVALID, "pbe_moc_correct_host: bad argument");

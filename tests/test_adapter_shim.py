@@ -27,6 +27,10 @@ uniformBinaryBreakupCoeffs { }
 """
 
 
+NOKERNELS = ("coalescenceKernel noCoalescence; breakupKernel noBreakup; daughterParticleDistribution uniformBinaryBreakup; "
+             "noCoalescenceCoeffs { } noBreakupCoeffs { } uniformBinaryBreakupCoeffs { } ")
+
+
 @pytest.fixture(scope="module")
 def shim():
     if not os.path.exists(os.path.join(ROOT, "openpbe_b200", "lib", "libpbe_b200.so")):
@@ -51,16 +55,20 @@ def run(shim, tmp_path, dict_text, state, eps, rho, nu, alpha, dt, steps=1, vcel
 def test_selection_errors_read_like_openfoam(shim, tmp_path):
     one = np.ones((2, 4))
     v = np.ones(4)
-    p, _ = run(shim, tmp_path, "method bogus; coalescenceKernel noCoalescence; breakupKernel noBreakup;"
-               " daughterParticleDistribution uniformBinaryBreakup;", one, v, v, v, v, 1e-3)
+    p, _ = run(shim, tmp_path, "method bogus; " + NOKERNELS, one, v, v, v, v, 1e-3)
     assert p.returncode == 1
     assert "Unknown pbeModelType type bogus" in p.stdout and "Valid PBEMethod types are" in p.stdout
-    assert "(methodOfClasses quadratureMethodOfMoments)" in p.stdout and "FOAM exiting" in p.stdout
-    p, _ = run(shim, tmp_path, "method methodOfClasses; MOCCoeffs { numberOfClasses 2; xi1 1; } coalescenceKernel Madsen;"
-               " breakupKernel noBreakup; daughterParticleDistribution uniformBinaryBreakup;", one, v, v, v, v, 1e-3)
+    # all four methods of the reference are registered (MOC.C:38-39, QMOM.C:50-51, MOM.C:51-52, dummy.C:37-38)
+    assert "(dummy methodOfClasses methodOfMoments quadratureMethodOfMoments)" in p.stdout and "FOAM exiting" in p.stdout
+    p, _ = run(shim, tmp_path, "method methodOfClasses; MOCCoeffs { numberOfClasses 2; xi1 1; } "
+               + NOKERNELS.replace("coalescenceKernel noCoalescence", "coalescenceKernel Madsen"), one, v, v, v, v, 1e-3)
     assert p.returncode == 1 and "Madsen" in p.stdout and "CoulaloglouTavlaridesC" in p.stdout
     p, _ = run(shim, tmp_path, "coalescenceKernel noCoalescence;", one, v, v, v, v, 1e-3)
     assert p.returncode == 1 and "keyword method is undefined in dictionary" in p.stdout
+    # <Type>Coeffs is looked up with subDict: fatal when absent, as coalescenceKernel.C:66-70
+    p, _ = run(shim, tmp_path, "method methodOfClasses; MOCCoeffs { numberOfClasses 2; xi1 1; } coalescenceKernel "
+               "noCoalescence; breakupKernel noBreakup; daughterParticleDistribution uniformBinaryBreakup;", one, v, v, v, v, 1e-3)
+    assert p.returncode == 1 and "keyword noCoalescenceCoeffs is undefined" in p.stdout
 
 
 def test_no_device_is_fatal_not_a_fallback(shim, tmp_path):
@@ -69,8 +77,7 @@ def test_no_device_is_fatal_not_a_fallback(shim, tmp_path):
         pytest.skip("a GPU is present")
     one = np.ones((2, 4))
     v = np.ones(4)
-    p, _ = run(shim, tmp_path, "method methodOfClasses; MOCCoeffs { numberOfClasses 2; xi1 1; } coalescenceKernel "
-               "noCoalescence; breakupKernel noBreakup; daughterParticleDistribution uniformBinaryBreakup;",
+    p, _ = run(shim, tmp_path, "method methodOfClasses; MOCCoeffs { numberOfClasses 2; xi1 1; } " + NOKERNELS,
                one, v, v, v, v, 1e-3)
     assert p.returncode == 1 and "FOAM FATAL ERROR" in p.stdout and "no CPU path" in p.stdout
 
@@ -116,12 +123,15 @@ def test_qmom_correct_matches_oracle(shim, tmp_path, oracle):
     assert np.all(m >= 1e-15)
 
 
-def _write_mesh(path, m):
+def _write_mesh(path, m, geometry=False):
     with open(path, "wb") as fh:
         np.array([m["owner"].size, m["boundary_owner"].size], dtype=np.float64).tofile(fh)
         for k in ("owner", "neighbour", "boundary_owner"):
             m[k].astype(np.int32).tofile(fh)
         m["phi"].astype(np.float64).tofile(fh)
+        if geometry:  # fvMesh::Sf(), C(), weights() for the limited schemes
+            for k in ("Sf", "C", "weights"):
+                np.ascontiguousarray(m[k], dtype=np.float64).tofile(fh)
 
 
 @pytest.mark.gpu
@@ -153,7 +163,74 @@ def test_moc_correct_with_transport_matches_oracle(shim, tmp_path, oracle):
     assert np.all(np.abs(n - n_o) <= 4 * w.dt * 1e-12 * scale + 1e-14 * np.abs(n_o))
     np.testing.assert_allclose(d, oracle.moc_d(n_o, w.xi1), rtol=1e-12)
     # a scheme without a device path is a FatalError that lists the valid ones
-    (tmp_path / "dict").write_text(text.replace("Gauss upwind", "Gauss vanLeer"))
+    (tmp_path / "dict").write_text(text.replace("Gauss upwind", "Gauss QUICK"))
     p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
                         str(tmp_path / "mesh.bin")], capture_output=True, text=True)
-    assert p.returncode == 1 and "vanLeer" in p.stdout and "Valid schemes are" in p.stdout and "FOAM exiting" in p.stdout
+    assert p.returncode == 1 and "QUICK" in p.stdout and "Valid schemes are" in p.stdout and "FOAM exiting" in p.stdout
+
+
+@pytest.mark.gpu
+def test_moc_correct_with_vanleer_mules_matches_port(shim, tmp_path, oracle):
+    """The scheme the reference's validation case selects (c01/system/fvSchemes:34) through the adapter:
+    MOC::correct() with solveWithMULES = sources, MULES::limit against max(alpha V / xi_k), limitSum,
+    explicitSolve -- against oracle sources + the port of the call sequence (oracle/pbe_oracle_mules.c)."""
+    tm = synthetic.block_mesh(12, 10, 8, velocity=(1.0, -0.5, 0.25))
+    nc = 12 * 10 * 8
+    w = synthetic.workload("moc30_ct", nc)
+    f = synthetic.moc_fields(w)
+    f["n"] *= 1.0 + 5.0 * np.sin(np.arange(nc) * 0.7)[None, :] ** 2
+    vcell = float(tm["vcell"][0])
+    dt = 0.01
+    text = ("method methodOfClasses; MOCCoeffs { numberOfClasses %d; xi1 %r; usingMULES on; divScheme Gauss vanLeer; }"
+            % (w.N, w.xi1) + C01 % (tuple(w.coal_coeffs) + tuple(w.br_coeffs)))
+    (tmp_path / "dict").write_text(text)
+    np.concatenate([[w.N, nc, dt, vcell], f["n"].ravel(), f["eps"], f["rho"], f["nu"], f["alpha"]]).tofile(tmp_path / "in.bin")
+    _write_mesh(tmp_path / "mesh.bin", tm, geometry=True)
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout + p.stderr
+    r = np.fromfile(tmp_path / "out.bin")
+    n = r[:w.N * nc].reshape(w.N, nc)
+    sp = oracle.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+    S, scale = oracle.moc_source(sp, w.N, w.xi1, w.relax, f["n"], f["eps"], f["rho"], f["nu"], dt)
+    xi = w.xi1 * np.arange(1, w.N + 1)
+    pmax = np.array([np.max(f["alpha"] * tm["vcell"] / x) for x in xi])
+    n_o = oracle.transport_mules(tm, "Gauss vanLeer", f["n"], tm["phi"], dt, pmax, S=S)
+    assert np.all(np.abs(n - n_o) <= 4 * dt * 1e-12 * scale.max(axis=1, keepdims=True) + 1e-13 * np.abs(n_o))
+    assert "Max continuity error between advection and PBE" in p.stdout and "min(n0)" in p.stdout
+    # without the geometry the limited scheme cannot be built: FatalError, not a silent upwind
+    _write_mesh(tmp_path / "mesh.bin", tm, geometry=False)
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 1 and "needs fvMesh::Sf()" in p.stdout
+
+
+@pytest.mark.gpu
+def test_all_four_methods_select_by_dictionary(shim, tmp_path):
+    """method methodOfClasses | quadratureMethodOfMoments | methodOfMoments | dummy through
+    diameterModel::New -> PBEDiameter -> PBEMethod::New (PBEDiameter.C:36-81, PBEMethod.C:81-108)."""
+    nc = 64
+    v = np.ones(nc)
+    kern = ("coalescenceKernel constantCoalescence; constantCoalescenceCoeffs { constant 0.1; } breakupKernel binaryBreakup; "
+            "binaryBreakupCoeffs { } daughterParticleDistribution uniformBinaryBreakup; uniformBinaryBreakupCoeffs { } ")
+    # dummy: constant diameter, no fields
+    p, out = run(shim, tmp_path, "method dummy; dummyCoeffs { constantDiameter 0.00123; } " + kern, np.ones((1, nc)), v, v, v, v, 1e-3)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert np.all(out[1] == 0.00123) and "Selecting population balance model: dummy" in p.stdout
+    # methodOfMoments: three moments of a gamma density, closed forms for constant coalescence + binary breakup
+    from oracle import mom_oracle as mo
+    k, th, m0 = 2.5, 0.3, 2.0
+    m = np.stack([np.full(nc, m0), np.full(nc, m0 * k * th), np.full(nc, m0 * k * (k + 1) * th ** 2)])
+    dt = 1e-3
+    p, out = run(shim, tmp_path, "method methodOfMoments; MOMCoeffs { } " + kern, m, v, v, v, v, dt)
+    assert p.returncode == 0, p.stdout + p.stderr
+    S = np.sum(mo.closed_form_constant_binary(m[:, 0], 0.1), axis=0)
+    assert np.allclose(out[0][:, 0], m[:, 0] + dt * S, rtol=1e-9)
+    assert np.allclose(out[1], np.cbrt(6 / np.pi * out[0][1] / out[0][0]), rtol=1e-12)
+    # the two hot-path methods select as well (their arithmetic is covered above)
+    p, out = run(shim, tmp_path, "method methodOfClasses; MOCCoeffs { numberOfClasses 4; xi1 0.25; } " + kern,
+                 np.ones((4, nc)), v, v, v, 0.05 * v, dt)
+    assert p.returncode == 0 and "Selecting diameterModel for phase air: PBEDiameter" in p.stdout
+    p, out = run(shim, tmp_path, "method quadratureMethodOfMoments; QMOMCoeffs { quadratureOrder 2; } " + kern,
+                 np.array([[1.0], [1.0], [1.5], [3.0]]) * np.ones((4, nc)), v, v, v, v, dt)
+    assert p.returncode == 0 and "moment sources:" in p.stdout and "diameter: avg, max,min" in p.stdout

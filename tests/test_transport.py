@@ -85,10 +85,12 @@ def test_oracle_upwind_is_bounded():
 def test_div_scheme_names():
     out = capi.C.c_int(-1)
     assert capi.lib().pbe_div_scheme_type(b"Gauss upwind", capi.C.byref(out)) == capi.PBE_OK and out.value == capi.DIV_UPWIND
-    rc = capi.lib().pbe_div_scheme_type(b"Gauss vanLeer", capi.C.byref(out))
+    # the scheme of the reference's validation case (simmons_and_azzopardi/c01/system/fvSchemes:34)
+    assert capi.lib().pbe_div_scheme_type(b"Gauss vanLeer", capi.C.byref(out)) == capi.PBE_OK and out.value == capi.DIV_VANLEER
+    rc = capi.lib().pbe_div_scheme_type(b"Gauss QUICK", capi.C.byref(out))
     assert rc == capi.PBE_E_UNKNOWN_TYPE
     msg = capi.last_error()
-    assert "vanLeer" in msg and "Valid schemes are" in msg and "upwind" in msg
+    assert "QUICK" in msg and "Valid schemes are" in msg and "upwind" in msg and "vanLeer" in msg
 
 
 # ------------------------------------------------------------------------------------------------
@@ -165,7 +167,7 @@ def test_device_argument_errors(ctx):
     phi = torch.zeros(m["phi"].size, dtype=torch.float64, device="cuda:0")
     with pytest.raises(capi.PbeError, match="alias"):
         mesh.transport_explicit(psi, phi, 0.1, out=psi)
-    with pytest.raises(capi.PbeError, match="vanLeer"):
+    with pytest.raises(capi.PbeError, match="pbe_transport_mules"):  # limited schemes take the MULES path
         mesh.transport_explicit(psi, phi, 0.1, scheme="Gauss vanLeer")
     with pytest.raises(capi.PbeError, match="owner"):
         engine.Mesh(ctx, [0, 70], [1, 2], [], np.ones(64))
