@@ -234,3 +234,10 @@ def test_all_four_methods_select_by_dictionary(shim, tmp_path):
     p, out = run(shim, tmp_path, "method quadratureMethodOfMoments; QMOMCoeffs { quadratureOrder 2; } " + kern,
                  np.array([[1.0], [1.0], [1.5], [3.0]]) * np.ones((4, nc)), v, v, v, v, dt)
     assert p.returncode == 0 and "moment sources:" in p.stdout and "diameter: avg, max,min" in p.stdout
+
+
+def test_real_openfoam_branch_has_no_error_directive():
+    """-DPBE_B200_REAL_OPENFOAM selects real OpenFOAM headers (absent here, so it cannot be compiled) but
+    no longer stops at an #error: both transport branches are written out."""
+    for fn in ("PBEMethodB200.H", "PBEMethodB200.C"):
+        assert "#error" not in open(os.path.join(ROOT, "adapter", fn)).read()
