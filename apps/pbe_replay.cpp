@@ -5,6 +5,10 @@
 // (PBEDiameter.H:95-99): method_->correct(); d_ = method_->d().
 //
 //   pbe_replay [--cells 4000000] [--steps 10] [--classes 50] [--order 3] [--device 0]
+//              [--ranks N]          one process per GPU (forked here, devices device..device+N-1): the cells are
+//                                   block-partitioned over the ranks (BASELINE configs[3]), an NCCL communicator
+//                                   is built through the C ABI (pbe_comm_unique_id / pbe_comm_init) and every
+//                                   printed diagnostic is the global one (pbe_reduce_diagnostics*)
 //              [--dict file]        (a PBEDiameterCoeffs-style dictionary; default: the c01 case)
 //              [--mesh nx ny nz [--velocity u v w]]   hex block in OpenFOAM face addressing: both methods then
 //                                   run solveWithMULES (source + explicit upwind transport, MOC.C:198-272,
@@ -12,12 +16,16 @@
 //
 // Prints one JSON line per method per step (wall ms with the diameter read-back, volume-averaged
 // / max / min diameter as printAvgMaxMin would, Utility.C:4-10) and a summary line per method.
+#include <sys/wait.h>
+#include <unistd.h>
+
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
 #include <iterator>
+#include <thread>
 
 #include "pbe_method.hpp"
 
@@ -62,38 +70,52 @@ double lognormalVolumePdf(double v, double dmean = 5.0e-4, double dstd = 5.0e-5)
 struct Stats {
     double avg, mx, mn;
 };
-Stats avgMaxMin(const std::vector<double> &f, const std::vector<double> &V) {
-    double sfv = 0, sv = 0, mx = -INFINITY, mn = INFINITY;
+// printAvgMaxMin (Utility.C:4-10): with ranks the three numbers are reduced over them through the C ABI
+Stats avgMaxMin(pbe_ctx *ctx, const std::vector<double> &f, const std::vector<double> &V) {
+    double sums[2] = {0, 0}, mx = -INFINITY, mn = INFINITY;
     for (size_t c = 0; c < f.size(); ++c) {
-        sfv += f[c] * V[c];
-        sv += V[c];
+        sums[0] += f[c] * V[c];
+        sums[1] += V[c];
         mx = std::max(mx, f[c]);
         mn = std::min(mn, f[c]);
     }
-    return {sfv / sv, mx, mn};
+    pbe::check(pbe_reduce_diagnostics_host(ctx, 2, sums, 1, &mn, 1, &mx), "printAvgMaxMin");
+    return {sums[0] / sums[1], mx, mn};
 }
 
-void replay(const char *label, pbe::PBEMethod &m, const std::vector<double> &V, int steps, int64_t cells,
-            double unitsPerCell, const char *unit, double dScale = 1.0) {
+// rank, ranks and the barrier-ish max over the ranks of a scalar (the slowest rank's time is the step's)
+struct Ranks {
+    int n = 1, rank = 0;
+    pbe_ctx *ctx = nullptr;
+    double maxOver(double x) const {
+        pbe::check(pbe_reduce_diagnostics_host(ctx, 0, nullptr, 0, nullptr, 1, &x), "max over ranks");
+        return x;
+    }
+};
+
+void replay(const char *label, pbe::PBEMethod &m, const Ranks &R, const std::vector<double> &V, int steps,
+            int64_t globalCells, double unitsPerCell, const char *unit, double dScale = 1.0) {
     double total = 0;
     for (int s = 0; s < steps; ++s) {
+        (void)R.maxOver(0.0); // the ranks start the step together
         auto t0 = std::chrono::steady_clock::now();
         m.correct();                              // PBEDiameter::correct(): method_->correct();
         const std::vector<double> &d = m.d();     //                         d_ = method_->d();
         auto t1 = std::chrono::steady_clock::now();
-        const double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        const double ms = R.maxOver(std::chrono::duration<double, std::milli>(t1 - t0).count());
         if (s > 0) total += ms; // step 0 carries one-time warm-up
-        Stats st = avgMaxMin(d, V);
+        Stats st = avgMaxMin(R.ctx, d, V);
         st.avg *= dScale, st.mx *= dScale, st.mn *= dScale;
-        std::printf("{\"method\": \"%s\", \"step\": %d, \"ms\": %.3f, \"d_avg\": %.9e, \"d_max\": %.9e, "
-                    "\"d_min\": %.9e}\n",
-                    label, s, ms, st.avg, st.mx, st.mn);
+        if (R.rank == 0)
+            std::printf("{\"method\": \"%s\", \"step\": %d, \"ms\": %.3f, \"d_avg\": %.9e, \"d_max\": %.9e, "
+                        "\"d_min\": %.9e}\n",
+                        label, s, ms, st.avg, st.mx, st.mn);
     }
-    if (steps > 1) {
+    if (steps > 1 && R.rank == 0) {
         const double ms = total / (steps - 1);
-        std::printf("{\"method\": \"%s\", \"summary\": true, \"cells\": %lld, \"ms_per_step\": %.3f, "
+        std::printf("{\"method\": \"%s\", \"summary\": true, \"ranks\": %d, \"cells\": %lld, \"ms_per_step\": %.3f, "
                     "\"%s\": %.4e}\n",
-                    label, (long long)cells, ms, unit, cells * unitsPerCell / (ms * 1e-3));
+                    label, R.n, (long long)globalCells, ms, unit, globalCells * unitsPerCell / (ms * 1e-3));
     }
 }
 
@@ -101,7 +123,7 @@ void replay(const char *label, pbe::PBEMethod &m, const std::vector<double> &V, 
 
 int main(int argc, char **argv) {
     int64_t cells = 4000000;
-    int steps = 10, classes = 50, order = 3, device = 0;
+    int steps = 10, classes = 50, order = 3, device = 0, ranks = 1;
     std::string dictFile;
     int meshN[3] = {0, 0, 0};
     double vel[3] = {1.0, 0.5, 0.25};
@@ -119,6 +141,7 @@ int main(int argc, char **argv) {
         else if (a == "--classes") classes = std::atoi(val());
         else if (a == "--order") order = std::atoi(val());
         else if (a == "--device") device = std::atoi(val());
+        else if (a == "--ranks") ranks = std::atoi(val());
         else if (a == "--dict") dictFile = val();
         else if (a == "--mesh") { // nx ny nz hex block: MOC runs solveWithMULES (transport + source)
             for (int k = 0; k < 3; ++k) meshN[k] = std::atoi(val());
@@ -130,7 +153,66 @@ int main(int argc, char **argv) {
             return 2;
         }
     }
+    // ---- one process per GPU: fork BEFORE anything touches CUDA; the children are the ranks ---------
+    Ranks R;
+    std::string idFile;
+    if (ranks > 1) {
+        if (meshN[0] > 0) {
+            std::fprintf(stderr, "--ranks with --mesh: the decomposed transport (processor patches + pbe_halo_exchange) is "
+                                 "driven from openpbe_b200/sharding.py; the replay driver shards the source path only\n");
+            return 2;
+        }
+        idFile = "/tmp/pbe_replay_nccl_id." + std::to_string((long)getpid());
+        std::vector<pid_t> kids;
+        int myRank = -1;
+        for (int r = 0; r < ranks; ++r) {
+            const pid_t pid = fork();
+            if (pid == 0) {
+                myRank = r;
+                break;
+            }
+            kids.push_back(pid);
+        }
+        if (myRank < 0) { // the launcher: wait for the ranks
+            int worst = 0;
+            for (pid_t k : kids) {
+                int st = 0;
+                waitpid(k, &st, 0);
+                if (!WIFEXITED(st) || WEXITSTATUS(st) != 0) worst = 1;
+            }
+            std::remove(idFile.c_str());
+            return worst;
+        }
+        R.n = ranks;
+        R.rank = myRank;
+        device += myRank;
+    }
+    const int64_t globalCells = cells;
+    if (R.n > 1) { // contiguous, balanced block of the cell range (cells are independent: no data-path collective)
+        const int64_t base = cells / R.n, rem = cells % R.n;
+        cells = base + (R.rank < rem ? 1 : 0);
+    }
     try {
+        pbe::Context ctx(device);
+        R.ctx = ctx.get();
+        if (R.n > 1) {
+            char id[PBE_COMM_UNIQUE_ID_BYTES];
+            if (R.rank == 0) {
+                pbe::check(pbe_comm_unique_id(id), "pbe_comm_unique_id");
+                const std::string tmp = idFile + ".tmp";
+                std::FILE *f = std::fopen(tmp.c_str(), "wb");
+                if (!f || std::fwrite(id, 1, sizeof(id), f) != sizeof(id)) throw pbe::FatalError("cannot write " + tmp);
+                std::fclose(f);
+                std::rename(tmp.c_str(), idFile.c_str());
+            } else {
+                std::FILE *f = nullptr;
+                for (int tries = 0; tries < 6000 && !(f = std::fopen(idFile.c_str(), "rb")); ++tries)
+                    std::this_thread::sleep_for(std::chrono::milliseconds(10));
+                if (!f || std::fread(id, 1, sizeof(id), f) != sizeof(id)) throw pbe::FatalError("no NCCL id from rank 0");
+                std::fclose(f);
+            }
+            pbe::check(pbe_comm_init(ctx.get(), R.n, R.rank, id), "pbe_comm_init");
+        }
         std::string text = kDefaultDict;
         if (!dictFile.empty()) {
             std::ifstream in(dictFile);
@@ -138,7 +220,7 @@ int main(int argc, char **argv) {
             text.assign(std::istreambuf_iterator<char>(in), std::istreambuf_iterator<char>());
         }
         // ---- synthetic phase fields, seed 20240611 -------------------------------
-        Rng rng(20240611);
+        Rng rng(20240611 + 7919ull * (uint64_t)R.rank);
         std::vector<double> eps(cells), alpha(cells), rho(cells, 1166.0), nu(cells, 1.599752e-3 / 1166.0),
             V(cells, 1e-9);
         for (int64_t c = 0; c < cells; ++c) {
@@ -155,6 +237,7 @@ int main(int argc, char **argv) {
         phase.V = V.data();
         phase.deltaT = 2.5e-4;
         phase.device = device;
+        phase.ctx = ctx.get(); // both methods share the rank's context (and its communicator)
         // ---- optional hex block in OpenFOAM face addressing (blockMesh order: internal faces by
         // owner then neighbour; patches x-, x+, y-, y+, z-, z+), unit cube, uniform velocity ----
         pbe::FaceMesh fm;
@@ -234,9 +317,10 @@ int main(int argc, char **argv) {
             }
             pbe::PBEMethods::MOC moc(dict, phase, n0.data());
             std::vector<double>().swap(n0);
-            replay("methodOfClasses", moc, V, steps, cells, classes, "cell_class_updates_per_s");
-            std::printf("{\"method\": \"methodOfClasses\", \"min_n0\": %.6e, \"continuity_error\": %.6e}\n",
-                        moc.classMin(0), moc.continuityError());
+            replay("methodOfClasses", moc, R, V, steps, globalCells, classes, "cell_class_updates_per_s");
+            if (R.rank == 0) // global values: the library reduced them over the ranks inside correct()
+                std::printf("{\"method\": \"methodOfClasses\", \"min_n0\": %.6e, \"continuity_error\": %.6e}\n",
+                            moc.classMin(0), moc.continuityError());
         }
         {   // ---- quadratureMethodOfMoments: the 2*order moments of the same initial condition ------
             pbe::Dictionary dict = pbe::Dictionary::parse(text, "PBEDiameterCoeffs");
@@ -253,10 +337,11 @@ int main(int argc, char **argv) {
             if (phase.mesh) dict.subDictOrAdd("QMOMCoeffs").set("usingMULES", std::string("true"));
             pbe::PBEMethods::QMOM q(dict, phase, m0.data());
             std::vector<double>().swap(m0);
-            replay("quadratureMethodOfMoments", q, V, steps, cells, 1.0, "cell_updates_per_s", std::cbrt(volUnit));
+            replay("quadratureMethodOfMoments", q, R, V, steps, globalCells, 1.0, "cell_updates_per_s", std::cbrt(volUnit));
             const auto a = q.avgMaxMin(0);
-            std::printf("{\"method\": \"quadratureMethodOfMoments\", \"m0_avg\": %.6e, \"m0_max\": %.6e, "
-                        "\"m0_min\": %.6e}\n", a.avg, a.max, a.min);
+            if (R.rank == 0)
+                std::printf("{\"method\": \"quadratureMethodOfMoments\", \"m0_avg\": %.6e, \"m0_max\": %.6e, "
+                            "\"m0_min\": %.6e}\n", a.avg, a.max, a.min);
         }
     } catch (const pbe::FatalError &e) {
         std::cerr << e.what() << "\n\nFOAM exiting\n";

@@ -421,9 +421,42 @@ int pbe_eval_integrate_exp(pbe_ctx *ctx, int64_t count, const double *rate, cons
 
 /* ---- global diagnostics, Utility.C:4-10 printAvgMaxMin: out[0] = sum(f V), out[1] = sum V,
  * out[2] = max f, out[3] = min f over this rank's cells (DEVICE out[4]); the caller
- * all-reduces (sum, sum, max, min) across ranks -- NCCL in bench.py / the replay driver. */
+ * all-reduces (sum, sum, max, min) across ranks: pbe_reduce_diagnostics. */
 int pbe_field_avg_max_min(pbe_ctx *ctx, int64_t ncells, const double *f, const double *vcell,
                           double *out4, void *cuda_stream);
+
+/* ======================================================================================= */
+/* Multi-GPU: one process per GPU, cells block-partitioned (they are independent on the      */
+/* source path: no data-path collective).  The library owns an NCCL communicator over the   */
+/* ranks and carries what the reference gets from OpenFOAM's implicit MPI all-reduces        */
+/* (SURVEY.md 2.3): min(n_k) MOC.C:181-183, max(alpha V / xi_k) MOC.C:238, max continuity      */
+/* error MOC.C:276-279, max(m_k) QMOM.C:171, printAvgMaxMin Utility.C:4-10 -- and the halo     */
+/* exchange of the transport step.  NCCL is bound at run time (dlopen libnccl.so.2, or        */
+/* $PBE_NCCL_LIB): a single-GPU host needs none.  With a communicator on the context,          */
+/* pbe_moc_correct_resident / pbe_qmom_correct_resident return GLOBAL diagnostics.             */
+/* ======================================================================================= */
+#define PBE_COMM_UNIQUE_ID_BYTES 128
+/* rank 0 creates the id (ncclGetUniqueId); the host hands it to the other ranks (MPI_Bcast, a file) */
+int pbe_comm_unique_id(void *id128);
+/* ncclCommInitRank on the context's device; collective over the nranks processes */
+int pbe_comm_init(pbe_ctx *ctx, int nranks, int rank, const void *id128);
+/* adopt a communicator the host already has (an ncclComm_t; not destroyed with the context) */
+int pbe_comm_init_from(pbe_ctx *ctx, void *nccl_comm);
+int pbe_comm_destroy(pbe_ctx *ctx);
+int pbe_comm_info(pbe_ctx *ctx, int *nranks, int *rank); /* 1, 0 without a communicator */
+/* in-place all-reduces of DEVICE vectors (sum / min / max) as one NCCL group on the stream */
+int pbe_reduce_diagnostics(pbe_ctx *ctx, int nsum, double *sums, int nmin, double *mins, int nmax,
+                           double *maxs, void *cuda_stream);
+/* the same for HOST vectors, synchronous (staged on the communicator's side stream) */
+int pbe_reduce_diagnostics_host(pbe_ctx *ctx, int nsum, double *sums, int nmin, double *mins,
+                                int nmax, double *maxs);
+/* Halo exchange of a decomposed transport step: send [nfields][stride_s] = this rank's cell values
+ * along its processor-patch faces (pbe_gather_cells), recv [nfields][stride_r] = the values across
+ * them (psi_halo of pbe_transport_explicit_halo); neighbour q = rank peer[q] shares coupled faces
+ * [off[q], off[q] + cnt[q]) (same order on both sides).  One NCCL group of sends / receives. */
+int pbe_halo_exchange(pbe_ctx *ctx, int nneigh, const int *peer, const int64_t *off,
+                      const int64_t *cnt, int nfields, const double *send, int64_t stride_s,
+                      double *recv, int64_t stride_r, void *cuda_stream);
 
 /* ---- memory helpers so a C/C++ host needs no CUDA headers ------------------------------ */
 int pbe_device_alloc(pbe_ctx *ctx, int64_t bytes, void **out);

@@ -22,9 +22,12 @@
 // What it is not: OpenFOAM.  `Phase` stands in for phaseModel + fvMesh: the caller hands in the
 // per-cell fields the kernels read (alpha, rho, nu, epsilon.<phase>, mesh.V()) and deltaT.  The
 // mesh-coupled transport of MOC::solveWithMULES / QMOM::momentTransport is outside this path:
-// correct() applies the zero-flux form  n += dt S  (MOC.C:259-272 with phi = 0), the form the
-// reference's own 1-cell integration cases reduce to.  State stays RESIDENT on the device between
-// time steps; d() and the field accessors copy back on demand.
+// without a FaceMesh correct() applies the zero-flux form  n += dt S  (MOC.C:259-272 with phi = 0), the
+// form the reference's own 1-cell integration cases reduce to; with one it runs solveWithMULES on the
+// device (Gauss upwind, or Gauss vanLeer with the MULES limiter).  The methods OWN their class / moment
+// fields on the device (pbe_moc_state / pbe_qmom_state, as MOC.H:66); correct() sends this step's
+// phase fields and brings d back (pbe_*_correct_resident); the field accessors copy back on demand.
+// With Phase::ctx carrying a communicator (pbe_comm_init) the diagnostics are global.
 #pragma once
 
 #include <cmath>
@@ -197,6 +200,7 @@ struct Phase {
     double deltaT = 0.0;             // runTime.deltaT()
     int device = 0;                  // CUDA device the state lives on
     const struct FaceMesh *mesh = nullptr; // fvMesh addressing + phase_.phi(): enables transport
+    pbe_ctx *ctx = nullptr;          // optional: a context the caller owns (e.g. with a communicator); else one per method
 };
 
 // ---- stand-in for fvMesh's face addressing, phase_.phi() and fvSchemes' div(phi,n.*) entry ------------
@@ -208,15 +212,21 @@ struct FaceMesh {
     const int32_t *boundaryOwner = nullptr;               // faceCells of every patch, patch order
     const double *phi = nullptr;                          // [nInternalFaces + nBoundaryFaces]
     const double *boundaryValues = nullptr; // [fields][nBoundaryFaces] patch values, null = zeroGradient
-    std::string divScheme = "Gauss upwind"; // fvSchemes: "div\\(phi,n.*\\)"
+    std::string divScheme = "Gauss upwind"; // fvSchemes: "div\\(phi,n.*\\)"; "Gauss vanLeer" needs the geometry:
+    const double *Sf = nullptr;             // fvMesh::Sf() [nInternalFaces + nBoundaryFaces][3]
+    const double *C = nullptr;              // fvMesh::C()  [ncells][3]
+    const double *weights = nullptr;        // fvMesh::weights() [nInternalFaces]
 };
 
 // ---- RAII over the C-ABI context and device buffers -------------------------------------------------
 class Context {
 public:
-    explicit Context(int device) { check(pbe_ctx_create(device, &h_), "pbe::Context"); }
+    explicit Context(int device) : owned_(true) { check(pbe_ctx_create(device, &h_), "pbe::Context"); }
+    Context(int device, pbe_ctx *borrowed) : h_(borrowed), owned_(borrowed == nullptr) {
+        if (!borrowed) check(pbe_ctx_create(device, &h_), "pbe::Context");
+    }
     ~Context() {
-        if (h_) pbe_ctx_destroy(h_);
+        if (h_ && owned_) pbe_ctx_destroy(h_);
     }
     Context(const Context &) = delete;
     Context &operator=(const Context &) = delete;
@@ -224,6 +234,7 @@ public:
 
 private:
     pbe_ctx *h_ = nullptr;
+    bool owned_ = true;
 };
 
 class DeviceArray {
@@ -314,7 +325,7 @@ public:
 
 protected:
     PBEMethod(const Dictionary &pbeProperties, const Phase &phase)
-        : phase_(phase), ctx_(phase.device), spec_(kernelSpecFromDict(pbeProperties)) {
+        : phase_(phase), ctx_(phase.device, phase.ctx), spec_(kernelSpecFromDict(pbeProperties)) {
         if (phase.ncells < 0 || phase.deltaT <= 0.0) throw FatalError("PBEMethod: bad phase (ncells, deltaT)");
     }
     // upload the per-cell kernel inputs once; update() refreshes them (coalescence_().update(), MOC.C:173)
@@ -345,6 +356,31 @@ protected:
 
 namespace PBEMethods {
 
+// page-lock a caller-owned host array so that correct() copies it asynchronously at full PCIe rate; a
+// failure (already registered, not page-aligned enough for the driver) only costs speed
+inline void tryPin(pbe_ctx *ctx, const void *p, int64_t bytes) {
+    if (p && bytes > 0) (void)pbe_host_register(ctx, const_cast<void *>(p), bytes);
+}
+inline void tryUnpin(pbe_ctx *ctx, const void *p) {
+    if (p) (void)pbe_host_unregister(ctx, const_cast<void *>(p));
+}
+// device mesh of a FaceMesh (+ geometry for the limited schemes)
+inline pbe_mesh *makeDeviceMesh(pbe_ctx *ctx, const Phase &phase, int scheme, const char *where) {
+    const FaceMesh &fm = *phase.mesh;
+    pbe_mesh *m = nullptr;
+    check(pbe_mesh_create(ctx, phase.ncells, fm.nInternalFaces, fm.owner, fm.neighbour, fm.nBoundaryFaces, fm.boundaryOwner,
+                          phase.V, &m),
+          where);
+    if (scheme != PBE_DIV_UPWIND) {
+        if (!fm.Sf || !fm.C || !fm.weights) {
+            pbe_mesh_destroy(m);
+            throw FatalError(std::string(where) + ": the limited divergence scheme needs FaceMesh::Sf, C and weights");
+        }
+        check(pbe_mesh_set_geometry(m, fm.Sf, fm.C, fm.weights), where);
+    }
+    return m;
+}
+
 // ---- methodOfClasses (MOC.H:57-127, MOC.C:49-83, 159-184, 282-290) --------------------------------------
 class MOC : public PBEMethod {
 public:
@@ -360,131 +396,80 @@ public:
         usingMULES_ = c.lookupOrDefault<bool>("usingMULES", false);
         relax_ = c.lookupOrDefault<double>("sourceRelaxation", 1.0);
         check(pbe_moc_create(ctx_.get(), N_, xi1_, &spec_, relax_, &h_), "MOC::MOC");
-        stageCellFields();
         const int64_t nc = phase.ncells;
-        n_ = DeviceArray(ctx_, (int64_t)N_ * nc);
-        d_dev_ = DeviceArray(ctx_, nc);
-        diag_ = DeviceArray(ctx_, 2 * N_ + 1); // per-class min, max; continuity error
-        if (n0)
-            n_.upload(n0, (int64_t)N_ * nc);
-        else
-            n_.zero();
+        check(pbe_moc_state_create(h_, nc, phase.V, &state_), "MOC::MOC");
+        if (n0) check(pbe_moc_state_upload(state_, nc, n0), "MOC::MOC");
         d_host_.assign((size_t)nc, 0.0);
-        if (nc) check(pbe_moc_d(h_, nc, nc, n_.data(), d_dev_.data(), nullptr), "MOC::MOC d");
-        d_stale_ = true;
+        classMin_.assign((size_t)N_, 0.0);
+        classMax_.assign((size_t)N_, 0.0);
         if (phase.mesh && nc) {
-            const FaceMesh &fm = *phase.mesh;
             if (!usingMULES_)
                 throw FatalError("MOC: usingMULES false selects the implicit fvm::ddt + fvm::div solve "
                                  "(MOC.C:186-198), which has no device path; set usingMULES true");
             if (!phase.V) throw FatalError("MOC: transport needs the cell volumes (Phase::V)");
-            check(pbe_div_scheme_type(fm.divScheme.c_str(), &scheme_), "MOC::MOC div(phi,n.*)");
-            check(pbe_mesh_create(ctx_.get(), nc, fm.nInternalFaces, fm.owner, fm.neighbour, fm.nBoundaryFaces,
-                                  fm.boundaryOwner, phase.V, &mesh_),
-                  "MOC::MOC mesh");
-            const int64_t nf = fm.nInternalFaces + fm.nBoundaryFaces;
-            phi_ = DeviceArray(ctx_, std::max<int64_t>(nf, 1));
-            S_ = DeviceArray(ctx_, (int64_t)N_ * nc);
-            nNew_ = DeviceArray(ctx_, (int64_t)N_ * nc);
-            if (fm.boundaryValues) psiB_ = DeviceArray(ctx_, std::max<int64_t>((int64_t)N_ * fm.nBoundaryFaces, 1));
+            check(pbe_div_scheme_type(phase.mesh->divScheme.c_str(), &scheme_), "MOC::MOC div(phi,n.*)");
+            mesh_ = makeDeviceMesh(ctx_.get(), phase, scheme_, "MOC::MOC mesh");
+            check(pbe_moc_state_attach_mesh(state_, mesh_, scheme_), "MOC::MOC");
+            tryPin(ctx_.get(), phase.mesh->phi, (phase.mesh->nInternalFaces + phase.mesh->nBoundaryFaces) * 8);
         }
+        for (const double *p : {phase.epsilon, phase.rho, phase.nu, phase.alpha}) tryPin(ctx_.get(), p, nc * 8);
+        tryPin(ctx_.get(), d_host_.data(), nc * 8);
+        if (nc) check(pbe_moc_state_d(state_, d_host_.data()), "MOC::MOC d"); // PBEDiameter's d_(method_->d())
     }
     ~MOC() override {
+        for (const double *p : {phase_.epsilon, phase_.rho, phase_.nu, phase_.alpha}) tryUnpin(ctx_.get(), p);
+        if (phase_.mesh) tryUnpin(ctx_.get(), phase_.mesh->phi);
+        tryUnpin(ctx_.get(), d_host_.data());
+        if (state_) pbe_moc_state_destroy(state_);
         if (mesh_) pbe_mesh_destroy(mesh_);
         if (h_) pbe_moc_destroy(h_);
     }
 
-    // MOC::correct(): sources of every class, limiter, zero-flux update, per-class global min
-    // (the `Info << min(n_k)` of MOC.C:181-183), continuity error (MOC.C:276-279), d.
+    // MOC::correct() (MOC.C:159-184) + d() (PBEDiameter.H:95-99) in one library call: sources of every
+    // class, limiter, solveWithMULES (or the zero-flux update), per-class min (the `Info << min(n_k)` of
+    // MOC.C:181-183), continuity error (MOC.C:276-279), d -- the phase fields are re-read every step.
     void correct() override {
-        const int64_t nc = phase_.ncells;
-        if (nc == 0) return;
-        if (mesh_) {
-            solveWithMULES();
-            return;
-        }
-        pbe_moc_io io;
-        std::memset(&io, 0, sizeof(io));
-        io.d = d_dev_.data();
-        double *cont = diag_.data() + 2 * N_;
-        if (phase_.alpha && phase_.V) {
-            io.alpha = alpha_.data();
-            io.vcell = vcell_.data();
-            io.cont_err_max = cont;
-            check(pbe_memset(ctx_.get(), cont, 0, sizeof(double)), "MOC::correct");
-        }
-        check(pbe_moc_step(h_, nc, nc, n_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, &io,
-                           nullptr),
+        if (phase_.ncells == 0) return;
+        if (!phase_.epsilon || !phase_.rho || !phase_.nu) throw FatalError("PBEMethod: phase lacks epsilon/rho/nu");
+        pbe_moc_diag diag;
+        std::memset(&diag, 0, sizeof(diag));
+        diag.class_min = classMin_.data();
+        diag.class_max = classMax_.data();
+        const FaceMesh *fm = mesh_ ? phase_.mesh : nullptr;
+        check(pbe_moc_correct_resident(state_, phase_.epsilon, phase_.rho, phase_.nu, phase_.V ? phase_.alpha : nullptr,
+                                       fm ? fm->phi : nullptr, fm ? fm->boundaryValues : nullptr,
+                                       fm ? fm->nBoundaryFaces : 0, phase_.deltaT, d_host_.data(), &diag),
               "MOC::correct");
-        check(pbe_moc_class_minmax(h_, nc, nc, n_.data(), diag_.data(), diag_.data() + N_, nullptr),
-              "MOC::correct minmax");
-        d_stale_ = true;
-        diag_stale_ = true;
+        continuityError_ = diag.cont_err_max;
     }
-    // MOC::solveWithMULES (MOC.C:198-272) for `Gauss upwind`: S_k of the current n, then
-    // n_k <- (n_k rDeltaT + S_k - div(phi n_k)) / rDeltaT on the device, d, per-class min / max.
-    // (The continuity print of MOC.C:276-279 is left to continuityError() of the zero-flux path.)
-    void solveWithMULES() {
-        const int64_t nc = phase_.ncells;
-        const FaceMesh &fm = *phase_.mesh;
-        const int64_t nf = fm.nInternalFaces + fm.nBoundaryFaces;
-        if (nf) phi_.upload(fm.phi, nf);
-        if (fm.boundaryValues && fm.nBoundaryFaces) psiB_.upload(fm.boundaryValues, (int64_t)N_ * fm.nBoundaryFaces);
-        check(pbe_moc_source(h_, nc, nc, n_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, S_.data(),
-                             nullptr),
-              "MOC::correct source");
-        check(pbe_transport_explicit(mesh_, scheme_, N_, nc, n_.data(), phi_.data(),
-                                     fm.boundaryValues ? psiB_.data() : nullptr, fm.nBoundaryFaces, S_.data(),
-                                     phase_.deltaT, nNew_.data(), nullptr),
-              "MOC::correct transport");
-        std::swap(n_, nNew_);
-        check(pbe_moc_d(h_, nc, nc, n_.data(), d_dev_.data(), nullptr), "MOC::correct d");
-        check(pbe_moc_class_minmax(h_, nc, nc, n_.data(), diag_.data(), diag_.data() + N_, nullptr),
-              "MOC::correct minmax");
-        d_stale_ = true;
-        diag_stale_ = true;
-    }
-    const std::vector<double> &d() const override {
-        if (d_stale_ && phase_.ncells) {
-            check(pbe_sync(ctx_.get()), "MOC::d");
-            d_dev_.download(d_host_.data(), phase_.ncells);
-            d_stale_ = false;
-        }
-        return d_host_;
-    }
+    const std::vector<double> &d() const override { return d_host_; }
     int numberOfClasses() const { return N_; }
     double xi(int i) const { return xi1_ * (i + 1); } // MOC.C:79
-    // class field n<i>, host copy
+    // class field n<i>, host copy (runTime.write() of one field)
     std::vector<double> classNumberDensity(int i) const {
-        std::vector<double> v((size_t)phase_.ncells);
-        check(pbe_sync(ctx_.get()), "MOC::classNumberDensity");
-        if (phase_.ncells) n_.download(v.data(), phase_.ncells, (int64_t)i * phase_.ncells);
-        return v;
+        const int64_t nc = phase_.ncells;
+        std::vector<double> all((size_t)N_ * nc);
+        if (nc) check(pbe_moc_state_download(state_, nc, all.data()), "MOC::classNumberDensity");
+        return std::vector<double>(all.begin() + (size_t)i * nc, all.begin() + (size_t)(i + 1) * nc);
     }
-    double classMin(int i) const { return fetchDiag()[i]; }
-    double classMax(int i) const { return fetchDiag()[N_ + i]; }
-    double continuityError() const { return fetchDiag()[2 * N_]; }
-    double *deviceClassFields() const { return n_.data(); } // [N][ncells], for adapters that keep state resident
+    double classMin(int i) const { return classMin_[(size_t)i]; }
+    double classMax(int i) const { return classMax_[(size_t)i]; }
+    double continuityError() const { return continuityError_; }
+    double *deviceClassFields() const { // [N][ncells], for callers that chain their own device work
+        double *n = nullptr;
+        check(pbe_moc_state_device(state_, &n, nullptr, nullptr), "MOC::deviceClassFields");
+        return n;
+    }
 
 private:
-    const std::vector<double> &fetchDiag() const {
-        if (diag_stale_) {
-            diag_host_.resize((size_t)2 * N_ + 1);
-            check(pbe_sync(ctx_.get()), "MOC diag");
-            diag_.download(diag_host_.data(), 2 * N_ + 1);
-            diag_stale_ = false;
-        }
-        return diag_host_;
-    }
     pbe_moc *h_ = nullptr;
+    pbe_moc_state *state_ = nullptr;
     int N_ = 0;
-    double xi1_ = 0, relax_ = 1.0;
+    double xi1_ = 0, relax_ = 1.0, continuityError_ = 0.0;
     bool usingMULES_ = false;
     pbe_mesh *mesh_ = nullptr;
     int scheme_ = 0;
-    DeviceArray n_, d_dev_, diag_, phi_, S_, nNew_, psiB_;
-    mutable std::vector<double> d_host_, diag_host_;
-    mutable bool d_stale_ = true, diag_stale_ = true;
+    std::vector<double> d_host_, classMin_, classMax_;
 };
 
 // ---- quadratureMethodOfMoments (QMOM.H:55-112, QMOM.C:59-129) ----------------------------------------------
@@ -499,109 +484,80 @@ public:
         order_ = c.readLabel("quadratureOrder");
         usingMULES_ = c.lookupOrDefault<bool>("usingMULES", false);
         check(pbe_qmom_create(ctx_.get(), order_, &spec_, &h_), "QMOM::QMOM");
-        stageCellFields();
         const int64_t nc = phase.ncells;
-        m_ = DeviceArray(ctx_, (int64_t)2 * order_ * nc);
-        S_ = DeviceArray(ctx_, (int64_t)2 * order_ * nc);
-        d_dev_ = DeviceArray(ctx_, nc);
-        diag_ = DeviceArray(ctx_, 4);
-        if (m0)
-            m_.upload(m0, (int64_t)2 * order_ * nc);
-        else
-            m_.zero();
+        check(pbe_qmom_state_create(h_, nc, phase.V, &state_), "QMOM::QMOM");
+        if (m0) check(pbe_qmom_state_upload(state_, nc, m0), "QMOM::QMOM");
+        stats_.assign((size_t)(4 * order_ + 1) * 4, 0.0);
         if (phase.mesh && nc) {
-            const FaceMesh &fm = *phase.mesh;
             if (!usingMULES_)
                 throw FatalError("QMOM: usingMULES false selects the implicit fvm::ddt + fvm::div solve "
                                  "(QMOM.C:199-209), which has no device path; set usingMULES true");
             if (!phase.V) throw FatalError("QMOM: transport needs the cell volumes (Phase::V)");
-            check(pbe_div_scheme_type(fm.divScheme.c_str(), &scheme_), "QMOM::QMOM div(phi,m.*)");
-            check(pbe_mesh_create(ctx_.get(), nc, fm.nInternalFaces, fm.owner, fm.neighbour, fm.nBoundaryFaces,
-                                  fm.boundaryOwner, phase.V, &mesh_),
-                  "QMOM::QMOM mesh");
-            phi_ = DeviceArray(ctx_, std::max<int64_t>(fm.nInternalFaces + fm.nBoundaryFaces, 1));
-            mNew_ = DeviceArray(ctx_, (int64_t)2 * order_ * nc);
-            if (fm.boundaryValues)
-                psiB_ = DeviceArray(ctx_, std::max<int64_t>((int64_t)2 * order_ * fm.nBoundaryFaces, 1));
+            check(pbe_div_scheme_type(phase.mesh->divScheme.c_str(), &scheme_), "QMOM::QMOM div(phi,m.*)");
+            mesh_ = makeDeviceMesh(ctx_.get(), phase, scheme_, "QMOM::QMOM mesh");
+            check(pbe_qmom_state_attach_mesh(state_, mesh_, scheme_), "QMOM::QMOM");
+            tryPin(ctx_.get(), phase.mesh->phi, (phase.mesh->nInternalFaces + phase.mesh->nBoundaryFaces) * 8);
         }
         d_host_.assign((size_t)nc, 0.0);
-        if (m0 && order_ >= 1) { // d_ = pow(6/pi m1/m0, 1/3) at construction, QMOM.C:81
-            for (int64_t c2 = 0; c2 < nc; ++c2)
-                d_host_[(size_t)c2] = std::pow(6.0 / M_PI * m0[nc + c2] / m0[c2], 1.0 / 3.0);
-            d_stale_ = false;
-        }
+        for (const double *p : {phase.epsilon, phase.rho, phase.nu}) tryPin(ctx_.get(), p, nc * 8);
+        tryPin(ctx_.get(), d_host_.data(), nc * 8);
+        if (m0 && nc && order_ >= 1) check(pbe_qmom_state_d(state_, d_host_.data()), "QMOM::QMOM d"); // QMOM.C:81
     }
     ~QMOM() override {
+        for (const double *p : {phase_.epsilon, phase_.rho, phase_.nu}) tryUnpin(ctx_.get(), p);
+        if (phase_.mesh) tryUnpin(ctx_.get(), phase_.mesh->phi);
+        tryUnpin(ctx_.get(), d_host_.data());
+        if (state_) pbe_qmom_state_destroy(state_);
         if (mesh_) pbe_mesh_destroy(mesh_);
         if (h_) pbe_qmom_destroy(h_);
     }
 
-    // QMOM::correct(): moment sources, NaN scrub, zero-flux update, clamp to SMALL, d (QMOM.C:85-129)
+    // QMOM::correct() (QMOM.C:85-129) in one library call: moment sources, NaN scrub, solveWithMULES (or the
+    // zero-flux update), clamp to SMALL, d and the printAvgMaxMin partials of sources, moments and d
     void correct() override {
-        const int64_t nc = phase_.ncells;
-        if (nc == 0) return;
-        if (mesh_) { // sources, NaN scrub, solveWithMULES (QMOM.C:131-197, Gauss upwind), clamp, d
-            const FaceMesh &fm = *phase_.mesh;
-            const int nm = 2 * order_;
-            const int64_t nf = fm.nInternalFaces + fm.nBoundaryFaces;
-            if (nf) phi_.upload(fm.phi, nf);
-            if (fm.boundaryValues && fm.nBoundaryFaces) psiB_.upload(fm.boundaryValues, (int64_t)nm * fm.nBoundaryFaces);
-            check(pbe_qmom_source(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), S_.data(), nullptr),
-                  "QMOM::correct source");
-            check(pbe_field_scrub_nan(ctx_.get(), (int64_t)nm * nc, S_.data(), nullptr), "QMOM::correct scrub");
-            check(pbe_transport_explicit(mesh_, scheme_, nm, nc, m_.data(), phi_.data(),
-                                         fm.boundaryValues ? psiB_.data() : nullptr, fm.nBoundaryFaces, S_.data(),
-                                         phase_.deltaT, mNew_.data(), nullptr),
-                  "QMOM::correct transport");
-            std::swap(m_, mNew_);
-            check(pbe_qmom_clamp_d(ctx_.get(), nm, nc, nc, m_.data(), d_dev_.data(), nullptr), "QMOM::correct clamp");
-            d_stale_ = true;
-            return;
-        }
-        check(pbe_qmom_step(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, S_.data(),
-                            d_dev_.data(), nullptr),
+        if (phase_.ncells == 0) return;
+        if (!phase_.epsilon || !phase_.rho || !phase_.nu) throw FatalError("PBEMethod: phase lacks epsilon/rho/nu");
+        const int nm = 2 * order_;
+        pbe_qmom_diag diag;
+        diag.source = stats_.data();
+        diag.moment = stats_.data() + (size_t)4 * nm;
+        diag.d = stats_.data() + (size_t)8 * nm;
+        const FaceMesh *fm = mesh_ ? phase_.mesh : nullptr;
+        check(pbe_qmom_correct_resident(state_, phase_.epsilon, phase_.rho, phase_.nu, fm ? fm->phi : nullptr,
+                                        fm ? fm->boundaryValues : nullptr, fm ? fm->nBoundaryFaces : 0, phase_.deltaT,
+                                        d_host_.data(), &diag),
               "QMOM::correct");
-        d_stale_ = true;
     }
-    const std::vector<double> &d() const override {
-        if (d_stale_ && phase_.ncells) {
-            check(pbe_sync(ctx_.get()), "QMOM::d");
-            d_dev_.download(d_host_.data(), phase_.ncells);
-            d_stale_ = false;
-        }
-        return d_host_;
-    }
+    const std::vector<double> &d() const override { return d_host_; }
     int quadratureOrder() const { return order_; }
     std::vector<double> moment(int k) const {
-        std::vector<double> v((size_t)phase_.ncells);
-        check(pbe_sync(ctx_.get()), "QMOM::moment");
-        if (phase_.ncells) m_.download(v.data(), phase_.ncells, (int64_t)k * phase_.ncells);
-        return v;
+        const int64_t nc = phase_.ncells;
+        std::vector<double> all((size_t)2 * order_ * nc);
+        if (nc) check(pbe_qmom_state_download(state_, nc, all.data()), "QMOM::moment");
+        return std::vector<double>(all.begin() + (size_t)k * nc, all.begin() + (size_t)(k + 1) * nc);
     }
-    // printAvgMaxMin(mesh, field) of Utility.C:4-10 for moment k or its (scrubbed) source: {avg, max, min}
+    // printAvgMaxMin(mesh, field) of Utility.C:4-10 for moment k or its (scrubbed) source, as of the last
+    // correct(): {avg, max, min} (global when the context carries a communicator)
     struct AvgMaxMin {
         double avg, max, min;
     };
     AvgMaxMin avgMaxMin(int k, bool source = false) const {
-        const int64_t nc = phase_.ncells;
-        const double *f = (source ? S_.data() : m_.data()) + (int64_t)k * nc;
-        check(pbe_field_avg_max_min(ctx_.get(), nc, f, phase_.V ? vcell_.data() : nullptr, diag_.data(), nullptr),
-              "printAvgMaxMin");
-        double o[4];
-        check(pbe_sync(ctx_.get()), "printAvgMaxMin");
-        diag_.download(o, 4);
+        const double *o = stats_.data() + (size_t)4 * ((source ? 0 : 2 * order_) + k);
+        return {o[0] / o[1], o[2], o[3]};
+    }
+    AvgMaxMin avgMaxMinDiameter() const {
+        const double *o = stats_.data() + (size_t)16 * order_;
         return {o[0] / o[1], o[2], o[3]};
     }
 
 private:
     pbe_qmom *h_ = nullptr;
+    pbe_qmom_state *state_ = nullptr;
     int order_ = 0;
     bool usingMULES_ = false;
     pbe_mesh *mesh_ = nullptr;
     int scheme_ = 0;
-    DeviceArray m_, S_, d_dev_, diag_, phi_, mNew_, psiB_;
-    mutable std::vector<double> d_host_;
-    mutable bool d_stale_ = true;
+    std::vector<double> d_host_, stats_;
 };
 
 // ---- methodOfMoments (MOM.H:55-96, MOM.C:60-236): three moments, presumed gamma density -----------------

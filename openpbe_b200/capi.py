@@ -149,6 +149,14 @@ PROTOTYPES = {
     "pbe_qmom_state_attach_mesh": (C.c_int, [_vp, _vp, C.c_int]),
     "pbe_qmom_correct_resident": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_double, _vp,
                                             C.POINTER(QmomDiag)]),
+    "pbe_comm_unique_id": (C.c_int, [_vp]),
+    "pbe_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "pbe_comm_init_from": (C.c_int, [_vp, _vp]),
+    "pbe_comm_destroy": (C.c_int, [_vp]),
+    "pbe_comm_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "pbe_reduce_diagnostics": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp]),
+    "pbe_reduce_diagnostics_host": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp]),
+    "pbe_halo_exchange": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, _i64, _vp, _i64, _vp]),
     "pbe_host_register": (C.c_int, [_vp, _vp, _i64]),
     "pbe_host_unregister": (C.c_int, [_vp, _vp]),
     "pbe_moc_correct_host": (C.c_int, [_vp, _vp, C.c_int, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64,

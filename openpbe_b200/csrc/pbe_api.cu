@@ -157,6 +157,7 @@ int pbe_ctx_destroy(pbe_ctx *ctx) {
     if (!ctx) return PBE_OK;
     DeviceGuard g(ctx->device);
     cudaDeviceSynchronize();
+    if (ctx->comm) pbe_comm_destroy(ctx);
     for (int s = 0; s < kHostSlots; ++s) {
         if (ctx->stage[s]) cudaFree(ctx->stage[s]);
         if (ctx->slot_stream[s]) cudaStreamDestroy(ctx->slot_stream[s]);

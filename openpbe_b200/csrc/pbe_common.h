@@ -37,6 +37,8 @@ constexpr int kHostSlots = 3; // H2D(k+1) | kernel(k) | D2H(k-1)
 
 } // namespace pbe
 
+struct pbe_comm; // NCCL communicator + side stream (pbe_comm.cu); null on a single-rank context
+
 // The opaque handles of include/pbe_b200.h
 struct pbe_ctx {
     int device = 0;
@@ -54,6 +56,7 @@ struct pbe_ctx {
     // not to a handle: the largest request any handle of this context has made so far
     std::mutex smem_mu;
     std::map<const void *, size_t> smem_limit;
+    pbe_comm *comm = nullptr; // pbe_comm_init / pbe_comm_init_from
 };
 
 namespace pbe {

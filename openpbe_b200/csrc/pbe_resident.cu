@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256) rows_stats_partial_kernel(int64_t ncells,
         o[3] = mn;
     }
 }
-// Stage 2: one warp per row folds its partials -> out[row][4]
+// Stage 2: one warp per row folds its partials -> out[4][rows]
 __global__ void rows_stats_final_kernel(int nparts, const double *__restrict__ part, double *__restrict__ out) {
     const int k = blockIdx.x;
     double sfv = 0.0, sv = 0.0, mx = -INFINITY, mn = INFINITY;
@@ -147,11 +147,12 @@ __global__ void rows_stats_final_kernel(int nparts, const double *__restrict__ p
         mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
         mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
     }
-    if (threadIdx.x == 0) {
-        out[(size_t)k * 4 + 0] = sfv;
-        out[(size_t)k * 4 + 1] = sv;
-        out[(size_t)k * 4 + 2] = mx;
-        out[(size_t)k * 4 + 3] = mn;
+    if (threadIdx.x == 0) { // structure of arrays [sum f V | sum V | min | max][rows]: each is one NCCL all-reduce
+        const size_t nr = gridDim.x;
+        out[0 * nr + k] = sfv;
+        out[1 * nr + k] = sv;
+        out[2 * nr + k] = mn;
+        out[3 * nr + k] = mx;
     }
 }
 
@@ -424,9 +425,15 @@ int moc_correct_impl(pbe_moc_state *s, const double *eps_h, const double *rho_h,
     }
     PBE_CUDA(cudaEventRecord(P.ev_side, P.s_side));
     PBE_CUDA(cudaStreamWaitEvent(P.s_comp, P.ev_side, 0));
-    if (diag)
+    if (diag) {
+        // with a communicator on the context the printed quantities are the GLOBAL ones, as the reference's
+        // gMin / gMax / gSum are (MOC.C:181-183, 238, 276-279): [min N] | [max N, continuity] | [moments 8]
+        int rc = pbe_reduce_diagnostics(ctx, 8, mom_dev, want_minmax ? N : 0, s->diag + (size_t)2 * N, want_minmax ? N + 1 : 1,
+                                        want_minmax ? s->diag + (size_t)3 * N : cont_dev, P.s_comp);
+        if (rc) return rc;
         PBE_CUDA(cudaMemcpyAsync(s->diag_host, s->diag, ((size_t)N * 4 + 9) * sizeof(double), cudaMemcpyDeviceToHost,
                                  P.s_comp));
+    }
     PBE_CUDA(cudaStreamSynchronize(P.s_in));
     PBE_CUDA(cudaStreamSynchronize(P.s_comp));
     PBE_CUDA(cudaStreamSynchronize(P.s_out));
@@ -434,8 +441,8 @@ int moc_correct_impl(pbe_moc_state *s, const double *eps_h, const double *rho_h,
     if (nu_h) s->have_nu = true;
     if (diag) {
         for (int k = 0; k < N; ++k) {
-            if (diag->class_max) diag->class_max[k] = s->diag_host[(size_t)k * 4 + 2];
-            if (diag->class_min) diag->class_min[k] = s->diag_host[(size_t)k * 4 + 3];
+            if (diag->class_min) diag->class_min[k] = s->diag_host[(size_t)2 * N + k];
+            if (diag->class_max) diag->class_max[k] = s->diag_host[(size_t)3 * N + k];
         }
         diag->cont_err_max = want_cont ? s->diag_host[(size_t)N * 4] : 0.0;
         for (int q = 0; q < 8; ++q) diag->moments[q] = (q < nmom) ? s->diag_host[(size_t)N * 4 + 1 + q] : 0.0;
@@ -738,20 +745,34 @@ int qmom_correct_impl(pbe_qmom_state *s, const double *eps_h, const double *rho_
             rc = launch_stats_partial(ctx, 1, nc, nc, s->d, V, true, s->part + (size_t)2 * nm * parts_all * 4, parts_all,
                                       0, parts_all, P.s_comp);
         if (rc) return rc;
-        rows_stats_final_kernel<<<2 * nm + 1, 32, 0, P.s_comp>>>(parts_all, s->part, s->diag);
+        const int nr = 2 * nm + 1;
+        rows_stats_final_kernel<<<nr, 32, 0, P.s_comp>>>(parts_all, s->part, s->diag);
         PBE_CUDA(cudaGetLastError());
         ctx->launches++;
-        PBE_CUDA(cudaMemcpyAsync(s->diag_host, s->diag, (size_t)(2 * nm + 1) * 4 * sizeof(double),
-                                 cudaMemcpyDeviceToHost, P.s_comp));
+        // global printAvgMaxMin (Utility.C:4-10 reduces over the ranks): [sum f V, sum V] | [min] | [max]
+        rc = pbe_reduce_diagnostics(ctx, 2 * nr, s->diag, nr, s->diag + 2 * nr, nr, s->diag + 3 * nr, P.s_comp);
+        if (rc) return rc;
+        PBE_CUDA(cudaMemcpyAsync(s->diag_host, s->diag, (size_t)nr * 4 * sizeof(double), cudaMemcpyDeviceToHost, P.s_comp));
     }
     PBE_CUDA(cudaStreamSynchronize(P.s_in));
     PBE_CUDA(cudaStreamSynchronize(P.s_comp));
     PBE_CUDA(cudaStreamSynchronize(P.s_out));
     if (rho_h) s->have_rho = true;
     if (nu_h) s->have_nu = true;
-    if (want_src) memcpy(diag->source, s->diag_host, (size_t)nm * 4 * sizeof(double));
-    if (want_mom) memcpy(diag->moment, s->diag_host + (size_t)nm * 4, (size_t)nm * 4 * sizeof(double));
-    if (want_d) memcpy(diag->d, s->diag_host + (size_t)2 * nm * 4, 4 * sizeof(double));
+    {   // device layout [sum f V | sum V | min | max][rows] -> the caller's [row][sum f V, sum V, max, min]
+        const int nr = 2 * nm + 1;
+        auto row = [&](int r, double *o) {
+            o[0] = s->diag_host[r];
+            o[1] = s->diag_host[nr + r];
+            o[2] = s->diag_host[3 * nr + r];
+            o[3] = s->diag_host[2 * nr + r];
+        };
+        for (int k = 0; k < nm; ++k) {
+            if (want_src) row(k, diag->source + 4 * k);
+            if (want_mom) row(nm + k, diag->moment + 4 * k);
+        }
+        if (want_d) row(2 * nm, diag->d);
+    }
     return PBE_OK;
 }
 

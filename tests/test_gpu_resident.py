@@ -316,3 +316,35 @@ def test_moc_state_range_io_and_device_view(ctx):
     assert np.array_equal(st.download().numpy(), 2.0 * f["n"])
     st.close()
     moc.close()
+
+
+def test_comm_through_the_c_abi_single_rank(ctx):
+    """pbe_comm_unique_id / pbe_comm_init (NCCL bound at run time) with one rank: the reductions are the
+    identity, the resident correct() still returns its diagnostics (now routed through NCCL)."""
+    import ctypes as C
+    from openpbe_b200 import capi
+    L = capi.lib()
+    c2 = engine.Context(0)
+    ident = C.create_string_buffer(128)
+    capi.check(L.pbe_comm_unique_id(ident))
+    capi.check(L.pbe_comm_init(c2.handle, 1, 0, ident))
+    nr, rk = C.c_int(-1), C.c_int(-1)
+    capi.check(L.pbe_comm_info(c2.handle, C.byref(nr), C.byref(rk)))
+    assert (nr.value, rk.value) == (1, 0)
+    s, mn, mx = np.array([1.5, 2.5]), np.array([-3.0]), np.array([7.0, 8.0, 9.0])
+    capi.check(L.pbe_reduce_diagnostics_host(c2.handle, 2, s.ctypes.data, 1, mn.ctypes.data, 3, mx.ctypes.data))
+    assert s.tolist() == [1.5, 2.5] and mn.tolist() == [-3.0] and mx.tolist() == [7.0, 8.0, 9.0]
+    w = synthetic.workload("moc30_ct", 5000)
+    f = synthetic.moc_fields(w)
+    spec = engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+    moc = engine.MOC(c2, w.N, w.xi1, spec, w.relax)
+    st = engine.MOCState(moc, 5000, vcell=f["vcell"], n0=f["n"])
+    d, diag = st.correct(f["eps"], f["rho"], f["nu"], f["alpha"], w.dt, minmax=True, n_moments=2)
+    n_g = st.download().numpy()
+    assert np.array_equal(diag["class_min"], n_g.min(axis=1)) and np.array_equal(diag["class_max"], n_g.max(axis=1))
+    assert diag["cont_err_max"] > 0.0 and diag["moments"][0] > 0.0
+    st.close(); moc.close()
+    with pytest.raises(capi.PbeError, match="already has a communicator"):
+        capi.check(L.pbe_comm_init(c2.handle, 1, 0, ident))
+    capi.check(L.pbe_comm_destroy(c2.handle))
+    c2.close()
