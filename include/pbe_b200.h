@@ -178,9 +178,19 @@ typedef struct pbe_mom pbe_mom;
 #define PBE_MOM_DEFAULT_PANELS 12
 #define PBE_MOM_MAX_PANELS 28
 #define PBE_MOM_GRADED_LEVELS 20 /* bisections of the panel next to the lower limit */
+/* The rule is FIXED where QAGIU adapts: it resolves densities whose mass lies between x ~ 1e-7 and
+ * x ~ panels (mean volumes of O(1), the scales of the reference's own 0-D cases,
+ * tests/integration/MOC/setupCases.py:41-54; validated for shapes k in (0.3, 4], tests/test_mom.py).
+ * Every call checks, per cell, that the rule gives back the density's own m0 and m1; cells off by more
+ * than this relative tolerance are counted (pbe_mom_coverage) instead of being integrated silently
+ * wrong -- rescale the volume unit of such a case (the kernels are homogeneous in xi). */
+#define PBE_MOM_COVERAGE_TOL 1.0e-6
 
 int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mom **out);
 int pbe_mom_destroy(pbe_mom *h);
+/* uncovered cells since the last reset and the worst relative deviation seen (see
+ * PBE_MOM_COVERAGE_TOL); synchronises the device; reset != 0 clears the counters */
+int pbe_mom_coverage(pbe_mom *h, int64_t *uncovered_cells, double *worst_deviation, int reset);
 /* S[k][c] = coalescenceSourceTerm(k) + breakupSourceTerm(k), k < 3, NOT NaN-scrubbed
  * (MOM::momentSourceTerm, MOM.C:244-254).  m, S: [3][stride] device arrays.  gamma (optional,
  * [3][stride]) receives gamma_c0, gamma_k, gamma_theta (MOM.C:151-161).  Cells whose moments give

@@ -111,6 +111,7 @@ PROTOTYPES = {
     "pbe_qmom_source_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "pbe_mom_create": (C.c_int, [_vp, C.c_int, C.POINTER(KernelSpec), C.POINTER(_vp)]),
     "pbe_mom_destroy": (C.c_int, [_vp]),
+    "pbe_mom_coverage": (C.c_int, [_vp, C.POINTER(_i64), _dp, C.c_int]),
     "pbe_mom_source": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "pbe_mom_step": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp, _vp, _vp]),
     "pbe_mesh_create": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp, C.POINTER(_vp)]),

@@ -18,6 +18,8 @@
 // of the CT coalescence kernel come from a per-handle pair table.
 #include <algorithm>
 
+#include <string.h>
+
 #include "pbe_common.h"
 #include "pbe_kernels.cuh"
 
@@ -28,6 +30,7 @@ struct pbe_mom {
     int panels = 0;
     DevKernelSpec ks{};
     double *pair_tab = nullptr; // device, owned
+    unsigned long long *d_cov = nullptr; // device [2]: uncovered-cell count, worst deviation (bit pattern)
 };
 
 namespace {
@@ -67,6 +70,7 @@ struct MomParams {
     int do_step;
     int panels;
     const double *pair_tab; // CT coalescence: G, H of every node pair, [2][nq][nq], or NULL
+    unsigned long long *cov; // [2]: cells whose density the fixed rule does not cover; worst deviation (bits)
     DevKernelSpec ks;
 };
 
@@ -167,7 +171,28 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, NC == 1 ? 6 : 3) mom_kernel
             gtheta[i] = (m0[i] * m2[i] - m1[i] * m1[i]) / fmax(m0[i] * m1[i], kSmall);
             const GammaPdf pdf(gk[i], gtheta[i]);
             cc[i] = cell_coef(p.ks, p.eps[c], p.rho[c], p.nu[c]);
-            for (int q = lane; q < nq; q += 32) fq[i * nq + q] = wq[q] * (m0[i] * pdf(xq[q]));
+            // coverage of the presumed density by the FIXED rule: sum_q f_q must give back m0 and
+            // sum_q f_q x_q m1.  QAGIU would refine where this rule cannot (mass beyond the last
+            // equal panel, or below the last graded one): such cells are counted, not silently wrong.
+            double cv0 = 0.0, cv1 = 0.0;
+            for (int q = lane; q < nq; q += 32) {
+                const double fv = wq[q] * (m0[i] * pdf(xq[q]));
+                fq[i * nq + q] = fv;
+                cv0 += fv;
+                cv1 = fma_(fv, xq[q], cv1);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                cv0 += __shfl_xor_sync(0xffffffffu, cv0, o);
+                cv1 += __shfl_xor_sync(0xffffffffu, cv1, o);
+            }
+            if (lane == 0 && cb + i < p.ncells && p.cov != nullptr) {
+                const double dev = fmax(fabs(cv0 / m0[i] - 1.0), fabs(cv1 / m1[i] - 1.0));
+                if (dev > PBE_MOM_COVERAGE_TOL) { // NaN (invalid gamma parameters) compares false: scrubbed as in the reference
+                    atomicAdd(p.cov, 1ull);
+                    atomicMax(p.cov + 1, (unsigned long long)__double_as_longlong(dev));
+                }
+            }
         }
         __syncwarp();
 
@@ -300,6 +325,7 @@ int launch_mom(pbe_mom *h, MomParams &p, cudaStream_t st) {
     p.panels = h->panels;
     p.ks = h->ks;
     p.pair_tab = h->pair_tab;
+    p.cov = h->d_cov;
     const int nq = 15 * (h->panels + PBE_MOM_GRADED_LEVELS);
     // CT coalescence (pair table): two cells per warp share every table load; the cell-independent
     // kernels have nothing to share and run one cell per warp (measured: 13.8 vs 85 ms per 4e5 cells)
@@ -359,8 +385,11 @@ int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mo
             ctx->launches++;
         }
     }
+    if (e == cudaSuccess) e = cudaMalloc((void **)&h->d_cov, 2 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->d_cov, 0, 2 * sizeof(unsigned long long));
     if (e != cudaSuccess) {
         if (h->pair_tab) cudaFree(h->pair_tab);
+        if (h->d_cov) cudaFree(h->d_cov);
         delete h;
         return cuda_fail(e, "pbe_mom_create", __FILE__, __LINE__);
     }
@@ -369,11 +398,30 @@ int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mo
 }
 
 int pbe_mom_destroy(pbe_mom *h) {
-    if (h && h->pair_tab) {
+    if (h) {
         DeviceGuard g(h->ctx->device);
-        cudaFree(h->pair_tab);
+        if (h->pair_tab) cudaFree(h->pair_tab);
+        if (h->d_cov) cudaFree(h->d_cov);
     }
     delete h;
+    return PBE_OK;
+}
+
+// Cells (since the last reset) whose presumed gamma density the fixed quadrature rule did not cover:
+// |sum_q f_q / m0 - 1| or |sum_q f_q x_q / m1 - 1| above PBE_MOM_COVERAGE_TOL.  Synchronises the device.
+int pbe_mom_coverage(pbe_mom *h, int64_t *uncovered_cells, double *worst_deviation, int reset) {
+    PBE_REQUIRE(h != nullptr, PBE_E_INVALID, "pbe_mom_coverage: NULL handle");
+    DeviceGuard g(h->ctx->device);
+    unsigned long long v[2] = {0, 0};
+    PBE_CUDA(cudaDeviceSynchronize());
+    PBE_CUDA(cudaMemcpy(v, h->d_cov, sizeof(v), cudaMemcpyDeviceToHost));
+    if (uncovered_cells) *uncovered_cells = (int64_t)v[0];
+    if (worst_deviation) {
+        double d;
+        memcpy(&d, &v[1], sizeof(d));
+        *worst_deviation = d;
+    }
+    if (reset) PBE_CUDA(cudaMemset(h->d_cov, 0, sizeof(v)));
     return PBE_OK;
 }
 

@@ -530,6 +530,12 @@ class MOM:
         except Exception:
             pass
 
+    def coverage(self, reset: bool = True):
+        """(cells the fixed rule did not cover since the last reset, worst relative deviation of m0 / m1)"""
+        n, w = C.c_int64(), C.c_double()
+        capi.check(capi.lib().pbe_mom_coverage(self._h, C.byref(n), C.byref(w), int(reset)))
+        return n.value, w.value
+
     @staticmethod
     def _dims(m):
         assert m.dim() == 2 and m.shape[0] == 3

@@ -286,8 +286,15 @@ def test_reference_unit_test_goldens_on_device(ctx):
     assert r == pytest.approx(g6["head_expected"], rel=1e-13)
     assert r / g6["V"] == pytest.approx(g6["file_expected"], rel=1e-13)   # the file's stale "/ Vcell" literal
     g9 = g["G9_integrate_exp"]
-    assert ctx.eval_integrate_exp(1.0, g9["lower"])[0] == pytest.approx(g9["expected"], abs=1e-7)  # GSL epsabs
-    assert ctx.eval_integrate_exp(1.0, 2.0)[0] == pytest.approx(math.exp(-2.0), abs=1e-7)
+    # the reference's own assertion: ASSERT_DOUBLE_EQ(integrate(exp(-x), 0), 1.0), i.e. 4 ulp
+    # (tests/unit_tests/integration.cpp:6-13); GSL's request is only epsabs 1e-7 (Integrator.H:21-22)
+    got = ctx.eval_integrate_exp(1.0, g9["lower"])[0]
+    assert abs(got - g9["expected"]) <= 4 * np.spacing(g9["expected"]), got - g9["expected"]
+    # the family exp(-rate x) from other lower limits: closed form exp(-rate lower) / rate
+    rate = np.array([1.0, 0.5, 3.0, 10.0, 1.0, 2.0])
+    lower = np.array([2.0, 0.0, 0.25, 0.0, 10.0, 1.5])
+    got = ctx.eval_integrate_exp(rate, lower)
+    assert np.allclose(got, np.exp(-rate * lower) / rate, rtol=1e-13, atol=0.0), got * rate / np.exp(-rate * lower) - 1
     assert list(ctx.eval_daughter_beta([1.0, 4.0, 5.0], 4.0)) == [0.5, 0.5, 0.0]   # pos(0) = 1
     assert list(ctx.eval_daughter_moment([3.0, 3.0, 0.0], [2, 0, 0])) == [6.0, 2.0, 2.0]
 

@@ -206,3 +206,37 @@ def test_device_empty_input_and_errors(ctx):
     with pytest.raises(capi.PbeError, match="NULL field pointer"):
         capi.check(capi.lib().pbe_mom_source(mom._h, 8, 8, m.data_ptr(), None, None, None, m.data_ptr(), None, None))
     mom.close()
+
+
+@pytest.mark.gpu
+def test_device_coverage_diagnostic_and_wider_range(ctx):
+    """the rule is fixed where QAGIU adapts, so every call checks that it gives back the
+    density's own m0 and m1.  (a) Shapes k in (0.3, 1) -- the integrable singularity at x = 0 the
+    graded panels exist for -- and mean volumes from 1e-3 to 30 are covered and meet the closed forms;
+    (b) densities at SI drop volumes (1e-10) or far beyond the last panel are COUNTED, not silently
+    integrated wrong."""
+    from openpbe_b200 import engine
+    rng = np.random.default_rng(17)
+    nc = 600
+    m0 = rng.uniform(0.5, 3.0, nc)
+    k = np.concatenate([rng.uniform(0.3, 1.0, nc // 2), rng.uniform(1.0, 6.0, nc - nc // 2)])
+    mean = 10.0 ** rng.uniform(-3.0, np.log10(30.0), nc)  # k theta
+    theta = mean / k
+    m = np.stack([m0, m0 * k * theta, m0 * k * (k + 1) * theta ** 2])
+    one = np.ones(nc)
+    mom = engine.MOM(ctx, dev_spec("const_binary"))
+    mom.coverage(reset=True)
+    S = mom.source(T(m), T(one), T(one), T(one)).cpu().numpy()
+    bad, worst = mom.coverage()
+    assert bad == 0, (bad, worst)
+    want = np.stack([np.sum(mo.closed_form_constant_binary(m[:, c], 0.1), axis=0) for c in range(nc)], axis=1)
+    assert np.all(np.abs(S - want) <= 1e-7 * scale(want)), np.max(np.abs(S - want) / scale(want))
+    # (b) out of range: SI volumes and a mean volume of 1e5
+    for mean_bad in (1e-10, 1e5):
+        kb = np.full(50, 2.5)
+        mb = np.stack([np.ones(50), kb * (mean_bad / kb), kb * (kb + 1) * (mean_bad / kb) ** 2])
+        mom.source(T(mb), T(np.ones(50)), T(np.ones(50)), T(np.ones(50)))
+        bad, worst = mom.coverage()
+        assert bad == 50 and worst > 1e-3, (mean_bad, bad, worst)
+    assert mom.coverage() == (0, 0.0)  # reset
+    mom.close()
