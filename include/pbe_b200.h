@@ -170,17 +170,21 @@ int pbe_qmom_source_host(pbe_qmom *q, int64_t ncells, int64_t stride, const doub
 /* presumed gamma density with k = m1^2 / (m2 m0 - m1^2 + SMALL), theta = (m0 m2 - m1^2) /   */
 /* max(m0 m1, SMALL) (MOM.C:151-161).  integrate() (Integrator.H:12-27, GSL QAGIU) becomes a */
 /* fixed-depth 15-point Gauss-Kronrod rule on the same x = lower + (1-t)/t transform with    */
-/* `panels` equal panels of (0,1] (0 = default), the one at the lower limit bisected         */
-/* PBE_MOM_GRADED_LEVELS times.  The implicit fvm::ddt + fvm::div solve of   */
+/* `panels` equal panels of (0,1] (0 = default), the end ones graded towards x = 0 and       */
+/* x = inf (the macros below).  The implicit fvm::ddt + fvm::div solve of                    */
 /* MOM.C:211-222 is out of scope (zero-flux update only).  Parity unpinned in the reference. */
 /* ======================================================================================= */
 typedef struct pbe_mom pbe_mom;
 #define PBE_MOM_DEFAULT_PANELS 12
 #define PBE_MOM_MAX_PANELS 28
-#define PBE_MOM_GRADED_LEVELS 20 /* bisections of the panel next to the lower limit */
-/* The rule is FIXED where QAGIU adapts: it resolves densities whose mass lies between x ~ 1e-7 and
- * x ~ panels (mean volumes of O(1), the scales of the reference's own 0-D cases,
- * tests/integration/MOC/setupCases.py:41-54; validated for shapes k in (0.3, 4], tests/test_mom.py).
+#define PBE_MOM_GRADED_LEVELS 15 /* bisections of the panel next to the lower limit (x -> 0) */
+#define PBE_MOM_TAIL_LEVELS 5    /* bisections of the panel next to t = 0 (x -> inf) */
+#define PBE_MOM_ORIGIN_POWER 8   /* u = a s^8 on the panel that touches x = 0 (density ~ x^(k-1)) */
+#define PBE_MOM_EXTRA_PANELS (PBE_MOM_GRADED_LEVELS + PBE_MOM_TAIL_LEVELS) /* nodes = 15 (panels + this) */
+/* The rule is FIXED where QAGIU adapts.  With the default 12 panels it gives back m0 and m1 of a gamma
+ * density to better than 1e-6 for mean volumes m1/m0 between 1e-5 and 30 and shapes k between 0.3 and
+ * 20 (the reference's own 0-D cases have mean volumes of O(1): tests/integration/MOC/setupCases.py:41-54;
+ * map and closed-form checks in tests/test_mom.py).
  * Every call checks, per cell, that the rule gives back the density's own m0 and m1; cells off by more
  * than this relative tolerance are counted (pbe_mom_coverage) instead of being integrated silently
  * wrong -- rescale the volume unit of such a case (the kernels are homogeneous in xi). */

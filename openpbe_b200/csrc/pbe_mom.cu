@@ -6,8 +6,8 @@
 // The reference evaluates every integral with integrate() = GSL QAGIU (Integrator.H:12-27:
 // x = lower + (1-t)/t on t in (0,1], adaptive 15-point Gauss-Kronrod, epsabs 1e-7).  The device
 // version keeps the transform and the 15-point rule on a FIXED set of panels (`panels` equal
-// panels of (0,1], the one next to t = 1 bisected PBE_MOM_GRADED_LEVELS times towards the lower
-// limit, where the gamma density is x^(k-1)): with a fixed rule the kernel evaluations
+// panels of (0,1], the two end ones graded towards the lower limit, where the gamma density is
+// x^(k-1), and towards infinity: mom_node below): with a fixed rule the kernel evaluations
 // are shared by the three moment indices and by the birth and death integrals, so a cell
 // costs (15 panels)^2 / 2 coalescence-kernel evaluations instead of 6 nested adaptive runs.  Parity is UNPINNED in the reference (no MOM test exists; Boost.Math / GSL absent
 // here): the tests compare against nested adaptive QUADPACK QAGI integrals in the reference's
@@ -89,26 +89,47 @@ struct GammaPdf {
     }
 };
 
-// node q of the rule: panels in u = 1 - t: [h, 1) in P - 1 equal panels, [0, h) bisected
-// PBE_MOM_GRADED_LEVELS times towards u = 0 (x = 0), where the gamma density behaves like
-// x^(k-1) -- the panels an adaptive QAGIU run ends up with for non-integer shapes
+// node q of the rule, panels in u = 1 - t (x = u / (1 - u)):
+//   [h, 1 - h)   P - 2 equal panels;
+//   [1 - h, 1)   bisected PBE_MOM_TAIL_LEVELS times towards u = 1 (x -> inf), the refinement QAGIU
+//                makes for densities whose mass sits beyond x = P - 1;
+//   [a, h)       bisected PBE_MOM_GRADED_LEVELS times towards u = 0, a = h 2^-GRADED;
+//   [0, a)       one panel under u = a s^PBE_MOM_ORIGIN_POWER: the gamma density is x^(k-1) there, and
+//                s^(8k-1) is smooth enough for the 15-point rule down to k = 0.3 where plain bisection
+//                converges like a^k (the panels an adaptive run keeps splitting for shapes below 1).
 __device__ __forceinline__ void mom_node(int P, int q, double &x, double &w) {
     const double h = 1.0 / P;
     const int panel = q / 15, j = q - 15 * panel;
-    double lo, hi;
-    if (panel < P - 1) {
-        lo = (panel + 1) * h;
-        hi = (panel + 2) * h;
+    const int n_eq = P - 2, n_tail = PBE_MOM_TAIL_LEVELS + 1;
+    double u, wu;
+    if (panel == P + PBE_MOM_GRADED_LEVELS + PBE_MOM_TAIL_LEVELS - 1) {
+        const double a = ldexp(h, -PBE_MOM_GRADED_LEVELS);
+        const double s = 0.5 + 0.5 * GK15_X[j];
+        double sp = s; // s^(POWER-1)
+        for (int i = 2; i < PBE_MOM_ORIGIN_POWER; ++i) sp *= s;
+        u = a * sp * s;
+        wu = 0.5 * GK15_W[j] * a * PBE_MOM_ORIGIN_POWER * sp;
     } else {
-        const int l = panel - (P - 1);
-        hi = ldexp(h, -l);
-        lo = (l < PBE_MOM_GRADED_LEVELS) ? ldexp(h, -(l + 1)) : 0.0;
+        double lo, hi;
+        if (panel < n_eq) {
+            lo = (panel + 1) * h;
+            hi = (panel + 2) * h;
+        } else if (panel < n_eq + n_tail) {
+            const int l = panel - n_eq;
+            lo = 1.0 - ldexp(h, -l);
+            hi = (l < PBE_MOM_TAIL_LEVELS) ? 1.0 - ldexp(h, -(l + 1)) : 1.0;
+        } else {
+            const int l = panel - n_eq - n_tail;
+            hi = ldexp(h, -l);
+            lo = ldexp(h, -(l + 1));
+        }
+        const double uc = 0.5 * (lo + hi), uh = 0.5 * (hi - lo);
+        u = uc + uh * GK15_X[j];
+        wu = GK15_W[j] * uh;
     }
-    const double uc = 0.5 * (lo + hi), uh = 0.5 * (hi - lo);
-    const double u = uc + uh * GK15_X[j];
     const double t = 1.0 - u;
     x = u / t;
-    w = GK15_W[j] * uh / (t * t);
+    w = wu / (t * t);
 }
 
 // The CT coalescence kernel factorises into per-cell and per-pair parts, S = A_c G_ab
@@ -135,7 +156,7 @@ __global__ void mom_pair_table_kernel(int P, int nq, double *__restrict__ tab) {
 template <int NC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, NC == 1 ? 6 : 3) mom_kernel(MomParams p) {
     extern __shared__ double sh[];
-    const int P = p.panels, npan = P + PBE_MOM_GRADED_LEVELS;
+    const int P = p.panels, npan = P + PBE_MOM_EXTRA_PANELS;
     const int nq = 15 * npan;
     double *xq = sh;            // node position x = u / (1 - u), u = 1 - t (lower limit 0)
     double *wq = xq + nq;       // Kronrod weight * panel half-width / t^2
@@ -326,7 +347,7 @@ int launch_mom(pbe_mom *h, MomParams &p, cudaStream_t st) {
     p.ks = h->ks;
     p.pair_tab = h->pair_tab;
     p.cov = h->d_cov;
-    const int nq = 15 * (h->panels + PBE_MOM_GRADED_LEVELS);
+    const int nq = 15 * (h->panels + PBE_MOM_EXTRA_PANELS);
     // CT coalescence (pair table): two cells per warp share every table load; the cell-independent
     // kernels have nothing to share and run one cell per warp (measured: 13.8 vs 85 ms per 4e5 cells)
     const int NC = h->pair_tab ? 2 : 1;
@@ -353,8 +374,8 @@ int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mo
     PBE_REQUIRE(ctx && spec && out, PBE_E_INVALID, "pbe_mom_create: NULL argument");
     *out = nullptr;
     if (panels == 0) panels = PBE_MOM_DEFAULT_PANELS;
-    PBE_REQUIRE(panels >= 1 && panels <= PBE_MOM_MAX_PANELS, PBE_E_UNSUPPORTED,
-                "pbe_mom_create: panels must be in [1,%d] (got %d)", PBE_MOM_MAX_PANELS, panels);
+    PBE_REQUIRE(panels >= 2 && panels <= PBE_MOM_MAX_PANELS, PBE_E_UNSUPPORTED,
+                "pbe_mom_create: panels must be in [2,%d] (got %d)", PBE_MOM_MAX_PANELS, panels);
     PBE_REQUIRE(spec->coalescence >= PBE_COAL_NONE && spec->coalescence <= PBE_COAL_CT,
                 spec->coalescence == PBE_COAL_TABLE ? PBE_E_UNSUPPORTED : PBE_E_UNKNOWN_TYPE,
                 "pbe_mom_create: coalescenceKernel id %d is not available for methodOfMoments",
@@ -370,7 +391,7 @@ int pbe_mom_create(pbe_ctx *ctx, int panels, const pbe_kernel_spec *spec, pbe_mo
     h->panels = panels;
     h->ks = make_dev_spec(*spec);
     DeviceGuard g(ctx->device);
-    const int nq = 15 * (panels + PBE_MOM_GRADED_LEVELS);
+    const int nq = 15 * (panels + PBE_MOM_EXTRA_PANELS);
     // 12 rows of nq doubles per CTA (4 node tables + 2 cells x 4 warps): above 48 KB from 33 panels on
     cudaError_t e = raise_dyn_smem(ctx, (const void *)mom_kernel<2>, (4 + 2 * kWarpsPerCta) * nq * sizeof(double));
     if (e == cudaSuccess)

@@ -98,25 +98,35 @@ def mom_source_cell(spec, m, eps, rho, nu):
     return out
 
 
-GRADED_LEVELS = 20  # PBE_MOM_GRADED_LEVELS
+GRADED_LEVELS = 15  # PBE_MOM_GRADED_LEVELS
+TAIL_LEVELS = 5     # PBE_MOM_TAIL_LEVELS
+ORIGIN_POWER = 8    # PBE_MOM_ORIGIN_POWER
 
 
 def fixed_rule(panels):
     """Nodes x = u/(1-u) and weights w/(1-u)^2 (u = 1 - t) of the device kernel's rule
-    (openpbe_b200/csrc/pbe_mom.cu): the 15-point rule on [h, 1) in panels - 1 equal panels
-    (h = 1/panels) and on [0, h) bisected GRADED_LEVELS times towards u = 0."""
+    (openpbe_b200/csrc/pbe_mom.cu mom_node): the 15-point rule on [h, 1-h) in panels - 2 equal
+    panels (h = 1/panels), on [1-h, 1) bisected TAIL_LEVELS times towards u = 1, on [a, h) bisected
+    GRADED_LEVELS times towards u = 0 (a = h 2^-GRADED_LEVELS), and on [0, a) under u = a s^ORIGIN_POWER."""
     h = 1.0 / panels
-    lo = [(j + 1) * h for j in range(panels - 1)]
-    hi = [(j + 2) * h for j in range(panels - 1)]
-    for l in range(GRADED_LEVELS + 1):
+    lo = [(j + 1) * h for j in range(panels - 2)]
+    hi = [(j + 2) * h for j in range(panels - 2)]
+    for l in range(TAIL_LEVELS + 1):
+        lo.append(1.0 - math.ldexp(h, -l))
+        hi.append(1.0 - math.ldexp(h, -(l + 1)) if l < TAIL_LEVELS else 1.0)
+    for l in range(GRADED_LEVELS):
         hi.append(math.ldexp(h, -l))
-        lo.append(math.ldexp(h, -(l + 1)) if l < GRADED_LEVELS else 0.0)
+        lo.append(math.ldexp(h, -(l + 1)))
     lo, hi = np.array(lo), np.array(hi)
     uc, uh = 0.5 * (lo + hi), 0.5 * (hi - lo)
     u = (uc[:, None] + uh[:, None] * GK15_X[None, :]).ravel()
+    wu = (GK15_W[None, :] * uh[:, None]).ravel()
+    a = math.ldexp(h, -GRADED_LEVELS)
+    s = 0.5 + 0.5 * GK15_X
+    u = np.concatenate([u, a * s ** ORIGIN_POWER])
+    wu = np.concatenate([wu, 0.5 * GK15_W * a * ORIGIN_POWER * s ** (ORIGIN_POWER - 1)])
     t = 1.0 - u
-    w = (GK15_W[None, :] * uh[:, None]).ravel() / (t * t)
-    return u / t, w
+    return u / t, wu / (t * t)
 
 
 def mom_source_cell_fixed(spec, m, eps, rho, nu, panels=12):

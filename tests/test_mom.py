@@ -211,16 +211,16 @@ def test_device_empty_input_and_errors(ctx):
 @pytest.mark.gpu
 def test_device_coverage_diagnostic_and_wider_range(ctx):
     """the rule is fixed where QAGIU adapts, so every call checks that it gives back the
-    density's own m0 and m1.  (a) Shapes k in (0.3, 1) -- the integrable singularity at x = 0 the
-    graded panels exist for -- and mean volumes from 1e-3 to 30 are covered and meet the closed forms;
-    (b) densities at SI drop volumes (1e-10) or far beyond the last panel are COUNTED, not silently
-    integrated wrong."""
+    density's own m0 and m1.  (a) Shapes k in (0.3, 20) -- below 1 the integrable singularity at
+    x = 0 the origin panel exists for -- and mean volumes from 1e-5 to 30 are covered and meet the closed
+    forms (which involve m4); (b) densities at SI drop volumes (1e-10) or far beyond the last panel are
+    COUNTED, not silently integrated wrong."""
     from openpbe_b200 import engine
     rng = np.random.default_rng(17)
     nc = 600
     m0 = rng.uniform(0.5, 3.0, nc)
-    k = np.concatenate([rng.uniform(0.3, 1.0, nc // 2), rng.uniform(1.0, 6.0, nc - nc // 2)])
-    mean = 10.0 ** rng.uniform(-3.0, np.log10(30.0), nc)  # k theta
+    k = np.concatenate([rng.uniform(0.3, 1.0, nc // 2), rng.uniform(1.0, 20.0, nc - nc // 2)])
+    mean = 10.0 ** rng.uniform(-5.0, np.log10(30.0), nc)  # k theta
     theta = mean / k
     m = np.stack([m0, m0 * k * theta, m0 * k * (k + 1) * theta ** 2])
     one = np.ones(nc)
@@ -232,7 +232,7 @@ def test_device_coverage_diagnostic_and_wider_range(ctx):
     want = np.stack([np.sum(mo.closed_form_constant_binary(m[:, c], 0.1), axis=0) for c in range(nc)], axis=1)
     assert np.all(np.abs(S - want) <= 1e-7 * scale(want)), np.max(np.abs(S - want) / scale(want))
     # (b) out of range: SI volumes and a mean volume of 1e5
-    for mean_bad in (1e-10, 1e5):
+    for mean_bad in (1e-10, 1e6):
         kb = np.full(50, 2.5)
         mb = np.stack([np.ones(50), kb * (mean_bad / kb), kb * (kb + 1) * (mean_bad / kb) ** 2])
         mom.source(T(mb), T(np.ones(50)), T(np.ones(50)), T(np.ones(50)))
@@ -240,3 +240,20 @@ def test_device_coverage_diagnostic_and_wider_range(ctx):
         assert bad == 50 and worst > 1e-3, (mean_bad, bad, worst)
     assert mom.coverage() == (0, 0.0)  # reset
     mom.close()
+
+
+def test_fixed_rule_coverage_map():
+    """The validated range include/pbe_b200.h states for the default rule: m0 and m1 of a gamma density
+    come back to 1e-6 for mean volumes in [1e-5, 30] and shapes in [0.3, 20]; outside (SI volumes) the
+    deviation is large, which is what pbe_mom_coverage counts."""
+    x, w = mo.fixed_rule(12)
+    assert x.size == 15 * (12 + mo.GRADED_LEVELS + mo.TAIL_LEVELS) and np.all(np.diff(np.sort(x)) > 0)
+
+    def dev(k, mean):
+        f = w * mo.gamma_pdf(k, mean / k, x)
+        return max(abs(f.sum() - 1.0), abs((f * x).sum() / mean - 1.0))
+
+    for k in (0.3, 0.5, 0.9, 1.0, 1.5, 3.0, 6.0, 20.0):
+        for mean in (1e-5, 1e-4, 1e-2, 1.0, 10.0, 30.0):
+            assert dev(k, mean) < 1e-6, (k, mean, dev(k, mean))
+    assert dev(2.5, 1e-10) > 1e-2 and dev(2.5, 1e6) > 1e-2
