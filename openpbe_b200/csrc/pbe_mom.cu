@@ -192,8 +192,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, NC == 1 ? 6 : 3) mom_kernel
             gtheta[i] = (m0[i] * m2[i] - m1[i] * m1[i]) / fmax(m0[i] * m1[i], kSmall);
             const GammaPdf pdf(gk[i], gtheta[i]);
             cc[i] = cell_coef(p.ks, p.eps[c], p.rho[c], p.nu[c]);
-            // coverage of the presumed density by the FIXED rule: sum_q f_q must give back m0 and
-            // sum_q f_q x_q m1.  QAGIU would refine where this rule cannot (mass beyond the last
+            // coverage of the presumed density by the FIXED rule: sum_q f_q must give back the density's
+            // own zeroth and first moments, m0 and m0 k theta (= m1 up to the SMALL of MOM.C:154).  QAGIU would refine where this rule cannot (mass beyond the last
             // equal panel, or below the last graded one): such cells are counted, not silently wrong.
             double cv0 = 0.0, cv1 = 0.0;
             for (int q = lane; q < nq; q += 32) {
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, NC == 1 ? 6 : 3) mom_kernel
                 cv1 += __shfl_xor_sync(0xffffffffu, cv1, o);
             }
             if (lane == 0 && cb + i < p.ncells && p.cov != nullptr) {
-                const double dev = fmax(fabs(cv0 / m0[i] - 1.0), fabs(cv1 / m1[i] - 1.0));
+                const double dev = fmax(fabs(cv0 / m0[i] - 1.0), fabs(cv1 / (m0[i] * gk[i] * gtheta[i]) - 1.0));
                 if (dev > PBE_MOM_COVERAGE_TOL) { // NaN (invalid gamma parameters) compares false: scrubbed as in the reference
                     atomicAdd(p.cov, 1ull);
                     atomicMax(p.cov + 1, (unsigned long long)__double_as_longlong(dev));

@@ -230,7 +230,8 @@ def test_device_coverage_diagnostic_and_wider_range(ctx):
     bad, worst = mom.coverage()
     assert bad == 0, (bad, worst)
     want = np.stack([np.sum(mo.closed_form_constant_binary(m[:, c], 0.1), axis=0) for c in range(nc)], axis=1)
-    assert np.all(np.abs(S - want) <= 1e-7 * scale(want)), np.max(np.abs(S - want) / scale(want))
+    # m4 of the k = 0.3, mean 30 corner is the least resolved (4e-7): the documented 1e-6
+    assert np.all(np.abs(S - want) <= 1e-6 * scale(want)), np.max(np.abs(S - want) / scale(want))
     # (b) out of range: SI volumes and a mean volume of 1e5
     for mean_bad in (1e-10, 1e6):
         kb = np.full(50, 2.5)
