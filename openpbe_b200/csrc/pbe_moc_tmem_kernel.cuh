@@ -37,6 +37,17 @@ constexpr int MOCT_SUB_TILES = 12;    // ring slot = at most 12 tiles (3072 B) o
 // 16 entries 22.80 ms, 32 entries 21.96 ms, 128 entries 21.08 ms -- the two FP64 instructions the
 // shorter polynomial saves per pair outweigh the bank conflicts of the 1 KB table.
 constexpr int MOCT_LOGT = PBE_MOCT_LOGT;
+#ifndef PBE_MOCT_BIASED_TAB
+#define PBE_MOCT_BIASED_TAB 1
+#endif
+// 2^y through the table staged in shared memory (pbe_math.cuh)
+__device__ __forceinline__ double moct_exp2(double y, const double *T) {
+#if PBE_MOCT_BIASED_TAB
+    return exp2_neg_tabb<MOCT_LOGT>(y, T);
+#else
+    return exp2_neg_tab<MOCT_LOGT>(y, T);
+#endif
+}
 constexpr int MOCT_MAX_SUBS = 2 * MOC_MAX_BLOCKS;
 
 
@@ -177,7 +188,7 @@ __device__ __forceinline__ void moct_tile(const double2 *__restrict__ tab, doubl
             const double2 gh = tab[r * MOC_TJ + c];
             const double w = ni[r] * nj[C0 + c];
             if (COAL == DCOAL_CT) {
-                const double eg = exp2_neg_tab<MOCT_LOGT>(fma_(K2, gh.y, gh.x), T16);
+                const double eg = moct_exp2(fma_(K2, gh.y, gh.x), T16);
                 di[r] = fma_(eg, w, di[r]);
                 dj[C0 + c] = fma_(eg, w, dj[C0 + c]);
                 bw[r + C0 + c] = fma_(eg, w, bw[r + C0 + c]);
@@ -228,7 +239,11 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
     }
     for (int k = tid; k < CLS_ROWS * (N + 1); k += BLOCK) cls_s[k] = p.cls[k];
     n_s[N * BLOCK + tid] = 0.0; // dummy class: absorbs padded table slots
+#if PBE_MOCT_BIASED_TAB
+    if (tid < (1 << MOCT_LOGT)) T16[tid] = exp2_tab_bias(PBE_EXP2_TAB128[tid << (7 - MOCT_LOGT)], tid, MOCT_LOGT);
+#else
     if (tid < (1 << MOCT_LOGT)) T16[tid] = PBE_EXP2_TAB128[tid << (7 - MOCT_LOGT)];
+#endif
     tmem_fence_before_sync();
     __syncthreads();
     tmem_fence_after_sync();
@@ -444,7 +459,10 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
 #pragma unroll
                         for (int w = 0; w < NB2; ++w) bw[w] = (w + MOC_TJ < NB2) ? bw[w + MOC_TJ] : 0.0;
                     }
-                    __syncthreads(); // every warp is done with ring slot q&1
+                    // every warp is done with ring slot q&1.  (Measured: releasing the slot per warp through
+                    // an "empty" mbarrier instead -- no CTA-wide barrier, warps free to drift by one
+                    // sub-chunk -- is 6 % SLOWER, 57.9 vs 54.4 ms at 1.6e7 cells.)
+                    __syncthreads();
                     if (tid == 0 && q + 2 < total_q) issue(q + 2);
                 }
                 // flush the TI-1 anti-diagonals still in the window and the row sums (death of
@@ -504,7 +522,7 @@ __global__ void __launch_bounds__(MOCT_BLOCK, WIDE ? 2 : 3)
                 const double ni = n_s[ii * BLOCK + tid];
                 // breakupCache_ (MOC.C:165-171): CT = Ab xi^(-2/9) exp(-Kb xi^(-5/9))
                 double g = cBP[ii];
-                if (BR == DBR_CT) g = (Ab * g) * exp2_neg_tab<MOCT_LOGT>(Kb2 * cBQ[ii], T16);
+                if (BR == DBR_CT) g = (Ab * g) * moct_exp2(Kb2 * cBQ[ii], T16);
                 const double gn = g * ni;
                 const double B = R - gn; // -g_i n_i + sum_{j>i} beta g_j n_j dxi (MOC.C:142-155)
                 R = fma_(cW[ii], gn, R);
