@@ -227,9 +227,10 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
 int pbe_mesh_destroy(pbe_mesh *mesh);
 int pbe_mesh_info(pbe_mesh *mesh, int64_t *ncells, int64_t *n_internal_faces,
                   int64_t *n_boundary_faces, int *max_faces_per_cell);
-/* How the device tables split the cells: "regular" cells (no boundary face, exactly
- * *faces_per_regular_cell internal faces -- the mesh's most common count among 4, 5, 6) go through
- * the register-resident kernel, all others through the general one. */
+/* How the device tables split the cells: "regular" cells (exactly *faces_per_regular_cell faces,
+ * internal or on a physical patch -- the mesh's most common count among 4, 5, 6 -- and none on a
+ * processor patch) go through the register-resident kernel, all others through the general one.
+ * pbe_mesh_set_coupled re-splits: cells on processor patches need halo values and leave the set. */
 int pbe_mesh_regular_cells(pbe_mesh *mesh, int *faces_per_regular_cell, int64_t *n_regular);
 
 /* fvSchemes divSchemes entry "div(phi,n.*)" -> enum ("Gauss upwind" | "upwind" | "Gauss vanLeer" |
@@ -315,7 +316,7 @@ int pbe_transport_explicit_halo(pbe_mesh *mesh, int scheme, int nfields, int64_t
                                 int64_t stride_b, const double *psi_halo, int64_t stride_h,
                                 const double *S, double dt, double *psi_out, void *cuda_stream);
 /* The same update restricted to one of the two cell sets of pbe_mesh_regular_cells, so that the
- * halo exchange overlaps the bulk of the work: launch PBE_CELLS_REGULAR (interior cells: they read
+ * halo exchange overlaps the bulk of the work: launch PBE_CELLS_REGULAR (they read
  * no halo value, psi_halo may be NULL) while the exchange is in flight, then PBE_CELLS_IRREGULAR
  * (boundary and processor-patch cells) once psi_halo has arrived.  Both together = PBE_CELLS_ALL. */
 enum { PBE_CELLS_ALL = 0, PBE_CELLS_REGULAR = 1, PBE_CELLS_IRREGULAR = 2 };

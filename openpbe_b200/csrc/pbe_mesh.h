@@ -2,6 +2,8 @@
 // pbe_mules.cu (MULES-limited update): OpenFOAM face addressing turned into cell-centred tables.
 #pragma once
 
+#include <vector>
+
 #include "pbe_common.h"
 
 struct pbe_mesh {
@@ -9,8 +11,10 @@ struct pbe_mesh {
     int64_t ncells = 0, nint = 0, nbnd = 0, nirr = 0;
     int maxf = 0; // most faces on any cell (info)
     int F = 0;    // face count of the regular cells (0: none)
-    int32_t *d_other = nullptr; // [F][ncells]: neighbour cell; row 0 holds -1 for irregular cells
-    int32_t *d_face = nullptr;  // [F][ncells]: face index f (this cell owns it) or ~f (it is the neighbour)
+    int32_t *d_other = nullptr; // [F][ncells]: neighbour cell, or -(b + 2) for boundary face b; row 0 holds -1 for irregular cells
+    int32_t *d_face = nullptr;  // [F][ncells]: face index f (this cell owns it), ~f (it is the neighbour), nint + b (boundary)
+    // host copies of the face addressing: pbe_mesh_set_coupled re-splits the cells
+    std::vector<int32_t> h_owner, h_neigh, h_bown;
     double *d_vcell = nullptr;  // [ncells]
     // irregular cells, CSR: entries of cell irr_cell[i] are irr_ptr[i] .. irr_ptr[i+1]-1
     int32_t *d_irr_cell = nullptr, *d_irr_ptr = nullptr;

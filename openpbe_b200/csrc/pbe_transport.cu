@@ -12,13 +12,17 @@
 // into cell-centred tables whose entries are in ascending face order per cell -- the order
 // fvc::surfaceIntegrate's face loops add them in -- so per-cell sums are bit-identical to a face
 // loop.  Cells are split in two sets:
-//   * regular cells: no boundary face and exactly F internal faces (F = the mesh's most common
-//     count: 6 for hexahedra, 4 for tetrahedra, 5 for prisms).  ELL table [F][ncells], cell
+//   * regular cells: exactly F faces (F = the mesh's most common count: 6 for hexahedra, 4 for
+//     tetrahedra, 5 for prisms), none of them on a processor patch.  ELL table [F][ncells], cell
 //     fastest; one thread per cell keeps its F (neighbour, signed flux, lambda) triples in
 //     registers and sweeps a chunk of fields with F + 2 loads, 4 F + 9 FP64 instructions and no
-//     branch per field.
-//   * everything else (boundary cells, other face counts): a compact CSR list, one thread per
-//     listed cell, any number of faces, patch values from psi_b.
+//     branch per field.  A boundary face is a slot like any other whose value comes from the
+//     patch row psi_b (or from the cell itself: zero gradient); warps without such a slot -- the
+//     bulk -- run a loop that does not know about them.  (Until r02 boundary cells went to the
+//     list below: scattered 8-byte reads of 32-byte sectors, 1.9 GB of DRAM reads for 0.24 GB of
+//     cell data and 0.55 of the 3.3 ms of a 160^3 x 100 update.)
+//   * everything else (other face counts, processor-patch cells): a compact CSR list, one thread
+//     per listed cell, any number of faces.
 // HBM-bound: 24 B per cell-field (psi and S in, psi out); neighbour gathers are L1 / L2 hits.
 #include <algorithm>
 #include <cstdlib>
@@ -107,24 +111,57 @@ __device__ __forceinline__ double updated(const TransportParams &p, double mine,
     return res;
 }
 
+// The F faces of an ELL cell, decoded once per thread.  A boundary face b is a slot whose value is the
+// patch value psi_b[k][b] (bit s of `patch` set: read from the patch rows) or, without patch values,
+// the cell's own (zero gradient); its flux term is phi_b * value as it stands (bit s of `bnd`),
+// fvc::surfaceIntegrate's boundary loop.
 template <int F>
-__global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(TransportParams p) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x; // 32-bit labels (pbe_mesh_create checks)
-    if (c >= p.ncells) return;
-    int oth[F];
-    oth[0] = __ldg(p.other + c);
-    if (oth[0] < 0) return; // irregular cell: transport_upwind_irregular_kernel
+struct CellFaces {
+    int idx[F];
     Side sd[F];
+    unsigned bnd, patch;
+};
+
+template <int F>
+__device__ __forceinline__ bool load_cell_faces(const TransportParams &p, int c, CellFaces<F> &cf) {
+    cf.idx[0] = __ldg(p.other + c);
+    if (cf.idx[0] == -1) return false; // irregular cell: transport_upwind_irregular_kernel
+    cf.bnd = cf.patch = 0u;
 #pragma unroll
     for (int s = 0; s < F; ++s) {
-        if (s > 0) oth[s] = __ldg(p.other + (size_t)s * p.ncells + c);
-        sd[s] = make_side(__ldg(p.face + (size_t)s * p.ncells + c), p.phi);
+        if (s > 0) cf.idx[s] = __ldg(p.other + (size_t)s * p.ncells + c);
+        cf.sd[s] = make_side(__ldg(p.face + (size_t)s * p.ncells + c), p.phi); // boundary: face = nint + b >= 0
+        if (cf.idx[s] < 0) {
+            cf.bnd |= 1u << s;
+            if (p.psi_b != nullptr) {
+                cf.patch |= 1u << s;
+                cf.idx[s] = -cf.idx[s] - 2;
+            } else {
+                cf.idx[s] = c;
+            }
+        }
     }
-    const double V = __ldg(p.vcell + c);
-    const double rV = __ddiv_rn(1.0, V);
+    return true;
+}
+
+template <int F, bool BND>
+__device__ __forceinline__ const double *slot_addr(const CellFaces<F> &cf, int s, const double *row,
+                                                   const double *brow) {
+    return (BND && ((cf.patch >> s) & 1u)) ? brow + cf.idx[s] : row + cf.idx[s];
+}
+template <int F, bool BND>
+__device__ __forceinline__ double add_slot(double acc, const CellFaces<F> &cf, int s, double mine, double theirs) {
+    if (BND && ((cf.bnd >> s) & 1u)) return __dadd_rn(acc, __dmul_rn(cf.sd[s].phs, theirs));
+    return add_internal(acc, cf.sd[s], mine, theirs);
+}
+
+template <int F, bool BND>
+__device__ __forceinline__ void sweep_regs(const TransportParams &p, int c, const CellFaces<F> &cf, double V,
+                                           double rV) {
     const int k0 = blockIdx.y * p.chunk;
     const int k1 = min(p.nfields, k0 + p.chunk);
     const double *row = p.psi + (size_t)k0 * p.stride;
+    const double *brow = BND ? p.psi_b + (size_t)k0 * p.stride_b : nullptr; // only dereferenced for patch slots
     const double *srow = (p.S != nullptr) ? p.S + (size_t)k0 * p.stride : nullptr;
     double *orow = p.out + (size_t)k0 * p.stride;
 #pragma unroll 2
@@ -132,7 +169,7 @@ __global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(Tran
         const double mine = __ldg(row + c);
         double th[F];
 #pragma unroll
-        for (int s = 0; s < F; ++s) th[s] = __ldg(row + oth[s]);
+        for (int s = 0; s < F; ++s) th[s] = __ldg(slot_addr<F, BND>(cf, s, row, brow));
         double Su = 0.0;
         if (srow != nullptr) {
             Su = __ldg(srow + c);
@@ -140,9 +177,25 @@ __global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(Tran
         }
         double acc = 0.0;
 #pragma unroll
-        for (int s = 0; s < F; ++s) acc = add_internal(acc, sd[s], mine, th[s]);
+        for (int s = 0; s < F; ++s) acc = add_slot<F, BND>(acc, cf, s, mine, th[s]);
         __stcs(orow + c, updated(p, mine, Su, acc, V, rV));
+        if (BND) brow += p.stride_b;
     }
+}
+
+template <int F>
+__global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(TransportParams p) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x; // 32-bit labels (pbe_mesh_create checks)
+    if (c >= p.ncells) return;
+    CellFaces<F> cf;
+    if (!load_cell_faces<F>(p, c, cf)) return;
+    const double V = __ldg(p.vcell + c);
+    const double rV = __ddiv_rn(1.0, V);
+    // warps with a boundary slot (the cells next to a patch) take the loop that knows about them
+    if (__any_sync(__activemask(), cf.bnd != 0u))
+        sweep_regs<F, true>(p, c, cf, V, rV);
+    else
+        sweep_regs<F, false>(p, c, cf, V, rV);
 }
 
 // The same sweep with the loads of the next PBE_TR_STAGES-1 fields in flight as asynchronous
@@ -151,26 +204,13 @@ __global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(Tran
 // shared between threads, so no barrier is needed; the copies hold no registers while they are in
 // flight, which is what the register-staged loop above runs out of (ncu: 7.2 of 13.5 stall cycles
 // per issue are long-scoreboard waits).
-template <int F, int D>
-__global__ void __launch_bounds__(256) transport_upwind_async_kernel(TransportParams p) {
-    extern __shared__ double tr_sm[]; // [D][F + 2][256]
-    const int tid = threadIdx.x;
-    const int c = blockIdx.x * blockDim.x + tid;
-    if (c >= p.ncells) return;
-    int oth[F];
-    oth[0] = __ldg(p.other + c);
-    if (oth[0] < 0) return; // irregular cell
-    Side sd[F];
-#pragma unroll
-    for (int s = 0; s < F; ++s) {
-        if (s > 0) oth[s] = __ldg(p.other + (size_t)s * p.ncells + c);
-        sd[s] = make_side(__ldg(p.face + (size_t)s * p.ncells + c), p.phi);
-    }
-    const double V = __ldg(p.vcell + c);
-    const double rV = __ddiv_rn(1.0, V);
+template <int F, int D, bool BND>
+__device__ __forceinline__ void sweep_async(const TransportParams &p, int c, int tid, const CellFaces<F> &cf,
+                                            double V, double rV, double *tr_sm) {
     const int k0 = blockIdx.y * p.chunk;
     const int nk = min(p.nfields, k0 + p.chunk) - k0;
     const double *row = p.psi + (size_t)k0 * p.stride;       // row of the field being ISSUED
+    const double *brow = BND ? p.psi_b + (size_t)k0 * p.stride_b : nullptr;
     const double *srow = (p.S != nullptr) ? p.S + (size_t)k0 * p.stride : nullptr;
     double *orow = p.out + (size_t)k0 * p.stride;
     const uint32_t sm0 = (uint32_t)__cvta_generic_to_shared(tr_sm + tid);
@@ -183,12 +223,13 @@ __global__ void __launch_bounds__(256) transport_upwind_async_kernel(TransportPa
             const uint32_t d = sm0 + (uint32_t)(k % D) * kStageBytes;
             cp8(d, row + c);
 #pragma unroll
-            for (int s = 0; s < F; ++s) cp8(d + (uint32_t)(1 + s) * 256u * 8u, row + oth[s]);
+            for (int s = 0; s < F; ++s) cp8(d + (uint32_t)(1 + s) * 256u * 8u, slot_addr<F, BND>(cf, s, row, brow));
             if (srow != nullptr) {
                 cp8(d + (uint32_t)(F + 1) * 256u * 8u, srow + c);
                 srow += p.stride;
             }
             row += p.stride;
+            if (BND) brow += p.stride_b;
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -201,13 +242,29 @@ __global__ void __launch_bounds__(256) transport_upwind_async_kernel(TransportPa
         const double mine = st[0];
         double acc = 0.0;
 #pragma unroll
-        for (int s = 0; s < F; ++s) acc = add_internal(acc, sd[s], mine, st[(1 + s) * 256]);
+        for (int s = 0; s < F; ++s) acc = add_slot<F, BND>(acc, cf, s, mine, st[(1 + s) * 256]);
         const double Su = (p.S != nullptr) ? st[(F + 1) * 256] : 0.0;
         __stcs(orow + c, updated(p, mine, Su, acc, V, rV));
     }
 }
 
-// boundary cells and cells with another face count: one thread per listed cell.  Up to kIrrRegs
+template <int F, int D>
+__global__ void __launch_bounds__(256) transport_upwind_async_kernel(TransportParams p) {
+    extern __shared__ double tr_sm[]; // [D][F + 2][256]
+    const int tid = threadIdx.x;
+    const int c = blockIdx.x * blockDim.x + tid;
+    if (c >= p.ncells) return;
+    CellFaces<F> cf;
+    if (!load_cell_faces<F>(p, c, cf)) return;
+    const double V = __ldg(p.vcell + c);
+    const double rV = __ddiv_rn(1.0, V);
+    if (__any_sync(__activemask(), cf.bnd != 0u))
+        sweep_async<F, D, true>(p, c, tid, cf, V, rV, tr_sm);
+    else
+        sweep_async<F, D, false>(p, c, tid, cf, V, rV, tr_sm);
+}
+
+// cells with another face count and cells on processor patches: one thread per listed cell.  Up to kIrrRegs
 // faces are decoded once into registers (like the regular cells'), so a field costs independent
 // loads only; cells with more faces re-read their list per field.
 constexpr int kIrrRegs = 8;
@@ -343,6 +400,85 @@ int pbe_div_scheme_type(const char *name, int *out) {
     return PBE_E_UNKNOWN_TYPE;
 }
 
+// Splits the cells into the ELL set (exactly F faces, none coupled) and the CSR list of the rest, and
+// (re)builds the device tables of both; pbe_mesh_set_coupled calls it again, because which boundary
+// faces are processor patches is only known then.
+static int mesh_split_cells(pbe_mesh *m) {
+    const int64_t ncells = m->ncells, nint = m->nint, nbnd = m->nbnd;
+    const int32_t *owner = m->h_owner.data(), *neighbour = m->h_neigh.data(), *bown = m->h_bown.data();
+    std::vector<int32_t> cnt((size_t)ncells, 0), bcnt((size_t)ncells, 0);
+    std::vector<char> coupled((size_t)ncells, 0);
+    for (int64_t f = 0; f < nint; ++f) {
+        cnt[owner[f]]++;
+        cnt[neighbour[f]]++;
+    }
+    for (int64_t b = 0; b < nbnd; ++b) {
+        bcnt[bown[b]]++;
+        if (b >= m->coupled0 && b < m->coupled0 + m->ncoupled) coupled[bown[b]] = 1;
+    }
+    // F: the most common face count among the cells the ELL kernel can take, if a kernel exists for it
+    int64_t hist[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int64_t c = 0; c < ncells; ++c) {
+        const int t = cnt[c] + bcnt[c];
+        if (!coupled[c] && t >= 4 && t <= 6) hist[t]++;
+    }
+    int F = 0;
+    for (int f = 4; f <= 6; ++f)
+        if (hist[f] > 0 && (F == 0 || hist[f] > hist[F])) F = f;
+    auto regular = [&](int64_t c) { return F > 0 && !coupled[c] && cnt[c] + bcnt[c] == F; };
+    // irregular cells -> CSR
+    std::vector<int32_t> irr_cell, irr_ptr(1, 0), slot_of((size_t)ncells, -1);
+    for (int64_t c = 0; c < ncells; ++c)
+        if (!regular(c)) {
+            slot_of[c] = (int32_t)irr_cell.size();
+            irr_cell.push_back((int32_t)c);
+            irr_ptr.push_back(irr_ptr.back() + cnt[c] + bcnt[c]);
+        }
+    std::vector<int32_t> irr_other((size_t)irr_ptr.back()), irr_face((size_t)irr_ptr.back());
+    const int Fa = std::max(F, 1);
+    std::vector<int32_t> other((size_t)Fa * ncells, -1), face((size_t)Fa * ncells, 0), fill((size_t)ncells, 0);
+    // ascending face order per cell = the order of fvc::surfaceIntegrate's face loops (internal
+    // faces, then the patches' faces)
+    auto put = [&](int32_t c, int32_t oth, int32_t fc) {
+        const int32_t k = fill[c]++;
+        if (slot_of[c] < 0) {
+            other[(size_t)k * ncells + c] = oth;
+            face[(size_t)k * ncells + c] = fc;
+        } else {
+            irr_other[(size_t)irr_ptr[slot_of[c]] + k] = oth;
+            irr_face[(size_t)irr_ptr[slot_of[c]] + k] = fc;
+        }
+    };
+    for (int64_t f = 0; f < nint; ++f) {
+        put(owner[f], neighbour[f], (int32_t)f);
+        put(neighbour[f], owner[f], ~(int32_t)f);
+    }
+    for (int64_t b = 0; b < nbnd; ++b) put(bown[b], -(int32_t)b - 2, (int32_t)(nint + b));
+    for (int64_t c = 0; c < ncells; ++c)
+        if (slot_of[c] >= 0) other[c] = -1; // row 0: "not an ELL cell"
+
+    DeviceGuard g(m->ctx->device);
+    cudaError_t e = cudaDeviceSynchronize(); // a re-split must not pull tables from under a running kernel
+    auto upload = [&](int32_t **dst, const std::vector<int32_t> &v) {
+        if (e != cudaSuccess) return;
+        cudaFree(*dst);
+        *dst = nullptr;
+        e = cudaMalloc((void **)dst, std::max<size_t>(v.size(), 1) * sizeof(int32_t));
+        if (e == cudaSuccess && !v.empty())
+            e = cudaMemcpy(*dst, v.data(), v.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    };
+    upload(&m->d_other, other);
+    upload(&m->d_face, face);
+    upload(&m->d_irr_cell, irr_cell);
+    upload(&m->d_irr_ptr, irr_ptr);
+    upload(&m->d_irr_other, irr_other);
+    upload(&m->d_irr_face, irr_face);
+    if (e != cudaSuccess) return cuda_fail(e, "pbe_mesh: cell tables", __FILE__, __LINE__);
+    m->nirr = (int64_t)irr_cell.size();
+    m->F = F;
+    return PBE_OK;
+}
+
 int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, const int32_t *owner,
                     const int32_t *neighbour, int64_t n_boundary_faces,
                     const int32_t *boundary_owner, const double *vcell, pbe_mesh **out) {
@@ -356,62 +492,26 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     PBE_REQUIRE(vcell != nullptr && (n_internal_faces == 0 || (owner && neighbour)) &&
                     (n_boundary_faces == 0 || boundary_owner),
                 PBE_E_INVALID, "pbe_mesh_create: NULL array");
-    std::vector<int32_t> cnt((size_t)ncells, 0), bcnt((size_t)ncells, 0);
     for (int64_t f = 0; f < n_internal_faces; ++f) {
         const int32_t o = owner[f], n = neighbour[f];
         PBE_REQUIRE(o >= 0 && o < ncells && n >= 0 && n < ncells && o != n, PBE_E_INVALID,
                     "pbe_mesh_create: internal face %lld has owner %d, neighbour %d (ncells %lld)",
                     (long long)f, o, n, (long long)ncells);
-        cnt[o]++;
-        cnt[n]++;
     }
     for (int64_t b = 0; b < n_boundary_faces; ++b) {
         const int32_t o = boundary_owner[b];
         PBE_REQUIRE(o >= 0 && o < ncells, PBE_E_INVALID,
                     "pbe_mesh_create: boundary face %lld has owner %d (ncells %lld)", (long long)b, o,
                     (long long)ncells);
-        bcnt[o]++;
     }
-    // F: the most common face count among cells without boundary faces, if a kernel exists for it
-    int maxf = 0;
-    int64_t hist[7] = {0, 0, 0, 0, 0, 0, 0};
-    for (int64_t c = 0; c < ncells; ++c) {
-        maxf = std::max(maxf, (int)(cnt[c] + bcnt[c]));
-        if (bcnt[c] == 0 && cnt[c] >= 4 && cnt[c] <= 6) hist[cnt[c]]++;
-    }
-    int F = 0;
-    for (int f = 4; f <= 6; ++f)
-        if (hist[f] > 0 && (F == 0 || hist[f] > hist[F])) F = f;
-    auto regular = [&](int64_t c) { return F > 0 && bcnt[c] == 0 && cnt[c] == F; };
-    // irregular cells -> CSR
-    std::vector<int32_t> irr_cell, irr_ptr(1, 0), slot_of((size_t)ncells, -1);
-    for (int64_t c = 0; c < ncells; ++c)
-        if (!regular(c)) {
-            slot_of[c] = (int32_t)irr_cell.size();
-            irr_cell.push_back((int32_t)c);
-            irr_ptr.push_back(irr_ptr.back() + cnt[c] + bcnt[c]);
-        }
-    const int64_t nirr = (int64_t)irr_cell.size();
-    std::vector<int32_t> irr_other((size_t)irr_ptr.back()), irr_face((size_t)irr_ptr.back());
-    const int Fa = std::max(F, 1);
-    std::vector<int32_t> other((size_t)Fa * ncells, -1), face((size_t)Fa * ncells, 0), fill((size_t)ncells, 0);
-    // ascending face order per cell = the order of fvc::surfaceIntegrate's face loops
-    auto put = [&](int32_t c, int32_t oth, int32_t fc) {
-        const int32_t k = fill[c]++;
-        if (slot_of[c] < 0) {
-            other[(size_t)k * ncells + c] = oth;
-            face[(size_t)k * ncells + c] = fc;
-        } else {
-            irr_other[(size_t)irr_ptr[slot_of[c]] + k] = oth;
-            irr_face[(size_t)irr_ptr[slot_of[c]] + k] = fc;
-        }
-    };
+    std::vector<int32_t> cnt((size_t)ncells, 0), bcnt((size_t)ncells, 0);
     for (int64_t f = 0; f < n_internal_faces; ++f) {
-        put(owner[f], neighbour[f], (int32_t)f);
-        put(neighbour[f], owner[f], ~(int32_t)f);
+        cnt[owner[f]]++;
+        cnt[neighbour[f]]++;
     }
-    for (int64_t b = 0; b < n_boundary_faces; ++b)
-        put(boundary_owner[b], -(int32_t)b - 2, (int32_t)(n_internal_faces + b));
+    for (int64_t b = 0; b < n_boundary_faces; ++b) bcnt[boundary_owner[b]]++;
+    int maxf = 0;
+    for (int64_t c = 0; c < ncells; ++c) maxf = std::max(maxf, (int)(cnt[c] + bcnt[c]));
 
     // one CSR over ALL cells, ascending face order per cell (internal faces, then boundary faces): the
     // MULES kernels (pbe_mules.cu) walk it; entries as in the irregular-cell list
@@ -429,8 +529,6 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     }
     for (int64_t b = 0; b < n_boundary_faces; ++b)
         cput(boundary_owner[b], -(int32_t)b - 2, (int32_t)(n_internal_faces + b));
-    std::vector<int32_t> own_v(owner, owner + n_internal_faces), nei_v(neighbour, neighbour + n_internal_faces),
-        bown_v(boundary_owner, boundary_owner + n_boundary_faces);
 
     pbe_mesh *m = new (std::nothrow) pbe_mesh;
     PBE_REQUIRE(m != nullptr, PBE_E_NOMEM, "pbe_mesh_create: out of host memory");
@@ -438,9 +536,10 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     m->ncells = ncells;
     m->nint = n_internal_faces;
     m->nbnd = n_boundary_faces;
-    m->nirr = nirr;
     m->maxf = maxf;
-    m->F = F;
+    m->h_owner.assign(owner, owner + n_internal_faces);
+    m->h_neigh.assign(neighbour, neighbour + n_internal_faces);
+    m->h_bown.assign(boundary_owner, boundary_owner + n_boundary_faces);
     DeviceGuard g(ctx->device);
     cudaError_t e = cudaSuccess;
     auto upload = [&](auto **dst, const auto &v) {
@@ -449,18 +548,12 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
         e = cudaMalloc((void **)dst, bytes);
         if (e == cudaSuccess && !v.empty()) e = cudaMemcpy(*dst, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
     };
-    upload(&m->d_other, other);
-    upload(&m->d_face, face);
-    upload(&m->d_irr_cell, irr_cell);
-    upload(&m->d_irr_ptr, irr_ptr);
-    upload(&m->d_irr_other, irr_other);
-    upload(&m->d_irr_face, irr_face);
     upload(&m->d_csr_ptr, csr_ptr);
     upload(&m->d_csr_other, csr_other);
     upload(&m->d_csr_face, csr_face);
-    upload(&m->d_owner, own_v);
-    upload(&m->d_neigh, nei_v);
-    upload(&m->d_bown, bown_v);
+    upload(&m->d_owner, m->h_owner);
+    upload(&m->d_neigh, m->h_neigh);
+    upload(&m->d_bown, m->h_bown);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming);
@@ -470,6 +563,11 @@ int pbe_mesh_create(pbe_ctx *ctx, int64_t ncells, int64_t n_internal_faces, cons
     if (e != cudaSuccess) {
         pbe_mesh_destroy(m);
         return cuda_fail(e, "pbe_mesh_create: device tables", __FILE__, __LINE__);
+    }
+    const int rc = mesh_split_cells(m);
+    if (rc != PBE_OK) {
+        pbe_mesh_destroy(m);
+        return rc;
     }
     *out = m;
     return PBE_OK;
@@ -525,9 +623,10 @@ int pbe_mesh_set_coupled(pbe_mesh *m, int64_t first_boundary_face, int64_t count
     PBE_REQUIRE(first_boundary_face >= 0 && count >= 0 && first_boundary_face + count <= m->nbnd,
                 PBE_E_INVALID, "pbe_mesh_set_coupled: faces [%lld, %lld) outside the %lld boundary faces",
                 (long long)first_boundary_face, (long long)(first_boundary_face + count), (long long)m->nbnd);
+    if (m->coupled0 == first_boundary_face && m->ncoupled == count) return PBE_OK;
     m->coupled0 = first_boundary_face;
     m->ncoupled = count;
-    return PBE_OK;
+    return mesh_split_cells(m); // cells on processor patches leave the ELL set
 }
 
 int pbe_gather_cells(pbe_ctx *ctx, int nfields, int64_t stride, const double *psi, int64_t n,
