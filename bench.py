@@ -975,6 +975,30 @@ def leg_transport(B: Bench, w, moc):
                  "roofline": {"bound": "hbm", "achieved": tgbs, "peak": B.hbm_peak, "unit": "GB/s",
                               "frac": tgbs / B.hbm_peak, "algorithmic_bytes": tbytes, "traffic": traffic,
                               "traffic_source": f"committed constant ({tsrc}), not measured by this run"}}
+    if world == 1 and "Sf" in tm:
+        # the limited path of MOC::solveWithMULES (MOC.C:198-272): Gauss vanLeer face values, MULES limiter
+        # (3 sweeps), limitSum over the fields, explicitSolve -- the same fields, mesh and time step
+        tmesh.set_geometry(tm["Sf"], tm["C"], tm["weights"])
+        pmax = torch.full((tK,), 2.0, dtype=torch.float64, device=dev)
+        for _ in range(2):
+            tmesh.transport_mules(tpsi, tphi, tdt, pmax, S=tS, out=tout)
+        l0 = ctx.launch_count()
+        B.e0.record()
+        for _ in range(3):
+            tmesh.transport_mules(tpsi, tphi, tdt, pmax, S=tS, out=tout)
+        B.e1.record()
+        torch.cuda.synchronize()
+        mms = B.e0.elapsed_time(B.e1) / 3
+        transport["mules"] = {
+            "metric": "transport_cell_field_updates_per_s", "value": tc * tK / (mms * 1e-3),
+            "unit": "cell-field-updates/s", "ms_per_step": mms, "scheme": "Gauss vanLeer, nLimiterIter 3",
+            "launches_per_step": int((ctx.launch_count() - l0) // 3),
+            "roofline": {"bound": "hbm", "achieved": tbytes / (mms * 1e-3) / 1e9, "peak": B.hbm_peak, "unit": "GB/s",
+                         "frac": tbytes / (mms * 1e-3) / 1e9 / B.hbm_peak, "algorithmic_bytes": tbytes,
+                         "note": "same algorithmic bytes as the upwind update (psi and S in, psi out): the gradient, "
+                                 "correction-flux, limiter-sweep and limitSum passes in between are what the "
+                                 "fraction pays for", "traffic": None}}
+        del pmax
     if not args.no_e2e and world == 1:
         # MOC::correct() with solveWithMULES through the resident state: class fields stay on the device,
         # pinned host eps, rho, nu, alpha, phi in, d out
@@ -1035,6 +1059,8 @@ def run_b200(args):
     if not args.no_transport:
         transport = leg_transport(B, w, main["moc"])
         roofline["legs"]["transport"] = transport["roofline"]
+        if "mules" in transport:
+            roofline["legs"]["transport_mules"] = transport["mules"]["roofline"]
 
     # ---- CPU baselines on this box's host cores (rank 0, N = 1 only) -----------------------------
     cpu = None

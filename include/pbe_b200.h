@@ -95,7 +95,7 @@ int pbe_moc_destroy(pbe_moc *moc);
  * shared memory holds) and the tensor-memory kernel (accumulators in TMEM, 256 cells per CTA;
  * N <= 118).  pbe_moc_create picks by occupancy; these calls let tests and benches pin one.
  * Environment variable PBE_MOC_KERNEL=smem|tmem overrides the automatic choice at create. */
-enum { PBE_MOC_KERNEL_SMEM = 1, PBE_MOC_KERNEL_TMEM = 2 };
+enum { PBE_MOC_KERNEL_SMEM = 1, PBE_MOC_KERNEL_TMEM = 2, PBE_MOC_KERNEL_PIVOT = 3 /* fixed-pivot grids only */ };
 int pbe_moc_set_kernel(pbe_moc *moc, int which); /* PBE_E_UNSUPPORTED if not available */
 int pbe_moc_get_kernel(pbe_moc *moc, int *which, int *cells_per_cta, int *ctas_per_sm);
 
@@ -288,6 +288,20 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
 int pbe_moc_num_classes(pbe_moc *moc, int *N, pbe_ctx **ctx);
 /* MOCCoeffs of the handle: xi1 (MOC.C:56) and sourceRelaxation (MOC.C:60); either may be NULL */
 int pbe_moc_coeffs(pbe_moc *moc, double *xi1, double *source_relaxation);
+
+/* ---- geometric / arbitrary class grid (EXTENSION, parity unpinned) ------------------
+ * The reference's MOC only has xi_i = (i + 1) xi1 (MOC.C:56,79); its comment at MOC.C:147-148 names Kumar
+ * & Ramkrishna (1996), whose fixed-pivot technique this is, in the reference's conventions: a pair (i, j)
+ * with x_i + x_j <= x_{N-1} (death bound of MOC.C:107-109) dies in both classes and is born on the two
+ * pivots that bracket x_i + x_j with the number- and volume-preserving weights; breakup daughters
+ * (uniformBinaryBreakup) are assigned through the same hat functions (volume exact).  On the uniform
+ * volumes the coalescence terms are the reference's own.  pivots [N], strictly increasing, positive.
+ * The handle works with pbe_moc_source / _step / _d / _class_minmax / _source_host; the resident state
+ * and the MULES bound (which use xi1) take uniform grids only (PBE_E_UNSUPPORTED otherwise). */
+int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_kernel_spec *spec,
+                          double source_relaxation, pbe_moc **out);
+/* class volumes of the handle's grid ([N], may be NULL) and whether it is the reference's uniform one */
+int pbe_moc_grid(pbe_moc *moc, double *volumes, int *is_uniform);
 int pbe_moc_correct_host(pbe_moc *moc, pbe_mesh *mesh, int scheme, int64_t stride, double *n_host,
                          const double *eps_host, const double *rho_host, const double *nu_host,
                          const double *phi_host, const double *psi_b_host, int64_t stride_b,

@@ -18,7 +18,7 @@ COAL_NONE, COAL_CONSTANT, COAL_CT, COAL_TABLE = 0, 1, 2, 3
 BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
 DAUGHTER_UNIFORM_BINARY = 0
 QMOM_MAX_ORDER = 4
-MOC_KERNEL_SMEM, MOC_KERNEL_TMEM = 1, 2
+MOC_KERNEL_SMEM, MOC_KERNEL_TMEM, MOC_KERNEL_PIVOT = 1, 2, 3
 DIV_UPWIND, DIV_VANLEER = 0, 1
 CELLS_ALL, CELLS_REGULAR, CELLS_IRREGULAR = 0, 1, 2
 
@@ -94,6 +94,8 @@ PROTOTYPES = {
     "pbe_measure_fp64_peak": (C.c_int, [_vp, _dp, _dp]),
     "pbe_moc_create": (C.c_int, [_vp, C.c_int, C.c_double, C.POINTER(KernelSpec), C.c_double,
                                  C.POINTER(_vp)]),
+    "pbe_moc_create_pivots": (C.c_int, [_vp, C.c_int, _dp, C.POINTER(KernelSpec), C.c_double, C.POINTER(_vp)]),
+    "pbe_moc_grid": (C.c_int, [_vp, _dp, C.POINTER(C.c_int)]),
     "pbe_moc_destroy": (C.c_int, [_vp]),
     "pbe_moc_set_kernel": (C.c_int, [_vp, C.c_int]),
     "pbe_moc_get_kernel": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

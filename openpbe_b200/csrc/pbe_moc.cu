@@ -10,6 +10,7 @@
 
 #include "pbe_common.h"
 #include "pbe_moc_kernel.cuh"
+#include "pbe_moc_pivot_kernel.cuh"
 #include "pbe_moc_tmem_kernel.cuh"
 
 using namespace pbe;
@@ -37,6 +38,12 @@ struct pbe_moc {
     double2 *d_pair = nullptr;
     double2 *d_pair_log = nullptr; // CT, tensor-memory kernel: {log2 G_ij, H_ij}
     double *d_cls = nullptr;
+    // fixed-pivot grid (pbe_moc_create_pivots): arbitrary class volumes, pbe_moc_pivot_kernel.cuh
+    bool pivot = false;
+    std::vector<double> pivots;
+    FpPair *d_fp = nullptr;
+    double *d_fpw = nullptr; // [3][N]: hat areas, self shares, 2 / x_k
+    MocFpExtra fpx{};
 };
 
 namespace {
@@ -72,6 +79,20 @@ moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr, bool wide) {
     PBE_PICK(DCOAL_SYM, DBR_CT)
     PBE_PICK(DCOAL_ASYM, DBR_TAB)
     PBE_PICK(DCOAL_ASYM, DBR_CT)
+#undef PBE_PICK
+    return nullptr;
+}
+
+typedef void (*mocp_kernel_fn)(const MocParams, const MocFpExtra);
+mocp_kernel_fn pick_pivot_kernel(int dcoal, int dbr) {
+#define PBE_PICK(C, B) \
+    if (dcoal == C && dbr == B) return (mocp_kernel_fn)moc_pivot_kernel<C, B>;
+    PBE_PICK(DCOAL_OFF, DBR_TAB)
+    PBE_PICK(DCOAL_OFF, DBR_CT)
+    PBE_PICK(DCOAL_CT, DBR_TAB)
+    PBE_PICK(DCOAL_CT, DBR_CT)
+    PBE_PICK(DCOAL_SYM, DBR_TAB)
+    PBE_PICK(DCOAL_SYM, DBR_CT)
 #undef PBE_PICK
     return nullptr;
 }
@@ -177,6 +198,14 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int64_t nb = (p.ncells + m->block - 1) / m->block;
     const int64_t cap = (int64_t)m->ctx->sm_count * m->ctas_per_sm;
     const int grid = (int)std::min<int64_t>(nb, cap);
+    if (m->pivot) {
+        mocp_kernel_fn fn = pick_pivot_kernel(m->dcoal, m->dbr);
+        void *args[] = {(void *)&p, (void *)&m->fpx};
+        PBE_CUDA(raise_dyn_smem(m->ctx, (const void *)fn, m->smem));
+        PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
+        m->ctx->launches++;
+        return PBE_OK;
+    }
     if (m->use_tmem) {
         moct_kernel_fn fn = pick_tmem_kernel(m->dcoal, m->dbr, m->tmem_wide);
         if (m->dcoal == DCOAL_CT) p.pair_tab = m->d_pair_log;
@@ -489,6 +518,8 @@ int pbe_moc_set_kernel(pbe_moc *m, int which) {
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_set_kernel: NULL handle");
     PBE_REQUIRE(which == PBE_MOC_KERNEL_SMEM || which == PBE_MOC_KERNEL_TMEM, PBE_E_INVALID,
                 "pbe_moc_set_kernel: unknown kernel id %d", which);
+    PBE_REQUIRE(!m->pivot, PBE_E_UNSUPPORTED,
+                "pbe_moc_set_kernel: a fixed-pivot grid (pbe_moc_create_pivots) has one kernel");
     PBE_REQUIRE(which != PBE_MOC_KERNEL_TMEM || m->tmem_ok, PBE_E_UNSUPPORTED,
                 "pbe_moc_set_kernel: the tensor-memory kernel is not available for numberOfClasses %d "
                 "(needs N <= %d, n[N+1][256] in shared memory and an H table spanning < 1e6)",
@@ -497,9 +528,161 @@ int pbe_moc_set_kernel(pbe_moc *m, int which) {
     return PBE_OK;
 }
 
+// Fixed-pivot method of classes on the class volumes pivots[0] < ... < pivots[N-1] (SURVEY 8 row f4;
+// pbe_moc_pivot_kernel.cuh).  Parity unpinned: the reference has no such grid.
+int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_kernel_spec *spec,
+                          double source_relaxation, pbe_moc **out) {
+    PBE_REQUIRE(ctx && spec && out && pivots, PBE_E_INVALID, "pbe_moc_create_pivots: NULL argument");
+    *out = nullptr;
+    PBE_REQUIRE(N >= 1, PBE_E_INVALID, "pbe_moc_create_pivots: numberOfClasses must be >= 1 (got %d)", N);
+    PBE_REQUIRE(pivots[0] > 0.0, PBE_E_INVALID, "pbe_moc_create_pivots: class volumes must be positive (got %g)",
+                pivots[0]);
+    for (int i = 1; i < N; ++i)
+        PBE_REQUIRE(pivots[i] > pivots[i - 1] && std::isfinite(pivots[i]), PBE_E_INVALID,
+                    "pbe_moc_create_pivots: class volumes must increase (pivot %d = %g after %g)", i, pivots[i],
+                    pivots[i - 1]);
+    PBE_REQUIRE(spec->coalescence >= PBE_COAL_NONE && spec->coalescence <= PBE_COAL_TABLE, PBE_E_UNKNOWN_TYPE,
+                "pbe_moc_create_pivots: unknown coalescenceKernel id %d", spec->coalescence);
+    PBE_REQUIRE(spec->breakup >= PBE_BR_NONE && spec->breakup <= PBE_BR_TABLE, PBE_E_UNKNOWN_TYPE,
+                "pbe_moc_create_pivots: unknown breakupKernel id %d", spec->breakup);
+    PBE_REQUIRE(spec->daughter == PBE_DAUGHTER_UNIFORM_BINARY, PBE_E_UNKNOWN_TYPE,
+                "pbe_moc_create_pivots: unknown daughterParticleDistribution id %d", spec->daughter);
+    PBE_REQUIRE(spec->coalescence != PBE_COAL_TABLE || spec->coal_table, PBE_E_INVALID,
+                "pbe_moc_create_pivots: PBE_COAL_TABLE needs coal_table");
+    PBE_REQUIRE(spec->breakup != PBE_BR_TABLE || spec->br_table, PBE_E_INVALID,
+                "pbe_moc_create_pivots: PBE_BR_TABLE needs br_table");
+    if (spec->coalescence == PBE_COAL_TABLE)
+        for (int i = 0; i < N; ++i)
+            for (int j = 0; j < i; ++j)
+                PBE_REQUIRE(spec->coal_table[(size_t)i * N + j] == spec->coal_table[(size_t)j * N + i],
+                            PBE_E_UNSUPPORTED, "pbe_moc_create_pivots: the tabulated coalescence kernel must be symmetric");
+    const size_t smem = mocp_smem_bytes(N);
+    PBE_REQUIRE(smem <= ctx->smem_optin, PBE_E_UNSUPPORTED,
+                "pbe_moc_create_pivots: numberOfClasses %d needs %zu B of shared memory per CTA, device offers %zu", N,
+                smem, ctx->smem_optin);
+    DeviceGuard g(ctx->device);
+    pbe_moc *m = new pbe_moc();
+    m->ctx = ctx;
+    m->N = N;
+    m->xi1 = pivots[0];
+    m->relax = source_relaxation;
+    m->spec = *spec;
+    m->spec.coal_table = nullptr;
+    m->spec.br_table = nullptr;
+    m->pivot = true;
+    m->pivots.assign(pivots, pivots + N);
+    const std::vector<double> &xi = m->pivots;
+    switch (spec->coalescence) {
+    case PBE_COAL_NONE: m->dcoal = DCOAL_OFF; break;
+    case PBE_COAL_CT: m->dcoal = DCOAL_CT; break;
+    default: m->dcoal = DCOAL_SYM; break;
+    }
+    m->dbr = (spec->breakup == PBE_BR_CT) ? DBR_CT : DBR_TAB;
+
+    // pairs that stay on the grid (the death bound of MOC.C:107-109), i-major; the new drop goes to the
+    // pivots that bracket it with the number- and volume-preserving weights
+    std::vector<FpPair> pairs;
+    if (m->dcoal != DCOAL_OFF)
+        for (int i = 0; i < N; ++i)
+            for (int j = i; j < N; ++j) {
+                // a sum within a few ulp of a pivot is ON that pivot (so that volumes (i + 1) xi1 that are not
+                // exact in binary still reproduce the reference's i + j + 1 rule and death bound)
+                const double snap = 8.0 * 2.220446049250313e-16;
+                const double v = xi[i] + xi[j], vt = v * (1.0 + snap);
+                if (v > xi[N - 1] * (1.0 + snap)) break;
+                FpPair pr{};
+                pr.i = i;
+                pr.j = j;
+                pr.t = std::min(N - 1, (int)(std::upper_bound(xi.begin(), xi.end(), vt) - xi.begin()) - 1);
+                pr.eta = (pr.t == N - 1) ? 1.0
+                                         : std::min(1.0, std::max(0.0, (xi[pr.t + 1] - v) / (xi[pr.t + 1] - xi[pr.t])));
+                switch (spec->coalescence) {
+                case PBE_COAL_CONSTANT: pr.a = spec->coal_c[0]; break;
+                case PBE_COAL_CT: ct_pair_geometry(xi[i], xi[j], &pr.a, &pr.b); break;
+                case PBE_COAL_TABLE: pr.a = spec->coal_table[(size_t)i * N + j]; break;
+                }
+                if (i == j) pr.a *= 0.5; // MOC.C:118
+                pairs.push_back(pr);
+            }
+    if (pairs.empty()) m->dcoal = DCOAL_OFF;
+
+    MocParams &b = m->base;
+    b.N = N;
+    b.nblocks = 0;
+    b.chunk_max_pairs = 1;
+    std::vector<double> cls((size_t)CLS_ROWS * (N + 1), 0.0), fpw((size_t)3 * N, 0.0);
+    for (int i = 0; i < N; ++i) {
+        double P = 0.0, Q = 0.0;
+        switch (spec->breakup) {
+        case PBE_BR_BINARY: P = xi[i] * xi[i]; break;
+        case PBE_BR_CT:
+            P = 1.0 / pow(xi[i], 2.0 / 9.0);
+            Q = 1.0 / pow(xi[i], 5.0 / 9.0);
+            break;
+        case PBE_BR_TABLE: P = spec->br_table[i]; break;
+        default: break;
+        }
+        cls[(size_t)CLS_BR_P * (N + 1) + i] = P;
+        cls[(size_t)CLS_BR_Q * (N + 1) + i] = Q;
+        cls[(size_t)CLS_DVOL * (N + 1) + i] = pow(6.0 / M_PI * xi[i], 1.0 / 3.0);
+        cls[(size_t)CLS_XI * (N + 1) + i] = xi[i];
+        const double xm = (i > 0) ? xi[i - 1] : 0.0, xp = (i + 1 < N) ? xi[i + 1] : xi[i];
+        fpw[i] = 0.5 * (xp - xm);
+        fpw[(size_t)N + i] = (xi[i] - xm) / xi[i];
+        fpw[(size_t)2 * N + i] = 2.0 / xi[i];
+    }
+    {
+        const double c1 = spec->coal_c[0], c2 = spec->coal_c[1], gm = spec->coal_c[2], sg = spec->coal_c[3];
+        b.coalA = c1 / (1 + gm);
+        b.coalK = c2 / (sg * sg * ((1 + gm) * (1 + gm) * (1 + gm)));
+    }
+    {
+        const double c1 = spec->br_c[0], c2 = spec->br_c[1], gm = spec->br_c[2], sg = spec->br_c[3];
+        b.brA = c1 / (1 + gm);
+        b.brK = c2 * sg * ((1 + gm) * (1 + gm));
+    }
+    b.negK_floor = b.negKb_floor = -INFINITY;
+    m->block = m->smem_block = MOCP_BLOCK;
+    m->smem = m->smem_bytes = smem;
+    const void *fn = (const void *)pick_pivot_kernel(m->dcoal, m->dbr);
+    cudaError_t e = raise_dyn_smem(ctx, fn, smem);
+    if (e == cudaSuccess) {
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, MOCP_BLOCK, smem);
+        m->ctas_per_sm = m->smem_ctas_per_sm = std::max(1, occ);
+    }
+    if (e == cudaSuccess && !pairs.empty()) {
+        e = cudaMalloc(&m->d_fp, pairs.size() * sizeof(FpPair));
+        if (e == cudaSuccess) e = cudaMemcpy(m->d_fp, pairs.data(), pairs.size() * sizeof(FpPair), cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&m->d_fpw, fpw.size() * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemcpy(m->d_fpw, fpw.data(), fpw.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc(&m->d_cls, cls.size() * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemcpy(m->d_cls, cls.data(), cls.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        int rc = cuda_fail(e, "pbe_moc_create_pivots device setup", __FILE__, __LINE__);
+        pbe_moc_destroy(m);
+        return rc;
+    }
+    b.pair_tab = nullptr;
+    b.cls = m->d_cls;
+    m->fpx = MocFpExtra{m->d_fp, (int)pairs.size(), m->d_fpw, m->d_fpw + N, m->d_fpw + 2 * N};
+    *out = m;
+    return PBE_OK;
+}
+
+// class volumes of the handle's grid: (i + 1) xi1 or the pivots it was created with
+int pbe_moc_grid(pbe_moc *m, double *volumes, int *is_uniform) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_grid: NULL handle");
+    if (volumes)
+        for (int i = 0; i < m->N; ++i) volumes[i] = m->pivot ? m->pivots[i] : m->xi1 * (i + 1);
+    if (is_uniform) *is_uniform = m->pivot ? 0 : 1;
+    return PBE_OK;
+}
+
 int pbe_moc_get_kernel(pbe_moc *m, int *which, int *cells_per_cta, int *ctas_per_sm) {
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_get_kernel: NULL handle");
-    if (which) *which = m->use_tmem ? PBE_MOC_KERNEL_TMEM : PBE_MOC_KERNEL_SMEM;
+    if (which) *which = m->pivot ? PBE_MOC_KERNEL_PIVOT : (m->use_tmem ? PBE_MOC_KERNEL_TMEM : PBE_MOC_KERNEL_SMEM);
     if (cells_per_cta) *cells_per_cta = m->block;
     if (ctas_per_sm) *ctas_per_sm = m->ctas_per_sm;
     return PBE_OK;
@@ -525,6 +708,8 @@ int pbe_moc_destroy(pbe_moc *m) {
     if (m->d_pair) cudaFree(m->d_pair);
     if (m->d_pair_log) cudaFree(m->d_pair_log);
     if (m->d_cls) cudaFree(m->d_cls);
+    if (m->d_fp) cudaFree(m->d_fp);
+    if (m->d_fpw) cudaFree(m->d_fpw);
     delete m;
     return PBE_OK;
 }

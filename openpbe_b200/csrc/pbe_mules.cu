@@ -428,6 +428,9 @@ int pbe_moc_psi_max(pbe_moc *moc, int64_t ncells, const double *alpha, const dou
     int N = 0;
     pbe_ctx *ctx = nullptr;
     double xi1 = 0.0;
+    int uniform = 1;
+    if (moc != nullptr) pbe_moc_grid(moc, nullptr, &uniform);
+    PBE_REQUIRE(uniform, PBE_E_UNSUPPORTED, "pbe_moc_psi_max: uniform class grid only");
     int rc = pbe_moc_num_classes(moc, &N, &ctx);
     if (rc) return rc;
     pbe_moc_coeffs(moc, &xi1, nullptr);

@@ -460,6 +460,10 @@ int pbe_moc_state_create(pbe_moc *moc, int64_t ncells, const double *vcell_host,
     PBE_REQUIRE(ncells >= 0, PBE_E_INVALID, "pbe_moc_state_create: ncells < 0");
     int N = 0, block = 128, ctas = 1;
     pbe_ctx *ctx = nullptr;
+    int uniform = 1;
+    if (moc != nullptr) pbe_moc_grid(moc, nullptr, &uniform);
+    PBE_REQUIRE(uniform, PBE_E_UNSUPPORTED,
+                "pbe_moc_state_create: the resident state takes the reference's uniform class grid only");
     int rc = pbe_moc_num_classes(moc, &N, &ctx);
     if (rc) return rc;
     pbe_moc_get_kernel(moc, nullptr, &block, &ctas);

@@ -203,13 +203,29 @@ class MOC:
     """pbe_moc: PBEMethods::MOC's source path (MOCCoeffs: numberOfClasses, xi1, sourceRelaxation)."""
 
     def __init__(self, ctx: Context, numberOfClasses: int, xi1: float, spec: capi.KernelSpec,
-                 sourceRelaxation: float = 1.0):
+                 sourceRelaxation: float = 1.0, pivots=None):
+        """pivots: class volumes of a geometric / arbitrary grid (fixed-pivot extension, row f4; xi1 is
+        then ignored); None: the reference's uniform grid (i + 1) xi1."""
         self.ctx = ctx
         self.N = int(numberOfClasses)
-        self.xi1 = float(xi1)
         self._h = C.c_void_p()
+        if pivots is not None:
+            pv = np.ascontiguousarray(pivots, dtype=np.float64)
+            assert pv.shape == (self.N,)
+            self.xi1 = float(pv[0])
+            capi.check(capi.lib().pbe_moc_create_pivots(ctx.handle, self.N, pv.ctypes.data_as(C.POINTER(C.c_double)),
+                                                        C.byref(spec), float(sourceRelaxation), C.byref(self._h)))
+            return
+        self.xi1 = float(xi1)
         capi.check(capi.lib().pbe_moc_create(ctx.handle, self.N, self.xi1, C.byref(spec),
                                              float(sourceRelaxation), C.byref(self._h)))
+
+    def grid(self):
+        """(class volumes [N], is_uniform)"""
+        v = np.empty(self.N)
+        u = C.c_int()
+        capi.check(capi.lib().pbe_moc_grid(self._h, v.ctypes.data_as(C.POINTER(C.c_double)), C.byref(u)))
+        return v, bool(u.value)
 
     def close(self):
         if self._h:
@@ -230,7 +246,8 @@ class MOC:
     def kernel(self):
         w, b, c = C.c_int(), C.c_int(), C.c_int()
         capi.check(capi.lib().pbe_moc_get_kernel(self._h, C.byref(w), C.byref(b), C.byref(c)))
-        return {"kernel": {capi.MOC_KERNEL_SMEM: "smem", capi.MOC_KERNEL_TMEM: "tmem"}[w.value],
+        return {"kernel": {capi.MOC_KERNEL_SMEM: "smem", capi.MOC_KERNEL_TMEM: "tmem",
+                           capi.MOC_KERNEL_PIVOT: "pivot"}[w.value],
                 "cells_per_cta": b.value, "ctas_per_sm": c.value}
 
     def _dims(self, n):
