@@ -898,6 +898,49 @@ def leg_mom(B: Bench):
                          "note": "flop convention of SURVEY 8(d) applied to the reference's arithmetic per node pair"}}
 
 
+def leg_geometric(B: Bench, w):
+    """BASELINE configs[2] as worded ("100 geometric classes"): the fixed-pivot extension (row f4, parity
+    unpinned) on a geometric grid, beside the headline which runs the reference's uniform grid."""
+    torch, args = B.torch, B.args
+    from openpbe_b200 import engine, synthetic
+
+    gc, ratio = int(args.geo_cells), float(args.geo_ratio)
+    x = w.xi1 * ratio ** np.arange(w.N)
+    f = synthetic.moc_fields(w, ncells=min(gc, 200_000))
+    rep = (gc + f["n"].shape[1] - 1) // f["n"].shape[1]
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(B.dev)  # noqa: E731
+    n = T(np.tile(f["n"], (1, rep))[:, :gc])
+    e, r, v = (T(np.tile(f[k], rep)[:gc]) for k in ("eps", "rho", "nu"))
+    moc = engine.MOC(B.ctx, w.N, 0.0, engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs),
+                     w.relax, pivots=x)
+    mom = torch.zeros(6, dtype=torch.float64, device=B.dev)
+    for _ in range(2):
+        moc.step(n, e, r, v, w.dt, moments=mom)
+    B.barrier()
+    gsteps = 3
+    B.e0.record()
+    for _ in range(gsteps):
+        moc.step(n, e, r, v, w.dt, moments=mom)
+    B.e1.record()
+    torch.cuda.synchronize()
+    gms = B.allmax(B.e0.elapsed_time(B.e1) / gsteps)
+    top = x[-1] * (1 + 2e-15)
+    npairs = int(sum(np.searchsorted(x, top - x[i], side="right") - i for i in range(w.N) if 2 * x[i] <= top))
+    gflops = 40.0 + 43.0 * npairs + 40.0 * w.N  # SURVEY 8(d) convention + the two-pivot split (mul, sub) per pair
+    gtf = gc * gflops / (gms * 1e-3) / 1e12
+    info = moc.kernel()
+    moc.close()
+    return {"metric": "moc_cell_class_updates_per_s", "value": B.world * gc * w.N / (gms * 1e-3),
+            "unit": "cell-class-updates/s", "ms_per_step": gms, "cells_per_gpu": gc, "classes": w.N,
+            "grid": f"geometric, ratio {ratio}: class volumes xi1 {ratio}^i", "pairs_per_cell": npairs,
+            "workload": "MOC fixed-pivot step (Kumar-Ramkrishna two-pivot redistribution in the reference's "
+                        "conventions; extension, parity unpinned), CT + CT kernels, c01 constants, in-place step + "
+                        "6 fused moments", "kernel": info,
+            "roofline": {"bound": "fp64", "achieved": gtf, "peak": B.fp64_tf, "unit": "TFLOP/s",
+                         "frac": gtf / B.fp64_tf, "flops_per_cell": gflops, "traffic": None,
+                         "note": "shared-memory scatter kernel, one CTA per SM: not tuned like the uniform-grid kernels"}}
+
+
 def leg_transport(B: Bench, w, moc):
     torch, args = B.torch, B.args
     from openpbe_b200 import capi, engine, sharding, synthetic
@@ -1056,6 +1099,10 @@ def run_b200(args):
     if not args.no_mom:
         mom_leg = leg_mom(B)
         roofline["legs"]["mom"] = mom_leg["roofline"]
+    geometric = None
+    if not args.no_geometric:
+        geometric = leg_geometric(B, w)
+        roofline["legs"]["moc100_geometric"] = geometric["roofline"]
     if not args.no_transport:
         transport = leg_transport(B, w, main["moc"])
         roofline["legs"]["transport"] = transport["roofline"]
@@ -1134,12 +1181,12 @@ def run_b200(args):
                                       if world > 1 else "1 GPU",
                        "device": B.info["name"], "sm_count": B.info["sm_count"],
                        "other_legs": "config1 (configs[0]), qmom (configs[1]), strong (configs[3]), replay "
-                                     "(configs[4]), transport, mom: own keys of this line; their rooflines, CPU "
+                                     "(configs[4]), transport, mom, moc100_geometric (configs[2] as worded: fixed-pivot extension): own keys of this line; their rooflines, CPU "
                                      "baselines and e2e numbers are repeated under roofline.legs, cpu_baseline.legs, "
                                      "e2e.legs"},
             "clocks": main["clocks"], "e2e": e2e, "gpu_launches": main["launches"], "roofline": roofline,
             "cpu_baseline": cpu, "strong": main["strong"], "config1": config1, "qmom": qmom, "replay": replay,
-            "transport": transport, "mom": mom_leg, "checks": main["checks"],
+            "transport": transport, "mom": mom_leg, "moc100_geometric": geometric, "checks": main["checks"],
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -1171,6 +1218,9 @@ def main():
     ap.add_argument("--no-replay", action="store_true")
     ap.add_argument("--no-transport", action="store_true")
     ap.add_argument("--no-mom", action="store_true")
+    ap.add_argument("--no-geometric", action="store_true")
+    ap.add_argument("--geo-cells", type=float, default=1_212_416, help="fixed-pivot (geometric grid) leg: cells per GPU")
+    ap.add_argument("--geo-ratio", type=float, default=1.08, help="volume ratio of consecutive classes")
     ap.add_argument("--mom-cells", type=float, default=200000, help="methodOfMoments leg: cells per GPU")
     ap.add_argument("--halo-nccl", action="store_true", help="transport leg: NCCL send/recv halo exchange")
     ap.add_argument("--transport-n", type=int, default=160, help="transport leg: hex block of n^3 cells")
