@@ -126,6 +126,19 @@ int pbe_moc_d(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n, dou
 /* per-class global min / max over cells (MOC.C:181-183, 238): out_min/out_max DEVICE [N] */
 int pbe_moc_class_minmax(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n,
                          double *out_min, double *out_max, void *cuda_stream);
+/* The same result without any allocation (pbe_moc_class_minmax takes its per-CTA partials from
+ * cudaMallocAsync).  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The partials live in ONE file-scope device array of PBE_NOALLOC_MAX_CLASSES x PBE_NOALLOC_MAX_PARTS x 2
+ * doubles (1 MiB, held by every GPU that loads the library until exit), whose device address is resolved
+ * once per device when a MOC handle is created on it.  numberOfClasses > PBE_NOALLOC_MAX_CLASSES returns
+ * PBE_E_UNSUPPORTED; ncells is not limited (at most PBE_NOALLOC_MAX_PARTS partials per class).  Every call
+ * on a device shares the array: calls that overlap on the GPU (different streams, no dependency) RACE --
+ * order them.  n, out_min, out_max: DEVICE pointers as above; calls no cudaMalloc / cudaFree. */
+#define PBE_NOALLOC_MAX_CLASSES 128
+#define PBE_NOALLOC_MAX_PARTS 512
+int pbe_moc_class_minmax_noalloc(pbe_moc *moc, int64_t ncells, int64_t stride, const double *n,
+                                 double *out_min, double *out_max, void *cuda_stream);
 
 /* HOST-buffer entry point: what the OpenFOAM adapter calls from MOC::correct().  Copies the
  * fields host->device in cell chunks, runs pbe_moc_source per chunk, copies S back; copies and

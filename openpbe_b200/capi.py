@@ -104,6 +104,7 @@ PROTOTYPES = {
                                _vp]),
     "pbe_moc_d": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "pbe_moc_class_minmax": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "pbe_moc_class_minmax_noalloc": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
     "pbe_moc_source_host": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.c_double, _vp]),
     "pbe_qmom_create": (C.c_int, [_vp, C.c_int, C.POINTER(KernelSpec), C.POINTER(_vp)]),
     "pbe_qmom_destroy": (C.c_int, [_vp]),

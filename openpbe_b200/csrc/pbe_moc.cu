@@ -15,6 +15,10 @@
 
 using namespace pbe;
 
+namespace {
+cudaError_t resolve_minmax_scratch(int device); // static scratch of pbe_moc_class_minmax_noalloc (end of file)
+}
+
 struct pbe_moc {
     pbe_ctx *ctx = nullptr;
     int N = 0;
@@ -510,6 +514,7 @@ int pbe_moc_create(pbe_ctx *ctx, int N, double xi1, const pbe_kernel_spec *spec,
     }
     b.pair_tab = m->d_pair;
     b.cls = m->d_cls;
+    (void)resolve_minmax_scratch(ctx->device); // set-up of pbe_moc_class_minmax_noalloc; a failure is reported there
     *out = m;
     return PBE_OK;
 }
@@ -667,6 +672,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
     b.pair_tab = nullptr;
     b.cls = m->d_cls;
     m->fpx = MocFpExtra{m->d_fp, (int)pairs.size(), m->d_fpw, m->d_fpw + N, m->d_fpw + 2 * N};
+    (void)resolve_minmax_scratch(ctx->device); // set-up of pbe_moc_class_minmax_noalloc; a failure is reported there
     *out = m;
     return PBE_OK;
 }
@@ -866,3 +872,61 @@ int pbe_moc_source_host(pbe_moc *m, int64_t ncells, int64_t stride, const double
 }
 
 } // extern "C"
+
+// ---- allocation-free variant of pbe_moc_class_minmax -------------------------------------------------
+// No counterpart in the reference: added for callers that must not
+// allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// pbe_moc_class_minmax takes its per-CTA partials from cudaMallocAsync; this variant keeps them in a
+// file-scope device array instead: PBE_NOALLOC_MAX_CLASSES x PBE_NOALLOC_MAX_PARTS x {min, max} doubles
+// = 1 MiB, held by every GPU that loads the library until the process exits.
+//   * In host code `g_minmax_scratch` is a host-side stand-in, NOT a device address: the address is
+//     resolved with cudaGetSymbolAddress once per device, with that device current, when a handle is
+//     first created on it (pbe_moc_create / pbe_moc_create_pivots), and kept in g_minmax_scratch_dev[].
+//   * Every call on a device shares the array and finds the last call's contents in it.  Nothing has to
+//     start at zero: the first kernel writes every partial [k][b], b < nparts, that the second one reads.
+//   * Calls that overlap on the GPU (two streams, no dependency) race on the array: order them.
+static __device__ __align__(256) double g_minmax_scratch[(size_t)PBE_NOALLOC_MAX_CLASSES * PBE_NOALLOC_MAX_PARTS * 2];
+
+namespace {
+constexpr int kMaxDevices = 64;
+double *g_minmax_scratch_dev[kMaxDevices]; // per device: the array's DEVICE address (nullptr: not resolved)
+std::mutex g_minmax_scratch_mu;
+
+// set-up: once per device, that device current (the caller's DeviceGuard)
+cudaError_t resolve_minmax_scratch(int device) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_minmax_scratch_mu);
+    if (g_minmax_scratch_dev[device] != nullptr) return cudaSuccess;
+    double *ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_minmax_scratch);
+    if (e != cudaSuccess) return e;
+    g_minmax_scratch_dev[device] = ptr;
+    return cudaSuccess;
+}
+} // namespace
+
+extern "C" int pbe_moc_class_minmax_noalloc(pbe_moc *m, int64_t ncells, int64_t stride, const double *n,
+                                            double *out_min, double *out_max, void *cuda_stream) {
+    PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_class_minmax_noalloc: NULL handle");
+    PBE_REQUIRE(ncells >= 0 && stride >= ncells, PBE_E_INVALID, "pbe_moc_class_minmax_noalloc: bad ncells/stride");
+    PBE_REQUIRE(n != nullptr || ncells == 0, PBE_E_INVALID, "pbe_moc_class_minmax_noalloc: NULL field");
+    PBE_REQUIRE(m->N <= PBE_NOALLOC_MAX_CLASSES, PBE_E_UNSUPPORTED,
+                "pbe_moc_class_minmax_noalloc: numberOfClasses %d exceeds the static scratch's limit %d "
+                "(use pbe_moc_class_minmax, which allocates)",
+                m->N, PBE_NOALLOC_MAX_CLASSES);
+    const int dev = m->ctx->device;
+    PBE_REQUIRE(dev >= 0 && dev < kMaxDevices && g_minmax_scratch_dev[dev] != nullptr, PBE_E_CUDA,
+                "pbe_moc_class_minmax_noalloc: the static scratch of device %d was not resolved at set-up "
+                "(cudaGetSymbolAddress failed in pbe_moc_create)", dev);
+    DeviceGuard g(dev);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    double *part = g_minmax_scratch_dev[dev];
+    const int nparts = (int)std::max<int64_t>(
+        1, std::min<int64_t>(std::min<int64_t>((ncells + 2047) / 2048, (int64_t)m->ctx->sm_count * 2),
+                             PBE_NOALLOC_MAX_PARTS));
+    moc_minmax_partial_kernel<<<dim3(nparts, m->N), 256, 0, st>>>(ncells, stride, n, part);
+    moc_minmax_final_kernel<<<m->N, 32, 0, st>>>(nparts, part, out_min, out_max);
+    PBE_CUDA(cudaGetLastError());
+    m->ctx->launches += 2;
+    return PBE_OK;
+}
