@@ -248,6 +248,33 @@ def test_device_mules_matches_port_random_topology(ctx, nint, nbnd):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("n_iter", [1, 3, 5])
+def test_device_mules_fused_path_equals_per_field_path(ctx, n_iter, monkeypatch):
+    """The fused kernels (field chunks per thread, lambda rebuilt from the lm / lp rows of the earlier sweeps,
+    limitSum applied in the solve) against the per-field kernels they replaced and against the port."""
+    rng = np.random.default_rng(n_iter)
+    m = synthetic.block_mesh(21, 14, 9, velocity=(0.8, -0.6, 0.3))
+    K = 11
+    psi = bump_fields(m, K, rng, 0.0, 3.0)
+    S = rng.normal(size=psi.shape) * 0.3
+    pmax = psi.max(axis=1) * rng.uniform(0.6, 1.2, K)
+    psi_b = rng.uniform(0.0, 3.0, (K, m["boundary_owner"].size))
+    want = orc.transport_mules(m, "Gauss vanLeer", psi, m["phi"], 0.02, pmax, S=S, psi_b=psi_b, n_limiter_iter=n_iter)
+    monkeypatch.setenv("PBE_MULES_CHUNK", "4")
+    fused = device_mules(ctx, m, "Gauss vanLeer", psi, m["phi"], 0.02, pmax, S=S, psi_b=psi_b, n_iter=n_iter)
+    monkeypatch.setenv("PBE_MULES_PATH", "0")
+    plain = device_mules(ctx, m, "Gauss vanLeer", psi, m["phi"], 0.02, pmax, S=S, psi_b=psi_b, n_iter=n_iter)
+    assert np.array_equal(fused, want) and np.array_equal(plain, want)
+    # polyhedral cells with more faces than the fused kernels keep in registers
+    m = random_geometry_mesh(rng, 40, 400, 30)
+    psi = rng.uniform(0.0, 2.0, (K, 40))
+    pmax = np.full(K, 1.7)
+    want = orc.transport_mules(m, "Gauss vanLeer", psi, m["phi"], 0.1, pmax, n_limiter_iter=n_iter)
+    monkeypatch.delenv("PBE_MULES_PATH")
+    assert np.array_equal(device_mules(ctx, m, "Gauss vanLeer", psi, m["phi"], 0.1, pmax, n_iter=n_iter), want)
+
+
+@pytest.mark.gpu
 def test_device_psi_max_helpers(ctx):
     from openpbe_b200 import engine
     rng = np.random.default_rng(9)

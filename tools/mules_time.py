@@ -1,0 +1,28 @@
+"""Timing of the MULES-limited transport (vanLeer + limiter + limitSum): python tools/mules_time.py [n K reps]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+from openpbe_b200 import capi
+capi.LIB_PATH = os.environ.get('PBE_LIB', capi.LIB_PATH)
+from openpbe_b200 import engine, synthetic
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 160
+K = int(sys.argv[2]) if len(sys.argv) > 2 else 100
+reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+ctx = engine.Context(0); dev = torch.device("cuda:0")
+m = synthetic.block_mesh(n, n, n, velocity=(1.0, 0.5, 0.25))
+mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+mesh.set_geometry(m["Sf"], m["C"], m["weights"])
+nc = n ** 3
+g = torch.Generator(device=dev); g.manual_seed(1)
+psi = torch.rand(K, nc, dtype=torch.float64, device=dev, generator=g)
+S = torch.rand(K, nc, dtype=torch.float64, device=dev, generator=g)
+out = torch.empty_like(psi); phi = torch.from_numpy(m["phi"]).to(dev)
+pmax = torch.full((K,), 2.0, dtype=torch.float64, device=dev)
+dt = 0.4 / (n * 1.75)
+for _ in range(2): mesh.transport_mules(psi, phi, dt, pmax, S=S, out=out)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True); best = 1e9
+for _ in range(reps):
+    e0.record(); mesh.transport_mules(psi, phi, dt, pmax, S=S, out=out); e1.record(); torch.cuda.synchronize()
+    best = min(best, e0.elapsed_time(e1))
+print(f"mules vanLeer {n}^3 x {K}: {best:.2f} ms, {nc*K/best*1e3:.3e} cell-field-updates/s, checksum {float(out.sum()):.12e}")
