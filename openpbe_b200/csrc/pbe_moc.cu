@@ -45,7 +45,7 @@ struct pbe_moc {
     // fixed-pivot grid (pbe_moc_create_pivots): arbitrary class volumes, pbe_moc_pivot_kernel.cuh
     bool pivot = false;
     std::vector<double> pivots;
-    FpPair *d_fp = nullptr;
+    FpTile *d_fp = nullptr;
     double *d_fpw = nullptr; // [3][N]: hat areas, self shares, 2 / x_k
     MocFpExtra fpx{};
 };
@@ -586,7 +586,11 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
 
     // pairs that stay on the grid (the death bound of MOC.C:107-109), i-major; the new drop goes to the
     // pivots that bracket it with the number- and volume-preserving weights
-    std::vector<FpPair> pairs;
+    struct HostPair {
+        int i, j, t;
+        double a, b, eta;
+    };
+    std::vector<HostPair> pairs;
     if (m->dcoal != DCOAL_OFF)
         for (int i = 0; i < N; ++i)
             for (int j = i; j < N; ++j) {
@@ -595,7 +599,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
                 const double snap = 8.0 * 2.220446049250313e-16;
                 const double v = xi[i] + xi[j], vt = v * (1.0 + snap);
                 if (v > xi[N - 1] * (1.0 + snap)) break;
-                FpPair pr{};
+                HostPair pr{};
                 pr.i = i;
                 pr.j = j;
                 pr.t = std::min(N - 1, (int)(std::upper_bound(xi.begin(), xi.end(), vt) - xi.begin()) - 1);
@@ -609,6 +613,34 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
                 if (i == j) pr.a *= 0.5; // MOC.C:118
                 pairs.push_back(pr);
             }
+    // tiles: up to MOCP_TILE pairs of one i with consecutive j whose births fit one window of MOCP_WIN pivots
+    std::vector<FpTile> tiles;
+    for (size_t q = 0; q < pairs.size();) {
+        FpTile T{};
+        T.i = pairs[q].i;
+        T.j0 = pairs[q].j;
+        T.tb = pairs[q].t;
+        int k = 0;
+        for (; k < MOCP_TILE && q + k < pairs.size(); ++k) {
+            const HostPair &pr = pairs[q + k];
+            if (pr.i != T.i || pr.j != T.j0 + k || pr.t < T.tb || pr.t - T.tb > MOCP_WIN - 2) break;
+            T.a[k] = pr.a;
+            T.b[k] = pr.b;
+            T.cw[k][pr.t - T.tb] = pr.eta;
+            if (pr.t < N - 1) T.cw[k][pr.t - T.tb + 1] = 1.0 - pr.eta;
+        }
+        T.npairs = k; // >= 1: the first pair always fits
+        // padding pairs (k .. MOCP_TILE-1) keep a = 0 and zero weights; their j may run past the grid: the kernel clamps
+        tiles.push_back(T);
+        q += (size_t)k;
+    }
+    while (!tiles.empty() && tiles.size() % MOCP_SLOT_TILES != 0) { // whole ring slots: empty tiles that touch the dummy rows only
+        FpTile T{};
+        T.i = tiles.back().i;
+        T.j0 = N;
+        T.tb = N;
+        tiles.push_back(T);
+    }
     if (pairs.empty()) m->dcoal = DCOAL_OFF;
 
     MocParams &b = m->base;
@@ -656,9 +688,9 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, MOCP_BLOCK, smem);
         m->ctas_per_sm = m->smem_ctas_per_sm = std::max(1, occ);
     }
-    if (e == cudaSuccess && !pairs.empty()) {
-        e = cudaMalloc(&m->d_fp, pairs.size() * sizeof(FpPair));
-        if (e == cudaSuccess) e = cudaMemcpy(m->d_fp, pairs.data(), pairs.size() * sizeof(FpPair), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && !tiles.empty()) {
+        e = cudaMalloc(&m->d_fp, tiles.size() * sizeof(FpTile));
+        if (e == cudaSuccess) e = cudaMemcpy(m->d_fp, tiles.data(), tiles.size() * sizeof(FpTile), cudaMemcpyHostToDevice);
     }
     if (e == cudaSuccess) e = cudaMalloc(&m->d_fpw, fpw.size() * sizeof(double));
     if (e == cudaSuccess) e = cudaMemcpy(m->d_fpw, fpw.data(), fpw.size() * sizeof(double), cudaMemcpyHostToDevice);
@@ -671,7 +703,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
     }
     b.pair_tab = nullptr;
     b.cls = m->d_cls;
-    m->fpx = MocFpExtra{m->d_fp, (int)pairs.size(), m->d_fpw, m->d_fpw + N, m->d_fpw + 2 * N};
+    m->fpx = MocFpExtra{m->d_fp, (int)tiles.size(), m->d_fpw, m->d_fpw + N, m->d_fpw + 2 * N};
     (void)resolve_minmax_scratch(ctx->device); // set-up of pbe_moc_class_minmax_noalloc; a failure is reported there
     *out = m;
     return PBE_OK;

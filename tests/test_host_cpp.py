@@ -85,6 +85,15 @@ def test_construction_fails_loudly_without_gpu(probe):
     assert "no CUDA device" in out and "no CPU path" in out
 
 
+def test_replay_driver_rejects_ranks_with_mesh():
+    """--ranks forks one process per GPU before CUDA is touched; the decomposed transport is not wired into the
+    driver, and it says so instead of running a wrong case (checked before any device is needed)."""
+    exe = os.path.join(ROOT, "apps", "pbe_replay")
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "apps"), "-s"])
+    r = subprocess.run([exe, "--ranks", "2", "--mesh", "8", "8", "8"], capture_output=True, text=True)
+    assert r.returncode != 0 and "--ranks with --mesh" in r.stderr
+
+
 @pytest.mark.gpu
 def test_replay_driver_moc_and_qmom(oracle):
     exe = os.path.join(ROOT, "apps", "pbe_replay")

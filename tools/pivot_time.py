@@ -2,6 +2,8 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
+from openpbe_b200 import capi
+capi.LIB_PATH = os.environ.get('PBE_LIB', capi.LIB_PATH)
 from openpbe_b200 import engine, synthetic
 ctx = engine.Context(0); dev = torch.device("cuda:0")
 T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
