@@ -909,7 +909,8 @@ def leg_geometric(B: Bench, w):
     f = synthetic.moc_fields(w, ncells=min(gc, 200_000))
     rep = (gc + f["n"].shape[1] - 1) // f["n"].shape[1]
     T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(B.dev)  # noqa: E731
-    n = T(np.tile(f["n"], (1, rep))[:, :gc])
+    n0 = T(np.tile(f["n"], (1, rep))[:, :gc])
+    n = n0.clone()
     e, r, v = (T(np.tile(f[k], rep)[:gc]) for k in ("eps", "rho", "nu"))
     moc = engine.MOC(B.ctx, w.N, 0.0, engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs),
                      w.relax, pivots=x)
@@ -929,8 +930,26 @@ def leg_geometric(B: Bench, w):
     gflops = 40.0 + 43.0 * npairs + 40.0 * w.N  # SURVEY 8(d) convention + the two-pivot split (mul, sub) per pair
     gtf = gc * gflops / (gms * 1e-3) / 1e12
     info = moc.kernel()
+    ge2e = None
+    if not args.no_e2e:
+        # the same step end to end: class fields owned on the device, pinned host eps, rho, nu, alpha -> d
+        st = engine.MOCState(moc, gc, vcell=np.tile(f["vcell"], rep)[:gc])
+        sn, _ = st.device_fields()
+        sn.copy_(n0)
+        hb = {k: B.pinned(np.tile(f[k], rep)[:gc]) for k in ("eps", "rho", "nu", "alpha")}
+        dh = torch.empty(gc, dtype=torch.float64, pin_memory=True)
+        st.correct(hb["eps"], hb["rho"], hb["nu"], hb["alpha"], w.dt, d_out=dh, minmax=True, n_moments=6)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            st.correct(hb["eps"], hb["rho"], hb["nu"], hb["alpha"], w.dt, d_out=dh, minmax=True, n_moments=6)
+        te = (time.perf_counter() - t0) / 3
+        ge2e = {"value": gc * w.N / te, "unit": "cell-class-updates/s", "ms_per_step": te * 1e3,
+                "h2d_bytes_per_step": 32 * gc, "d2h_bytes_per_step": 8 * gc,
+                "call": "pbe_moc_correct_resident on a fixed-pivot handle (zero flux)"}
+        del sn
+        st.close()
     moc.close()
-    return {"metric": "moc_cell_class_updates_per_s", "value": B.world * gc * w.N / (gms * 1e-3),
+    return {"metric": "moc_cell_class_updates_per_s", "value": B.world * gc * w.N / (gms * 1e-3), "e2e": ge2e,
             "unit": "cell-class-updates/s", "ms_per_step": gms, "cells_per_gpu": gc, "classes": w.N,
             "grid": f"geometric, ratio {ratio}: class volumes xi1 {ratio}^i", "pairs_per_cell": npairs,
             "workload": "MOC fixed-pivot step (Kumar-Ramkrishna two-pivot redistribution in the reference's "
@@ -938,7 +957,7 @@ def leg_geometric(B: Bench, w):
                         "6 fused moments", "kernel": info,
             "roofline": {"bound": "fp64", "achieved": gtf, "peak": B.fp64_tf, "unit": "TFLOP/s",
                          "frac": gtf / B.fp64_tf, "flops_per_cell": gflops, "traffic": None,
-                         "note": "shared-memory scatter kernel, one CTA per SM: not tuned like the uniform-grid kernels"}}
+                         "note": "tiles of four pairs, register birth window, accumulators in shared memory: one CTA per SM (DESIGN.md 4.8)"}}
 
 
 def leg_transport(B: Bench, w, moc):
@@ -1103,6 +1122,8 @@ def run_b200(args):
     if not args.no_geometric:
         geometric = leg_geometric(B, w)
         roofline["legs"]["moc100_geometric"] = geometric["roofline"]
+        if e2e is not None and geometric.get("e2e"):
+            e2e["legs"]["moc100_geometric"] = geometric["e2e"]
     if not args.no_transport:
         transport = leg_transport(B, w, main["moc"])
         roofline["legs"]["transport"] = transport["roofline"]

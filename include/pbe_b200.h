@@ -309,8 +309,9 @@ int pbe_moc_coeffs(pbe_moc *moc, double *xi1, double *source_relaxation);
  * pivots that bracket x_i + x_j with the number- and volume-preserving weights; breakup daughters
  * (uniformBinaryBreakup) are assigned through the same hat functions (volume exact).  On the uniform
  * volumes the coalescence terms are the reference's own.  pivots [N], strictly increasing, positive.
- * The handle works with pbe_moc_source / _step / _d / _class_minmax / _source_host; the resident state
- * and the MULES bound (which use xi1) take uniform grids only (PBE_E_UNSUPPORTED otherwise). */
+ * The handle works with pbe_moc_source / _step / _d / _class_minmax / _source_host and with the resident state's
+ * zero-flux correct(); attaching a mesh to such a state and the MULES bound (which use xi1) take uniform grids
+ * only (PBE_E_UNSUPPORTED otherwise). */
 int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_kernel_spec *spec,
                           double source_relaxation, pbe_moc **out);
 /* class volumes of the handle's grid ([N], may be NULL) and whether it is the reference's uniform one */

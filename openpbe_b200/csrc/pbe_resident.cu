@@ -460,10 +460,6 @@ int pbe_moc_state_create(pbe_moc *moc, int64_t ncells, const double *vcell_host,
     PBE_REQUIRE(ncells >= 0, PBE_E_INVALID, "pbe_moc_state_create: ncells < 0");
     int N = 0, block = 128, ctas = 1;
     pbe_ctx *ctx = nullptr;
-    int uniform = 1;
-    if (moc != nullptr) pbe_moc_grid(moc, nullptr, &uniform);
-    PBE_REQUIRE(uniform, PBE_E_UNSUPPORTED,
-                "pbe_moc_state_create: the resident state takes the reference's uniform class grid only");
     int rc = pbe_moc_num_classes(moc, &N, &ctx);
     if (rc) return rc;
     pbe_moc_get_kernel(moc, nullptr, &block, &ctas);
@@ -568,6 +564,13 @@ int pbe_moc_state_device(pbe_moc_state *s, double **n_dev, int64_t *stride, doub
 }
 
 int pbe_moc_state_attach_mesh(pbe_moc_state *s, pbe_mesh *mesh, int scheme) {
+    {
+        int uniform = 1;
+        if (s != nullptr && s->moc != nullptr) pbe_moc_grid(s->moc, nullptr, &uniform);
+        PBE_REQUIRE(uniform, PBE_E_UNSUPPORTED,
+                    "pbe_moc_state_attach_mesh: transport of a fixed-pivot state is not built (continuity check and MULES "
+                    "bound use the uniform class grid); the zero-flux resident correct() works on any grid");
+    }
     PBE_REQUIRE(s && mesh, PBE_E_INVALID, "pbe_moc_state_attach_mesh: NULL argument");
     int64_t mc = 0, nint = 0, nbnd = 0;
     int rc = pbe_mesh_info(mesh, &mc, &nint, &nbnd, nullptr);

@@ -140,5 +140,40 @@ def test_device_errors(ctx):
     moc = engine.MOC(ctx, 4, 0.0, ks, pivots=np.array([1.0, 2.0, 4.0, 8.0]))
     with pytest.raises(capi.PbeError, match="one kernel"):
         moc.set_kernel("smem")
-    with pytest.raises(capi.PbeError, match="uniform class grid"):
-        engine.MOCState(moc, 10)
+    st = engine.MOCState(moc, 10)  # the zero-flux resident state takes any grid
+    st.close()
+    from openpbe_b200 import synthetic
+    m = synthetic.block_mesh(3, 2, 2)
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    with pytest.raises(capi.PbeError, match="fixed-pivot state"):
+        engine.MOCState(moc, 12, vcell=m["vcell"], mesh=mesh)
+
+
+@gpu
+def test_resident_correct_on_a_geometric_grid(ctx):
+    """MOC::correct() through the resident state (class fields owned on the device) on fixed pivots: the same
+    numbers as the device-pointer step, diagnostics included."""
+    import torch
+    rng = np.random.default_rng(21)
+    N, nc, dt = 40, 3000, 2.5e-4
+    x = fp.geometric_pivots(N, 1e-11, 1.2)
+    n, eps, rho, nu = fields(rng, N, nc, x)
+    n *= 1e-3
+    vcell = rng.uniform(0.5, 2.0, nc)
+    alpha = (x @ n) / vcell
+    moc = _dev(ctx, CT, x)
+    from openpbe_b200 import engine
+    st = engine.MOCState(moc, nc, vcell=vcell, n0=n)
+    d = torch.empty(nc, dtype=torch.float64).pin_memory()
+    _, diag = st.correct(eps, rho, nu, alpha, dt, d_out=d, minmax=True, n_moments=3)
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    nn = T(n.copy())
+    dd = torch.empty(nc, dtype=torch.float64, device="cuda")
+    moc.step(nn, T(eps), T(rho), T(nu), dt, d=dd)
+    assert torch.equal(st.download(), nn.cpu()) and torch.equal(d, dd.cpu())
+    want, scale = fp.moc_source(CT, x, 1.0, n, eps, rho, nu, dt)
+    n1 = n + dt * want
+    assert np.all(np.abs(st.download().numpy() - n1) <= dt * 1e-12 * scale + 1e-15 * np.abs(n1))
+    np.testing.assert_allclose(np.asarray(diag["class_min"]), n1.min(axis=1), rtol=1e-9, atol=1e-300)
+    assert diag["cont_err_max"] == pytest.approx(np.abs((x @ n1) / vcell - alpha).max(), rel=1e-6, abs=1e-18)
+    st.close()
