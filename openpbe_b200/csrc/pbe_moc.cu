@@ -613,30 +613,53 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
                 if (i == j) pr.a *= 0.5; // MOC.C:118
                 pairs.push_back(pr);
             }
-    // tiles: up to MOCP_TILE pairs of one i with consecutive j whose births fit one window of MOCP_WIN pivots
+    // tiles of MOCP_TI x MOCP_TJ pairs (rows i0.., columns j0..) whose births fit one window of MOCP_WIN pivots; a tile
+    // whose window would overflow is cut into row tiles, and those into single pairs (any increasing grid works)
     std::vector<FpTile> tiles;
-    for (size_t q = 0; q < pairs.size();) {
-        FpTile T{};
-        T.i = pairs[q].i;
-        T.j0 = pairs[q].j;
-        T.tb = pairs[q].t;
-        int k = 0;
-        for (; k < MOCP_TILE && q + k < pairs.size(); ++k) {
-            const HostPair &pr = pairs[q + k];
-            if (pr.i != T.i || pr.j != T.j0 + k || pr.t < T.tb || pr.t - T.tb > MOCP_WIN - 2) break;
-            T.a[k] = pr.a;
-            T.b[k] = pr.b;
-            T.cw[k][pr.t - T.tb] = pr.eta;
-            if (pr.t < N - 1) T.cw[k][pr.t - T.tb + 1] = 1.0 - pr.eta;
-        }
-        T.npairs = k; // >= 1: the first pair always fits
-        // padding pairs (k .. MOCP_TILE-1) keep a = 0 and zero weights; their j may run past the grid: the kernel clamps
-        tiles.push_back(T);
-        q += (size_t)k;
+    {
+        std::vector<int> pidx((size_t)N * N, -1); // (i, j) -> index into pairs
+        for (size_t q = 0; q < pairs.size(); ++q) pidx[(size_t)pairs[q].i * N + pairs[q].j] = (int)q;
+        auto emit = [&](int i0, int j0, int r_lo, int r_hi, int c_lo, int c_hi) -> bool { // false: window overflow
+            int tmin = N, tmax = -1, cnt = 0;
+            for (int r = r_lo; r < r_hi; ++r)
+                for (int c = c_lo; c < c_hi; ++c) {
+                    const int i = i0 + r, j = j0 + c;
+                    if (i >= N || j >= N || pidx[(size_t)i * N + j] < 0) continue;
+                    const HostPair &pr = pairs[pidx[(size_t)i * N + j]];
+                    tmin = std::min(tmin, pr.t);
+                    tmax = std::max(tmax, pr.t);
+                    ++cnt;
+                }
+            if (cnt == 0) return true;
+            if (tmax - tmin > MOCP_WIN - 2) return false;
+            FpTile T{};
+            T.i0 = i0, T.j0 = j0, T.tb = tmin, T.npairs = cnt;
+            for (int r = r_lo; r < r_hi; ++r)
+                for (int c = c_lo; c < c_hi; ++c) {
+                    const int i = i0 + r, j = j0 + c;
+                    if (i >= N || j >= N || pidx[(size_t)i * N + j] < 0) continue;
+                    const HostPair &pr = pairs[pidx[(size_t)i * N + j]];
+                    const int k = r * MOCP_TJ + c;
+                    T.a[k] = pr.a;
+                    T.b[k] = pr.b;
+                    T.cw[k][pr.t - tmin] = pr.eta;
+                    if (pr.t < N - 1) T.cw[k][pr.t - tmin + 1] = 1.0 - pr.eta;
+                }
+            tiles.push_back(T);
+            return true;
+        };
+        for (int i0 = 0; i0 < N; i0 += MOCP_TI)
+            for (int j0 = i0; j0 < N; j0 += MOCP_TJ) {
+                if (emit(i0, j0, 0, MOCP_TI, 0, MOCP_TJ)) continue;
+                for (int r = 0; r < MOCP_TI; ++r) {
+                    if (emit(i0, j0, r, r + 1, 0, MOCP_TJ)) continue;
+                    for (int c = 0; c < MOCP_TJ; ++c) emit(i0, j0, r, r + 1, c, c + 1); // a single pair always fits
+                }
+            }
     }
     while (!tiles.empty() && tiles.size() % MOCP_SLOT_TILES != 0) { // whole ring slots: empty tiles that touch the dummy rows only
         FpTile T{};
-        T.i = tiles.back().i;
+        T.i0 = tiles.back().i0;
         T.j0 = N;
         T.tb = N;
         tiles.push_back(T);

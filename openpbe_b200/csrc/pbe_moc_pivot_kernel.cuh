@@ -13,14 +13,16 @@
 //
 // One thread per cell (lane = cell) as in the other kernels; per-cell class densities and source
 // accumulators are columns of shared-memory arrays.  The pair list is cell-independent and cut into TILES of
-// up to four pairs (i, j0 .. j0+3) whose births all land inside a window of MOCP_WIN consecutive pivots
-// starting at tb (for a geometric grid the targets of four consecutive j span at most five pivots; any grid
-// works: a tile is simply cut shorter when its window would overflow).  A tile is read through uniform
-// (broadcast) loads; its four kernel values are independent chains (the exponentials overlap), the births are
-// formed in a register window as weighted sums (weights = the two-pivot shares, zero elsewhere) and retired
-// with one batch of independent shared-memory read-modify-writes, the deaths of the four j likewise; the death
-// of class i is a register sum flushed when i changes.  (First version: one pair at a time, four dependent
-// read-modify-writes each: 78.8 ms per 1.2e6 cells at N = 100)
+// MOCP_TI x MOCP_TJ class pairs (rows i0 .. i0+3, columns j0 .. j0+3, as the uniform-grid kernels walk them) whose
+// births all land inside a window of MOCP_WIN consecutive pivots starting at tb: on the uniform grid a 4 x 4 tile
+// spans 7 pivots, on a geometric grid 4-5; any increasing grid works, because a tile whose window would overflow is
+// cut into row tiles and those into single pairs.  Invalid slots (i > j, sum beyond the grid, cut away) carry a
+// zero kernel value and zero weights, so the loop has no predicates.  A tile is read through uniform (broadcast)
+// shared-memory loads from a ring that cp.async.bulk fills; its 16 kernel values are independent chains, row sums
+// (death of i) stay in registers for the whole row block, column sums (death of j) and the births -- formed in a
+// register window as weighted sums, weights = the two-pivot shares -- retire with one batch of independent
+// read-modify-writes each per TILE.  History (N = 100, ratio 1.08, 1.2e6 cells): one pair at a time 78.8 ms; 1 x 4
+// tiles from global memory 111 ms, through the ring 29.7 ms, + table exponential 26.5 ms; 4 x 4 tiles: DESIGN.md 4.8.
 #pragma once
 
 #include "pbe_moc_kernel.cuh"
@@ -28,21 +30,21 @@
 namespace pbe {
 
 #ifndef PBE_MOCP_UNROLL
-#define PBE_MOCP_UNROLL 2
+#define PBE_MOCP_UNROLL 1
 #endif
 constexpr int MOCP_UNROLL = PBE_MOCP_UNROLL; // tiles in flight per trip of the slot loop
-constexpr int MOCP_TILE = 4;        // pairs per tile
-constexpr int MOCP_WIN = 8;         // birth window, pivots
-constexpr int MOCP_SLOT_TILES = 16; // tiles per ring slot: the tile list streams through two shared-memory slots
-                                    // filled by cp.async.bulk (UBLKCP) on mbarriers, as the pair table of the
-                                    // uniform-grid kernels does (read straight from global memory a tile cost
-                                    // 42 L2 round trips at the head of its dependency chain: 111 ms)
+constexpr int MOCP_TI = 4, MOCP_TJ = 4;      // rows x columns of a tile
+constexpr int MOCP_PAIRS = MOCP_TI * MOCP_TJ;
+constexpr int MOCP_WIN = 8;                  // birth window, pivots
+constexpr int MOCP_SLOT_TILES = 4;           // tiles per ring slot: the tile list streams through two shared-memory slots
+                                             // filled by cp.async.bulk (UBLKCP) on mbarriers, as the pair table of the
+                                             // uniform-grid kernels does
 
 struct alignas(16) FpTile {
-    int i, j0, tb, npairs;
-    double a[MOCP_TILE];  // CT: G_ij (halved on the diagonal); otherwise S_ij (halved on the diagonal); 0 = padding
-    double b[MOCP_TILE];  // CT: H_ij
-    double cw[MOCP_TILE][MOCP_WIN]; // share of pair k's birth that goes to pivot tb + w
+    int i0, j0, tb, npairs;
+    double a[MOCP_PAIRS];  // [r][c]: CT: G_ij (halved on the diagonal); otherwise S_ij (halved on the diagonal); 0 = no pair
+    double b[MOCP_PAIRS];  // CT: H_ij
+    double cw[MOCP_PAIRS][MOCP_WIN]; // share of the pair's birth that goes to pivot tb + w
 };
 
 struct MocFpExtra {
@@ -139,8 +141,18 @@ __global__ void __launch_bounds__(MOCP_BLOCK, 1) moc_pivot_kernel(const __grid_c
             negK = -(p.coalK * rho * eps * (rho * nu)) * 1.4426950408889634074; // x log2(e): exp(x) = 2^(x log2 e)
         }
         if (COAL != DCOAL_OFF) {
-            int irow = -1;
-            double ni = 0.0, di = 0.0;
+            int iblk = -1;
+            double ni[MOCP_TI], di[MOCP_TI];
+            int irow[MOCP_TI];
+#pragma unroll
+            for (int r = 0; r < MOCP_TI; ++r) ni[r] = di[r] = 0.0, irow[r] = N * BLOCK + tid;
+            auto flush_rows = [&]() { // death of the row block's classes: distinct rows, one batch
+                double cur[MOCP_TI];
+#pragma unroll
+                for (int r = 0; r < MOCP_TI; ++r) cur[r] = sv[irow[r]];
+#pragma unroll
+                for (int r = 0; r < MOCP_TI; ++r) sv[irow[r]] = cur[r] - di[r];
+            };
 #pragma unroll 1
             for (int sl = 0; sl < nslots; ++sl, ++qq) {
               mbar_wait(&bars[qq & 1], (unsigned)((qq >> 1) & 1));
@@ -148,42 +160,51 @@ __global__ void __launch_bounds__(MOCP_BLOCK, 1) moc_pivot_kernel(const __grid_c
 #pragma unroll MOCP_UNROLL
               for (int q = 0; q < MOCP_SLOT_TILES; ++q) {
                 const FpTile &T = slot[q]; // uniform shared-memory address: broadcast loads
-                const int ti = T.i, j0 = T.j0, tb = T.tb;
-                if (ti != irow) { // warp-uniform
-                    if (irow >= 0) sv[irow * BLOCK + tid] -= di;
-                    irow = ti;
-                    ni = n_s[irow * BLOCK + tid];
-                    di = 0.0;
+                const int i0 = T.i0, j0 = T.j0, tb = T.tb;
+                if (i0 != iblk) { // warp-uniform: a new row block
+                    if (iblk >= 0) flush_rows();
+                    iblk = i0;
+#pragma unroll
+                    for (int r = 0; r < MOCP_TI; ++r) {
+                        irow[r] = min(i0 + r, N) * BLOCK + tid; // rows past the grid: the zero class
+                        ni[r] = n_s[irow[r]];
+                        di[r] = 0.0;
+                    }
                 }
-                double tt[MOCP_TILE];
-                int jrow[MOCP_TILE];
+                double nj[MOCP_TJ], dj[MOCP_TJ], bw[MOCP_WIN];
+                int jrow[MOCP_TJ];
 #pragma unroll
-                for (int k = 0; k < MOCP_TILE; ++k) {
-                    jrow[k] = min(j0 + k, N) * BLOCK + tid; // padding pairs: the zero class
-                    const double w = ni * n_s[jrow[k]];
-                    if (COAL == DCOAL_CT)
-                        tt[k] = (exp2_neg_tab_safe(negK * T.b[k], T128) * T.a[k]) * w; // 8 FP64 instructions (exp_neg: ~25)
-                    else
-                        tt[k] = T.a[k] * w;
+                for (int c = 0; c < MOCP_TJ; ++c) {
+                    jrow[c] = min(j0 + c, N) * BLOCK + tid;
+                    nj[c] = n_s[jrow[c]];
+                    dj[c] = 0.0;
                 }
-                // deaths of the four j: independent targets (padding pairs all hit the dummy row with tt = 0)
-                double dj[MOCP_TILE];
 #pragma unroll
-                for (int k = 0; k < MOCP_TILE; ++k) dj[k] = sv[jrow[k]];
+                for (int w = 0; w < MOCP_WIN; ++w) bw[w] = 0.0;
 #pragma unroll
-                for (int k = 0; k < MOCP_TILE; ++k) {
-                    di += tt[k];
-                    sv[jrow[k]] = dj[k] - tt[k];
+                for (int r = 0; r < MOCP_TI; ++r) {
+#pragma unroll
+                    for (int c = 0; c < MOCP_TJ; ++c) {
+                        const int k = r * MOCP_TJ + c;
+                        const double w = ni[r] * nj[c];
+                        double tt;
+                        if (COAL == DCOAL_CT)
+                            tt = (exp2_neg_tab_safe(negK * T.b[k], T128) * T.a[k]) * w; // 8 FP64 instructions (exp_neg: ~25)
+                        else
+                            tt = T.a[k] * w;
+                        di[r] += tt;
+                        dj[c] += tt;
+#pragma unroll
+                        for (int ww = 0; ww < MOCP_WIN; ++ww) bw[ww] = fma_(T.cw[k][ww], tt, bw[ww]);
+                    }
                 }
-                // births: weighted sums into the window tb .. tb + WIN - 1, then one batch of read-modify-writes
-                double bw[MOCP_WIN];
+                // deaths of the four j: independent targets (columns past the grid hit the dummy row with 0)
+                double cj[MOCP_TJ];
 #pragma unroll
-                for (int w = 0; w < MOCP_WIN; ++w) {
-                    double acc = T.cw[0][w] * tt[0];
+                for (int c = 0; c < MOCP_TJ; ++c) cj[c] = sv[jrow[c]];
 #pragma unroll
-                    for (int k = 1; k < MOCP_TILE; ++k) acc = fma_(T.cw[k][w], tt[k], acc);
-                    bw[w] = acc;
-                }
+                for (int c = 0; c < MOCP_TJ; ++c) sv[jrow[c]] = cj[c] - dj[c];
+                // births: the window tb .. tb + WIN - 1, one batch of read-modify-writes
                 double cur[MOCP_WIN];
                 int wrow[MOCP_WIN];
 #pragma unroll
@@ -197,7 +218,7 @@ __global__ void __launch_bounds__(MOCP_BLOCK, 1) moc_pivot_kernel(const __grid_c
               __syncthreads(); // every warp is done with this ring slot
               if (tid == 0 && qq + 2 < total_q) issue(qq + 2);
             }
-            if (irow >= 0) sv[irow * BLOCK + tid] -= di;
+            if (iblk >= 0) flush_rows();
         }
 
         // ---- epilogue: breakup through the pivots' hat functions, limiter, update, d, diagnostics ----
