@@ -87,10 +87,10 @@ moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr, bool wide) {
     return nullptr;
 }
 
-typedef void (*mocp_kernel_fn)(const MocParams, const MocFpExtra);
-mocp_kernel_fn pick_pivot_kernel(int dcoal, int dbr) {
+typedef void (*mocp_kernel_fn)(const MocParams, const MocFpExtra, const int);
+mocp_kernel_fn pick_pivot_kernel(int dcoal, int dbr, bool tm) {
 #define PBE_PICK(C, B) \
-    if (dcoal == C && dbr == B) return (mocp_kernel_fn)moc_pivot_kernel<C, B>;
+    if (dcoal == C && dbr == B) return tm ? (mocp_kernel_fn)moc_pivot_kernel<C, B, true> : (mocp_kernel_fn)moc_pivot_kernel<C, B, false>;
     PBE_PICK(DCOAL_OFF, DBR_TAB)
     PBE_PICK(DCOAL_OFF, DBR_CT)
     PBE_PICK(DCOAL_CT, DBR_TAB)
@@ -203,8 +203,9 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int64_t cap = (int64_t)m->ctx->sm_count * m->ctas_per_sm;
     const int grid = (int)std::min<int64_t>(nb, cap);
     if (m->pivot) {
-        mocp_kernel_fn fn = pick_pivot_kernel(m->dcoal, m->dbr);
-        void *args[] = {(void *)&p, (void *)&m->fpx};
+        mocp_kernel_fn fn = pick_pivot_kernel(m->dcoal, m->dbr, m->use_tmem);
+        int cols = m->tmem_cols;
+        void *args[] = {(void *)&p, (void *)&m->fpx, (void *)&cols};
         PBE_CUDA(raise_dyn_smem(m->ctx, (const void *)fn, m->smem));
         PBE_CUDA(cudaLaunchKernel((const void *)fn, dim3(grid), dim3(m->block), args, m->smem, st));
         m->ctx->launches++;
@@ -561,7 +562,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
             for (int j = 0; j < i; ++j)
                 PBE_REQUIRE(spec->coal_table[(size_t)i * N + j] == spec->coal_table[(size_t)j * N + i],
                             PBE_E_UNSUPPORTED, "pbe_moc_create_pivots: the tabulated coalescence kernel must be symmetric");
-    const size_t smem = mocp_smem_bytes(N);
+    size_t smem = mocp_smem_bytes(N);
     PBE_REQUIRE(smem <= ctx->smem_optin, PBE_E_UNSUPPORTED,
                 "pbe_moc_create_pivots: numberOfClasses %d needs %zu B of shared memory per CTA, device offers %zu", N,
                 smem, ctx->smem_optin);
@@ -702,14 +703,32 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
         b.brK = c2 * sg * ((1 + gm) * (1 + gm));
     }
     b.negK_floor = b.negKb_floor = -INFINITY;
+    // accumulators in tensor memory (two CTAs per SM) when they fit 256 columns and two CTAs' shared memory fits the SM
+    // (cudaOccupancyMaxActiveBlocksPerMultiprocessor cannot see tcgen05.alloc: the limit is computed here)
+    m->tmem_cols = moct_cols_per_thread(N);
+    const size_t smem_tm = mocp_smem_bytes(N, true);
+    m->use_tmem = m->dcoal != DCOAL_OFF && m->tmem_cols > 0 && 2 * (smem_tm + 1024) <= ctx->smem_per_sm &&
+                  2 * m->tmem_cols <= 512;
+    if (const char *f = getenv("PBE_MOC_PIVOT_KERNEL")) {
+        if (strcmp(f, "smem") == 0) m->use_tmem = false;
+    }
+    if (m->use_tmem) smem = smem_tm;
     m->block = m->smem_block = MOCP_BLOCK;
     m->smem = m->smem_bytes = smem;
-    const void *fn = (const void *)pick_pivot_kernel(m->dcoal, m->dbr);
+    const void *fn = (const void *)pick_pivot_kernel(m->dcoal, m->dbr, m->use_tmem);
     cudaError_t e = raise_dyn_smem(ctx, fn, smem);
     if (e == cudaSuccess) {
-        int occ = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, MOCP_BLOCK, smem);
-        m->ctas_per_sm = m->smem_ctas_per_sm = std::max(1, occ);
+        if (m->use_tmem) {
+            cudaFuncAttributes fa{};
+            e = cudaFuncGetAttributes(&fa, fn);
+            const int regs_per_warp = ((fa.numRegs * 32 + 255) / 256) * 256;
+            const int by_regs = 65536 / (regs_per_warp * (MOCP_BLOCK / 32));
+            m->ctas_per_sm = m->smem_ctas_per_sm = std::max(1, std::min(2, by_regs));
+        } else {
+            int occ = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, MOCP_BLOCK, smem);
+            m->ctas_per_sm = m->smem_ctas_per_sm = std::max(1, occ);
+        }
     }
     if (e == cudaSuccess && !tiles.empty()) {
         e = cudaMalloc(&m->d_fp, tiles.size() * sizeof(FpTile));
