@@ -294,6 +294,10 @@ __global__ void __launch_bounds__(256) mules_solve_kernel(const MulesParams p) {
 // 100 fields: per-thread loops over 4-8 fields with the addressing in registers, faces walked from the CSR,
 // 106-111 ms; the same with every per-face load made unconditional, 110 registers, 23 % occupancy: 109-116 ms;
 // the per-field kernels above: 135 ms.)
+// resident 256-thread CTAs per SM the fused kernels are compiled for (40 registers): 124 -> 110 ms at 160^3 x 100 fields
+#ifndef PBE_MULES_MINB
+#define PBE_MULES_MINB 6
+#endif
 #ifndef PBE_MULES_BX
 #define PBE_MULES_BX 32
 #endif
@@ -358,7 +362,7 @@ __device__ __forceinline__ double face_lambda(const FusedParams &q, int kc, int 
     if (f >= p.nint || kc >= q.kn) return;                                   \
     const int k = p.k0 + kc
 
-__global__ void __launch_bounds__(256) fused_grad_kernel(const FusedParams q) {
+__global__ void __launch_bounds__(256, PBE_MULES_MINB) fused_grad_kernel(const FusedParams q) {
     FUSED_CELL_THREAD();
     const double *psi = p.psi + (size_t)k * p.stride;
     const int64_t nf = p.nint + p.nbnd;
@@ -393,7 +397,7 @@ __global__ void __launch_bounds__(256) fused_grad_kernel(const FusedParams q) {
 }
 
 // per internal face: the unlimited correction phiCorr = fvc::flux(phi, psi, scheme) - upwind flux
-__global__ void __launch_bounds__(256) fused_corr_kernel(const FusedParams q) {
+__global__ void __launch_bounds__(256, PBE_MULES_MINB) fused_corr_kernel(const FusedParams q) {
     FUSED_FACE_THREAD();
     const double *psi = p.psi + (size_t)k * p.stride;
     const int32_t own = __ldg(p.owner + f), nei = __ldg(p.neigh + f);
@@ -421,7 +425,7 @@ __global__ void __launch_bounds__(256) fused_corr_kernel(const FusedParams q) {
 
 // per cell: the limiter's bounds (mules_bounds_kernel) and the cell half of sweep 1, where lambda is 1
 // (1.0 * phiCorr is phiCorr)
-__global__ void __launch_bounds__(256) fused_bounds_kernel(const FusedParams q) {
+__global__ void __launch_bounds__(256, PBE_MULES_MINB) fused_bounds_kernel(const FusedParams q) {
     FUSED_CELL_THREAD();
     const double *psi = p.psi + (size_t)k * p.stride;
     const double *corr = p.corr + (size_t)k * p.nint;
@@ -472,7 +476,7 @@ __global__ void __launch_bounds__(256) fused_bounds_kernel(const FusedParams q) 
 }
 
 // per cell: the cell half of sweep q.sweep >= 2, the lambdas of its faces rebuilt from sweeps 1 .. sweep-1
-__global__ void __launch_bounds__(256) fused_sweep_kernel(const FusedParams q) {
+__global__ void __launch_bounds__(256, PBE_MULES_MINB) fused_sweep_kernel(const FusedParams q) {
     FUSED_CELL_THREAD();
     const double *corr = p.corr + (size_t)k * p.nint;
     const int sw = q.sweep - 1; // row this sweep writes
@@ -497,7 +501,7 @@ __global__ void __launch_bounds__(256) fused_sweep_kernel(const FusedParams q) {
 }
 
 // per internal face and field: the face half of the last sweep, phiCorr *= lambda
-__global__ void __launch_bounds__(256) fused_final_kernel(const FusedParams q) {
+__global__ void __launch_bounds__(256, PBE_MULES_MINB) fused_final_kernel(const FusedParams q) {
     FUSED_FACE_THREAD();
     const int32_t own = __ldg(p.owner + f), nei = __ldg(p.neigh + f);
     double *corr = p.corr + (size_t)k * p.nint + f;
@@ -528,7 +532,7 @@ __global__ void __launch_bounds__(256) fused_limit_sum_kernel(int nfields, int64
 }
 
 // per cell and field: limitSum's scaling applied, phiPsi = phiCorr + upwind flux, MULES::explicitSolve
-__global__ void __launch_bounds__(256) fused_solve_kernel(const FusedParams q) {
+__global__ void __launch_bounds__(256, PBE_MULES_MINB) fused_solve_kernel(const FusedParams q) {
     FUSED_CELL_THREAD();
     const double *psi = p.psi + (size_t)k * p.stride;
     const double *corr = p.corr + (size_t)k * p.nint;
