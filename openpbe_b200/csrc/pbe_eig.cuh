@@ -278,7 +278,13 @@ PBE_HD bool jacobi3_firstrow(double (&d)[3], double (&e)[3], double (&z)[3]) {
 #if !defined(__CUDA_ARCH__) && defined(PBE_EIG_COUNT_FALLBACKS)
         ++jacobi3_fallbacks;
 #endif
-        return jacobi3_generic(d, e, z); // d, e still hold the input
+        // copies made HERE: handing the caller's arrays to the out-of-line function would pin them in local memory
+        // on the common path as well (STL / LDL per cell in the SASS of qmom_kernel)
+        double dg[3] = {a0, a1, a2}, eg[3] = {e0, e1, 0.0}, zg[3];
+        const bool okg = jacobi3_generic(dg, eg, zg);
+        d[0] = dg[0], d[1] = dg[1], d[2] = dg[2];
+        z[0] = zg[0], z[1] = zg[1], z[2] = zg[2];
+        return okg;
     }
     cswap_firstrow(d0, d1, z0, z1);
     cswap_firstrow(d1, dd2, z1, z2);
