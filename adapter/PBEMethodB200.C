@@ -172,8 +172,20 @@ MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     classMin_ = scalarField(numberOfClasses_, 0.0);
     forAll(classNumberDensity_, i) // MOC.C:69-77: fields n0 .. n<N-1>, MUST_READ, registered on the mesh
         classNumberDensity_.set(i, new volScalarField(fieldName("n", i), phase.mesh()));
-    b200Check(pbe_moc_create(ctx_, numberOfClasses_, deltaXi_.value(), &spec_, source_term_relaxation_, &moc_),
-              "MOC::MOC");
+    // EXTENSION (no counterpart in the reference's MOCCoeffs): classGridRatio r > 1 -> geometric class
+    // volumes xi1 r^i through the fixed-pivot technique; absent: the reference's uniform grid (i + 1) xi1 (MOC.C:56,79)
+    const scalar gridRatio = MOCDict_.lookupOrDefault<scalar>("classGridRatio", 0.0);
+    if (gridRatio > 0.0) {
+        if (!(gridRatio > 1.0))
+            FatalErrorIn("MOC::MOC") << "classGridRatio must be > 1 (got " << gridRatio << ")" << exit(FatalError);
+        std::vector<double> piv((size_t)numberOfClasses_);
+        forAll(classNumberDensity_, i) piv[(size_t)i] = (i == 0) ? deltaXi_.value() : piv[(size_t)i - 1] * gridRatio;
+        b200Check(pbe_moc_create_pivots(ctx_, numberOfClasses_, piv.data(), &spec_, source_term_relaxation_, &moc_),
+                  "MOC::MOC");
+    } else {
+        b200Check(pbe_moc_create(ctx_, numberOfClasses_, deltaXi_.value(), &spec_, source_term_relaxation_, &moc_),
+                  "MOC::MOC");
+    }
     const fvMesh &mesh = phase.mesh();
     b200Check(pbe_moc_state_create(moc_, mesh.nCells(), mesh.V().cdata(), &state_), "MOC::MOC");
     if (mesh.hasFaces()) {

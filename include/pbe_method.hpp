@@ -395,7 +395,18 @@ public:
         xi1_ = c.readScalar("xi1");
         usingMULES_ = c.lookupOrDefault<bool>("usingMULES", false);
         relax_ = c.lookupOrDefault<double>("sourceRelaxation", 1.0);
-        check(pbe_moc_create(ctx_.get(), N_, xi1_, &spec_, relax_, &h_), "MOC::MOC");
+        // EXTENSION (no counterpart in the reference's MOCCoeffs): `classGridRatio r` > 1 makes the
+        // class volumes geometric, xi_i = xi1 r^i, handled by the fixed-pivot technique (pbe_moc_create_pivots);
+        // absent, the grid is the reference's uniform one, xi_i = (i + 1) xi1 (MOC.C:56,79)
+        gridRatio_ = c.lookupOrDefault<double>("classGridRatio", 0.0);
+        if (gridRatio_ > 0.0) {
+            if (!(gridRatio_ > 1.0)) throw FatalError("MOC::MOC: classGridRatio must be > 1 (got " + std::to_string(gridRatio_) + ")");
+            std::vector<double> piv((size_t)N_);
+            for (int i = 0; i < N_; ++i) piv[(size_t)i] = (i == 0) ? xi1_ : piv[(size_t)i - 1] * gridRatio_;
+            check(pbe_moc_create_pivots(ctx_.get(), N_, piv.data(), &spec_, relax_, &h_), "MOC::MOC");
+        } else {
+            check(pbe_moc_create(ctx_.get(), N_, xi1_, &spec_, relax_, &h_), "MOC::MOC");
+        }
         const int64_t nc = phase.ncells;
         check(pbe_moc_state_create(h_, nc, phase.V, &state_), "MOC::MOC");
         if (n0) check(pbe_moc_state_upload(state_, nc, n0), "MOC::MOC");
@@ -444,7 +455,9 @@ public:
     }
     const std::vector<double> &d() const override { return d_host_; }
     int numberOfClasses() const { return N_; }
-    double xi(int i) const { return xi1_ * (i + 1); } // MOC.C:79
+    double xi(int i) const { // MOC.C:79, or the geometric extension
+        return gridRatio_ > 0.0 ? xi1_ * std::pow(gridRatio_, i) : xi1_ * (i + 1);
+    }
     // class field n<i>, host copy (runTime.write() of one field)
     std::vector<double> classNumberDensity(int i) const {
         const int64_t nc = phase_.ncells;
@@ -465,7 +478,7 @@ private:
     pbe_moc *h_ = nullptr;
     pbe_moc_state *state_ = nullptr;
     int N_ = 0;
-    double xi1_ = 0, relax_ = 1.0, continuityError_ = 0.0;
+    double xi1_ = 0, relax_ = 1.0, continuityError_ = 0.0, gridRatio_ = 0.0;
     bool usingMULES_ = false;
     pbe_mesh *mesh_ = nullptr;
     int scheme_ = 0;

@@ -104,6 +104,31 @@ def test_moc_correct_matches_oracle(shim, tmp_path, oracle):
 
 
 @pytest.mark.gpu
+def test_moc_geometric_grid_through_the_adapter(shim, tmp_path):
+    """MOCCoeffs { classGridRatio r; } -- the fixed-pivot extension (row f4, not a reference key) selected by
+    dictionary through diameterModel::New -> PBEMethod::New -> MOC, against the CPU restatement."""
+    from oracle import fixed_pivot as fp
+    w = synthetic.workload("moc30_ct", 2001)
+    f = synthetic.moc_fields(w)
+    ratio = 1.25
+    x = fp.geometric_pivots(w.N, w.xi1, ratio)
+    n0 = f["n"] * ((w.xi1 * (np.arange(w.N) + 1)) / x)[:, None]  # same volume per class on the new pivots
+    text = ("method methodOfClasses; MOCCoeffs { numberOfClasses %d; xi1 %r; classGridRatio %r; }" % (w.N, w.xi1, ratio)
+            + C01 % (tuple(w.coal_coeffs) + tuple(w.br_coeffs)))
+    p, out = run(shim, tmp_path, text, n0, f["eps"], f["rho"], f["nu"], f["alpha"], w.dt, steps=1)
+    assert p.returncode == 0, p.stdout + p.stderr
+    n, d, _ = out
+    spec = {"coalescence": w.coalescence, "coal_c": tuple(w.coal_coeffs), "breakup": w.breakup, "br_c": tuple(w.br_coeffs)}
+    S, scale = fp.moc_source(spec, x, w.relax, n0, f["eps"], f["rho"], f["nu"], w.dt)
+    n1 = n0 + w.dt * S
+    assert np.all(np.abs(n - n1) <= w.dt * 1e-12 * scale + 4e-16 * np.abs(n1))
+    np.testing.assert_allclose(d, ((6.0 / np.pi * x) ** (1.0 / 3.0) @ n1) / n1.sum(axis=0), rtol=1e-12)
+    p, _ = run(shim, tmp_path, text.replace("classGridRatio %r" % ratio, "classGridRatio 0.9"), n0, f["eps"], f["rho"],
+               f["nu"], f["alpha"], w.dt)
+    assert p.returncode == 1 and "classGridRatio must be > 1" in p.stdout
+
+
+@pytest.mark.gpu
 def test_qmom_correct_matches_oracle(shim, tmp_path, oracle):
     w = synthetic.workload("qmom3_ct", 2003)
     f = synthetic.qmom_fields(w)
