@@ -309,13 +309,14 @@ int pbe_moc_coeffs(pbe_moc *moc, double *xi1, double *source_relaxation);
  * pivots that bracket x_i + x_j with the number- and volume-preserving weights; breakup daughters
  * (uniformBinaryBreakup) are assigned through the same hat functions (volume exact).  On the uniform
  * volumes the coalescence terms are the reference's own.  pivots [N], strictly increasing, positive.
- * The handle works with pbe_moc_source / _step / _d / _class_minmax / _source_host and with the resident state's
- * zero-flux correct(); attaching a mesh to such a state and the MULES bound (which use xi1) take uniform grids
- * only (PBE_E_UNSUPPORTED otherwise). */
+ * The handle works with every pbe_moc_* entry, the resident state and its transport (continuity check, MULES bound
+ * maxNk = max(alpha V) / x_k) included. */
 int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_kernel_spec *spec,
                           double source_relaxation, pbe_moc **out);
 /* class volumes of the handle's grid ([N], may be NULL) and whether it is the reference's uniform one */
 int pbe_moc_grid(pbe_moc *moc, double *volumes, int *is_uniform);
+/* the same N volumes as a DEVICE array owned by the handle (read by the transport path's continuity check and bound) */
+int pbe_moc_grid_device(pbe_moc *moc, const double **volumes_dev);
 int pbe_moc_correct_host(pbe_moc *moc, pbe_mesh *mesh, int scheme, int64_t stride, double *n_host,
                          const double *eps_host, const double *rho_host, const double *nu_host,
                          const double *phi_host, const double *psi_b_host, int64_t stride_b,

@@ -96,6 +96,7 @@ PROTOTYPES = {
                                  C.POINTER(_vp)]),
     "pbe_moc_create_pivots": (C.c_int, [_vp, C.c_int, _dp, C.POINTER(KernelSpec), C.c_double, C.POINTER(_vp)]),
     "pbe_moc_grid": (C.c_int, [_vp, _dp, C.POINTER(C.c_int)]),
+    "pbe_moc_grid_device": (C.c_int, [_vp, C.POINTER(_vp)]),
     "pbe_moc_destroy": (C.c_int, [_vp]),
     "pbe_moc_set_kernel": (C.c_int, [_vp, C.c_int]),
     "pbe_moc_get_kernel": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -760,6 +760,14 @@ int pbe_moc_grid(pbe_moc *m, double *volumes, int *is_uniform) {
     return PBE_OK;
 }
 
+// DEVICE pointer to the N class volumes (the CLS_XI row of the handle's per-class table): what the continuity check
+// and the MULES bound of the transport path read, uniform grid or pivots alike
+int pbe_moc_grid_device(pbe_moc *m, const double **volumes_dev) {
+    PBE_REQUIRE(m != nullptr && volumes_dev != nullptr, PBE_E_INVALID, "pbe_moc_grid_device: NULL argument");
+    *volumes_dev = m->d_cls + (size_t)CLS_XI * (m->N + 1);
+    return PBE_OK;
+}
+
 int pbe_moc_get_kernel(pbe_moc *m, int *which, int *cells_per_cta, int *ctas_per_sm) {
     PBE_REQUIRE(m != nullptr, PBE_E_INVALID, "pbe_moc_get_kernel: NULL handle");
     if (which) *which = m->pivot ? PBE_MOC_KERNEL_PIVOT : (m->use_tmem ? PBE_MOC_KERNEL_TMEM : PBE_MOC_KERNEL_SMEM);

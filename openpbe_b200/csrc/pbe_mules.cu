@@ -575,9 +575,9 @@ __global__ void __launch_bounds__(256) max_product_kernel(int64_t n, const doubl
     // non-negative doubles order like their bit patterns
     if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));
 }
-__global__ void moc_psi_max_kernel(int N, double xi1, const double *maxAV, double *out) {
+__global__ void moc_psi_max_kernel(int N, const double *__restrict__ xi_k, const double *maxAV, double *out) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k < N) out[k] = maxAV[0] / (xi1 * (k + 1)); // max(alpha V / xi_k) = max(alpha V) / xi_k (monotone rounding)
+    if (k < N) out[k] = maxAV[0] / xi_k[k]; // max(alpha V / xi_k) = max(alpha V) / xi_k (monotone rounding)
 }
 __global__ void qmom_psi_max_kernel(int nm, int64_t ncells, int64_t stride, const double *__restrict__ m,
                                     int64_t nbnd, int64_t stride_b, const double *__restrict__ psi_b, double *out) {
@@ -791,12 +791,11 @@ int pbe_moc_psi_max(pbe_moc *moc, int64_t ncells, const double *alpha, const dou
     int N = 0;
     pbe_ctx *ctx = nullptr;
     double xi1 = 0.0;
-    int uniform = 1;
-    if (moc != nullptr) pbe_moc_grid(moc, nullptr, &uniform);
-    PBE_REQUIRE(uniform, PBE_E_UNSUPPORTED, "pbe_moc_psi_max: uniform class grid only");
     int rc = pbe_moc_num_classes(moc, &N, &ctx);
     if (rc) return rc;
     pbe_moc_coeffs(moc, &xi1, nullptr);
+    const double *xi_dev = nullptr;
+    pbe_moc_grid_device(moc, &xi_dev);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     double *tmp = nullptr;
@@ -804,7 +803,7 @@ int pbe_moc_psi_max(pbe_moc *moc, int64_t ncells, const double *alpha, const dou
     PBE_CUDA(cudaMemsetAsync(tmp, 0, sizeof(double), st));
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((ncells + 255) / 256, (int64_t)ctx->sm_count * 8));
     max_product_kernel<<<grid, 256, 0, st>>>(ncells, alpha, vcell, (unsigned long long *)tmp);
-    moc_psi_max_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, xi1, tmp, psi_max);
+    moc_psi_max_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, xi_dev, tmp, psi_max);
     PBE_CUDA(cudaGetLastError());
     PBE_CUDA(cudaFreeAsync(tmp, st));
     ctx->launches += 2;

@@ -163,7 +163,8 @@ int stats_parts(pbe_ctx *ctx, int64_t ncells) {
 // Continuity check and global moments of the class fields after a transport update (the zero-flux
 // step kernel fuses them): err = max_c |sum_k xi_k n_k / V - alpha| (MOC.C:254-279), moments[q] +=
 // sum_c V_c sum_k xi_k^q n_k.  One thread per cell; block reduction, one atomic per CTA per value.
-__global__ void __launch_bounds__(256) moc_continuity_kernel(int N, int64_t ncells, int64_t stride, double xi1,
+__global__ void __launch_bounds__(256) moc_continuity_kernel(int N, int64_t ncells, int64_t stride,
+                                                             const double *__restrict__ xi_k, // [N] class volumes
                                                              const double *__restrict__ n,
                                                              const double *__restrict__ alpha,
                                                              const double *__restrict__ vcell, int n_moments,
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(256) moc_continuity_kernel(int N, int64_t ncel
         double vol = 0.0;
         for (int k = 0; k < N; ++k) {
             const double v = __ldg(n + (size_t)k * stride + c);
-            const double xi = xi1 * (k + 1); // MOC.C:79
+            const double xi = __ldg(xi_k + k); // (k + 1) xi1 on the reference's grid (MOC.C:79), or the pivot
             vol += xi * v;                   // volumeSum += xi_k N_k, MOC.C:272
             double pw = v;
             for (int q = 0; q < n_moments; ++q) {
@@ -242,6 +243,7 @@ struct pbe_moc_state {
     pbe_ctx *ctx = nullptr;
     int N = 0;
     double xi1 = 0.0;
+    const double *xi_dev = nullptr; // class volumes, owned by the pbe_moc handle
     int64_t nc = 0;
     int64_t quantum = 1; // cells of one wave of the persistent grid
     double *n = nullptr, *eps = nullptr, *rho = nullptr, *nu = nullptr, *alpha = nullptr, *vcell = nullptr,
@@ -404,7 +406,7 @@ int moc_correct_impl(pbe_moc_state *s, const double *eps_h, const double *rho_h,
         }
         if (want_cont || nmom > 0) {
             const int grid = (int)std::min<int64_t>((nc + 255) / 256, (int64_t)ctx->sm_count * 8);
-            moc_continuity_kernel<<<grid, 256, 0, P.s_comp>>>(N, nc, nc, s->xi1, s->n, want_cont ? s->alpha : nullptr,
+            moc_continuity_kernel<<<grid, 256, 0, P.s_comp>>>(N, nc, nc, s->xi_dev, s->n, want_cont ? s->alpha : nullptr,
                                                               s->have_vcell ? s->vcell : nullptr, nmom, mom_dev,
                                                               cont_dev);
             PBE_CUDA(cudaGetLastError());
@@ -471,6 +473,7 @@ int pbe_moc_state_create(pbe_moc *moc, int64_t ncells, const double *vcell_host,
     s->nc = ncells;
     s->quantum = (int64_t)block * ctx->sm_count * ctas;
     pbe_moc_coeffs(moc, &s->xi1, nullptr);
+    pbe_moc_grid_device(moc, &s->xi_dev);
     const size_t cells = (size_t)std::max<int64_t>(ncells, 1);
     cudaError_t e = cudaMalloc((void **)&s->n, (size_t)N * cells * 8);
     for (double **p : {&s->eps, &s->rho, &s->nu, &s->alpha, &s->vcell, &s->d})
@@ -564,13 +567,6 @@ int pbe_moc_state_device(pbe_moc_state *s, double **n_dev, int64_t *stride, doub
 }
 
 int pbe_moc_state_attach_mesh(pbe_moc_state *s, pbe_mesh *mesh, int scheme) {
-    {
-        int uniform = 1;
-        if (s != nullptr && s->moc != nullptr) pbe_moc_grid(s->moc, nullptr, &uniform);
-        PBE_REQUIRE(uniform, PBE_E_UNSUPPORTED,
-                    "pbe_moc_state_attach_mesh: transport of a fixed-pivot state is not built (continuity check and MULES "
-                    "bound use the uniform class grid); the zero-flux resident correct() works on any grid");
-    }
     PBE_REQUIRE(s && mesh, PBE_E_INVALID, "pbe_moc_state_attach_mesh: NULL argument");
     int64_t mc = 0, nint = 0, nbnd = 0;
     int rc = pbe_mesh_info(mesh, &mc, &nint, &nbnd, nullptr);

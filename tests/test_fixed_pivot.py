@@ -142,11 +142,39 @@ def test_device_errors(ctx):
         moc.set_kernel("smem")
     st = engine.MOCState(moc, 10)  # the zero-flux resident state takes any grid
     st.close()
-    from openpbe_b200 import synthetic
-    m = synthetic.block_mesh(3, 2, 2)
-    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
-    with pytest.raises(capi.PbeError, match="fixed-pivot state"):
-        engine.MOCState(moc, 12, vcell=m["vcell"], mesh=mesh)
+
+
+@gpu
+@pytest.mark.parametrize("scheme", ["Gauss upwind", "Gauss vanLeer"])
+def test_resident_correct_with_transport_on_a_geometric_grid(ctx, scheme):
+    """solveWithMULES on fixed pivots: the continuity check and the MULES bound maxNk = max(alpha V) / x_k read the
+    handle's class volumes.  Given the device's own sources the transport is bit-identical to the C restatement."""
+    import torch
+    from openpbe_b200 import engine, synthetic
+    from oracle import cpu_oracle as orc
+    tm = synthetic.block_mesh(9, 8, 6, velocity=(1.0, -0.5, 0.25))
+    nc, N, dt = 9 * 8 * 6, 16, 0.01
+    rng = np.random.default_rng(5)
+    x = fp.geometric_pivots(N, 1e-3, 1.35)
+    n, eps, rho, nu = fields(rng, N, nc, x)
+    n *= 1.0 + 3.0 * np.sin(np.arange(nc) * 0.7)[None, :] ** 2
+    alpha = (x @ n) / tm["vcell"] * rng.uniform(0.9, 1.1, nc)
+    moc = _dev(ctx, CONST, x)
+    mesh = engine.Mesh(ctx, tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"])
+    mesh.set_geometry(tm["Sf"], tm["C"], tm["weights"])
+    st = engine.MOCState(moc, nc, vcell=tm["vcell"], n0=n, mesh=mesh, scheme=scheme)
+    d, diag = st.correct(eps, rho, nu, alpha, dt, phi=tm["phi"], minmax=True, n_moments=2)
+    n_g = st.download().numpy()
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    S_dev = moc.source(T(n), T(eps), T(rho), T(nu), dt).cpu().numpy()
+    pmax = np.array([np.max(alpha * tm["vcell"] / xk) for xk in x])
+    want = orc.transport_mules(tm, scheme, n, tm["phi"], dt, pmax, S=S_dev)
+    assert np.array_equal(n_g, want)
+    want_S, scale = fp.moc_source(CONST, x, 1.0, n, eps, rho, nu, dt)
+    assert np.all(np.abs(S_dev - want_S) <= 1e-12 * scale + 1e-300)
+    assert diag["cont_err_max"] == pytest.approx(np.abs((x @ n_g) / tm["vcell"] - alpha).max(), rel=1e-9)
+    np.testing.assert_allclose(diag["moments"], [(n_g.sum(axis=0) * tm["vcell"]).sum(), ((x @ n_g) * tm["vcell"]).sum()], rtol=1e-11)
+    st.close(); mesh.close(); moc.close()
 
 
 @gpu
