@@ -193,3 +193,53 @@ def test_full_size_wheeler_round_trip(ctx):
     back = torch.stack([(w * x ** k).sum(0) for k in range(6)])
     assert float(((back - m).abs() / m).max()) < 1e-8
     assert float(((x - nodes).abs() / nodes).max()) < 1e-5
+
+
+def test_large_fixed_pivot_conserves_volume_and_scales(ctx):
+    """Fixed-pivot kernel (row f4) at N = 100 on a geometric grid, 3e5 cells: the two-pivot redistribution
+    conserves the volume of every coalescence event (sum_i x_i C_i = 0 against the gross volume exchanged), the
+    operator is exactly quadratic (powers of two commute with every rounding), breakup conserves volume."""
+    w = synthetic.workload("moc100_ct")
+    nc = 300_000
+    n, eps, rho, nu, _ = _device_moc_fields(w, nc, seed=4)
+    x = w.xi1 * 1.08 ** np.arange(w.N)
+    xd = T(x)
+    coal = engine.MOC(ctx, w.N, 0.0, engine.make_spec(w.coalescence, w.coal_coeffs), 1e300, pivots=x)
+    assert coal.kernel()["kernel"] == "pivot"
+    S = coal.source(n, eps, rho, nu, w.dt)
+    net = torch.einsum("i,ic->c", xd, S)
+    gross = torch.einsum("i,ic->c", xd, S.abs())
+    assert float((net.abs() / (gross + 1e-300)).max()) < 1e-11 and bool(torch.isfinite(S).all())
+    assert bool((S[0] <= 0).all())  # the smallest class can only lose drops to coalescence
+    S2 = coal.source(n * 2.0, eps, rho, nu, w.dt)
+    assert bool((S2 == 4.0 * S).all())
+    br = engine.MOC(ctx, w.N, 0.0, engine.make_spec("noCoalescence", (), w.breakup, w.br_coeffs), 1e300, pivots=x)
+    B = br.source(n, eps, rho, nu, w.dt)
+    netb = torch.einsum("i,ic->c", xd, B)
+    grossb = torch.einsum("i,ic->c", xd, B.abs())
+    assert float((netb.abs() / (grossb + 1e-300)).max()) < 1e-11
+    assert bool((br.source(n * 2.0, eps, rho, nu, w.dt) == 2.0 * B).all())
+
+
+def test_large_mules_update_is_bounded_and_form_independent(ctx, monkeypatch):
+    """MULES-limited transport (Gauss vanLeer, 3 limiter sweeps, limitSum) on a 96^3 block x 8 fields: the update
+    stays inside [psiMin, psiMax] (what the limiter is for), and the fused kernels give bit for bit what the
+    per-field kernels give."""
+    nx = 96
+    m = synthetic.block_mesh(nx, nx, nx, velocity=(1.0, 0.5, 0.25))
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    mesh.set_geometry(m["Sf"], m["C"], m["weights"])
+    nc, K = nx ** 3, 8
+    g = torch.Generator(device="cuda").manual_seed(11)
+    psi = torch.rand(K, nc, dtype=torch.float64, device="cuda", generator=g)
+    psi *= (torch.rand(K, nc, dtype=torch.float64, device="cuda", generator=g) > 0.3)  # sharp fronts
+    pmax = torch.full((K,), 1.0, dtype=torch.float64, device="cuda")
+    phi = T(m["phi"])
+    dt = 0.3 / (nx * 1.75)
+    out = mesh.transport_mules(psi, phi, dt, pmax)
+    assert bool(torch.isfinite(out).all())
+    assert float(out.min()) >= -1e-12 and float(out.max()) <= 1.0 + 1e-12
+    monkeypatch.setenv("PBE_MULES_PATH", "0")
+    ref = mesh.transport_mules(psi, phi, dt, pmax)
+    assert bool((out == ref).all())
+    mesh.close()
