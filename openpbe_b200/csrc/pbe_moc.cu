@@ -48,6 +48,7 @@ struct pbe_moc {
     FpTile *d_fp = nullptr;
     double *d_fpw = nullptr; // [3][N]: hat areas, self shares, 2 / x_k
     MocFpExtra fpx{};
+    int pivot_win = 8; // birth-window width the pivot kernel is instantiated for (6 or MOCP_WIN)
 };
 
 namespace {
@@ -88,9 +89,14 @@ moct_kernel_fn pick_tmem_kernel(int dcoal, int dbr, bool wide) {
 }
 
 typedef void (*mocp_kernel_fn)(const MocParams, const MocFpExtra, const int);
-mocp_kernel_fn pick_pivot_kernel(int dcoal, int dbr, bool tm) {
-#define PBE_PICK(C, B) \
-    if (dcoal == C && dbr == B) return tm ? (mocp_kernel_fn)moc_pivot_kernel<C, B, true> : (mocp_kernel_fn)moc_pivot_kernel<C, B, false>;
+mocp_kernel_fn pick_pivot_kernel(int dcoal, int dbr, bool tm, int win = MOCP_WIN) {
+#define PBE_PICK(C, B)                                                                                                  \
+    if (dcoal == C && dbr == B) {                                                                                       \
+        if (win <= 6)                                                                                                   \
+            return tm ? (mocp_kernel_fn)moc_pivot_kernel<C, B, true, 6> : (mocp_kernel_fn)moc_pivot_kernel<C, B, false, 6>; \
+        return tm ? (mocp_kernel_fn)moc_pivot_kernel<C, B, true, MOCP_WIN>                                              \
+                  : (mocp_kernel_fn)moc_pivot_kernel<C, B, false, MOCP_WIN>;                                            \
+    }
     PBE_PICK(DCOAL_OFF, DBR_TAB)
     PBE_PICK(DCOAL_OFF, DBR_CT)
     PBE_PICK(DCOAL_CT, DBR_TAB)
@@ -203,7 +209,7 @@ int launch(pbe_moc *m, MocParams &p, cudaStream_t st) {
     const int64_t cap = (int64_t)m->ctx->sm_count * m->ctas_per_sm;
     const int grid = (int)std::min<int64_t>(nb, cap);
     if (m->pivot) {
-        mocp_kernel_fn fn = pick_pivot_kernel(m->dcoal, m->dbr, m->use_tmem);
+        mocp_kernel_fn fn = pick_pivot_kernel(m->dcoal, m->dbr, m->use_tmem, m->pivot_win);
         int cols = m->tmem_cols;
         void *args[] = {(void *)&p, (void *)&m->fpx, (void *)&cols};
         PBE_CUDA(raise_dyn_smem(m->ctx, (const void *)fn, m->smem));
@@ -617,6 +623,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
     // tiles of MOCP_TI x MOCP_TJ pairs (rows i0.., columns j0..) whose births fit one window of MOCP_WIN pivots; a tile
     // whose window would overflow is cut into row tiles, and those into single pairs (any increasing grid works)
     std::vector<FpTile> tiles;
+    int win_used = 2; // widest birth window any tile needs
     {
         std::vector<int> pidx((size_t)N * N, -1); // (i, j) -> index into pairs
         for (size_t q = 0; q < pairs.size(); ++q) pidx[(size_t)pairs[q].i * N + pairs[q].j] = (int)q;
@@ -635,6 +642,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
             if (tmax - tmin > MOCP_WIN - 2) return false;
             FpTile T{};
             T.i0 = i0, T.j0 = j0, T.tb = tmin, T.npairs = cnt;
+            win_used = std::max(win_used, tmax - tmin + 2);
             for (int r = r_lo; r < r_hi; ++r)
                 for (int c = c_lo; c < c_hi; ++c) {
                     const int i = i0 + r, j = j0 + c;
@@ -666,6 +674,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
         tiles.push_back(T);
     }
     if (pairs.empty()) m->dcoal = DCOAL_OFF;
+    m->pivot_win = (win_used <= 6 && !(getenv("PBE_MOC_PIVOT_WIN8"))) ? 6 : MOCP_WIN;
 
     MocParams &b = m->base;
     b.N = N;
@@ -715,7 +724,7 @@ int pbe_moc_create_pivots(pbe_ctx *ctx, int N, const double *pivots, const pbe_k
     if (m->use_tmem) smem = smem_tm;
     m->block = m->smem_block = MOCP_BLOCK;
     m->smem = m->smem_bytes = smem;
-    const void *fn = (const void *)pick_pivot_kernel(m->dcoal, m->dbr, m->use_tmem);
+    const void *fn = (const void *)pick_pivot_kernel(m->dcoal, m->dbr, m->use_tmem, m->pivot_win);
     cudaError_t e = raise_dyn_smem(ctx, fn, smem);
     if (e == cudaSuccess) {
         if (m->use_tmem) {

@@ -76,7 +76,10 @@ __host__ __device__ inline size_t mocp_smem_bytes(int N, bool tm = false) {
 // TM: the per-cell source accumulators live in TENSOR MEMORY (class c in columns 2c, 2c+1 of the thread's lane, as
 // in pbe_moc_tmem_kernel.cuh) instead of shared memory: the CTA's shared memory halves and two CTAs share an SM --
 // two warps per scheduler for a loop that one warp runs at half rate.  tmem_cols: columns to allocate (power of 2).
-template <int COAL, int BR, bool TM>
+// WIN: the part of the MOCP_WIN-wide birth window the grid's tiles actually use (6 on geometric grids of ratio
+// >= ~1.06, where a 4 x 4 tile spans at most five pivots; 8 on the uniform grid): unused weight columns are neither
+// loaded nor multiplied.
+template <int COAL, int BR, bool TM, int WIN>
 __global__ void __launch_bounds__(MOCP_BLOCK, TM ? 2 : 1)
     moc_pivot_kernel(const __grid_constant__ MocParams p, const __grid_constant__ MocFpExtra x, const int tmem_cols) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -253,7 +256,7 @@ __global__ void __launch_bounds__(MOCP_BLOCK, TM ? 2 : 1)
                         // this loop it cuts the tile into 16 basic blocks and serialises the exponentials (25.2 ms),
                         // after the loop 16 branch round trips per tile remain (21.4 ms); the weights: 14.8 ms.
 #pragma unroll
-                        for (int ww = 0; ww < MOCP_WIN; ++ww) bw[ww] = fma_(T.cw[k][ww], tt, bw[ww]);
+                        for (int ww = 0; ww < WIN; ++ww) bw[ww] = fma_(T.cw[k][ww], tt, bw[ww]);
                     }
                 }
                 if (TM) {
@@ -268,10 +271,10 @@ __global__ void __launch_bounds__(MOCP_BLOCK, TM ? 2 : 1)
                         tmem_st4(a_bw + 8u, tv[2]);
                     } else {
                         switch (dwin) { // births at window offset dwin .. dwin + 7 of the 12 loaded classes
-                        case 0: tm_window_add<0, MOCP_WIN, 3>(tv, bw); break;
-                        case 1: tm_window_add<1, MOCP_WIN, 3>(tv, bw); break;
-                        case 2: tm_window_add<2, MOCP_WIN, 3>(tv, bw); break;
-                        default: tm_window_add<3, MOCP_WIN, 3>(tv, bw); break;
+                        case 0: tm_window_add<0, WIN, 3>(tv, bw); break;
+                        case 1: tm_window_add<1, WIN, 3>(tv, bw); break;
+                        case 2: tm_window_add<2, WIN, 3>(tv, bw); break;
+                        default: tm_window_add<3, WIN, 3>(tv, bw); break;
                         }
                         tmem_st4(a_dj, tv[0]);
                         tmem_st4(a_dj + 8u, tv[1]);
@@ -286,15 +289,15 @@ __global__ void __launch_bounds__(MOCP_BLOCK, TM ? 2 : 1)
 #pragma unroll
                 for (int c = 0; c < MOCP_TJ; ++c) sv[jrow[c]] = cj[c] - dj[c];
                 // births: the window tb .. tb + WIN - 1, one batch of read-modify-writes
-                double cur[MOCP_WIN];
-                int wrow[MOCP_WIN];
+                double cur[WIN];
+                int wrow[WIN];
 #pragma unroll
-                for (int w = 0; w < MOCP_WIN; ++w) {
+                for (int w = 0; w < WIN; ++w) {
                     wrow[w] = min(tb + w, N) * BLOCK + tid; // past the grid: weights are 0, the dummy row takes them
                     cur[w] = sv[wrow[w]];
                 }
 #pragma unroll
-                for (int w = 0; w < MOCP_WIN; ++w) sv[wrow[w]] = cur[w] + bw[w];
+                for (int w = 0; w < WIN; ++w) sv[wrow[w]] = cur[w] + bw[w];
               }
               __syncthreads(); // every warp is done with this ring slot
               if (tid == 0 && qq + NSLOT < total_q) issue(qq + NSLOT);
