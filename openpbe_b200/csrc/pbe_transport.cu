@@ -38,6 +38,9 @@
 #ifndef PBE_TR_CTAS
 #define PBE_TR_CTAS 4
 #endif
+#ifndef PBE_TR_DIRECT_OWN
+#define PBE_TR_DIRECT_OWN 1 // own value and source through registers instead of the shared-memory stage: 2.66 -> 2.55 ms
+#endif
 #ifndef PBE_TR_STAGES
 #define PBE_TR_STAGES 2 // 0: register-staged loop; 2..4: cp.async pipeline depth (measured: 2, 3, 4 alike)
 #endif
@@ -218,6 +221,39 @@ __device__ __forceinline__ void sweep_async(const TransportParams &p, int c, int
     auto cp8 = [](uint32_t dst, const double *src) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
     };
+    if constexpr (PBE_TR_DIRECT_OWN != 0 && D == 2) {
+    // The cell's own value and its source are coalesced streams that nobody else reads: they go through registers
+    // (one field ahead), only the F gathered values through the shared-memory stage -- two copies and two read-backs
+    // fewer per cell-field on the load-store pipe, which is what bounds this kernel (ncu: L1/TEX 80 % busy).
+    double mine_n = 0.0, su_n = 0.0;
+    auto issue = [&](int k) {
+        if (k < nk) {
+            const uint32_t d = sm0 + (uint32_t)(k % D) * kStageBytes;
+#pragma unroll
+            for (int s = 0; s < F; ++s) cp8(d + (uint32_t)(1 + s) * 256u * 8u, slot_addr<F, BND>(cf, s, row, brow));
+            mine_n = __ldg(row + c);
+            if (srow != nullptr) {
+                su_n = __ldg(srow + c);
+                srow += p.stride;
+            }
+            row += p.stride;
+            if (BND) brow += p.stride_b;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    issue(0);
+    for (int k = 0; k < nk; ++k, orow += p.stride) {
+        const double mine = mine_n, Su = su_n;
+        issue(k + 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(D - 1) : "memory");
+        const double *st = tr_sm + (size_t)(k % D) * ((F + 2) * 256) + tid;
+        double acc = 0.0;
+#pragma unroll
+        for (int s = 0; s < F; ++s) acc = add_slot<F, BND>(acc, cf, s, mine, st[(1 + s) * 256]);
+        __stcs(orow + c, updated(p, mine, Su, acc, V, rV));
+    }
+    return;
+    }
     auto issue = [&](int k) {
         if (k < nk) {
             const uint32_t d = sm0 + (uint32_t)(k % D) * kStageBytes;
@@ -744,7 +780,7 @@ int pbe_transport_explicit_part(pbe_mesh *m, int scheme, int which, int nfields,
         if (have_regular) PBE_CUDA(cudaEventRecord(m->ev_join, is));
     }
     if (have_regular) {
-        int start = 25;
+        int start = 50; // 160^3 x 100 fields: 25 -> 2.61 ms, 50 -> 2.55 ms, 100 -> slower (fewer CTAs per wave of rows)
         if (const char *e = getenv("PBE_TRANSPORT_CHUNK")) start = std::max(1, atoi(e));
         const int64_t blocks = (m->ncells + 255) / 256;
         p.chunk = chunk_for(blocks, start);
