@@ -70,7 +70,10 @@ int pbe_daughter_type(const char *type_name, int *out);
 const char *pbe_last_error(void);
 int pbe_version(void);
 
-/* ---- context: one per (process, device).  Owns streams, staging buffers, workspaces. --- */
+/* ---- context: one per (process, device).  Owns streams, staging buffers, workspaces. ---
+ * Every handle created on a context (pbe_moc, pbe_qmom, pbe_mom, pbe_mesh, pbe_*_state) keeps a pointer to it:
+ * destroy the handles BEFORE the context, as the reference's members are destroyed before the object that owns
+ * them (PBEMethod.H:69-73).  A handle destroyed after its context reads freed memory. */
 typedef struct pbe_ctx pbe_ctx;
 int pbe_ctx_create(int device, pbe_ctx **out);
 int pbe_ctx_destroy(pbe_ctx *ctx);

@@ -90,10 +90,23 @@ class Context:
     def __init__(self, device: int = 0):
         self._h = C.c_void_p()
         self.device = int(device)
+        self._deps = []  # weak references to the handles created on this context, in creation order
         capi.check(capi.lib().pbe_ctx_create(self.device, C.byref(self._h)))
+
+    def _adopt(self, obj):
+        """Handles (methods, meshes, resident states) hold a pointer to the C context: the C ABI wants them destroyed
+        BEFORE it (include/pbe_b200.h).  close() therefore closes what is still alive first, newest first -- a handle
+        that the garbage collector reaches after its context would otherwise read freed memory in its destructor."""
+        import weakref
+        self._deps.append(weakref.ref(obj))
 
     def close(self):
         if self._h:
+            for r in reversed(self._deps):
+                o = r()
+                if o is not None:
+                    o.close()
+            self._deps = []
             capi.lib().pbe_ctx_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -207,6 +220,7 @@ class MOC:
         """pivots: class volumes of a geometric / arbitrary grid (fixed-pivot extension, row f4; xi1 is
         then ignored); None: the reference's uniform grid (i + 1) xi1."""
         self.ctx = ctx
+        ctx._adopt(self)
         self.N = int(numberOfClasses)
         self._h = C.c_void_p()
         if pivots is not None:
@@ -337,6 +351,7 @@ class MOCState:
 
     def __init__(self, moc: "MOC", ncells: int, vcell=None, n0=None, mesh: "Mesh" = None, scheme="upwind"):
         self.moc, self.ncells = moc, int(ncells)
+        moc.ctx._adopt(self)  # created after its method and mesh: closed before them
         self._h = C.c_void_p()
         self._mesh = mesh  # keep alive
         capi.check(capi.lib().pbe_moc_state_create(moc._h, self.ncells, _hptr(vcell), C.byref(self._h)))
@@ -415,6 +430,7 @@ class QMOMState:
 
     def __init__(self, q: "QMOM", ncells: int, vcell=None, m0=None, mesh: "Mesh" = None, scheme="upwind"):
         self.q, self.ncells = q, int(ncells)
+        q.ctx._adopt(self)
         self._h = C.c_void_p()
         self._mesh = mesh
         capi.check(capi.lib().pbe_qmom_state_create(q._h, self.ncells, _hptr(vcell), C.byref(self._h)))
@@ -484,6 +500,7 @@ class QMOM:
 
     def __init__(self, ctx: Context, quadratureOrder: int, spec: capi.KernelSpec):
         self.ctx = ctx
+        ctx._adopt(self)
         self.order = int(quadratureOrder)
         self._h = C.c_void_p()
         capi.check(capi.lib().pbe_qmom_create(ctx.handle, self.order, C.byref(spec), C.byref(self._h)))
@@ -533,6 +550,7 @@ class MOM:
 
     def __init__(self, ctx: Context, spec: capi.KernelSpec, panels: int = 0):
         self.ctx = ctx
+        ctx._adopt(self)
         self._h = C.c_void_p()
         capi.check(capi.lib().pbe_mom_create(ctx.handle, int(panels), C.byref(spec), C.byref(self._h)))
 
@@ -588,6 +606,7 @@ class Mesh:
 
     def __init__(self, ctx: Context, owner, neighbour, boundary_owner, vcell):
         self.ctx = ctx
+        ctx._adopt(self)
         own = np.ascontiguousarray(owner, dtype=np.int32)
         nei = np.ascontiguousarray(neighbour, dtype=np.int32)
         bown = np.ascontiguousarray(boundary_owner, dtype=np.int32)

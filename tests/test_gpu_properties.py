@@ -219,6 +219,8 @@ def test_large_fixed_pivot_conserves_volume_and_scales(ctx):
     grossb = torch.einsum("i,ic->c", xd, B.abs())
     assert float((netb.abs() / (grossb + 1e-300)).max()) < 1e-11
     assert bool((br.source(n * 2.0, eps, rho, nu, w.dt) == 2.0 * B).all())
+    coal.close()
+    br.close()
 
 
 def test_large_mules_update_is_bounded_and_form_independent(ctx, monkeypatch):

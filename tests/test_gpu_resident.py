@@ -348,3 +348,28 @@ def test_comm_through_the_c_abi_single_rank(ctx):
         capi.check(L.pbe_comm_init(c2.handle, 1, 0, ident))
     capi.check(L.pbe_comm_destroy(c2.handle))
     c2.close()
+
+
+@pytest.mark.gpu
+def test_context_close_closes_live_handles_first():
+    """The C ABI wants handles destroyed before their context.  The Python wrapper enforces it: Context.close() closes
+    what is still alive (states before methods and meshes), so a handle collected later never touches a freed
+    context -- the failure mode was a stray cudaSetDevice(garbage) surfacing as CUDA error 101 in an unrelated call."""
+    import torch
+    from openpbe_b200 import engine, synthetic
+    c = engine.Context(0)
+    w = synthetic.workload("moc30_ct", 500)
+    f = synthetic.moc_fields(w)
+    moc = engine.MOC(c, w.N, w.xi1, engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs))
+    q = engine.QMOM(c, 3, engine.make_spec("constantCoalescence", (1.0,), "noBreakup", ()))
+    st = engine.MOCState(moc, 500, n0=f["n"])
+    c.close()  # handles still referenced
+    assert not moc._h and not q._h and not st._h
+    moc.close(); st.close(); q.close()  # idempotent
+    del moc, q, st
+    import gc
+    gc.collect()
+    c2 = engine.Context(0)
+    x, wts = c2.wheeler_batch(torch.tensor([[1.0] * 8, [2.0] * 8], dtype=torch.float64, device="cuda"))
+    assert torch.allclose(x, torch.full_like(x, 2.0))
+    c2.close()
