@@ -957,7 +957,7 @@ def leg_geometric(B: Bench, w):
                         "6 fused moments", "kernel": info,
             "roofline": {"bound": "fp64", "achieved": gtf, "peak": B.fp64_tf, "unit": "TFLOP/s",
                          "frac": gtf / B.fp64_tf, "flops_per_cell": gflops, "traffic": None,
-                         "note": "tiles of four pairs, register birth window, accumulators in shared memory: one CTA per SM (DESIGN.md 4.8)"}}
+                         "note": "4x4 pair tiles through a TMA-fed ring, register birth window, accumulators in tensor memory: two CTAs per SM (DESIGN.md 4.8)"}}
 
 
 def leg_transport(B: Bench, w, moc):
