@@ -294,6 +294,50 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
                            int64_t stride_b, const double *S, double dt, double *psi_out,
                            void *cuda_stream);
 
+/* ---- the implicit path: MOC::solveWithFVM (MOC.C:186-198), QMOM::solveWithFVM (QMOM.C:201-209) -- the
+ * reference's DEFAULT transport (usingMULES false, MOC.C:58, QMOM.C:71):
+ *     fvScalarMatrix eqn(fvm::ddt(psi_k) + fvm::div(phi, psi_k) == S_k);  eqn.relax();  eqn.solve();
+ * Euler implicit ddt (diag = rDeltaT V, source = rDeltaT psi0 V), Gauss convection with the scheme's weights
+ * (lower = -w phi, upper = lower + phi, diag = -(sums), gaussConvectionScheme::fvmDiv); zero-gradient patches add
+ * phi_b to the diagonal, fixed-value patches -phi_b psi_b to the source; fvMatrix::relax(factor) (diagonal dominance,
+ * D / factor, source += (D - D0) psi0) when relaxation > 0.  One matrix serves all nfields fields for
+ * PBE_DIV_UPWIND; the limited schemes take their per-field weights from the current field, as
+ * limitedScheme::weights does.  OpenFOAM solves field after field with the solver fvSolution names (PBiCG + DILU or
+ * smoothSolver symGaussSeidel in the reference's cases -- sequential sweeps); here ALL fields are solved together by
+ * Jacobi sweeps or a diagonally preconditioned BiCGStab whose vector updates and matrix-vector products run over
+ * [nfields][ncells] at once, each field with its own scalars, stopped by OpenFOAM's own criterion: normalised residual
+ * sum|b - Ax| / (sum(|Ax - xbar A1| + |b - xbar A1|) + 1e-20) < tolerance, or < rel_tol x initial, after >= min_iter
+ * iterations (lduMatrix::solver::normFactor, solverPerformance::checkConvergence).  The result is the matrix's
+ * solution to that tolerance -- as the reference's is: the two differ by what the tolerance allows (1e-5 in the
+ * reference's fvSolution files); parity unpinned against OpenFOAM itself, checked against a direct sparse solve of the
+ * restated matrix and against the reference's own MOC.C / QMOM.C driven through oracle/_ref. */
+typedef struct pbe_fvm_controls {
+    double tolerance;  /* fvSolution solvers { "n.*" { tolerance 1e-5; } }                                        */
+    double rel_tol;    /* relTol (0 = off)                                                                        */
+    int min_iter;      /* minIter (the reference's cases: 1)                                                      */
+    int max_iter;      /* maxIter (OpenFOAM default 1000)                                                         */
+    double relaxation; /* fvSolution relaxationFactors { equations { ".*" f; } }; <= 0: eqn.relax() does nothing  */
+    int solver;        /* PBE_FVM_SOLVER_*: which iteration; AUTO picks by the matrix (below)                     */
+} pbe_fvm_controls;
+/* JACOBI: x += z, z <- -D^-1 R z (the residual is D z: no extra pass), one kernel and 4 vector passes per matrix-vector
+ * product; BICGSTAB: diagonally preconditioned, ~9.5 passes per product.  Upwind convection makes the matrix triangular
+ * along the flow, so either needs about as many products as the solution travels cells in dt; Jacobi was the faster of
+ * the two at every Courant number measured (0.4 .. 150): AUTO = JACOBI. */
+enum { PBE_FVM_SOLVER_AUTO = 0, PBE_FVM_SOLVER_BICGSTAB = 1, PBE_FVM_SOLVER_JACOBI = 2 };
+/* OpenFOAM's SolverPerformance line per field: "Solving for n7, Initial residual = .., Final residual = .., No Iterations .." */
+typedef struct pbe_fvm_perf {
+    double initial_residual, final_residual;
+    int iterations;
+    int state; /* 1 converged, 2 breakdown (stagnated short of the tolerance), 3 max_iter reached */
+} pbe_fvm_perf;
+/* psi, S, psi_out DEVICE [nfields][stride] (psi_out must not alias psi); phi DEVICE [internal + boundary faces];
+ * psi_b DEVICE [nfields][stride_b] fixed patch values, or NULL = zero-gradient on every boundary face; controls NULL =
+ * {1e-5, 0, 1, 1000, 0, AUTO}; perf HOST [nfields] or NULL.  Synchronous on return (the iteration count is data dependent).
+ * Uncoupled patches only (PBE_E_UNSUPPORTED on a mesh with processor patches). */
+int pbe_transport_implicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stride, const double *psi,
+                           const double *phi, const double *psi_b, int64_t stride_b, const double *S, double dt,
+                           const pbe_fvm_controls *controls, double *psi_out, pbe_fvm_perf *perf, void *cuda_stream);
+
 /* HOST-buffer MOC::correct() with solveWithMULES (MOC.C:159-184, 198-272): what the OpenFOAM-side
  * adapter calls when the case's div(phi,n.*) scheme is on the device.  n_host [N][stride] is
  * updated in place (N = the method's numberOfClasses, ncells = the mesh's); phi_host

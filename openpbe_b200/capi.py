@@ -21,6 +21,7 @@ QMOM_MAX_ORDER = 4
 MOC_KERNEL_SMEM, MOC_KERNEL_TMEM, MOC_KERNEL_PIVOT = 1, 2, 3
 DIV_UPWIND, DIV_VANLEER = 0, 1
 CELLS_ALL, CELLS_REGULAR, CELLS_IRREGULAR = 0, 1, 2
+FVM_SOLVER_AUTO, FVM_SOLVER_BICGSTAB, FVM_SOLVER_JACOBI = 0, 1, 2
 
 _dp = C.POINTER(C.c_double)
 _vp = C.c_void_p
@@ -81,6 +82,18 @@ class PbeError(RuntimeError):
 
 
 # every exported symbol of include/pbe_b200.h: name -> (restype, argtypes)
+class FvmControls(C.Structure):
+    """pbe_fvm_controls (include/pbe_b200.h): fvSolution's tolerance / relTol / minIter / maxIter + the equation's
+    relaxation factor."""
+    _fields_ = [("tolerance", C.c_double), ("rel_tol", C.c_double), ("min_iter", C.c_int), ("max_iter", C.c_int),
+                ("relaxation", C.c_double), ("solver", C.c_int)]
+
+
+class FvmPerf(C.Structure):
+    _fields_ = [("initial_residual", C.c_double), ("final_residual", C.c_double), ("iterations", C.c_int),
+                ("state", C.c_int)]
+
+
 PROTOTYPES = {
     "pbe_coalescence_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
     "pbe_breakup_type": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
@@ -127,6 +140,8 @@ PROTOTYPES = {
     "pbe_transport_explicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
                                          C.c_double, _vp, _vp]),
     "pbe_mesh_set_geometry": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "pbe_transport_implicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp, C.c_double, _vp, _vp,
+                                          _vp, _vp]),
     "pbe_transport_mules": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp, _vp, C.c_double,
                                       C.c_int, C.c_double, _vp, _vp]),
     "pbe_moc_psi_max": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),

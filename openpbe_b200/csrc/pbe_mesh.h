@@ -38,4 +38,16 @@ struct pbe_mesh {
     double *d_Sf = nullptr, *d_C = nullptr, *d_w = nullptr;
     double *mules_ws = nullptr; // workspace of pbe_transport_mules, grown on demand
     size_t mules_ws_doubles = 0;
+    // ---- implicit path (pbe_implicit.cu) ------------------------------------------------------------
+    // every cell's faces as [imp_W][ncells] slots, ascending face order (imp_W = maxf rounded up to 4, 6 or 8; 0: not
+    // built / wider cells, which walk the CSR): other as csr_other, -1 = padding; face as csr_face
+    int imp_W = -1;
+    int32_t *d_imp_other = nullptr, *d_imp_face = nullptr;
+    double *imp_ws = nullptr; // solver vectors r, r0, p, v, t [nfields][ncells] + per-cell rows, grown on demand
+    size_t imp_ws_doubles = 0;
+    void *imp_small = nullptr; // per-field scalars and block partials
+    size_t imp_small_bytes = 0;
+    void *imp_pinned = nullptr; // host mirror of the per-field scalars
+    size_t imp_pinned_bytes = 0;
+    cudaEvent_t imp_ev[2] = {nullptr, nullptr};
 };

@@ -629,6 +629,13 @@ int pbe_mesh_destroy(pbe_mesh *m) {
     cudaFree(m->d_C);
     cudaFree(m->d_w);
     cudaFree(m->mules_ws);
+    cudaFree(m->d_imp_other);
+    cudaFree(m->d_imp_face);
+    cudaFree(m->imp_ws);
+    cudaFree(m->imp_small);
+    if (m->imp_pinned) cudaFreeHost(m->imp_pinned);
+    for (cudaEvent_t e : m->imp_ev)
+        if (e) cudaEventDestroy(e);
     cudaFree(m->res);
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);

@@ -669,6 +669,21 @@ class Mesh:
             float(psi_min), int(n_limiter_iter), float(dt), _ptr(out), _stream_ptr(psi.device)))
         return out
 
+    def transport_implicit(self, psi, phi, dt, *, scheme="upwind", psi_b=None, S=None, out=None, tolerance=1e-5,
+                           rel_tol=0.0, min_iter=1, max_iter=1000, relaxation=0.0, solver="auto"):
+        """MOC::solveWithFVM / QMOM::solveWithFVM (MOC.C:186-198, QMOM.C:201-209): fvm::ddt + fvm::div == S for all K
+        fields at once.  Returns (psi_new, perf) with perf = [(initial residual, final residual, iterations, state)]."""
+        K, ncells = psi.shape
+        out = torch.empty_like(psi) if out is None else out
+        ctl = capi.FvmControls(float(tolerance), float(rel_tol), int(min_iter), int(max_iter), float(relaxation),
+                               {"auto": 0, "bicgstab": 1, "jacobi": 2}[solver] if isinstance(solver, str) else int(solver))
+        perf = (capi.FvmPerf * K)()
+        capi.check(capi.lib().pbe_transport_implicit(
+            self._h, div_scheme(scheme) if isinstance(scheme, str) else int(scheme), K, psi.stride(0) if ncells else 0,
+            _ptr(psi), _ptr(phi), _ptr(psi_b), 0 if psi_b is None else psi_b.stride(0), _ptr(S), float(dt),
+            C.byref(ctl), _ptr(out), C.cast(perf, C.c_void_p), _stream_ptr(psi.device)))
+        return out, [(p.initial_residual, p.final_residual, p.iterations, p.state) for p in perf]
+
     def set_coupled(self, first_boundary_face: int, count: int):
         """Mark boundary faces [first, first+count) as processor-patch faces (decomposed mesh)."""
         capi.check(capi.lib().pbe_mesh_set_coupled(self._h, int(first_boundary_face), int(count)))

@@ -1,0 +1,93 @@
+"""Implicit transport of the class / moment fields -- CPU restatement of what MOC::solveWithFVM (MOC.C:186-198) and
+QMOM::solveWithFVM (QMOM.C:201-209) ask OpenFOAM for:
+
+    fvScalarMatrix eqn(fvm::ddt(psi) + fvm::div(phi, psi) == S);  eqn.relax();  eqn.solve();
+
+TEST INFRASTRUCTURE ONLY (tests/, __graft_entry__.smoke(), bench.py's cpu legs).
+
+PARITY UNPINNED: fvMatrix, the ddt / convection schemes and the linear solvers are OpenFOAM's (third-party, absent
+from /root/reference).  This file restates OpenFOAM 3.0.x's assembly --
+
+  * EulerDdtScheme::fvmDdt: diag = rDeltaT V, source = rDeltaT psi0 V;
+  * gaussConvectionScheme::fvmDiv: lower = -w phi, upper = lower + phi, diag = -(sum of the column's lower / upper)
+    (negSumDiag); patches: internalCoeffs = phi_b valueInternalCoeffs, boundaryCoeffs = -phi_b valueBoundaryCoeffs, i.e.
+    zero-gradient adds phi_b to the diagonal, fixed-value subtracts phi_b psi_b from the source;
+  * `== S`: source += S V;
+  * fvMatrix::relax(alpha): D += |internalCoeffs|; D = max(|D|, sum|off-diagonals|); D /= alpha; D -= internalCoeffs;
+    source += (D - D0) psi0;
+  * lduMatrix::solver::normFactor: sum(|Ax - xbar A1| + |b - xbar A1|) + 1e-20, xbar = average(x); residual =
+    sum|b - Ax| / normFactor
+
+-- and solves the matrix DIRECTLY (scipy.sparse): the answer every convergent solver tends to.  The reference's own
+MOC.C / QMOM.C reach the same matrix through oracle/ref_shim (tests/test_implicit.py compares the two).
+"""
+from __future__ import annotations
+
+import numpy as np
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+
+def assemble(mesh: dict, phi, dt, psi0, *, S=None, psi_b=None, relaxation=0.0):
+    """(A [csr], b) of one field.  mesh: owner, neighbour, boundary_owner, vcell (as tests/meshes.py builds them);
+    phi [internal + boundary faces]; psi_b [boundary faces] fixed patch values or None = zero-gradient patches."""
+    own = np.asarray(mesh["owner"], dtype=np.int64)
+    nei = np.asarray(mesh["neighbour"], dtype=np.int64)
+    bown = np.asarray(mesh["boundary_owner"], dtype=np.int64)
+    V = np.asarray(mesh["vcell"], dtype=np.float64)
+    nc, ni = V.size, own.size
+    phi = np.asarray(phi, dtype=np.float64)
+    rdt = 1.0 / dt
+    diag = rdt * V
+    b = rdt * psi0 * V
+    if S is not None:
+        b = b + S * V
+    w = (phi[:ni] >= 0).astype(np.float64)  # upwind: pos(faceFlux)
+    lower = -w * phi[:ni]
+    upper = lower + phi[:ni]
+    diag = diag.copy()
+    np.subtract.at(diag, own, lower)
+    np.subtract.at(diag, nei, upper)
+    ic = np.zeros(nc)
+    icmag = np.zeros(nc)
+    if psi_b is None:
+        np.add.at(ic, bown, phi[ni:])
+        np.add.at(icmag, bown, np.abs(phi[ni:]))
+    else:
+        np.subtract.at(b, bown, phi[ni:] * psi_b)
+    if relaxation > 0.0:
+        sum_off = np.zeros(nc)
+        np.add.at(sum_off, own, np.abs(upper))
+        np.add.at(sum_off, nei, np.abs(lower))
+        D0 = diag
+        D = np.maximum(np.abs(D0 + icmag), sum_off) / relaxation - ic
+        b = b + (D - D0) * psi0
+        diag = D
+    diag = diag + ic  # addBoundaryDiag
+    rows = np.concatenate([np.arange(nc), own, nei])
+    cols = np.concatenate([np.arange(nc), nei, own])
+    vals = np.concatenate([diag, upper, lower])
+    A = sp.csr_matrix((vals, (rows, cols)), shape=(nc, nc))
+    return A, b
+
+
+def norm_factor(A, b, x):
+    xbar = x.mean()
+    pA = xbar * np.asarray(A.sum(axis=1)).ravel()
+    return np.abs(A @ x - pA).sum() + np.abs(b - pA).sum() + 1.0e-20
+
+
+def residual(A, b, x, x0=None):
+    """OpenFOAM's normalised residual of x (normalised with the INITIAL field x0's factor, as the solvers do)."""
+    return np.abs(b - A @ x).sum() / norm_factor(A, b, x if x0 is None else x0)
+
+
+def solve(mesh: dict, phi, dt, psi, *, S=None, psi_b=None, relaxation=0.0):
+    """All fields psi [K][ncells] -> the matrices' exact solutions [K][ncells]."""
+    psi = np.asarray(psi, dtype=np.float64)
+    out = np.empty_like(psi)
+    for k in range(psi.shape[0]):
+        A, b = assemble(mesh, phi, dt, psi[k], S=None if S is None else S[k], psi_b=None if psi_b is None else psi_b[k],
+                        relaxation=relaxation)
+        out[k] = spla.spsolve(A.tocsc(), b)
+    return out

@@ -1,0 +1,285 @@
+"""Row f2, third slice: the implicit transport MOC::solveWithFVM (MOC.C:186-198) / QMOM::solveWithFVM
+(QMOM.C:201-209) -- the reference's default branch (usingMULES false).
+
+PARITY UNPINNED: fvMatrix and the linear solvers are OpenFOAM's.  What is checked:
+  * CPU: oracle/fvm_implicit.py (OpenFOAM's assembly restated, solved directly) has the properties the scheme must
+    have -- zero flux reduces to the explicit update, the update conserves, stays positive at any Courant number,
+    relax(1) leaves a dominant matrix alone;
+  * CPU: the reference's OWN MOC.C / QMOM.C with usingMULES false, compiled unmodified (oracle/_ref) and driven through
+    the shimmed fvm:: calls, land on the same solution as the direct solve of the restated matrix;
+  * GPU: pbe_transport_implicit (all fields at once, BiCGStab on the device) reaches the direct solution to the
+    tolerance asked, reports OpenFOAM's normalised residuals, and stops by OpenFOAM's criterion.
+"""
+import numpy as np
+import pytest
+
+from oracle import fvm_implicit as fvm
+from oracle import ref_oracle as ref
+from openpbe_b200 import synthetic
+
+needs_ref = pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built (no /root/reference at build time)")
+
+
+def random_mesh(rng, ncells, nint, nbnd):
+    a = rng.integers(0, ncells, size=nint)
+    b = (a + 1 + rng.integers(0, ncells - 1, size=nint)) % ncells
+    own, nei = np.minimum(a, b), np.maximum(a, b)
+    order = np.lexsort((nei, own))
+    return {"owner": own[order].astype(np.int32), "neighbour": nei[order].astype(np.int32),
+            "boundary_owner": rng.integers(0, ncells, size=nbnd).astype(np.int32),
+            "vcell": rng.uniform(0.5, 2.0, ncells), "phi": rng.normal(size=nint + nbnd) * 0.05}
+
+
+def fields(rng, K, nc):
+    return rng.uniform(0.1, 2.0, size=(K, nc)) * (1.0 + np.sin(np.arange(nc) * 0.3)[None, :] ** 2)
+
+
+# ---- CPU: properties of the restatement -------------------------------------------------------------------
+def test_zero_flux_is_the_explicit_update():
+    rng = np.random.default_rng(1)
+    m = synthetic.block_mesh(5, 4, 3, velocity=(0.0, 0.0, 0.0))
+    psi = fields(rng, 3, 60)
+    S = rng.normal(size=psi.shape)
+    out = fvm.solve(m, m["phi"], 0.01, psi, S=S)
+    assert np.allclose(out, psi + 0.01 * S, rtol=1e-14, atol=0)
+
+
+@pytest.mark.parametrize("courant", [0.3, 5.0, 80.0])
+def test_implicit_upwind_conserves_and_stays_positive(courant):
+    rng = np.random.default_rng(2)
+    m = synthetic.block_mesh(12, 9, 1, velocity=(1.0, -0.5, 0.0))
+    nc = 12 * 9
+    dx = 1.0 / 12
+    dt = courant * dx / 1.0
+    psi = fields(rng, 4, nc)
+    psi[:, rng.integers(0, nc, 20)] = 0.0
+    out = fvm.solve(m, m["phi"], dt, psi)  # zero-gradient patches
+    assert out.min() >= -1e-15  # M-matrix: positivity at any Courant number
+    # conservation: d/dt sum(psi V) = - boundary outflow of the NEW field
+    ni = m["owner"].size
+    bflux = np.zeros(4)
+    for k in range(4):
+        bflux[k] = np.sum(m["phi"][ni:] * out[k][m["boundary_owner"]])
+    lhs = ((out - psi) * m["vcell"]).sum(axis=1) / dt
+    assert np.allclose(lhs, -bflux, rtol=1e-10, atol=1e-12)
+
+
+def test_relaxation_one_keeps_a_dominant_matrix_and_damps_otherwise():
+    rng = np.random.default_rng(3)
+    m = synthetic.block_mesh(8, 6, 1, velocity=(1.0, 0.3, 0.0))
+    psi = fields(rng, 2, 48)
+    dt = 0.01
+    pb = rng.uniform(0.0, 1.0, size=(2, m["boundary_owner"].size))
+    a = fvm.solve(m, m["phi"], dt, psi, psi_b=pb)
+    b = fvm.solve(m, m["phi"], dt, psi, psi_b=pb, relaxation=1.0)
+    assert np.allclose(a, b, rtol=1e-13)  # uniform velocity, fixed-value patches: rows dominant, nothing to do
+    # zero-gradient patches with inflow: relax() adds |phi_b| where the patch coefficient is negative (OpenFOAM's
+    # "maximum magnitude diagonal contribution to ensure stability"): the matrix changes even at factor 1
+    a = fvm.solve(m, m["phi"], dt, psi)
+    assert not np.allclose(a, fvm.solve(m, m["phi"], dt, psi, relaxation=1.0), rtol=1e-6)
+    c = fvm.solve(m, m["phi"], dt, psi, relaxation=0.5)
+    # under-relaxed: the new field moves about half as far from the old one
+    assert np.all(np.abs(c - psi).sum(axis=1) < 0.62 * np.abs(a - psi).sum(axis=1))
+    assert np.all(np.abs(c - psi).sum(axis=1) > 0.38 * np.abs(a - psi).sum(axis=1))
+
+
+def test_residual_normalisation_is_openfoams():
+    rng = np.random.default_rng(4)
+    m = synthetic.block_mesh(6, 5, 4, velocity=(0.4, 0.2, -0.7))
+    psi = fields(rng, 1, 120)[0]
+    A, b = fvm.assemble(m, m["phi"], 0.05, psi)
+    x = np.asarray(np.linalg.solve(A.toarray(), b))
+    assert fvm.residual(A, b, x, psi) < 1e-14
+    r0 = fvm.residual(A, b, psi)
+    assert 1e-4 < r0 < 1.0  # the old field is no solution, and the factor makes it O(1) at most
+
+
+@needs_ref
+@pytest.mark.parametrize("method", ["moc", "qmom"])
+def test_reference_solve_with_fvm_lands_on_the_direct_solution(oracle, method):
+    """The reference's own sources with usingMULES false (its default): MOC.C:177-180 -> solveWithFVM -> the shimmed
+    fvm::ddt + fvm::div == S, relax(), solve()."""
+    tm = synthetic.block_mesh(9, 7, 5, velocity=(1.0, -0.5, 0.25))
+    nc = 9 * 7 * 5
+    dt = 0.02
+    if method == "moc":
+        w = synthetic.workload("moc30_ct", nc)
+        w.N, w.xi1 = 6, 3e-10 / 6
+        f = synthetic.moc_fields(w)
+        f0 = f["n"] * (1.0 + 5.0 * np.sin(np.arange(nc) * 0.7)[None, :] ** 2)
+        txt = ref.pbe_dict("methodOfClasses", w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs, N=w.N, xi1=w.xi1,
+                           relax=w.relax, usingMULES=False)
+        stem = "n"
+    else:
+        w = synthetic.workload("qmom3_const", nc)
+        f = synthetic.qmom_fields(w, degenerate_fraction=0.0)
+        f0 = f["m"]
+        txt = ref.pbe_dict("quadratureMethodOfMoments", w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs, order=w.N,
+                           usingMULES=False)
+        stem = "m"
+    try:
+        ref.set_mesh(nc, tm["owner"], tm["neighbour"], tm["boundary_owner"], Sf=tm["Sf"], C_=tm["C"], weights=tm["weights"],
+                     div_scheme="Gauss upwind")
+        f_ref, S_ref, _, _ = ref.method_steps(txt, stem, f0, f["eps"], f["rho"], f["nu"], dt, alpha=f.get("alpha"),
+                                              vcell=tm["vcell"], phi=tm["phi"])
+    finally:
+        ref.clear_mesh()
+    mine = fvm.solve(tm, tm["phi"], dt, f0, S=S_ref)
+    if method == "qmom":
+        mine = np.maximum(mine, 1e-15)  # QMOM.C:117-123
+    scale = np.abs(f0).max(axis=1, keepdims=True)
+    assert np.all(np.abs(f_ref - mine) <= 1e-11 * scale)
+
+
+# ---- GPU ---------------------------------------------------------------------------------------------------
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from openpbe_b200 import engine
+    assert torch.cuda.is_available(), "-m gpu tests need a CUDA device"
+    c = engine.Context(0)
+    yield c
+    c.close()
+
+
+def T(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).cuda()
+
+
+def device_solve(ctx, m, psi, phi, dt, S=None, psi_b=None, **kw):
+    from openpbe_b200 import engine
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    out, perf = mesh.transport_implicit(T(psi), T(phi), dt, S=None if S is None else T(S),
+                                        psi_b=None if psi_b is None else T(psi_b), **kw)
+    out = out.cpu().numpy()
+    mesh.close()
+    return out, perf
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,vel", [((12, 9, 7), (1.0, -0.5, 0.25)), ((40, 1, 1), (1.0, 0.0, 0.0)),
+                                       ((17, 13, 1), (-0.3, 0.8, 0.0)), ((48, 40, 24), (0.7, 0.4, -0.9))])
+@pytest.mark.parametrize("courant", [0.4, 6.0])
+@pytest.mark.parametrize("solver", ["jacobi", "bicgstab"])
+def test_device_implicit_reaches_the_direct_solution_block(ctx, shape, vel, courant, solver):
+    rng = np.random.default_rng(10)
+    m = synthetic.block_mesh(*shape, velocity=vel)
+    nc = shape[0] * shape[1] * shape[2]
+    K = 5
+    psi = fields(rng, K, nc)
+    S = rng.normal(size=psi.shape) * 0.1
+    dt = courant / (max(abs(v) for v in vel) * max(shape))
+    want = fvm.solve(m, m["phi"], dt, psi, S=S)
+    got, perf = device_solve(ctx, m, psi, m["phi"], dt, S=S, tolerance=1e-13, solver=solver)
+    scale = np.abs(want).max(axis=1, keepdims=True)
+    # a normalised L1 residual of 1e-13 bounds the error of one cell by ~1e-13 x ncells (all of it in one place)
+    assert np.all(np.abs(got - want) <= 1e-13 * max(nc, 100) * scale)
+    assert np.all(np.abs(got - want).sum(axis=1) <= 1e-11 * np.abs(want).sum(axis=1))
+    for k, (r0, r1, it, state) in enumerate(perf):
+        A, b = fvm.assemble(m, m["phi"], dt, psi[k], S=S[k])
+        assert state == 1 and it >= 1 and r1 < 1e-13
+        assert r0 == pytest.approx(fvm.residual(A, b, psi[k]), rel=1e-10)
+        assert fvm.residual(A, b, got[k], psi[k]) < 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nint,nbnd,fixed", [(0, 4, False), (60, 5, True), (900, 120, False), (6000, 300, True)])
+def test_device_implicit_random_topology_and_patches(ctx, nint, nbnd, fixed):
+    """any face count per cell (the slot tables' wide form), fixed-value patches in the source, zero-gradient patches
+    on the diagonal"""
+    rng = np.random.default_rng(11 + nint)
+    nc = 200
+    m = random_mesh(rng, nc, nint, nbnd)
+    m["vcell"] *= 1.0  # V / dt dominates the random (non-solenoidal) fluxes
+    K = 3
+    psi = fields(rng, K, nc)
+    psi_b = rng.uniform(0.0, 1.0, size=(K, nbnd)) if fixed else None
+    dt = 0.5
+    want = fvm.solve(m, m["phi"], dt, psi, psi_b=psi_b)
+    got, perf = device_solve(ctx, m, psi, m["phi"], dt, psi_b=psi_b, tolerance=1e-13)
+    assert np.all(np.abs(got - want) <= 1e-10 * np.abs(want).max())
+    assert all(p[3] == 1 for p in perf)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("relaxation", [1.0, 0.7])
+def test_device_implicit_relaxation(ctx, relaxation):
+    rng = np.random.default_rng(12)
+    m = random_mesh(rng, 300, 1500, 40)  # random fluxes: rows are NOT dominant, relax() changes the matrix
+    psi = fields(rng, 4, 300)
+    dt = 4.0
+    want = fvm.solve(m, m["phi"], dt, psi, relaxation=relaxation)
+    plain = fvm.solve(m, m["phi"], dt, psi)
+    assert np.abs(want - plain).max() > 1e-3
+    got, _ = device_solve(ctx, m, psi, m["phi"], dt, relaxation=relaxation, tolerance=1e-13)
+    assert np.all(np.abs(got - want) <= 1e-10 * np.abs(want).max())
+
+
+@pytest.mark.gpu
+def test_device_implicit_stops_by_openfoams_criterion(ctx):
+    """tolerance 1e-5, relTol 0, minIter 1 (the reference's fvSolution): every field stops at the first iterate below
+    the tolerance -- fields already below it still take one iteration -- and the answer is within what the tolerance
+    allows of the exact one"""
+    rng = np.random.default_rng(13)
+    m = synthetic.block_mesh(20, 16, 12, velocity=(1.0, -0.5, 0.25))
+    nc = 20 * 16 * 12
+    psi = fields(rng, 6, nc)
+    psi[5] = 1.0  # uniform field, zero-gradient patches, solenoidal flux: already the solution
+    dt = 0.5 / 20
+    got, perf = device_solve(ctx, m, psi, m["phi"], dt)
+    want = fvm.solve(m, m["phi"], dt, psi)
+    for k, (r0, r1, it, state) in enumerate(perf[:5]):
+        assert state == 1 and r1 < 1e-5 and 1 <= it <= 20
+        A, b = fvm.assemble(m, m["phi"], dt, psi[k])
+        assert fvm.residual(A, b, got[k], psi[k]) == pytest.approx(r1, rel=1e-6, abs=1e-16)
+    # the uniform field: OpenFOAM's normalisation is 0 / 0 there (the factor measures the deviation from the mean), so
+    # the residual says nothing; the field stays what it is
+    assert np.all(np.abs(got[5] - 1.0) <= 1e-13)
+    assert np.all(np.abs(got - want) <= 1e-4 * np.abs(want).max())
+    # min_iter 0 and a tolerance every field already meets: nothing is touched
+    got0, perf0 = device_solve(ctx, m, psi[:5], m["phi"], dt, min_iter=0, tolerance=1.0)
+    assert all(p[2] == 0 and p[3] == 1 for p in perf0) and np.array_equal(got0, psi[:5])
+    # the two solvers stop at different iterates, both within the tolerance of the exact solution
+    gj, pj = device_solve(ctx, m, psi[:5], m["phi"], dt, solver="jacobi")
+    gb, pb = device_solve(ctx, m, psi[:5], m["phi"], dt, solver="bicgstab")
+    assert all(p[3] == 1 for p in pj + pb)
+    assert np.all(np.abs(gj - gb) <= 1e-4 * np.abs(want).max())
+    # rel_tol: stop at 1e-2 of the initial residual
+    _, perf_r = device_solve(ctx, m, psi, m["phi"], dt, tolerance=0.0, rel_tol=1e-2)
+    for r0, r1, it, state in perf_r[:5]:
+        assert state == 1 and r1 < 1e-2 * r0
+    # max_iter
+    _, perf_m = device_solve(ctx, m, psi, m["phi"], dt, tolerance=1e-300, max_iter=2)
+    assert all(p[3] == 3 and p[2] == 2 for p in perf_m[:5])
+
+
+@pytest.mark.gpu
+def test_device_implicit_zero_flux_is_the_explicit_update(ctx):
+    rng = np.random.default_rng(14)
+    m = synthetic.block_mesh(6, 5, 4, velocity=(0.0, 0.0, 0.0))
+    psi = fields(rng, 3, 120)
+    S = rng.normal(size=psi.shape)
+    got, perf = device_solve(ctx, m, psi, m["phi"], 0.01, S=S)
+    assert np.allclose(got, psi + 0.01 * S, rtol=1e-14, atol=0)
+    assert all(p[2] == 1 for p in perf)
+
+
+@pytest.mark.gpu
+def test_device_implicit_argument_errors(ctx):
+    from openpbe_b200 import capi, engine
+    m = synthetic.block_mesh(4, 3, 2)
+    mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+    psi = T(np.ones((2, 24)))
+    with pytest.raises(capi.PbeError, match="Gauss upwind"):
+        mesh.transport_implicit(psi, T(m["phi"]), 0.1, scheme="vanLeer")
+    with pytest.raises(capi.PbeError, match="alias"):
+        mesh.transport_implicit(psi, T(m["phi"]), 0.1, out=psi)
+    with pytest.raises(capi.PbeError, match="dt"):
+        mesh.transport_implicit(psi, T(m["phi"]), 0.0)
+    with pytest.raises(capi.PbeError, match="controls"):
+        mesh.transport_implicit(psi, T(m["phi"]), 0.1, max_iter=0)
+    with pytest.raises(capi.PbeError, match="solver"):
+        mesh.transport_implicit(psi, T(m["phi"]), 0.1, solver=7)
+    mesh.close()
