@@ -104,6 +104,38 @@ int PBEMethod::divSchemeOf(const dictionary &coeffs, const char *where) const {
     return id;
 }
 
+// usingMULES false: the scheme of the implicit convection term -- fvSchemes "div\\(U,nk\\)" (MOC.C:194) or the default
+// name fvm::div builds, "div(phi,m<k>)" (QMOM.C:203-204) -- and what fvSolution says about the equation: solvers {
+// "n.*" { tolerance; relTol; minIter; maxIter; } } and relaxationFactors { equations { ".*" f; } } (what eqn.relax()
+// looks up).  The linear solver named there (PBiCG + DILU, smoothSolver) is replaced by the device iteration; the
+// stopping criterion is kept.  Returns false when the scheme has no implicit device path (limited schemes).
+bool PBEMethod::implicitControlsOf(const dictionary &coeffs, const word &field, const word &divName, int &scheme,
+                                   pbe_fvm_controls &ctl) const {
+    ctl.tolerance = 1e-6, ctl.rel_tol = 0.0, ctl.min_iter = 0, ctl.max_iter = 1000; // lduMatrix::solver defaults
+    ctl.relaxation = 0.0, ctl.solver = PBE_FVM_SOLVER_AUTO;
+#ifdef PBE_B200_REAL_OPENFOAM
+    ITstream &is = phase_.mesh().divScheme(divName);
+    word name(is);
+    if (!is.eof()) name += " " + word(is);
+    const dictionary &sd = phase_.mesh().solverDict(field);
+    ctl.tolerance = sd.lookupOrDefault<scalar>("tolerance", 1e-6);
+    ctl.rel_tol = sd.lookupOrDefault<scalar>("relTol", 0.0);
+    ctl.min_iter = sd.lookupOrDefault<label>("minIter", 0);
+    ctl.max_iter = sd.lookupOrDefault<label>("maxIter", 1000);
+    if (phase_.mesh().relaxEquation(field)) ctl.relaxation = phase_.mesh().equationRelaxationFactor(field);
+#else
+    (void)field, (void)divName;
+    const word name = coeffs.lookupOrDefault<word>("implicitDivScheme", "Gauss upwind");
+    ctl.tolerance = coeffs.lookupOrDefault<scalar>("tolerance", 1e-6);
+    ctl.rel_tol = coeffs.lookupOrDefault<scalar>("relTol", 0.0);
+    ctl.min_iter = coeffs.lookupOrDefault<label>("minIter", 0);
+    ctl.max_iter = coeffs.lookupOrDefault<label>("maxIter", 1000);
+    ctl.relaxation = coeffs.lookupOrDefault<scalar>("relaxationFactor", 0.0);
+#endif
+    if (pbe_div_scheme_type(name.c_str(), &scheme) != PBE_OK) return false; // e.g. Gauss limitedLinear 1
+    return scheme == PBE_DIV_UPWIND;
+}
+
 pbe_mesh *PBEMethod::newDeviceMesh(int scheme, const char *where) const {
     const fvMesh &mesh = phase_.mesh();
     pbe_mesh *m = nullptr;
@@ -160,7 +192,7 @@ addToRunTimeSelectionTable(PBEMethod, MOC, dictionary);
 MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     : PBEMethod(pbeProperties, phase), runTime(phase.mesh().time()), deltaXi_("deltaXi", 0.0),
       numberOfClasses_(0), usingMULES_(false), source_term_relaxation_(1.0), moc_(nullptr), state_(nullptr),
-      b200Mesh_(nullptr), d_("d." + phase.name(), phase.mesh(), 0.0, false), continuityError_(0.0), hostStale_(false),
+      b200Mesh_(nullptr), implicitOnDevice_(false), d_("d." + phase.name(), phase.mesh(), 0.0, false), continuityError_(0.0), hostStale_(false),
       deviceStale_(true) {
     const dictionary &MOCDict_ = pbeProperties.subDict("MOCCoeffs"); // MOC.C:51-60
     numberOfClasses_ = readLabel(MOCDict_.lookup("numberOfClasses"));
@@ -189,13 +221,24 @@ MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
     const fvMesh &mesh = phase.mesh();
     b200Check(pbe_moc_state_create(moc_, mesh.nCells(), mesh.V().cdata(), &state_), "MOC::MOC");
     if (mesh.hasFaces()) {
-        if (!usingMULES_) {
+        if (!usingMULES_) { // solveWithFVM (MOC.C:177-180, 186-198), the reference's default
+            int scheme = PBE_DIV_UPWIND;
+            pbe_fvm_controls ctl;
+            if (implicitControlsOf(MOCDict_, fieldName("n", 0), "div(U,nk)", scheme, ctl)) {
+                b200Mesh_ = newDeviceMesh(scheme, "MOC::MOC mesh");
+                b200Check(pbe_moc_state_attach_mesh(state_, b200Mesh_, scheme), "MOC::MOC");
+                b200Check(pbe_moc_state_set_implicit(state_, &ctl), "MOC::MOC usingMULES false");
+                implicitOnDevice_ = true;
+            } else {
 #ifdef PBE_B200_REAL_OPENFOAM
-            // implicit path (MOC.C:186-198): kept on the host, see correct()
+                // a limited scheme in the implicit term: the solve stays on the host, see correct()
+                Info << "MOC: div(U,nk) is not Gauss upwind: sources on the device, fvm solve on the host" << endl;
 #else
-            FatalErrorIn("MOC::MOC") << "usingMULES false selects the implicit fvm::ddt + fvm::div solve (MOC.C:186-198), "
-                                        "which has no device path; set usingMULES true" << exit(FatalError);
+                FatalErrorIn("MOC::MOC") << "usingMULES false with a div(U,nk) scheme other than Gauss upwind: the implicit "
+                                            "fvm::ddt + fvm::div solve (MOC.C:186-198) has a device path for Gauss upwind only"
+                                         << exit(FatalError);
 #endif
+            }
         } else {
             const int scheme = divSchemeOf(MOCDict_, "MOC::MOC div(phi,n.*)");
             b200Mesh_ = newDeviceMesh(scheme, "MOC::MOC mesh");
@@ -247,8 +290,8 @@ void MOC::correct() {
     if (deviceStale_) upload();
     updatePhaseFields();
 #ifdef PBE_B200_REAL_OPENFOAM
-    if (!usingMULES_ && phase_.mesh().nInternalFaces() > 0) {
-        // implicit path: the sources come from the device, the reference's solveWithFVM(S) (MOC.C:186-198)
+    if (!usingMULES_ && !implicitOnDevice_ && phase_.mesh().nInternalFaces() > 0) {
+        // implicit path with a limited scheme: the sources come from the device, the reference's solveWithFVM(S) (MOC.C:186-198)
         // runs unchanged on the host fields, which are then uploaded again
         const label nCells = phase_.size();
         std::vector<double> nH((size_t)numberOfClasses_ * nCells), SH(nH.size());
@@ -309,12 +352,25 @@ QMOM::QMOM(const dictionary &pbeProperties, const phaseModel &phase)
     const fvMesh &mesh = phase.mesh();
     b200Check(pbe_qmom_state_create(qmom_, mesh.nCells(), mesh.V().cdata(), &state_), "QMOM::QMOM");
     if (mesh.hasFaces()) {
-        if (!usingMULES_)
-            FatalErrorIn("QMOM::QMOM") << "usingMULES false selects the implicit fvm::ddt + fvm::div solve (QMOM.C:199-209), "
-                                          "which has no device path; set usingMULES true" << exit(FatalError);
-        const int scheme = divSchemeOf(pbeProperties.subDict("QMOMCoeffs"), "QMOM::QMOM div(phi,m.*)");
+        int scheme = PBE_DIV_UPWIND;
+        pbe_fvm_controls ctl;
+        const dictionary &coeffs = pbeProperties.subDict("QMOMCoeffs");
+        if (!usingMULES_) { // solveWithFVM (QMOM.C:112-115, 201-209), the reference's default
+#ifdef PBE_B200_REAL_OPENFOAM
+            const word divName = "div(" + phase.phi().name() + ',' + fieldName("m", 0) + ')'; // fvm::div's default name
+#else
+            const word divName = "div(phi,m0)";
+#endif
+            if (!implicitControlsOf(coeffs, fieldName("m", 0), divName, scheme, ctl))
+                FatalErrorIn("QMOM::QMOM") << "usingMULES false with a div(phi,m.*) scheme other than Gauss upwind: the implicit "
+                                              "fvm::ddt + fvm::div solve (QMOM.C:201-209) has a device path for Gauss upwind only"
+                                           << exit(FatalError);
+        } else {
+            scheme = divSchemeOf(coeffs, "QMOM::QMOM div(phi,m.*)");
+        }
         b200Mesh_ = newDeviceMesh(scheme, "QMOM::QMOM mesh");
         b200Check(pbe_qmom_state_attach_mesh(state_, b200Mesh_, scheme), "QMOM::QMOM");
+        if (!usingMULES_) b200Check(pbe_qmom_state_set_implicit(state_, &ctl), "QMOM::QMOM usingMULES false");
     }
 }
 

@@ -13,6 +13,10 @@
 //              [--mesh nx ny nz [--velocity u v w]]   hex block in OpenFOAM face addressing: both methods then
 //                                   run solveWithMULES (source + explicit upwind transport, MOC.C:198-272,
 //                                   QMOM.C:131-197)
+//              [--implicit [--courant C]]  with --mesh: usingMULES stays at the reference's default (false) and both
+//                                   methods run solveWithFVM (fvm::ddt + fvm::div == S, MOC.C:186-198, QMOM.C:201-209),
+//                                   fvSolution controls of the reference's cases (tolerance 1e-5, relTol 0, minIter 1);
+//                                   --courant sets deltaT from the block's largest cell Courant number
 //
 // Prints one JSON line per method per step (wall ms with the diameter read-back, volume-averaged
 // / max / min diameter as printAvgMaxMin would, Utility.C:4-10) and a summary line per method.
@@ -127,6 +131,8 @@ int main(int argc, char **argv) {
     std::string dictFile;
     int meshN[3] = {0, 0, 0};
     double vel[3] = {1.0, 0.5, 0.25};
+    bool implicitSolve = false;
+    double courant = 0.0;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto val = [&]() -> const char * {
@@ -146,7 +152,11 @@ int main(int argc, char **argv) {
         else if (a == "--mesh") { // nx ny nz hex block: MOC runs solveWithMULES (transport + source)
             for (int k = 0; k < 3; ++k) meshN[k] = std::atoi(val());
             cells = (int64_t)meshN[0] * meshN[1] * meshN[2];
-        } else if (a == "--velocity")
+        } else if (a == "--implicit")
+            implicitSolve = true;
+        else if (a == "--courant")
+            courant = std::atof(val());
+        else if (a == "--velocity")
             for (int k = 0; k < 3; ++k) vel[k] = std::atof(val());
         else {
             std::fprintf(stderr, "unknown option %s\n", a.c_str());
@@ -278,6 +288,8 @@ int main(int argc, char **argv) {
             // CFL 0.4 on the block
             phase.deltaT = 0.4 / (std::fabs(vel[0]) * nx + std::fabs(vel[1]) * ny + std::fabs(vel[2]) * nz + 1e-300);
             if (phase.deltaT > 2.5e-4) phase.deltaT = 2.5e-4;
+            if (courant > 0.0) // the implicit solve is not bound by the Courant number: let the caller pick it
+                phase.deltaT = courant / (std::fabs(vel[0]) * nx + std::fabs(vel[1]) * ny + std::fabs(vel[2]) * nz + 1e-300);
         }
 
         // QMOM starts from the moments of the MOC initial condition (same physical state in both
@@ -298,7 +310,7 @@ int main(int argc, char **argv) {
             dict.set("method", "methodOfClasses");
             const double xi1 = 3.5918876006043295e-12 * 50.0 / classes;
             dict.subDictOrAdd("MOCCoeffs").set("numberOfClasses", (double)classes).set("xi1", xi1);
-            if (phase.mesh) dict.subDictOrAdd("MOCCoeffs").set("usingMULES", std::string("true"));
+            if (phase.mesh && !implicitSolve) dict.subDictOrAdd("MOCCoeffs").set("usingMULES", std::string("true"));
             std::vector<double> p(classes), n0((size_t)classes * cells);
             double norm = 0;
             for (int i = 0; i < classes; ++i) {
@@ -321,6 +333,16 @@ int main(int argc, char **argv) {
             if (R.rank == 0) // global values: the library reduced them over the ranks inside correct()
                 std::printf("{\"method\": \"methodOfClasses\", \"min_n0\": %.6e, \"continuity_error\": %.6e}\n",
                             moc.classMin(0), moc.continuityError());
+            if (R.rank == 0 && phase.mesh && implicitSolve) { // OpenFOAM's "Solving for n<i>, ..." lines, condensed
+                int itMin = 1 << 30, itMax = 0;
+                double r0 = 0, r1 = 0;
+                for (const pbe_fvm_perf &q : moc.solverPerformance()) {
+                    itMin = std::min(itMin, q.iterations), itMax = std::max(itMax, q.iterations);
+                    r0 = std::max(r0, q.initial_residual), r1 = std::max(r1, q.final_residual);
+                }
+                std::printf("{\"method\": \"methodOfClasses\", \"transport\": \"solveWithFVM\", \"iterations\": [%d, %d], "
+                            "\"initial_residual_max\": %.3e, \"final_residual_max\": %.3e}\n", itMin, itMax, r0, r1);
+            }
         }
         {   // ---- quadratureMethodOfMoments: the 2*order moments of the same initial condition ------
             pbe::Dictionary dict = pbe::Dictionary::parse(text, "PBEDiameterCoeffs");
@@ -334,7 +356,7 @@ int main(int argc, char **argv) {
             };
             rescale("CoulaloglouTavlaridesCCoeffs", 7.0 / 9.0, 4.0 / 3.0, 0.00487, 0.008);
             rescale("CoulaloglouTavlaridesCoeffs", -2.0 / 9.0, -5.0 / 9.0, 0.00487, 0.008);
-            if (phase.mesh) dict.subDictOrAdd("QMOMCoeffs").set("usingMULES", std::string("true"));
+            if (phase.mesh && !implicitSolve) dict.subDictOrAdd("QMOMCoeffs").set("usingMULES", std::string("true"));
             pbe::PBEMethods::QMOM q(dict, phase, m0.data());
             std::vector<double>().swap(m0);
             replay("quadratureMethodOfMoments", q, R, V, steps, globalCells, 1.0, "cell_updates_per_s", std::cbrt(volUnit));

@@ -436,6 +436,12 @@ int pbe_moc_state_device(pbe_moc_state *st, double **n_dev, int64_t *stride, dou
 /* MOC::solveWithMULES (MOC.C:198-272) instead of the zero-flux update: the mesh's face
  * addressing and the div(phi,n.*) scheme; correct_resident then wants phi_host. */
 int pbe_moc_state_attach_mesh(pbe_moc_state *st, pbe_mesh *mesh, int scheme);
+/* usingMULES false -- the reference's default (MOC.C:58, 177-180; QMOM.C:71, 112-115): correct_resident then runs
+ * solveWithFVM (pbe_transport_implicit with these controls) instead of solveWithMULES.  controls NULL switches back.
+ * Needs an attached mesh with PBE_DIV_UPWIND.  solver_performance: what OpenFOAM prints per field for the LAST step,
+ * HOST perf [N] ([2 * order] for QMOM). */
+int pbe_moc_state_set_implicit(pbe_moc_state *st, const pbe_fvm_controls *controls);
+int pbe_moc_state_solver_performance(pbe_moc_state *st, pbe_fvm_perf *perf);
 
 /* What MOC::correct() prints every step (MOC.C:181-183, 276-279) plus configs[3]'s global
  * moments.  HOST memory; the caller all-reduces across ranks (pbe_comm_*). */
@@ -470,6 +476,8 @@ int pbe_qmom_state_d(pbe_qmom_state *st, double *d_host); /* d = (6/pi m1/m0)^(1
 int pbe_qmom_state_device(pbe_qmom_state *st, double **m_dev, int64_t *stride, double **d_dev,
                           double **S_dev);
 int pbe_qmom_state_attach_mesh(pbe_qmom_state *st, pbe_mesh *mesh, int scheme);
+int pbe_qmom_state_set_implicit(pbe_qmom_state *st, const pbe_fvm_controls *controls);
+int pbe_qmom_state_solver_performance(pbe_qmom_state *st, pbe_fvm_perf *perf);
 
 /* printAvgMaxMin (Utility.C:4-10) of what QMOM::correct() prints each step: per moment source
  * (QMOM.C:109), per moment (QMOM.C:122) and d (QMOM.C:128).  Each entry is {sum f V, sum V, max,

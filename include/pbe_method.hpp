@@ -216,6 +216,12 @@ struct FaceMesh {
     const double *Sf = nullptr;             // fvMesh::Sf() [nInternalFaces + nBoundaryFaces][3]
     const double *C = nullptr;              // fvMesh::C()  [ncells][3]
     const double *weights = nullptr;        // fvMesh::weights() [nInternalFaces]
+    // usingMULES false -- the reference's default -- solves fvm::ddt + fvm::div(phi, n_k, "div(U,nk)") == S
+    // (MOC.C:186-198, QMOM.C:201-209): the implicit term's scheme and what fvSolution says about the equation
+    std::string implicitDivScheme = "Gauss upwind"; // fvSchemes: "div\\(U,nk\\)" / "div\\(phi.*,m.*\\)"
+    double tolerance = 1e-5, relTol = 0.0;          // fvSolution: solvers { "n.*" { tolerance; relTol; minIter; maxIter; } }
+    int minIter = 1, maxIter = 1000;                // (values of the reference's cases, e.g. tests/validation/.../c01/system/fvSolution:47-55)
+    double relaxationFactor = 0.0;                  // fvSolution: relaxationFactors { equations { ".*" 1; } }; 0 = none
 };
 
 // ---- RAII over the C-ABI context and device buffers -------------------------------------------------
@@ -365,6 +371,13 @@ inline void tryUnpin(pbe_ctx *ctx, const void *p) {
     if (p) (void)pbe_host_unregister(ctx, const_cast<void *>(p));
 }
 // device mesh of a FaceMesh (+ geometry for the limited schemes)
+inline pbe_fvm_controls fvmControls(const FaceMesh &fm) {
+    pbe_fvm_controls c;
+    c.tolerance = fm.tolerance, c.rel_tol = fm.relTol, c.min_iter = fm.minIter, c.max_iter = fm.maxIter;
+    c.relaxation = fm.relaxationFactor, c.solver = PBE_FVM_SOLVER_AUTO;
+    return c;
+}
+
 inline pbe_mesh *makeDeviceMesh(pbe_ctx *ctx, const Phase &phase, int scheme, const char *where) {
     const FaceMesh &fm = *phase.mesh;
     pbe_mesh *m = nullptr;
@@ -414,13 +427,15 @@ public:
         classMin_.assign((size_t)N_, 0.0);
         classMax_.assign((size_t)N_, 0.0);
         if (phase.mesh && nc) {
-            if (!usingMULES_)
-                throw FatalError("MOC: usingMULES false selects the implicit fvm::ddt + fvm::div solve "
-                                 "(MOC.C:186-198), which has no device path; set usingMULES true");
             if (!phase.V) throw FatalError("MOC: transport needs the cell volumes (Phase::V)");
-            check(pbe_div_scheme_type(phase.mesh->divScheme.c_str(), &scheme_), "MOC::MOC div(phi,n.*)");
+            const std::string &sch = usingMULES_ ? phase.mesh->divScheme : phase.mesh->implicitDivScheme;
+            check(pbe_div_scheme_type(sch.c_str(), &scheme_), usingMULES_ ? "MOC::MOC div(phi,n.*)" : "MOC::MOC div(U,nk)");
             mesh_ = makeDeviceMesh(ctx_.get(), phase, scheme_, "MOC::MOC mesh");
             check(pbe_moc_state_attach_mesh(state_, mesh_, scheme_), "MOC::MOC");
+            if (!usingMULES_) { // solveWithFVM (MOC.C:177-180, 186-198), the reference's default
+                const pbe_fvm_controls ctl = fvmControls(*phase.mesh);
+                check(pbe_moc_state_set_implicit(state_, &ctl), "MOC::MOC usingMULES false");
+            }
             tryPin(ctx_.get(), phase.mesh->phi, (phase.mesh->nInternalFaces + phase.mesh->nBoundaryFaces) * 8);
         }
         for (const double *p : {phase.epsilon, phase.rho, phase.nu, phase.alpha}) tryPin(ctx_.get(), p, nc * 8);
@@ -468,6 +483,12 @@ public:
     double classMin(int i) const { return classMin_[(size_t)i]; }
     double classMax(int i) const { return classMax_[(size_t)i]; }
     double continuityError() const { return continuityError_; }
+    // "Solving for n<i>, Initial residual = .., Final residual = .., No Iterations .." of the last implicit step
+    std::vector<pbe_fvm_perf> solverPerformance() const {
+        std::vector<pbe_fvm_perf> p((size_t)N_);
+        check(pbe_moc_state_solver_performance(state_, p.data()), "MOC::solverPerformance");
+        return p;
+    }
     double *deviceClassFields() const { // [N][ncells], for callers that chain their own device work
         double *n = nullptr;
         check(pbe_moc_state_device(state_, &n, nullptr, nullptr), "MOC::deviceClassFields");
@@ -502,13 +523,15 @@ public:
         if (m0) check(pbe_qmom_state_upload(state_, nc, m0), "QMOM::QMOM");
         stats_.assign((size_t)(4 * order_ + 1) * 4, 0.0);
         if (phase.mesh && nc) {
-            if (!usingMULES_)
-                throw FatalError("QMOM: usingMULES false selects the implicit fvm::ddt + fvm::div solve "
-                                 "(QMOM.C:199-209), which has no device path; set usingMULES true");
             if (!phase.V) throw FatalError("QMOM: transport needs the cell volumes (Phase::V)");
-            check(pbe_div_scheme_type(phase.mesh->divScheme.c_str(), &scheme_), "QMOM::QMOM div(phi,m.*)");
+            const std::string &sch = usingMULES_ ? phase.mesh->divScheme : phase.mesh->implicitDivScheme;
+            check(pbe_div_scheme_type(sch.c_str(), &scheme_), "QMOM::QMOM div(phi,m.*)");
             mesh_ = makeDeviceMesh(ctx_.get(), phase, scheme_, "QMOM::QMOM mesh");
             check(pbe_qmom_state_attach_mesh(state_, mesh_, scheme_), "QMOM::QMOM");
+            if (!usingMULES_) { // solveWithFVM (QMOM.C:112-115, 201-209), the reference's default
+                const pbe_fvm_controls ctl = fvmControls(*phase.mesh);
+                check(pbe_qmom_state_set_implicit(state_, &ctl), "QMOM::QMOM usingMULES false");
+            }
             tryPin(ctx_.get(), phase.mesh->phi, (phase.mesh->nInternalFaces + phase.mesh->nBoundaryFaces) * 8);
         }
         d_host_.assign((size_t)nc, 0.0);

@@ -158,6 +158,8 @@ PROTOTYPES = {
     "pbe_moc_state_d": (C.c_int, [_vp, _vp]),
     "pbe_moc_state_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_i64), C.POINTER(_vp)]),
     "pbe_moc_state_attach_mesh": (C.c_int, [_vp, _vp, C.c_int]),
+    "pbe_moc_state_set_implicit": (C.c_int, [_vp, _vp]),
+    "pbe_moc_state_solver_performance": (C.c_int, [_vp, _vp]),
     "pbe_moc_correct_resident": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_double, _vp,
                                            C.POINTER(MocDiag)]),
     "pbe_qmom_state_create": (C.c_int, [_vp, _i64, _vp, C.POINTER(_vp)]),
@@ -167,6 +169,8 @@ PROTOTYPES = {
     "pbe_qmom_state_d": (C.c_int, [_vp, _vp]),
     "pbe_qmom_state_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_i64), C.POINTER(_vp), C.POINTER(_vp)]),
     "pbe_qmom_state_attach_mesh": (C.c_int, [_vp, _vp, C.c_int]),
+    "pbe_qmom_state_set_implicit": (C.c_int, [_vp, _vp]),
+    "pbe_qmom_state_solver_performance": (C.c_int, [_vp, _vp]),
     "pbe_qmom_correct_resident": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_double, _vp,
                                             C.POINTER(QmomDiag)]),
     "pbe_comm_unique_id": (C.c_int, [_vp]),

@@ -6,7 +6,7 @@
 //
 // OpenFOAM's fvMatrix / lduMatrix solvers are third-party code absent from the reference tree: PARITY UNPINNED.  The
 // matrix is assembled as OpenFOAM 3.0.x assembles it (EulerDdtScheme::fvmDdt, gaussConvectionScheme::fvmDiv,
-// fvMatrix::relax) -- the same restatement oracle/ref_shim drives the reference's own sources through -- and solved to
+// fvMatrix::relax) -- the restatement the test infrastructure drives the reference's own sources through -- and solved to
 // OpenFOAM's own stopping criterion, but by a solver made for this machine:
 //
 //   * the reference solves field after field (100 classes = 100 matrices assembled and solved one by one) with PBiCG +

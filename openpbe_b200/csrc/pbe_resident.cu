@@ -254,6 +254,10 @@ struct pbe_moc_state {
     int scheme = 0;
     int64_t nf = 0, nbnd = 0;
     double *S = nullptr, *nNew = nullptr, *phi = nullptr, *psi_b = nullptr, *psi_max = nullptr;
+    // usingMULES false (MOC.C:58, 177-180): solveWithFVM, the implicit solve
+    bool implicit = false;
+    pbe_fvm_controls fvm{};
+    std::vector<pbe_fvm_perf> perf;
     // diagnostics: [N][4] row statistics, then cont_err, then 8 moments
     double *diag = nullptr, *part = nullptr, *diag_host = nullptr;
     int parts_total = 0;
@@ -386,7 +390,11 @@ int moc_correct_impl(pbe_moc_state *s, const double *eps_h, const double *rho_h,
         // the continuity check (MOC.C:254-279) and the per-class statistics of the new fields
         PBE_CUDA(cudaStreamWaitEvent(P.s_comp, P.ev_in[nchunks - 1], 0));
         int rc;
-        if (s->scheme == PBE_DIV_UPWIND) { // the limited correction is identically zero
+        if (s->implicit) { // MOC::solveWithFVM (MOC.C:186-198): fvm::ddt + fvm::div == S, all classes at once
+            s->perf.resize((size_t)N);
+            rc = pbe_transport_implicit(s->mesh, s->scheme, N, nc, s->n, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
+                                        s->S, dt, &s->fvm, s->nNew, s->perf.data(), P.s_comp);
+        } else if (s->scheme == PBE_DIV_UPWIND) { // the limited correction is identically zero
             rc = pbe_transport_explicit(s->mesh, s->scheme, N, nc, s->n, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
                                         s->S, dt, s->nNew, P.s_comp);
         } else { // MULES::limit against max(alpha V / xi_k) (MOC.C:238-249), limitSum, explicitSolve
@@ -592,6 +600,26 @@ int pbe_moc_state_attach_mesh(pbe_moc_state *s, pbe_mesh *mesh, int scheme) {
     return PBE_OK;
 }
 
+int pbe_moc_state_set_implicit(pbe_moc_state *s, const pbe_fvm_controls *controls) {
+    PBE_REQUIRE(s != nullptr, PBE_E_INVALID, "pbe_moc_state_set_implicit: NULL state");
+    PBE_REQUIRE(controls == nullptr || s->mesh != nullptr, PBE_E_INVALID,
+                "pbe_moc_state_set_implicit: attach a mesh first (pbe_moc_state_attach_mesh)");
+    PBE_REQUIRE(controls == nullptr || s->scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
+                "pbe_moc_state_set_implicit: only `Gauss upwind` has an implicit device path");
+    s->implicit = controls != nullptr;
+    if (controls) s->fvm = *controls;
+    s->perf.clear();
+    return PBE_OK;
+}
+
+int pbe_moc_state_solver_performance(pbe_moc_state *s, pbe_fvm_perf *perf) {
+    PBE_REQUIRE(s && perf, PBE_E_INVALID, "pbe_moc_state_solver_performance: NULL argument");
+    PBE_REQUIRE((int)s->perf.size() == s->N, PBE_E_INVALID,
+                "pbe_moc_state_solver_performance: no implicit step has run on this state");
+    std::copy(s->perf.begin(), s->perf.end(), perf);
+    return PBE_OK;
+}
+
 int pbe_moc_correct_resident(pbe_moc_state *s, const double *eps_host, const double *rho_host,
                              const double *nu_host, const double *alpha_host, const double *phi_host,
                              const double *psi_b_host, int64_t stride_b, double dt, double *d_host,
@@ -610,7 +638,7 @@ int pbe_moc_correct_resident(pbe_moc_state *s, const double *eps_host, const dou
                 "pbe_moc_correct_resident: phi / psi_b without an attached mesh (pbe_moc_state_attach_mesh)");
     PBE_REQUIRE(psi_b_host == nullptr || stride_b >= s->nbnd, PBE_E_INVALID,
                 "pbe_moc_correct_resident: stride_b < boundary faces");
-    PBE_REQUIRE(s->mesh == nullptr || s->scheme == PBE_DIV_UPWIND || (alpha_host != nullptr && s->have_vcell),
+    PBE_REQUIRE(s->mesh == nullptr || s->implicit || s->scheme == PBE_DIV_UPWIND || (alpha_host != nullptr && s->have_vcell),
                 PBE_E_INVALID,
                 "pbe_moc_correct_resident: the MULES limiter's bound max(alpha V / xi_k) (MOC.C:238) needs alpha "
                 "and the cell volumes");
@@ -637,6 +665,9 @@ struct pbe_qmom_state {
     int scheme = 0;
     int64_t nf = 0, nbnd = 0;
     double *mNew = nullptr, *phi = nullptr, *psi_b = nullptr, *psi_max = nullptr;
+    bool implicit = false; // usingMULES false (QMOM.C:71, 112-115): solveWithFVM
+    pbe_fvm_controls fvm{};
+    std::vector<pbe_fvm_perf> perf;
     double *diag = nullptr, *part = nullptr, *diag_host = nullptr; // [2 nm + 1][4]
     int parts_total = 0;
     Pipeline pipe;
@@ -717,7 +748,11 @@ int qmom_correct_impl(pbe_qmom_state *s, const double *eps_h, const double *rho_
     if (s->mesh) {
         int rc = pbe_field_scrub_nan(ctx, (int64_t)nm * nc, s->S, P.s_comp); // QMOM.C:101-107
         if (rc) return rc;
-        if (s->scheme == PBE_DIV_UPWIND) {
+        if (s->implicit) { // QMOM::solveWithFVM (QMOM.C:201-209)
+            s->perf.resize((size_t)nm);
+            rc = pbe_transport_implicit(s->mesh, s->scheme, nm, nc, s->m, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
+                                        s->S, dt, &s->fvm, s->mNew, s->perf.data(), P.s_comp);
+        } else if (s->scheme == PBE_DIV_UPWIND) {
             rc = pbe_transport_explicit(s->mesh, s->scheme, nm, nc, s->m, s->phi, psi_b_h ? s->psi_b : nullptr, s->nbnd,
                                         s->S, dt, s->mNew, P.s_comp); // QMOM.C:131-197
         } else { // MULES::limit against 1.2 max(m_k) (QMOM.C:171-182), limitSum, explicitSolve
@@ -894,6 +929,26 @@ int pbe_qmom_state_attach_mesh(pbe_qmom_state *s, pbe_mesh *mesh, int scheme) {
     s->scheme = scheme;
     s->nf = nint + nbnd;
     s->nbnd = nbnd;
+    return PBE_OK;
+}
+
+int pbe_qmom_state_set_implicit(pbe_qmom_state *s, const pbe_fvm_controls *controls) {
+    PBE_REQUIRE(s != nullptr, PBE_E_INVALID, "pbe_qmom_state_set_implicit: NULL state");
+    PBE_REQUIRE(controls == nullptr || s->mesh != nullptr, PBE_E_INVALID,
+                "pbe_qmom_state_set_implicit: attach a mesh first (pbe_qmom_state_attach_mesh)");
+    PBE_REQUIRE(controls == nullptr || s->scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
+                "pbe_qmom_state_set_implicit: only `Gauss upwind` has an implicit device path");
+    s->implicit = controls != nullptr;
+    if (controls) s->fvm = *controls;
+    s->perf.clear();
+    return PBE_OK;
+}
+
+int pbe_qmom_state_solver_performance(pbe_qmom_state *s, pbe_fvm_perf *perf) {
+    PBE_REQUIRE(s && perf, PBE_E_INVALID, "pbe_qmom_state_solver_performance: NULL argument");
+    PBE_REQUIRE((int)s->perf.size() == s->nm, PBE_E_INVALID,
+                "pbe_qmom_state_solver_performance: no implicit step has run on this state");
+    std::copy(s->perf.begin(), s->perf.end(), perf);
     return PBE_OK;
 }
 

@@ -344,6 +344,11 @@ def _hptr(t):
     return None if t is None else C.c_void_p(_as_host(t).data_ptr())
 
 
+def _fvm_controls(tolerance=1e-5, rel_tol=0.0, min_iter=1, max_iter=1000, relaxation=0.0, solver="auto"):
+    return capi.FvmControls(float(tolerance), float(rel_tol), int(min_iter), int(max_iter), float(relaxation),
+                            {"auto": 0, "bicgstab": 1, "jacobi": 2}[solver] if isinstance(solver, str) else int(solver))
+
+
 class MOCState:
     """pbe_moc_state: the class fields owned on the device, as PBEMethods::MOC owns
     classNumberDensity_ (MOC.H:66, MOC.C:69-77); `correct()` is one MOC::correct() + d() with only
@@ -359,6 +364,18 @@ class MOCState:
             self.upload(n0)
         if mesh is not None:
             capi.check(capi.lib().pbe_moc_state_attach_mesh(self._h, mesh._h, div_scheme(scheme)))
+
+    def set_implicit(self, on=True, **controls):
+        """usingMULES false (MOC.C:58, 177-180): correct() solves fvm::ddt + fvm::div == S (solveWithFVM) instead of
+        the MULES update; controls as fvSolution's (tolerance, rel_tol, min_iter, max_iter, relaxation, solver)."""
+        ctl = _fvm_controls(**controls) if on else None
+        capi.check(capi.lib().pbe_moc_state_set_implicit(self._h, C.byref(ctl) if on else None))
+
+    def solver_performance(self):
+        """[(initial residual, final residual, iterations, state)] per class of the last implicit step"""
+        perf = (capi.FvmPerf * self.moc.N)()
+        capi.check(capi.lib().pbe_moc_state_solver_performance(self._h, C.cast(perf, C.c_void_p)))
+        return [(p.initial_residual, p.final_residual, p.iterations, p.state) for p in perf]
 
     def close(self):
         if self._h:
@@ -438,6 +455,18 @@ class QMOMState:
             self.upload(m0)
         if mesh is not None:
             capi.check(capi.lib().pbe_qmom_state_attach_mesh(self._h, mesh._h, div_scheme(scheme)))
+
+    def set_implicit(self, on=True, **controls):
+        """usingMULES false (QMOM.C:71, 112-115): correct() solves fvm::ddt + fvm::div == S (solveWithFVM) instead of
+        the MULES update; controls as fvSolution's (tolerance, rel_tol, min_iter, max_iter, relaxation, solver)."""
+        ctl = _fvm_controls(**controls) if on else None
+        capi.check(capi.lib().pbe_qmom_state_set_implicit(self._h, C.byref(ctl) if on else None))
+
+    def solver_performance(self):
+        """[(initial residual, final residual, iterations, state)] per moment of the last implicit step"""
+        perf = (capi.FvmPerf * (2 * self.q.order))()
+        capi.check(capi.lib().pbe_qmom_state_solver_performance(self._h, C.cast(perf, C.c_void_p)))
+        return [(p.initial_residual, p.final_residual, p.iterations, p.state) for p in perf]
 
     def close(self):
         if self._h:

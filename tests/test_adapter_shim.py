@@ -195,6 +195,43 @@ def test_moc_correct_with_transport_matches_oracle(shim, tmp_path, oracle):
 
 
 @pytest.mark.gpu
+def test_moc_correct_default_branch_is_the_implicit_solve(shim, tmp_path, oracle):
+    """usingMULES absent = false, the reference's default (MOC.C:58): MOC::correct() through the adapter runs
+    solveWithFVM on the device -- oracle sources + the direct solve of the restated fvMatrix; fvSolution's controls come
+    from the dictionary in the shim build."""
+    from oracle import fvm_implicit as fvm
+    tm = synthetic.block_mesh(14, 11, 9, velocity=(1.0, -0.5, 0.25))
+    nc = 14 * 11 * 9
+    w = synthetic.workload("moc30_ct", nc)
+    f = synthetic.moc_fields(w)
+    vcell = float(tm["vcell"][0])
+    dt = 0.02  # Courant ~0.5: far beyond what the case's 2.5e-4 would give, still cheap
+    text = ("method methodOfClasses; MOCCoeffs { numberOfClasses %d; xi1 %r; tolerance 1e-13; minIter 1; }" % (w.N, w.xi1)
+            + C01 % (tuple(w.coal_coeffs) + tuple(w.br_coeffs)))
+    K = w.N
+    (tmp_path / "dict").write_text(text)
+    np.concatenate([[K, nc, dt, vcell], f["n"].ravel(), f["eps"], f["rho"], f["nu"], f["alpha"]]).tofile(tmp_path / "in.bin")
+    _write_mesh(tmp_path / "mesh.bin", tm)
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "2",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout + p.stderr
+    r = np.fromfile(tmp_path / "out.bin")
+    n, d = r[:K * nc].reshape(K, nc), r[K * nc:K * nc + nc]
+    sp = oracle.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+    n_o = f["n"].copy()
+    for _ in range(2):
+        S, scale = oracle.moc_source(sp, w.N, w.xi1, w.relax, n_o, f["eps"], f["rho"], f["nu"], dt)
+        n_o = fvm.solve(tm, tm["phi"], dt, n_o, S=S)
+    assert np.all(np.abs(n - n_o) <= 1e-9 * np.abs(n_o).max(axis=1, keepdims=True))
+    np.testing.assert_allclose(d, oracle.moc_d(n_o, w.xi1), rtol=1e-9)
+    # a limited scheme in the implicit term has no device path: FatalError, not a silent change of scheme
+    (tmp_path / "dict").write_text(text.replace("minIter 1;", "minIter 1; implicitDivScheme Gauss vanLeer;"))
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 1 and "Gauss upwind only" in p.stdout and "FOAM exiting" in p.stdout
+
+
+@pytest.mark.gpu
 def test_moc_correct_with_vanleer_mules_matches_port(shim, tmp_path, oracle):
     """The scheme the reference's validation case selects (c01/system/fvSchemes:34) through the adapter:
     MOC::correct() with solveWithMULES = sources, MULES::limit against max(alpha V / xi_k), limitSum,

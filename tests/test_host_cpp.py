@@ -148,6 +148,42 @@ def test_replay_driver_with_transport(oracle):
     assert tail["min_n0"] >= 0.0
 
 
+@pytest.mark.gpu
+def test_replay_driver_with_the_implicit_solve(oracle):
+    """usingMULES left at the reference's default (false): both methods run solveWithFVM.  At a small Courant number the
+    implicit and the explicit upwind update agree to first order in dt; at Courant 5 -- where the explicit update would
+    blow up -- the implicit one stays bounded; zero velocity is the zero-flux update."""
+    exe = os.path.join(ROOT, "apps", "pbe_replay")
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "apps"), "-s"])
+
+    def run(*extra):
+        out = subprocess.check_output([exe, "--mesh", "30", "20", "24", "--steps", "3", "--classes", "30", *extra], text=True)
+        rows = [json.loads(ln) for ln in out.splitlines() if ln.startswith("{")]
+        return [r for r in rows if r["method"] == "methodOfClasses" and "step" in r], rows
+
+    expl, _ = run("--courant", "0.05")
+    impl, rows = run("--implicit", "--courant", "0.05")
+    for a, b in zip(expl, impl):
+        assert abs(a["d_avg"] / b["d_avg"] - 1) < 1e-4 and abs(a["d_max"] / b["d_max"] - 1) < 1e-2
+    perf = [r for r in rows if r.get("transport") == "solveWithFVM"][0]
+    assert 1 <= perf["iterations"][0] <= perf["iterations"][1] <= 10 and perf["final_residual_max"] < 1e-5
+    big, rows = run("--implicit", "--courant", "5")
+    still, _ = run("--implicit", "--velocity", "0", "0", "0")
+    for b in big:  # deltaT is 400 x the default here: the populations evolve much further, and stay physical
+        assert 1e-5 < b["d_min"] <= b["d_avg"] <= b["d_max"] < 2e-3
+    tail = [r for r in rows if "min_n0" in r][0]
+    assert tail["min_n0"] >= 0.0  # M-matrix: no class goes negative at any Courant number
+    perf = [r for r in rows if r.get("transport") == "solveWithFVM"][0]
+    assert perf["iterations"][1] > 10 and perf["final_residual_max"] < 1e-5
+    qm = [r for r in rows if r["method"] == "quadratureMethodOfMoments" and "step" in r]
+    assert len(qm) == 3 and all(1e-5 < r["d_min"] <= r["d_max"] < 2e-3 for r in qm)
+    out = subprocess.check_output([exe, "--cells", str(30 * 20 * 24), "--steps", "3", "--classes", "30"], text=True)
+    flat = [json.loads(ln) for ln in out.splitlines() if ln.startswith("{")]
+    flat = [r for r in flat if r["method"] == "methodOfClasses" and "step" in r]
+    for a, b in zip(still, flat):
+        assert abs(a["d_avg"] / b["d_avg"] - 1) < 1e-9 and abs(a["d_max"] / b["d_max"] - 1) < 1e-9
+
+
 MOM_PROBE = r'''
 #include "pbe_method.hpp"
 #include <cstdio>

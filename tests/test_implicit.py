@@ -283,3 +283,71 @@ def test_device_implicit_argument_errors(ctx):
     with pytest.raises(capi.PbeError, match="solver"):
         mesh.transport_implicit(psi, T(m["phi"]), 0.1, solver=7)
     mesh.close()
+
+
+@pytest.mark.gpu
+def test_resident_moc_correct_with_the_implicit_solve(ctx, oracle):
+    """MOC::correct() with usingMULES false (the reference's default) through the resident C-ABI call: the device's own
+    sources, then the implicit solve of every class; two steps, compared with the direct solution."""
+    from openpbe_b200 import engine
+    tm = synthetic.block_mesh(14, 12, 10, velocity=(1.0, -0.5, 0.25))
+    nc = 14 * 12 * 10
+    w = synthetic.workload("moc30_ct", nc)
+    f = synthetic.moc_fields(w)
+    f["n"] *= 1.0 + 5.0 * np.sin(np.arange(nc) * 0.7)[None, :] ** 2
+    dt = 0.03
+    spec = engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+    moc = engine.MOC(ctx, w.N, w.xi1, spec, w.relax)
+    mesh = engine.Mesh(ctx, tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"])
+    st = engine.MOCState(moc, nc, vcell=tm["vcell"], n0=f["n"], mesh=mesh, scheme="Gauss upwind")
+    with pytest.raises(engine.capi.PbeError, match="no implicit step"):
+        st.solver_performance()
+    st.set_implicit(tolerance=1e-13)
+    n = f["n"]
+    for _ in range(2):
+        S_dev = moc.source(T(n), T(f["eps"]), T(f["rho"]), T(f["nu"]), dt).cpu().numpy()
+        want = fvm.solve(tm, tm["phi"], dt, n, S=S_dev)
+        d, diag = st.correct(f["eps"], f["rho"], f["nu"], f["alpha"], dt, phi=tm["phi"], minmax=True)
+        n_g = st.download().numpy()
+        scale = np.abs(want).max(axis=1, keepdims=True)
+        assert np.all(np.abs(n_g - want) <= 1e-10 * scale)
+        assert np.allclose(d.numpy(), oracle.moc_d(n_g, w.xi1), rtol=1e-12)
+        assert np.array_equal(diag["class_min"], n_g.min(axis=1))
+        perf = st.solver_performance()
+        assert len(perf) == w.N and all(p[3] == 1 and p[1] < 1e-13 for p in perf)
+        n = n_g
+    # back to the explicit update
+    st.set_implicit(False)
+    st.correct(f["eps"], f["rho"], f["nu"], f["alpha"], dt, phi=tm["phi"])
+    S_dev = moc.source(T(n), T(f["eps"]), T(f["rho"]), T(f["nu"]), dt)
+    want = mesh.transport_explicit(T(n), T(tm["phi"]), dt, S=S_dev).cpu().numpy()
+    assert np.array_equal(st.download().numpy(), want)
+    st.close(); mesh.close(); moc.close()
+
+
+@pytest.mark.gpu
+def test_resident_qmom_correct_with_the_implicit_solve(ctx, oracle):
+    from openpbe_b200 import engine
+    tm = synthetic.block_mesh(16, 9, 7, velocity=(0.5, 1.0, -0.25))
+    nc = 16 * 9 * 7
+    w = synthetic.workload("qmom3_const", nc)
+    f = synthetic.qmom_fields(w, degenerate_fraction=0.0)
+    dt = 0.02
+    spec = engine.make_spec(w.coalescence, w.coal_coeffs, w.breakup, w.br_coeffs)
+    q = engine.QMOM(ctx, w.N, spec)
+    mesh = engine.Mesh(ctx, tm["owner"], tm["neighbour"], tm["boundary_owner"], tm["vcell"])
+    st = engine.QMOMState(q, nc, vcell=tm["vcell"], m0=f["m"], mesh=mesh, scheme="Gauss upwind")
+    st.set_implicit(tolerance=1e-13, min_iter=1)
+    d, _ = st.correct(f["eps"], f["rho"], f["nu"], dt, phi=tm["phi"])
+    m_g = st.download().numpy()
+    S_dev = q.source(T(f["m"]), T(f["eps"]), T(f["rho"]), T(f["nu"])).cpu().numpy()
+    S_dev = np.where(np.isnan(S_dev), 0.0, S_dev)
+    want = np.maximum(fvm.solve(tm, tm["phi"], dt, f["m"], S=S_dev), 1e-15)  # QMOM.C:117-123
+    assert np.all(np.abs(m_g - want) <= 1e-10 * np.abs(want).max(axis=1, keepdims=True))
+    assert np.allclose(d.numpy(), np.cbrt(6.0 / np.pi * m_g[1] / m_g[0]), rtol=1e-13)
+    assert all(p[3] == 1 for p in st.solver_performance())
+    # a limited scheme has no implicit device path: said at set-up, not at the first step
+    st2 = engine.QMOMState(q, nc, vcell=tm["vcell"], m0=f["m"], mesh=mesh, scheme="Gauss vanLeer")
+    with pytest.raises(engine.capi.PbeError, match="Gauss upwind"):
+        st2.set_implicit()
+    st2.close(); st.close(); mesh.close(); q.close()
