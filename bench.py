@@ -1061,6 +1061,33 @@ def leg_transport(B: Bench, w, moc):
                                  "correction-flux, limiter-sweep and limitSum passes in between are what the "
                                  "fraction pays for", "traffic": None}}
         del pmax
+    if world == 1:
+        # MOC::solveWithFVM (MOC.C:186-198), the reference's DEFAULT branch (usingMULES false): fvm::ddt + fvm::div == S
+        # of all fields at once, stopped by the fvSolution of the reference's cases (tolerance 1e-5, relTol 0, minIter 1)
+        for _ in range(2):
+            _, perf = tmesh.transport_implicit(tpsi, tphi, tdt, S=tS, out=tout)
+        l0 = ctx.launch_count()
+        B.e0.record()
+        for _ in range(3):
+            tmesh.transport_implicit(tpsi, tphi, tdt, S=tS, out=tout)
+        B.e1.record()
+        torch.cuda.synchronize()
+        ims = B.e0.elapsed_time(B.e1) / 3
+        its = [p[2] for p in perf]
+        # set-up: psi and S in, x and z out (32 B per cell-field); every Jacobi sweep of a field: z in, x in / out,
+        # z out (32 B per cell-field); the per-cell rows are small beside them
+        ibytes = tc * 32.0 * (tK + sum(its)) + tc * (8 + 6 * 8 + 3 * 8 + 4 * 8)
+        transport["implicit"] = {
+            "metric": "transport_cell_field_updates_per_s", "value": tc * tK / (ims * 1e-3),
+            "unit": "cell-field-updates/s", "ms_per_step": ims, "scheme": "Euler implicit + Gauss upwind",
+            "controls": {"tolerance": 1e-5, "relTol": 0, "minIter": 1, "solver": "Jacobi (auto)"},
+            "iterations": [min(its), max(its)], "initial_residual_max": max(p[0] for p in perf),
+            "final_residual_max": max(p[1] for p in perf),
+            "launches_per_step": int((ctx.launch_count() - l0) // 3),
+            "roofline": {"bound": "hbm", "achieved": ibytes / (ims * 1e-3) / 1e9, "peak": B.hbm_peak, "unit": "GB/s",
+                         "frac": ibytes / (ims * 1e-3) / 1e9 / B.hbm_peak, "algorithmic_bytes": ibytes,
+                         "note": "bytes of the iteration actually run: 32 B per cell-field for the set-up and for "
+                                 "every sweep a field needed (DESIGN.md 4.11)", "traffic": None}}
     if not args.no_e2e and world == 1:
         # MOC::correct() with solveWithMULES through the resident state: class fields stay on the device,
         # pinned host eps, rho, nu, alpha, phi in, d out
@@ -1129,6 +1156,8 @@ def run_b200(args):
         roofline["legs"]["transport"] = transport["roofline"]
         if "mules" in transport:
             roofline["legs"]["transport_mules"] = transport["mules"]["roofline"]
+        if "implicit" in transport:
+            roofline["legs"]["transport_implicit"] = transport["implicit"]["roofline"]
 
     # ---- CPU baselines on this box's host cores (rank 0, N = 1 only) -----------------------------
     cpu = None

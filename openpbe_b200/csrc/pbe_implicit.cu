@@ -23,6 +23,7 @@
 // HBM per iteration and cell-field (hex mesh): matrix-vector products 2 x (8 read + 8 written; neighbour gathers hit
 // L1 / L2), s = r - alpha v 24 B, x / r update 56 B, p update 32 B: ~144 B = 6 x the explicit update's 24 B.
 #include <algorithm>
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
 
@@ -332,34 +333,80 @@ template <int W>
 __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
     __shared__ double wsum[kMaxChunk][kBlock / 32];
     const int k0 = blockIdx.y * q.chunk, kend = min(q.nfields, k0 + q.chunk);
-    bool any = false; // uniform over the CTA: a chunk whose fields have all converged costs a few loads
-    for (int k = k0; k < kend; ++k) any |= q.sc[k].state == 0;
-    if (!any) return;
+    // converged fields are skipped: uniform over the CTA, a chunk with none left costs a few loads
+    auto next_active = [&](int k) {
+        while (k < kend && q.sc[k].state != 0) ++k;
+        return k;
+    };
+    int k = next_active(k0);
+    if (k >= kend) return;
     const int64_t c0 = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     const bool valid = c0 < q.nc;
     const int64_t c = valid ? c0 : q.nc - 1;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     Row<W> R;
     load_row<W>(q, c, false, R);
-    for (int k = k0; k < kend; ++k) {
-        if (q.sc[k].state != 0) continue;
-        const size_t o = (size_t)k * q.nc;
-        const double *zin = q.p + o;
-        const double rz = -offdiag<W>(q, c, false, R, zin);
-        if (valid) {
-            q.x[(size_t)k * q.stride + c] += zin[c];
-            q.v[o + c] = R.dinv * rz;
+    if constexpr (W > 0) {
+        // The W gathered values of the NEXT active field travel global -> shared (LDGSTS) into this thread's own column
+        // while the current field is summed: no registers held by loads in flight, no barrier (nothing is shared
+        // between threads) -- the pipeline of the explicit update (pbe_transport.cu, sweep_async).  The coalesced
+        // streams (own z, x) go through registers one field ahead.
+        __shared__ double stage[2][W][kBlock];
+        auto cp8 = [](double *dst, const double *src) {
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                         : "memory");
+        };
+        double mine_n = 0.0, x_n = 0.0;
+        auto issue = [&](int kk, int par) {
+            if (kk < kend) {
+                const double *zin = q.p + (size_t)kk * q.nc;
+#pragma unroll
+                for (int s = 0; s < W; ++s) cp8(&stage[par][s][threadIdx.x], zin + R.col[s]);
+                mine_n = __ldg(zin + c);
+                x_n = q.x[(size_t)kk * q.stride + c];
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        int par = 0;
+        issue(k, par);
+        while (k < kend) {
+            const int kn = next_active(k + 1);
+            const double mine = mine_n, xv = x_n;
+            issue(kn, par ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+            double acc = 0.0;
+#pragma unroll
+            for (int s = 0; s < W; ++s) acc = fma(R.cf[s], stage[par][s][threadIdx.x], acc);
+            const double rz = -acc;
+            if (valid) {
+                __stcs(q.x + (size_t)k * q.stride + c, xv + mine);
+                __stcs(q.v + (size_t)k * q.nc + c, R.dinv * rz);
+            }
+            const double sum = warp_sum(valid ? fabs(rz) : 0.0);
+            if (lane == 0) wsum[k - k0][wid] = sum;
+            k = kn;
+            par ^= 1;
         }
-        const double s = warp_sum(valid ? fabs(rz) : 0.0);
-        if (lane == 0) wsum[k - k0][wid] = s;
+    } else {
+        for (; k < kend; k = next_active(k + 1)) {
+            const size_t o = (size_t)k * q.nc;
+            const double *zin = q.p + o;
+            const double rz = -offdiag<W>(q, c, false, R, zin);
+            if (valid) {
+                q.x[(size_t)k * q.stride + c] += zin[c];
+                q.v[o + c] = R.dinv * rz;
+            }
+            const double sum = warp_sum(valid ? fabs(rz) : 0.0);
+            if (lane == 0) wsum[k - k0][wid] = sum;
+        }
     }
     __syncthreads(); // one barrier per chunk, not per field: the warps' sums wait in shared memory
-    const int k = k0 + threadIdx.x;
-    if (k < kend && q.sc[k].state == 0) {
-        double s = 0.0;
+    const int kt = k0 + threadIdx.x;
+    if (kt < kend && q.sc[kt].state == 0) {
+        double sum = 0.0;
 #pragma unroll
-        for (int i = 0; i < kBlock / 32; ++i) s += wsum[threadIdx.x][i];
-        q.partial[(size_t)k * kNS * q.G + blockIdx.x] = s;
+        for (int i = 0; i < kBlock / 32; ++i) sum += wsum[threadIdx.x][i];
+        q.partial[(size_t)kt * kNS * q.G + blockIdx.x] = sum;
     }
 }
 
