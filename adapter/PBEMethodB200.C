@@ -435,22 +435,35 @@ addToRunTimeSelectionTable(PBEMethod, MOM, dictionary);
 
 MOM::MOM(const dictionary &pbeProperties, const phaseModel &phase)
     : PBEMethod(pbeProperties, phase), runTime(phase.mesh().time()), moments_(3), mom_(nullptr), mDev_(nullptr),
-      epsDev_(nullptr), rhoDev_(nullptr), nuDev_(nullptr), dDev_(nullptr), d_("diameter", phase.mesh(), 0.0) {
+      epsDev_(nullptr), rhoDev_(nullptr), nuDev_(nullptr), dDev_(nullptr), SDev_(nullptr), mNewDev_(nullptr), phiDev_(nullptr),
+      b200Mesh_(nullptr), scheme_(PBE_DIV_UPWIND), d_("diameter", phase.mesh(), 0.0) {
     const dictionary &MOMDict_ = pbeProperties.subDict("MOMCoeffs"); // MOM.C:68
     forAll(moments_, k) moments_.set(k, new volScalarField(fieldName("m", k), phase.mesh())); // MOM.C:128-141
-    if (phase.mesh().hasFaces())
-        FatalErrorIn("MOM::MOM") << "methodOfMoments transports its moments with the implicit fvm::ddt + fvm::div solve "
-                                    "(MOM.C:211-222), which has no device path" << exit(FatalError);
     // the reference reads nothing from MOMCoeffs; quadraturePanels sizes the fixed rule standing in for QAGIU
     b200Check(pbe_mom_create(ctx_, MOMDict_.lookupOrDefault<label>("quadraturePanels", 0), &spec_, &mom_), "MOM::MOM");
     const int64_t row = (int64_t)sizeof(double) * (phase.size() > 0 ? phase.size() : 1);
     b200Check(pbe_device_alloc(ctx_, 3 * row, (void **)&mDev_), "MOM::MOM");
+    if (phase.mesh().hasFaces()) { // MOM.C:211-222: fvm::ddt + fvm::div(phi, m_i) == S_i, relax(), solve() for the 3 moments
+#ifdef PBE_B200_REAL_OPENFOAM
+        const word divName = "div(" + phase.phi().name() + ',' + fieldName("m", 0) + ')';
+#else
+        const word divName = "div(phi,m0)";
+#endif
+        if (!implicitControlsOf(MOMDict_, fieldName("m", 0), divName, scheme_, fvm_))
+            FatalErrorIn("MOM::MOM") << "methodOfMoments solves fvm::ddt + fvm::div == S (MOM.C:211-222): the device path "
+                                        "has Gauss upwind only for the implicit term" << exit(FatalError);
+        b200Mesh_ = newDeviceMesh(scheme_, "MOM::MOM mesh");
+        b200Check(pbe_device_alloc(ctx_, 3 * row, (void **)&SDev_), "MOM::MOM");
+        b200Check(pbe_device_alloc(ctx_, 3 * row, (void **)&mNewDev_), "MOM::MOM");
+        b200Check(pbe_device_alloc(ctx_, (int64_t)sizeof(double) * phase.phi().size(), (void **)&phiDev_), "MOM::MOM");
+    }
     for (double **p : {&epsDev_, &rhoDev_, &nuDev_, &dDev_}) b200Check(pbe_device_alloc(ctx_, row, (void **)p), "MOM::MOM");
 }
 
 MOM::~MOM() {
-    for (double *p : {mDev_, epsDev_, rhoDev_, nuDev_, dDev_})
+    for (double *p : {mDev_, epsDev_, rhoDev_, nuDev_, dDev_, SDev_, mNewDev_, phiDev_})
         if (p) pbe_device_free(ctx_, p);
+    if (b200Mesh_) pbe_mesh_destroy(b200Mesh_);
     if (mom_) pbe_mom_destroy(mom_);
 }
 
@@ -467,9 +480,20 @@ void MOM::correct() {
     b200Check(pbe_memcpy_h2d(ctx_, epsDev_, epsilonData(), row), "MOM::correct");
     b200Check(pbe_memcpy_h2d(ctx_, rhoDev_, rhoHost_.cdata(), row), "MOM::correct");
     b200Check(pbe_memcpy_h2d(ctx_, nuDev_, nuHost_.cdata(), row), "MOM::correct");
-    b200Check(pbe_mom_step(mom_, nCells, nCells, mDev_, epsDev_, rhoDev_, nuDev_, runTime.deltaT().value(), nullptr, dDev_,
-                           nullptr, nullptr),
-              "MOM::correct");
+    if (b200Mesh_) { // sources, NaN scrub (MOM.C:198-207), the implicit solve (:211-222), clamp (:224-231), d (:233)
+        b200Check(pbe_mom_source(mom_, nCells, nCells, mDev_, epsDev_, rhoDev_, nuDev_, SDev_, nullptr, nullptr), "MOM::correct");
+        b200Check(pbe_field_scrub_nan(ctx_, (int64_t)3 * nCells, SDev_, nullptr), "MOM::correct");
+        b200Check(pbe_memcpy_h2d(ctx_, phiDev_, phase_.phi().cdata(), (int64_t)sizeof(double) * phase_.phi().size()), "MOM::correct");
+        b200Check(pbe_transport_implicit(b200Mesh_, scheme_, 3, nCells, mDev_, phiDev_, nullptr /* zeroGradient patches */, 0,
+                                         SDev_, runTime.deltaT().value(), &fvm_, mNewDev_, nullptr, nullptr),
+                  "MOM::correct");
+        std::swap(mDev_, mNewDev_);
+        b200Check(pbe_qmom_clamp_d(ctx_, 3, nCells, nCells, mDev_, dDev_, nullptr), "MOM::correct");
+    } else {
+        b200Check(pbe_mom_step(mom_, nCells, nCells, mDev_, epsDev_, rhoDev_, nuDev_, runTime.deltaT().value(), nullptr, dDev_,
+                               nullptr, nullptr),
+                  "MOM::correct");
+    }
     b200Check(pbe_sync(ctx_), "MOM::correct");
     forAll(moments_, k)
         b200Check(pbe_memcpy_d2h(ctx_, moments_[k].internalField().data_ptr(), mDev_ + (size_t)k * nCells, row), "MOM::correct");

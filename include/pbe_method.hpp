@@ -608,12 +608,17 @@ public:
         // the reference reads nothing from MOMCoeffs; quadraturePanels sets the fixed rule that
         // stands in for integrate()'s adaptive QAGIU (0 = PBE_MOM_DEFAULT_PANELS)
         const int panels = (int)c.lookupOrDefault<double>("quadraturePanels", 0.0);
-        if (phase.mesh)
-            throw FatalError("MOM: moment transport is the implicit fvm::ddt + fvm::div solve (MOM.C:211-222), "
-                             "which has no device path; run methodOfMoments without a FaceMesh");
         check(pbe_mom_create(ctx_.get(), panels, &spec_, &h_), "MOM::MOM");
         stageCellFields();
         const int64_t nc = phase.ncells;
+        if (phase.mesh && nc) { // MOM::correct() ends in fvm::ddt + fvm::div(phi, m_i) == S_i for the 3 moments (MOM.C:211-222)
+            if (!phase.V) throw FatalError("MOM: transport needs the cell volumes (Phase::V)");
+            check(pbe_div_scheme_type(phase.mesh->implicitDivScheme.c_str(), &scheme_), "MOM::MOM div(phi,m.*)");
+            mesh_ = makeDeviceMesh(ctx_.get(), phase, scheme_, "MOM::MOM mesh");
+            const int64_t nf = phase.mesh->nInternalFaces + phase.mesh->nBoundaryFaces;
+            mNew_ = DeviceArray(ctx_, 3 * nc), phi_ = DeviceArray(ctx_, nf);
+            if (phase.mesh->boundaryValues) psib_ = DeviceArray(ctx_, 3 * phase.mesh->nBoundaryFaces);
+        }
         m_ = DeviceArray(ctx_, 3 * nc), S_ = DeviceArray(ctx_, 3 * nc), gamma_ = DeviceArray(ctx_, 3 * nc);
         d_dev_ = DeviceArray(ctx_, nc);
         if (m0)
@@ -628,6 +633,7 @@ public:
         }
     }
     ~MOM() override {
+        if (mesh_) pbe_mesh_destroy(mesh_);
         if (h_) pbe_mom_destroy(h_);
     }
 
@@ -635,6 +641,23 @@ public:
     void correct() override {
         const int64_t nc = phase_.ncells;
         if (nc == 0) return;
+        if (mesh_) { // sources, NaN scrub (MOM.C:198-207), the implicit solve (:211-222), clamp (:224-231), d (:233)
+            const FaceMesh &fm = *phase_.mesh;
+            check(pbe_mom_source(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), S_.data(), gamma_.data(), nullptr),
+                  "MOM::correct");
+            check(pbe_field_scrub_nan(ctx_.get(), 3 * nc, S_.data(), nullptr), "MOM::correct");
+            phi_.upload(fm.phi, fm.nInternalFaces + fm.nBoundaryFaces);
+            if (fm.boundaryValues) psib_.upload(fm.boundaryValues, 3 * fm.nBoundaryFaces);
+            const pbe_fvm_controls ctl = fvmControls(fm);
+            perf_.resize(3);
+            check(pbe_transport_implicit(mesh_, scheme_, 3, nc, m_.data(), phi_.data(), fm.boundaryValues ? psib_.data() : nullptr,
+                                         fm.nBoundaryFaces, S_.data(), phase_.deltaT, &ctl, mNew_.data(), perf_.data(), nullptr),
+                  "MOM::correct");
+            std::swap(m_, mNew_);
+            check(pbe_qmom_clamp_d(ctx_.get(), 3, nc, nc, m_.data(), d_dev_.data(), nullptr), "MOM::correct");
+            d_stale_ = true;
+            return;
+        }
         check(pbe_mom_step(h_, nc, nc, m_.data(), eps_.data(), rho_.data(), nu_.data(), phase_.deltaT, S_.data(),
                            d_dev_.data(), gamma_.data(), nullptr),
               "MOM::correct");
@@ -660,7 +683,10 @@ public:
 
 private:
     pbe_mom *h_ = nullptr;
-    DeviceArray m_, S_, gamma_, d_dev_;
+    pbe_mesh *mesh_ = nullptr;
+    int scheme_ = 0;
+    std::vector<pbe_fvm_perf> perf_;
+    DeviceArray m_, S_, gamma_, d_dev_, mNew_, phi_, psib_;
     mutable std::vector<double> d_host_;
     mutable bool d_stale_ = true;
 };

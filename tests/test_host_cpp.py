@@ -249,3 +249,74 @@ def test_method_of_moments_host_mirror(tmp_path):
     d0 = float([ln for ln in out.splitlines() if ln.startswith("d0")][0].split()[1])
     r2 = rows[2]
     assert d0 == (6 / np.pi * r2[1] / r2[0]) ** (1 / 3) or abs(d0 / (6 / np.pi * r2[1] / r2[0]) ** (1 / 3) - 1) < 1e-15
+
+
+MOM_MESH_PROBE = r'''
+#include "pbe_method.hpp"
+#include <cstdio>
+// methodOfMoments on a chain of 6 cells (5 internal faces, an inlet and an outlet face) with a uniform flux: MOM::correct()
+// then ends in the implicit solve of MOM.C:211-222.  Prints moments before / after and the scrubbed sources.
+int main(int argc, char **argv) {
+    const int nc = 6;
+    const double flux = argc > 1 ? std::atof(argv[1]) : 0.0;
+    std::vector<double> m(3 * nc), eps(nc, 1.0), rho(nc, 1.0), nu(nc, 1.0), V(nc, 0.5), alpha(nc, 0.1);
+    for (int c = 0; c < nc; ++c) {
+        const double m0 = 1.0 + 0.3 * c, k = 1.5 + 0.4 * c, th = 0.2 + 0.05 * c;
+        m[c] = m0; m[nc + c] = m0 * k * th; m[2 * nc + c] = m0 * k * (k + 1) * th * th;
+    }
+    std::vector<int32_t> own = {0, 1, 2, 3, 4}, nei = {1, 2, 3, 4, 5}, bown = {0, 5};
+    std::vector<double> phi = {flux, flux, flux, flux, flux, -flux, flux};
+    pbe::FaceMesh fm;
+    fm.nInternalFaces = 5; fm.nBoundaryFaces = 2;
+    fm.owner = own.data(); fm.neighbour = nei.data(); fm.boundaryOwner = bown.data(); fm.phi = phi.data();
+    fm.tolerance = 1e-14;
+    pbe::Phase ph; ph.ncells = nc; ph.deltaT = 1e-2; ph.epsilon = eps.data(); ph.rho = rho.data(); ph.nu = nu.data();
+    ph.V = V.data(); ph.alpha = alpha.data(); ph.mesh = &fm;
+    auto dict = pbe::Dictionary::parse(R"(
+        method methodOfMoments; MOMCoeffs { }
+        coalescenceKernel constantCoalescence; breakupKernel binaryBreakup;
+        daughterParticleDistribution uniformBinaryBreakup;
+        constantCoalescenceCoeffs { constant 0.1; } binaryBreakupCoeffs { } uniformBinaryBreakupCoeffs { }
+    )");
+    try {
+        pbe::PBEMethods::MOM mom(dict, ph, m.data());
+        mom.correct();
+        for (int c = 0; c < nc; ++c) {
+            std::printf("cell");
+            for (int k = 0; k < 3; ++k) std::printf(" %.17g", m[k * nc + c]);
+            for (auto f : {pbe::PBEMethods::MOM::Moment, pbe::PBEMethods::MOM::Source})
+                for (int k = 0; k < 3; ++k) std::printf(" %.17g", mom.field(f, k)[c]);
+            std::printf(" %.17g\n", mom.d()[c]);
+        }
+    } catch (const pbe::FatalError &e) { std::printf("FATAL<<%s>>\n", e.what()); return 1; }
+    return 0;
+}
+'''
+
+
+@pytest.mark.gpu
+def test_method_of_moments_with_the_implicit_transport(tmp_path):
+    """MOM::correct() with face fluxes (MOM.C:211-222: fvm::ddt + fvm::div == S for the three moments): the host mirror's
+    result against the direct solve of the restated matrix with the device's own sources; zero flux = the zero-flux
+    update."""
+    from oracle import fvm_implicit as fvm
+    src = tmp_path / "mom_mesh_probe.cpp"
+    src.write_text(MOM_MESH_PROBE)
+    exe = tmp_path / "mom_mesh_probe"
+    subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I",
+                           os.path.join(ROOT, "include"), str(src), "-o", str(exe), "-L", LIBDIR,
+                           "-lpbe_b200", f"-Wl,-rpath,{LIBDIR}"])
+    mesh = {"owner": np.arange(5), "neighbour": np.arange(1, 6), "boundary_owner": np.array([0, 5]), "vcell": np.full(6, 0.5)}
+    for flux in (0.0, 3.0):
+        out = subprocess.check_output([str(exe), repr(flux)], text=True)
+        rows = np.array([ln.split()[1:] for ln in out.splitlines() if ln.startswith("cell")], dtype=float)
+        assert rows.shape == (6, 10), out
+        m_in, m_out, S, d = rows[:, 0:3].T, rows[:, 3:6].T, rows[:, 6:9].T, rows[:, 9]
+        phi = np.array([flux] * 5 + [-flux, flux])
+        want = np.maximum(fvm.solve(mesh, phi, 1e-2, m_in, S=S), 1e-15)
+        np.testing.assert_allclose(m_out, want, rtol=1e-12)
+        np.testing.assert_allclose(d, np.cbrt(6 / np.pi * m_out[1] / m_out[0]), rtol=1e-14)
+        if flux == 0.0:
+            np.testing.assert_allclose(m_out, m_in + 1e-2 * S, rtol=1e-14)
+        else:
+            assert np.abs(m_out - (m_in + 1e-2 * S)).max() > 1e-3  # the flux did move something
