@@ -108,7 +108,7 @@ int PBEMethod::divSchemeOf(const dictionary &coeffs, const char *where) const {
 // name fvm::div builds, "div(phi,m<k>)" (QMOM.C:203-204) -- and what fvSolution says about the equation: solvers {
 // "n.*" { tolerance; relTol; minIter; maxIter; } } and relaxationFactors { equations { ".*" f; } } (what eqn.relax()
 // looks up).  The linear solver named there (PBiCG + DILU, smoothSolver) is replaced by the device iteration; the
-// stopping criterion is kept.  Returns false when the scheme has no implicit device path (limited schemes).
+// stopping criterion is kept.  Returns false when the scheme has no device path (pbe_last_error() lists the valid ones).
 bool PBEMethod::implicitControlsOf(const dictionary &coeffs, const word &field, const word &divName, int &scheme,
                                    pbe_fvm_controls &ctl) const {
     ctl.tolerance = 1e-6, ctl.rel_tol = 0.0, ctl.min_iter = 0, ctl.max_iter = 1000; // lduMatrix::solver defaults
@@ -132,8 +132,7 @@ bool PBEMethod::implicitControlsOf(const dictionary &coeffs, const word &field, 
     ctl.max_iter = coeffs.lookupOrDefault<label>("maxIter", 1000);
     ctl.relaxation = coeffs.lookupOrDefault<scalar>("relaxationFactor", 0.0);
 #endif
-    if (pbe_div_scheme_type(name.c_str(), &scheme) != PBE_OK) return false; // e.g. Gauss limitedLinear 1
-    return scheme == PBE_DIV_UPWIND;
+    return pbe_div_scheme_type(name.c_str(), &scheme) == PBE_OK; // upwind, vanLeer, limitedLinear 1
 }
 
 pbe_mesh *PBEMethod::newDeviceMesh(int scheme, const char *where) const {
@@ -231,12 +230,11 @@ MOC::MOC(const dictionary &pbeProperties, const phaseModel &phase)
                 implicitOnDevice_ = true;
             } else {
 #ifdef PBE_B200_REAL_OPENFOAM
-                // a limited scheme in the implicit term: the solve stays on the host, see correct()
-                Info << "MOC: div(U,nk) is not Gauss upwind: sources on the device, fvm solve on the host" << endl;
+                // a scheme without a device path: the solve stays on the host, see correct()
+                Info << "MOC: div(U,nk) has no device path: sources on the device, fvm solve on the host" << endl;
 #else
-                FatalErrorIn("MOC::MOC") << "usingMULES false with a div(U,nk) scheme other than Gauss upwind: the implicit "
-                                            "fvm::ddt + fvm::div solve (MOC.C:186-198) has a device path for Gauss upwind only"
-                                         << exit(FatalError);
+                FatalErrorIn("MOC::MOC") << "usingMULES false, div(U,nk) of the implicit solve (MOC.C:186-198): "
+                                         << pbe_last_error() << exit(FatalError);
 #endif
             }
         } else {
@@ -362,9 +360,8 @@ QMOM::QMOM(const dictionary &pbeProperties, const phaseModel &phase)
             const word divName = "div(phi,m0)";
 #endif
             if (!implicitControlsOf(coeffs, fieldName("m", 0), divName, scheme, ctl))
-                FatalErrorIn("QMOM::QMOM") << "usingMULES false with a div(phi,m.*) scheme other than Gauss upwind: the implicit "
-                                              "fvm::ddt + fvm::div solve (QMOM.C:201-209) has a device path for Gauss upwind only"
-                                           << exit(FatalError);
+                FatalErrorIn("QMOM::QMOM") << "usingMULES false, div(phi,m.*) of the implicit solve (QMOM.C:201-209): "
+                                           << pbe_last_error() << exit(FatalError);
         } else {
             scheme = divSchemeOf(coeffs, "QMOM::QMOM div(phi,m.*)");
         }
@@ -450,8 +447,8 @@ MOM::MOM(const dictionary &pbeProperties, const phaseModel &phase)
         const word divName = "div(phi,m0)";
 #endif
         if (!implicitControlsOf(MOMDict_, fieldName("m", 0), divName, scheme_, fvm_))
-            FatalErrorIn("MOM::MOM") << "methodOfMoments solves fvm::ddt + fvm::div == S (MOM.C:211-222): the device path "
-                                        "has Gauss upwind only for the implicit term" << exit(FatalError);
+            FatalErrorIn("MOM::MOM") << "div(phi,m.*) of the implicit solve (MOM.C:211-222): " << pbe_last_error()
+                                     << exit(FatalError);
         b200Mesh_ = newDeviceMesh(scheme_, "MOM::MOM mesh");
         b200Check(pbe_device_alloc(ctx_, 3 * row, (void **)&SDev_), "MOM::MOM");
         b200Check(pbe_device_alloc(ctx_, 3 * row, (void **)&mNewDev_), "MOM::MOM");

@@ -250,10 +250,13 @@ int pbe_mesh_info(pbe_mesh *mesh, int64_t *ncells, int64_t *n_internal_faces,
 int pbe_mesh_regular_cells(pbe_mesh *mesh, int *faces_per_regular_cell, int64_t *n_regular);
 
 /* fvSchemes divSchemes entry "div(phi,n.*)" -> enum ("Gauss upwind" | "upwind" | "Gauss vanLeer" |
- * "vanLeer"); anything else returns PBE_E_UNKNOWN_TYPE with the valid names listed (the
+ * "vanLeer" | "Gauss limitedLinear 1" | "limitedLinear 1"); anything else returns PBE_E_UNKNOWN_TYPE with the valid names listed (the
  * reference's FatalError convention).  The reference's validation case selects Gauss vanLeer
  * (tests/validation/simmons_and_azzopardi/c01/system/fvSchemes:34). */
-enum { PBE_DIV_UPWIND = 0, PBE_DIV_VANLEER = 1 };
+enum { PBE_DIV_UPWIND = 0, PBE_DIV_VANLEER = 1,
+       PBE_DIV_LIMITEDLINEAR = 2 /* "Gauss limitedLinear 1": the implicit term only (pbe_transport_implicit), the
+                                    scheme of "div(U,nk)" in the reference's MOC cases (tests/integration/MOC/template/
+                                    system/fvSchemes:44) */ };
 int pbe_div_scheme_type(const char *scheme_name, int *out);
 
 /* Mesh geometry the limited schemes need (fvMesh::Sf(), C(), weights()): HOST arrays, copied.
@@ -301,8 +304,8 @@ int pbe_transport_explicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stri
  * (lower = -w phi, upper = lower + phi, diag = -(sums), gaussConvectionScheme::fvmDiv); zero-gradient patches add
  * phi_b to the diagonal, fixed-value patches -phi_b psi_b to the source; fvMatrix::relax(factor) (diagonal dominance,
  * D / factor, source += (D - D0) psi0) when relaxation > 0.  One matrix serves all nfields fields for
- * PBE_DIV_UPWIND; the limited schemes take their per-field weights from the current field, as
- * limitedScheme::weights does.  OpenFOAM solves field after field with the solver fvSolution names (PBiCG + DILU or
+ * PBE_DIV_UPWIND; the limited schemes (PBE_DIV_VANLEER, PBE_DIV_LIMITEDLINEAR; they need pbe_mesh_set_geometry) take
+ * their per-field weights from the current field, as limitedScheme::weights does: one matrix per field, Jacobi only.  OpenFOAM solves field after field with the solver fvSolution names (PBiCG + DILU or
  * smoothSolver symGaussSeidel in the reference's cases -- sequential sweeps); here ALL fields are solved together by
  * Jacobi sweeps or a diagonally preconditioned BiCGStab whose vector updates and matrix-vector products run over
  * [nfields][ncells] at once, each field with its own scalars, stopped by OpenFOAM's own criterion: normalised residual
@@ -438,7 +441,7 @@ int pbe_moc_state_device(pbe_moc_state *st, double **n_dev, int64_t *stride, dou
 int pbe_moc_state_attach_mesh(pbe_moc_state *st, pbe_mesh *mesh, int scheme);
 /* usingMULES false -- the reference's default (MOC.C:58, 177-180; QMOM.C:71, 112-115): correct_resident then runs
  * solveWithFVM (pbe_transport_implicit with these controls) instead of solveWithMULES.  controls NULL switches back.
- * Needs an attached mesh with PBE_DIV_UPWIND.  solver_performance: what OpenFOAM prints per field for the LAST step,
+ * Needs an attached mesh (its scheme is then the implicit term's).  solver_performance: what OpenFOAM prints per field for the LAST step,
  * HOST perf [N] ([2 * order] for QMOM). */
 int pbe_moc_state_set_implicit(pbe_moc_state *st, const pbe_fvm_controls *controls);
 int pbe_moc_state_solver_performance(pbe_moc_state *st, pbe_fvm_perf *perf);

@@ -56,6 +56,8 @@ struct ImpParams {
     double *x, *r, *r0, *p, *v, *t;
     FieldSc *sc;
     double *partial; // [nfields][kNS][G]
+    const double *wface; // limited schemes: limitedScheme::weights of every internal face, [nfields][nint]
+    double *dinvK;       // limited schemes: the fields' own inverse diagonals, [nfields][nc]
     double rdt, relax, tol, rel_tol;
     int min_iter, max_iter;
 };
@@ -410,6 +412,137 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
     }
 }
 
+// ---- limited schemes in the implicit term (Gauss vanLeer, Gauss limitedLinear 1) ------------------------------------
+// The weights come from the CURRENT field (limitedScheme::weights(vf) inside gaussConvectionScheme::fvmDiv), so every
+// field has its own matrix: lower = -w phi, upper = lower + phi with w = wface[k][f].  Nothing but the inverse diagonal
+// is stored per field; a sweep rebuilds a cell's coefficients from phi (registers) and the field's face weights.
+template <int W>
+struct LimRow {
+    int32_t col[W], fidx[W];
+    double ph[W], addc[W]; // coefficient of slot s = addc - w ph: owner side (1 - w) phi, neighbour side -w phi
+};
+
+template <int W>
+__device__ __forceinline__ void load_lim_row(const ImpParams &q, int64_t c, LimRow<W> &R) {
+#pragma unroll
+    for (int s = 0; s < W; ++s) {
+        const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c), fc = __ldg(q.face + (size_t)s * q.nc + c);
+        R.col[s] = (int32_t)c, R.fidx[s] = 0, R.ph[s] = 0.0, R.addc[s] = 0.0;
+        if (oth >= 0) {
+            const bool own = fc >= 0;
+            const int32_t f = own ? fc : ~fc;
+            const double ph = __ldg(q.phi + f);
+            R.col[s] = oth, R.fidx[s] = f, R.ph[s] = ph, R.addc[s] = own ? ph : 0.0;
+        }
+    }
+}
+
+// per field: the diagonal (negSumDiag, patches, relax()), b, r0 = b - A x0, z0 = r0 / D; sums: normFactor, |r0|_1
+template <int W>
+__global__ void __launch_bounds__(kBlock) imp_lim_init_kernel(const ImpParams q) {
+    const int64_t c0 = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    const bool valid = c0 < q.nc;
+    const int64_t c = valid ? c0 : q.nc - 1;
+    LimRow<W> R;
+    load_lim_row<W>(q, c, R);
+    const double V = __ldg(q.V + c);
+    // zero-gradient patch faces: internalCoeffs = phi_b (the same for every field)
+    double ic = 0.0, icmag = 0.0;
+    for (int s = 0; s < q.W; ++s) {
+        const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c);
+        if (oth <= -2 && q.psi_b == nullptr) {
+            const double phb = __ldg(q.phi + q.nint + (-(int64_t)oth - 2));
+            ic += phb;
+            icmag += fabs(phb);
+        }
+    }
+    const int kend = min(q.nfields, (int)(blockIdx.y + 1) * q.chunk);
+    for (int k = blockIdx.y * q.chunk; k < kend; ++k) {
+        const double *x = q.psi + (size_t)k * q.stride;
+        const double *wk = q.wface + (size_t)k * q.nint;
+        const double mine = x[c];
+        double D0 = q.rdt * V, sumOff = 0.0, offsum = 0.0, offx = 0.0;
+#pragma unroll
+        for (int s = 0; s < W; ++s) {
+            const double w = __ldg(wk + R.fidx[s]);
+            const double cf = fma(-w, R.ph[s], R.addc[s]);
+            D0 += fma(w, R.ph[s], R.addc[s] - R.ph[s]); // -lower on the owner side, -upper on the neighbour side
+            sumOff += fabs(cf);
+            offsum += cf;
+            offx = fma(cf, __ldg(x + R.col[s]), offx);
+        }
+        double b = q.rdt * mine * V;
+        if (q.S) b += __ldg(q.S + (size_t)k * q.stride + c) * V;
+        if (q.relax > 0.0) { // fvMatrix::relax(alpha)
+            const double Dfin = fmax(fabs(D0 + icmag), sumOff) / q.relax - ic;
+            b += (Dfin - D0) * mine;
+            D0 = Dfin;
+        }
+        const double diag = D0 + ic;
+        if (q.psi_b) {
+            for (int s = 0; s < q.W; ++s) {
+                const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c);
+                if (oth <= -2) {
+                    const int64_t bf = -(int64_t)oth - 2;
+                    b -= __ldg(q.phi + q.nint + bf) * __ldg(q.psi_b + (size_t)k * q.stride_b + bf);
+                }
+            }
+        }
+        const double Ax = fma(diag, mine, offx);
+        const double res = b - Ax, dinv = 1.0 / diag;
+        if (valid) {
+            const size_t o = (size_t)k * q.nc + c;
+            q.x[(size_t)k * q.stride + c] = mine;
+            q.dinvK[o] = dinv;
+            q.p[o] = dinv * res;
+        }
+        const double pA = __ldg(&q.sc[k].xbar) * (diag + offsum);
+        double sm[3] = {valid ? fabs(Ax - pA) + fabs(b - pA) : 0.0, valid ? fabs(res) : 0.0, valid ? res * res : 0.0};
+        block_sums<3>(q, k, sm);
+    }
+}
+
+template <int W>
+__global__ void __launch_bounds__(kBlock) imp_lim_jacobi_kernel(const ImpParams q) {
+    __shared__ double wsum[kMaxChunk][kBlock / 32];
+    const int k0 = blockIdx.y * q.chunk, kend = min(q.nfields, k0 + q.chunk);
+    auto next_active = [&](int k) {
+        while (k < kend && q.sc[k].state != 0) ++k;
+        return k;
+    };
+    int k = next_active(k0);
+    if (k >= kend) return;
+    const int64_t c0 = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    const bool valid = c0 < q.nc;
+    const int64_t c = valid ? c0 : q.nc - 1;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    LimRow<W> R;
+    load_lim_row<W>(q, c, R);
+    for (; k < kend; k = next_active(k + 1)) {
+        const size_t o = (size_t)k * q.nc;
+        const double *zin = q.p + o;
+        const double *wk = q.wface + (size_t)k * q.nint;
+        double acc = 0.0;
+#pragma unroll
+        for (int s = 0; s < W; ++s) acc = fma(fma(-__ldg(wk + R.fidx[s]), R.ph[s], R.addc[s]), __ldg(zin + R.col[s]), acc);
+        const double rz = -acc;
+        if (valid) {
+            q.x[(size_t)k * q.stride + c] += zin[c];
+            q.v[o + c] = __ldg(q.dinvK + o + c) * rz;
+        }
+        const double sum = warp_sum(valid ? fabs(rz) : 0.0);
+        if (lane == 0) wsum[k - k0][wid] = sum;
+    }
+    __syncthreads();
+    const int kt = k0 + threadIdx.x;
+    if (kt < kend && q.sc[kt].state == 0) {
+        double sum = 0.0;
+#pragma unroll
+        for (int i = 0; i < kBlock / 32; ++i) sum += wsum[threadIdx.x][i];
+        q.partial[(size_t)kt * kNS * q.G + blockIdx.x] = sum;
+    }
+}
+
 // One CTA per field: the CTAs' partial sums added in a fixed order, then the field's scalars.
 __global__ void __launch_bounds__(kBlock) imp_finalize_kernel(const ImpParams q, int phase, int G) {
     const int k = blockIdx.x;
@@ -524,8 +657,8 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     PBE_REQUIRE(psi_b == nullptr || stride_b >= m->nbnd, PBE_E_INVALID, "pbe_transport_implicit: stride_b %lld < boundary faces %lld",
                 (long long)stride_b, (long long)m->nbnd);
     PBE_REQUIRE(dt > 0.0, PBE_E_INVALID, "pbe_transport_implicit: dt must be positive");
-    PBE_REQUIRE(scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
-                "pbe_transport_implicit: only `Gauss upwind` has an implicit device path (scheme %d asked)", scheme);
+    PBE_REQUIRE(scheme == PBE_DIV_UPWIND || scheme == PBE_DIV_VANLEER || scheme == PBE_DIV_LIMITEDLINEAR, PBE_E_UNKNOWN_TYPE,
+                "pbe_transport_implicit: unknown divergence scheme id %d", scheme);
     PBE_REQUIRE(m->ncoupled == 0, PBE_E_UNSUPPORTED, "pbe_transport_implicit: processor patches are not supported");
     pbe_fvm_controls ctl = {1.0e-5, 0.0, 1, 1000, 0.0, PBE_FVM_SOLVER_AUTO};
     if (controls) ctl = *controls;
@@ -539,8 +672,27 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     if (rc != PBE_OK) return rc;
     const int64_t nc = m->ncells;
     const int Gs = (int)((nc + kBlock - 1) / kBlock), Gp = (int)((nc + (int64_t)kBlock * kPW - 1) / ((int64_t)kBlock * kPW));
-    // workspace: 5 vectors + 4 per-cell rows
-    const size_t need = (size_t)5 * nfields * nc + (size_t)4 * nc;
+    // Which solver.  Upwind convection makes the matrix triangular along the flow: ANY iteration needs about as many
+    // matrix-vector products as the solution travels cells in dt, Jacobi at 4 vector passes per product, BiCGStab at
+    // ~9.5.  Measured, 160^3 x 100 fields to 1e-5: Courant 0.4 40 / 69 ms, 4 196 / 326 ms, 40 1 304 / 2 535 ms,
+    // 150 1 984 / 5 238 ms (Jacobi / BiCGStab): AUTO is Jacobi.
+    const int solver = ctl.solver == PBE_FVM_SOLVER_AUTO ? PBE_FVM_SOLVER_JACOBI : ctl.solver;
+    const bool jac = solver == PBE_FVM_SOLVER_JACOBI;
+    // a limited scheme: one matrix per field (weights from the field itself); without internal faces there is no
+    // convection coefficient to weight
+    const bool lim = scheme != PBE_DIV_UPWIND && m->nint > 0;
+    PBE_REQUIRE(!lim || jac, PBE_E_UNSUPPORTED,
+                "pbe_transport_implicit: the limited schemes are solved by the Jacobi iteration only (solver %d asked)", solver);
+    PBE_REQUIRE(!lim || m->imp_W <= 8, PBE_E_UNSUPPORTED,
+                "pbe_transport_implicit: limited schemes on cells with more than 8 faces (%d) are not built", m->imp_W);
+    PBE_REQUIRE(!lim || (m->d_Sf && m->d_C && m->d_w), PBE_E_INVALID,
+                "pbe_transport_implicit: a limited scheme needs the mesh geometry (pbe_mesh_set_geometry)");
+    // workspace: Jacobi z, z' (+ the fields' inverse diagonals, face weights and a gradient scratch for a limited
+    // scheme); BiCGStab r, r0, p, v, t; 4 per-cell rows
+    const int KCg = lim ? (int)std::max<size_t>(1, std::min<size_t>((size_t)nfields, ((size_t)1 << 30) / ((size_t)3 * nc * 8) + 1)) : 0;
+    const size_t nvec = jac ? (lim ? 3 : 2) : 5;
+    const size_t need = nvec * nfields * nc + (size_t)4 * nc +
+                        (lim ? (size_t)nfields * m->nint + (size_t)KCg * 3 * nc : 0);
     if (m->imp_ws_doubles < need) {
         PBE_CUDA(cudaStreamSynchronize(st));
         cudaFree(m->imp_ws);
@@ -579,9 +731,20 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     q.other = m->d_imp_other, q.face = m->d_imp_face;
     q.phi = phi, q.V = m->d_vcell;
     double *w = m->imp_ws;
-    q.r = w, q.r0 = w + (size_t)nfields * nc, q.p = w + (size_t)2 * nfields * nc, q.v = w + (size_t)3 * nfields * nc,
-    q.t = w + (size_t)4 * nfields * nc;
-    double *rows = w + (size_t)5 * nfields * nc;
+    const size_t vec = (size_t)nfields * nc;
+    double *grad_ws = nullptr, *wface = nullptr;
+    if (jac) {
+        q.p = w, q.v = w + vec;
+        if (lim) q.dinvK = w + 2 * vec;
+    } else {
+        q.r = w, q.r0 = w + vec, q.p = w + 2 * vec, q.v = w + 3 * vec, q.t = w + 4 * vec;
+    }
+    double *rows = w + nvec * vec;
+    if (lim) {
+        wface = rows + 4 * nc;
+        grad_ws = wface + (size_t)nfields * m->nint;
+        q.wface = wface;
+    }
     q.diag = rows, q.dinv = rows + nc, q.a1 = rows + 2 * nc, q.drel = rows + 3 * nc;
     q.psi = psi, q.psi_b = psi_b, q.S = S, q.x = psi_out;
     q.sc = (FieldSc *)m->imp_small;
@@ -618,16 +781,16 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         return PBE_OK;
     };
 
-    imp_diag_kernel<<<Gs, kBlock, 0, st>>>(q);
+    if (lim) {
+        rc = limited_weights(m, scheme, nfields, stride, psi, phi, psi_b, stride_b, wface, grad_ws, KCg, st, &launches);
+        if (rc != PBE_OK) return rc;
+    } else {
+        imp_diag_kernel<<<Gs, kBlock, 0, st>>>(q);
+        ++launches;
+    }
     imp_xsum_kernel<<<grid_p, kBlock, 0, st>>>(q);
-    launches += 2;
+    ++launches;
     finalize(PH_XSUM, Gp);
-    // Which solver.  Upwind convection makes the matrix triangular along the flow: ANY iteration needs about as many
-    // matrix-vector products as the solution travels cells in dt, Jacobi at 4 vector passes per product, BiCGStab at
-    // ~9.5.  Measured, 160^3 x 100 fields to 1e-5: Courant 0.4 40 / 69 ms, 4 196 / 326 ms, 40 1 304 / 2 535 ms,
-    // 150 1 984 / 5 238 ms (Jacobi / BiCGStab): AUTO is Jacobi.
-    const int solver = ctl.solver == PBE_FVM_SOLVER_AUTO ? PBE_FVM_SOLVER_JACOBI : ctl.solver;
-    const bool jac = solver == PBE_FVM_SOLVER_JACOBI;
 #define PBE_IMP_W(KERNEL, ...)                                               \
     switch (W) {                                                             \
     case 4: KERNEL<4 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;      \
@@ -635,8 +798,16 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     case 8: KERNEL<8 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;      \
     default: KERNEL<0 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;     \
     }
+#define PBE_IMP_WL(KERNEL)                                                   \
+    switch (W) {                                                             \
+    case 4: KERNEL<4><<<grid_s, kBlock, 0, st>>>(q); break;                  \
+    case 6: KERNEL<6><<<grid_s, kBlock, 0, st>>>(q); break;                  \
+    default: KERNEL<8><<<grid_s, kBlock, 0, st>>>(q); break;                 \
+    }
 #define PBE_IMP_COMMA ,
-    if (jac) {
+    if (lim) {
+        PBE_IMP_WL(imp_lim_init_kernel)
+    } else if (jac) {
         PBE_IMP_W(imp_init_kernel, PBE_IMP_COMMA true)
     } else {
         PBE_IMP_W(imp_init_kernel, PBE_IMP_COMMA false)
@@ -650,7 +821,11 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         // device never waits for the host.  Converged fields are frozen on the device (their state is not 0), hence the
         // one iteration queued past the end changes nothing.
         auto issue = [&](int slot) -> int {
-            PBE_IMP_W(imp_jacobi_kernel)
+            if (lim) {
+                PBE_IMP_WL(imp_lim_jacobi_kernel)
+            } else {
+                PBE_IMP_W(imp_jacobi_kernel)
+            }
             ++launches;
             finalize(PH_J, Gs);
             std::swap(q.p, q.v);
@@ -690,6 +865,7 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     }
 #undef PBE_IMP_W
 #undef PBE_IMP_COMMA
+#undef PBE_IMP_WL
     m->ctx->launches += launches;
     if (rc != PBE_OK) return rc;
     PBE_CUDA(cudaGetLastError());

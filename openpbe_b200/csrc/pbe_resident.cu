@@ -604,8 +604,6 @@ int pbe_moc_state_set_implicit(pbe_moc_state *s, const pbe_fvm_controls *control
     PBE_REQUIRE(s != nullptr, PBE_E_INVALID, "pbe_moc_state_set_implicit: NULL state");
     PBE_REQUIRE(controls == nullptr || s->mesh != nullptr, PBE_E_INVALID,
                 "pbe_moc_state_set_implicit: attach a mesh first (pbe_moc_state_attach_mesh)");
-    PBE_REQUIRE(controls == nullptr || s->scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
-                "pbe_moc_state_set_implicit: only `Gauss upwind` has an implicit device path");
     s->implicit = controls != nullptr;
     if (controls) s->fvm = *controls;
     s->perf.clear();
@@ -936,8 +934,6 @@ int pbe_qmom_state_set_implicit(pbe_qmom_state *s, const pbe_fvm_controls *contr
     PBE_REQUIRE(s != nullptr, PBE_E_INVALID, "pbe_qmom_state_set_implicit: NULL state");
     PBE_REQUIRE(controls == nullptr || s->mesh != nullptr, PBE_E_INVALID,
                 "pbe_qmom_state_set_implicit: attach a mesh first (pbe_qmom_state_attach_mesh)");
-    PBE_REQUIRE(controls == nullptr || s->scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
-                "pbe_qmom_state_set_implicit: only `Gauss upwind` has an implicit device path");
     s->implicit = controls != nullptr;
     if (controls) s->fvm = *controls;
     s->perf.clear();

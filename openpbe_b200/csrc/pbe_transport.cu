@@ -430,8 +430,13 @@ int pbe_div_scheme_type(const char *name, int *out) {
         *out = PBE_DIV_VANLEER;
         return PBE_OK;
     }
+    if (!strcmp(name, "limitedLinear 1") || !strcmp(name, "Gauss limitedLinear 1") || !strcmp(name, "limitedLinear 1.0") ||
+        !strcmp(name, "Gauss limitedLinear 1.0")) {
+        *out = PBE_DIV_LIMITEDLINEAR; // implicit convection term only
+        return PBE_OK;
+    }
     set_error("Unknown or not yet supported divergence scheme \"%s\" for the device transport\n\n"
-              "Valid schemes are :\n2\n(\nupwind\nvanLeer\n)",
+              "Valid schemes are :\n3\n(\nupwind\nvanLeer\nlimitedLinear 1\n)",
               name);
     return PBE_E_UNKNOWN_TYPE;
 }

@@ -28,7 +28,42 @@ import scipy.sparse as sp
 import scipy.sparse.linalg as spla
 
 
-def assemble(mesh: dict, phi, dt, psi0, *, S=None, psi_b=None, relaxation=0.0):
+def limited_weights(mesh: dict, scheme: str, phi, psi, psi_b=None):
+    """limitedScheme::weights(vf) on the internal faces: limiter CDweights + (1 - limiter) pos(faceFlux), with
+    gaussGrad (linear) gradients, NVDTVD::r and the limiter of `Gauss vanLeer` ((r + |r|) / (1 + |r|)) or
+    `Gauss limitedLinear 1` (max(min(2 r, 1), 0)).  mesh needs Sf, C, weights."""
+    own = np.asarray(mesh["owner"], dtype=np.int64)
+    nei = np.asarray(mesh["neighbour"], dtype=np.int64)
+    bown = np.asarray(mesh["boundary_owner"], dtype=np.int64)
+    V, Sf, C, wl = (np.asarray(mesh[k], dtype=np.float64) for k in ("vcell", "Sf", "C", "weights"))
+    ni = own.size
+    phi = np.asarray(phi, dtype=np.float64)
+    P, N = psi[own], psi[nei]
+    ssf = wl * (P - N) + N  # linear face values
+    grad = np.zeros((V.size, 3))
+    np.add.at(grad, own, Sf[:ni] * ssf[:, None])
+    np.subtract.at(grad, nei, Sf[:ni] * ssf[:, None])
+    pv = psi[bown] if psi_b is None else np.asarray(psi_b, dtype=np.float64)
+    np.add.at(grad, bown, Sf[ni:] * pv[:, None])
+    grad /= V[:, None]
+    d = C[nei] - C[own]
+    up = np.where(phi[:ni] > 0, own, nei)
+    gradcf = np.einsum("ij,ij->i", d, grad[up])
+    gradf = N - P
+    sgn = lambda a: np.where(a >= 0, 1.0, -1.0)
+    big = np.abs(gradcf) >= 1000 * np.abs(gradf)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        r = np.where(big, 2 * 1000 * sgn(gradcf) * sgn(gradf) - 1, 2 * (gradcf / np.where(big, 1.0, gradf)) - 1)
+    if scheme in ("Gauss vanLeer", "vanLeer"):
+        lim = (r + np.abs(r)) / (1 + np.abs(r))
+    elif scheme in ("Gauss limitedLinear 1", "limitedLinear 1"):
+        lim = np.maximum(np.minimum(2.0 * r, 1.0), 0.0)
+    else:
+        raise ValueError(scheme)
+    return lim * wl + (1.0 - lim) * (phi[:ni] >= 0)
+
+
+def assemble(mesh: dict, phi, dt, psi0, *, S=None, psi_b=None, relaxation=0.0, scheme="Gauss upwind"):
     """(A [csr], b) of one field.  mesh: owner, neighbour, boundary_owner, vcell (as tests/meshes.py builds them);
     phi [internal + boundary faces]; psi_b [boundary faces] fixed patch values or None = zero-gradient patches."""
     own = np.asarray(mesh["owner"], dtype=np.int64)
@@ -42,7 +77,10 @@ def assemble(mesh: dict, phi, dt, psi0, *, S=None, psi_b=None, relaxation=0.0):
     b = rdt * psi0 * V
     if S is not None:
         b = b + S * V
-    w = (phi[:ni] >= 0).astype(np.float64)  # upwind: pos(faceFlux)
+    if scheme in ("Gauss upwind", "upwind") or ni == 0:
+        w = (phi[:ni] >= 0).astype(np.float64)  # upwind: pos(faceFlux)
+    else:
+        w = limited_weights(mesh, scheme, phi, np.asarray(psi0, dtype=np.float64), psi_b)
     lower = -w * phi[:ni]
     upper = lower + phi[:ni]
     diag = diag.copy()
@@ -82,12 +120,12 @@ def residual(A, b, x, x0=None):
     return np.abs(b - A @ x).sum() / norm_factor(A, b, x if x0 is None else x0)
 
 
-def solve(mesh: dict, phi, dt, psi, *, S=None, psi_b=None, relaxation=0.0):
+def solve(mesh: dict, phi, dt, psi, *, S=None, psi_b=None, relaxation=0.0, scheme="Gauss upwind"):
     """All fields psi [K][ncells] -> the matrices' exact solutions [K][ncells]."""
     psi = np.asarray(psi, dtype=np.float64)
     out = np.empty_like(psi)
     for k in range(psi.shape[0]):
         A, b = assemble(mesh, phi, dt, psi[k], S=None if S is None else S[k], psi_b=None if psi_b is None else psi_b[k],
-                        relaxation=relaxation)
+                        relaxation=relaxation, scheme=scheme)
         out[k] = spla.spsolve(A.tocsc(), b)
     return out

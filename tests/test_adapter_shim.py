@@ -224,11 +224,21 @@ def test_moc_correct_default_branch_is_the_implicit_solve(shim, tmp_path, oracle
         n_o = fvm.solve(tm, tm["phi"], dt, n_o, S=S)
     assert np.all(np.abs(n - n_o) <= 1e-9 * np.abs(n_o).max(axis=1, keepdims=True))
     np.testing.assert_allclose(d, oracle.moc_d(n_o, w.xi1), rtol=1e-9)
-    # a limited scheme in the implicit term has no device path: FatalError, not a silent change of scheme
-    (tmp_path / "dict").write_text(text.replace("minIter 1;", "minIter 1; implicitDivScheme Gauss vanLeer;"))
+    # the scheme of the reference's MOC cases for the implicit term (tests/integration/MOC/template/system/fvSchemes:44)
+    (tmp_path / "dict").write_text(text.replace("minIter 1;", "minIter 1; implicitDivScheme Gauss limitedLinear 1;"))
+    _write_mesh(tmp_path / "mesh.bin", tm, geometry=True)
     p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
                         str(tmp_path / "mesh.bin")], capture_output=True, text=True)
-    assert p.returncode == 1 and "Gauss upwind only" in p.stdout and "FOAM exiting" in p.stdout
+    assert p.returncode == 0, p.stdout + p.stderr
+    n1 = np.fromfile(tmp_path / "out.bin")[:K * nc].reshape(K, nc)
+    S, _ = oracle.moc_source(sp, w.N, w.xi1, w.relax, f["n"], f["eps"], f["rho"], f["nu"], dt)
+    want = fvm.solve(tm, tm["phi"], dt, f["n"], S=S, scheme="Gauss limitedLinear 1")
+    assert np.all(np.abs(n1 - want) <= 1e-9 * np.abs(want).max(axis=1, keepdims=True))
+    # a scheme without a device path: FatalError that lists the valid ones, not a silent change of scheme
+    (tmp_path / "dict").write_text(text.replace("minIter 1;", "minIter 1; implicitDivScheme Gauss QUICK;"))
+    p = subprocess.run([shim, str(tmp_path / "dict"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "1",
+                        str(tmp_path / "mesh.bin")], capture_output=True, text=True)
+    assert p.returncode == 1 and "QUICK" in p.stdout and "Valid schemes are" in p.stdout and "FOAM exiting" in p.stdout
 
 
 @pytest.mark.gpu

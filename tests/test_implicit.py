@@ -94,6 +94,39 @@ def test_residual_normalisation_is_openfoams():
     assert 1e-4 < r0 < 1.0  # the old field is no solution, and the factor makes it O(1) at most
 
 
+def test_limited_weights_are_the_mules_restatements(oracle):
+    """The NumPy weights of the implicit term against the C restatement the MULES path is checked with: the vanLeer
+    face flux phi (w (P - N) + N) must be what orc_div_flux gives; limitedLinear 1 stays between upwind and linear."""
+    rng = np.random.default_rng(5)
+    m = synthetic.block_mesh(9, 7, 5, velocity=(1.0, -0.5, 0.25))
+    ni = m["owner"].size
+    psi = fields(rng, 1, 9 * 7 * 5)[0]
+    w = fvm.limited_weights(m, "Gauss vanLeer", m["phi"], psi)
+    P, N = psi[m["owner"]], psi[m["neighbour"]]
+    flux = oracle.div_flux(m, "Gauss vanLeer", m["phi"], psi)
+    assert np.allclose(m["phi"][:ni] * (w * (P - N) + N), flux[:ni], rtol=1e-13, atol=1e-15)
+    wl = fvm.limited_weights(m, "Gauss limitedLinear 1", m["phi"], psi)
+    up = (m["phi"][:ni] >= 0).astype(float)
+    lo, hi = np.minimum(up, m["weights"]), np.maximum(up, m["weights"])
+    assert np.all(wl >= lo - 1e-15) and np.all(wl <= hi + 1e-15)
+    assert np.any(wl == up) and np.any(np.abs(wl - m["weights"]) < 1e-15)  # both branches of the limiter occur
+
+
+@pytest.mark.parametrize("scheme", ["Gauss vanLeer", "Gauss limitedLinear 1"])
+def test_limited_implicit_is_less_diffusive_and_conserves(scheme):
+    rng = np.random.default_rng(6)
+    m = synthetic.block_mesh(40, 1, 1, velocity=(1.0, 0.0, 0.0))
+    x = (np.arange(40) + 0.5) / 40
+    psi = np.exp(-((x - 0.3) / 0.08) ** 2)[None, :]
+    dt = 0.2 / 40
+    a, b = psi, psi
+    for _ in range(20):
+        a = fvm.solve(m, m["phi"], dt, a)
+        b = fvm.solve(m, m["phi"], dt, b, scheme=scheme)
+    assert b.max() > a.max() * 1.05  # the peak survives better
+    assert np.allclose((a * m["vcell"]).sum(), (b * m["vcell"]).sum(), rtol=1e-6)  # nothing has reached the outlet yet
+
+
 @needs_ref
 @pytest.mark.parametrize("method", ["moc", "qmom"])
 def test_reference_solve_with_fvm_lands_on_the_direct_solution(oracle, method):
@@ -204,6 +237,39 @@ def test_device_implicit_random_topology_and_patches(ctx, nint, nbnd, fixed):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("scheme", ["Gauss vanLeer", "Gauss limitedLinear 1"])
+@pytest.mark.parametrize("shape,vel", [((12, 9, 7), (1.0, -0.5, 0.25)), ((40, 1, 1), (1.0, 0.0, 0.0)), ((30, 24, 12), (0.7, 0.4, -0.9))])
+def test_device_implicit_limited_schemes(ctx, scheme, shape, vel):
+    """one matrix per field: the weights of the implicit term come from the field itself (limitedScheme::weights)"""
+    from openpbe_b200 import engine
+    rng = np.random.default_rng(15)
+    m = synthetic.block_mesh(*shape, velocity=vel)
+    nc = shape[0] * shape[1] * shape[2]
+    K = 4
+    psi = fields(rng, K, nc)
+    S = rng.normal(size=psi.shape) * 0.1
+    dt = 0.3 / sum(abs(v) * n for v, n in zip(vel, shape))
+    for pb in (None, rng.uniform(0.1, 2.0, size=(K, m["boundary_owner"].size))):
+        want = fvm.solve(m, m["phi"], dt, psi, S=S, psi_b=pb, scheme=scheme)
+        assert np.abs(want - fvm.solve(m, m["phi"], dt, psi, S=S, psi_b=pb)).max() > 1e-4  # not the upwind answer
+        mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+        with pytest.raises(engine.capi.PbeError, match="geometry"):
+            mesh.transport_implicit(T(psi), T(m["phi"]), dt, scheme=scheme)
+        mesh.set_geometry(m["Sf"], m["C"], m["weights"])
+        got, perf = mesh.transport_implicit(T(psi), T(m["phi"]), dt, S=T(S), psi_b=None if pb is None else T(pb),
+                                            scheme=scheme, tolerance=1e-13)
+        got = got.cpu().numpy()
+        assert all(p[3] == 1 for p in perf)
+        assert np.all(np.abs(got - want).sum(axis=1) <= 1e-10 * np.abs(want).sum(axis=1))
+        for k in range(K):
+            A, b = fvm.assemble(m, m["phi"], dt, psi[k], S=S[k], psi_b=None if pb is None else pb[k], scheme=scheme)
+            assert perf[k][0] == pytest.approx(fvm.residual(A, b, psi[k]), rel=1e-9)
+        with pytest.raises(engine.capi.PbeError, match="Jacobi iteration only"):
+            mesh.transport_implicit(T(psi), T(m["phi"]), dt, scheme=scheme, solver="bicgstab")
+        mesh.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("relaxation", [1.0, 0.7])
 def test_device_implicit_relaxation(ctx, relaxation):
     rng = np.random.default_rng(12)
@@ -272,7 +338,7 @@ def test_device_implicit_argument_errors(ctx):
     m = synthetic.block_mesh(4, 3, 2)
     mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
     psi = T(np.ones((2, 24)))
-    with pytest.raises(capi.PbeError, match="Gauss upwind"):
+    with pytest.raises(capi.PbeError, match="geometry"):
         mesh.transport_implicit(psi, T(m["phi"]), 0.1, scheme="vanLeer")
     with pytest.raises(capi.PbeError, match="alias"):
         mesh.transport_implicit(psi, T(m["phi"]), 0.1, out=psi)
@@ -346,8 +412,11 @@ def test_resident_qmom_correct_with_the_implicit_solve(ctx, oracle):
     assert np.all(np.abs(m_g - want) <= 1e-10 * np.abs(want).max(axis=1, keepdims=True))
     assert np.allclose(d.numpy(), np.cbrt(6.0 / np.pi * m_g[1] / m_g[0]), rtol=1e-13)
     assert all(p[3] == 1 for p in st.solver_performance())
-    # a limited scheme has no implicit device path: said at set-up, not at the first step
+    # the same step with a limited scheme in the implicit term
+    mesh.set_geometry(tm["Sf"], tm["C"], tm["weights"])
     st2 = engine.QMOMState(q, nc, vcell=tm["vcell"], m0=f["m"], mesh=mesh, scheme="Gauss vanLeer")
-    with pytest.raises(engine.capi.PbeError, match="Gauss upwind"):
-        st2.set_implicit()
+    st2.set_implicit(tolerance=1e-13)
+    st2.correct(f["eps"], f["rho"], f["nu"], dt, phi=tm["phi"])
+    want = np.maximum(fvm.solve(tm, tm["phi"], dt, f["m"], S=S_dev, scheme="Gauss vanLeer"), 1e-15)
+    assert np.all(np.abs(st2.download().numpy() - want) <= 1e-10 * np.abs(want).max(axis=1, keepdims=True))
     st2.close(); st.close(); mesh.close(); q.close()
