@@ -58,6 +58,7 @@ struct ImpParams {
     double *partial; // [nfields][kNS][G]
     const double *wface; // limited schemes: limitedScheme::weights of every internal face, [nfields][nint]
     double *dinvK;       // limited schemes: the fields' own inverse diagonals, [nfields][nc]
+    unsigned long long *est; // limited schemes: bits of max over fields and cells of sum|off-diagonal| / diagonal
     double rdt, relax, tol, rel_tol;
     int min_iter, max_iter;
 };
@@ -303,7 +304,7 @@ __global__ void __launch_bounds__(kBlock) imp_update_kernel(const ImpParams q) {
     for (int j = 0; j < kPW; ++j) {
         const int64_t i = ((int64_t)blockIdx.x * kPW + j) * kBlock + threadIdx.x;
         if (i < q.nc) {
-            const double di = __ldg(q.dinv + i), sv = q.r[o + i];
+            const double di = q.dinvK ? __ldg(q.dinvK + o + i) : __ldg(q.dinv + i), sv = q.r[o + i];
             x[i] += di * fma(alpha, q.p[o + i], omega * sv);
             const double rn = omega != 0.0 ? fma(-omega, q.t[o + i], sv) : sv;
             q.r[o + i] = rn;
@@ -438,7 +439,7 @@ __device__ __forceinline__ void load_lim_row(const ImpParams &q, int64_t c, LimR
 }
 
 // per field: the diagonal (negSumDiag, patches, relax()), b, r0 = b - A x0, z0 = r0 / D; sums: normFactor, |r0|_1
-template <int W>
+template <int W, bool JAC>
 __global__ void __launch_bounds__(kBlock) imp_lim_init_kernel(const ImpParams q) {
     const int64_t c0 = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     const bool valid = c0 < q.nc;
@@ -494,11 +495,85 @@ __global__ void __launch_bounds__(kBlock) imp_lim_init_kernel(const ImpParams q)
             const size_t o = (size_t)k * q.nc + c;
             q.x[(size_t)k * q.stride + c] = mine;
             q.dinvK[o] = dinv;
-            q.p[o] = dinv * res;
+            if (JAC) {
+                q.p[o] = dinv * res;
+            } else {
+                q.r[o] = res;
+                q.r0[o] = res;
+                q.p[o] = res;
+            }
         }
         const double pA = __ldg(&q.sc[k].xbar) * (diag + offsum);
         double sm[3] = {valid ? fabs(Ax - pA) + fabs(b - pA) : 0.0, valid ? fabs(res) : 0.0, valid ? res * res : 0.0};
         block_sums<3>(q, k, sm);
+    }
+}
+
+// How far from diagonally dominant the fields' matrices are: max over fields and cells of sum|off-diagonal| / diagonal
+// (< 1: Jacobi contracts).  Downwind weights put positive coefficients off the diagonal, so unlike the upwind matrix
+// these are M-matrices only while the cell Courant number is small.
+template <int W>
+__global__ void __launch_bounds__(kBlock) imp_lim_est_kernel(const ImpParams q) {
+    const int64_t c0 = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    const bool valid = c0 < q.nc;
+    const int64_t c = valid ? c0 : q.nc - 1;
+    LimRow<W> R;
+    load_lim_row<W>(q, c, R);
+    const double V = __ldg(q.V + c);
+    double ic = 0.0;
+    for (int s = 0; s < q.W; ++s) {
+        const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c);
+        if (oth <= -2 && q.psi_b == nullptr) ic += __ldg(q.phi + q.nint + (-(int64_t)oth - 2));
+    }
+    double worst = 0.0;
+    const int kend = min(q.nfields, (int)(blockIdx.y + 1) * q.chunk);
+    for (int k = blockIdx.y * q.chunk; k < kend; ++k) {
+        const double *wk = q.wface + (size_t)k * q.nint;
+        double D0 = q.rdt * V + ic, sumOff = 0.0;
+#pragma unroll
+        for (int s = 0; s < W; ++s) {
+            const double w = __ldg(wk + R.fidx[s]);
+            D0 += fma(w, R.ph[s], R.addc[s] - R.ph[s]);
+            sumOff += fabs(fma(-w, R.ph[s], R.addc[s]));
+        }
+        const double e = D0 > 0.0 ? sumOff / D0 : 1.0e30;
+        worst = fmax(worst, e);
+    }
+    if (!valid) worst = 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    if ((threadIdx.x & 31) == 0 && worst > 0.0) atomicMax(q.est, (unsigned long long)__double_as_longlong(worst));
+}
+
+// out = A_k M_k^-1 in for the fields' own matrices (BiCGStab on a limited scheme); modes as imp_spmv_kernel
+template <int W, int MODE>
+__global__ void __launch_bounds__(kBlock) imp_lim_spmv_kernel(const ImpParams q) {
+    const int64_t c0 = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    const bool valid = c0 < q.nc;
+    const int64_t c = valid ? c0 : q.nc - 1;
+    LimRow<W> R;
+    load_lim_row<W>(q, c, R);
+    const int kend = min(q.nfields, (int)(blockIdx.y + 1) * q.chunk);
+    for (int k = blockIdx.y * q.chunk; k < kend; ++k) {
+        const FieldSc *sc = q.sc + k;
+        if (sc->state != 0 || (MODE == 1 && sc->half)) continue;
+        const size_t o = (size_t)k * q.nc;
+        const double *in = (MODE == 0 ? q.p : q.r) + o;
+        const double *wk = q.wface + (size_t)k * q.nint, *di = q.dinvK + o;
+        const double mine = in[c];
+        double y = mine; // D (D^-1 in)
+#pragma unroll
+        for (int s = 0; s < W; ++s)
+            y = fma(fma(-__ldg(wk + R.fidx[s]), R.ph[s], R.addc[s]) * __ldg(di + R.col[s]), __ldg(in + R.col[s]), y);
+        if (MODE == 0) {
+            if (valid) q.v[o + c] = y;
+            double sm[1] = {valid ? __ldg(q.r0 + o + c) * y : 0.0};
+            block_sums<1>(q, k, sm);
+        } else {
+            if (valid) q.t[o + c] = y;
+            double sm[2] = {valid ? y * mine : 0.0, valid ? y * y : 0.0};
+            block_sums<2>(q, k, sm);
+        }
     }
 }
 
@@ -590,7 +665,7 @@ __global__ void __launch_bounds__(kBlock) imp_finalize_kernel(const ImpParams q,
         sc->iters += 1;
         if (conv(sc->res) && sc->iters >= q.min_iter) sc->state = 1;
         else if (sc->iters >= q.max_iter) sc->state = 3;
-        else if (!isfinite(s0)) sc->state = 2;
+        else if (!(sc->res <= 1.0e6 * fmax(sc->res0, 1.0e-30))) sc->state = 2; // diverging (or NaN): stop before it overflows
         break;
     case PH_D: {
         sc->res = s0 / sc->norm;
@@ -675,22 +750,22 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     // Which solver.  Upwind convection makes the matrix triangular along the flow: ANY iteration needs about as many
     // matrix-vector products as the solution travels cells in dt, Jacobi at 4 vector passes per product, BiCGStab at
     // ~9.5.  Measured, 160^3 x 100 fields to 1e-5: Courant 0.4 40 / 69 ms, 4 196 / 326 ms, 40 1 304 / 2 535 ms,
-    // 150 1 984 / 5 238 ms (Jacobi / BiCGStab): AUTO is Jacobi.
-    const int solver = ctl.solver == PBE_FVM_SOLVER_AUTO ? PBE_FVM_SOLVER_JACOBI : ctl.solver;
-    const bool jac = solver == PBE_FVM_SOLVER_JACOBI;
-    // a limited scheme: one matrix per field (weights from the field itself); without internal faces there is no
-    // convection coefficient to weight
+    // 150 1 984 / 5 238 ms (Jacobi / BiCGStab): for the upwind matrix AUTO is Jacobi.
+    // A limited scheme gives one matrix per field (weights from the field itself) that is diagonally dominant only at
+    // small Courant numbers: AUTO measures the dominance once the weights are known and takes Jacobi below 0.9,
+    // BiCGStab above (Jacobi diverges beyond 1).  Without internal faces there is no coefficient to weight.
     const bool lim = scheme != PBE_DIV_UPWIND && m->nint > 0;
-    PBE_REQUIRE(!lim || jac, PBE_E_UNSUPPORTED,
-                "pbe_transport_implicit: the limited schemes are solved by the Jacobi iteration only (solver %d asked)", solver);
+    int solver = ctl.solver;
+    if (!lim && solver == PBE_FVM_SOLVER_AUTO) solver = PBE_FVM_SOLVER_JACOBI;
+    const bool may_bicg = solver != PBE_FVM_SOLVER_JACOBI;
     PBE_REQUIRE(!lim || m->imp_W <= 8, PBE_E_UNSUPPORTED,
                 "pbe_transport_implicit: limited schemes on cells with more than 8 faces (%d) are not built", m->imp_W);
     PBE_REQUIRE(!lim || (m->d_Sf && m->d_C && m->d_w), PBE_E_INVALID,
                 "pbe_transport_implicit: a limited scheme needs the mesh geometry (pbe_mesh_set_geometry)");
-    // workspace: Jacobi z, z' (+ the fields' inverse diagonals, face weights and a gradient scratch for a limited
-    // scheme); BiCGStab r, r0, p, v, t; 4 per-cell rows
+    // workspace: Jacobi z, z'; BiCGStab r, r0, p, v, t; for a limited scheme the fields' inverse diagonals, the face
+    // weights and a gradient scratch; 4 per-cell rows
     const int KCg = lim ? (int)std::max<size_t>(1, std::min<size_t>((size_t)nfields, ((size_t)1 << 30) / ((size_t)3 * nc * 8) + 1)) : 0;
-    const size_t nvec = jac ? (lim ? 3 : 2) : 5;
+    const size_t nvec = (may_bicg ? 5 : 2) + (lim ? 1 : 0);
     const size_t need = nvec * nfields * nc + (size_t)4 * nc +
                         (lim ? (size_t)nfields * m->nint + (size_t)KCg * 3 * nc : 0);
     if (m->imp_ws_doubles < need) {
@@ -707,6 +782,7 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         m->imp_ws_doubles = need;
     }
     const size_t small = (size_t)nfields * sizeof(FieldSc) + (size_t)nfields * kNS * Gs * sizeof(double) + 16;
+    static_assert(sizeof(FieldSc) % 8 == 0, "the partial sums follow the per-field scalars");
     if (m->imp_small_bytes < small) {
         PBE_CUDA(cudaStreamSynchronize(st));
         cudaFree(m->imp_small);
@@ -733,12 +809,11 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     double *w = m->imp_ws;
     const size_t vec = (size_t)nfields * nc;
     double *grad_ws = nullptr, *wface = nullptr;
-    if (jac) {
-        q.p = w, q.v = w + vec;
-        if (lim) q.dinvK = w + 2 * vec;
-    } else {
+    if (may_bicg)
         q.r = w, q.r0 = w + vec, q.p = w + 2 * vec, q.v = w + 3 * vec, q.t = w + 4 * vec;
-    }
+    else
+        q.p = w, q.v = w + vec;
+    if (lim) q.dinvK = w + (nvec - 1) * vec;
     double *rows = w + nvec * vec;
     if (lim) {
         wface = rows + 4 * nc;
@@ -749,6 +824,7 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     q.psi = psi, q.psi_b = psi_b, q.S = S, q.x = psi_out;
     q.sc = (FieldSc *)m->imp_small;
     q.partial = (double *)((char *)m->imp_small + (size_t)nfields * sizeof(FieldSc));
+    q.est = (unsigned long long *)(q.partial + (size_t)nfields * kNS * Gs);
     q.rdt = 1.0 / dt, q.relax = ctl.relaxation, q.tol = ctl.tolerance, q.rel_tol = ctl.rel_tol;
     q.min_iter = ctl.min_iter, q.max_iter = ctl.max_iter;
     // fields per CTA of the row-holding kernels: enough CTAs to fill the machine, rows amortised over many fields
@@ -764,6 +840,15 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         ++launches;
     };
     auto spmv = [&](int mode) {
+        if (q.wface) {
+            switch (W) {
+            case 4: mode == 0 ? imp_lim_spmv_kernel<4, 0><<<grid_s, kBlock, 0, st>>>(q) : imp_lim_spmv_kernel<4, 1><<<grid_s, kBlock, 0, st>>>(q); break;
+            case 6: mode == 0 ? imp_lim_spmv_kernel<6, 0><<<grid_s, kBlock, 0, st>>>(q) : imp_lim_spmv_kernel<6, 1><<<grid_s, kBlock, 0, st>>>(q); break;
+            default: mode == 0 ? imp_lim_spmv_kernel<8, 0><<<grid_s, kBlock, 0, st>>>(q) : imp_lim_spmv_kernel<8, 1><<<grid_s, kBlock, 0, st>>>(q); break;
+            }
+            ++launches;
+            return;
+        }
         switch (W) {
         case 4: launch_spmv<4>(q, mode, grid_s, st); break;
         case 6: launch_spmv<6>(q, mode, grid_s, st); break;
@@ -781,16 +866,6 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         return PBE_OK;
     };
 
-    if (lim) {
-        rc = limited_weights(m, scheme, nfields, stride, psi, phi, psi_b, stride_b, wface, grad_ws, KCg, st, &launches);
-        if (rc != PBE_OK) return rc;
-    } else {
-        imp_diag_kernel<<<Gs, kBlock, 0, st>>>(q);
-        ++launches;
-    }
-    imp_xsum_kernel<<<grid_p, kBlock, 0, st>>>(q);
-    ++launches;
-    finalize(PH_XSUM, Gp);
 #define PBE_IMP_W(KERNEL, ...)                                               \
     switch (W) {                                                             \
     case 4: KERNEL<4 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;      \
@@ -804,9 +879,37 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     case 6: KERNEL<6><<<grid_s, kBlock, 0, st>>>(q); break;                  \
     default: KERNEL<8><<<grid_s, kBlock, 0, st>>>(q); break;                 \
     }
+#define PBE_IMP_W8(KERNEL, ...)                                              \
+    switch (W) {                                                             \
+    case 4: KERNEL<4 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;      \
+    case 6: KERNEL<6 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;      \
+    default: KERNEL<8 __VA_ARGS__><<<grid_s, kBlock, 0, st>>>(q); break;     \
+    }
 #define PBE_IMP_COMMA ,
     if (lim) {
-        PBE_IMP_WL(imp_lim_init_kernel)
+        rc = limited_weights(m, scheme, nfields, stride, psi, phi, psi_b, stride_b, wface, grad_ws, KCg, st, &launches);
+        if (rc != PBE_OK) return rc;
+        if (solver == PBE_FVM_SOLVER_AUTO) {
+            double est = 0.0;
+            PBE_CUDA(cudaMemsetAsync(q.est, 0, sizeof(unsigned long long), st));
+            PBE_IMP_WL(imp_lim_est_kernel)
+            ++launches;
+            PBE_CUDA(cudaMemcpyAsync(&est, q.est, sizeof(double), cudaMemcpyDeviceToHost, st));
+            PBE_CUDA(cudaStreamSynchronize(st));
+            solver = est <= 0.9 ? PBE_FVM_SOLVER_JACOBI : PBE_FVM_SOLVER_BICGSTAB;
+        }
+    } else {
+        imp_diag_kernel<<<Gs, kBlock, 0, st>>>(q);
+        ++launches;
+    }
+    const bool jac = solver == PBE_FVM_SOLVER_JACOBI;
+    imp_xsum_kernel<<<grid_p, kBlock, 0, st>>>(q);
+    ++launches;
+    finalize(PH_XSUM, Gp);
+    if (lim && jac) {
+        PBE_IMP_W8(imp_lim_init_kernel, PBE_IMP_COMMA true)
+    } else if (lim) {
+        PBE_IMP_W8(imp_lim_init_kernel, PBE_IMP_COMMA false)
     } else if (jac) {
         PBE_IMP_W(imp_init_kernel, PBE_IMP_COMMA true)
     } else {
@@ -866,11 +969,17 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
 #undef PBE_IMP_W
 #undef PBE_IMP_COMMA
 #undef PBE_IMP_WL
+#undef PBE_IMP_W8
     m->ctx->launches += launches;
     if (rc != PBE_OK) return rc;
     PBE_CUDA(cudaGetLastError());
     if (perf)
         for (int k = 0; k < nfields; ++k)
             perf[k] = pbe_fvm_perf{host[k].res0, host[k].res, host[k].iters, host[k].state};
+    for (int k = 0; k < nfields; ++k) // a field left worse than it came in is an error, not a result
+        PBE_REQUIRE(host[k].state != 2 || host[k].res <= host[k].res0, PBE_E_UNSUPPORTED,
+                    "pbe_transport_implicit: field %d diverged (%s, residual %g -> %g after %d iterations): the matrix is "
+                    "not diagonally dominant at this time step; ask for PBE_FVM_SOLVER_BICGSTAB or reduce deltaT",
+                    k, jac ? "Jacobi" : "BiCGStab", host[k].res0, host[k].res, host[k].iters);
     return PBE_OK;
 }
