@@ -579,6 +579,7 @@ __global__ void __launch_bounds__(kBlock) imp_lim_spmv_kernel(const ImpParams q)
 
 template <int W>
 __global__ void __launch_bounds__(kBlock) imp_lim_jacobi_kernel(const ImpParams q) {
+    extern __shared__ double lim_stage[]; // [2][2 W][kBlock]: the gathered z and face weights of two fields
     __shared__ double wsum[kMaxChunk][kBlock / 32];
     const int k0 = blockIdx.y * q.chunk, kend = min(q.nfields, k0 + q.chunk);
     auto next_active = [&](int k) {
@@ -593,20 +594,49 @@ __global__ void __launch_bounds__(kBlock) imp_lim_jacobi_kernel(const ImpParams 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     LimRow<W> R;
     load_lim_row<W>(q, c, R);
-    for (; k < kend; k = next_active(k + 1)) {
-        const size_t o = (size_t)k * q.nc;
-        const double *zin = q.p + o;
-        const double *wk = q.wface + (size_t)k * q.nint;
+    // the pipeline of imp_jacobi_kernel, with the field's face weights travelling beside its z values
+    auto cp8 = [](double *dst, const double *src) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                     : "memory");
+    };
+    double mine_n = 0.0, x_n = 0.0, di_n = 0.0;
+    auto issue = [&](int kk, int par) {
+        if (kk < kend) {
+            const size_t o = (size_t)kk * q.nc;
+            const double *zin = q.p + o, *wk = q.wface + (size_t)kk * q.nint;
+            double *st = lim_stage + (size_t)par * 2 * W * kBlock + threadIdx.x;
+#pragma unroll
+            for (int s = 0; s < W; ++s) {
+                cp8(st + (size_t)s * kBlock, zin + R.col[s]);
+                cp8(st + (size_t)(W + s) * kBlock, wk + R.fidx[s]);
+            }
+            mine_n = __ldg(zin + c);
+            x_n = q.x[(size_t)kk * q.stride + c];
+            di_n = __ldg(q.dinvK + o + c);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int par = 0;
+    issue(k, par);
+    while (k < kend) {
+        const int kn = next_active(k + 1);
+        const double mine = mine_n, xv = x_n, di = di_n;
+        issue(kn, par ^ 1);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        const double *st = lim_stage + (size_t)par * 2 * W * kBlock + threadIdx.x;
         double acc = 0.0;
 #pragma unroll
-        for (int s = 0; s < W; ++s) acc = fma(fma(-__ldg(wk + R.fidx[s]), R.ph[s], R.addc[s]), __ldg(zin + R.col[s]), acc);
+        for (int s = 0; s < W; ++s)
+            acc = fma(fma(-st[(size_t)(W + s) * kBlock], R.ph[s], R.addc[s]), st[(size_t)s * kBlock], acc);
         const double rz = -acc;
         if (valid) {
-            q.x[(size_t)k * q.stride + c] += zin[c];
-            q.v[o + c] = __ldg(q.dinvK + o + c) * rz;
+            __stcs(q.x + (size_t)k * q.stride + c, xv + mine);
+            __stcs(q.v + (size_t)k * q.nc + c, di * rz);
         }
         const double sum = warp_sum(valid ? fabs(rz) : 0.0);
         if (lane == 0) wsum[k - k0][wid] = sum;
+        k = kn;
+        par ^= 1;
     }
     __syncthreads();
     const int kt = k0 + threadIdx.x;
@@ -925,7 +955,15 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         // one iteration queued past the end changes nothing.
         auto issue = [&](int slot) -> int {
             if (lim) {
-                PBE_IMP_WL(imp_lim_jacobi_kernel)
+                const size_t smem = (size_t)2 * 2 * W * kBlock * sizeof(double);
+                const void *fn = W == 4 ? (const void *)imp_lim_jacobi_kernel<4>
+                                        : W == 6 ? (const void *)imp_lim_jacobi_kernel<6> : (const void *)imp_lim_jacobi_kernel<8>;
+                PBE_CUDA(raise_dyn_smem(m->ctx, fn, smem));
+                switch (W) {
+                case 4: imp_lim_jacobi_kernel<4><<<grid_s, kBlock, smem, st>>>(q); break;
+                case 6: imp_lim_jacobi_kernel<6><<<grid_s, kBlock, smem, st>>>(q); break;
+                default: imp_lim_jacobi_kernel<8><<<grid_s, kBlock, smem, st>>>(q); break;
+                }
             } else {
                 PBE_IMP_W(imp_jacobi_kernel)
             }
