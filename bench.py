@@ -1109,6 +1109,21 @@ def leg_transport(B: Bench, w, moc):
                             "call": "pbe_moc_correct_resident with an attached mesh (pinned host eps, rho, nu, alpha, "
                                     "phi -> d): sources + upwind transport update of the resident class fields",
                             "d_mean": float(dh.mean())}
+        # the same call with usingMULES false, the reference's default: sources + solveWithFVM (implicit, fvSolution of the
+        # reference's cases); deltaT is the transport legs' (Courant 0.4) so that the solve is the one timed above
+        st.set_implicit(tolerance=1e-5, min_iter=1)
+        st.correct(sm["eps"], sm["rho"], sm["nu"], sm["alpha"], tdt, phi=ph, d_out=dh, minmax=True)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            st.correct(sm["eps"], sm["rho"], sm["nu"], sm["alpha"], tdt, phi=ph, d_out=dh, minmax=True)
+        ti = (time.perf_counter() - t0) / 3
+        pf = st.solver_performance()
+        transport["e2e_implicit"] = {"value": tc * tK / ti, "unit": "cell-class-updates/s", "ms_per_step": ti * 1e3,
+                                     "h2d_bytes_per_step": 32 * tc + tm["phi"].size * 8, "d2h_bytes_per_step": 8 * tc,
+                                     "iterations": [min(p[2] for p in pf), max(p[2] for p in pf)],
+                                     "call": "pbe_moc_correct_resident after pbe_moc_state_set_implicit: sources + the "
+                                             "implicit solve of all class fields (MOC::solveWithFVM)",
+                                     "d_mean": float(dh.mean())}
         del sn
         st.close()
     del tpsi, tS, tout, tphi, tmesh

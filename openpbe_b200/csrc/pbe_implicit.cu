@@ -58,6 +58,11 @@ struct ImpParams {
     double *partial; // [nfields][kNS][G]
     const double *wface; // limited schemes: limitedScheme::weights of every internal face, [nfields][nint]
     double *dinvK;       // limited schemes: the fields' own inverse diagonals, [nfields][nc]
+    const double *Sf, *Cc, *wlin; // mesh geometry (component-major Sf [3][faces], C [3][nc]; linear weights [nint])
+    const int32_t *owner, *neigh;
+    double *grad;   // [chunk of fields][3][nc] scratch
+    double *wout;   // = wface, written by the weights kernel
+    int k0, kn, scheme;
     unsigned long long *est; // limited schemes: bits of max over fields and cells of sum|off-diagonal| / diagonal
     double rdt, relax, tol, rel_tol;
     int min_iter, max_iter;
@@ -88,6 +93,35 @@ __device__ __forceinline__ void block_sums(const ImpParams &q, int k, double (&v
     }
     __syncthreads();
 }
+
+// The per-field sums of a CTA that sweeps a chunk of fields: every warp parks its sums in shared memory, ONE barrier at
+// the end of the chunk, then thread j adds the warps' values of field k0 + j in a fixed order (instead of two barriers
+// per field as block_sums needs).
+template <int NS>
+struct ChunkSums {
+    double (*w)[NS][kBlock / 32];
+    __device__ __forceinline__ void put(int kk, const double (&v)[NS]) {
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+            const double s = warp_sum(v[j]);
+            if (lane == 0) w[kk][j][wid] = s;
+        }
+    }
+    __device__ __forceinline__ void flush(const ImpParams &q, int k0, int kend) {
+        __syncthreads();
+        const int k = k0 + threadIdx.x;
+        if (k < kend) {
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                double s = 0.0;
+#pragma unroll
+                for (int i = 0; i < kBlock / 32; ++i) s += w[threadIdx.x][j][i];
+                q.partial[((size_t)k * kNS + j) * q.G + blockIdx.x] = s;
+            }
+        }
+    }
+};
 
 // gaussConvectionScheme::fvmDiv with the upwind weights w = pos(phi): lower = -w phi, upper = lower + phi
 __device__ __forceinline__ void face_coeffs(double ph, double &lower, double &upper) {
@@ -208,8 +242,11 @@ __global__ void __launch_bounds__(kBlock) imp_init_kernel(const ImpParams q) {
     Row<W> R;
     load_row<W>(q, c, false, R);
     const double V = __ldg(q.V + c), a1 = __ldg(q.a1 + c), drel = __ldg(q.drel + c);
+    __shared__ double csum[kMaxChunk][3][kBlock / 32];
+    ChunkSums<3> sums{csum};
+    const int kbeg = blockIdx.y * q.chunk;
     const int kend = min(q.nfields, (int)(blockIdx.y + 1) * q.chunk);
-    for (int k = blockIdx.y * q.chunk; k < kend; ++k) {
+    for (int k = kbeg; k < kend; ++k) {
         const double *x = q.psi + (size_t)k * q.stride;
         const double mine = x[c];
         double b = q.rdt * mine * V;
@@ -239,8 +276,9 @@ __global__ void __launch_bounds__(kBlock) imp_init_kernel(const ImpParams q) {
         }
         const double pA = __ldg(&q.sc[k].xbar) * a1;
         double s[3] = {valid ? fabs(Ax - pA) + fabs(b - pA) : 0.0, valid ? fabs(res) : 0.0, valid ? res * res : 0.0};
-        block_sums<3>(q, k, s);
+        sums.put(k - kbeg, s);
     }
+    sums.flush(q, kbeg, kend);
 }
 
 // out = A M^-1 in.  MODE 0: in = p, out = v, sum (r0, v).  MODE 1: in = s (held in r), out = t, sums (t, s), (t, t).
@@ -457,8 +495,11 @@ __global__ void __launch_bounds__(kBlock) imp_lim_init_kernel(const ImpParams q)
             icmag += fabs(phb);
         }
     }
+    __shared__ double csum[kMaxChunk][3][kBlock / 32];
+    ChunkSums<3> sums{csum};
+    const int kbeg = blockIdx.y * q.chunk;
     const int kend = min(q.nfields, (int)(blockIdx.y + 1) * q.chunk);
-    for (int k = blockIdx.y * q.chunk; k < kend; ++k) {
+    for (int k = kbeg; k < kend; ++k) {
         const double *x = q.psi + (size_t)k * q.stride;
         const double *wk = q.wface + (size_t)k * q.nint;
         const double mine = x[c];
@@ -505,7 +546,86 @@ __global__ void __launch_bounds__(kBlock) imp_lim_init_kernel(const ImpParams q)
         }
         const double pA = __ldg(&q.sc[k].xbar) * (diag + offsum);
         double sm[3] = {valid ? fabs(Ax - pA) + fabs(b - pA) : 0.0, valid ? fabs(res) : 0.0, valid ? res * res : 0.0};
-        block_sums<3>(q, k, sm);
+        sums.put(k - kbeg, sm);
+    }
+    sums.flush(q, kbeg, kend);
+}
+
+// gaussGrad with linear interpolation for a chunk of fields: grad_c = (sum_f Sf psi_f) / V, faces in ascending order.
+// The cell's geometry (per slot: +-Sf, linear weight) lives in registers, a field costs its own value and W gathers.
+template <int W>
+__global__ void __launch_bounds__(kBlock) imp_lim_grad_kernel(const ImpParams q) {
+    const int64_t c = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (c >= q.nc) return;
+    const int64_t nf = q.nint + q.nbnd;
+    int32_t col[W], kind[W]; // kind: 0 padding, 1 owner side, 2 neighbour side, 3 + b boundary face b
+    double sx[W], sy[W], sz[W], wl[W];
+#pragma unroll
+    for (int s = 0; s < W; ++s) {
+        const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c), fc = __ldg(q.face + (size_t)s * q.nc + c);
+        col[s] = (int32_t)c, kind[s] = 0, sx[s] = sy[s] = sz[s] = 0.0, wl[s] = 0.0;
+        if (oth >= 0) {
+            const bool own = fc >= 0;
+            const int64_t f = own ? fc : ~fc;
+            const double sg = own ? 1.0 : -1.0;
+            col[s] = oth, kind[s] = own ? 1 : 2, wl[s] = __ldg(q.wlin + f);
+            sx[s] = sg * __ldg(q.Sf + f), sy[s] = sg * __ldg(q.Sf + nf + f), sz[s] = sg * __ldg(q.Sf + 2 * nf + f);
+        } else if (oth <= -2) {
+            const int64_t b = -(int64_t)oth - 2, f = q.nint + b;
+            kind[s] = 3 + (int32_t)b;
+            sx[s] = __ldg(q.Sf + f), sy[s] = __ldg(q.Sf + nf + f), sz[s] = __ldg(q.Sf + 2 * nf + f);
+        }
+    }
+    const double rV = 1.0 / __ldg(q.V + c);
+    const int kend = min(q.kn, (int)(blockIdx.y + 1) * q.chunk);
+    for (int kc = blockIdx.y * q.chunk; kc < kend; ++kc) {
+        const int k = q.k0 + kc;
+        const double *psi = q.psi + (size_t)k * q.stride;
+        const double mine = psi[c];
+        double g0 = 0.0, g1 = 0.0, g2 = 0.0;
+#pragma unroll
+        for (int s = 0; s < W; ++s) {
+            double fv;
+            if (kind[s] >= 3)
+                fv = q.psi_b ? __ldg(q.psi_b + (size_t)k * q.stride_b + (kind[s] - 3)) : mine;
+            else {
+                const double theirs = __ldg(psi + col[s]);
+                const double P = kind[s] == 1 ? mine : theirs, N = kind[s] == 1 ? theirs : mine;
+                fv = fma(wl[s], P - N, N);
+            }
+            g0 = fma(sx[s], fv, g0), g1 = fma(sy[s], fv, g1), g2 = fma(sz[s], fv, g2);
+        }
+        double *g = q.grad + (size_t)kc * 3 * q.nc;
+        g[c] = g0 * rV, g[q.nc + c] = g1 * rV, g[2 * q.nc + c] = g2 * rV;
+    }
+}
+
+// limitedScheme::weights(vf) of the internal faces for the chunk's fields: limiter CDweight + (1 - limiter) pos(phi),
+// limiter(r) of vanLeer or limitedLinear(1), r = NVDTVD::r from the upwind cell's gradient.  One thread per face keeps
+// the face's geometry in registers.
+__global__ void __launch_bounds__(kBlock) imp_lim_weights_kernel(const ImpParams q) {
+    const int64_t f = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (f >= q.nint) return;
+    const int32_t own = __ldg(q.owner + f), nei = __ldg(q.neigh + f);
+    const double ph = __ldg(q.phi + f), wl = __ldg(q.wlin + f), up_w = ph >= 0.0 ? 1.0 : 0.0;
+    const int32_t up = ph > 0.0 ? own : nei;
+    const double d0 = __ldg(q.Cc + nei) - __ldg(q.Cc + own), d1 = __ldg(q.Cc + q.nc + nei) - __ldg(q.Cc + q.nc + own),
+                 d2 = __ldg(q.Cc + 2 * q.nc + nei) - __ldg(q.Cc + 2 * q.nc + own);
+    const int kend = min(q.kn, (int)(blockIdx.y + 1) * q.chunk);
+    for (int kc = blockIdx.y * q.chunk; kc < kend; ++kc) {
+        const int k = q.k0 + kc;
+        const double *psi = q.psi + (size_t)k * q.stride;
+        const double *g = q.grad + (size_t)kc * 3 * q.nc;
+        const double P = __ldg(psi + own), N = __ldg(psi + nei);
+        const double gradcf = d0 * g[up] + d1 * g[q.nc + up] + d2 * g[2 * q.nc + up];
+        const double gradf = N - P;
+        double r;
+        if (fabs(gradcf) >= 1000 * fabs(gradf))
+            r = 2 * 1000 * (gradcf >= 0 ? 1.0 : -1.0) * (gradf >= 0 ? 1.0 : -1.0) - 1;
+        else
+            r = 2 * (gradcf / gradf) - 1;
+        const double lim = q.scheme == PBE_DIV_VANLEER ? (r + fabs(r)) / (1 + fabs(r)) : fmax(fmin(2.0 * r, 1.0), 0.0);
+        q.wout[(size_t)k * q.nint + f] = lim * wl + (1.0 - lim) * up_w;
     }
 }
 
@@ -794,7 +914,7 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
                 "pbe_transport_implicit: a limited scheme needs the mesh geometry (pbe_mesh_set_geometry)");
     // workspace: Jacobi z, z'; BiCGStab r, r0, p, v, t; for a limited scheme the fields' inverse diagonals, the face
     // weights and a gradient scratch; 4 per-cell rows
-    const int KCg = lim ? (int)std::max<size_t>(1, std::min<size_t>((size_t)nfields, ((size_t)1 << 30) / ((size_t)3 * nc * 8) + 1)) : 0;
+    const int KCg = lim ? (int)std::max<size_t>(1, std::min<size_t>((size_t)nfields, ((size_t)1 << 31) / ((size_t)3 * nc * 8) + 1)) : 0;
     const size_t nvec = (may_bicg ? 5 : 2) + (lim ? 1 : 0);
     const size_t need = nvec * nfields * nc + (size_t)4 * nc +
                         (lim ? (size_t)nfields * m->nint + (size_t)KCg * 3 * nc : 0);
@@ -917,8 +1037,24 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     }
 #define PBE_IMP_COMMA ,
     if (lim) {
-        rc = limited_weights(m, scheme, nfields, stride, psi, phi, psi_b, stride_b, wface, grad_ws, KCg, st, &launches);
-        if (rc != PBE_OK) return rc;
+        // gradient and face weights of all fields, KCg fields at a time (the gradient scratch holds one chunk)
+        q.Sf = m->d_Sf, q.Cc = m->d_C, q.wlin = m->d_w, q.owner = m->d_owner, q.neigh = m->d_neigh;
+        q.grad = grad_ws, q.wout = wface, q.scheme = scheme;
+        const int chunk_keep = q.chunk;
+        for (int k0 = 0; k0 < nfields; k0 += KCg) {
+            q.k0 = k0, q.kn = std::min(KCg, nfields - k0);
+            q.chunk = std::min(chunk_keep, q.kn);
+            const unsigned gy = (unsigned)((q.kn + q.chunk - 1) / q.chunk);
+            switch (W) {
+            case 4: imp_lim_grad_kernel<4><<<dim3((unsigned)Gs, gy), kBlock, 0, st>>>(q); break;
+            case 6: imp_lim_grad_kernel<6><<<dim3((unsigned)Gs, gy), kBlock, 0, st>>>(q); break;
+            default: imp_lim_grad_kernel<8><<<dim3((unsigned)Gs, gy), kBlock, 0, st>>>(q); break;
+            }
+            imp_lim_weights_kernel<<<dim3((unsigned)((m->nint + kBlock - 1) / kBlock), gy), kBlock, 0, st>>>(q);
+            launches += 2;
+        }
+        q.chunk = chunk_keep;
+        (void)&limited_weights; // the per-field kernels of the MULES path (pbe_mules.cu) remain the cross-check
         if (solver == PBE_FVM_SOLVER_AUTO) {
             double est = 0.0;
             PBE_CUDA(cudaMemsetAsync(q.est, 0, sizeof(unsigned long long), st));

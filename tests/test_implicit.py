@@ -193,7 +193,7 @@ def device_solve(ctx, m, psi, phi, dt, S=None, psi_b=None, **kw):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("shape,vel", [((12, 9, 7), (1.0, -0.5, 0.25)), ((40, 1, 1), (1.0, 0.0, 0.0)),
-                                       ((17, 13, 1), (-0.3, 0.8, 0.0)), ((48, 40, 24), (0.7, 0.4, -0.9))])
+                                       ((17, 13, 1), (-0.3, 0.8, 0.0)), ((32, 24, 16), (0.7, 0.4, -0.9))])
 @pytest.mark.parametrize("courant", [0.4, 6.0])
 @pytest.mark.parametrize("solver", ["jacobi", "bicgstab"])
 def test_device_implicit_reaches_the_direct_solution_block(ctx, shape, vel, courant, solver):
