@@ -1054,7 +1054,6 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
             launches += 2;
         }
         q.chunk = chunk_keep;
-        (void)&limited_weights; // the per-field kernels of the MULES path (pbe_mules.cu) remain the cross-check
         if (solver == PBE_FVM_SOLVER_AUTO) {
             double est = 0.0;
             PBE_CUDA(cudaMemsetAsync(q.est, 0, sizeof(unsigned long long), st));

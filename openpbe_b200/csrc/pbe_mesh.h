@@ -51,10 +51,3 @@ struct pbe_mesh {
     size_t imp_pinned_bytes = 0;
     cudaEvent_t imp_ev[2] = {nullptr, nullptr};
 };
-
-namespace pbe {
-// limitedScheme::weights of all internal faces, wout [nfields][nint] (pbe_mules.cu); grad_ws: [KC][3][ncells] scratch
-int limited_weights(pbe_mesh *m, int scheme, int nfields, int64_t stride, const double *psi, const double *phi,
-                    const double *psi_b, int64_t stride_b, double *wout, double *grad_ws, int KC, cudaStream_t st,
-                    int64_t *launches);
-} // namespace pbe

@@ -600,64 +600,6 @@ __global__ void qmom_psi_max_kernel(int nm, int64_t ncells, int64_t stride, cons
 
 } // namespace
 
-// limitedScheme::weights(vf) of every internal face for a chunk of fields (after mules_grad_kernel):
-//   w = limiter CDweight + (1 - limiter) pos(faceFlux),  limiter(r) of vanLeer or limitedLinear(1), r = NVDTVD::r
-// -- the weights gaussConvectionScheme::fvmDiv puts into the matrix of an implicit convection term.
-namespace {
-__global__ void __launch_bounds__(256) limited_weights_kernel(const MulesParams p, double *__restrict__ wout) {
-    const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= p.nint) return;
-    const int kc = blockIdx.y, k = p.k0 + kc;
-    const double *psi = p.psi + (size_t)k * p.stride;
-    const int32_t own = __ldg(p.owner + f), nei = __ldg(p.neigh + f);
-    const double P = __ldg(psi + own), N = __ldg(psi + nei), ph = __ldg(p.phi + f);
-    const double *g = p.grad + (size_t)kc * 3 * p.nc;
-    const double d0 = __ldg(p.C + nei) - __ldg(p.C + own), d1 = __ldg(p.C + p.nc + nei) - __ldg(p.C + p.nc + own),
-                 d2 = __ldg(p.C + 2 * p.nc + nei) - __ldg(p.C + 2 * p.nc + own);
-    const int32_t up = (ph > 0) ? own : nei;
-    const double gradcf = d0 * g[up] + d1 * g[p.nc + up] + d2 * g[2 * p.nc + up];
-    const double gradf = N - P;
-    double r;
-    if (fabs(gradcf) >= 1000 * fabs(gradf))
-        r = 2 * 1000 * sign_(gradcf) * sign_(gradf) - 1;
-    else
-        r = 2 * (gradcf / gradf) - 1;
-    double lim;
-    if (p.scheme == PBE_DIV_VANLEER)
-        lim = (r + fabs(r)) / (1 + fabs(r));
-    else // limitedLinear(k = 1): twoByk = 2 / max(k, SMALL); max(min(twoByk r, 1), 0)
-        lim = dmax_(dmin_(2.0 * r, 1.0), 0.0);
-    wout[(size_t)k * p.nint + f] = lim * __ldg(p.w + f) + (1.0 - lim) * pos_(ph);
-}
-} // namespace
-
-namespace pbe {
-int limited_weights(pbe_mesh *m, int scheme, int nfields, int64_t stride, const double *psi, const double *phi,
-                    const double *psi_b, int64_t stride_b, double *wout, double *grad_ws, int KC, cudaStream_t st,
-                    int64_t *launches) {
-    PBE_REQUIRE(m->d_Sf && m->d_C && m->d_w, PBE_E_INVALID,
-                "limited divergence scheme: the mesh geometry is missing (pbe_mesh_set_geometry)");
-    if (m->nint == 0) return PBE_OK;
-    MulesParams p{};
-    p.nc = m->ncells, p.nint = m->nint, p.nbnd = m->nbnd, p.stride = stride, p.stride_b = stride_b;
-    p.csr_ptr = m->d_csr_ptr, p.csr_other = m->d_csr_other, p.csr_face = m->d_csr_face;
-    p.owner = m->d_owner, p.neigh = m->d_neigh;
-    p.V = m->d_vcell, p.Sf = m->d_Sf, p.C = m->d_C, p.w = m->d_w;
-    p.psi = psi, p.psi_b = psi_b, p.phi = phi;
-    p.scheme = scheme;
-    p.grad = grad_ws;
-    for (int k0 = 0; k0 < nfields; k0 += KC) {
-        const int kn = std::min(KC, nfields - k0);
-        p.k0 = k0;
-        mules_grad_kernel<<<dim3((unsigned)((p.nc + 255) / 256), (unsigned)kn), 256, 0, st>>>(p);
-        limited_weights_kernel<<<dim3((unsigned)((p.nint + 255) / 256), (unsigned)kn), 256, 0, st>>>(p, wout);
-        *launches += 2;
-    }
-    PBE_CUDA(cudaGetLastError());
-    return PBE_OK;
-}
-} // namespace pbe
-
 extern "C" {
 
 int pbe_mesh_set_geometry(pbe_mesh *m, const double *Sf, const double *C, const double *weights) {
