@@ -878,7 +878,7 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     PBE_REQUIRE(nfields >= 1 && psi && phi && psi_out, PBE_E_INVALID, "pbe_transport_implicit: NULL field or nfields < 1");
     PBE_REQUIRE(stride >= m->ncells, PBE_E_INVALID, "pbe_transport_implicit: stride %lld < ncells %lld", (long long)stride,
                 (long long)m->ncells);
-    PBE_REQUIRE(psi_out != psi, PBE_E_INVALID, "pbe_transport_implicit: psi_out must not alias psi");
+    PBE_REQUIRE(psi_out != psi && psi_out != S, PBE_E_INVALID, "pbe_transport_implicit: psi_out must not alias psi or S");
     PBE_REQUIRE(psi_b == nullptr || stride_b >= m->nbnd, PBE_E_INVALID, "pbe_transport_implicit: stride_b %lld < boundary faces %lld",
                 (long long)stride_b, (long long)m->nbnd);
     PBE_REQUIRE(dt > 0.0, PBE_E_INVALID, "pbe_transport_implicit: dt must be positive");
