@@ -1088,6 +1088,19 @@ def leg_transport(B: Bench, w, moc):
                          "frac": ibytes / (ims * 1e-3) / 1e9 / B.hbm_peak, "algorithmic_bytes": ibytes,
                          "note": "bytes of the iteration actually run: 32 B per cell-field for the set-up and for "
                                  "every sweep a field needed (DESIGN.md 4.11)", "traffic": None}}
+        if "Sf" in tm:  # the scheme of the reference's cases in the implicit term: one matrix per field
+            for _ in range(2):
+                _, perf = tmesh.transport_implicit(tpsi, tphi, tdt, S=tS, out=tout, scheme="Gauss vanLeer")
+            B.e0.record()
+            for _ in range(3):
+                tmesh.transport_implicit(tpsi, tphi, tdt, S=tS, out=tout, scheme="Gauss vanLeer")
+            B.e1.record()
+            torch.cuda.synchronize()
+            vms = B.e0.elapsed_time(B.e1) / 3
+            transport["implicit"]["vanLeer"] = {"ms_per_step": vms, "value": tc * tK / (vms * 1e-3),
+                                                "unit": "cell-field-updates/s", "scheme": "Euler implicit + Gauss vanLeer",
+                                                "iterations": [min(p[2] for p in perf), max(p[2] for p in perf)],
+                                                "final_residual_max": max(p[1] for p in perf)}
     if not args.no_e2e and world == 1:
         # MOC::correct() with solveWithMULES through the resident state: class fields stay on the device,
         # pinned host eps, rho, nu, alpha, phi in, d out

@@ -19,7 +19,7 @@ BR_NONE, BR_BINARY, BR_CT, BR_TABLE = 0, 1, 2, 3
 DAUGHTER_UNIFORM_BINARY = 0
 QMOM_MAX_ORDER = 4
 MOC_KERNEL_SMEM, MOC_KERNEL_TMEM, MOC_KERNEL_PIVOT = 1, 2, 3
-DIV_UPWIND, DIV_VANLEER = 0, 1
+DIV_UPWIND, DIV_VANLEER, DIV_LIMITEDLINEAR = 0, 1, 2
 CELLS_ALL, CELLS_REGULAR, CELLS_IRREGULAR = 0, 1, 2
 FVM_SOLVER_AUTO, FVM_SOLVER_BICGSTAB, FVM_SOLVER_JACOBI = 0, 1, 2
 

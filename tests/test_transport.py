@@ -87,10 +87,13 @@ def test_div_scheme_names():
     assert capi.lib().pbe_div_scheme_type(b"Gauss upwind", capi.C.byref(out)) == capi.PBE_OK and out.value == capi.DIV_UPWIND
     # the scheme of the reference's validation case (simmons_and_azzopardi/c01/system/fvSchemes:34)
     assert capi.lib().pbe_div_scheme_type(b"Gauss vanLeer", capi.C.byref(out)) == capi.PBE_OK and out.value == capi.DIV_VANLEER
+    # the scheme the reference's MOC cases put on the implicit term, div(U,nk) (tests/integration/MOC/template/system/fvSchemes:44)
+    assert capi.lib().pbe_div_scheme_type(b"Gauss limitedLinear 1", capi.C.byref(out)) == capi.PBE_OK and out.value == capi.DIV_LIMITEDLINEAR
+    assert capi.lib().pbe_div_scheme_type(b"Gauss limitedLinear 0.5", capi.C.byref(out)) == capi.PBE_E_UNKNOWN_TYPE  # only k = 1
     rc = capi.lib().pbe_div_scheme_type(b"Gauss QUICK", capi.C.byref(out))
     assert rc == capi.PBE_E_UNKNOWN_TYPE
     msg = capi.last_error()
-    assert "QUICK" in msg and "Valid schemes are" in msg and "upwind" in msg and "vanLeer" in msg
+    assert "QUICK" in msg and "Valid schemes are" in msg and "upwind" in msg and "vanLeer" in msg and "limitedLinear 1" in msg
 
 
 # ------------------------------------------------------------------------------------------------
