@@ -336,10 +336,25 @@ typedef struct pbe_fvm_perf {
 /* psi, S, psi_out DEVICE [nfields][stride] (psi_out must not alias psi); phi DEVICE [internal + boundary faces];
  * psi_b DEVICE [nfields][stride_b] fixed patch values, or NULL = zero-gradient on every boundary face; controls NULL =
  * {1e-5, 0, 1, 1000, 0, AUTO}; perf HOST [nfields] or NULL.  Synchronous on return (the iteration count is data dependent).
- * Uncoupled patches only (PBE_E_UNSUPPORTED on a mesh with processor patches). */
+ * Processor patches: see pbe_mesh_set_halo_plan below (PBE_E_UNSUPPORTED without a plan). */
 int pbe_transport_implicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stride, const double *psi,
                            const double *phi, const double *psi_b, int64_t stride_b, const double *S, double dt,
                            const pbe_fvm_controls *controls, double *psi_out, pbe_fvm_perf *perf, void *cuda_stream);
+
+/* The implicit solve on a DECOMPOSED mesh (one sub-domain per GPU, processor patches marked by pbe_mesh_set_coupled,
+ * a communicator on the context: pbe_comm_init).  OpenFOAM treats a processor patch as a coupled patch: w phi_b on the
+ * diagonal, (1 - w) phi_b times the value ACROSS the face as an off-diagonal coefficient that every solver iteration
+ * refreshes through the interface update, and global sums (gSum / gAverage) in the residual.  Here a coupled face is
+ * one more column of the cell's row, read from a halo row; before every Jacobi sweep the rank's boundary values of z
+ * are packed (pbe_gather_cells) and exchanged (ncclSend / ncclRecv in one group), and the per-field sums are
+ * all-reduced before the fields' states are updated -- all on the caller's stream, so all ranks take the same decisions
+ * and the host still looks at the states one sweep behind.  The plan: neighbour q = rank peer[q] shares the coupled
+ * faces [off[q], off[q] + cnt[q]) (indices within the coupled range, same order on both sides as for
+ * pbe_halo_exchange); send_cells HOST [ncoupled]: this rank's cell on each coupled face; global_ncells: cells of the
+ * whole mesh (gAverage).  pbe_transport_implicit then solves the GLOBAL system (Gauss upwind, Jacobi); every rank must
+ * call it with the same nfields and controls. */
+int pbe_mesh_set_halo_plan(pbe_mesh *mesh, int nneigh, const int *peer, const int64_t *off, const int64_t *cnt,
+                           const int32_t *send_cells, int64_t global_ncells);
 
 /* HOST-buffer MOC::correct() with solveWithMULES (MOC.C:159-184, 198-272): what the OpenFOAM-side
  * adapter calls when the case's div(phi,n.*) scheme is on the device.  n_host [N][stride] is

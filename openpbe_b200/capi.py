@@ -140,6 +140,7 @@ PROTOTYPES = {
     "pbe_transport_explicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp,
                                          C.c_double, _vp, _vp]),
     "pbe_mesh_set_geometry": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "pbe_mesh_set_halo_plan": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _i64]),
     "pbe_transport_implicit": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp, C.c_double, _vp, _vp,
                                           _vp, _vp]),
     "pbe_transport_mules": (C.c_int, [_vp, C.c_int, C.c_int, _i64, _vp, _vp, _vp, _i64, _vp, _vp, C.c_double,

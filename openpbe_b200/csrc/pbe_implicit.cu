@@ -56,6 +56,11 @@ struct ImpParams {
     double *x, *r, *r0, *p, *v, *t;
     FieldSc *sc;
     double *partial; // [nfields][kNS][G]
+    // decomposed mesh: boundary faces [coupled0, coupled0 + ncpl) are processor-patch faces; halo_x / halo_z
+    // [nfields][ncpl]: psi0 / the current z across them; gsum [nfields][kNS]: the all-reduced sums (null: one rank)
+    int64_t coupled0, ncpl, nc_global;
+    const double *halo_x, *halo_z;
+    double *gsum;
     const double *wface; // limited schemes: limitedScheme::weights of every internal face, [nfields][nint]
     double *dinvK;       // limited schemes: the fields' own inverse diagonals, [nfields][nc]
     const double *Sf, *Cc, *wlin; // mesh geometry (component-major Sf [3][faces], C [3][nc]; linear weights [nint])
@@ -136,7 +141,7 @@ __global__ void __launch_bounds__(kBlock) imp_diag_kernel(const ImpParams q) {
     const int64_t c = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (c >= q.nc) return;
     const double V = __ldg(q.V + c);
-    double D0 = q.rdt * V, sumOff = 0.0, offsum = 0.0, ic = 0.0, icmag = 0.0;
+    double D0 = q.rdt * V, sumOff = 0.0, offsum = 0.0, ic = 0.0, icmag = 0.0, icc = 0.0;
     for (int s = 0; s < q.W; ++s) {
         const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c), fc = __ldg(q.face + (size_t)s * q.nc + c);
         if (oth >= 0) {
@@ -147,20 +152,31 @@ __global__ void __launch_bounds__(kBlock) imp_diag_kernel(const ImpParams q) {
             const double coef = own ? upper : lower;
             sumOff += fabs(coef);
             offsum += coef;
-        } else if (oth <= -2 && q.psi_b == nullptr) { // zero-gradient patch face: internalCoeffs = phi_b
-            const double phb = __ldg(q.phi + q.nint + (-(int64_t)oth - 2));
-            ic += phb;
-            icmag += fabs(phb);
+        } else if (oth <= -2) {
+            const int64_t bf = -(int64_t)oth - 2;
+            const double phb = __ldg(q.phi + q.nint + bf);
+            if (bf >= q.coupled0 && bf < q.coupled0 + q.ncpl) {
+                // processor patch = coupled: internalCoeffs = w phi_b on the diagonal, boundaryCoeffs = -(1 - w) phi_b
+                // times the value across: an off-diagonal coefficient like an internal face's upper
+                double lower, upper;
+                face_coeffs(phb, lower, upper);
+                icc -= lower;
+                sumOff += fabs(upper);
+                offsum += upper;
+            } else if (q.psi_b == nullptr) { // zero-gradient patch face: internalCoeffs = phi_b
+                ic += phb;
+                icmag += fabs(phb);
+            }
         }
     }
     double drel = 0.0;
-    if (q.relax > 0.0) { // fvMatrix::relax(alpha)
-        const double Dr = fmax(fabs(D0 + icmag), sumOff) / q.relax;
-        const double Dfin = Dr - ic;
+    if (q.relax > 0.0) { // fvMatrix::relax(alpha): coupled patches add their (signed) diagonal, uncoupled the magnitude
+        const double Dr = fmax(fabs(D0 + icc + icmag), sumOff) / q.relax;
+        const double Dfin = Dr - ic - icc;
         drel = Dfin - D0;
         D0 = Dfin;
     }
-    const double diag = D0 + ic; // addBoundaryDiag
+    const double diag = D0 + ic + icc; // addBoundaryDiag
     q.diag[c] = diag;
     q.dinv[c] = 1.0 / diag;
     q.a1[c] = diag + offsum;
@@ -187,7 +203,20 @@ __device__ __forceinline__ void slot(const ImpParams &q, int64_t c, int s, bool 
         face_coeffs(__ldg(q.phi + (own ? fc : ~fc)), lower, upper);
         col = oth;
         cf = (own ? upper : lower) * (precond ? __ldg(q.dinv + oth) : 1.0);
+    } else if (oth <= -2) {
+        const int64_t bf = -(int64_t)oth - 2;
+        if (bf >= q.coupled0 && bf < q.coupled0 + q.ncpl) { // column -(j + 1): entry j of the halo row
+            double lower, upper;
+            face_coeffs(__ldg(q.phi + q.nint + bf), lower, upper);
+            col = -(int32_t)(bf - q.coupled0) - 1;
+            cf = upper; // Jacobi only on decomposed meshes: no preconditioned operator
+        }
     }
+}
+
+// the value a column refers to: a cell of this sub-domain, or the cell across a processor-patch face (halo row)
+__device__ __forceinline__ const double *col_src(const double *field, const double *halo, int32_t col) {
+    return col >= 0 ? field + col : halo + (-(int64_t)col - 1);
 }
 
 template <int W>
@@ -203,17 +232,17 @@ __device__ __forceinline__ void load_row(const ImpParams &q, int64_t c, bool pre
 // sum_s cf_s in[col_s]
 template <int W>
 __device__ __forceinline__ double offdiag(const ImpParams &q, int64_t c, bool precond, const Row<W> &R,
-                                          const double *__restrict__ in) {
+                                          const double *__restrict__ in, const double *__restrict__ halo = nullptr) {
     double acc = 0.0;
     if constexpr (W > 0) {
 #pragma unroll
-        for (int s = 0; s < W; ++s) acc = fma(R.cf[s], __ldg(in + R.col[s]), acc);
+        for (int s = 0; s < W; ++s) acc = fma(R.cf[s], __ldg(col_src(in, halo, R.col[s])), acc);
     } else {
         for (int s = 0; s < q.W; ++s) {
             int32_t col;
             double cf;
             slot<0>(q, c, s, precond, col, cf);
-            acc = fma(cf, __ldg(in + col), acc);
+            acc = fma(cf, __ldg(col_src(in, halo, col)), acc);
         }
     }
     return acc;
@@ -257,11 +286,12 @@ __global__ void __launch_bounds__(kBlock) imp_init_kernel(const ImpParams q) {
                 const int32_t oth = __ldg(q.other + (size_t)s * q.nc + c);
                 if (oth <= -2) {
                     const int64_t bf = -(int64_t)oth - 2;
+                    if (bf >= q.coupled0 && bf < q.coupled0 + q.ncpl) continue; // processor patch: in the matrix
                     b -= __ldg(q.phi + q.nint + bf) * __ldg(q.psi_b + (size_t)k * q.stride_b + bf);
                 }
             }
         }
-        const double Ax = fma(R.diag, mine, offdiag<W>(q, c, false, R, x));
+        const double Ax = fma(R.diag, mine, offdiag<W>(q, c, false, R, x, q.halo_x ? q.halo_x + (size_t)k * q.ncpl : nullptr));
         const double res = b - Ax;
         if (valid) {
             const size_t o = (size_t)k * q.nc + c;
@@ -401,8 +431,9 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
         auto issue = [&](int kk, int par) {
             if (kk < kend) {
                 const double *zin = q.p + (size_t)kk * q.nc;
+                const double *zh = q.halo_z ? q.halo_z + (size_t)kk * q.ncpl : nullptr;
 #pragma unroll
-                for (int s = 0; s < W; ++s) cp8(&stage[par][s][threadIdx.x], zin + R.col[s]);
+                for (int s = 0; s < W; ++s) cp8(&stage[par][s][threadIdx.x], col_src(zin, zh, R.col[s]));
                 mine_n = __ldg(zin + c);
                 x_n = q.x[(size_t)kk * q.stride + c];
             }
@@ -432,7 +463,7 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
         for (; k < kend; k = next_active(k + 1)) {
             const size_t o = (size_t)k * q.nc;
             const double *zin = q.p + o;
-            const double rz = -offdiag<W>(q, c, false, R, zin);
+            const double rz = -offdiag<W>(q, c, false, R, zin, q.halo_z ? q.halo_z + (size_t)k * q.ncpl : nullptr);
             if (valid) {
                 q.x[(size_t)k * q.stride + c] += zin[c];
                 q.v[o + c] = R.dinv * rz;
@@ -769,28 +800,38 @@ __global__ void __launch_bounds__(kBlock) imp_lim_jacobi_kernel(const ImpParams 
 }
 
 // One CTA per field: the CTAs' partial sums added in a fixed order, then the field's scalars.
-__global__ void __launch_bounds__(kBlock) imp_finalize_kernel(const ImpParams q, int phase, int G) {
+// mode 0: one rank, sums and states in one go.  Decomposed meshes split it around the all-reduce: mode 1 writes this
+// rank's sums to gsum [nfields][kNS], mode 2 takes the all-reduced gsum and updates the states (every rank computes the
+// same states from the same sums: the ranks' loops stay in step without talking about it).
+__global__ void __launch_bounds__(kBlock) imp_finalize_kernel(const ImpParams q, int phase, int G, int mode) {
     const int k = blockIdx.x;
     FieldSc *sc = q.sc + k;
     if (phase >= PH_A && (sc->state != 0 || (phase == PH_C && sc->half))) return;
     __shared__ double sm[kNS][kBlock];
-    const double *part = q.partial + (size_t)k * kNS * q.G;
-    for (int j = 0; j < kNS; ++j) {
-        double s = 0.0;
-        for (int i = threadIdx.x; i < G; i += kBlock) s += part[(size_t)j * q.G + i];
-        sm[j][threadIdx.x] = s;
-    }
-    __syncthreads();
-    for (int w = kBlock / 2; w > 0; w >>= 1) {
-        if ((int)threadIdx.x < w)
-            for (int j = 0; j < kNS; ++j) sm[j][threadIdx.x] += sm[j][threadIdx.x + w];
+    if (mode != 2) {
+        const double *part = q.partial + (size_t)k * kNS * q.G;
+        for (int j = 0; j < kNS; ++j) {
+            double s = 0.0;
+            for (int i = threadIdx.x; i < G; i += kBlock) s += part[(size_t)j * q.G + i];
+            sm[j][threadIdx.x] = s;
+        }
         __syncthreads();
+        for (int w = kBlock / 2; w > 0; w >>= 1) {
+            if ((int)threadIdx.x < w)
+                for (int j = 0; j < kNS; ++j) sm[j][threadIdx.x] += sm[j][threadIdx.x + w];
+            __syncthreads();
+        }
     }
     if (threadIdx.x != 0) return;
-    const double s0 = sm[0][0], s1 = sm[1][0], s2 = sm[2][0];
+    if (mode == 1) {
+        for (int j = 0; j < kNS; ++j) q.gsum[(size_t)k * kNS + j] = sm[j][0];
+        return;
+    }
+    const double s0 = mode == 2 ? q.gsum[(size_t)k * kNS] : sm[0][0], s1 = mode == 2 ? q.gsum[(size_t)k * kNS + 1] : sm[1][0],
+                 s2 = mode == 2 ? q.gsum[(size_t)k * kNS + 2] : sm[2][0];
     auto conv = [&](double res) { return res < q.tol || (q.rel_tol > 0.0 && res < q.rel_tol * sc->res0); };
     switch (phase) {
-    case PH_XSUM: sc->xbar = s0 / (double)q.nc; break;
+    case PH_XSUM: sc->xbar = s0 / (double)q.nc_global; break;
     case PH_INIT:
         sc->norm = s0 + kNormSmall;
         sc->res0 = sc->res = s1 / sc->norm;
@@ -884,7 +925,14 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     PBE_REQUIRE(dt > 0.0, PBE_E_INVALID, "pbe_transport_implicit: dt must be positive");
     PBE_REQUIRE(scheme == PBE_DIV_UPWIND || scheme == PBE_DIV_VANLEER || scheme == PBE_DIV_LIMITEDLINEAR, PBE_E_UNKNOWN_TYPE,
                 "pbe_transport_implicit: unknown divergence scheme id %d", scheme);
-    PBE_REQUIRE(m->ncoupled == 0, PBE_E_UNSUPPORTED, "pbe_transport_implicit: processor patches are not supported");
+    const bool decomposed = m->global_ncells > 0; // pbe_mesh_set_halo_plan: the ranks solve ONE system together
+    PBE_REQUIRE(m->ncoupled == 0 || decomposed, PBE_E_UNSUPPORTED,
+                "pbe_transport_implicit: the mesh has processor patches but no halo plan (pbe_mesh_set_halo_plan)");
+    PBE_REQUIRE(!decomposed || m->ctx->comm != nullptr, PBE_E_INVALID,
+                "pbe_transport_implicit: decomposed mesh, but the context has no communicator (pbe_comm_init)");
+    PBE_REQUIRE(!decomposed || scheme == PBE_DIV_UPWIND, PBE_E_UNSUPPORTED,
+                "pbe_transport_implicit: decomposed meshes are solved for Gauss upwind only (the limited schemes' weights "
+                "on processor patches need the neighbour's gradient)");
     pbe_fvm_controls ctl = {1.0e-5, 0.0, 1, 1000, 0.0, PBE_FVM_SOLVER_AUTO};
     if (controls) ctl = *controls;
     PBE_REQUIRE(ctl.tolerance >= 0.0 && ctl.rel_tol >= 0.0 && ctl.max_iter >= 1 && ctl.min_iter >= 0, PBE_E_INVALID,
@@ -908,6 +956,8 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     int solver = ctl.solver;
     if (!lim && solver == PBE_FVM_SOLVER_AUTO) solver = PBE_FVM_SOLVER_JACOBI;
     const bool may_bicg = solver != PBE_FVM_SOLVER_JACOBI;
+    PBE_REQUIRE(!decomposed || !may_bicg, PBE_E_UNSUPPORTED,
+                "pbe_transport_implicit: decomposed meshes are solved by the Jacobi iteration only (solver %d asked)", solver);
     PBE_REQUIRE(!lim || m->imp_W <= 8, PBE_E_UNSUPPORTED,
                 "pbe_transport_implicit: limited schemes on cells with more than 8 faces (%d) are not built", m->imp_W);
     PBE_REQUIRE(!lim || (m->d_Sf && m->d_C && m->d_w), PBE_E_INVALID,
@@ -975,6 +1025,31 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     q.sc = (FieldSc *)m->imp_small;
     q.partial = (double *)((char *)m->imp_small + (size_t)nfields * sizeof(FieldSc));
     q.est = (unsigned long long *)(q.partial + (size_t)nfields * kNS * Gs);
+    q.nc_global = decomposed ? m->global_ncells : nc;
+    q.coupled0 = m->coupled0, q.ncpl = m->ncoupled;
+    double *halo_send = nullptr, *halo_recv = nullptr;
+    if (decomposed) {
+        const size_t hneed = (size_t)2 * nfields * std::max<int64_t>(m->ncoupled, 1) + (size_t)nfields * kNS;
+        if (m->imp_halo_doubles < hneed) {
+            PBE_CUDA(cudaStreamSynchronize(st));
+            cudaFree(m->imp_halo);
+            m->imp_halo = nullptr;
+            m->imp_halo_doubles = 0;
+            PBE_CUDA(cudaMalloc((void **)&m->imp_halo, hneed * sizeof(double)));
+            m->imp_halo_doubles = hneed;
+        }
+        halo_send = m->imp_halo;
+        halo_recv = halo_send + (size_t)nfields * std::max<int64_t>(m->ncoupled, 1);
+        q.gsum = halo_recv + (size_t)nfields * std::max<int64_t>(m->ncoupled, 1);
+    }
+    // this rank's values along its processor patches -> the neighbours' halo rows, and theirs into ours
+    auto exchange = [&](const double *field, int64_t fstride) -> int {
+        if (!decomposed || m->ncoupled == 0) return PBE_OK;
+        int e = pbe_gather_cells(m->ctx, nfields, fstride, field, m->ncoupled, m->d_send_cells, halo_send, m->ncoupled, st);
+        if (e != PBE_OK) return e;
+        return pbe_halo_exchange(m->ctx, (int)m->halo_peer.size(), m->halo_peer.data(), m->halo_off.data(), m->halo_cnt.data(),
+                                 nfields, halo_send, m->ncoupled, halo_recv, m->ncoupled, st);
+    };
     q.rdt = 1.0 / dt, q.relax = ctl.relaxation, q.tol = ctl.tolerance, q.rel_tol = ctl.rel_tol;
     q.min_iter = ctl.min_iter, q.max_iter = ctl.max_iter;
     // fields per CTA of the row-holding kernels: enough CTAs to fill the machine, rows amortised over many fields
@@ -985,9 +1060,18 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     const dim3 grid_s((unsigned)Gs, (unsigned)((nfields + q.chunk - 1) / q.chunk)), grid_p((unsigned)Gp, (unsigned)nfields);
     const int W = q.W <= 8 ? q.W : 0;
     int64_t launches = 0;
+    int frc = PBE_OK;
     auto finalize = [&](int phase, int G) {
-        imp_finalize_kernel<<<nfields, kBlock, 0, st>>>(q, phase, G);
-        ++launches;
+        if (!decomposed) {
+            imp_finalize_kernel<<<nfields, kBlock, 0, st>>>(q, phase, G, 0);
+            ++launches;
+            return;
+        }
+        imp_finalize_kernel<<<nfields, kBlock, 0, st>>>(q, phase, G, 1);
+        const int e = pbe_reduce_diagnostics(m->ctx, nfields * kNS, q.gsum, 0, nullptr, 0, nullptr, st); // gSum
+        if (e != PBE_OK && frc == PBE_OK) frc = e;
+        imp_finalize_kernel<<<nfields, kBlock, 0, st>>>(q, phase, G, 2);
+        launches += 2;
     };
     auto spmv = [&](int mode) {
         if (q.wface) {
@@ -1071,6 +1155,9 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     imp_xsum_kernel<<<grid_p, kBlock, 0, st>>>(q);
     ++launches;
     finalize(PH_XSUM, Gp);
+    rc = exchange(psi, stride); // psi0 across the processor patches, for b - A x0
+    if (rc != PBE_OK) return rc;
+    q.halo_x = (decomposed && m->ncoupled) ? halo_recv : nullptr;
     if (lim && jac) {
         PBE_IMP_W8(imp_lim_init_kernel, PBE_IMP_COMMA true)
     } else if (lim) {
@@ -1089,6 +1176,9 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
         // device never waits for the host.  Converged fields are frozen on the device (their state is not 0), hence the
         // one iteration queued past the end changes nothing.
         auto issue = [&](int slot) -> int {
+            const int e = exchange(q.p, nc); // z across the processor patches
+            if (e != PBE_OK) return e;
+            q.halo_z = (decomposed && m->ncoupled) ? halo_recv : nullptr;
             if (lim) {
                 const size_t smem = (size_t)2 * 2 * W * kBlock * sizeof(double);
                 const void *fn = W == 4 ? (const void *)imp_lim_jacobi_kernel<4>
@@ -1144,6 +1234,7 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
 #undef PBE_IMP_WL
 #undef PBE_IMP_W8
     m->ctx->launches += launches;
+    if (rc == PBE_OK) rc = frc;
     if (rc != PBE_OK) return rc;
     PBE_CUDA(cudaGetLastError());
     if (perf)
@@ -1154,5 +1245,38 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
                     "pbe_transport_implicit: field %d diverged (%s, residual %g -> %g after %d iterations): the matrix is "
                     "not diagonally dominant at this time step; ask for PBE_FVM_SOLVER_BICGSTAB or reduce deltaT",
                     k, jac ? "Jacobi" : "BiCGStab", host[k].res0, host[k].res, host[k].iters);
+    return PBE_OK;
+}
+
+extern "C" int pbe_mesh_set_halo_plan(pbe_mesh *m, int nneigh, const int *peer, const int64_t *off, const int64_t *cnt,
+                                      const int32_t *send_cells, int64_t global_ncells) {
+    PBE_REQUIRE(m != nullptr && nneigh >= 0 && global_ncells >= m->ncells, PBE_E_INVALID,
+                "pbe_mesh_set_halo_plan: bad argument (global cells %lld, local %lld)", (long long)global_ncells,
+                (long long)(m ? m->ncells : 0));
+    PBE_REQUIRE(nneigh == 0 || (peer && off && cnt), PBE_E_INVALID, "pbe_mesh_set_halo_plan: NULL plan arrays");
+    PBE_REQUIRE(m->ncoupled == 0 || send_cells != nullptr, PBE_E_INVALID, "pbe_mesh_set_halo_plan: NULL send_cells");
+    int64_t covered = 0;
+    for (int q = 0; q < nneigh; ++q) {
+        PBE_REQUIRE(off[q] >= 0 && cnt[q] >= 0 && off[q] + cnt[q] <= m->ncoupled, PBE_E_INVALID,
+                    "pbe_mesh_set_halo_plan: neighbour %d covers faces [%lld, %lld) of %lld coupled faces", q, (long long)off[q],
+                    (long long)(off[q] + cnt[q]), (long long)m->ncoupled);
+        covered += cnt[q];
+    }
+    PBE_REQUIRE(covered == m->ncoupled, PBE_E_INVALID,
+                "pbe_mesh_set_halo_plan: the neighbours cover %lld of the %lld coupled faces (pbe_mesh_set_coupled first)",
+                (long long)covered, (long long)m->ncoupled);
+    for (int64_t j = 0; j < m->ncoupled; ++j)
+        PBE_REQUIRE(send_cells[j] >= 0 && send_cells[j] < m->ncells, PBE_E_INVALID, "pbe_mesh_set_halo_plan: send cell out of range");
+    DeviceGuard g(m->ctx->device);
+    cudaFree(m->d_send_cells);
+    m->d_send_cells = nullptr;
+    if (m->ncoupled) {
+        PBE_CUDA(cudaMalloc((void **)&m->d_send_cells, (size_t)m->ncoupled * sizeof(int32_t)));
+        PBE_CUDA(cudaMemcpy(m->d_send_cells, send_cells, (size_t)m->ncoupled * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    m->halo_peer.assign(peer, peer + nneigh);
+    m->halo_off.assign(off, off + nneigh);
+    m->halo_cnt.assign(cnt, cnt + nneigh);
+    m->global_ncells = global_ncells;
     return PBE_OK;
 }

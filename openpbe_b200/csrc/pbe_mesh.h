@@ -50,4 +50,13 @@ struct pbe_mesh {
     void *imp_pinned = nullptr; // host mirror of the per-field scalars
     size_t imp_pinned_bytes = 0;
     cudaEvent_t imp_ev[2] = {nullptr, nullptr};
+    // decomposed solve (pbe_mesh_set_halo_plan): neighbour q = rank halo_peer[q] shares the coupled faces
+    // [halo_off[q], halo_off[q] + halo_cnt[q]) (indices into the coupled range); d_send_cells [ncoupled]: this rank's cell
+    // on every coupled face
+    std::vector<int> halo_peer;
+    std::vector<int64_t> halo_off, halo_cnt;
+    int32_t *d_send_cells = nullptr;
+    int64_t global_ncells = 0;
+    double *imp_halo = nullptr; // send [nfields][ncoupled] | recv [nfields][ncoupled]
+    size_t imp_halo_doubles = 0;
 };

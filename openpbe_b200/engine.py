@@ -713,6 +713,17 @@ class Mesh:
             C.byref(ctl), _ptr(out), C.cast(perf, C.c_void_p), _stream_ptr(psi.device)))
         return out, [(p.initial_residual, p.final_residual, p.iterations, p.state) for p in perf]
 
+    def set_halo_plan(self, neighbours, send_cells, global_ncells: int):
+        """The decomposed implicit solve (pbe_mesh_set_halo_plan): neighbours = [(rank, first coupled face, count)] as
+        sharding.partition_mesh gives them, send_cells = this rank's cell on every coupled face."""
+        import numpy as np
+        peer = np.ascontiguousarray([q[0] for q in neighbours], dtype=np.int32)
+        off = np.ascontiguousarray([q[1] for q in neighbours], dtype=np.int64)
+        cnt = np.ascontiguousarray([q[2] for q in neighbours], dtype=np.int64)
+        sc = np.ascontiguousarray(send_cells, dtype=np.int32)
+        capi.check(capi.lib().pbe_mesh_set_halo_plan(self._h, len(neighbours), peer.ctypes.data, off.ctypes.data,
+                                                     cnt.ctypes.data, sc.ctypes.data, int(global_ncells)))
+
     def set_coupled(self, first_boundary_face: int, count: int):
         """Mark boundary faces [first, first+count) as processor-patch faces (decomposed mesh)."""
         capi.check(capi.lib().pbe_mesh_set_coupled(self._h, int(first_boundary_face), int(count)))

@@ -453,3 +453,143 @@ def test_resident_qmom_correct_with_the_implicit_solve(ctx, oracle):
     want = np.maximum(fvm.solve(tm, tm["phi"], dt, f["m"], S=S_dev, scheme="Gauss vanLeer"), 1e-15)
     assert np.all(np.abs(st2.download().numpy() - want) <= 1e-10 * np.abs(want).max(axis=1, keepdims=True))
     st2.close(); st.close(); mesh.close(); q.close()
+
+
+# ---- decomposed meshes: the ranks solve ONE system (halo exchange of z per sweep, all-reduced sums) ---------------------
+def _periodic_pair(nx, ny, nz, vel):
+    """A block whose z- / z+ patches are processor patches towards ITSELF (send_cells = the cell across the periodic
+    link), and the same domain as one global mesh with the periodic links as internal faces."""
+    m = synthetic.block_mesh(nx, ny, nz, velocity=vel)
+    ps = m["patch_start"]
+    ni = m["owner"].size
+    zlo, zhi = np.arange(ps[4], ps[5]), np.arange(ps[5], ps[6])
+    bot, top = m["boundary_owner"][zlo], m["boundary_owner"][zhi]
+    assert np.array_equal(bot + nx * ny * (nz - 1), top)
+    local = dict(m)
+    local["coupled"] = (int(ps[4]), int(ps[6] - ps[4]))
+    local["send_cells"] = np.concatenate([top, bot]).astype(np.int32)  # what lies ACROSS each coupled face
+    keep = np.arange(0, ps[4])
+    glob = {"owner": np.concatenate([m["owner"], bot]), "neighbour": np.concatenate([m["neighbour"], top]),
+            "boundary_owner": m["boundary_owner"][keep], "vcell": m["vcell"],
+            "phi": np.concatenate([m["phi"][:ni], m["phi"][ni + zlo], m["phi"][ni + keep]])}
+    return local, glob
+
+
+def _one_rank_comm(c):
+    import ctypes as C
+    from openpbe_b200 import capi
+    ident = C.create_string_buffer(128)
+    capi.check(capi.lib().pbe_comm_unique_id(ident))
+    capi.check(capi.lib().pbe_comm_init(c.handle, 1, 0, ident))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("psib", [False, True])
+def test_device_implicit_decomposed_path_on_one_rank(psib):
+    """The whole decomposed machinery on ONE device: a one-rank NCCL communicator, a block that is its own neighbour
+    across z (periodic), so that every sweep packs the processor-patch values, exchanges them (ncclSend / ncclRecv to
+    itself), reads them as extra columns of the rows, and all-reduces the sums -- against the direct solve of the
+    periodic domain as one mesh."""
+    from openpbe_b200 import capi, engine
+    rng = np.random.default_rng(20)
+    shape, vel = (9, 7, 6), (0.4, -0.3, 1.0)
+    local, glob = _periodic_pair(*shape, vel)
+    nc = 9 * 7 * 6
+    K = 4
+    psi = fields(rng, K, nc)
+    S = rng.normal(size=psi.shape) * 0.1
+    dt = 1.5 / sum(abs(v) * n for v, n in zip(vel, shape))
+    nb = local["boundary_owner"].size
+    pb_local = rng.uniform(0.1, 2.0, size=(K, nb)) if psib else None
+    pb_glob = None if pb_local is None else pb_local[:, :local["coupled"][0]]
+    want = fvm.solve(glob, glob["phi"], dt, psi, S=S, psi_b=pb_glob)
+    assert np.abs(want - fvm.solve(local, local["phi"], dt, psi, S=S, psi_b=pb_local)).max() > 1e-3  # the links matter
+    c = engine.Context(0)
+    _one_rank_comm(c)
+    mesh = engine.Mesh(c, local["owner"], local["neighbour"], local["boundary_owner"], local["vcell"])
+    mesh.set_coupled(*local["coupled"])
+    with pytest.raises(capi.PbeError, match="halo plan"):
+        mesh.transport_implicit(T(psi), T(local["phi"]), dt)
+    mesh.set_halo_plan([(0, 0, local["coupled"][1])], local["send_cells"], nc)
+    got, perf = mesh.transport_implicit(T(psi), T(local["phi"]), dt, S=T(S), psi_b=None if pb_local is None else T(pb_local),
+                                        tolerance=1e-13)
+    got = got.cpu().numpy()
+    assert all(p[3] == 1 for p in perf)
+    assert np.all(np.abs(got - want).sum(axis=1) <= 1e-10 * np.abs(want).sum(axis=1))
+    for k in range(K):
+        A, b = fvm.assemble(glob, glob["phi"], dt, psi[k], S=S[k], psi_b=None if pb_glob is None else pb_glob[k])
+        assert perf[k][0] == pytest.approx(fvm.residual(A, b, psi[k]), rel=1e-9)
+    with pytest.raises(capi.PbeError, match="Jacobi iteration only"):
+        mesh.transport_implicit(T(psi), T(local["phi"]), dt, solver="bicgstab")
+    mesh.close()
+    capi.check(capi.lib().pbe_comm_destroy(c.handle))
+    c.close()
+
+
+def _implicit_rank(rank, world, port, out):
+    import os
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from openpbe_b200 import capi, engine, sharding
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)  # only to hand the NCCL id around and to gather
+    ident = C.create_string_buffer(128)
+    if rank == 0:
+        capi.check(capi.lib().pbe_comm_unique_id(ident))
+    box = [bytes(ident.raw)]
+    dist.broadcast_object_list(box, src=0)
+    ident = C.create_string_buffer(box[0], 128)
+    c = engine.Context(rank)
+    capi.check(capi.lib().pbe_comm_init(c.handle, world, rank, ident))
+    rng = np.random.default_rng(21)
+    g = synthetic.block_mesh(10, 8, 12, velocity=(0.4, -0.3, 1.0))
+    nc = 10 * 8 * 12
+    psi = fields(rng, 5, nc)
+    S = rng.normal(size=psi.shape) * 0.1
+    dt = 1.2 / (0.4 * 10 + 0.3 * 8 + 1.0 * 12)
+    p = sharding.partition_mesh(g, rank, world)
+    lo, hi = p["cell_range"]
+    dev = torch.device(f"cuda:{rank}")
+    D = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+    mesh = engine.Mesh(c, p["owner"], p["neighbour"], p["boundary_owner"], p["vcell"])
+    mesh.set_coupled(*p["coupled"])
+    mesh.set_halo_plan(p["neighbours"], p["send_cells"], nc)
+    got, perf = mesh.transport_implicit(D(psi[:, lo:hi]), D(p["phi"]), dt, S=D(S[:, lo:hi]), tolerance=1e-13)
+    parts = [None] * world
+    dist.all_gather_object(parts, (lo, hi, got.cpu().numpy(), perf))
+    if rank == 0:
+        full = np.empty_like(psi)
+        for a, b, v, _ in parts:
+            full[:, a:b] = v
+        np.save(out, full)
+        assert all(pp == parts[0][3] for _, _, _, pp in parts), "the ranks disagree about residuals / iterations"
+        assert all(q[3] == 1 for q in parts[0][3])
+    dist.barrier()
+    mesh.close()
+    capi.check(capi.lib().pbe_comm_destroy(c.handle))
+    c.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_device_implicit_two_ranks_solve_one_system(tmp_path):
+    """two GPUs, two sub-domains of one block (sharding.partition_mesh), NCCL through the C ABI: the gathered result
+    is the direct solution of the undecomposed mesh"""
+    import os
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2); the one-rank test above covers the same code on one")
+    out = str(tmp_path / "imp2.npy")
+    port = 32500 + (os.getpid() % 2000)
+    mp.spawn(_implicit_rank, args=(2, port, out), nprocs=2, join=True)
+    rng = np.random.default_rng(21)
+    g = synthetic.block_mesh(10, 8, 12, velocity=(0.4, -0.3, 1.0))
+    psi = fields(rng, 5, 960)
+    S = rng.normal(size=psi.shape) * 0.1
+    dt = 1.2 / (0.4 * 10 + 0.3 * 8 + 1.0 * 12)
+    want = fvm.solve(g, g["phi"], dt, psi, S=S)
+    got = np.load(out)
+    assert np.all(np.abs(got - want).sum(axis=1) <= 1e-10 * np.abs(want).sum(axis=1))
