@@ -874,6 +874,28 @@ __global__ void __launch_bounds__(kBlock) imp_finalize_kernel(const ImpParams q,
 
 } // namespace
 
+// Halo traffic of a sweep in ONE message per neighbour: the values along the processor patches are packed
+// neighbour-major ([neighbour][field][face]: contiguous per neighbour) and unpacked into the field-major halo rows the
+// sweeps read.  Face j of neighbour q (first face off_q, cnt_q faces) sits at nfields off_q + k cnt_q + (j - off_q).
+__global__ void __launch_bounds__(256) imp_halo_pack_kernel(int nfields, int64_t fstride, const double *__restrict__ field,
+                                                            int64_t ncpl, const int32_t *__restrict__ cells,
+                                                            const int64_t *__restrict__ qoff, const int64_t *__restrict__ qcnt,
+                                                            double *__restrict__ out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= ncpl) return;
+    const int64_t o = qoff[j], n = qcnt[j], base = (int64_t)nfields * o + (j - o);
+    const int32_t c = cells[j];
+    for (int k = blockIdx.y; k < nfields; k += gridDim.y) out[base + (int64_t)k * n] = __ldg(field + (size_t)k * fstride + c);
+}
+__global__ void __launch_bounds__(256) imp_halo_unpack_kernel(int nfields, int64_t ncpl, const int64_t *__restrict__ qoff,
+                                                              const int64_t *__restrict__ qcnt, const double *__restrict__ in,
+                                                              double *__restrict__ halo) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= ncpl) return;
+    const int64_t o = qoff[j], n = qcnt[j], base = (int64_t)nfields * o + (j - o);
+    for (int k = blockIdx.y; k < nfields; k += gridDim.y) halo[(size_t)k * ncpl + j] = in[base + (int64_t)k * n];
+}
+
 // every cell's faces as [W][ncells] slots in ascending face order (internal faces, then the patches' faces)
 static int build_slots(pbe_mesh *m) {
     if (m->imp_W >= 0) return PBE_OK;
@@ -1027,9 +1049,11 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     q.est = (unsigned long long *)(q.partial + (size_t)nfields * kNS * Gs);
     q.nc_global = decomposed ? m->global_ncells : nc;
     q.coupled0 = m->coupled0, q.ncpl = m->ncoupled;
-    double *halo_send = nullptr, *halo_recv = nullptr;
+    int64_t launches = 0;
+    double *halo_send = nullptr, *halo_stage = nullptr, *halo_recv = nullptr;
+    std::vector<int64_t> blk_off, blk_cnt; // the neighbours' blocks of the packed buffers
     if (decomposed) {
-        const size_t hneed = (size_t)2 * nfields * std::max<int64_t>(m->ncoupled, 1) + (size_t)nfields * kNS;
+        const size_t hneed = (size_t)3 * nfields * std::max<int64_t>(m->ncoupled, 1) + (size_t)nfields * kNS;
         if (m->imp_halo_doubles < hneed) {
             PBE_CUDA(cudaStreamSynchronize(st));
             cudaFree(m->imp_halo);
@@ -1039,16 +1063,27 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
             m->imp_halo_doubles = hneed;
         }
         halo_send = m->imp_halo;
-        halo_recv = halo_send + (size_t)nfields * std::max<int64_t>(m->ncoupled, 1);
+        halo_stage = halo_send + (size_t)nfields * std::max<int64_t>(m->ncoupled, 1);
+        halo_recv = halo_stage + (size_t)nfields * std::max<int64_t>(m->ncoupled, 1);
         q.gsum = halo_recv + (size_t)nfields * std::max<int64_t>(m->ncoupled, 1);
+        for (size_t i = 0; i < m->halo_peer.size(); ++i) {
+            blk_off.push_back(m->halo_off[i] * nfields);
+            blk_cnt.push_back(m->halo_cnt[i] * nfields);
+        }
     }
     // this rank's values along its processor patches -> the neighbours' halo rows, and theirs into ours
     auto exchange = [&](const double *field, int64_t fstride) -> int {
         if (!decomposed || m->ncoupled == 0) return PBE_OK;
-        int e = pbe_gather_cells(m->ctx, nfields, fstride, field, m->ncoupled, m->d_send_cells, halo_send, m->ncoupled, st);
+        const dim3 hg((unsigned)((m->ncoupled + 255) / 256), (unsigned)std::min(nfields, 16));
+        imp_halo_pack_kernel<<<hg, 256, 0, st>>>(nfields, fstride, field, m->ncoupled, m->d_send_cells, m->d_halo_qoff,
+                                                 m->d_halo_qcnt, halo_send);
+        // one ncclSend / ncclRecv per neighbour (a "field" of pbe_halo_exchange is then the neighbour's whole block)
+        const int e = pbe_halo_exchange(m->ctx, (int)m->halo_peer.size(), m->halo_peer.data(), blk_off.data(), blk_cnt.data(), 1,
+                                        halo_send, 0, halo_stage, 0, st);
         if (e != PBE_OK) return e;
-        return pbe_halo_exchange(m->ctx, (int)m->halo_peer.size(), m->halo_peer.data(), m->halo_off.data(), m->halo_cnt.data(),
-                                 nfields, halo_send, m->ncoupled, halo_recv, m->ncoupled, st);
+        imp_halo_unpack_kernel<<<hg, 256, 0, st>>>(nfields, m->ncoupled, m->d_halo_qoff, m->d_halo_qcnt, halo_stage, halo_recv);
+        launches += 2;
+        return PBE_OK;
     };
     q.rdt = 1.0 / dt, q.relax = ctl.relaxation, q.tol = ctl.tolerance, q.rel_tol = ctl.rel_tol;
     q.min_iter = ctl.min_iter, q.max_iter = ctl.max_iter;
@@ -1059,7 +1094,6 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     q.chunk = std::min(std::min(chunk, kMaxChunk), nfields);
     const dim3 grid_s((unsigned)Gs, (unsigned)((nfields + q.chunk - 1) / q.chunk)), grid_p((unsigned)Gp, (unsigned)nfields);
     const int W = q.W <= 8 ? q.W : 0;
-    int64_t launches = 0;
     int frc = PBE_OK;
     auto finalize = [&](int phase, int G) {
         if (!decomposed) {
@@ -1273,6 +1307,22 @@ extern "C" int pbe_mesh_set_halo_plan(pbe_mesh *m, int nneigh, const int *peer, 
     if (m->ncoupled) {
         PBE_CUDA(cudaMalloc((void **)&m->d_send_cells, (size_t)m->ncoupled * sizeof(int32_t)));
         PBE_CUDA(cudaMemcpy(m->d_send_cells, send_cells, (size_t)m->ncoupled * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    cudaFree(m->d_halo_qoff);
+    cudaFree(m->d_halo_qcnt);
+    m->d_halo_qoff = m->d_halo_qcnt = nullptr;
+    if (m->ncoupled) {
+        std::vector<int64_t> qo((size_t)m->ncoupled, -1), qc((size_t)m->ncoupled, 0);
+        for (int q = 0; q < nneigh; ++q)
+            for (int64_t j = off[q]; j < off[q] + cnt[q]; ++j) {
+                PBE_REQUIRE(qo[(size_t)j] < 0, PBE_E_INVALID, "pbe_mesh_set_halo_plan: coupled face %lld belongs to two neighbours",
+                            (long long)j);
+                qo[(size_t)j] = off[q], qc[(size_t)j] = cnt[q];
+            }
+        PBE_CUDA(cudaMalloc((void **)&m->d_halo_qoff, qo.size() * sizeof(int64_t)));
+        PBE_CUDA(cudaMalloc((void **)&m->d_halo_qcnt, qc.size() * sizeof(int64_t)));
+        PBE_CUDA(cudaMemcpy(m->d_halo_qoff, qo.data(), qo.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+        PBE_CUDA(cudaMemcpy(m->d_halo_qcnt, qc.data(), qc.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
     }
     m->halo_peer.assign(peer, peer + nneigh);
     m->halo_off.assign(off, off + nneigh);

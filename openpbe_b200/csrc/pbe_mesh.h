@@ -56,6 +56,7 @@ struct pbe_mesh {
     std::vector<int> halo_peer;
     std::vector<int64_t> halo_off, halo_cnt;
     int32_t *d_send_cells = nullptr;
+    int64_t *d_halo_qoff = nullptr, *d_halo_qcnt = nullptr; // per coupled face: its neighbour's first face and face count
     int64_t global_ncells = 0;
     double *imp_halo = nullptr; // send [nfields][ncoupled] | recv [nfields][ncoupled]
     size_t imp_halo_doubles = 0;

@@ -638,6 +638,8 @@ int pbe_mesh_destroy(pbe_mesh *m) {
     cudaFree(m->d_imp_face);
     cudaFree(m->imp_ws);
     cudaFree(m->d_send_cells);
+    cudaFree(m->d_halo_qoff);
+    cudaFree(m->d_halo_qcnt);
     cudaFree(m->imp_halo);
     cudaFree(m->imp_small);
     if (m->imp_pinned) cudaFreeHost(m->imp_pinned);
