@@ -129,3 +129,62 @@ def solve(mesh: dict, phi, dt, psi, *, S=None, psi_b=None, relaxation=0.0, schem
                         relaxation=relaxation, scheme=scheme)
         out[k] = spla.spsolve(A.tocsc(), b)
     return out
+
+
+def jacobi_decomposed(part: dict, dt, psi, S, exchange, allreduce, nc_global, tol=1e-13, max_iter=2000):
+    """The decomposed solve as the device runs it, restated for ONE rank of a partition (sharding.partition_mesh):
+    processor-patch faces are coupled -- w phi_b on the diagonal, (1 - w) phi_b times the value across the face off
+    it -- and every Jacobi sweep (x += z, z <- -D^-1 (R z + C z_halo)) starts with a halo exchange of z and ends with
+    the global residual sum.  exchange(field [K][nlocal]) -> [K][ncoupled] values across the coupled faces;
+    allreduce(array) -> the sum over the ranks.  Zero-gradient physical patches.  Returns (x, iterations, residuals)."""
+    own = np.asarray(part["owner"], dtype=np.int64)
+    nei = np.asarray(part["neighbour"], dtype=np.int64)
+    bown = np.asarray(part["boundary_owner"], dtype=np.int64)
+    V = np.asarray(part["vcell"], dtype=np.float64)
+    phi = np.asarray(part["phi"], dtype=np.float64)
+    ni = own.size
+    nphys, ncpl = part["coupled"]
+    w = (phi[:ni] >= 0).astype(np.float64)
+    lower = -w * phi[:ni]
+    upper = lower + phi[:ni]
+    diag = V / dt
+    diag = diag.copy()
+    np.subtract.at(diag, own, lower)
+    np.subtract.at(diag, nei, upper)
+    np.add.at(diag, bown[:nphys], phi[ni:ni + nphys])
+    phb = phi[ni + nphys:ni + nphys + ncpl]
+    lowb = -(phb >= 0).astype(np.float64) * phb
+    cfb = lowb + phb  # multiplies the value across the face
+    cells_b = bown[nphys:nphys + ncpl]
+    np.subtract.at(diag, cells_b, lowb)
+
+    def offd(f, halo):  # [K][n] -> R f + C halo
+        out = np.zeros_like(f)
+        for k in range(f.shape[0]):
+            np.add.at(out[k], own, upper * f[k][nei])
+            np.add.at(out[k], nei, lower * f[k][own])
+            np.add.at(out[k], cells_b, cfb * halo[k])
+        return out
+
+    a1 = diag.copy()
+    np.add.at(a1, own, upper)
+    np.add.at(a1, nei, lower)
+    np.add.at(a1, cells_b, cfb)
+    x = np.array(psi, dtype=np.float64, copy=True)
+    b = x * V / dt + (0.0 if S is None else S * V)
+    Ax = diag * x + offd(x, exchange(x))
+    xbar = allreduce(x.sum(axis=1)) / nc_global
+    pA = xbar[:, None] * a1[None, :]
+    norm = allreduce((np.abs(Ax - pA) + np.abs(b - pA)).sum(axis=1)) + 1.0e-20
+    r = b - Ax
+    res0 = allreduce(np.abs(r).sum(axis=1)) / norm
+    z = r / diag
+    res, it = res0, 0
+    while it < max_iter and np.any(res >= tol):
+        halo = exchange(z)
+        x += z
+        rz = -offd(z, halo)
+        res = allreduce(np.abs(rz).sum(axis=1)) / norm
+        z = rz / diag
+        it += 1
+    return x, it, (res0, res)
