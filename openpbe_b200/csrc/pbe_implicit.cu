@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(kBlock) imp_p_kernel(const ImpParams q) {
 // Jacobi in correction form: x_{k+1} = x_k + z_k, z_{k+1} = -D^-1 R z_k (R = the off-diagonal part), so that
 // D z_{k+1} = b - A x_{k+1} is the CURRENT iterate's residual: sum |D z_{k+1}|.  The matrix is column-dominant (column
 // sums = V / dt + boundary outflow), hence the residual's L1 norm contracts at every step.  z_k in p, z_{k+1} in v.
-template <int W>
+template <int W, bool HALO>
 __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
     __shared__ double wsum[kMaxChunk][kBlock / 32];
     const int k0 = blockIdx.y * q.chunk, kend = min(q.nfields, k0 + q.chunk);
@@ -427,15 +427,27 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
             asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
                          : "memory");
         };
+        // Addresses: one base pointer per field (uniform) + per-thread BYTE offsets computed once -- the compiler
+        // otherwise rebuilds k nc + col in 64 bits for every slot and field (6 instructions per gather: the sweep was
+        // issue-bound, ncu: issue slots 79 % busy, DRAM 49 %).
+        long long off[W];
+#pragma unroll
+        for (int s = 0; s < W; ++s) off[s] = (long long)R.col[s] * 8;
+        const long long c8 = (long long)c * 8;
         double mine_n = 0.0, x_n = 0.0;
         auto issue = [&](int kk, int par) {
             if (kk < kend) {
-                const double *zin = q.p + (size_t)kk * q.nc;
-                const double *zh = q.halo_z ? q.halo_z + (size_t)kk * q.ncpl : nullptr;
+                const char *zb = reinterpret_cast<const char *>(q.p + (size_t)kk * q.nc);
+                const char *xb = reinterpret_cast<const char *>(q.x + (size_t)kk * q.stride);
+                // (the choice between the field and the halo row costs ~10 instructions per slot and field: only
+                // decomposed meshes pay it)
+                const double *zh = HALO ? q.halo_z + (size_t)kk * q.ncpl : nullptr;
 #pragma unroll
-                for (int s = 0; s < W; ++s) cp8(&stage[par][s][threadIdx.x], col_src(zin, zh, R.col[s]));
-                mine_n = __ldg(zin + c);
-                x_n = q.x[(size_t)kk * q.stride + c];
+                for (int s = 0; s < W; ++s)
+                    cp8(&stage[par][s][threadIdx.x], HALO ? col_src(reinterpret_cast<const double *>(zb), zh, R.col[s])
+                                                          : reinterpret_cast<const double *>(zb + off[s]));
+                mine_n = __ldg(reinterpret_cast<const double *>(zb + c8));
+                x_n = *reinterpret_cast<const double *>(xb + c8);
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
         };
@@ -444,6 +456,7 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
         while (k < kend) {
             const int kn = next_active(k + 1);
             const double mine = mine_n, xv = x_n;
+            char *xo = reinterpret_cast<char *>(q.x + (size_t)k * q.stride), *vo = reinterpret_cast<char *>(q.v + (size_t)k * q.nc);
             issue(kn, par ^ 1);
             asm volatile("cp.async.wait_group 1;" ::: "memory");
             double acc = 0.0;
@@ -451,8 +464,8 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
             for (int s = 0; s < W; ++s) acc = fma(R.cf[s], stage[par][s][threadIdx.x], acc);
             const double rz = -acc;
             if (valid) {
-                __stcs(q.x + (size_t)k * q.stride + c, xv + mine);
-                __stcs(q.v + (size_t)k * q.nc + c, R.dinv * rz);
+                __stcs(reinterpret_cast<double *>(xo + c8), xv + mine);
+                __stcs(reinterpret_cast<double *>(vo + c8), R.dinv * rz);
             }
             const double sum = warp_sum(valid ? fabs(rz) : 0.0);
             if (lane == 0) wsum[k - k0][wid] = sum;
@@ -463,7 +476,7 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
         for (; k < kend; k = next_active(k + 1)) {
             const size_t o = (size_t)k * q.nc;
             const double *zin = q.p + o;
-            const double rz = -offdiag<W>(q, c, false, R, zin, q.halo_z ? q.halo_z + (size_t)k * q.ncpl : nullptr);
+            const double rz = -offdiag<W>(q, c, false, R, zin, HALO ? q.halo_z + (size_t)k * q.ncpl : nullptr);
             if (valid) {
                 q.x[(size_t)k * q.stride + c] += zin[c];
                 q.v[o + c] = R.dinv * rz;
@@ -1223,8 +1236,10 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
                 case 6: imp_lim_jacobi_kernel<6><<<grid_s, kBlock, smem, st>>>(q); break;
                 default: imp_lim_jacobi_kernel<8><<<grid_s, kBlock, smem, st>>>(q); break;
                 }
+            } else if (q.halo_z) {
+                PBE_IMP_W(imp_jacobi_kernel, PBE_IMP_COMMA true)
             } else {
-                PBE_IMP_W(imp_jacobi_kernel)
+                PBE_IMP_W(imp_jacobi_kernel, PBE_IMP_COMMA false)
             }
             ++launches;
             finalize(PH_J, Gs);
