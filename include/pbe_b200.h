@@ -336,7 +336,8 @@ typedef struct pbe_fvm_perf {
 /* psi, S, psi_out DEVICE [nfields][stride] (psi_out must not alias psi); phi DEVICE [internal + boundary faces];
  * psi_b DEVICE [nfields][stride_b] fixed patch values, or NULL = zero-gradient on every boundary face; controls NULL =
  * {1e-5, 0, 1, 1000, 0, AUTO}; perf HOST [nfields] or NULL.  Synchronous on return (the iteration count is data dependent).
- * Processor patches: see pbe_mesh_set_halo_plan below (PBE_E_UNSUPPORTED without a plan). */
+ * Processor patches: see pbe_mesh_set_halo_plan below (PBE_E_UNSUPPORTED without a plan).  The solver's vectors live on
+ * the mesh handle: calls on one mesh must not overlap (use one mesh handle per concurrent solve). */
 int pbe_transport_implicit(pbe_mesh *mesh, int scheme, int nfields, int64_t stride, const double *psi,
                            const double *phi, const double *psi_b, int64_t stride_b, const double *S, double dt,
                            const pbe_fvm_controls *controls, double *psi_out, pbe_fvm_perf *perf, void *cuda_stream);
