@@ -12,16 +12,22 @@
 //   * the reference solves field after field (100 classes = 100 matrices assembled and solved one by one) with PBiCG +
 //     DILU or symGaussSeidel sweeps: sequential recurrences along the cell numbering;
 //   * for `Gauss upwind` ALL fields share ONE matrix (it depends on phi, V and dt only), so the fields are solved
-//     together: a BiCGStab whose vectors are [nfields][ncells] arrays, every field with its own alpha / omega / beta /
-//     residual, preconditioned by the diagonal (the matrix is an M-matrix, column-dominant by V / dt).  One thread per
-//     cell keeps the cell's row (neighbour columns and coefficients x inverse diagonals) in registers and sweeps a chunk
-//     of fields: the row is read once per chunk, the vectors stream through HBM.
-//   * reductions (dot products, L1 norms) are two-stage and ordered: per-CTA partials, then one CTA per field adds them
-//     in a fixed order and updates the field's scalars on the device.  The host only reads the scalars back once per
-//     iteration to decide whether any field is still active.
-//
-// HBM per iteration and cell-field (hex mesh): matrix-vector products 2 x (8 read + 8 written; neighbour gathers hit
-// L1 / L2), s = r - alpha v 24 B, x / r update 56 B, p update 32 B: ~144 B = 6 x the explicit update's 24 B.
+//     together, every field with its own scalars, residual and stopping point.  One thread per cell keeps the cell's
+//     row (neighbour columns and coefficients) in registers and sweeps a chunk of fields: the row is read once per
+//     chunk, the vectors stream through HBM.  Two iterations: JACOBI in correction form (x += z, z <- -D^-1 R z; D z is
+//     the current residual, so the stopping test costs nothing; the matrix is an M-matrix, column-dominant by V / dt:
+//     the residual's L1 norm contracts every sweep) at 32 B per cell-field and sweep, and a diagonally preconditioned
+//     BiCGStab at ~150 B per iteration.  Upwind convection makes the matrix triangular along the flow, so either needs
+//     about as many matrix-vector products as the solution travels cells in dt: Jacobi won at every Courant number
+//     measured and is what AUTO takes.
+//   * the limited schemes of the reference's cases (Gauss vanLeer, Gauss limitedLinear 1) take their weights from the
+//     field being solved for: one matrix per field, rebuilt per sweep from phi and the field's face weights.
+//   * reductions (L1 norms, dot products) are two-stage and ordered: per-CTA partials, then one CTA per field adds them
+//     in a fixed order and updates the field's state on the device.  The host reads the states back one sweep BEHIND
+//     what it has queued, so the device never waits for it; converged fields are frozen on the device.
+//   * on a decomposed mesh the ranks solve ONE system: a processor-patch face is one more column of the row, read from
+//     a halo row that is exchanged before every sweep (one NCCL message per neighbour), and the sums are all-reduced
+//     before the states are updated -- all on the caller's stream.
 #include <algorithm>
 #include <cstdint>
 #include <cstdlib>
