@@ -39,10 +39,17 @@ using namespace pbe;
 
 namespace {
 
+// Where the next field's gathered values wait (sweep of the shared upwind matrix on one rank): 1 = in registers
+// (6 LDG per cell-field), 0 = in a per-thread shared-memory column filled by cp.async (6 LDGSTS + 6 LDS).  The sweep is
+// bound by the load-store path: 160^3 x 100 fields 3.74 ms per sweep with 0, 3.40 ms with 1 (50 fields per CTA).
+#ifndef PBE_IMP_REGSTAGE
+#define PBE_IMP_REGSTAGE 1
+#endif
+
 constexpr int kBlock = 256;
 constexpr int kPW = 4;    // cells per thread of the pointwise kernels
 constexpr int kNS = 3;    // sums per field and kernel, at most
-constexpr int kMaxChunk = 64; // fields per CTA of the row-holding kernels, at most
+constexpr int kMaxChunk = 128; // fields per CTA of the row-holding kernels, at most
 constexpr double kNormSmall = 1.0e-20; // lduMatrix::small_
 
 struct FieldSc { // one per field, on the device
@@ -440,6 +447,45 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
 #pragma unroll
         for (int s = 0; s < W; ++s) off[s] = (long long)R.col[s] * 8;
         const long long c8 = (long long)c * 8;
+#if PBE_IMP_REGSTAGE
+        if constexpr (!HALO) {
+            // the next field's gathers wait in registers instead of shared memory (6 LDG instead of 6 LDGSTS + 6 LDS
+            // per cell-field on the load-store pipe); the loads have a whole field's work to land
+            double gn[W], mine_n = 0.0, x_n = 0.0;
+            auto issue = [&](int kk) {
+                if (kk < kend) {
+                    const char *zb = reinterpret_cast<const char *>(q.p + (size_t)kk * q.nc);
+                    const char *xb = reinterpret_cast<const char *>(q.x + (size_t)kk * q.stride);
+#pragma unroll
+                    for (int s = 0; s < W; ++s) gn[s] = __ldg(reinterpret_cast<const double *>(zb + off[s]));
+                    mine_n = __ldg(reinterpret_cast<const double *>(zb + c8));
+                    x_n = *reinterpret_cast<const double *>(xb + c8);
+                }
+            };
+            issue(k);
+            while (k < kend) {
+                const int kn = next_active(k + 1);
+                double g[W];
+#pragma unroll
+                for (int s = 0; s < W; ++s) g[s] = gn[s];
+                const double mine = mine_n, xv = x_n;
+                char *xo = reinterpret_cast<char *>(q.x + (size_t)k * q.stride), *vo = reinterpret_cast<char *>(q.v + (size_t)k * q.nc);
+                issue(kn);
+                double acc = 0.0;
+#pragma unroll
+                for (int s = 0; s < W; ++s) acc = fma(R.cf[s], g[s], acc);
+                const double rz = -acc;
+                if (valid) {
+                    __stcs(reinterpret_cast<double *>(xo + c8), xv + mine);
+                    __stcs(reinterpret_cast<double *>(vo + c8), R.dinv * rz);
+                }
+                const double sum = warp_sum(valid ? fabs(rz) : 0.0);
+                if (lane == 0) wsum[k - k0][wid] = sum;
+                k = kn;
+            }
+        } else
+#endif
+        {
         double mine_n = 0.0, x_n = 0.0;
         auto issue = [&](int kk, int par) {
             if (kk < kend) {
@@ -477,6 +523,7 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
             if (lane == 0) wsum[k - k0][wid] = sum;
             k = kn;
             par ^= 1;
+        }
         }
     } else {
         for (; k < kend; k = next_active(k + 1)) {
@@ -1108,7 +1155,8 @@ int pbe_transport_implicit(pbe_mesh *m, int scheme, int nfields, int64_t stride,
     q.min_iter = ctl.min_iter, q.max_iter = ctl.max_iter;
     // fields per CTA of the row-holding kernels: enough CTAs to fill the machine, rows amortised over many fields
     static const int env_chunk = [] { const char *e = getenv("PBE_IMPLICIT_CHUNK"); return e ? atoi(e) : 0; }();
-    int chunk = env_chunk > 0 ? env_chunk : 32;
+    // 160^3 x 100, upwind sweep: 32 -> 3.67, 50 / 64 -> 3.40, 100 -> 3.42 ms; the limited sweeps (more registers) like 32
+    int chunk = env_chunk > 0 ? env_chunk : (lim ? 32 : 50);
     while (chunk > 4 && (int64_t)Gs * ((nfields + chunk - 1) / chunk) < 4 * (int64_t)m->ctx->sm_count) chunk /= 2;
     q.chunk = std::min(std::min(chunk, kMaxChunk), nfields);
     const dim3 grid_s((unsigned)Gs, (unsigned)((nfields + q.chunk - 1) / q.chunk)), grid_p((unsigned)Gp, (unsigned)nfields);
