@@ -186,6 +186,62 @@ __device__ __forceinline__ void sweep_regs(const TransportParams &p, int c, cons
     }
 }
 
+// The same sweep with the NEXT field's values (own, source, F gathered) already on their way into registers while the
+// current field is summed: the loads have a whole field's arithmetic to land, and nothing goes through shared memory
+// (F + 2 LDG per cell-field instead of F LDGSTS + F LDS + 2 LDG of the cp.async form below).  MEASURED SLOWER here --
+// 160^3 x 100: 3.19 ms against 2.55 ms (PBE_TRANSPORT_KERNEL=1): the update's arithmetic needs 80 registers with the
+// second set of values (three CTAs per SM), whereas the implicit sweep (pbe_implicit.cu), which gains 9 % from this
+// form, stays at 57.  Kept selectable for that comparison.
+template <int F, bool BND>
+__device__ __forceinline__ void sweep_ahead(const TransportParams &p, int c, const CellFaces<F> &cf, double V, double rV) {
+    const int k0 = blockIdx.y * p.chunk;
+    const int nk = min(p.nfields, k0 + p.chunk) - k0;
+    const double *row = p.psi + (size_t)k0 * p.stride;
+    const double *brow = BND ? p.psi_b + (size_t)k0 * p.stride_b : nullptr;
+    const double *srow = (p.S != nullptr) ? p.S + (size_t)k0 * p.stride : nullptr;
+    double *orow = p.out + (size_t)k0 * p.stride;
+    double thn[F], mine_n = 0.0, su_n = 0.0;
+    auto fetch = [&](int k) {
+        if (k < nk) {
+#pragma unroll
+            for (int s = 0; s < F; ++s) thn[s] = __ldg(slot_addr<F, BND>(cf, s, row, brow));
+            mine_n = __ldg(row + c);
+            if (srow != nullptr) {
+                su_n = __ldg(srow + c);
+                srow += p.stride;
+            }
+            row += p.stride;
+            if (BND) brow += p.stride_b;
+        }
+    };
+    fetch(0);
+    for (int k = 0; k < nk; ++k, orow += p.stride) {
+        double th[F];
+#pragma unroll
+        for (int s = 0; s < F; ++s) th[s] = thn[s];
+        const double mine = mine_n, Su = su_n;
+        fetch(k + 1);
+        double acc = 0.0;
+#pragma unroll
+        for (int s = 0; s < F; ++s) acc = add_slot<F, BND>(acc, cf, s, mine, th[s]);
+        __stcs(orow + c, updated(p, mine, Su, acc, V, rV));
+    }
+}
+
+template <int F>
+__global__ void __launch_bounds__(256, 3) transport_upwind_ahead_kernel(TransportParams p) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= p.ncells) return;
+    CellFaces<F> cf;
+    if (!load_cell_faces<F>(p, c, cf)) return;
+    const double V = __ldg(p.vcell + c);
+    const double rV = __ddiv_rn(1.0, V);
+    if (__any_sync(__activemask(), cf.bnd != 0u))
+        sweep_ahead<F, true>(p, c, cf, V, rV);
+    else
+        sweep_ahead<F, false>(p, c, cf, V, rV);
+}
+
 template <int F>
 __global__ void __launch_bounds__(256, PBE_TR_CTAS) transport_upwind_kernel(TransportParams p) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x; // 32-bit labels (pbe_mesh_create checks)
@@ -809,6 +865,7 @@ int pbe_transport_explicit_part(pbe_mesh *m, int scheme, int which, int nfields,
         };
 #define PBE_TR_ASYNC(F)                                                                      \
     switch (variant) {                                                                       \
+    case 1: transport_upwind_ahead_kernel<F><<<grid, 256, 0, st>>>(p); break;                \
     case 2: launch_async(transport_upwind_async_kernel<F, 2>, F, 2); break;                  \
     case 3: launch_async(transport_upwind_async_kernel<F, 3>, F, 3); break;                  \
     case 4: launch_async(transport_upwind_async_kernel<F, 4>, F, 4); break;                  \

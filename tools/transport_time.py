@@ -1,28 +1,28 @@
-"""Timing of the explicit transport update (row f2): python tools/transport_time.py [nx ny nz K]"""
-import os, sys, time
+"""Timing of the explicit upwind transport update: python tools/transport_time.py [n K reps]  (PBE_TRANSPORT_KERNEL, PBE_TRANSPORT_CHUNK)"""
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from openpbe_b200 import capi
-capi.LIB_PATH = os.environ.get('PBE_LIB', capi.LIB_PATH)  # A/B builds of the library
+capi.LIB_PATH = os.environ.get('PBE_LIB', capi.LIB_PATH)
 from openpbe_b200 import engine, synthetic
-
-nx, ny, nz, K = (int(a) for a in sys.argv[1:5]) if len(sys.argv) >= 5 else (160, 160, 160, 100)
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 160
+K = int(sys.argv[2]) if len(sys.argv) > 2 else 100
+reps = int(sys.argv[3]) if len(sys.argv) > 3 else 10
 ctx = engine.Context(0); dev = torch.device("cuda:0")
-t0 = time.time(); m = synthetic.block_mesh(nx, ny, nz, velocity=(1.0, 0.5, 0.25)); t1 = time.time()
-mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"]); t2 = time.time()
-nc = nx * ny * nz
-print(f"mesh {nx}x{ny}x{nz}: {nc} cells, generator {t1-t0:.1f} s, pbe_mesh_create {t2-t1:.1f} s, {mesh.info()}")
+m = synthetic.block_mesh(n, n, n, velocity=(1.0, 0.5, 0.25))
+mesh = engine.Mesh(ctx, m["owner"], m["neighbour"], m["boundary_owner"], m["vcell"])
+nc = n ** 3
 g = torch.Generator(device=dev); g.manual_seed(1)
 psi = torch.rand(K, nc, dtype=torch.float64, device=dev, generator=g)
 S = torch.rand(K, nc, dtype=torch.float64, device=dev, generator=g)
-out = torch.empty_like(psi)
-phi = torch.from_numpy(m["phi"]).to(dev)
-alg = nc * (24.0 * K + 8 + 6 * 8 + 3 * 8)
-for chunk in (os.environ.get("CHUNKS", "5,10,25,50,100").split(",")):
-    os.environ["PBE_TRANSPORT_CHUNK"] = chunk
-    for _ in range(2): mesh.transport_explicit(psi, phi, 1e-4, S=S, out=out)
-    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True); best = 1e9
-    for _ in range(5):
-        e0.record(); mesh.transport_explicit(psi, phi, 1e-4, S=S, out=out); e1.record(); torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    print(f"chunk {chunk}: {best:.3f} ms, {nc*K/best*1e3:.3e} cell-field-updates/s, algorithmic {alg/best/1e6:.0f} GB/s")
+out = torch.empty_like(psi); phi = torch.from_numpy(m["phi"]).to(dev)
+dt = 0.4 / (n * 1.75)
+for _ in range(3): mesh.transport_explicit(psi, phi, dt, S=S, out=out)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+e0.record()
+for _ in range(reps): mesh.transport_explicit(psi, phi, dt, S=S, out=out)
+e1.record(); torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / reps
+print(f"explicit upwind {n}^3 x {K} (kernel {os.environ.get('PBE_TRANSPORT_KERNEL', 'default')}, chunk {os.environ.get('PBE_TRANSPORT_CHUNK', 'default')}): "
+      f"{ms:.3f} ms, {24.0 * nc * K / ms / 1e6:.0f} GB/s, checksum {float(out.sum()):.12e}")
