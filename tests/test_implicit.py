@@ -544,8 +544,8 @@ def _one_rank_comm(c):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("psib", [False, True])
-def test_device_implicit_decomposed_path_on_one_rank(psib):
+@pytest.mark.parametrize("psib,relaxation", [(False, 0.0), (True, 0.0), (False, 0.8)])
+def test_device_implicit_decomposed_path_on_one_rank(psib, relaxation):
     """The whole decomposed machinery on ONE device: a one-rank NCCL communicator, a block that is its own neighbour
     across z (periodic), so that every sweep packs the processor-patch values, exchanges them (ncclSend / ncclRecv to
     itself), reads them as extra columns of the rows, and all-reduces the sums -- against the direct solve of the
@@ -562,8 +562,8 @@ def test_device_implicit_decomposed_path_on_one_rank(psib):
     nb = local["boundary_owner"].size
     pb_local = rng.uniform(0.1, 2.0, size=(K, nb)) if psib else None
     pb_glob = None if pb_local is None else pb_local[:, :local["coupled"][0]]
-    want = fvm.solve(glob, glob["phi"], dt, psi, S=S, psi_b=pb_glob)
-    assert np.abs(want - fvm.solve(local, local["phi"], dt, psi, S=S, psi_b=pb_local)).max() > 1e-3  # the links matter
+    want = fvm.solve(glob, glob["phi"], dt, psi, S=S, psi_b=pb_glob, relaxation=relaxation)  # relax(): coupled-patch rule
+    assert np.abs(want - fvm.solve(local, local["phi"], dt, psi, S=S, psi_b=pb_local, relaxation=relaxation)).max() > 1e-3
     c = engine.Context(0)
     _one_rank_comm(c)
     mesh = engine.Mesh(c, local["owner"], local["neighbour"], local["boundary_owner"], local["vcell"])
@@ -572,12 +572,13 @@ def test_device_implicit_decomposed_path_on_one_rank(psib):
         mesh.transport_implicit(T(psi), T(local["phi"]), dt)
     mesh.set_halo_plan([(0, 0, local["coupled"][1])], local["send_cells"], nc)
     got, perf = mesh.transport_implicit(T(psi), T(local["phi"]), dt, S=T(S), psi_b=None if pb_local is None else T(pb_local),
-                                        tolerance=1e-13)
+                                        tolerance=1e-13, relaxation=relaxation)
     got = got.cpu().numpy()
     assert all(p[3] == 1 for p in perf)
     assert np.all(np.abs(got - want).sum(axis=1) <= 1e-10 * np.abs(want).sum(axis=1))
     for k in range(K):
-        A, b = fvm.assemble(glob, glob["phi"], dt, psi[k], S=S[k], psi_b=None if pb_glob is None else pb_glob[k])
+        A, b = fvm.assemble(glob, glob["phi"], dt, psi[k], S=S[k], psi_b=None if pb_glob is None else pb_glob[k],
+                            relaxation=relaxation)
         assert perf[k][0] == pytest.approx(fvm.residual(A, b, psi[k]), rel=1e-9)
     with pytest.raises(capi.PbeError, match="Jacobi iteration only"):
         mesh.transport_implicit(T(psi), T(local["phi"]), dt, solver="bicgstab")
