@@ -448,7 +448,16 @@ __global__ void __launch_bounds__(kBlock) imp_jacobi_kernel(const ImpParams q) {
         for (int s = 0; s < W; ++s) off[s] = (long long)R.col[s] * 8;
         const long long c8 = (long long)c * 8;
 #if PBE_IMP_REGSTAGE
-        if constexpr (!HALO) {
+        // decomposed meshes: only the warps that hold a processor-patch cell need the halo row (and the per-slot choice of
+        // address); all others -- the bulk -- run the same loop as on one rank
+        bool warp_halo = false;
+        if constexpr (HALO) {
+            bool mine_halo = false;
+#pragma unroll
+            for (int s = 0; s < W; ++s) mine_halo |= R.col[s] < 0;
+            warp_halo = __any_sync(0xffffffffu, mine_halo);
+        }
+        if (!HALO || !warp_halo) {
             // the next field's gathers wait in registers instead of shared memory (6 LDG instead of 6 LDGSTS + 6 LDS
             // per cell-field on the load-store pipe); the loads have a whole field's work to land
             double gn[W], mine_n = 0.0, x_n = 0.0;
